@@ -1,0 +1,274 @@
+"""Thin Python host layer over the libfgs C ABI.
+
+Everything here is plumbing for tests and bench.py: it builds ctypes views of numpy arrays, calls the
+``extern "C"`` entry points of include/fgs.h and hands numpy arrays back. No scheduling arithmetic
+lives in Python; if libfgs.so or a CUDA device is missing the calls raise.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+
+
+class FgsError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libfgs error {code}: {msg}")
+        self.code = code
+        self.msg = msg
+
+
+def _ptr(a, ctype):
+    return a.ctypes.data_as(C.POINTER(ctype))
+
+
+def plugin_cfg(filter_plugins=("NodeResourcesFit", "FlexGPU"), score_plugins=(("FlexGPU", 1), ("NodeResourcesFit", 1)),
+               fit_strategy="LeastAllocated", fit_resources=(("cpu", 1), ("memory", 1)), fit_ignored_scalar_mask=0,
+               alloc_mode="Least", alloc_resources=(("cpu", 1 << 20), ("memory", 1))):
+    """Build an fgs_plugin_cfg the way a KubeSchedulerConfiguration profile would.
+
+    Plugin names are the reference's: "FlexGPU" (pkg/flexgpu/flex_gpu.go:17), "NodeResourcesFit",
+    "NodeResourcesAllocatable" (pkg/noderesources/allocatable.go:43). Resources are "cpu", "memory",
+    "ephemeral-storage", ("scalar", s) for slot s, or any other string for a name the scorer ignores.
+    """
+    ids = {"FlexGPU": L.FGS_PL_FLEXGPU, "NodeResourcesFit": L.FGS_PL_FIT, "NodeResourcesAllocatable": L.FGS_PL_ALLOCATABLE}
+
+    def res_id(r):
+        if r == "cpu":
+            return L.FGS_RES_CPU
+        if r == "memory":
+            return L.FGS_RES_MEM
+        if r == "ephemeral-storage":
+            return L.FGS_RES_EPH
+        if isinstance(r, tuple) and r[0] == "scalar":
+            return L.FGS_RES_SCALAR0 + int(r[1])
+        return L.FGS_RES_UNKNOWN
+
+    c = L.PluginCfg()
+    for k, name in enumerate(filter_plugins):
+        c.filter_mask |= ids[name]
+        c.filter_order[k] = ids[name]
+    c.weight_flex = c.weight_fit = c.weight_alloc = 1
+    for name, w in score_plugins:
+        c.score_mask |= ids[name]
+        if name == "FlexGPU":
+            c.weight_flex = w
+        elif name == "NodeResourcesFit":
+            c.weight_fit = w
+        else:
+            c.weight_alloc = w
+    c.fit_strategy = {"LeastAllocated": 0, "MostAllocated": 1}[fit_strategy]
+    c.fit_n_res = len(fit_resources)
+    for k, (r, w) in enumerate(fit_resources):
+        c.fit_res[k] = res_id(r)
+        c.fit_res_w[k] = w
+    c.fit_ignored_scalar_mask = fit_ignored_scalar_mask
+    c.alloc_mode = {"Least": 0, "Most": 1}.get(alloc_mode, 2)
+    c.alloc_n_res = len(alloc_resources)
+    for k, (r, w) in enumerate(alloc_resources):
+        c.alloc_res[k] = res_id(r)
+        c.alloc_res_w[k] = w
+    return c
+
+
+class Synth:
+    """Deterministic synthetic cluster; owns the object-level snapshot."""
+
+    DEFAULTS = dict(seed_nodes=0xF6500000, seed_pods=0xF6510000, n_nodes=1000, n_pending=1000, n_scalars=2, n_devices=8,
+                    max_existing_pods=24, pm_fractional=600, pm_whole=300, pm_nogpu=50, pm_degenerate=50, pm_missing_req=100,
+                    pm_init_ctr=100, pm_overhead=30, pm_two_ctrs=200, pm_extra_scalar=0, pm_quirk_nodes=20, pm_nongpu_nodes=0,
+                    pm_panic_nodes=0, pm_invalid_nodes=0, n_groups=0, min_member_lo=4, min_member_hi=64, pm_groups_placed=400,
+                    pm_groups_short=50, pm_neg_left_nodes=10, n_namespaces=0, pm_pods_without_eq=50, n_nominated=0)
+
+    def __init__(self, **kw):
+        lib = L.load()
+        p = L.SynthParams()
+        vals = dict(self.DEFAULTS)
+        vals.update(kw)
+        for k, v in vals.items():
+            setattr(p, k, v)
+        self.params = vals
+        h = C.c_void_p()
+        rc = lib.fgs_synth_create(C.byref(p), C.byref(h))
+        if rc != 0:
+            raise FgsError(rc, "fgs_synth_create: invalid parameters")
+        self._h = h
+        self._lib = lib
+        self.snapshot = lib.fgs_synth_snapshot(h)
+        self.pending = lib.fgs_synth_pending(h)
+        self.nominated = lib.fgs_synth_nominated(h)
+        self.podgroups = lib.fgs_synth_podgroups(h)
+        self.quotas = lib.fgs_synth_quotas(h)
+
+    @property
+    def n_nodes(self):
+        return int(self.snapshot.contents.n_nodes)
+
+    @property
+    def n_pending(self):
+        return int(self.pending.contents.n_pods)
+
+    def close(self):
+        if self._h:
+            self._lib.fgs_synth_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Results:
+    def __init__(self, P):
+        self.feasible_count = np.zeros(P, np.int32)
+        self.selected_node = np.zeros(P, np.int32)
+        self.selected_score = np.zeros(P, np.int64)
+        self.pod_err = np.zeros(P, np.uint32)
+        self.feasible_bitmap = None
+        self.scores = None
+        self.words_per_row = 0
+        self.score_row_stride = 0
+
+    def feasible(self, n_nodes):
+        """bool [P][n_nodes] from the bitmap"""
+        bits = np.unpackbits(self.feasible_bitmap.view(np.uint8), axis=1, bitorder="little")
+        return bits[:, :n_nodes].astype(bool)
+
+
+class Engine:
+    """One libfgs engine = one GPU's shard of the node table."""
+
+    def __init__(self, device=0, n_scalars=2, node_index_base=0, total_nodes=0, seed=0x5EED, stream=None):
+        self._lib = L.load()
+        cfg = L.Config(device=device, n_scalars=n_scalars, node_index_base=node_index_base, total_nodes=total_nodes,
+                       select_seed=seed, stream=stream)
+        h = C.c_void_p()
+        rc = self._lib.fgs_create(C.byref(cfg), C.byref(h))
+        if rc != 0:
+            raise FgsError(rc, self._lib.fgs_last_error(None).decode())
+        self._h = h
+        self.n_nodes = 0
+        self.n_pods = 0
+        self._keep = []
+
+    def _check(self, rc):
+        if rc != 0:
+            raise FgsError(rc, self._lib.fgs_last_error(self._h).decode())
+
+    def close(self):
+        if self._h:
+            self._lib.fgs_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- configuration / upload ------------------------------------------------------------------
+    def set_plugins(self, cfg):
+        self._check(self._lib.fgs_set_plugins(self._h, C.byref(cfg)))
+
+    def pack_nodes(self, snapshot):
+        t = C.POINTER(L.NodeTable)()
+        self._check(self._lib.fgs_pack_nodes(self._h, snapshot, C.byref(t)))
+        return t
+
+    def pack_pods(self, podset):
+        t = C.POINTER(L.PodTable)()
+        self._check(self._lib.fgs_pack_pods(self._h, podset, C.byref(t)))
+        return t
+
+    def upload_nodes(self, table):
+        self._check(self._lib.fgs_upload_nodes(self._h, table))
+        self.n_nodes = int(table.contents.n_nodes)
+
+    def update_nodes(self, rows, dirty_idx):
+        idx = np.ascontiguousarray(dirty_idx, dtype=np.int64)
+        self._check(self._lib.fgs_update_nodes(self._h, rows, _ptr(idx, C.c_int64)))
+
+    # -- evaluation ----------------------------------------------------------------------------------
+    def _results(self, P, want_planes):
+        r = Results(P)
+        cr = L.Results()
+        cr.feasible_count = _ptr(r.feasible_count, C.c_int32)
+        cr.selected_node = _ptr(r.selected_node, C.c_int32)
+        cr.selected_score = _ptr(r.selected_score, C.c_int64)
+        cr.pod_err = _ptr(r.pod_err, C.c_uint32)
+        if want_planes:
+            n_pad = (max(self.n_nodes, 1) + 511) // 512 * 512
+            r.feasible_bitmap = np.zeros((P, n_pad // 32), np.uint32)
+            r.scores = np.zeros((P, n_pad), np.int64)
+            cr.feasible_bitmap = _ptr(r.feasible_bitmap, C.c_uint32)
+            cr.scores = _ptr(r.scores, C.c_int64)
+        return r, cr
+
+    @staticmethod
+    def _opts(emit_mask=0, emit_raw=0, skip_pass_b=0):
+        return L.EvalOpts(emit_mask=emit_mask, emit_raw=emit_raw, skip_pass_b=skip_pass_b)
+
+    def evaluate(self, pod_table, want_planes=False, **opts):
+        P = int(pod_table.contents.n_pods)
+        self.n_pods = P
+        r, cr = self._results(P, want_planes)
+        o = self._opts(**opts)
+        self._check(self._lib.fgs_evaluate(self._h, pod_table, C.byref(o), C.byref(cr)))
+        r.words_per_row, r.score_row_stride = int(cr.words_per_row), int(cr.score_row_stride)
+        return r
+
+    def stage_pods(self, pod_table):
+        self.n_pods = int(pod_table.contents.n_pods)
+        self._check(self._lib.fgs_stage_pods(self._h, pod_table))
+
+    def pass_reduce(self):
+        self._check(self._lib.fgs_pass_reduce(self._h))
+
+    def pass_emit(self, **opts):
+        o = self._opts(**opts)
+        self._check(self._lib.fgs_pass_emit(self._h, C.byref(o)))
+
+    def fetch_results(self, want_planes=False):
+        r, cr = self._results(self.n_pods, want_planes)
+        self._check(self._lib.fgs_fetch_results(self._h, C.byref(cr)))
+        r.words_per_row, r.score_row_stride = int(cr.words_per_row), int(cr.score_row_stride)
+        return r
+
+    def device_view(self):
+        v = L.DeviceView()
+        self._check(self._lib.fgs_get_device_view(self._h, C.byref(v)))
+        return v
+
+    def synchronize(self):
+        self._check(self._lib.fgs_synchronize(self._h))
+
+    def status_plane(self, plugin=0):
+        out = np.zeros((self.n_pods, self.n_nodes), np.uint8)
+        self._check(self._lib.fgs_status_plane(self._h, plugin, _ptr(out, C.c_uint8)))
+        return out
+
+    def timings(self):
+        t = L.Timings()
+        self._check(self._lib.fgs_get_timings(self._h, C.byref(t)))
+        return dict(h2d_ms=t.h2d_ms, reduce_ms=t.reduce_ms, emit_ms=t.emit_ms, d2h_ms=t.d2h_ms, kernel_launches=t.kernel_launches)
+
+    # -- coscheduling / capacity scheduling ----------------------------------------------------------
+    def gang_check(self, snapshot, pending, podgroups):
+        P = int(pending.contents.n_pods)
+        G = int(podgroups.contents.n_groups)
+        pre = np.zeros(max(P, 1), np.uint8)
+        permit = np.zeros(max(P, 1), np.uint8)
+        assigned = np.zeros(max(G, 1), np.int32)
+        self._check(self._lib.fgs_gang_check(self._h, snapshot, pending, podgroups, _ptr(pre, C.c_uint8), _ptr(permit, C.c_uint8),
+                                             _ptr(assigned, C.c_int32)))
+        return pre[:P], permit[:P], assigned[:G]
+
+    def quota_check(self, pod_table, quotas, nominated_table=None, pod_uid=None, nominated_uid=None):
+        P = int(pod_table.contents.n_pods)
+        code = np.zeros(max(P, 1), np.uint8)
+        pu = _ptr(np.ascontiguousarray(pod_uid, np.int64), C.c_int64) if pod_uid is not None else None
+        nu = _ptr(np.ascontiguousarray(nominated_uid, np.int64), C.c_int64) if nominated_uid is not None else None
+        self._check(self._lib.fgs_quota_check(self._h, pod_table, quotas, nominated_table, pu, nu, _ptr(code, C.c_uint8)))
+        return code[:P]

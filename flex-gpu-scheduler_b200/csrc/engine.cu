@@ -1,0 +1,604 @@
+// engine.cu — host side of libfgs: device memory, H2D/D2H staging, kernel sequencing and the
+// extern "C" entry points declared in include/fgs.h. There is no CPU evaluation path in this file:
+// every verdict and score comes from the kernels in kernels.cu / gang_quota.cu.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "engine.h"
+#include "kernels.cuh"
+#include "pack.h"
+
+namespace fgs {
+
+static std::string g_create_error;
+
+#define FGS_CUDA(e, call)                                                                               \
+    do {                                                                                                \
+        cudaError_t _err = (call);                                                                      \
+        if (_err != cudaSuccess) {                                                                      \
+            (e)->err = std::string(#call) + ": " + cudaGetErrorString(_err);                            \
+            return FGS_E_CUDA;                                                                          \
+        }                                                                                               \
+    } while (0)
+
+static int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+int Engine::fail(int code, const std::string& msg) {
+    err = msg;
+    return code;
+}
+
+int Engine::ensure_nodes(int64_t n, int D_) {
+    const int64_t np = round_up(std::max<int64_t>(n, 1), kTileN);
+    if (np <= n_pad_cap && D_ <= D_cap) {
+        n_pad = np;
+        return FGS_OK;
+    }
+    if (d_raw) cudaFree(d_raw);
+    if (d_nd) cudaFree(d_nd);
+    if (h_raw) cudaFreeHost(h_raw);
+    d_raw = d_nd = nullptr;
+    h_raw = nullptr;
+    n_pad_cap = np;
+    D_cap = std::max(D_, D_cap);
+    n_pad = np;
+    FGS_CUDA(this, cudaMalloc(&d_raw, sizeof(int64_t) * nr_cols(S, D_cap) * np));
+    FGS_CUDA(this, cudaMalloc(&d_nd, sizeof(int64_t) * nd_cols(S) * np));
+    FGS_CUDA(this, cudaMallocHost(&h_raw, sizeof(int64_t) * nr_cols(S, D_cap) * np));
+    return FGS_OK;
+}
+
+int Engine::ensure_pods(int64_t p) {
+    const int64_t pp = round_up(std::max<int64_t>(p, 1), kTileP);
+    const int64_t wpr = n_pad / 32;
+    const int64_t stride = n_pad;
+    const bool planes_ok = (pp <= p_plane_cap) && (wpr == words_per_row) && (stride == score_stride);
+    if (pp > p_pad_cap) {
+        if (d_pods) cudaFree(d_pods);
+        if (d_perpod) cudaFree(d_perpod);
+        if (h_pods) cudaFreeHost(h_pods);
+        if (h_perpod) cudaFreeHost(h_perpod);
+        d_pods = d_perpod = nullptr;
+        h_pods = h_perpod = nullptr;
+        p_pad_cap = pp;
+        FGS_CUDA(this, cudaMalloc(&d_pods, sizeof(int64_t) * pd_cols(S) * pp));
+        FGS_CUDA(this, cudaMalloc(&d_perpod, sizeof(int64_t) * kPerPodRows * pp));
+        FGS_CUDA(this, cudaMallocHost(&h_pods, sizeof(int64_t) * pd_cols(S) * pp));
+        FGS_CUDA(this, cudaMallocHost(&h_perpod, sizeof(int64_t) * kPerPodRows * pp));
+    }
+    if (!planes_ok) {
+        if (d_bitmap) cudaFree(d_bitmap);
+        if (d_scores) cudaFree(d_scores);
+        d_bitmap = nullptr;
+        d_scores = nullptr;
+        p_plane_cap = std::max(pp, p_plane_cap);
+        words_per_row = wpr;
+        score_stride = stride;
+        FGS_CUDA(this, cudaMalloc(&d_bitmap, sizeof(uint32_t) * p_plane_cap * words_per_row));
+        FGS_CUDA(this, cudaMalloc(&d_scores, sizeof(int64_t) * p_plane_cap * score_stride));
+    }
+    p_pad = pp;
+    return FGS_OK;
+}
+
+void Engine::free_all() {
+    if (d_raw) cudaFree(d_raw);
+    if (d_nd) cudaFree(d_nd);
+    if (d_pods) cudaFree(d_pods);
+    if (d_perpod) cudaFree(d_perpod);
+    if (d_bitmap) cudaFree(d_bitmap);
+    if (d_scores) cudaFree(d_scores);
+    if (h_raw) cudaFreeHost(h_raw);
+    if (h_pods) cudaFreeHost(h_pods);
+    if (h_perpod) cudaFreeHost(h_perpod);
+    for (auto& ev : events)
+        if (ev) cudaEventDestroy(ev);
+    if (own_stream && stream) cudaStreamDestroy(stream);
+    gang_free();
+}
+
+// plugin args → kernel parameters; validation mirrors the reference constructors
+int Engine::set_plugins(const fgs_plugin_cfg* c) {
+    if (!c) return fail(FGS_E_INVALID, "fgs_set_plugins: null config");
+    if (c->filter_mask & ~(FGS_PL_FLEXGPU | FGS_PL_FIT)) return fail(FGS_E_INVALID, "fgs_set_plugins: unknown filter plugin bit");
+    if (c->score_mask & ~(FGS_PL_FLEXGPU | FGS_PL_FIT | FGS_PL_ALLOCATABLE))
+        return fail(FGS_E_INVALID, "fgs_set_plugins: unknown score plugin bit");
+    if (c->score_mask & FGS_PL_ALLOCATABLE) {
+        if (c->alloc_mode != 0 && c->alloc_mode != 1) return fail(FGS_E_INVALID, "invalid mode, got " + std::to_string(c->alloc_mode));
+        if (c->alloc_n_res < 1 || c->alloc_n_res > FGS_MAX_SCORE_RES) return fail(FGS_E_INVALID, "NodeResourcesAllocatable: 1..8 resources");
+        for (int k = 0; k < c->alloc_n_res; ++k)
+            if (c->alloc_res_w[k] <= 0) // pkg/noderesources/allocatable.go:51-58
+                return fail(FGS_E_INVALID, "resource Weight of slot " + std::to_string(c->alloc_res[k]) + " should be a positive value, got " +
+                                               std::to_string(c->alloc_res_w[k]));
+    }
+    if (c->score_mask & FGS_PL_FIT) {
+        if (c->fit_strategy != 0 && c->fit_strategy != 1)
+            return fail(FGS_E_INVALID, "scoring strategy " + std::to_string(c->fit_strategy) + " is not supported");
+        if (c->fit_n_res < 1 || c->fit_n_res > FGS_MAX_SCORE_RES) return fail(FGS_E_INVALID, "NodeResourcesFit: 1..8 scoring resources");
+        for (int k = 0; k < c->fit_n_res; ++k) {
+            // ValidateNodeResourcesFitArgs: weight in [1,100]
+            if (c->fit_res_w[k] < 1 || c->fit_res_w[k] > 100) return fail(FGS_E_INVALID, "NodeResourcesFit: resource weight not in [1, 100]");
+            if (c->fit_res[k] >= FGS_RES_SCALAR0 + S) return fail(FGS_E_INVALID, "NodeResourcesFit: resource slot out of range");
+        }
+    }
+    for (int64_t w : {c->weight_flex, c->weight_fit, c->weight_alloc})
+        if (w < 0) return fail(FGS_E_INVALID, "score plugin weight must be >= 0");
+    cfg = *c;
+    have_cfg = true;
+    nodes_derived = false; // Allocatable raw scores depend on the args
+    return FGS_OK;
+}
+
+void Engine::fill_eval_params(EvalParams* p, const fgs_eval_opts* opts) const {
+    std::memset(p, 0, sizeof(*p));
+    p->nd = (const int64_t*)d_nd;
+    p->pods = (const int64_t*)d_pods;
+    p->reduce_max = (int64_t*)d_perpod;
+    p->reduce_sum = (int64_t*)d_perpod + (int64_t)FGS_REDUCE_ROWS * p_pad;
+    p->select_key = (int64_t*)d_perpod + (int64_t)(FGS_REDUCE_ROWS + 1) * p_pad;
+    p->bitmap = (uint32_t*)d_bitmap;
+    p->scores = (int64_t*)d_scores;
+    p->n_nodes = n_nodes;
+    p->n_pad = n_pad;
+    p->node_base = node_base;
+    p->n_pods = n_pods;
+    p->p_pad = p_pad;
+    p->words_per_row = words_per_row;
+    p->score_stride = score_stride;
+    p->S = S;
+    p->filter_mask = cfg.filter_mask;
+    p->score_mask = cfg.score_mask;
+    p->emit_mask = (opts && opts->emit_mask) ? opts->emit_mask : cfg.score_mask;
+    p->emit_raw = opts ? opts->emit_raw : 0;
+    // profile order of the two filter plugins (runtime/framework.go:674-689 early exit)
+    p->flex_filter_first = 1;
+    for (int k = 0; k < 2 && cfg.filter_order[k]; ++k) {
+        if (cfg.filter_order[k] == (int)FGS_PL_FLEXGPU) break;
+        if (cfg.filter_order[k] == (int)FGS_PL_FIT) {
+            p->flex_filter_first = 0;
+            break;
+        }
+    }
+    p->w_flex = cfg.weight_flex ? cfg.weight_flex : 1; // runtime/framework.go:405-408
+    p->w_fit = cfg.weight_fit ? cfg.weight_fit : 1;
+    p->w_alloc = cfg.weight_alloc ? cfg.weight_alloc : 1;
+    p->fit_strategy = cfg.fit_strategy;
+    p->fit_n_res = (cfg.score_mask & FGS_PL_FIT) ? cfg.fit_n_res : 0;
+    p->fit_ignored = cfg.fit_ignored_scalar_mask;
+    int wc = 0, wm = 0;
+    bool fast = true;
+    for (int k = 0; k < p->fit_n_res; ++k) {
+        p->fit_res[k] = cfg.fit_res[k];
+        p->fit_w[k] = cfg.fit_res_w[k];
+        if (cfg.fit_res[k] == FGS_RES_CPU && wc == 0) wc = (int)cfg.fit_res_w[k];
+        else if (cfg.fit_res[k] == FGS_RES_MEM && wm == 0) wm = (int)cfg.fit_res_w[k];
+        else fast = false;
+    }
+    fast = fast && wc > 0 && wm > 0;
+    p->fit_fast = fast ? 1 : 0;
+    p->fit_w_cpu = wc;
+    p->fit_w_mem = wm;
+    p->fit_wsum = wc + wm;
+    p->fit_inv_wsum = (wc + wm) > 0 ? 1.0f / (float)(wc + wm) : 0.f;
+    p->seed = seed;
+    // selectHost key: score field above a 16-bit hash and a 24-bit node index when Σw·100 < 2^23
+    int64_t max_total = 0;
+    if (cfg.score_mask & FGS_PL_FLEXGPU) max_total += 100 * p->w_flex;
+    if (cfg.score_mask & FGS_PL_FIT) max_total += 100 * p->w_fit;
+    if (cfg.score_mask & FGS_PL_ALLOCATABLE) max_total += 100 * p->w_alloc;
+    p->key_shift = (max_total < ((int64_t)1 << 23) && !p->emit_raw) ? 40 : 24;
+    // pods per CTA: enough CTAs for a few waves of 148 SMs × 2 resident CTAs
+    const int64_t node_tiles = n_pad / kTileN;
+    const int64_t target_ctas = 148 * 2 * 4;
+    int64_t chunks = std::max<int64_t>(1, target_ctas / std::max<int64_t>(1, node_tiles));
+    int64_t ppc = round_up(std::max<int64_t>(kTileP, (p_pad + chunks - 1) / chunks), kTileP);
+    if (ppc > 65536) ppc = 65536;
+    p->pods_per_cta = (int)ppc;
+}
+
+} // namespace fgs
+
+using namespace fgs;
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+
+extern "C" const char* fgs_last_error(const fgs_engine* e) {
+    if (!e) return g_create_error.c_str();
+    return ((const Engine*)e)->err.c_str();
+}
+
+extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
+    if (!c || !out) {
+        g_create_error = "fgs_create: null argument";
+        return FGS_E_INVALID;
+    }
+    if (c->n_scalars < 2 || c->n_scalars > FGS_MAX_SCALARS) {
+        g_create_error = "fgs_create: n_scalars must be in [2, 8]";
+        return FGS_E_INVALID;
+    }
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev <= 0 || c->device < 0 || c->device >= ndev) {
+        g_create_error = std::string("fgs_create: no usable CUDA device (") + (ce != cudaSuccess ? cudaGetErrorString(ce) : "ordinal out of range") +
+                         "); libfgs has no CPU fallback";
+        return FGS_E_CUDA;
+    }
+    ce = cudaSetDevice(c->device);
+    if (ce != cudaSuccess) {
+        g_create_error = std::string("cudaSetDevice: ") + cudaGetErrorString(ce);
+        return FGS_E_CUDA;
+    }
+    Engine* e = new (std::nothrow) Engine();
+    if (!e) return FGS_E_INVALID;
+    e->device = c->device;
+    e->S = c->n_scalars;
+    e->node_base = c->node_index_base;
+    e->total_nodes = c->total_nodes;
+    e->seed = c->select_seed;
+    if (c->stream) {
+        e->stream = (cudaStream_t)c->stream;
+        e->own_stream = false;
+    } else {
+        ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+        if (ce != cudaSuccess) {
+            g_create_error = std::string("cudaStreamCreate: ") + cudaGetErrorString(ce);
+            delete e;
+            return FGS_E_CUDA;
+        }
+        e->own_stream = true;
+    }
+    for (auto& ev : e->events) {
+        ce = cudaEventCreate(&ev);
+        if (ce != cudaSuccess) {
+            g_create_error = std::string("cudaEventCreate: ") + cudaGetErrorString(ce);
+            e->free_all();
+            delete e;
+            return FGS_E_CUDA;
+        }
+    }
+    ce = eval_setup();
+    if (ce != cudaSuccess) {
+        g_create_error = std::string("kernel attribute setup: ") + cudaGetErrorString(ce) + " (libfgs is built for sm_100a only)";
+        e->free_all();
+        delete e;
+        return FGS_E_CUDA;
+    }
+    // default plugin set = the flexgpu profile: FlexGPU filter+score (manifests/flexgpu/templates/configmap.yaml)
+    fgs_plugin_cfg d;
+    std::memset(&d, 0, sizeof(d));
+    d.filter_mask = FGS_PL_FLEXGPU | FGS_PL_FIT;
+    d.filter_order[0] = FGS_PL_FIT;
+    d.filter_order[1] = FGS_PL_FLEXGPU;
+    d.score_mask = FGS_PL_FLEXGPU | FGS_PL_FIT;
+    d.weight_flex = d.weight_fit = d.weight_alloc = 1;
+    d.fit_strategy = 0;
+    d.fit_n_res = 2;
+    d.fit_res[0] = FGS_RES_CPU;
+    d.fit_res[1] = FGS_RES_MEM;
+    d.fit_res_w[0] = d.fit_res_w[1] = 1; // vendor/.../apis/config/v1beta2/defaults.go:241-257
+    d.alloc_mode = 0;
+    d.alloc_n_res = 2;
+    d.alloc_res[0] = FGS_RES_CPU;
+    d.alloc_res_w[0] = 1 << 20; // pkg/noderesources/resource_allocation.go:38
+    d.alloc_res[1] = FGS_RES_MEM;
+    d.alloc_res_w[1] = 1;
+    e->set_plugins(&d);
+    *out = (fgs_engine*)e;
+    return FGS_OK;
+}
+
+extern "C" void fgs_destroy(fgs_engine* eh) {
+    if (!eh) return;
+    Engine* e = (Engine*)eh;
+    cudaSetDevice(e->device);
+    cudaStreamSynchronize(e->stream);
+    e->free_all();
+    delete e;
+}
+
+extern "C" int fgs_set_plugins(fgs_engine* eh, const fgs_plugin_cfg* c) {
+    if (!eh) return FGS_E_INVALID;
+    return ((Engine*)eh)->set_plugins(c);
+}
+
+extern "C" int fgs_pack_nodes(fgs_engine* eh, const fgs_snapshot* snap, const fgs_node_table** out) {
+    if (!eh || !out) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (snap && snap->n_scalars != e->S) return e->fail(FGS_E_INVALID, "fgs_pack_nodes: snapshot n_scalars differs from the engine's");
+    int rc = pack_nodes(snap, &e->packed_nodes, &e->err);
+    if (rc) return rc;
+    *out = &e->packed_nodes.view;
+    return FGS_OK;
+}
+
+extern "C" int fgs_pack_pods(fgs_engine* eh, const fgs_podset* pods, const fgs_pod_table** out) {
+    if (!eh || !out) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (pods && pods->n_scalars != e->S) return e->fail(FGS_E_INVALID, "fgs_pack_pods: podset n_scalars differs from the engine's");
+    int rc = pack_pods(pods, &e->packed_pods, &e->err);
+    if (rc) return rc;
+    *out = &e->packed_pods.view;
+    return FGS_OK;
+}
+
+static int run_derive(Engine* e) {
+    DeriveParams dp;
+    std::memset(&dp, 0, sizeof(dp));
+    dp.raw = (const int64_t*)e->d_raw;
+    dp.nd = (int64_t*)e->d_nd;
+    dp.n_nodes = e->n_nodes;
+    dp.n_pad = e->n_pad;
+    dp.S = e->S;
+    dp.D = e->D;
+    dp.alloc_mode = e->cfg.alloc_mode;
+    dp.alloc_n_res = (e->cfg.score_mask & FGS_PL_ALLOCATABLE) ? e->cfg.alloc_n_res : 0;
+    for (int k = 0; k < dp.alloc_n_res; ++k) {
+        dp.alloc_res[k] = e->cfg.alloc_res[k];
+        dp.alloc_w[k] = e->cfg.alloc_res_w[k];
+    }
+    launch_derive(dp, e->stream);
+    e->launches++;
+    FGS_CUDA(e, cudaGetLastError());
+    e->nodes_derived = true;
+    return FGS_OK;
+}
+
+// copy one table row-set into the pinned column-major staging buffer
+static void stage_node_columns(Engine* e, const fgs_node_table* t, int64_t dst0, int64_t count, int64_t src0) {
+    const int64_t np = e->n_pad;
+    const int S = e->S, D = e->D;
+    int64_t* h = (int64_t*)e->h_raw;
+    auto col = [&](int c, const int64_t* src) { std::memcpy(h + (int64_t)c * np + dst0, src + src0, sizeof(int64_t) * (size_t)count); };
+    col(NR_ALLOC_MCPU, t->alloc_mcpu);
+    col(NR_ALLOC_MEM, t->alloc_mem);
+    col(NR_ALLOC_EPH, t->alloc_eph);
+    col(NR_ALLOC_PODS, t->alloc_pods);
+    col(NR_REQ_MCPU, t->req_mcpu);
+    col(NR_REQ_MEM, t->req_mem);
+    col(NR_REQ_EPH, t->req_eph);
+    col(NR_NUM_PODS, t->num_pods);
+    col(NR_NZ_MCPU, t->nz_mcpu);
+    col(NR_NZ_MEM, t->nz_mem);
+    col(NR_FLEX_GPU_SUM, t->flex_gpu_sum);
+    col(NR_FLEX_MEM_SUM, t->flex_mem_sum);
+    for (int64_t i = 0; i < count; ++i) {
+        h[(int64_t)NR_META * np + dst0 + i] = (int64_t)(((uint64_t)t->monopoly_mask[src0 + i] << 32) | (uint64_t)t->flags[src0 + i]);
+        h[(int64_t)NR_PRESENT * np + dst0 + i] = (int64_t)t->alloc_scalar_present[src0 + i];
+    }
+    for (int s = 0; s < S; ++s) {
+        col(nr_alloc_scalar(s), t->alloc_scalar + (int64_t)s * t->n_nodes);
+        col(nr_req_scalar(S, s), t->req_scalar + (int64_t)s * t->n_nodes);
+    }
+    for (int d = 0; d < D; ++d) {
+        if (d < t->n_devices) col(nr_used(S, d), t->used_mem + (int64_t)d * t->n_nodes);
+        else std::memset(h + (int64_t)nr_used(S, d) * np + dst0, 0, sizeof(int64_t) * (size_t)count);
+    }
+}
+
+static int validate_node_table(Engine* e, const fgs_node_table* t) {
+    if (!t || t->n_nodes < 0) return e->fail(FGS_E_INVALID, "node table: null or negative size");
+    if (t->n_scalars != e->S) return e->fail(FGS_E_INVALID, "node table: n_scalars differs from the engine's");
+    if (t->n_devices < 1 || t->n_devices > FGS_MAX_DEVICES) return e->fail(FGS_E_TOO_LARGE, "node table: n_devices must be in [1, 16]");
+    if (t->n_nodes >= ((int64_t)1 << 24) - 1) return e->fail(FGS_E_TOO_LARGE, "node table: at most 2^24-2 nodes per engine");
+    return FGS_OK;
+}
+
+extern "C" int fgs_upload_nodes(fgs_engine* eh, const fgs_node_table* t) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    int rc = validate_node_table(e, t);
+    if (rc) return rc;
+    cudaSetDevice(e->device);
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream)); // staging buffer reuse
+    rc = e->ensure_nodes(t->n_nodes, t->n_devices);
+    if (rc) return rc;
+    e->n_nodes = t->n_nodes;
+    e->D = std::max(e->D_cap, 1);
+    std::memset(e->h_raw, 0, sizeof(int64_t) * nr_cols(e->S, e->D) * e->n_pad);
+    stage_node_columns(e, t, 0, t->n_nodes, 0);
+    FGS_CUDA(e, cudaMemcpyAsync(e->d_raw, e->h_raw, sizeof(int64_t) * nr_cols(e->S, e->D) * e->n_pad, cudaMemcpyHostToDevice, e->stream));
+    e->have_nodes = true;
+    return run_derive(e);
+}
+
+extern "C" int fgs_update_nodes(fgs_engine* eh, const fgs_node_table* rows, const int64_t* dirty_idx) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_update_nodes before fgs_upload_nodes");
+    int rc = validate_node_table(e, rows);
+    if (rc) return rc;
+    if (rows->n_devices > e->D) return e->fail(FGS_E_INVALID, "fgs_update_nodes: more device slots than the uploaded table; re-upload");
+    if (rows->n_nodes && !dirty_idx) return e->fail(FGS_E_INVALID, "fgs_update_nodes: null dirty_idx");
+    cudaSetDevice(e->device);
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    const int ncols = nr_cols(e->S, e->D);
+    for (int64_t r = 0; r < rows->n_nodes; ++r) {
+        const int64_t n = dirty_idx[r];
+        if (n < 0 || n >= e->n_nodes) return e->fail(FGS_E_INVALID, "fgs_update_nodes: dirty index out of range");
+        stage_node_columns(e, rows, n, 1, r);
+        // one small strided copy per dirty row: ncols values, pitch = n_pad
+        FGS_CUDA(e, cudaMemcpy2DAsync((int64_t*)e->d_raw + n, sizeof(int64_t) * e->n_pad, (int64_t*)e->h_raw + n, sizeof(int64_t) * e->n_pad,
+                                      sizeof(int64_t), (size_t)ncols, cudaMemcpyHostToDevice, e->stream));
+    }
+    return run_derive(e);
+}
+
+extern "C" int fgs_stage_pods(fgs_engine* eh, const fgs_pod_table* t) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_stage_pods before fgs_upload_nodes");
+    if (!t || t->n_pods < 0) return e->fail(FGS_E_INVALID, "pod table: null or negative size");
+    if (t->n_scalars != e->S) return e->fail(FGS_E_INVALID, "pod table: n_scalars differs from the engine's");
+    cudaSetDevice(e->device);
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    int rc = e->ensure_pods(t->n_pods);
+    if (rc) return rc;
+    if (!e->nodes_derived) {
+        rc = run_derive(e);
+        if (rc) return rc;
+    }
+    e->n_pods = t->n_pods;
+    const int64_t P = t->n_pods, pp = e->p_pad;
+    const int S = e->S;
+    int64_t* h = (int64_t*)e->h_pods;
+    FGS_CUDA(e, cudaEventRecord(e->events[0], e->stream));
+    auto col = [&](int c, const int64_t* src) {
+        std::memcpy(h + (int64_t)c * pp, src, sizeof(int64_t) * (size_t)P);
+        std::memset(h + (int64_t)c * pp + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+    };
+    col(PD_GPU_LIM, t->flex_gpu_limit);
+    col(PD_MEM_LIM, t->flex_mem_limit);
+    col(PD_REQ_CPU, t->req_mcpu);
+    col(PD_REQ_MEM, t->req_mem);
+    col(PD_REQ_EPH, t->req_eph);
+    col(PD_NZ_CPU, t->nz_mcpu);
+    col(PD_NZ_MEM, t->nz_mem);
+    for (int64_t i = 0; i < P; ++i) h[(int64_t)PD_META * pp + i] = (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]);
+    std::memset(h + (int64_t)PD_META * pp + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+    for (int s = 0; s < S; ++s) col(PD_FIXED_COLS + s, t->req_scalar + (int64_t)s * P);
+    FGS_CUDA(e, cudaMemcpyAsync(e->d_pods, e->h_pods, sizeof(int64_t) * pd_cols(S) * pp, cudaMemcpyHostToDevice, e->stream));
+    FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
+    e->have_pods = true;
+    return FGS_OK;
+}
+
+extern "C" int fgs_pass_reduce(fgs_engine* eh) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_reduce before fgs_stage_pods");
+    cudaSetDevice(e->device);
+    EvalParams p;
+    e->fill_eval_params(&p, nullptr);
+    launch_init_perpod((int64_t*)e->d_perpod, e->p_pad, e->stream);
+    e->launches++;
+    launch_eval_reduce(p, e->stream);
+    e->launches++;
+    FGS_CUDA(e, cudaGetLastError());
+    FGS_CUDA(e, cudaEventRecord(e->events[2], e->stream));
+    return FGS_OK;
+}
+
+extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_emit before fgs_stage_pods");
+    cudaSetDevice(e->device);
+    EvalParams p;
+    e->fill_eval_params(&p, opts);
+    e->last_key_shift = p.key_shift;
+    launch_eval_emit(p, e->stream);
+    e->launches++;
+    FGS_CUDA(e, cudaGetLastError());
+    FGS_CUDA(e, cudaEventRecord(e->events[3], e->stream));
+    e->emitted = true;
+    return FGS_OK;
+}
+
+extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
+    if (!eh || !out) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_fetch_results before an evaluation");
+    cudaSetDevice(e->device);
+    const int64_t P = e->n_pods, pp = e->p_pad;
+    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, e->d_perpod, sizeof(int64_t) * kPerPodRows * pp, cudaMemcpyDeviceToHost, e->stream));
+    if (out->feasible_bitmap)
+        FGS_CUDA(e, cudaMemcpyAsync(out->feasible_bitmap, e->d_bitmap, sizeof(uint32_t) * P * e->words_per_row, cudaMemcpyDeviceToHost, e->stream));
+    if (out->scores && e->emitted)
+        FGS_CUDA(e, cudaMemcpyAsync(out->scores, e->d_scores, sizeof(int64_t) * P * e->score_stride, cudaMemcpyDeviceToHost, e->stream));
+    FGS_CUDA(e, cudaEventRecord(e->events[4], e->stream));
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    const int64_t* h = (const int64_t*)e->h_perpod;
+    const int64_t* filter_panic = h + (int64_t)RR_FILTER_PANIC * pp;
+    const int64_t* count = h + (int64_t)FGS_REDUCE_ROWS * pp;
+    const int64_t* key = h + (int64_t)(FGS_REDUCE_ROWS + 1) * pp;
+    const int64_t* e_range = key + pp;
+    const int64_t* e_panic = key + 2 * pp;
+    const int shift = e->last_key_shift;
+    for (int64_t p = 0; p < P; ++p) {
+        if (out->feasible_count) out->feasible_count[p] = (int32_t)count[p];
+        uint32_t err = 0;
+        if (filter_panic[p] > 0) err |= FGS_PODERR_REF_PANIC;
+        if (e->emitted) {
+            if (e_range[p] > 0) err |= FGS_PODERR_SCORE_RANGE;
+            if (e_panic[p] > 0) err |= FGS_PODERR_REF_PANIC;
+        }
+        if (out->pod_err) out->pod_err[p] = err;
+        int32_t sel = -1;
+        int64_t sc = 0;
+        if (e->emitted && key[p] > 0) {
+            const uint64_t k = (uint64_t)key[p] - 1;
+            sel = (int32_t)(k & 0xffffffu);
+            sc = (int64_t)(k >> shift);
+        }
+        if (out->selected_node) out->selected_node[p] = sel;
+        if (out->selected_score) out->selected_score[p] = sc;
+    }
+    out->words_per_row = e->words_per_row;
+    out->score_row_stride = e->score_stride;
+    cudaEventElapsedTime(&e->tm.h2d_ms, e->events[0], e->events[1]);
+    cudaEventElapsedTime(&e->tm.reduce_ms, e->events[1], e->events[2]);
+    if (e->emitted) {
+        cudaEventElapsedTime(&e->tm.emit_ms, e->events[2], e->events[3]);
+        cudaEventElapsedTime(&e->tm.d2h_ms, e->events[3], e->events[4]);
+    } else {
+        e->tm.emit_ms = 0.f;
+        cudaEventElapsedTime(&e->tm.d2h_ms, e->events[2], e->events[4]);
+    }
+    return FGS_OK;
+}
+
+extern "C" int fgs_evaluate(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts, fgs_results* out) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    int rc = fgs_stage_pods(eh, pods);
+    if (rc) return rc;
+    e->emitted = false;
+    rc = fgs_pass_reduce(eh);
+    if (rc) return rc;
+    if (!(opts && opts->skip_pass_b)) {
+        rc = fgs_pass_emit(eh, opts);
+        if (rc) return rc;
+    }
+    return fgs_fetch_results(eh, out);
+}
+
+extern "C" int fgs_get_device_view(fgs_engine* eh, fgs_device_view* v) {
+    if (!eh || !v) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_get_device_view before fgs_stage_pods");
+    v->reduce_max = e->d_perpod;
+    v->reduce_sum = (int64_t*)e->d_perpod + (int64_t)FGS_REDUCE_ROWS * e->p_pad;
+    v->select_key = (int64_t*)e->d_perpod + (int64_t)(FGS_REDUCE_ROWS + 1) * e->p_pad;
+    v->feasible_bitmap = e->d_bitmap;
+    v->scores = e->d_scores;
+    v->p_pad = e->p_pad;
+    v->words_per_row = e->words_per_row;
+    v->score_row_stride = e->score_stride;
+    v->stream = (void*)e->stream;
+    return FGS_OK;
+}
+
+extern "C" int fgs_synchronize(fgs_engine* eh) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    cudaSetDevice(e->device);
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    return FGS_OK;
+}
+
+extern "C" int fgs_get_timings(fgs_engine* eh, fgs_timings* t) {
+    if (!eh || !t) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    *t = e->tm;
+    t->kernel_launches = e->launches;
+    return FGS_OK;
+}

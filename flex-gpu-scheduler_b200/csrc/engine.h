@@ -1,0 +1,63 @@
+// engine.h — the object behind the opaque fgs_engine handle.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+
+#include "../../include/fgs.h"
+#include "kernels.cuh"
+#include "pack.h"
+
+namespace fgs {
+
+// per-pod device block: reduce_max[FGS_REDUCE_ROWS] | reduce_sum | select_key[3]
+constexpr int kPerPodRows = FGS_REDUCE_ROWS + 1 + 3;
+
+struct GangState; // gang_quota.cu
+
+struct Engine {
+    int device = 0;
+    int S = 2, D = 1, D_cap = 0;
+    int64_t node_base = 0, total_nodes = 0;
+    uint64_t seed = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    cudaEvent_t events[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    std::string err;
+
+    fgs_plugin_cfg cfg;
+    bool have_cfg = false, have_nodes = false, nodes_derived = false, have_pods = false, emitted = false;
+    int last_key_shift = 40;
+
+    // nodes
+    int64_t n_nodes = 0, n_pad = 0, n_pad_cap = 0;
+    void* d_raw = nullptr;
+    void* d_nd = nullptr;
+    void* h_raw = nullptr;
+    // pods / results
+    int64_t n_pods = 0, p_pad = 0, p_pad_cap = 0, p_plane_cap = 0;
+    int64_t words_per_row = 0, score_stride = 0;
+    void* d_pods = nullptr;
+    void* d_perpod = nullptr;
+    void* d_bitmap = nullptr;
+    void* d_scores = nullptr;
+    void* h_pods = nullptr;
+    void* h_perpod = nullptr;
+
+    PackedNodes packed_nodes;
+    PackedPods packed_pods;
+    GangState* gang = nullptr;
+
+    fgs_timings tm = {0, 0, 0, 0, 0};
+    int64_t launches = 0;
+
+    int fail(int code, const std::string& msg);
+    int ensure_nodes(int64_t n, int D);
+    int ensure_pods(int64_t p);
+    int set_plugins(const fgs_plugin_cfg* c);
+    void fill_eval_params(EvalParams* p, const fgs_eval_opts* opts) const;
+    void free_all();
+    void gang_free();
+};
+
+} // namespace fgs

@@ -1,0 +1,227 @@
+// pack.cpp — object snapshot → SoA tables. One walk over each node's pod list replaces the walks
+// the reference repeats for every (pod,node) pair:
+//   nodeResourceLimitSum        pkg/flexgpu/flex_gpu.go:133-140   → flex_gpu_sum / flex_mem_sum
+//   NewGPUNode / constructGPUs  pkg/flexgpu/gpu_node.go:30-120    → used_mem[D][N], monopoly_mask, REF_PANIC flag
+//   len(nodeInfo.Pods)          vendor/.../noderesources/fit.go:259 → num_pods
+// and each pending pod is reduced once to the numbers the plugins derive from it on every call.
+#include "pack.h"
+
+#include <cstring>
+
+#include "podmath.h"
+
+namespace fgs {
+
+void PackedNodes::make_view() {
+    std::memset(&view, 0, sizeof(view));
+    view.n_nodes = n;
+    view.n_scalars = S;
+    view.n_devices = D;
+    view.alloc_mcpu = alloc_mcpu.data();
+    view.alloc_mem = alloc_mem.data();
+    view.alloc_eph = alloc_eph.data();
+    view.alloc_pods = alloc_pods.data();
+    view.req_mcpu = req_mcpu.data();
+    view.req_mem = req_mem.data();
+    view.req_eph = req_eph.data();
+    view.num_pods = num_pods.data();
+    view.nz_mcpu = nz_mcpu.data();
+    view.nz_mem = nz_mem.data();
+    view.alloc_scalar = alloc_scalar.data();
+    view.req_scalar = req_scalar.data();
+    view.alloc_scalar_present = alloc_scalar_present.data();
+    view.flex_gpu_sum = flex_gpu_sum.data();
+    view.flex_mem_sum = flex_mem_sum.data();
+    view.used_mem = used_mem.data();
+    view.monopoly_mask = monopoly_mask.data();
+    view.flags = flags.data();
+}
+
+void PackedPods::make_view() {
+    std::memset(&view, 0, sizeof(view));
+    view.n_pods = n;
+    view.n_scalars = S;
+    view.flex_gpu_limit = flex_gpu_limit.data();
+    view.flex_mem_limit = flex_mem_limit.data();
+    view.flags = flags.data();
+    view.req_mcpu = req_mcpu.data();
+    view.req_mem = req_mem.data();
+    view.req_eph = req_eph.data();
+    view.req_scalar = req_scalar.data();
+    view.req_scalar_present = req_scalar_present.data();
+    view.nz_mcpu = nz_mcpu.data();
+    view.nz_mem = nz_mem.data();
+    view.ns = ns.data();
+    view.pg = pg.data();
+    view.priority = priority.data();
+}
+
+int pack_nodes(const fgs_snapshot* snap, PackedNodes* out, std::string* err) {
+    if (!snap || snap->n_nodes < 0 || snap->n_scalars < 2 || snap->n_scalars > FGS_MAX_SCALARS) {
+        *err = "pack_nodes: bad snapshot header";
+        return FGS_E_INVALID;
+    }
+    const int64_t N = snap->n_nodes;
+    const int S = snap->n_scalars, AW = 4 + S, RW = 3 + S;
+    // device slots = largest gpu count on any node
+    int D = 1;
+    for (int64_t n = 0; n < N; ++n) {
+        if (!((snap->alloc_scalar_present[n] >> FGS_SCALAR_FLEX_GPU) & 1u)) continue;
+        const int64_t g = snap->alloc[n * AW + 4 + FGS_SCALAR_FLEX_GPU];
+        if (g > FGS_MAX_DEVICES) {
+            *err = "pack_nodes: node " + std::to_string(n) + " has " + std::to_string(g) + " flex gpus; at most " +
+                   std::to_string(FGS_MAX_DEVICES) + " device slots are supported";
+            return FGS_E_TOO_LARGE;
+        }
+        if (g > D) D = (int)g;
+    }
+    PackedNodes& t = *out;
+    t.n = N;
+    t.S = S;
+    t.D = D;
+    auto z = [&](std::vector<int64_t>& v, int64_t k) { v.assign((size_t)k, 0); };
+    z(t.alloc_mcpu, N), z(t.alloc_mem, N), z(t.alloc_eph, N), z(t.alloc_pods, N);
+    z(t.req_mcpu, N), z(t.req_mem, N), z(t.req_eph, N), z(t.num_pods, N), z(t.nz_mcpu, N), z(t.nz_mem, N);
+    z(t.alloc_scalar, N * S), z(t.req_scalar, N * S), z(t.flex_gpu_sum, N), z(t.flex_mem_sum, N), z(t.used_mem, N * D);
+    t.alloc_scalar_present.assign((size_t)N, 0);
+    t.monopoly_mask.assign((size_t)N, 0);
+    t.flags.assign((size_t)N, 0);
+
+    const fgs_podset* ps = &snap->pods;
+    for (int64_t n = 0; n < N; ++n) {
+        const int64_t* al = snap->alloc + n * AW;
+        const int64_t* rq = snap->requested + n * RW;
+        for (int k = 0; k < AW; ++k)
+            if (!in_range(al[k])) {
+                *err = "pack_nodes: allocatable of node " + std::to_string(n) + " out of range";
+                return FGS_E_RANGE;
+            }
+        for (int k = 0; k < RW; ++k)
+            if (!in_range(rq[k])) {
+                *err = "pack_nodes: requested of node " + std::to_string(n) + " out of range";
+                return FGS_E_RANGE;
+            }
+        t.alloc_mcpu[(size_t)n] = al[0];
+        t.alloc_mem[(size_t)n] = al[1];
+        t.alloc_eph[(size_t)n] = al[2];
+        t.alloc_pods[(size_t)n] = al[3];
+        t.req_mcpu[(size_t)n] = rq[0];
+        t.req_mem[(size_t)n] = rq[1];
+        t.req_eph[(size_t)n] = rq[2];
+        t.nz_mcpu[(size_t)n] = snap->nonzero[n * 2 + 0];
+        t.nz_mem[(size_t)n] = snap->nonzero[n * 2 + 1];
+        if (!in_range(t.nz_mcpu[(size_t)n]) || !in_range(t.nz_mem[(size_t)n])) {
+            *err = "pack_nodes: non-zero requested of node " + std::to_string(n) + " out of range";
+            return FGS_E_RANGE;
+        }
+        const uint32_t present = snap->alloc_scalar_present[n];
+        t.alloc_scalar_present[(size_t)n] = present;
+        for (int s = 0; s < S; ++s) {
+            t.alloc_scalar[(size_t)(s * N + n)] = ((present >> s) & 1u) ? al[4 + s] : 0;
+            t.req_scalar[(size_t)(s * N + n)] = rq[3 + s];
+        }
+        const int64_t p0 = snap->pod_off[n], p1 = snap->pod_off[n + 1];
+        t.num_pods[(size_t)n] = p1 - p0;
+
+        uint32_t fl = 0;
+        if (snap->node_valid[n]) fl |= FGS_NF_VALID;
+        const bool has_gpu = (present >> FGS_SCALAR_FLEX_GPU) & 1u, has_mem = (present >> FGS_SCALAR_FLEX_MEM) & 1u;
+        if (has_gpu) fl |= FGS_NF_HAS_GPU_RES;
+        if (has_mem) fl |= FGS_NF_HAS_MEM_RES;
+        if (has_gpu && has_mem) fl |= FGS_NF_HAS_FLEX;
+        // gpu count as NewGPUNode reads it: a missing key is the zero Quantity (gpu_node.go:37-42)
+        const int64_t gpu_cnt = has_gpu ? al[4 + FGS_SCALAR_FLEX_GPU] : 0;
+        if (gpu_cnt <= 0) fl |= FGS_NF_REF_PANIC; // divide by zero (:55) / negative make (:68)
+
+        int64_t gsum = 0, msum = 0;
+        uint32_t mono = 0;
+        for (int64_t q = p0; q < p1; ++q) {
+            const PodLimits l = pod_limits(ps, q);
+            if (!in_range(l.gpu) || !in_range(l.mem)) {
+                *err = "pack_nodes: flex limit of a pod on node " + std::to_string(n) + " out of range";
+                return FGS_E_RANGE;
+            }
+            gsum = wrap_add(gsum, l.gpu);
+            msum = wrap_add(msum, l.mem);
+            if (!l.gpu_exist && !l.mem_exist) continue;       // gpu_node.go:85-88
+            const int32_t idx = ps->index_annot[q];
+            if (idx == FGS_ANNOT_NONE) continue;              // :91-96
+            if (idx < 0 || idx >= gpu_cnt) {                  // :110 / :115 index out of range
+                fl |= FGS_NF_REF_PANIC;
+                continue;
+            }
+            if (l.gpu_exist) mono |= 1u << idx;
+            if (l.mem_exist) {
+                int64_t& u = t.used_mem[(size_t)((int64_t)idx * N + n)];
+                u = wrap_add(u, l.mem);
+            }
+        }
+        if (!in_range(gsum) || !in_range(msum)) {
+            *err = "pack_nodes: flex limit sum of node " + std::to_string(n) + " out of range";
+            return FGS_E_RANGE;
+        }
+        for (int d = 0; d < D; ++d)
+            if (!in_range(t.used_mem[(size_t)((int64_t)d * N + n)])) {
+                *err = "pack_nodes: per-device used memory of node " + std::to_string(n) + " out of range";
+                return FGS_E_RANGE;
+            }
+        t.flex_gpu_sum[(size_t)n] = gsum;
+        t.flex_mem_sum[(size_t)n] = msum;
+        t.monopoly_mask[(size_t)n] = mono;
+        t.flags[(size_t)n] = fl;
+    }
+    t.make_view();
+    return FGS_OK;
+}
+
+int pack_pods(const fgs_podset* pods, PackedPods* out, std::string* err) {
+    if (!pods || pods->n_pods < 0 || pods->n_scalars < 2 || pods->n_scalars > FGS_MAX_SCALARS) {
+        *err = "pack_pods: bad podset header";
+        return FGS_E_INVALID;
+    }
+    const int64_t P = pods->n_pods;
+    const int S = pods->n_scalars;
+    PackedPods& t = *out;
+    t.n = P;
+    t.S = S;
+    auto z = [&](std::vector<int64_t>& v, int64_t k) { v.assign((size_t)k, 0); };
+    z(t.flex_gpu_limit, P), z(t.flex_mem_limit, P), z(t.req_mcpu, P), z(t.req_mem, P), z(t.req_eph, P);
+    z(t.req_scalar, P * S), z(t.nz_mcpu, P), z(t.nz_mem, P);
+    t.flags.assign((size_t)P, 0);
+    t.req_scalar_present.assign((size_t)P, 0);
+    t.ns.assign((size_t)P, 0);
+    t.pg.assign((size_t)P, -1);
+    t.priority.assign((size_t)P, 0);
+    for (int64_t i = 0; i < P; ++i) {
+        const PodLimits l = pod_limits(pods, i);
+        const PodRequest r = pod_request(pods, i);
+        bool ok = in_range(l.gpu) && in_range(l.mem) && in_range(r.score_mcpu) && in_range(r.score_mem);
+        for (int k = 0; k < 3 + S; ++k) ok = ok && in_range(r.v[k]);
+        if (!ok) {
+            *err = "pack_pods: a quantity of pod " + std::to_string(i) + " is out of range";
+            return FGS_E_RANGE;
+        }
+        uint32_t fl = 0;
+        if (l.gpu_exist) fl |= FGS_PF_GPU_LIMIT;
+        if (l.mem_exist) fl |= FGS_PF_MEM_LIMIT;
+        // fit.go:270-275: MilliCPU == 0 && Memory == 0 && EphemeralStorage == 0 && len(ScalarResources) == 0
+        if (r.v[0] == 0 && r.v[1] == 0 && r.v[2] == 0 && r.scalar_keys == 0) fl |= FGS_PF_REQ_NONE;
+        t.flags[(size_t)i] = fl;
+        t.flex_gpu_limit[(size_t)i] = l.gpu;
+        t.flex_mem_limit[(size_t)i] = l.mem;
+        t.req_mcpu[(size_t)i] = r.v[0];
+        t.req_mem[(size_t)i] = r.v[1];
+        t.req_eph[(size_t)i] = r.v[2];
+        for (int s = 0; s < S; ++s) t.req_scalar[(size_t)(s * P + i)] = r.v[3 + s];
+        t.req_scalar_present[(size_t)i] = r.scalar_keys;
+        t.nz_mcpu[(size_t)i] = r.score_mcpu;
+        t.nz_mem[(size_t)i] = r.score_mem;
+        t.ns[(size_t)i] = pods->ns ? pods->ns[i] : 0;
+        t.pg[(size_t)i] = pods->pg ? pods->pg[i] : -1;
+        t.priority[(size_t)i] = pods->priority ? pods->priority[i] : 0;
+    }
+    t.make_view();
+    return FGS_OK;
+}
+
+} // namespace fgs

@@ -1,0 +1,41 @@
+// pack.h — host packer: object snapshot → SoA int64 tables (the new PreFilter/PreScore stage's
+// "pack" step, north_star). Product code.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "../../include/fgs.h"
+
+namespace fgs {
+
+struct PackedNodes {
+    int64_t n = 0;
+    int S = 2, D = 1;
+    std::vector<int64_t> alloc_mcpu, alloc_mem, alloc_eph, alloc_pods, req_mcpu, req_mem, req_eph, num_pods, nz_mcpu,
+        nz_mem, alloc_scalar, req_scalar, flex_gpu_sum, flex_mem_sum, used_mem;
+    std::vector<uint32_t> alloc_scalar_present, monopoly_mask, flags;
+    fgs_node_table view;
+    void make_view();
+};
+
+struct PackedPods {
+    int64_t n = 0;
+    int S = 2;
+    std::vector<int64_t> flex_gpu_limit, flex_mem_limit, req_mcpu, req_mem, req_eph, req_scalar, nz_mcpu, nz_mem;
+    std::vector<uint32_t> flags, req_scalar_present;
+    std::vector<int32_t> ns, pg, priority;
+    fgs_pod_table view;
+    void make_view();
+};
+
+// Both return FGS_OK or a negative FGS_E_* with `err` set.
+int pack_nodes(const fgs_snapshot* snap, PackedNodes* out, std::string* err);
+int pack_pods(const fgs_podset* pods, PackedPods* out, std::string* err);
+
+// Range rule shared by the packer and the table-level entry points: every quantity must satisfy
+// |v| < 2^53 so that the sums the reference forms in int64 (and in arbitrary-precision Quantity,
+// pkg/flexgpu/flex_gpu.go:85-98) cannot wrap where Go would not.
+constexpr int64_t kMaxQuantity = (int64_t)1 << 53;
+inline bool in_range(int64_t v) { return v > -kMaxQuantity && v < kMaxQuantity; }
+
+} // namespace fgs

@@ -1,0 +1,221 @@
+/*
+ * fgs.h — C ABI of libfgs, the B200-native batched Filter+Score engine.
+ *
+ * libfgs replaces ONE path of the reference scheduler (WLBF/flex-gpu-scheduler, a fork of
+ * kubernetes-sigs/scheduler-plugins): the per-cycle evaluation of pending pods against every
+ * NodeInfo of the snapshot — Filter, Score, NormalizeScore, weighting and selectHost for the
+ * FlexGPU, NodeResourcesFit (Least/MostAllocated) and NodeResourcesAllocatable plugins, plus the
+ * PreFilter arithmetic of Coscheduling (PodGroup minMember / MinResources) and CapacityScheduling
+ * (ElasticQuota). The Go plugins keep their framework interfaces; a PreFilter/PreScore stage
+ * fills the flat tables of fgs_types.h, calls these entry points through cgo and
+ * answers Filter/Score from the returned bitmap / score matrix.
+ *
+ * The reference has no FFI of its own (it is pure Go, CGO_ENABLED=0, Makefile:17); each entry
+ * point therefore cites the Go function(s) whose work it takes over. Paths are relative to the
+ * reference repo; "sched/" abbreviates vendor/k8s.io/kubernetes/pkg/scheduler/.
+ *
+ * Conventions: every function returns 0 on success or a negative FGS_E_* code;
+ * fgs_last_error(engine) gives the message. All pointers are plain host pointers unless the
+ * name says `dev`. No function falls back to a CPU path: without a usable CUDA device
+ * fgs_create fails with FGS_E_CUDA.
+ *
+ * Threading: one caller at a time per engine (the scheduling goroutine); result buffers handed
+ * back by fgs_evaluate are read-only afterwards and may be read concurrently (the 16 Filter /
+ * Score goroutines of sched/framework/parallelize/parallelism.go:27).
+ */
+#ifndef FGS_H
+#define FGS_H
+
+#include "fgs_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FGS_OK 0
+#define FGS_E_INVALID (-1)   /* bad argument / table failed validation */
+#define FGS_E_CUDA (-2)      /* CUDA runtime error (message has the cudaError string) */
+#define FGS_E_RANGE (-3)     /* a quantity is outside the supported int64 range (|v| >= 2^53) */
+#define FGS_E_STATE (-4)     /* call sequence error (e.g. evaluate before upload) */
+#define FGS_E_TOO_LARGE (-5) /* exceeds a stated fixed maximum */
+
+typedef struct fgs_engine fgs_engine;
+
+typedef struct fgs_config {
+    int32_t device;            /* CUDA device ordinal this engine owns */
+    int32_t n_scalars;         /* S, number of scalar resource slots (2..FGS_MAX_SCALARS) */
+    int64_t node_index_base;   /* global index of this shard's first node (multi-GPU sharding) */
+    int64_t total_nodes;       /* nodes over all shards (== shard size on one GPU) */
+    uint64_t select_seed;      /* seed of the selectHost tie-break hash */
+    void* stream;              /* cudaStream_t to run on, NULL = a stream the engine creates */
+} fgs_config;
+
+/* Per-pod outputs of one evaluation (host buffers owned by the caller, each [P]). */
+typedef struct fgs_results {
+    int32_t* feasible_count;   /* len(feasibleNodes) — sched/generic_scheduler.go:106-127 */
+    int32_t* selected_node;    /* global node index chosen by selectHost, -1 when none feasible */
+    int64_t* selected_score;   /* its total score */
+    uint32_t* pod_err;         /* FGS_PODERR_* */
+    /* optional full planes; NULL = leave on the device */
+    uint32_t* feasible_bitmap; /* [P][words_per_row]; bit n%32 of word n/32 = node n feasible */
+    int64_t* scores;           /* [P][score_row_stride] total weighted score per node */
+    int64_t words_per_row;     /* filled in by the engine */
+    int64_t score_row_stride;  /* filled in by the engine */
+} fgs_results;
+
+typedef struct fgs_eval_opts {
+    uint32_t emit_mask;   /* score plugins summed into `scores` (0 = all of score_mask); lets a
+                             caller read ONE plugin's normalised scores (the Go Score/NormalizeScore
+                             answers) */
+    uint32_t emit_raw;    /* 1: emit the plugin's raw Score instead of the normalised×weight value */
+    uint32_t skip_pass_b; /* 1: Filter only (bitmap + counts come from the reduce pass) */
+    uint32_t _pad;
+} fgs_eval_opts;
+
+/* device-side buffers of the current batch, for callers that keep results in HBM or that run
+ * the cross-GPU merges themselves (torch.distributed / NCCL on these pointers) */
+typedef struct fgs_device_view {
+    void* reduce_max;      /* int64 [FGS_REDUCE_ROWS][P_pad]: merge across shards with MAX */
+    void* reduce_sum;      /* int64 [P_pad] feasible counts: merge with SUM */
+    void* select_key;      /* int64 [3][P_pad]: row 0 packed (score,hash,node) keys, row 1 score-range
+                              error flag, row 2 score-time panic flag: merge with MAX */
+    void* feasible_bitmap; /* uint32 [P][words_per_row] */
+    void* scores;          /* int64 [P][score_row_stride] */
+    int64_t p_pad;
+    int64_t words_per_row;
+    int64_t score_row_stride;
+    void* stream;          /* the cudaStream_t all engine work is ordered on */
+} fgs_device_view;
+
+#define FGS_REDUCE_ROWS 6 /* flex max, alloc hi, -alloc lo, filter-panic flag, (2 spare) */
+
+/* ---- lifecycle ------------------------------------------------------------------------- */
+
+/* Replaces plugin construction: flexgpu.New (pkg/flexgpu/flex_gpu.go:37-39), NewAllocatable
+ * (pkg/noderesources/allocatable.go:79-118), NewFit (sched/framework/plugins/noderesources/
+ * fit.go:104-130) — the engine is the shared state those plugins point at. */
+int fgs_create(const fgs_config* cfg, fgs_engine** out);
+void fgs_destroy(fgs_engine* e);
+const char* fgs_last_error(const fgs_engine* e); /* e may be NULL: last create error */
+
+/* Plugin args → engine configuration. Mirrors NodeResourcesAllocatableArgs / NodeResourcesFitArgs
+ * decoding and validation (pkg/noderesources/allocatable.go:51-58,84-108; weights per
+ * sched/framework/runtime/framework.go:395-415). */
+int fgs_set_plugins(fgs_engine* e, const fgs_plugin_cfg* cfg);
+
+/* ---- packing (host) -------------------------------------------------------------------- */
+
+/* Object snapshot → SoA node table. Takes over the per-call object walks of
+ * nodeResourceLimitSum (pkg/flexgpu/flex_gpu.go:133-140) and NewGPUNode/constructGPUs
+ * (pkg/flexgpu/gpu_node.go:30-120), and reads NodeInfo aggregates
+ * (sched/framework/types.go:359-419). The returned table is owned by the engine and valid
+ * until the next fgs_pack_nodes or fgs_destroy. */
+int fgs_pack_nodes(fgs_engine* e, const fgs_snapshot* snap, const fgs_node_table** out);
+
+/* Pending pods → SoA pod table. Takes over podResourceLimit (flex_gpu.go:121-131),
+ * computePodResourceRequest (fit.go:162-180) and calculatePodResourceRequest
+ * (sched/framework/plugins/noderesources/resource_allocation.go:119-143). */
+int fgs_pack_pods(fgs_engine* e, const fgs_podset* pods, const fgs_pod_table** out);
+
+/* ---- upload + evaluate ----------------------------------------------------------------- */
+
+/* H2D of the node table and derivation of the pod-independent columns on the GPU
+ * (memEach, per-device max free memory, GPUScore/MemScore — gpu_node.go:55,179-199 —
+ * Allocatable raw score — allocatable.go:120-143). Replaces Cache.UpdateSnapshot's role as the
+ * per-cycle input (sched/internal/cache/cache.go:197-276). */
+int fgs_upload_nodes(fgs_engine* e, const fgs_node_table* t);
+
+/* Same for a subset of rows: `rows` has n_dirty rows, row r replaces node dirty_idx[r]. */
+int fgs_update_nodes(fgs_engine* e, const fgs_node_table* rows, const int64_t* dirty_idx);
+
+/* One batched scheduling evaluation = for every pod: findNodesThatPassFilters over all nodes
+ * (sched/generic_scheduler.go:266-338 with percentageOfNodesToScore=100; FlexGPU.Filter
+ * flex_gpu.go:41-119; Fit.Filter fit.go:221-329), RunScorePlugins (runtime/framework.go:861-933;
+ * FlexGPU.Score/NormalizeScore flex_gpu.go:142-176; Fit.Score fit.go:332-339 with
+ * least_allocated.go:29-57 / most_allocated.go:29-61; Allocatable.Score/NormalizeScore
+ * allocatable.go:61-72,146-171), the per-node sum (generic_scheduler.go:440-447) and selectHost
+ * (:146-167). Host pod table in, per-pod results out (H2D + kernels + D2H). */
+int fgs_evaluate(fgs_engine* e, const fgs_pod_table* pods, const fgs_eval_opts* opts,
+                 fgs_results* out);
+
+/* The same evaluation in stages, for node-sharded multi-GPU runs (one engine per GPU/process):
+ *   fgs_stage_pods → fgs_pass_reduce → [merge reduce_max / reduce_sum across shards]
+ *   → fgs_pass_emit → [merge select_key across shards] → fgs_fetch_results.
+ * All stages are asynchronous on the engine stream except fgs_fetch_results. */
+int fgs_stage_pods(fgs_engine* e, const fgs_pod_table* pods);
+int fgs_pass_reduce(fgs_engine* e);
+int fgs_pass_emit(fgs_engine* e, const fgs_eval_opts* opts);
+int fgs_fetch_results(fgs_engine* e, fgs_results* out);
+int fgs_get_device_view(fgs_engine* e, fgs_device_view* v);
+int fgs_synchronize(fgs_engine* e);
+
+/* Filter verdicts of the last staged batch as framework.Code bytes, out[P][n_nodes]:
+ *   plugin == FGS_PL_FLEXGPU  what FlexGPU.Filter returns (flex_gpu.go:41-119): 0 Success,
+ *                             2 Unschedulable, 3 UnschedulableAndUnresolvable
+ *   plugin == FGS_PL_FIT      what Fit.Filter returns (fit.go:221-238)
+ *   plugin == 0               RunFilterPlugins' merged result (runtime/framework.go:667-693):
+ *                             low nibble = code, high nibble = id of the plugin that failed
+ * 0xF1 marks a (pod,node) on which the reference would panic inside NewGPUNode. This is the
+ * diagnosis plane the Go Filter methods answer from (NodeToStatusMap, generic_scheduler.go:309-313). */
+int fgs_status_plane(fgs_engine* e, uint32_t plugin, uint8_t* out);
+
+/* ---- coscheduling / capacity scheduling --------------------------------------------------- */
+
+/* PodGroupManager.PreFilter for every pending pod (pkg/coscheduling/core/core.go:149-196 incl.
+ * CheckClusterResource :322-342 and getNodeResource :349-382) and CalculateAssignedPods / Permit
+ * (:199-216,301-318). Needs fgs_upload_nodes first; `snap` supplies the pods already on nodes.
+ * prefilter_code[p]: 0 pass, 1 denied, 2 too few siblings, 3 resource gap.
+ * permit_status[p]: 0 Success, 1 Wait, 2 PodGroupNotSpecified, 3 PodGroupNotFound.
+ * assigned[g]: CalculateAssignedPods. Any output may be NULL. */
+int fgs_gang_check(fgs_engine* e, const fgs_snapshot* snap, const fgs_podset* pending,
+                   const fgs_podgroups* pgs, uint8_t* prefilter_code, uint8_t* permit_status,
+                   int32_t* assigned);
+
+/* CapacityScheduling.PreFilter for every pending pod
+ * (pkg/capacityscheduling/capacity_scheduling.go:201-275; elasticquota.go:40-51,90-100,161-181).
+ * code[p]: 0 Success, 1 over Max, 2 aggregated used over Σmin. `nominated` may be NULL. */
+int fgs_quota_check(fgs_engine* e, const fgs_pod_table* pods, const fgs_quotas* q,
+                    const fgs_pod_table* nominated, const int64_t* pod_uid,
+                    const int64_t* nominated_uid, uint8_t* code);
+
+/* ---- timings ---------------------------------------------------------------------------- */
+
+typedef struct fgs_timings {
+    float h2d_ms, reduce_ms, emit_ms, d2h_ms; /* last fgs_evaluate, CUDA events on the stream */
+    int64_t kernel_launches;                  /* kernels launched by this engine so far */
+} fgs_timings;
+int fgs_get_timings(fgs_engine* e, fgs_timings* t);
+
+/* ---- synthetic clusters (deterministic) ------------------------------------ */
+
+typedef struct fgs_synth_params {
+    uint64_t seed_nodes, seed_pods;
+    int64_t n_nodes, n_pending;
+    int32_t n_scalars, n_devices;
+    int32_t max_existing_pods;     /* pods per node ~ U{0..max} */
+    /* pending mix, per mille (rest = whole-GPU) */
+    int32_t pm_fractional, pm_whole, pm_nogpu, pm_degenerate;
+    int32_t pm_missing_req, pm_init_ctr, pm_overhead, pm_two_ctrs, pm_extra_scalar;
+    /* node quirks, per mille */
+    int32_t pm_quirk_nodes, pm_nongpu_nodes, pm_panic_nodes, pm_invalid_nodes;
+    /* coscheduling */
+    int64_t n_groups;
+    int32_t min_member_lo, min_member_hi, pm_groups_placed, pm_groups_short, pm_neg_left_nodes;
+    /* capacity scheduling */
+    int64_t n_namespaces;
+    int32_t pm_pods_without_eq, n_nominated;
+} fgs_synth_params;
+
+typedef struct fgs_synth fgs_synth;
+int fgs_synth_create(const fgs_synth_params* p, fgs_synth** out);
+void fgs_synth_destroy(fgs_synth* s);
+const fgs_snapshot* fgs_synth_snapshot(const fgs_synth* s);
+const fgs_podset* fgs_synth_pending(const fgs_synth* s);
+const fgs_podset* fgs_synth_nominated(const fgs_synth* s);
+const fgs_podgroups* fgs_synth_podgroups(const fgs_synth* s);
+const fgs_quotas* fgs_synth_quotas(const fgs_synth* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FGS_H */

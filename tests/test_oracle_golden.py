@@ -1,0 +1,67 @@
+"""CPU tests: the oracle (oracle/ref_walk.cpp) against the golden vectors transcribed from the
+reference's own unit tests (tests/golden/make_golden.py cites every case)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import golden_cases as G
+import flex_gpu_scheduler_b200 as fgs
+from flex_gpu_scheduler_b200 import _lib as L
+
+FW_CODE = {0: 0, 1: 2, 2: 2}  # oracle quota code → framework.Code (Success / Unschedulable)
+
+
+@pytest.mark.parametrize("case", [c for c in G.load("allocatable") if "want_err" not in c], ids=lambda c: c["name"][:60])
+def test_allocatable_scores(oracle, case):
+    # pkg/noderesources/allocatable_test.go:112-219
+    snap, pend, resources, mode = G.allocatable_case(case)
+    cfg = fgs.plugin_cfg(filter_plugins=(), score_plugins=(("NodeResourcesAllocatable", 1),), alloc_mode=mode, alloc_resources=resources)
+    r = oracle.evaluate(snap.ptr, pend.ptr, cfg, per_plugin=True)
+    assert r.norm_alloc[0].tolist() == case["expected"]
+    assert r.total[0].tolist() == case["expected"]
+    assert int(r.pod_err[0]) == 0
+
+
+def test_gang_prefilter(oracle):
+    # pkg/coscheduling/core/core_test.go:42-176
+    g = G.load("gang_prefilter")
+    for case in g["cases"]:
+        snap, pend, pgs, unlisted, me = G.gang_prefilter_case(g, case)
+        code = oracle.gang_prefilter(snap.ptr, pend.ptr, pgs.ptr, unlisted=unlisted)
+        assert (code[me] == 0) == case["expected"], case["name"]
+
+
+def test_gang_permit(oracle):
+    # pkg/coscheduling/core/core_test.go:178-234
+    g = G.load("gang_permit")
+    for case in g["cases"]:
+        snap, pend, pgs = G.gang_permit_case(g, case)
+        st, assigned = oracle.gang_permit(snap.ptr, pend.ptr, pgs.ptr)
+        assert int(st[0]) == case["expected"], case["name"]
+
+
+def test_check_cluster_resource(oracle):
+    # pkg/coscheduling/core/core_test.go:303-355
+    c = G.load("check_cluster_resource")
+    for case in c["cases"]:
+        snap, req, keys, desired = G.check_cluster_resource_case(c, case)
+        ok = oracle.check_cluster_resource_raw(snap.ptr, req, keys, desired)
+        assert bool(ok) == case["expected"], case["name"]
+
+
+def test_capacity_prefilter(oracle):
+    # pkg/capacityscheduling/capacity_scheduling_test.go:52-164
+    for case in G.load("capacity_prefilter"):
+        pend, qs = G.capacity_case(case)
+        code = oracle.quota_prefilter(pend.ptr, qs.ptr)
+        assert [FW_CODE[int(c)] for c in code] == case["expected"], case["name"]
+
+
+def test_capacity_reject_reasons(oracle):
+    # the two rejections of TestPreFilter come from different checks (capacity_scheduling.go:266 vs :270)
+    cases = G.load("capacity_prefilter")
+    pend, qs = G.capacity_case(cases[0])
+    assert oracle.quota_prefilter(pend.ptr, qs.ptr).tolist() == [0, 1]
+    pend, qs = G.capacity_case(cases[1])
+    assert oracle.quota_prefilter(pend.ptr, qs.ptr).tolist() == [2]
