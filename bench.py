@@ -1,0 +1,388 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the batched Filter+Score path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--config C] [--impl ours|reference]
+
+One "step" = one full evaluation of the pending-pod batch against every node of this rank's shard:
+reduce pass (Filter + bitmap + normaliser reductions), the cross-shard merges (N > 1), emit pass
+(Score / NormalizeScore / weights / sum / selectHost key). The timed region starts with the node and
+pod tables resident in HBM. Prints ONE JSON line on rank 0.
+
+  N = 1   workload = config 2 (5k nodes × 8 GPUs, 100k mixed pods, FlexGPU + Fit filter,
+          FlexGPU + LeastAllocated scores) — BASELINE.json configs[1]
+  N > 1   weak scaling: every rank holds a config-2-sized node shard (5k nodes) of a 5k·N-node
+          cluster, all ranks see the same 100k pods; per-pod reductions are merged with NCCL
+          all-reduce (MAX / SUM) over NVLink. `--config 5` runs the 50k-node / 1M-pod config
+          node-sharded instead (strong scaling).
+
+--impl reference times the reference's own algorithm on the host cores: the Go plugins cannot be built
+here (no Go toolchain), so this is the object-walking C++ restatement under oracle/ ("port").
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "pod_x_node_filter_score_evals_per_sec"
+UNIT = "evals/s"
+BATCH = 65536  # pods per evaluation batch for configs whose score matrix would not fit otherwise
+
+
+def workload_name(cfg_id, n_nodes, n_pods, n_gpus, scaling):
+    return (f"C{cfg_id}: {n_nodes} nodes x 8 GPUs, {n_pods} pending pods, FlexGPU+NodeResourcesFit filter, "
+            f"FlexGPU+{'NodeResourcesAllocatable(Least)' if cfg_id == 1 else 'LeastAllocated'} scores, "
+            f"{'single GPU' if n_gpus == 1 else f'nodes sharded over {n_gpus} GPUs ({scaling})'}")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device = device
+        self.rows = []
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.device)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except Exception:
+                continue
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            for nm, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_port_baseline(fgs, synth, cfg, budget_s=12.0, workers=None):
+    """Time the oracle (object-walking port of the Go plugins) on the host cores on a bounded sample."""
+    from oracle import oracle
+    cores = os.cpu_count() or 1
+    if workers is None:
+        workers = cores
+    N, P = synth.n_nodes, synth.n_pending
+    probe = min(P, 32)
+    t0 = time.perf_counter()
+    oracle.evaluate(synth.snapshot, synth.pending, cfg, 0, probe, workers=workers, planes=())
+    dt = max(time.perf_counter() - t0, 1e-6)
+    n = int(min(P, max(probe, probe * budget_s / dt)))
+    t0 = time.perf_counter()
+    oracle.evaluate(synth.snapshot, synth.pending, cfg, 0, n, workers=workers, planes=())
+    dt = time.perf_counter() - t0
+    return {"value": n * N / dt, "unit": UNIT, "cores": cores, "threads": workers, "kind": "port",
+            "sample": f"first {n} pending pods x all {N} nodes, {workers} worker threads in the reference's chunked "
+                      f"parallelize.Until shape, {dt:.1f} s wall"}
+
+
+def run_reference(args):
+    """--impl reference: the CPU restatement of the Go plugins, all host threads, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import flex_gpu_scheduler_b200 as fgs
+    from oracle import oracle
+    cfg_id = args.config or 2
+    n_nodes = fgs.CONFIGS[cfg_id]["n_nodes"] * (args.gpus if (args.gpus > 1 and cfg_id != 5) else 1)
+    cores = os.cpu_count() or 1
+    # calibrate the per-step sample so that the whole run stays within a few minutes
+    s = fgs.config_synth(cfg_id, n_nodes=n_nodes, n_pending=4096)
+    cfg = fgs.config_plugins(cfg_id)
+    t0 = time.perf_counter()
+    oracle.evaluate(s.snapshot, s.pending, cfg, 0, 16, workers=cores, planes=())
+    per_pod = max((time.perf_counter() - t0) / 16, 1e-6)
+    total_steps = args.steps + args.warmup
+    n = int(max(16, min(4096, (120.0 / total_steps) / per_pod)))
+    for _ in range(args.warmup):
+        oracle.evaluate(s.snapshot, s.pending, cfg, 0, n, workers=cores, planes=())
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle.evaluate(s.snapshot, s.pending, cfg, 0, n, workers=cores, planes=())
+    dt = time.perf_counter() - t0
+    val = args.steps * n * n_nodes / dt
+    scaling = "strong" if cfg_id == 5 else "weak"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "int64",
+        "data": "synthetic",
+        "config": {"workload": workload_name(cfg_id, n_nodes, fgs.CONFIGS[cfg_id]["n_pending"], args.gpus, scaling),
+                   "note": "Go toolchain absent: oracle/ref_walk.cpp, the object-walking C++ restatement of the Go plugins, "
+                           "percentageOfNodesToScore=100"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "threads": cores, "kind": "port",
+                         "sample": f"each step = first {n} pending pods x all {n_nodes} nodes"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def torch_view(ptr, nbytes_elems, dtype, torch):
+    """zero-copy torch tensor over a device pointer owned by the engine"""
+    class _A:
+        pass
+    a = _A()
+    a.__cuda_array_interface__ = {"shape": (nbytes_elems,), "typestr": "<i8", "data": (int(ptr), False), "version": 2}
+    return torch.as_tensor(a, device="cuda")
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import flex_gpu_scheduler_b200 as fgs
+    from flex_gpu_scheduler_b200 import _lib as L
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cfg_id = args.config or 2
+    base = fgs.CONFIGS[cfg_id]
+    strong = cfg_id == 5
+    scaling = "strong" if strong else "weak"
+    n_total = base["n_nodes"] * (1 if strong else world)
+    n_pods = args.pods or base["n_pending"]
+    # every rank generates the same cluster (deterministic) and packs only its node range
+    synth = fgs.config_synth(cfg_id, n_nodes=n_total, n_pending=n_pods)
+    per = (n_total + world - 1) // world
+    n0, n1 = min(n_total, rank * per), min(n_total, (rank + 1) * per)
+    plugins = fgs.config_plugins(cfg_id)
+    stream = torch.cuda.Stream()
+    eng = fgs.Engine(device=local, n_scalars=2, node_index_base=n0, total_nodes=n_total, stream=stream.cuda_stream)
+    eng.set_plugins(plugins)
+    pk_n, pk_p = fgs.Packer(2), fgs.Packer(2)
+    eng.upload_nodes(pk_n.nodes(synth.snapshot, n0, n1))
+    n_shard = n1 - n0
+
+    # pods go through in batches when the score matrix of the whole set would not fit comfortably
+    n_pad = (max(n_shard, 1) + 511) // 512 * 512
+    batch = n_pods if n_pods * n_pad * 8 <= 48 * 2 ** 30 else BATCH
+    batches = [(b, min(n_pods, b + batch)) for b in range(0, n_pods, batch)]
+    packers = [fgs.Packer(2) for _ in batches]
+    tables = [pk.pods(synth.pending, b0, b1) for pk, (b0, b1) in zip(packers, batches)]
+    multi = len(batches) > 1
+
+    def merges_after_reduce(view):
+        if world == 1:
+            return
+        rm = torch_view(view.reduce_max, L.FGS_REDUCE_ROWS * view.p_pad, "i8", torch)
+        rs = torch_view(view.reduce_sum, view.p_pad, "i8", torch)
+        dist.all_reduce(rm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(rs, op=dist.ReduceOp.SUM)
+
+    def merges_after_emit(view):
+        if world == 1:
+            return
+        sk = torch_view(view.select_key, 3 * view.p_pad, "i8", torch)
+        dist.all_reduce(sk, op=dist.ReduceOp.MAX)
+
+    with torch.cuda.stream(stream):
+        lib = L.load()
+        step_evals = n_pods * n_total  # whole job: all pods x all nodes of all shards
+
+        def one_step(ev=None):
+            for t in tables:
+                if multi:  # only one batch is resident at a time: restaging is part of the step
+                    eng.stage_pods(t)
+                v = eng.device_view() if multi else view
+                if ev is not None:
+                    e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+                    ev.append(e)
+                    e[0].record(stream)
+                eng.pass_reduce()
+                if ev is not None:
+                    e[1].record(stream)
+                merges_after_reduce(v)
+                if ev is not None:
+                    e[2].record(stream)
+                eng.pass_emit()
+                if ev is not None:
+                    e[3].record(stream)
+                merges_after_emit(v)
+
+        eng.stage_pods(tables[0])
+        view = eng.device_view()
+        eng.synchronize()
+        for _ in range(args.warmup):
+            one_step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        launches0 = eng.timings()["kernel_launches"]
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        evs = []
+        e_start, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e_start.record(stream)
+        for k in range(args.steps):
+            one_step(evs)
+        e_end.record(stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = e_start.elapsed_time(e_end)
+        launches = eng.timings()["kernel_launches"] - launches0
+        reduce_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
+        emit_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / args.steps
+        if world > 1:
+            t = torch.tensor([ms, reduce_ms, emit_ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, reduce_ms, emit_ms = [float(x) for x in t.tolist()]
+
+        # ---- end to end through the public C-ABI call with HOST buffers ---------------------------------
+        # fgs_evaluate: H2D of the pod table from pinned staging + both passes + D2H of the per-pod results.
+        # With N > 1 the staged calls are used so that the NCCL merges sit between the passes.
+        res_holder = [None]
+
+        def e2e_step():
+            for t in tables:
+                if world == 1:
+                    res_holder[0] = eng.evaluate(t)
+                else:
+                    eng.stage_pods(t)
+                    v = eng.device_view()
+                    eng.pass_reduce()
+                    merges_after_reduce(v)
+                    eng.pass_emit()
+                    merges_after_emit(v)
+                    res_holder[0] = eng.fetch_results()
+
+        e2e_steps = max(1, min(args.steps, 5))
+        e2e_step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        e_s, e_e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e_s.record(stream)
+        for _ in range(e2e_steps):
+            e2e_step()
+        e_e.record(stream)
+        torch.cuda.synchronize()
+        e2e_wall = time.perf_counter() - t0
+        e2e_ms = max(e_s.elapsed_time(e_e), 1e3 * e2e_wall)  # host-side packing into pinned memory counts too
+        if world > 1:
+            t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_ms = float(t.item())
+        clocks = sampler.stop() if rank == 0 else None
+
+    if rank == 0:
+        res = res_holder[0]
+        P, N = n_pods, n_shard
+        p_pad = sum((b1 - b0 + 63) // 64 * 64 for b0, b1 in batches)
+        S = 2
+        # algorithmic bytes of the dominant kernel (emit pass): one int64 score per (pod,node) + each table once
+        nd_cols, pd_cols = 15 + 2 * S, 8 + S
+        emit_bytes = P * N * 8 + N * nd_cols * 8 + P * (pd_cols + 4) * 8
+        path_bytes = P * N * (8 + 1 / 8) + 2 * (N * nd_cols * 8 + P * pd_cols * 8) + P * 10 * 8
+        peak, peak_src = measured_peak_gbs()
+        achieved = emit_bytes / (emit_ms * 1e-3) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "r01_emit_traffic.json")
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        value = args.steps * step_evals / (ms * 1e-3)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "int64",
+            "data": "synthetic",
+            "config": {"workload": workload_name(cfg_id, n_total, n_pods, world, scaling), "nodes_per_gpu": n_shard,
+                       "l2": "outputs (8 B per eval, %.1f GB per step per GPU) exceed the 126 MB L2; node and pod tables "
+                             "(%.1f MB) are L2-resident by design" % (P * N * 8 / 1e9, (N * nd_cols * 8 + P * pd_cols * 8) / 1e6),
+                       "parity": "all nodes evaluated for every pod (percentageOfNodesToScore=100)",
+                       "pod_batches": len(batches)},
+            "kernel_ms": {"reduce_pass": reduce_ms, "emit_pass": emit_ms},
+            "scheduling_cycles_per_sec": args.steps * n_pods / (ms * 1e-3),
+            "roofline": {"bound": "hbm", "kernel": "eval_kernel<EMIT>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": emit_bytes,
+                         "path_frac": (path_bytes / ((reduce_ms + emit_ms) * 1e-3) / 1e9) / peak},
+            "e2e": {"value": e2e_steps * step_evals / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pd_cols * p_pad * 8,
+                    "d2h_bytes_per_step": 10 * p_pad * 8, "steps": e2e_steps,
+                    "api": "fgs_evaluate (host pod table in, per-pod selected node / count / error out)"
+                    if world == 1 else "fgs_stage_pods + fgs_pass_reduce + NCCL + fgs_pass_emit + NCCL + fgs_fetch_results"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "selected_nodes_checksum": int(res.selected_node.astype("int64").sum()) if res is not None else None,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_port_baseline(fgs, synth, plugins)
+        print(json.dumps(line))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--config", type=int, default=0, help="1..5 (default 2)")
+    ap.add_argument("--pods", type=int, default=0, help="override the number of pending pods")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

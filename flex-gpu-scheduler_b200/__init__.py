@@ -4,7 +4,7 @@ The directory name follows the reference repo (``flex-gpu-scheduler``) and is no
 identifier; import it as ``flex_gpu_scheduler_b200`` (the alias package at the repo root).
 """
 from . import _lib
-from .api import Engine, FgsError, Results, Synth, plugin_cfg
+from .api import Engine, FgsError, Packer, Results, Synth, plugin_cfg
 from .configs import CONFIGS, config_plugins, config_synth
 
-__all__ = ["Engine", "FgsError", "Results", "Synth", "plugin_cfg", "CONFIGS", "config_plugins", "config_synth", "_lib"]
+__all__ = ["Engine", "FgsError", "Packer", "Results", "Synth", "plugin_cfg", "CONFIGS", "config_plugins", "config_synth", "_lib"]

@@ -141,8 +141,11 @@ ABI = {
     "fgs_destroy": (None, [C.c_void_p]),
     "fgs_last_error": (C.c_char_p, [C.c_void_p]),
     "fgs_set_plugins": (C.c_int, [C.c_void_p, C.POINTER(PluginCfg)]),
-    "fgs_pack_nodes": (C.c_int, [C.c_void_p, C.POINTER(Snapshot), C.POINTER(C.POINTER(NodeTable))]),
-    "fgs_pack_pods": (C.c_int, [C.c_void_p, C.POINTER(Podset), C.POINTER(C.POINTER(PodTable))]),
+    "fgs_packer_create": (C.c_int, [C.c_int32, C.POINTER(C.c_void_p)]),
+    "fgs_packer_destroy": (None, [C.c_void_p]),
+    "fgs_packer_error": (C.c_char_p, [C.c_void_p]),
+    "fgs_packer_nodes": (C.c_int, [C.c_void_p, C.POINTER(Snapshot), C.c_int64, C.c_int64, C.POINTER(C.POINTER(NodeTable))]),
+    "fgs_packer_pods": (C.c_int, [C.c_void_p, C.POINTER(Podset), C.c_int64, C.c_int64, C.POINTER(C.POINTER(PodTable))]),
     "fgs_upload_nodes": (C.c_int, [C.c_void_p, C.POINTER(NodeTable)]),
     "fgs_update_nodes": (C.c_int, [C.c_void_p, C.POINTER(NodeTable), p_i64]),
     "fgs_evaluate": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts), C.POINTER(Results)]),

@@ -120,6 +120,48 @@ class Synth:
             pass
 
 
+class Packer:
+    """Host-side packer (no GPU needed): object snapshot → SoA tables. A table stays valid until the
+    next call of the same kind on the same Packer, so use one Packer per table you keep."""
+
+    def __init__(self, n_scalars=2):
+        self._lib = L.load()
+        h = C.c_void_p()
+        rc = self._lib.fgs_packer_create(n_scalars, C.byref(h))
+        if rc != 0:
+            raise FgsError(rc, "fgs_packer_create")
+        self._h = h
+
+    def _check(self, rc):
+        if rc != 0:
+            raise FgsError(rc, self._lib.fgs_packer_error(self._h).decode())
+
+    def nodes(self, snapshot, n0=0, n1=None):
+        if n1 is None:
+            n1 = int(snapshot.contents.n_nodes)
+        t = C.POINTER(L.NodeTable)()
+        self._check(self._lib.fgs_packer_nodes(self._h, snapshot, n0, n1, C.byref(t)))
+        return t
+
+    def pods(self, podset, p0=0, p1=None):
+        if p1 is None:
+            p1 = int(podset.contents.n_pods)
+        t = C.POINTER(L.PodTable)()
+        self._check(self._lib.fgs_packer_pods(self._h, podset, p0, p1, C.byref(t)))
+        return t
+
+    def close(self):
+        if self._h:
+            self._lib.fgs_packer_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class Results:
     def __init__(self, P):
         self.feasible_count = np.zeros(P, np.int32)
@@ -171,16 +213,6 @@ class Engine:
     # -- configuration / upload ------------------------------------------------------------------
     def set_plugins(self, cfg):
         self._check(self._lib.fgs_set_plugins(self._h, C.byref(cfg)))
-
-    def pack_nodes(self, snapshot):
-        t = C.POINTER(L.NodeTable)()
-        self._check(self._lib.fgs_pack_nodes(self._h, snapshot, C.byref(t)))
-        return t
-
-    def pack_pods(self, podset):
-        t = C.POINTER(L.PodTable)()
-        self._check(self._lib.fgs_pack_pods(self._h, podset, C.byref(t)))
-        return t
 
     def upload_nodes(self, table):
         self._check(self._lib.fgs_upload_nodes(self._h, table))

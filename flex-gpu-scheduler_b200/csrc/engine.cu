@@ -310,26 +310,6 @@ extern "C" int fgs_set_plugins(fgs_engine* eh, const fgs_plugin_cfg* c) {
     return ((Engine*)eh)->set_plugins(c);
 }
 
-extern "C" int fgs_pack_nodes(fgs_engine* eh, const fgs_snapshot* snap, const fgs_node_table** out) {
-    if (!eh || !out) return FGS_E_INVALID;
-    Engine* e = (Engine*)eh;
-    if (snap && snap->n_scalars != e->S) return e->fail(FGS_E_INVALID, "fgs_pack_nodes: snapshot n_scalars differs from the engine's");
-    int rc = pack_nodes(snap, &e->packed_nodes, &e->err);
-    if (rc) return rc;
-    *out = &e->packed_nodes.view;
-    return FGS_OK;
-}
-
-extern "C" int fgs_pack_pods(fgs_engine* eh, const fgs_podset* pods, const fgs_pod_table** out) {
-    if (!eh || !out) return FGS_E_INVALID;
-    Engine* e = (Engine*)eh;
-    if (pods && pods->n_scalars != e->S) return e->fail(FGS_E_INVALID, "fgs_pack_pods: podset n_scalars differs from the engine's");
-    int rc = pack_pods(pods, &e->packed_pods, &e->err);
-    if (rc) return rc;
-    *out = &e->packed_pods.view;
-    return FGS_OK;
-}
-
 static int run_derive(Engine* e) {
     DeriveParams dp;
     std::memset(&dp, 0, sizeof(dp));

@@ -44,8 +44,6 @@ struct Engine {
     void* h_pods = nullptr;
     void* h_perpod = nullptr;
 
-    PackedNodes packed_nodes;
-    PackedPods packed_pods;
     GangState* gang = nullptr;
 
     fgs_timings tm = {0, 0, 0, 0, 0};

@@ -7,6 +7,7 @@
 #include "pack.h"
 
 #include <cstring>
+#include <new>
 
 #include "podmath.h"
 
@@ -56,11 +57,31 @@ void PackedPods::make_view() {
     view.priority = priority.data();
 }
 
-int pack_nodes(const fgs_snapshot* snap, PackedNodes* out, std::string* err) {
+static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::string* err);
+
+int pack_nodes(const fgs_snapshot* snap, int64_t n0, int64_t n1, PackedNodes* out, std::string* err) {
     if (!snap || snap->n_nodes < 0 || snap->n_scalars < 2 || snap->n_scalars > FGS_MAX_SCALARS) {
         *err = "pack_nodes: bad snapshot header";
         return FGS_E_INVALID;
     }
+    if (n0 < 0 || n1 < n0 || n1 > snap->n_nodes) {
+        *err = "pack_nodes: node range outside the snapshot";
+        return FGS_E_INVALID;
+    }
+    // a shard is the same snapshot with the per-node arrays advanced; pod_off stays absolute
+    fgs_snapshot sub = *snap;
+    const int S = snap->n_scalars;
+    sub.n_nodes = n1 - n0;
+    sub.node_valid = snap->node_valid + n0;
+    sub.alloc = snap->alloc + n0 * (4 + S);
+    sub.alloc_scalar_present = snap->alloc_scalar_present + n0;
+    sub.requested = snap->requested + n0 * (3 + S);
+    sub.nonzero = snap->nonzero + n0 * 2;
+    sub.pod_off = snap->pod_off + n0;
+    return pack_nodes_all(&sub, out, err);
+}
+
+static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::string* err) {
     const int64_t N = snap->n_nodes;
     const int S = snap->n_scalars, AW = 4 + S, RW = 3 + S;
     // device slots = largest gpu count on any node
@@ -174,12 +195,16 @@ int pack_nodes(const fgs_snapshot* snap, PackedNodes* out, std::string* err) {
     return FGS_OK;
 }
 
-int pack_pods(const fgs_podset* pods, PackedPods* out, std::string* err) {
+int pack_pods(const fgs_podset* pods, int64_t p0, int64_t p1, PackedPods* out, std::string* err) {
     if (!pods || pods->n_pods < 0 || pods->n_scalars < 2 || pods->n_scalars > FGS_MAX_SCALARS) {
         *err = "pack_pods: bad podset header";
         return FGS_E_INVALID;
     }
-    const int64_t P = pods->n_pods;
+    if (p0 < 0 || p1 < p0 || p1 > pods->n_pods) {
+        *err = "pack_pods: pod range outside the podset";
+        return FGS_E_INVALID;
+    }
+    const int64_t P = p1 - p0;
     const int S = pods->n_scalars;
     PackedPods& t = *out;
     t.n = P;
@@ -193,12 +218,15 @@ int pack_pods(const fgs_podset* pods, PackedPods* out, std::string* err) {
     t.pg.assign((size_t)P, -1);
     t.priority.assign((size_t)P, 0);
     for (int64_t i = 0; i < P; ++i) {
-        const PodLimits l = pod_limits(pods, i);
-        const PodRequest r = pod_request(pods, i);
-        bool ok = in_range(l.gpu) && in_range(l.mem) && in_range(r.score_mcpu) && in_range(r.score_mem);
-        for (int k = 0; k < 3 + S; ++k) ok = ok && in_range(r.v[k]);
+        const int64_t src = p0 + i;
+        const PodLimits l = pod_limits(pods, src);
+        const PodRequest r = pod_request(pods, src);
+        // API validation forbids negative quantities; the kernels rely on requests and limits being >= 0
+        bool ok = in_range(l.gpu) && in_range(l.mem) && in_range(r.score_mcpu) && in_range(r.score_mem) && l.gpu >= 0 && l.mem >= 0 &&
+                  r.score_mcpu >= 0 && r.score_mem >= 0;
+        for (int k = 0; k < 3 + S; ++k) ok = ok && in_range(r.v[k]) && r.v[k] >= 0;
         if (!ok) {
-            *err = "pack_pods: a quantity of pod " + std::to_string(i) + " is out of range";
+            *err = "pack_pods: a quantity of pod " + std::to_string(src) + " is negative or out of range";
             return FGS_E_RANGE;
         }
         uint32_t fl = 0;
@@ -216,12 +244,58 @@ int pack_pods(const fgs_podset* pods, PackedPods* out, std::string* err) {
         t.req_scalar_present[(size_t)i] = r.scalar_keys;
         t.nz_mcpu[(size_t)i] = r.score_mcpu;
         t.nz_mem[(size_t)i] = r.score_mem;
-        t.ns[(size_t)i] = pods->ns ? pods->ns[i] : 0;
-        t.pg[(size_t)i] = pods->pg ? pods->pg[i] : -1;
-        t.priority[(size_t)i] = pods->priority ? pods->priority[i] : 0;
+        t.ns[(size_t)i] = pods->ns ? pods->ns[src] : 0;
+        t.pg[(size_t)i] = pods->pg ? pods->pg[src] : -1;
+        t.priority[(size_t)i] = pods->priority ? pods->priority[src] : 0;
     }
     t.make_view();
     return FGS_OK;
 }
 
 } // namespace fgs
+
+// ---- C ABI: the packer object (host only) ---------------------------------------------------------
+
+struct fgs_packer {
+    int S = 2;
+    fgs::PackedNodes nodes;
+    fgs::PackedPods pods;
+    std::string err;
+};
+
+extern "C" int fgs_packer_create(int32_t n_scalars, fgs_packer** out) {
+    if (!out || n_scalars < 2 || n_scalars > FGS_MAX_SCALARS) return FGS_E_INVALID;
+    fgs_packer* p = new (std::nothrow) fgs_packer();
+    if (!p) return FGS_E_INVALID;
+    p->S = n_scalars;
+    *out = p;
+    return FGS_OK;
+}
+
+extern "C" void fgs_packer_destroy(fgs_packer* p) { delete p; }
+
+extern "C" const char* fgs_packer_error(const fgs_packer* p) { return p ? p->err.c_str() : "null packer"; }
+
+extern "C" int fgs_packer_nodes(fgs_packer* p, const fgs_snapshot* snap, int64_t n0, int64_t n1, const fgs_node_table** out) {
+    if (!p || !out) return FGS_E_INVALID;
+    if (snap && snap->n_scalars != p->S) {
+        p->err = "fgs_packer_nodes: snapshot n_scalars differs from the packer's";
+        return FGS_E_INVALID;
+    }
+    const int rc = fgs::pack_nodes(snap, n0, n1, &p->nodes, &p->err);
+    if (rc) return rc;
+    *out = &p->nodes.view;
+    return FGS_OK;
+}
+
+extern "C" int fgs_packer_pods(fgs_packer* p, const fgs_podset* pods, int64_t p0, int64_t p1, const fgs_pod_table** out) {
+    if (!p || !out) return FGS_E_INVALID;
+    if (pods && pods->n_scalars != p->S) {
+        p->err = "fgs_packer_pods: podset n_scalars differs from the packer's";
+        return FGS_E_INVALID;
+    }
+    const int rc = fgs::pack_pods(pods, p0, p1, &p->pods, &p->err);
+    if (rc) return rc;
+    *out = &p->pods.view;
+    return FGS_OK;
+}

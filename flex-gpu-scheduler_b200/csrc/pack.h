@@ -29,8 +29,8 @@ struct PackedPods {
 };
 
 // Both return FGS_OK or a negative FGS_E_* with `err` set.
-int pack_nodes(const fgs_snapshot* snap, PackedNodes* out, std::string* err);
-int pack_pods(const fgs_podset* pods, PackedPods* out, std::string* err);
+int pack_nodes(const fgs_snapshot* snap, int64_t n0, int64_t n1, PackedNodes* out, std::string* err);
+int pack_pods(const fgs_podset* pods, int64_t p0, int64_t p1, PackedPods* out, std::string* err);
 
 // Range rule shared by the packer and the table-level entry points: every quantity must satisfy
 // |v| < 2^53 so that the sums the reference forms in int64 (and in arbitrary-precision Quantity,

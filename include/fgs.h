@@ -103,19 +103,27 @@ const char* fgs_last_error(const fgs_engine* e); /* e may be NULL: last create e
  * sched/framework/runtime/framework.go:395-415). */
 int fgs_set_plugins(fgs_engine* e, const fgs_plugin_cfg* cfg);
 
-/* ---- packing (host) -------------------------------------------------------------------- */
+/* ---- packing (host only: no CUDA call, usable before any engine exists) -------------------- */
 
-/* Object snapshot → SoA node table. Takes over the per-call object walks of
- * nodeResourceLimitSum (pkg/flexgpu/flex_gpu.go:133-140) and NewGPUNode/constructGPUs
- * (pkg/flexgpu/gpu_node.go:30-120), and reads NodeInfo aggregates
- * (sched/framework/types.go:359-419). The returned table is owned by the engine and valid
- * until the next fgs_pack_nodes or fgs_destroy. */
-int fgs_pack_nodes(fgs_engine* e, const fgs_snapshot* snap, const fgs_node_table** out);
+typedef struct fgs_packer fgs_packer; /* owns the tables it returns */
 
-/* Pending pods → SoA pod table. Takes over podResourceLimit (flex_gpu.go:121-131),
+int fgs_packer_create(int32_t n_scalars, fgs_packer** out);
+void fgs_packer_destroy(fgs_packer* p);
+const char* fgs_packer_error(const fgs_packer* p);
+
+/* Object snapshot → SoA node table for nodes [n0, n1) of the snapshot (a shard; 0..n_nodes = all).
+ * Takes over the per-call object walks of nodeResourceLimitSum (pkg/flexgpu/flex_gpu.go:133-140)
+ * and NewGPUNode/constructGPUs (pkg/flexgpu/gpu_node.go:30-120), and reads the NodeInfo aggregates
+ * (sched/framework/types.go:359-419). Valid until the next fgs_packer_nodes on this packer. */
+int fgs_packer_nodes(fgs_packer* p, const fgs_snapshot* snap, int64_t n0, int64_t n1,
+                     const fgs_node_table** out);
+
+/* Pods [p0, p1) of the podset → SoA pod table (a batch; 0..n_pods = all). Takes over podResourceLimit (flex_gpu.go:121-131),
  * computePodResourceRequest (fit.go:162-180) and calculatePodResourceRequest
- * (sched/framework/plugins/noderesources/resource_allocation.go:119-143). */
-int fgs_pack_pods(fgs_engine* e, const fgs_podset* pods, const fgs_pod_table** out);
+ * (sched/framework/plugins/noderesources/resource_allocation.go:119-143).
+ * Valid until the next fgs_packer_pods on this packer. */
+int fgs_packer_pods(fgs_packer* p, const fgs_podset* pods, int64_t p0, int64_t p1,
+                    const fgs_pod_table** out);
 
 /* ---- upload + evaluate ----------------------------------------------------------------- */
 

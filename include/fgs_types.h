@@ -10,7 +10,7 @@
  *      oracle/ walks them the way the Go plugins do.
  *
  *  (2) the TABLE level (fgs_node_table / fgs_pod_table): SoA int64 columns produced from (1)
- *      by the packer (fgs_pack_nodes / fgs_pack_pods); this is what is uploaded to HBM and
+ *      by the packer (fgs_packer_nodes / fgs_packer_pods); this is what is uploaded to HBM and
  *      what the CUDA kernels read.
  *
  * Quantities are int64 in the units the reference's framework.Resource uses

@@ -1,0 +1,271 @@
+"""GPU parity tests: the CUDA path, called through the libfgs C ABI, against the CPU oracle on the same
+seeded object snapshots, and against the golden vectors transcribed from the reference's unit tests.
+Integer work: every comparison is bit-exact."""
+import numpy as np
+import pytest
+
+import golden_cases as G
+import flex_gpu_scheduler_b200 as fgs
+from flex_gpu_scheduler_b200 import _lib as L
+
+pytestmark = pytest.mark.gpu
+
+FLEX, FIT, ALLOC = L.FGS_PL_FLEXGPU, L.FGS_PL_FIT, L.FGS_PL_ALLOCATABLE
+
+
+def run_engine(synth_or_pair, cfg, S=2, want_planes=True, **opts):
+    snapshot, pending = synth_or_pair
+    eng = fgs.Engine(device=0, n_scalars=S, total_nodes=int(snapshot.contents.n_nodes))
+    eng.set_plugins(cfg)
+    pk = fgs.Packer(S)
+    eng.upload_nodes(pk.nodes(snapshot))
+    res = eng.evaluate(pk.pods(pending), want_planes=want_planes, **opts)
+    return eng, pk, res
+
+
+def check_against_oracle(oracle, snapshot, pending, cfg, S=2, per_plugin=True):
+    N = int(snapshot.contents.n_nodes)
+    P = int(pending.contents.n_pods)
+    ref = oracle.evaluate(snapshot, pending, cfg, workers=4, per_plugin=per_plugin)
+    eng, pk, res = run_engine((snapshot, pending), cfg, S=S)
+    feas_ref = ref.status == 0
+    # identical feasible set, counts and error flags
+    feas = res.feasible(N)
+    assert np.array_equal(feas, feas_ref)
+    assert np.array_equal(res.feasible_count, ref.feasible_count)
+    assert np.array_equal(res.pod_err, ref.pod_err)
+    # identical Filter status plane (merged, with the failing plugin) and per-plugin verdicts
+    st = eng.status_plane(0)
+    assert np.array_equal(st, ref.status)
+    ok = ref.pod_err == 0  # scores of pods whose cycle errors out in the reference are not defined
+    scored = ok & (ref.feasible_count >= 1)
+    tot = res.scores[:, :N]
+    m = feas_ref & scored[:, None]
+    assert np.array_equal(tot[m], ref.total[m])
+    # selectHost: chosen node lies in the reference's max-score tie set
+    has = ok & (ref.feasible_count >= 1)
+    sel = res.selected_node
+    assert np.all(sel[ref.feasible_count == 0] == -1)
+    idx = np.nonzero(has)[0]
+    assert np.all(sel[idx] >= 0)
+    assert np.all(feas_ref[idx, sel[idx]])
+    assert np.array_equal(ref.total[idx, sel[idx]], ref.max_total[idx])
+    assert np.array_equal(res.selected_score[idx], ref.max_total[idx])
+    if per_plugin:
+        pend_table = pk.pods(pending)
+        for bit, raw_ref, norm_ref, w in ((FLEX, ref.raw_flex, ref.norm_flex, cfg.weight_flex), (FIT, ref.raw_fit, ref.norm_fit, cfg.weight_fit),
+                                          (ALLOC, ref.raw_alloc, ref.norm_alloc, cfg.weight_alloc)):
+            if not (cfg.score_mask & bit):
+                continue
+            r_raw = eng.evaluate(pend_table, want_planes=True, emit_mask=bit, emit_raw=1)
+            assert np.array_equal(r_raw.scores[:, :N][m], raw_ref[m])
+            r_norm = eng.evaluate(pend_table, want_planes=True, emit_mask=bit)
+            assert np.array_equal(r_norm.scores[:, :N][m], norm_ref[m] * (w if w else 1))
+    eng.close()
+    return ref, res
+
+
+CONFIG_CASES = [
+    # (name, synth kwargs, plugin kwargs)
+    ("c1-flex-allocatable", dict(cfg=1, n_nodes=700, n_pending=600), None),
+    ("c2-flex-least", dict(cfg=2, n_nodes=1100, n_pending=500), None),
+    ("c2-quirks-panics", dict(cfg=2, n_nodes=600, n_pending=400, pm_quirk_nodes=150, pm_panic_nodes=60, pm_nongpu_nodes=80),
+     None),
+    ("most-allocated-weights", dict(cfg=2, n_nodes=520, n_pending=300),
+     dict(score_plugins=(("FlexGPU", 3), ("NodeResourcesFit", 2)), fit_strategy="MostAllocated", fit_resources=(("cpu", 3), ("memory", 7)))),
+    ("flex-first-order", dict(cfg=2, n_nodes=520, n_pending=300, pm_panic_nodes=80),
+     dict(filter_plugins=("FlexGPU", "NodeResourcesFit"))),
+    ("all-three-scores", dict(cfg=2, n_nodes=513, n_pending=257),
+     dict(score_plugins=(("FlexGPU", 2), ("NodeResourcesFit", 1), ("NodeResourcesAllocatable", 5)), alloc_mode="Most")),
+    ("generic-fit-resources", dict(cfg=2, n_nodes=400, n_pending=300, n_scalars=4, pm_extra_scalar=400),
+     dict(fit_resources=(("cpu", 2), ("memory", 1), ("ephemeral-storage", 1), (("scalar", 0), 4), (("scalar", 2), 1)))),
+    ("allocatable-scalar-and-unknown", dict(cfg=1, n_nodes=300, n_pending=200),
+     dict(score_plugins=(("NodeResourcesAllocatable", 2),), alloc_resources=(("cpu", 1 << 20), ("memory", 1), (("scalar", 1), 7), ("pods", 3)))),
+    ("filter-only-flex", dict(cfg=2, n_nodes=300, n_pending=200), dict(filter_plugins=("FlexGPU",), score_plugins=(("FlexGPU", 1),))),
+    ("ignored-scalar", dict(cfg=2, n_nodes=300, n_pending=200, n_scalars=3, pm_extra_scalar=500), dict(fit_ignored_scalar_mask=0b100)),
+    ("huge-weight-keys", dict(cfg=2, n_nodes=300, n_pending=200), dict(score_plugins=(("FlexGPU", 50000), ("NodeResourcesFit", 70000)))),
+]
+
+
+@pytest.mark.parametrize("name,skw,pkw", CONFIG_CASES, ids=[c[0] for c in CONFIG_CASES])
+def test_evaluate_matches_oracle(gpu_ok, oracle, name, skw, pkw):
+    skw = dict(skw)
+    cfg_id = skw.pop("cfg")
+    s = fgs.config_synth(cfg_id, **skw)
+    cfg = fgs.config_plugins(cfg_id) if pkw is None else fgs.plugin_cfg(**pkw)
+    ref, res = check_against_oracle(oracle, s.snapshot, s.pending, cfg, S=s.params["n_scalars"])
+    # the synthetic data must exercise what the case is about
+    assert ref.feasible_count.max() > 1
+    if "panic" in name:
+        assert (ref.pod_err & L.FGS_PODERR_REF_PANIC).any()
+
+
+def _flex_node(B, gpus, mem_alloc, used):
+    pods = [B.pod(containers=[B.ctr({("scalar", 1): u}, mem_limit=u)], node_name=True, index=i) for i, u in enumerate(used) if u]
+    return B.node(alloc={"cpu": 64000, "memory": 1 << 40, "pods": 110, ("scalar", 0): gpus, ("scalar", 1): mem_alloc}, pods=pods)
+
+
+def test_negative_memscore_range_error(gpu_ok, oracle):
+    """The one way a normalised score leaves [0,100] on this path (runtime/framework.go:920-923): MemScore < 0
+    on a feasible node. It needs memory allocatable not divisible by the gpu count, an over-committed device
+    and a pod whose memory limit key is present with value 0:
+      node 0: 2 gpus, 2001 memory → memEach 1000; devices used 1000 and 1001 → limit sum 2001 + 0 <= 2001 passes,
+              device 0 fits (1000 >= 1000 + 0) → feasible; MemScore = 2000 - 2001 = -1
+      node 1: memEach = other/2, empty → MemScore = other
+    other = 100  → max 100:  100*(-1)/100 = -1 → 100 - (-1) = 101 → the cycle errors out
+    other = 1000 → max 1000: 100*(-1)/1000 truncates to 0 → 100 → fine."""
+    import builders as B
+    cfg = fgs.plugin_cfg(filter_plugins=("FlexGPU",), score_plugins=(("FlexGPU", 1),))
+    pend = B.build_podset([B.pod(containers=[B.ctr({"cpu": 100}, mem_limit=0)])])
+    for other, want_err in ((100, L.FGS_PODERR_SCORE_RANGE), (1000, 0)):
+        snap = B.build_snapshot([_flex_node(B, 2, 2001, [1000, 1001]), _flex_node(B, 2, other, [0, 0])])
+        ref, res = check_against_oracle(oracle, snap.ptr, pend.ptr, cfg)
+        assert ref.feasible_count.tolist() == [2]
+        assert ref.raw_flex[0].tolist() == [-1, other]
+        assert ref.pod_err.tolist() == [want_err]
+        assert res.pod_err.tolist() == [want_err]
+
+
+def test_whole_gpu_pod_skips_device_check(gpu_ok, oracle):
+    """FlexGPU.Filter checks devices only for memory pods (flex_gpu.go:109): a whole-GPU pod fits a node whose
+    devices are all partly used as long as the limit sums pass; its score is the count of idle devices."""
+    import builders as B
+    cfg = fgs.plugin_cfg(filter_plugins=("FlexGPU",), score_plugins=(("FlexGPU", 1),))
+    snap = B.build_snapshot([_flex_node(B, 2, 2000, [500, 700]), _flex_node(B, 2, 2000, [0, 700]), _flex_node(B, 2, 2000, [0, 0])])
+    pend = B.build_podset([B.pod(containers=[B.ctr({"cpu": 100}, gpu_limit=1)]), B.pod(containers=[B.ctr({"cpu": 100}, gpu_limit=3)])])
+    ref, res = check_against_oracle(oracle, snap.ptr, pend.ptr, cfg)
+    assert ref.feasible_count.tolist() == [3, 0]  # limit 3 > 2 allocatable everywhere
+    assert ref.raw_flex[0].tolist() == [0, 1, 2]
+    assert ref.norm_flex[0].tolist() == [100, 50, 0]  # reverse normalisation: bin-packing prefers the fuller node
+
+
+def test_edge_shapes(gpu_ok, oracle):
+    """ragged sizes around the tile boundaries, a single node, a single pod"""
+    for n_nodes, n_pending in ((1, 1), (31, 65), (512, 64), (513, 63), (1025, 129)):
+        s = fgs.config_synth(2, n_nodes=n_nodes, n_pending=n_pending)
+        check_against_oracle(oracle, s.snapshot, s.pending, fgs.config_plugins(2), per_plugin=False)
+
+
+def test_empty_pod_batch(gpu_ok):
+    s = fgs.config_synth(2, n_nodes=100, n_pending=0)
+    eng, pk, res = run_engine((s.snapshot, s.pending), fgs.config_plugins(2), want_planes=False)
+    assert res.feasible_count.shape == (0,)
+    eng.close()
+
+
+def test_plugin_arg_validation(gpu_ok):
+    # pkg/noderesources/allocatable_test.go:220-235 and NewAllocatable's mode check (allocatable.go:93-98)
+    eng = fgs.Engine(device=0)
+    for case in [c for c in G.load("allocatable") if "want_err" in c]:
+        cfg = fgs.plugin_cfg(score_plugins=(("NodeResourcesAllocatable", 1),), alloc_resources=[tuple(r) for r in case["resources"]])
+        with pytest.raises(fgs.FgsError) as ei:
+            eng.set_plugins(cfg)
+        assert case["want_err"] in str(ei.value)
+    with pytest.raises(fgs.FgsError):
+        eng.set_plugins(fgs.plugin_cfg(score_plugins=(("NodeResourcesAllocatable", 1),), alloc_mode="Sideways"))
+    eng.close()
+
+
+@pytest.mark.parametrize("case", [c for c in G.load("allocatable") if "want_err" not in c], ids=lambda c: c["name"][:60])
+def test_golden_allocatable(gpu_ok, case):
+    # pkg/noderesources/allocatable_test.go:112-219 through the CUDA path
+    snap, pend, resources, mode = G.allocatable_case(case)
+    cfg = fgs.plugin_cfg(filter_plugins=(), score_plugins=(("NodeResourcesAllocatable", 1),), alloc_mode=mode, alloc_resources=resources)
+    eng, pk, res = run_engine((snap.ptr, pend.ptr), cfg)
+    n = len(case["expected"])
+    assert res.scores[0, :n].tolist() == case["expected"]
+    eng.close()
+
+
+def test_golden_gang(gpu_ok, oracle):
+    # pkg/coscheduling/core/core_test.go:42-234 through the CUDA path. The evaluated pod is part of the pending
+    # set here (in production the pod lister knows it), which does not change any expected outcome.
+    g = G.load("gang_prefilter")
+    for case in g["cases"]:
+        snap, pend, pgs, unlisted, me = G.gang_prefilter_case(g, case)
+        eng = fgs.Engine(device=0)
+        eng.upload_nodes(fgs.Packer(2).nodes(snap.ptr))
+        pre, permit, assigned = eng.gang_check(snap.ptr, pend.ptr, pgs.ptr)
+        assert (pre[me] == 0) == case["expected"], case["name"]
+        assert np.array_equal(pre, oracle.gang_prefilter(snap.ptr, pend.ptr, pgs.ptr))
+        eng.close()
+    g = G.load("gang_permit")
+    for case in g["cases"]:
+        snap, pend, pgs = G.gang_permit_case(g, case)
+        eng = fgs.Engine(device=0)
+        eng.upload_nodes(fgs.Packer(2).nodes(snap.ptr))
+        pre, permit, assigned = eng.gang_check(snap.ptr, pend.ptr, pgs.ptr)
+        assert int(permit[0]) == case["expected"], case["name"]
+        eng.close()
+
+
+def test_golden_capacity(gpu_ok):
+    # pkg/capacityscheduling/capacity_scheduling_test.go:52-164 through the CUDA path
+    fw = {0: 0, 1: 2, 2: 2}
+    for case in G.load("capacity_prefilter"):
+        pend, qs = G.capacity_case(case)
+        eng = fgs.Engine(device=0, n_scalars=3)
+        code = eng.quota_check(fgs.Packer(3).pods(pend.ptr), qs.ptr)
+        assert [fw[int(c)] for c in code] == case["expected"], case["name"]
+        eng.close()
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_gang_matches_oracle(gpu_ok, oracle, seed):
+    s = fgs.config_synth(3, n_nodes=1500, n_pending=4000, n_groups=150, n_namespaces=7, pm_invalid_nodes=30, pm_neg_left_nodes=60,
+                         seed_nodes=0xF6500003 + seed, seed_pods=0xF6510003 + seed)
+    eng = fgs.Engine(device=0)
+    eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot))
+    pre, permit, assigned = eng.gang_check(s.snapshot, s.pending, s.podgroups)
+    ref_pre = oracle.gang_prefilter(s.snapshot, s.pending, s.podgroups)
+    ref_permit, ref_assigned = oracle.gang_permit(s.snapshot, s.pending, s.podgroups)
+    assert np.array_equal(pre, ref_pre)
+    assert np.array_equal(permit, ref_permit)
+    assert np.array_equal(assigned, ref_assigned)
+    assert set(np.unique(ref_pre)) >= {0, 2, 3}  # the generator reaches every outcome
+    eng.close()
+
+
+@pytest.mark.parametrize("n_nominated", [0, 40])
+def test_quota_matches_oracle(gpu_ok, oracle, n_nominated):
+    s = fgs.config_synth(4, n_nodes=800, n_pending=5000, n_namespaces=40, n_nominated=n_nominated, n_scalars=3, pm_extra_scalar=300)
+    eng = fgs.Engine(device=0, n_scalars=3)
+    pk_p, pk_n = fgs.Packer(3), fgs.Packer(3)
+    P = s.n_pending
+    puid = np.arange(P, dtype=np.int64)
+    nuid = np.arange(n_nominated, dtype=np.int64) * 7  # some nominated pods ARE pending pods (same uid)
+    nom_t = pk_n.pods(s.nominated) if n_nominated else None
+    code = eng.quota_check(pk_p.pods(s.pending), s.quotas, nom_t, puid if n_nominated else None, nuid if n_nominated else None)
+    ref = oracle.quota_prefilter(s.pending, s.quotas, s.nominated if n_nominated else None, puid if n_nominated else None,
+                                 nuid if n_nominated else None)
+    assert np.array_equal(code, ref)
+    assert set(np.unique(ref)) == {0, 1, 2}
+    eng.close()
+
+
+def test_dirty_row_update(gpu_ok, oracle):
+    """fgs_update_nodes on a few rows == a full upload of the changed snapshot"""
+    a = fgs.config_synth(2, n_nodes=600, n_pending=200)
+    b = fgs.config_synth(2, n_nodes=600, n_pending=200, seed_nodes=0xABCDEF)  # same pods, different nodes
+    cfg = fgs.config_plugins(2)
+    eng = fgs.Engine(device=0)
+    eng.set_plugins(cfg)
+    pk, pk2, pkp = fgs.Packer(2), fgs.Packer(2), fgs.Packer(2)
+    eng.upload_nodes(pk.nodes(a.snapshot))
+    dirty = np.array([3, 77, 511, 512, 599], np.int64)
+    # rows taken from b replace the same indices of a: pack b's single-node shards
+    import ctypes as C
+    full_b = pk2.nodes(b.snapshot)
+    N = 600
+    for i in dirty:
+        row = fgs.Packer(2)
+        eng.update_nodes(row.nodes(b.snapshot, int(i), int(i) + 1), [int(i)])
+    res = eng.evaluate(pkp.pods(a.pending), want_planes=True)
+    # reference: oracle on a with those rows replaced — build by evaluating both and splicing columns
+    ra = oracle.evaluate(a.snapshot, a.pending, cfg, workers=4)
+    rb = oracle.evaluate(b.snapshot, a.pending, cfg, workers=4)
+    feas = res.feasible(N)
+    exp = ra.status == 0
+    exp[:, dirty] = (rb.status == 0)[:, dirty]
+    assert np.array_equal(feas, exp)
+    eng.close()
