@@ -117,7 +117,7 @@ class DeviceView(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("reduce_ms", C.c_float), ("emit_ms", C.c_float), ("d2h_ms", C.c_float),
-                ("kernel_launches", C.c_int64)]
+                ("kernel_launches", C.c_int64), ("reduce_int32", C.c_int32), ("emit_int32", C.c_int32)]
 
 
 class SynthParams(C.Structure):

@@ -286,7 +286,8 @@ class Engine:
     def timings(self):
         t = L.Timings()
         self._check(self._lib.fgs_get_timings(self._h, C.byref(t)))
-        return dict(h2d_ms=t.h2d_ms, reduce_ms=t.reduce_ms, emit_ms=t.emit_ms, d2h_ms=t.d2h_ms, kernel_launches=t.kernel_launches)
+        return dict(h2d_ms=t.h2d_ms, reduce_ms=t.reduce_ms, emit_ms=t.emit_ms, d2h_ms=t.d2h_ms, kernel_launches=t.kernel_launches,
+                    reduce_int32=bool(t.reduce_int32), emit_int32=bool(t.emit_int32))
 
     # -- coscheduling / capacity scheduling ----------------------------------------------------------
     def gang_check(self, snapshot, pending, podgroups):

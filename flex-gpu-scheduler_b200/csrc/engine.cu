@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -95,6 +96,9 @@ void Engine::free_all() {
     if (d_perpod) cudaFree(d_perpod);
     if (d_bitmap) cudaFree(d_bitmap);
     if (d_scores) cudaFree(d_scores);
+    if (d_nn) cudaFree(d_nn);
+    if (d_pn) cudaFree(d_pn);
+    if (d_an) cudaFree(d_an);
     if (h_raw) cudaFreeHost(h_raw);
     if (h_pods) cudaFreeHost(h_pods);
     if (h_perpod) cudaFreeHost(h_perpod);
@@ -244,6 +248,10 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
     e->node_base = c->node_index_base;
     e->total_nodes = c->total_nodes;
     e->seed = c->select_seed;
+    {
+        const char* fw = getenv("FGS_FORCE_INT64");
+        e->force_wide = fw && fw[0] == '1';
+    }
     if (c->stream) {
         e->stream = (cudaStream_t)c->stream;
         e->own_stream = false;
@@ -310,6 +318,127 @@ extern "C" int fgs_set_plugins(fgs_engine* eh, const fgs_plugin_cfg* c) {
     return ((Engine*)eh)->set_plugins(c);
 }
 
+// ---- int32 specialisation: can this (node table, pod batch) pair run on the narrow kernels? --------------
+//
+// Per resource dimension the shift is the number of trailing zero bits common to every value of that
+// dimension on both sides (OR of all values), so dividing by 2^shift is exact; the batch qualifies when
+// every shifted value stays below the limits the int32 arithmetic needs (2^24 where a value is multiplied
+// by 100, 2^30 where it is only compared). Anything else runs on the int64 kernels.
+static int tz64(uint64_t v) { return v ? __builtin_ctzll(v) : 62; }
+
+int Engine::decide_narrow(const fgs_pod_table* t) {
+    narrow_batch = false;
+    if (force_wide || !node_an_valid || S < 2) return FGS_OK;
+    const bool sc_flex = cfg.score_mask & FGS_PL_FLEXGPU, sc_fit = cfg.score_mask & FGS_PL_FIT, sc_alloc = cfg.score_mask & FGS_PL_ALLOCATABLE;
+    EvalParams ep;
+    fill_eval_params(&ep, nullptr);
+    if (sc_fit && !ep.fit_fast) return FGS_OK;                 // scoring resources beyond cpu/memory
+    if (sc_fit && (node_an.flags & 1)) return FGS_OK;          // a node with zero cpu/memory capacity drops out of the average
+    const int64_t wsum = (sc_flex ? ep.w_flex : 0) + (sc_fit ? ep.w_fit : 0) + (sc_alloc ? ep.w_alloc : 0);
+    if (ep.w_flex > 327 || ep.w_fit > 327 || ep.w_alloc > 327 || wsum * 100 >= (1 << 15)) return FGS_OK; // 15-bit score field of the warp key
+    const int64_t P = t->n_pods;
+    uint64_t o[ND_DIMS] = {0};
+    int64_t mx[ND_DIMS] = {0};
+    uint32_t extra = 0;
+    auto scan = [&](int d, const int64_t* col) {
+        uint64_t oo = 0;
+        int64_t mm = 0;
+        for (int64_t i = 0; i < P; ++i) {
+            const int64_t v = col[i];
+            oo |= (uint64_t)v;
+            mm = v > mm ? v : mm;
+        }
+        o[d] |= oo;
+        mx[d] = mm > mx[d] ? mm : mx[d];
+    };
+    scan(DIM_CPU, t->req_mcpu);
+    scan(DIM_CPU, t->nz_mcpu);
+    scan(DIM_MEM, t->req_mem);
+    scan(DIM_MEM, t->nz_mem);
+    scan(DIM_EPH, t->req_eph);
+    scan(DIM_S0, t->req_scalar + 0 * P);
+    scan(DIM_S1, t->req_scalar + 1 * P);
+    scan(DIM_FG, t->flex_gpu_limit);
+    scan(DIM_FM, t->flex_mem_limit);
+    for (int64_t i = 0; i < P; ++i) extra |= t->req_scalar_present[i];
+    if (extra & ~3u & ~cfg.fit_ignored_scalar_mask) return FGS_OK; // a pod asks for a scalar beyond the two flex slots
+    NarrowShifts sh;
+    for (int d = 0; d < ND_DIMS; ++d) {
+        const uint64_t both = o[d] | node_an.or_bits[d];
+        int s = d == DIM_FG ? 0 : tz64(both);
+        if (s > 40) s = 40;
+        const int64_t m = std::max(mx[d], (int64_t)node_an.max_val[d]) >> s;
+        const int64_t limit = (d == DIM_EPH || d == DIM_S0 || d == DIM_S1) ? ((int64_t)1 << 30) : ((int64_t)1 << 24);
+        if (m >= limit) return FGS_OK;
+        sh.s[d] = s;
+    }
+    // buffers
+    if (n_pad > nn_cap) {
+        if (d_nn) cudaFree(d_nn);
+        d_nn = nullptr;
+        FGS_CUDA(this, cudaMalloc(&d_nn, sizeof(int) * NN_COLS * n_pad));
+        nn_cap = n_pad;
+        narrow_nodes_sig = -1;
+    }
+    if (p_pad > pn_cap) {
+        if (d_pn) cudaFree(d_pn);
+        d_pn = nullptr;
+        FGS_CUDA(this, cudaMalloc(&d_pn, sizeof(int) * PN_COLS * p_pad));
+        pn_cap = p_pad;
+    }
+    const int sig = cfg.fit_strategy;
+    if (narrow_nodes_sig != sig || std::memcmp(&sh, &narrow_sh, sizeof(sh)) != 0) {
+        launch_narrow_nodes((const int64_t*)d_nd, n_pad, sh, cfg.fit_strategy, (int*)d_nn, stream);
+        launches++;
+        narrow_nodes_sig = sig;
+        narrow_sh = sh;
+    }
+    launch_narrow_pods((const int64_t*)d_pods, p_pad, S, sh, cfg.fit_ignored_scalar_mask, (int*)d_pn, stream);
+    launches++;
+    FGS_CUDA(this, cudaGetLastError());
+    narrow_batch = true;
+    return FGS_OK;
+}
+
+void Engine::fill_narrow_params(NarrowParams* p) const {
+    EvalParams ep;
+    fill_eval_params(&ep, nullptr);
+    std::memset(p, 0, sizeof(*p));
+    p->nn = (const int*)d_nn;
+    p->pn = (const int*)d_pn;
+    p->nd = (const int64_t*)d_nd;
+    p->reduce_max = ep.reduce_max;
+    p->reduce_sum = ep.reduce_sum;
+    p->select_key = ep.select_key;
+    p->bitmap = ep.bitmap;
+    p->scores = ep.scores;
+    p->n_nodes = n_nodes;
+    p->n_pad = n_pad;
+    p->node_base = node_base;
+    p->n_pods = n_pods;
+    p->p_pad = p_pad;
+    p->words_per_row = words_per_row;
+    p->score_stride = score_stride;
+    p->pods_per_cta = ep.pods_per_cta;
+    p->flex_filter_first = ep.flex_filter_first;
+    p->sh = narrow_sh;
+    p->w_flex = (int)ep.w_flex;
+    p->w_fit = (int)ep.w_fit;
+    p->w_alloc = (int)ep.w_alloc;
+    p->fit_w_cpu = ep.fit_w_cpu;
+    p->fit_w_mem = ep.fit_w_mem;
+    p->fit_inv_wsum = ep.fit_inv_wsum;
+    p->seed = seed;
+}
+
+static uint32_t narrow_spec(const Engine* e) {
+    EvalParams ep;
+    e->fill_eval_params(&ep, nullptr);
+    return narrow_spec_bits(e->cfg.filter_mask & FGS_PL_FLEXGPU, e->cfg.filter_mask & FGS_PL_FIT, e->cfg.score_mask & FGS_PL_FLEXGPU,
+                            e->cfg.score_mask & FGS_PL_FIT, e->cfg.fit_strategy == 1, e->cfg.score_mask & FGS_PL_ALLOCATABLE,
+                            ep.fit_w_cpu == ep.fit_w_mem);
+}
+
 static int run_derive(Engine* e) {
     DeriveParams dp;
     std::memset(&dp, 0, sizeof(dp));
@@ -329,6 +458,22 @@ static int run_derive(Engine* e) {
     e->launches++;
     FGS_CUDA(e, cudaGetLastError());
     e->nodes_derived = true;
+    // node-side analysis for the int32 specialisation (upload time only; one small round trip)
+    e->node_an_valid = false;
+    e->narrow_nodes_sig = -1;
+    if (!e->d_an) FGS_CUDA(e, cudaMalloc(&e->d_an, sizeof(NodeAnalysis)));
+    NodeAnalysis init;
+    std::memset(&init, 0, sizeof(init));
+    init.araw_min = INT64_MAX;
+    init.araw_max = INT64_MIN;
+    FGS_CUDA(e, cudaMemcpyAsync(e->d_an, &init, sizeof(init), cudaMemcpyHostToDevice, e->stream));
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream)); // `init` lives on this stack frame
+    launch_analyze_nodes((const int64_t*)e->d_nd, e->n_nodes, e->n_pad, e->S, (NodeAnalysis*)e->d_an, e->stream);
+    e->launches++;
+    FGS_CUDA(e, cudaGetLastError());
+    FGS_CUDA(e, cudaMemcpyAsync(&e->node_an, e->d_an, sizeof(NodeAnalysis), cudaMemcpyDeviceToHost, e->stream));
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    e->node_an_valid = true;
     return FGS_OK;
 }
 
@@ -446,6 +591,8 @@ extern "C" int fgs_stage_pods(fgs_engine* eh, const fgs_pod_table* t) {
     std::memset(h + (int64_t)PD_META * pp + P, 0, sizeof(int64_t) * (size_t)(pp - P));
     for (int s = 0; s < S; ++s) col(PD_FIXED_COLS + s, t->req_scalar + (int64_t)s * P);
     FGS_CUDA(e, cudaMemcpyAsync(e->d_pods, e->h_pods, sizeof(int64_t) * pd_cols(S) * pp, cudaMemcpyHostToDevice, e->stream));
+    rc = e->decide_narrow(t); // int32 tables for this batch when every value qualifies
+    if (rc) return rc;
     FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
     e->have_pods = true;
     return FGS_OK;
@@ -460,7 +607,14 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     e->fill_eval_params(&p, nullptr);
     launch_init_perpod((int64_t*)e->d_perpod, e->p_pad, e->stream);
     e->launches++;
-    launch_eval_reduce(p, e->stream);
+    bool done = false;
+    if (e->narrow_batch) {
+        NarrowParams np;
+        e->fill_narrow_params(&np);
+        done = launch_reduce_narrow(np, narrow_spec(e), e->stream);
+    }
+    if (!done) launch_eval_reduce(p, e->stream);
+    e->reduce_was_narrow = done;
     e->launches++;
     FGS_CUDA(e, cudaGetLastError());
     FGS_CUDA(e, cudaEventRecord(e->events[2], e->stream));
@@ -475,7 +629,15 @@ extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
     EvalParams p;
     e->fill_eval_params(&p, opts);
     e->last_key_shift = p.key_shift;
-    launch_eval_emit(p, e->stream);
+    bool done = false;
+    const bool default_opts = !opts || ((opts->emit_mask == 0 || opts->emit_mask == e->cfg.score_mask) && !opts->emit_raw);
+    if (e->narrow_batch && default_opts && p.key_shift == 40) {
+        NarrowParams np;
+        e->fill_narrow_params(&np);
+        done = launch_emit_narrow(np, narrow_spec(e), e->stream);
+    }
+    if (!done) launch_eval_emit(p, e->stream);
+    e->emit_was_narrow = done;
     e->launches++;
     FGS_CUDA(e, cudaGetLastError());
     FGS_CUDA(e, cudaEventRecord(e->events[3], e->stream));
@@ -580,5 +742,7 @@ extern "C" int fgs_get_timings(fgs_engine* eh, fgs_timings* t) {
     Engine* e = (Engine*)eh;
     *t = e->tm;
     t->kernel_launches = e->launches;
+    t->reduce_int32 = e->reduce_was_narrow ? 1 : 0;
+    t->emit_int32 = e->emit_was_narrow ? 1 : 0;
     return FGS_OK;
 }

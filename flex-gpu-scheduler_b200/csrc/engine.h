@@ -6,6 +6,7 @@
 
 #include "../../include/fgs.h"
 #include "kernels.cuh"
+#include "kernels_narrow.cuh"
 #include "pack.h"
 
 namespace fgs {
@@ -44,9 +45,24 @@ struct Engine {
     void* h_pods = nullptr;
     void* h_perpod = nullptr;
 
+    // int32 specialisation (kernels_narrow.cu): analysis of the node side, current shifts, tables
+    NodeAnalysis node_an;
+    bool node_an_valid = false;
+    NarrowShifts narrow_sh;
+    int narrow_nodes_sig = -1; // fit strategy the narrow node table was built for (-1 = stale)
+    bool narrow_batch = false; // the staged pod batch qualifies
+    bool force_wide = false;   // FGS_FORCE_INT64=1: always take the int64 kernels (tests)
+    bool reduce_was_narrow = false, emit_was_narrow = false;
+    void* d_nn = nullptr;
+    void* d_pn = nullptr;
+    void* d_an = nullptr;
+    int64_t nn_cap = 0, pn_cap = 0;
+    int decide_narrow(const fgs_pod_table* t);
+    void fill_narrow_params(NarrowParams* p) const;
+
     GangState* gang = nullptr;
 
-    fgs_timings tm = {0, 0, 0, 0, 0};
+    fgs_timings tm = {0, 0, 0, 0, 0, 0, 0};
     int64_t launches = 0;
 
     int fail(int code, const std::string& msg);

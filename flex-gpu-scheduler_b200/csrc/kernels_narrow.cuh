@@ -1,0 +1,69 @@
+// kernels_narrow.cuh — int32 table layouts and launchers of the narrow evaluation kernels.
+#pragma once
+#include <cstdint>
+
+namespace fgs {
+
+// resource dimensions that get one exact power-of-two shift each
+enum NarrowDim : int {
+    DIM_CPU = 0, // milli-cores: free cpu, capacity, non-zero requested, pod requests
+    DIM_MEM,     // bytes
+    DIM_EPH,
+    DIM_S0,      // scalar slot 0 (nvidia.flex.com/gpu) as a Fit.Filter request
+    DIM_S1,      // scalar slot 1 (nvidia.flex.com/memory) as a Fit.Filter request
+    DIM_FG,      // whole-GPU limits / GPUScore (never shifted; tracked for the range check)
+    DIM_FM,      // fractional memory limits / per-device free memory / MemScore
+    ND_DIMS
+};
+
+struct NarrowShifts {
+    int s[ND_DIMS];
+};
+
+struct NodeAnalysis {
+    unsigned long long or_bits[ND_DIMS];
+    long long max_val[ND_DIMS];
+    long long araw_min, araw_max;
+    int flags; // bit0: a valid node has cpu or memory capacity <= 0; bit1: a MemScore is negative
+    int _pad;
+};
+
+enum NarrowNodeCol : int {
+    NN_THR_GPU = 0, NN_THR_MEM, NN_FREE_CPU, NN_FREE_MEM, NN_FREE_EPH, NN_FS0, NN_FS1, NN_FLAGS,
+    NN_CAP_C, NN_X_C, NN_CAP_M, NN_X_M, NN_GSCORE, NN_MSCORE,
+    NN_INV_C, NN_XQ_C, NN_INV_M, NN_XQ_M, NN_GS100F, NN_MS100F, // float bits
+    NN_COLS
+};
+
+enum NarrowPodCol : int { PN_LIM_G = 0, PN_LIM_M, PN_RC, PN_RM, PN_RE, PN_RS0, PN_RS1, PN_NZC, PN_NZM, PN_KIND, PN_COLS };
+
+struct NarrowParams {
+    const int* nn;          // [NN_COLS][n_pad]
+    const int* pn;          // [PN_COLS][p_pad]
+    const int64_t* nd;      // derived int64 node table (Allocatable raw score column)
+    int64_t* reduce_max;
+    int64_t* reduce_sum;
+    int64_t* select_key;
+    uint32_t* bitmap;
+    int64_t* scores;
+    int64_t n_nodes, n_pad, node_base;
+    int64_t n_pods, p_pad;
+    int64_t words_per_row, score_stride;
+    int pods_per_cta;
+    int flex_filter_first;
+    NarrowShifts sh;
+    int w_flex, w_fit, w_alloc;
+    int fit_w_cpu, fit_w_mem;
+    float fit_inv_wsum;
+    uint64_t seed;
+};
+
+void launch_analyze_nodes(const int64_t* nd, int64_t n_nodes, int64_t n_pad, int S, NodeAnalysis* out, void* stream);
+void launch_narrow_nodes(const int64_t* nd, int64_t n_pad, const NarrowShifts& sh, int fit_most, int* nn, void* stream);
+void launch_narrow_pods(const int64_t* pods, int64_t p_pad, int S, const NarrowShifts& sh, uint32_t fit_ignored, int* pn, void* stream);
+uint32_t narrow_spec_bits(bool flex_f, bool fit_f, bool sc_flex, bool sc_fit, bool fit_most, bool sc_alloc, bool w_eq);
+// false = no instantiation for that plugin combination (the caller falls back to the int64 kernels)
+bool launch_reduce_narrow(const NarrowParams& p, uint32_t spec, void* stream);
+bool launch_emit_narrow(const NarrowParams& p, uint32_t spec, void* stream);
+
+} // namespace fgs

@@ -191,6 +191,7 @@ int fgs_quota_check(fgs_engine* e, const fgs_pod_table* pods, const fgs_quotas* 
 typedef struct fgs_timings {
     float h2d_ms, reduce_ms, emit_ms, d2h_ms; /* last fgs_evaluate, CUDA events on the stream */
     int64_t kernel_launches;                  /* kernels launched by this engine so far */
+    int32_t reduce_int32, emit_int32;         /* 1: the last pass ran the int32 specialisation */
 } fgs_timings;
 int fgs_get_timings(fgs_engine* e, fgs_timings* t);
 

@@ -1,6 +1,8 @@
 """GPU parity tests: the CUDA path, called through the libfgs C ABI, against the CPU oracle on the same
 seeded object snapshots, and against the golden vectors transcribed from the reference's unit tests.
 Integer work: every comparison is bit-exact."""
+import os
+
 import numpy as np
 import pytest
 
@@ -23,11 +25,34 @@ def run_engine(synth_or_pair, cfg, S=2, want_planes=True, **opts):
     return eng, pk, res
 
 
-def check_against_oracle(oracle, snapshot, pending, cfg, S=2, per_plugin=True):
-    N = int(snapshot.contents.n_nodes)
-    P = int(pending.contents.n_pods)
+PATHS_TAKEN = {}  # test id → (reduce_int32, emit_int32) of the unforced run
+
+
+def check_against_oracle(oracle, snapshot, pending, cfg, S=2, per_plugin=True, tag=None):
+    """Both kernel families must agree with the oracle: the default run (int32 specialisation when the batch
+    qualifies) and a run with FGS_FORCE_INT64=1 (always the int64 kernels)."""
     ref = oracle.evaluate(snapshot, pending, cfg, workers=4, per_plugin=per_plugin)
+    res = None
+    for force in ("0", "1"):
+        os.environ["FGS_FORCE_INT64"] = force
+        try:
+            res_i, took = _check_one(ref, snapshot, pending, cfg, S, per_plugin)
+        finally:
+            os.environ.pop("FGS_FORCE_INT64", None)
+        if force == "0":
+            res = res_i
+            if tag:
+                PATHS_TAKEN[tag] = took
+        else:
+            assert took == (False, False)
+    return ref, res
+
+
+def _check_one(ref, snapshot, pending, cfg, S, per_plugin):
+    N = int(snapshot.contents.n_nodes)
     eng, pk, res = run_engine((snapshot, pending), cfg, S=S)
+    t = eng.timings()
+    took = (t["reduce_int32"], t["emit_int32"])
     feas_ref = ref.status == 0
     # identical feasible set, counts and error flags
     feas = res.feasible(N)
@@ -62,7 +87,7 @@ def check_against_oracle(oracle, snapshot, pending, cfg, S=2, per_plugin=True):
             r_norm = eng.evaluate(pend_table, want_planes=True, emit_mask=bit)
             assert np.array_equal(r_norm.scores[:, :N][m], norm_ref[m] * (w if w else 1))
     eng.close()
-    return ref, res
+    return res, took
 
 
 CONFIG_CASES = [
@@ -93,11 +118,18 @@ def test_evaluate_matches_oracle(gpu_ok, oracle, name, skw, pkw):
     cfg_id = skw.pop("cfg")
     s = fgs.config_synth(cfg_id, **skw)
     cfg = fgs.config_plugins(cfg_id) if pkw is None else fgs.plugin_cfg(**pkw)
-    ref, res = check_against_oracle(oracle, s.snapshot, s.pending, cfg, S=s.params["n_scalars"])
+    ref, res = check_against_oracle(oracle, s.snapshot, s.pending, cfg, S=s.params["n_scalars"], tag=name)
     # the synthetic data must exercise what the case is about
     assert ref.feasible_count.max() > 1
     if "panic" in name:
         assert (ref.pod_err & L.FGS_PODERR_REF_PANIC).any()
+    # which kernel family the unforced run took: the benchmark configurations must qualify for int32,
+    # configurations outside its scope must have fallen back to int64
+    expect_int32 = {"c1-flex-allocatable": (True, True), "c2-flex-least": (True, True), "c2-quirks-panics": (True, True),
+                    "most-allocated-weights": (True, True), "all-three-scores": (True, True), "filter-only-flex": (True, True),
+                    "generic-fit-resources": (False, False), "huge-weight-keys": (False, False)}
+    if name in expect_int32:
+        assert PATHS_TAKEN[name] == expect_int32[name], PATHS_TAKEN[name]
 
 
 def _flex_node(B, gpus, mem_alloc, used):
