@@ -1,0 +1,659 @@
+// eval_narrow.cu — int32 evaluation kernels (see kernels_narrow.cu for when they apply and why they are
+// exact).
+//
+//   reduce_narrow<SPEC>  pass A: Filter for every (pod,node) → feasibility bitmap (warp ballot, written as
+//                        whole 32-byte sectors) + per-pod feasible count, max FlexGPU score, Allocatable hi/lo.
+//   emit_narrow<SPEC>    pass B: Score, NormalizeScore, ×weight, Σ plugins → int64 score rows (streaming
+//                        256-byte stores per warp) + the per-pod selectHost key. Feasibility is READ from the
+//                        bitmap (staged per pod tile by TMA), not recomputed; an external mask can be
+//                        substituted (the feasible list the framework hands to PreScore).
+//
+// One CTA = 512 nodes in registers (2 per thread) × a range of pods; pod tiles of 64 arrive through a
+// two-stage cp.async.bulk + mbarrier ring. SPEC (plugin set, strategy, weights equal) is a template
+// parameter, so the pod loop has no configuration branches. HBM-write bound by design; the inner loop is
+// integer ALU work, ~45 lane-instructions per (pod,node).
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "kernels.cuh"
+#include "kernels_narrow.cuh"
+
+namespace fgs {
+
+namespace {
+
+typedef long long i64;
+typedef unsigned long long u64;
+constexpr i64 kI64Min = (i64)0x8000000000000000ull;
+constexpr int kPass = (int)0x80000000;
+constexpr int kNever = 0x7fffffff;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+// TMA bulk copy global → shared (SASS: UBLKCP), completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+__device__ __forceinline__ int rn_small(float x) { return __float_as_int(x + 12582912.0f) - 0x4B400000; }
+
+// floor(x / d) for 0 <= x < 2^31, 0 < d < 2^24 given a float estimate within 0.5 of x/d (quotient < 2^22):
+// k = round(est) is the quotient or one above it; the sign of the exact remainder x − k·d decides.
+__device__ __forceinline__ int qfix32(int x, int d, float est) {
+    const int k = rn_small(est);
+    const int r = (int)((uint32_t)x - (uint32_t)k * (uint32_t)d); // wraps harmlessly on don't-care lanes
+    return k + (r >> 31);
+}
+
+constexpr uint32_t SP_FLEX_F = 1, SP_FIT_F = 2, SP_SC_FLEX = 4, SP_SC_FIT = 8, SP_FIT_MOST = 16, SP_SC_ALLOC = 32, SP_W_EQ = 64;
+
+// =================================================================================================
+// pass A
+// =================================================================================================
+
+struct __align__(16) PodR { // 32 bytes: two broadcast LDS.128 per pod
+    int lim_g, lim_m, rc, rm;
+    int re, rs0, rs1, kind;
+};
+
+struct SmemR {
+    int bars, raw, pod, wred, whi, wnlo, bm, total, raw_stage_bytes;
+};
+__host__ __device__ inline SmemR smem_reduce(bool alloc) {
+    SmemR L;
+    int off = 0;
+    L.bars = off;
+    off += 64;
+    L.raw = off;
+    L.raw_stage_bytes = PN_COLS * kTileP * 4;
+    off += 2 * L.raw_stage_bytes;
+    L.pod = off;
+    off += kTileP * (int)sizeof(PodR);
+    L.wred = off; // int2 {max flex score, count | panic<<31} [kTileP][kWarps]
+    off += kTileP * kWarps * 8;
+    L.whi = off;
+    off += alloc ? kTileP * kWarps * 8 : 0;
+    L.wnlo = off;
+    off += alloc ? kTileP * kWarps * 8 : 0;
+    L.bm = off; // uint32 [kTileP][16]
+    off += kTileP * 16 * 4;
+    L.total = off;
+    return L;
+}
+
+__device__ __forceinline__ i64 warp_max_i64(i64 v) {
+    const int hi = (int)(v >> 32);
+    const int mhi = __reduce_max_sync(0xffffffffu, hi);
+    const uint32_t mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? (uint32_t)v : 0u);
+    return (i64)(((u64)(uint32_t)mhi << 32) | mlo);
+}
+
+template <uint32_t SPEC>
+__global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_constant__ NarrowParams prm) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    constexpr bool kAlloc = SPEC & SP_SC_ALLOC;
+    const SmemR L = smem_reduce(kAlloc);
+    uint64_t* bars = (uint64_t*)(smem + L.bars);
+    PodR* s_pod = (PodR*)(smem + L.pod);
+    int2* wred = (int2*)(smem + L.wred);
+    i64* whi = (i64*)(smem + L.whi);
+    i64* wnlo = (i64*)(smem + L.wnlo);
+    uint32_t* bm = (uint32_t*)(smem + L.bm);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const i64 node_tile0 = (i64)blockIdx.x * kTileN;
+    const i64 pod_begin = (i64)blockIdx.y * prm.pods_per_cta;
+    i64 pod_end = pod_begin + prm.pods_per_cta;
+    if (pod_end > prm.p_pad) pod_end = prm.p_pad;
+    const int n_tiles = (int)((pod_end - pod_begin + kTileP - 1) / kTileP);
+    if (n_tiles <= 0) return;
+
+    auto issue = [&](int it) {
+        const int stage = it & 1;
+        const i64 p0 = pod_begin + (i64)it * kTileP;
+        int* dst = (int*)(smem + L.raw + stage * L.raw_stage_bytes);
+        mbar_expect_tx(&bars[stage], (uint32_t)L.raw_stage_bytes);
+        for (int c = 0; c < PN_COLS; ++c) bulk_g2s(dst + c * kTileP, prm.pn + (i64)c * prm.p_pad + p0, kTileP * 4, &bars[stage]);
+    };
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        issue(0);
+        if (n_tiles > 1) issue(1);
+    }
+
+    // node tile → registers (thread owns nodes 64·warp + lane and + 32, so each ballot is one bitmap word)
+    int thr_g[2], thr_m[2], fc[2], fm[2], fe[2], fs0[2], fs1[2], gsc[2], msc[2];
+    bool node_ok[2], node_panic[2];
+    i64 araw[2];
+    uint32_t flags_or = 0;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const i64 n = node_tile0 + warp * 64 + j * 32 + lane;
+        auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
+        const uint32_t fl = (uint32_t)C(NN_FLAGS);
+        flags_or |= fl;
+        thr_g[j] = (SPEC & SP_FLEX_F) ? C(NN_THR_GPU) : kNever;
+        thr_m[j] = (SPEC & SP_FLEX_F) ? C(NN_THR_MEM) : kNever;
+        fc[j] = (SPEC & SP_FIT_F) ? C(NN_FREE_CPU) : kNever;
+        fm[j] = (SPEC & SP_FIT_F) ? C(NN_FREE_MEM) : kNever;
+        fe[j] = (SPEC & SP_FIT_F) ? C(NN_FREE_EPH) : kNever;
+        fs0[j] = (SPEC & SP_FIT_F) ? C(NN_FS0) : kNever;
+        fs1[j] = (SPEC & SP_FIT_F) ? C(NN_FS1) : kNever;
+        gsc[j] = C(NN_GSCORE);
+        msc[j] = C(NN_MSCORE);
+        node_ok[j] = (fl & FGS_NF_VALID) && (!(SPEC & SP_FIT_F) || (fl & NDF_PODS_OK)); // fit.go:259
+        node_panic[j] = fl & FGS_NF_REF_PANIC;
+        araw[j] = kAlloc ? __ldg((const i64*)prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n) : 0;
+    }
+    const bool tile_has_panic = (SPEC & SP_FLEX_F) && __syncthreads_or((flags_or & FGS_NF_REF_PANIC) != 0);
+
+    for (int it = 0; it < n_tiles; ++it) {
+        const int stage = it & 1;
+        const i64 tile_p0 = pod_begin + (i64)it * kTileP;
+        const i64 left = prm.n_pods - tile_p0;
+        const int n_valid = left >= kTileP ? kTileP : (left > 0 ? (int)left : 0);
+        mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
+        if (tid < kTileP) {
+            const int* raw = (const int*)(smem + L.raw + stage * L.raw_stage_bytes);
+            PodR u;
+            u.lim_g = raw[PN_LIM_G * kTileP + tid];
+            u.lim_m = raw[PN_LIM_M * kTileP + tid];
+            u.rc = raw[PN_RC * kTileP + tid];
+            u.rm = raw[PN_RM * kTileP + tid];
+            u.re = raw[PN_RE * kTileP + tid];
+            u.rs0 = raw[PN_RS0 * kTileP + tid];
+            u.rs1 = raw[PN_RS1 * kTileP + tid];
+            u.kind = raw[PN_KIND * kTileP + tid];
+            s_pod[tid] = u;
+        }
+        __syncthreads();
+        if (tid == 0 && it + 2 < n_tiles) {
+            fence_proxy_async();
+            issue(it + 2);
+        }
+        for (int jp = 0; jp < n_valid; ++jp) {
+            const int4 a = *(const int4*)&s_pod[jp].lim_g;
+            const int4 b = *(const int4*)&s_pod[jp].re;
+            const int kind = b.w;
+            bool feas[2];
+            bool fpanic = false;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                // FlexGPU.Filter: kind none passes, "both" never, else limit <= per-kind threshold (flex_gpu.go:54-116)
+                const bool flex_ok = a.x <= thr_g[j] && a.y <= thr_m[j];
+                // Fit.Filter: request <= allocatable − requested per resource (fit.go:277-326)
+                const bool fit_ok = a.z <= fc[j] && a.w <= fm[j] && b.x <= fe[j] && b.y <= fs0[j] && b.z <= fs1[j];
+                bool ok = flex_ok && fit_ok && node_ok[j];
+                if (tile_has_panic) { // NewGPUNode would panic inside FlexGPU.Filter (flex_gpu.go:101)
+                    const bool reach = (kind == 1 || kind == 2) && flex_ok && node_panic[j] && (prm.flex_filter_first || (fit_ok && node_ok[j]));
+                    fpanic = fpanic || reach;
+                    ok = ok && !reach;
+                }
+                feas[j] = ok;
+            }
+            const uint32_t b0 = __ballot_sync(0xffffffffu, feas[0]);
+            const uint32_t b1 = __ballot_sync(0xffffffffu, feas[1]);
+            int vflex = kPass;
+            if (SPEC & SP_SC_FLEX) {
+                int s0 = 0, s1 = 0;
+                if (kind == 1) {
+                    s0 = gsc[0];
+                    s1 = gsc[1];
+                } else if (kind == 2) {
+                    s0 = msc[0];
+                    s1 = msc[1];
+                }
+                vflex = __reduce_max_sync(0xffffffffu, max(feas[0] ? s0 : kPass, feas[1] ? s1 : kPass));
+            }
+            uint32_t cnt = (uint32_t)(__popc(b0) + __popc(b1));
+            if (tile_has_panic && __ballot_sync(0xffffffffu, fpanic)) cnt |= 0x80000000u;
+            if (kAlloc) {
+                i64 vhi = kI64Min, vnlo = kI64Min;
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+                    if (feas[j]) {
+                        vhi = araw[j] > vhi ? araw[j] : vhi;
+                        vnlo = -araw[j] > vnlo ? -araw[j] : vnlo;
+                    }
+                vhi = warp_max_i64(vhi);
+                vnlo = warp_max_i64(vnlo);
+                if (lane == 0) {
+                    whi[jp * kWarps + warp] = vhi;
+                    wnlo[jp * kWarps + warp] = vnlo;
+                }
+            }
+            if (lane == 0) {
+                wred[jp * kWarps + warp] = make_int2(vflex, (int)cnt);
+                *(uint2*)&bm[jp * 16 + warp * 2] = make_uint2(b0, b1);
+            }
+        }
+        __syncthreads();
+        // ---- flush the tile: per-pod partials → global atomics, bitmap rows → whole sectors ----------
+        if (tid < n_valid) {
+            const i64 p = tile_p0 + tid;
+            uint32_t c = 0, pn = 0;
+            int vf = kPass;
+            i64 vh = kI64Min, vl = kI64Min;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) {
+                const int2 x = wred[tid * kWarps + w];
+                c += (uint32_t)x.y & 0x7fffffffu;
+                pn |= (uint32_t)x.y >> 31;
+                vf = x.x > vf ? x.x : vf;
+                if (kAlloc) {
+                    const i64 h = whi[tid * kWarps + w], l = wnlo[tid * kWarps + w];
+                    vh = h > vh ? h : vh;
+                    vl = l > vl ? l : vl;
+                }
+            }
+            if (c) atomicAdd((u64*)prm.reduce_sum + p, (u64)c);
+            if (pn) atomicMax((i64*)prm.reduce_max + (i64)RR_FILTER_PANIC * prm.p_pad + p, (i64)1);
+            if ((SPEC & SP_SC_FLEX) && vf != kPass) {
+                // back to the reference's units: merged across shards and read by either emit kernel
+                const i64 v = s_pod[tid].kind == 2 ? (i64)vf * ((i64)1 << prm.sh.s[DIM_FM]) : (i64)vf;
+                atomicMax((i64*)prm.reduce_max + (i64)RR_FLEX_MAX * prm.p_pad + p, v);
+            }
+            if (kAlloc) {
+                if (vh != kI64Min) atomicMax((i64*)prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + p, vh);
+                if (vl != kI64Min) atomicMax((i64*)prm.reduce_max + (i64)RR_ALLOC_NEGLO * prm.p_pad + p, vl);
+            }
+        }
+        {
+            const i64 word0 = node_tile0 / 32; // 16 words = 64 bytes per pod row per CTA
+            for (int idx = tid; idx < n_valid * 16; idx += kThreads) {
+                const int jp = idx >> 4, w = idx & 15;
+                prm.bitmap[(tile_p0 + jp) * prm.words_per_row + word0 + w] = bm[idx];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// =================================================================================================
+// pass B
+// =================================================================================================
+
+struct __align__(16) PodE { // 64 bytes: four broadcast LDS.128 per pod
+    int nzc, nzm, nz100c, nz100m;
+    float fnzc, fnzm, finv, ainv;
+    int fmax, count, arange32, kind; // arange32 < 0: exact 64-bit path for Allocatable
+    uint32_t hmul;
+    int _pad;
+    i64 alo;
+};
+
+struct SmemE {
+    int bars, raw, pod, wkey, bm, total, raw_stage_bytes;
+};
+__host__ __device__ inline SmemE smem_emit() {
+    SmemE L;
+    int off = 0;
+    L.bars = off;
+    off += 64;
+    L.raw = off;
+    L.raw_stage_bytes = 3 * kTileP * 4 + 4 * kTileP * 8; // kind, nzc, nzm + flex max, alloc hi, alloc −lo, count
+    off += 2 * L.raw_stage_bytes;
+    L.pod = off;
+    off += kTileP * (int)sizeof(PodE);
+    L.wkey = off;
+    off += kTileP * kWarps * 4;
+    L.bm = off; // uint32 [2][kTileP][16]: the feasibility words of this node tile, two pod tiles deep
+    off += 2 * kTileP * 16 * 4;
+    L.total = off;
+    return L;
+}
+
+template <uint32_t SPEC>
+__global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant__ NarrowParams prm) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    constexpr bool kFlex = SPEC & SP_SC_FLEX, kFit = SPEC & SP_SC_FIT, kAlloc = SPEC & SP_SC_ALLOC, kMost = SPEC & SP_FIT_MOST;
+    const SmemE L = smem_emit();
+    uint64_t* bars = (uint64_t*)(smem + L.bars); // [0,1] pod columns, [2,3] bitmap rows
+    PodE* s_pod = (PodE*)(smem + L.pod);
+    uint32_t* wkey = (uint32_t*)(smem + L.wkey);
+    uint32_t* s_bm = (uint32_t*)(smem + L.bm);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const i64 node_tile0 = (i64)blockIdx.x * kTileN;
+    const i64 pod_begin = (i64)blockIdx.y * prm.pods_per_cta;
+    i64 pod_end = pod_begin + prm.pods_per_cta;
+    if (pod_end > prm.p_pad) pod_end = prm.p_pad;
+    const int n_tiles = (int)((pod_end - pod_begin + kTileP - 1) / kTileP);
+    if (n_tiles <= 0) return;
+    const i64 word0 = node_tile0 / 32;
+
+    auto issue_pods = [&](int it) { // one thread
+        const int stage = it & 1;
+        const i64 p0 = pod_begin + (i64)it * kTileP;
+        int* dst = (int*)(smem + L.raw + stage * L.raw_stage_bytes);
+        mbar_expect_tx(&bars[stage], (uint32_t)L.raw_stage_bytes);
+        bulk_g2s(dst + 0 * kTileP, prm.pn + (i64)PN_KIND * prm.p_pad + p0, kTileP * 4, &bars[stage]);
+        bulk_g2s(dst + 1 * kTileP, prm.pn + (i64)PN_NZC * prm.p_pad + p0, kTileP * 4, &bars[stage]);
+        bulk_g2s(dst + 2 * kTileP, prm.pn + (i64)PN_NZM * prm.p_pad + p0, kTileP * 4, &bars[stage]);
+        i64* d2 = (i64*)(dst + 3 * kTileP);
+        bulk_g2s(d2 + 0 * kTileP, prm.reduce_max + (i64)RR_FLEX_MAX * prm.p_pad + p0, kTileP * 8, &bars[stage]);
+        bulk_g2s(d2 + 1 * kTileP, prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + p0, kTileP * 8, &bars[stage]);
+        bulk_g2s(d2 + 2 * kTileP, prm.reduce_max + (i64)RR_ALLOC_NEGLO * prm.p_pad + p0, kTileP * 8, &bars[stage]);
+        bulk_g2s(d2 + 3 * kTileP, prm.reduce_sum + p0, kTileP * 8, &bars[stage]);
+    };
+    // 64 threads, one 64-byte bitmap row each (rows are words_per_row apart in global memory)
+    auto issue_bitmap = [&](int it) {
+        const int stage = it & 1;
+        const i64 p0 = pod_begin + (i64)it * kTileP;
+        if (tid == 0) mbar_expect_tx(&bars[2 + stage], (uint32_t)(kTileP * 64));
+        if (tid < kTileP) bulk_g2s(s_bm + (stage * kTileP + tid) * 16, prm.bitmap + (p0 + tid) * prm.words_per_row + word0, 64, &bars[2 + stage]);
+    };
+    if (tid == 0) {
+        for (int b = 0; b < 4; ++b) mbar_init(&bars[b], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        issue_pods(0);
+        if (n_tiles > 1) issue_pods(1);
+    }
+    issue_bitmap(0);
+    if (n_tiles > 1) issue_bitmap(1);
+
+    // node tile → registers
+    int capc[2], xc[2], x100c[2], capm[2], xm[2], x100m[2], g100[2], m100[2], nloc[2];
+    float invc[2], xqc[2], invm[2], xqm[2], g100f[2], m100f[2];
+    i64 araw[2];
+    bool inrange[2], npanic[2];
+    uint32_t flags_or = 0;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        nloc[j] = warp * 64 + j * 32 + lane;
+        const i64 n = node_tile0 + nloc[j];
+        inrange[j] = n < prm.n_nodes;
+        auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
+        if (kFit) {
+            capc[j] = C(NN_CAP_C);
+            xc[j] = C(NN_X_C);
+            capm[j] = C(NN_CAP_M);
+            xm[j] = C(NN_X_M);
+            x100c[j] = 100 * xc[j];
+            x100m[j] = 100 * xm[j];
+            invc[j] = __int_as_float(C(NN_INV_C));
+            xqc[j] = __int_as_float(C(NN_XQ_C));
+            invm[j] = __int_as_float(C(NN_INV_M));
+            xqm[j] = __int_as_float(C(NN_XQ_M));
+        }
+        if (kFlex) {
+            g100[j] = 100 * C(NN_GSCORE);
+            m100[j] = 100 * C(NN_MSCORE);
+            g100f[j] = __int_as_float(C(NN_GS100F));
+            m100f[j] = __int_as_float(C(NN_MS100F));
+        }
+        const uint32_t fl = (uint32_t)C(NN_FLAGS);
+        flags_or |= fl;
+        npanic[j] = fl & FGS_NF_REF_PANIC;
+        araw[j] = kAlloc ? __ldg((const i64*)prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n) : 0;
+    }
+    const bool tile_has_panic = kFlex && __syncthreads_or((flags_or & FGS_NF_REF_PANIC) != 0);
+    const bool tile_has_neg = kFlex && __syncthreads_or((flags_or & NDF_MEMSCORE_NEG) != 0);
+
+    for (int it = 0; it < n_tiles; ++it) {
+        const int stage = it & 1;
+        const uint32_t parity = (uint32_t)((it >> 1) & 1);
+        const i64 tile_p0 = pod_begin + (i64)it * kTileP;
+        const i64 left = prm.n_pods - tile_p0;
+        const int n_valid = left >= kTileP ? kTileP : (left > 0 ? (int)left : 0);
+        mbar_wait(&bars[stage], parity);
+        if (tid < kTileP) {
+            const int* raw = (const int*)(smem + L.raw + stage * L.raw_stage_bytes);
+            const i64* raw64 = (const i64*)(raw + 3 * kTileP);
+            PodE u;
+            u.kind = raw[0 * kTileP + tid];
+            u.nzc = raw[1 * kTileP + tid];
+            u.nzm = raw[2 * kTileP + tid];
+            u.nz100c = (int)(100u * (uint32_t)u.nzc);
+            u.nz100m = (int)(100u * (uint32_t)u.nzm);
+            u.fnzc = (float)u.nzc;
+            u.fnzm = (float)u.nzm;
+            i64 fmx = raw64[0 * kTileP + tid];
+            if (fmx < 0) fmx = 0; // maxCount starts at 0 (normalize_score.go:27)
+            if (u.kind == 2) fmx >>= prm.sh.s[DIM_FM];
+            u.fmax = (int)fmx;
+            u.finv = fmx > 0 ? (float)(1.0 / (double)fmx) : 0.f;
+            u.count = (int)raw64[3 * kTileP + tid];
+            u.alo = 0;
+            u.arange32 = 0;
+            u.ainv = 0.f;
+            if (kAlloc && u.count > 0) {
+                const i64 hi = raw64[1 * kTileP + tid], lo = -raw64[2 * kTileP + tid];
+                const i64 range = (i64)((u64)hi - (u64)lo);
+                u.alo = lo;
+                if (range >= 0 && range < (1 << 24)) {
+                    u.arange32 = (int)range;
+                    u.ainv = range > 0 ? (float)(100.0 / (double)range) : 0.f;
+                } else {
+                    u.arange32 = -1;
+                }
+            }
+            uint32_t h = (uint32_t)(prm.seed ^ (prm.seed >> 32)) ^ ((uint32_t)(tile_p0 + tid) * 0x85EBCA6Bu);
+            h ^= h >> 15;
+            h *= 0x9E3779B1u;
+            u.hmul = h | 1u;
+            u._pad = 0;
+            s_pod[tid] = u;
+        }
+        __syncthreads();
+        if (tid == 0 && it + 2 < n_tiles) {
+            fence_proxy_async();
+            issue_pods(it + 2);
+        }
+        mbar_wait(&bars[2 + stage], parity);
+
+        const uint32_t* bmrow = s_bm + stage * kTileP * 16 + warp * 2;
+        i64* rowp = (i64*)prm.scores + tile_p0 * prm.score_stride + node_tile0 + nloc[0];
+        for (int jp = 0; jp < n_valid; ++jp, rowp += prm.score_stride) {
+            const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz100c nz100m
+            const float4 q3 = *(const float4*)&s_pod[jp].fnzc; // fnzc fnzm finv ainv
+            const int4 q4 = *(const int4*)&s_pod[jp].fmax;     // fmax count arange32 kind
+            const uint32_t hmul = s_pod[jp].hmul;
+            const uint2 fw = *(const uint2*)(bmrow + jp * 16);
+            const bool feas[2] = {(bool)((fw.x >> lane) & 1u), (bool)((fw.y >> lane) & 1u)};
+            const int kind = q4.w;
+            int tot[2];
+            uint32_t key = 0;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                int t = 0;
+                if (kFlex) { // FlexGPU.Score + DefaultNormalizeScore(reverse) (flex_gpu.go:142-176, normalize_score.go:26-54)
+                    int v = 100;
+                    if (q4.x != 0 && kind != 0) {
+                        const int s100 = kind == 1 ? g100[j] : m100[j];
+                        const float sf = kind == 1 ? g100f[j] : m100f[j];
+                        v = 100 - qfix32(s100, q4.x, sf * q3.z);
+                        if (tile_has_neg && s100 < 0) {
+                            // over-committed device: Go's '/' truncates toward zero like C++; the score leaves
+                            // [0,100] and the framework aborts the cycle (runtime/framework.go:920-923)
+                            v = 100 - s100 / q4.x;
+                            if (feas[j] && q4.y >= 2 && (v > 100 || v < 0))
+                                atomicMax((i64*)prm.select_key + prm.p_pad + (tile_p0 + jp), (i64)1);
+                        }
+                    }
+                    t += v * prm.w_flex;
+                }
+                if (kFit) { // Least/MostAllocated over cpu and memory, non-zero requests (least_allocated.go:29-57, most_allocated.go:29-61)
+                    int sc, sm;
+                    if (!kMost) {
+                        sc = qfix32(x100c[j] - q2.z, capc[j], fmaf(-q3.x, invc[j], xqc[j]));
+                        sm = qfix32(x100m[j] - q2.w, capm[j], fmaf(-q3.y, invm[j], xqm[j]));
+                        sc = q2.x > xc[j] ? 0 : sc; // requested > capacity → 0
+                        sm = q2.y > xm[j] ? 0 : sm;
+                    } else {
+                        sc = qfix32(x100c[j] + q2.z, capc[j], fmaf(q3.x, invc[j], xqc[j]));
+                        sm = qfix32(x100m[j] + q2.w, capm[j], fmaf(q3.y, invm[j], xqm[j]));
+                        sc = q2.x > capc[j] - xc[j] ? 100 : sc; // requested clamps to capacity
+                        sm = q2.y > capm[j] - xm[j] ? 100 : sm;
+                    }
+                    int v;
+                    if (SPEC & SP_W_EQ) {
+                        v = (sc + sm) >> 1;
+                    } else { // Σ score·w / Σ w, w in [1,100]: exact through a float floor
+                        const int num = sc * prm.fit_w_cpu + sm * prm.fit_w_mem;
+                        v = __float_as_int(__fadd_rd(((float)num + 0.5f) * prm.fit_inv_wsum, 8388608.0f)) & 0x7fffff;
+                    }
+                    t += v * prm.w_fit;
+                }
+                if (kAlloc) { // Allocatable.NormalizeScore (allocatable.go:146-171)
+                    int v = 0;
+                    if (q4.z > 0) {
+                        const int a = (int)(uint32_t)((u64)araw[j] - (u64)s_pod[jp].alo);
+                        v = qfix32((int)(100u * (uint32_t)a), q4.z, (float)a * q3.w);
+                    } else if (q4.z < 0) {
+                        const i64 alo = s_pod[jp].alo;
+                        const i64 range = (i64)((u64)__ldg((const i64*)prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + tile_p0 + jp) - (u64)alo);
+                        v = (int)((i64)((u64)((i64)((u64)araw[j] - (u64)alo)) * 100ull) / range);
+                    }
+                    t += v * prm.w_alloc;
+                }
+                tot[j] = t;
+                // selectHost candidate: score | 8 hash bits | node-in-tile, 0 = none (generic_scheduler.go:146-167)
+                const uint32_t low = (((uint32_t)nloc[j] * hmul) >> 15 & 0x1fe00u) | (uint32_t)nloc[j];
+                const uint32_t k = ((uint32_t)(t + 1) << 17) | low;
+                key = max(key, feas[j] ? k : 0u);
+            }
+            if (inrange[0]) __stcs(rowp, (i64)(u64)(uint32_t)tot[0]);
+            if (inrange[1]) __stcs(rowp + 32, (i64)(u64)(uint32_t)tot[1]);
+            key = __reduce_max_sync(0xffffffffu, key);
+            if (lane == 0) wkey[jp * kWarps + warp] = key;
+            if (tile_has_panic && q4.y >= 2) { // FlexGPU.Score → NewGPUNode panics (flex_gpu.go:148)
+                const bool pz = (feas[0] && npanic[0]) || (feas[1] && npanic[1]);
+                if (__ballot_sync(0xffffffffu, pz) && lane == 0) atomicMax((i64*)prm.select_key + 2 * prm.p_pad + (tile_p0 + jp), (i64)1);
+            }
+        }
+        __syncthreads();
+        if (it + 2 < n_tiles) { // this stage's bitmap rows are consumed: fetch the rows of tile it+2
+            if (tid < kTileP) fence_proxy_async();
+            issue_bitmap(it + 2);
+        }
+        if (tid < n_valid) {
+            const i64 p = tile_p0 + tid;
+            uint32_t k = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) {
+                const uint32_t x = wkey[tid * kWarps + w];
+                k = x > k ? x : k;
+            }
+            if (k) {
+                const u64 t = (u64)(k >> 17) - 1, h8 = (k >> 9) & 0xffu, nl = k & 0x1ffu;
+                const u64 ng = (u64)(prm.node_base + node_tile0) + nl;
+                // cross-tile ties: re-hash the winner with the tile index so that no tile is favoured
+                uint32_t h16 = ((uint32_t)h8 << 8) | (((uint32_t)blockIdx.x * 0x9E3779B1u ^ s_pod[tid].hmul) >> 24);
+                const u64 key64 = ((t << 40) | ((u64)h16 << 24) | ng) + 1; // layout shared with the int64 kernels
+                atomicMax((i64*)prm.select_key + p, (i64)key64);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+template <uint32_t SPEC>
+void launch_reduce_spec(const NarrowParams& p, dim3 grid, cudaStream_t st) {
+    const int sm = smem_reduce(SPEC & SP_SC_ALLOC).total;
+    cudaFuncSetAttribute(reduce_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    reduce_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
+}
+template <uint32_t SPEC>
+void launch_emit_spec(const NarrowParams& p, dim3 grid, cudaStream_t st) {
+    const int sm = smem_emit().total;
+    cudaFuncSetAttribute(emit_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    emit_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
+}
+
+dim3 narrow_grid(const NarrowParams& p) {
+    return dim3((unsigned)(p.n_pad / kTileN), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
+}
+
+} // namespace
+
+// reduce: the SPEC bits that matter are the two filters, "needs the flex max", "needs Allocatable hi/lo"
+bool launch_reduce_narrow(const NarrowParams& p, uint32_t spec, void* stream) {
+    const dim3 g = narrow_grid(p);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (spec & (SP_FLEX_F | SP_FIT_F | SP_SC_FLEX | SP_SC_ALLOC)) {
+#define RCASE(v)                         \
+    case v:                              \
+        launch_reduce_spec<v>(p, g, st); \
+        return true;
+        RCASE(SP_FLEX_F | SP_FIT_F | SP_SC_FLEX)
+        RCASE(SP_FLEX_F | SP_FIT_F | SP_SC_FLEX | SP_SC_ALLOC)
+        RCASE(SP_FLEX_F | SP_FIT_F)
+        RCASE(SP_FLEX_F | SP_FIT_F | SP_SC_ALLOC)
+        RCASE(SP_FLEX_F | SP_SC_FLEX)
+        RCASE(SP_FIT_F)
+        RCASE(SP_FIT_F | SP_SC_FLEX)
+        RCASE(SP_FLEX_F)
+#undef RCASE
+        default:
+            return false;
+    }
+}
+
+bool launch_emit_narrow(const NarrowParams& p, uint32_t spec, void* stream) {
+    const dim3 g = narrow_grid(p);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (spec & (SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST | SP_SC_ALLOC | SP_W_EQ)) {
+#define ECASE(v)                       \
+    case v:                            \
+        launch_emit_spec<v>(p, g, st); \
+        return true;
+        ECASE(SP_SC_FLEX | SP_SC_FIT | SP_W_EQ) // C2 / C5: FlexGPU + LeastAllocated cpu:1 memory:1
+        ECASE(SP_SC_FLEX | SP_SC_FIT)
+        ECASE(SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST | SP_W_EQ)
+        ECASE(SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST)
+        ECASE(SP_SC_FLEX | SP_SC_ALLOC) // C1: FlexGPU + Allocatable
+        ECASE(SP_SC_FLEX)               // the reference's own profile: FlexGPU only
+        ECASE(SP_SC_FIT | SP_W_EQ)
+        ECASE(SP_SC_FIT)
+        ECASE(SP_SC_FLEX | SP_SC_FIT | SP_SC_ALLOC | SP_W_EQ)
+        ECASE(SP_SC_FLEX | SP_SC_FIT | SP_SC_ALLOC)
+        ECASE(SP_SC_ALLOC)
+#undef ECASE
+        default:
+            return false;
+    }
+}
+
+uint32_t narrow_spec_bits(bool flex_f, bool fit_f, bool sc_flex, bool sc_fit, bool fit_most, bool sc_alloc, bool w_eq) {
+    return (flex_f ? SP_FLEX_F : 0) | (fit_f ? SP_FIT_F : 0) | (sc_flex ? SP_SC_FLEX : 0) | (sc_fit ? SP_SC_FIT : 0) |
+           ((sc_fit && fit_most) ? SP_FIT_MOST : 0) | (sc_alloc ? SP_SC_ALLOC : 0) | ((sc_fit && w_eq) ? SP_W_EQ : 0);
+}
+
+} // namespace fgs
