@@ -15,6 +15,8 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
+#include <type_traits>
 
 #include "kernels.cuh"
 #include "kernels_narrow.cuh"
@@ -26,7 +28,7 @@ namespace {
 typedef long long i64;
 typedef unsigned long long u64;
 constexpr i64 kI64Min = (i64)0x8000000000000000ull;
-constexpr int kPass = (int)0x80000000;
+constexpr int kNone = (int)0x80000000; // node side: below every pod value, sentinels included; also 'no feasible node'
 constexpr int kNever = 0x7fffffff;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -75,6 +77,22 @@ __device__ __forceinline__ int qfix32(int x, int d, float est) {
 
 constexpr uint32_t SP_FLEX_F = 1, SP_FIT_F = 2, SP_SC_FLEX = 4, SP_SC_FIT = 8, SP_FIT_MOST = 16, SP_SC_ALLOC = 32, SP_W_EQ = 64;
 
+// rare paths kept out of line so that they add no loop-carried address arithmetic to the pod loops
+__device__ __noinline__ void raise_flag(i64* row, i64 idx) { atomicMax(row + idx, (i64)1); }
+
+__device__ __forceinline__ i64 warp_max_i64(i64 v) {
+    const int hi = (int)(v >> 32);
+    const int mhi = __reduce_max_sync(0xffffffffu, hi);
+    const uint32_t mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? (uint32_t)v : 0u);
+    return (i64)(((u64)(uint32_t)mhi << 32) | mlo);
+}
+
+// Both kernels run the same software pipeline over the CTA's pod tiles, ONE __syncthreads per tile:
+//   TMA (cp.async.bulk → mbarrier) brings tile k+2's pod columns while tile k is evaluated;
+//   warps 0-1 turn tile k+1's columns into the per-pod broadcast records right after finishing tile k;
+//   per-warp results of tile k are flushed after the barrier while tile k+1 is already running.
+// Every shared buffer is double-buffered by tile parity.
+
 // =================================================================================================
 // pass A
 // =================================================================================================
@@ -96,24 +114,17 @@ __host__ __device__ inline SmemR smem_reduce(bool alloc) {
     L.raw_stage_bytes = PN_COLS * kTileP * 4;
     off += 2 * L.raw_stage_bytes;
     L.pod = off;
-    off += kTileP * (int)sizeof(PodR);
-    L.wred = off; // int2 {max flex score, count | panic<<31} [kTileP][kWarps]
-    off += kTileP * kWarps * 8;
+    off += 2 * kTileP * (int)sizeof(PodR);
+    L.wred = off; // int2 {max flex score, count | panic<<31} [2][kTileP][kWarps]
+    off += 2 * kTileP * kWarps * 8;
     L.whi = off;
-    off += alloc ? kTileP * kWarps * 8 : 0;
+    off += alloc ? 2 * kTileP * kWarps * 8 : 0;
     L.wnlo = off;
-    off += alloc ? kTileP * kWarps * 8 : 0;
-    L.bm = off; // uint32 [kTileP][16]
-    off += kTileP * 16 * 4;
+    off += alloc ? 2 * kTileP * kWarps * 8 : 0;
+    L.bm = off; // uint32 [2][kTileP][16]
+    off += 2 * kTileP * 16 * 4;
     L.total = off;
     return L;
-}
-
-__device__ __forceinline__ i64 warp_max_i64(i64 v) {
-    const int hi = (int)(v >> 32);
-    const int mhi = __reduce_max_sync(0xffffffffu, hi);
-    const uint32_t mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? (uint32_t)v : 0u);
-    return (i64)(((u64)(uint32_t)mhi << 32) | mlo);
 }
 
 template <uint32_t SPEC>
@@ -122,11 +133,6 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
     constexpr bool kAlloc = SPEC & SP_SC_ALLOC;
     const SmemR L = smem_reduce(kAlloc);
     uint64_t* bars = (uint64_t*)(smem + L.bars);
-    PodR* s_pod = (PodR*)(smem + L.pod);
-    int2* wred = (int2*)(smem + L.wred);
-    i64* whi = (i64*)(smem + L.whi);
-    i64* wnlo = (i64*)(smem + L.wnlo);
-    uint32_t* bm = (uint32_t*)(smem + L.bm);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const i64 node_tile0 = (i64)blockIdx.x * kTileN;
@@ -136,12 +142,27 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
     const int n_tiles = (int)((pod_end - pod_begin + kTileP - 1) / kTileP);
     if (n_tiles <= 0) return;
 
-    auto issue = [&](int it) {
+    auto issue = [&](int it) { // one thread
         const int stage = it & 1;
         const i64 p0 = pod_begin + (i64)it * kTileP;
         int* dst = (int*)(smem + L.raw + stage * L.raw_stage_bytes);
         mbar_expect_tx(&bars[stage], (uint32_t)L.raw_stage_bytes);
         for (int c = 0; c < PN_COLS; ++c) bulk_g2s(dst + c * kTileP, prm.pn + (i64)c * prm.p_pad + p0, kTileP * 4, &bars[stage]);
+    };
+    auto derive = [&](int it) { // threads 0..63
+        const int stage = it & 1;
+        mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
+        const int* raw = (const int*)(smem + L.raw + stage * L.raw_stage_bytes);
+        PodR u;
+        u.lim_g = raw[PN_LIM_G * kTileP + tid];
+        u.lim_m = raw[PN_LIM_M * kTileP + tid];
+        u.rc = raw[PN_RC * kTileP + tid];
+        u.rm = raw[PN_RM * kTileP + tid];
+        u.re = raw[PN_RE * kTileP + tid];
+        u.rs0 = raw[PN_RS0 * kTileP + tid];
+        u.rs1 = raw[PN_RS1 * kTileP + tid];
+        u.kind = raw[PN_KIND * kTileP + tid];
+        ((PodR*)(smem + L.pod))[stage * kTileP + tid] = u;
     };
     if (tid == 0) {
         mbar_init(&bars[0], 1);
@@ -156,7 +177,7 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
 
     // node tile → registers (thread owns nodes 64·warp + lane and + 32, so each ballot is one bitmap word)
     int thr_g[2], thr_m[2], fc[2], fm[2], fe[2], fs0[2], fs1[2], gsc[2], msc[2];
-    bool node_ok[2], node_panic[2];
+    int node_ok[2], node_panic[2];
     i64 araw[2];
     uint32_t flags_or = 0;
 #pragma unroll
@@ -174,36 +195,37 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
         fs1[j] = (SPEC & SP_FIT_F) ? C(NN_FS1) : kNever;
         gsc[j] = C(NN_GSCORE);
         msc[j] = C(NN_MSCORE);
-        node_ok[j] = (fl & FGS_NF_VALID) && (!(SPEC & SP_FIT_F) || (fl & NDF_PODS_OK)); // fit.go:259
-        node_panic[j] = fl & FGS_NF_REF_PANIC;
+        node_panic[j] = (fl & FGS_NF_REF_PANIC) ? 1 : 0;
         araw[j] = kAlloc ? __ldg((const i64*)prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n) : 0;
+        // node-only verdicts folded into the compares (every pod value, sentinels included, is > kNone):
+        // a row that is not a node fails FlexGPU's side, "too many pods" (fit.go:259) fails Fit's side
+        if (!(fl & FGS_NF_VALID)) thr_g[j] = thr_m[j] = kNone;
+        if ((SPEC & SP_FIT_F) && !(fl & NDF_PODS_OK)) fc[j] = kNone;
     }
     const bool tile_has_panic = (SPEC & SP_FLEX_F) && __syncthreads_or((flags_or & FGS_NF_REF_PANIC) != 0);
+    if (tid < kTileP) derive(0);
+    __syncthreads();
+    if (tid == 0 && n_tiles > 2) {
+        fence_proxy_async();
+        issue(2);
+    }
+    const i64 word0 = node_tile0 / 32; // 16 words = 64 bytes per pod row per CTA
 
     for (int it = 0; it < n_tiles; ++it) {
         const int stage = it & 1;
         const i64 tile_p0 = pod_begin + (i64)it * kTileP;
         const i64 left = prm.n_pods - tile_p0;
         const int n_valid = left >= kTileP ? kTileP : (left > 0 ? (int)left : 0);
-        mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
-        if (tid < kTileP) {
-            const int* raw = (const int*)(smem + L.raw + stage * L.raw_stage_bytes);
-            PodR u;
-            u.lim_g = raw[PN_LIM_G * kTileP + tid];
-            u.lim_m = raw[PN_LIM_M * kTileP + tid];
-            u.rc = raw[PN_RC * kTileP + tid];
-            u.rm = raw[PN_RM * kTileP + tid];
-            u.re = raw[PN_RE * kTileP + tid];
-            u.rs0 = raw[PN_RS0 * kTileP + tid];
-            u.rs1 = raw[PN_RS1 * kTileP + tid];
-            u.kind = raw[PN_KIND * kTileP + tid];
-            s_pod[tid] = u;
-        }
-        __syncthreads();
-        if (tid == 0 && it + 2 < n_tiles) {
-            fence_proxy_async();
-            issue(it + 2);
-        }
+        const PodR* s_pod = (const PodR*)(smem + L.pod) + stage * kTileP;
+        int2* wred = (int2*)(smem + L.wred) + stage * kTileP * kWarps;
+        i64* whi = (i64*)(smem + L.whi) + stage * kTileP * kWarps;
+        i64* wnlo = (i64*)(smem + L.wnlo) + stage * kTileP * kWarps;
+        uint32_t* bm = (uint32_t*)(smem + L.bm) + stage * kTileP * 16;
+
+        // the pod loop exists twice: tiles without a node on which NewGPUNode would panic (the normal case) carry
+        // none of the bookkeeping for it
+        auto pod_loop = [&](auto rare_tag) {
+        constexpr bool kRare = decltype(rare_tag)::value;
         for (int jp = 0; jp < n_valid; ++jp) {
             const int4 a = *(const int4*)&s_pod[jp].lim_g;
             const int4 b = *(const int4*)&s_pod[jp].re;
@@ -216,9 +238,9 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
                 const bool flex_ok = a.x <= thr_g[j] && a.y <= thr_m[j];
                 // Fit.Filter: request <= allocatable − requested per resource (fit.go:277-326)
                 const bool fit_ok = a.z <= fc[j] && a.w <= fm[j] && b.x <= fe[j] && b.y <= fs0[j] && b.z <= fs1[j];
-                bool ok = flex_ok && fit_ok && node_ok[j];
-                if (tile_has_panic) { // NewGPUNode would panic inside FlexGPU.Filter (flex_gpu.go:101)
-                    const bool reach = (kind == 1 || kind == 2) && flex_ok && node_panic[j] && (prm.flex_filter_first || (fit_ok && node_ok[j]));
+                bool ok = flex_ok && fit_ok;
+                if (kRare) { // NewGPUNode would panic inside FlexGPU.Filter (flex_gpu.go:101)
+                    const bool reach = (kind == 1 || kind == 2) && flex_ok && node_panic[j] && (prm.flex_filter_first || fit_ok);
                     fpanic = fpanic || reach;
                     ok = ok && !reach;
                 }
@@ -226,7 +248,7 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
             }
             const uint32_t b0 = __ballot_sync(0xffffffffu, feas[0]);
             const uint32_t b1 = __ballot_sync(0xffffffffu, feas[1]);
-            int vflex = kPass;
+            int vflex = kNone;
             if (SPEC & SP_SC_FLEX) {
                 int s0 = 0, s1 = 0;
                 if (kind == 1) {
@@ -236,10 +258,10 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
                     s0 = msc[0];
                     s1 = msc[1];
                 }
-                vflex = __reduce_max_sync(0xffffffffu, max(feas[0] ? s0 : kPass, feas[1] ? s1 : kPass));
+                vflex = __reduce_max_sync(0xffffffffu, max(feas[0] ? s0 : kNone, feas[1] ? s1 : kNone));
             }
             uint32_t cnt = (uint32_t)(__popc(b0) + __popc(b1));
-            if (tile_has_panic && __ballot_sync(0xffffffffu, fpanic)) cnt |= 0x80000000u;
+            if (kRare && __ballot_sync(0xffffffffu, fpanic)) cnt |= 0x80000000u;
             if (kAlloc) {
                 i64 vhi = kI64Min, vnlo = kI64Min;
 #pragma unroll
@@ -260,12 +282,20 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
                 *(uint2*)&bm[jp * 16 + warp * 2] = make_uint2(b0, b1);
             }
         }
+        };
+        if (tile_has_panic) pod_loop(std::true_type{});
+        else pod_loop(std::false_type{});
+        if (tid < kTileP && it + 1 < n_tiles) derive(it + 1);
         __syncthreads();
-        // ---- flush the tile: per-pod partials → global atomics, bitmap rows → whole sectors ----------
+        if (tid == 0 && it + 3 < n_tiles) { // tile it+1's columns are consumed: that stage takes tile it+3
+            fence_proxy_async();
+            issue(it + 3);
+        }
+        // ---- flush tile `it` (overlaps tile it+1 of the faster warps) ------------------------------
         if (tid < n_valid) {
             const i64 p = tile_p0 + tid;
             uint32_t c = 0, pn = 0;
-            int vf = kPass;
+            int vf = kNone;
             i64 vh = kI64Min, vl = kI64Min;
 #pragma unroll
             for (int w = 0; w < kWarps; ++w) {
@@ -281,7 +311,7 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
             }
             if (c) atomicAdd((u64*)prm.reduce_sum + p, (u64)c);
             if (pn) atomicMax((i64*)prm.reduce_max + (i64)RR_FILTER_PANIC * prm.p_pad + p, (i64)1);
-            if ((SPEC & SP_SC_FLEX) && vf != kPass) {
+            if ((SPEC & SP_SC_FLEX) && vf != kNone) {
                 // back to the reference's units: merged across shards and read by either emit kernel
                 const i64 v = s_pod[tid].kind == 2 ? (i64)vf * ((i64)1 << prm.sh.s[DIM_FM]) : (i64)vf;
                 atomicMax((i64*)prm.reduce_max + (i64)RR_FLEX_MAX * prm.p_pad + p, v);
@@ -291,14 +321,10 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
                 if (vl != kI64Min) atomicMax((i64*)prm.reduce_max + (i64)RR_ALLOC_NEGLO * prm.p_pad + p, vl);
             }
         }
-        {
-            const i64 word0 = node_tile0 / 32; // 16 words = 64 bytes per pod row per CTA
-            for (int idx = tid; idx < n_valid * 16; idx += kThreads) {
-                const int jp = idx >> 4, w = idx & 15;
-                prm.bitmap[(tile_p0 + jp) * prm.words_per_row + word0 + w] = bm[idx];
-            }
+        for (int idx = tid; idx < n_valid * 16; idx += kThreads) { // bitmap rows as whole 32-byte sectors
+            const int jp = idx >> 4, w = idx & 15;
+            prm.bitmap[(tile_p0 + jp) * prm.words_per_row + word0 + w] = bm[idx];
         }
-        __syncthreads();
     }
 }
 
@@ -327,9 +353,9 @@ __host__ __device__ inline SmemE smem_emit() {
     L.raw_stage_bytes = 3 * kTileP * 4 + 4 * kTileP * 8; // kind, nzc, nzm + flex max, alloc hi, alloc −lo, count
     off += 2 * L.raw_stage_bytes;
     L.pod = off;
-    off += kTileP * (int)sizeof(PodE);
+    off += 2 * kTileP * (int)sizeof(PodE);
     L.wkey = off;
-    off += kTileP * kWarps * 4;
+    off += 2 * kTileP * kWarps * 4;
     L.bm = off; // uint32 [2][kTileP][16]: the feasibility words of this node tile, two pod tiles deep
     off += 2 * kTileP * 16 * 4;
     L.total = off;
@@ -342,9 +368,6 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
     constexpr bool kFlex = SPEC & SP_SC_FLEX, kFit = SPEC & SP_SC_FIT, kAlloc = SPEC & SP_SC_ALLOC, kMost = SPEC & SP_FIT_MOST;
     const SmemE L = smem_emit();
     uint64_t* bars = (uint64_t*)(smem + L.bars); // [0,1] pod columns, [2,3] bitmap rows
-    PodE* s_pod = (PodE*)(smem + L.pod);
-    uint32_t* wkey = (uint32_t*)(smem + L.wkey);
-    uint32_t* s_bm = (uint32_t*)(smem + L.bm);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const i64 node_tile0 = (i64)blockIdx.x * kTileN;
@@ -369,12 +392,54 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
         bulk_g2s(d2 + 2 * kTileP, prm.reduce_max + (i64)RR_ALLOC_NEGLO * prm.p_pad + p0, kTileP * 8, &bars[stage]);
         bulk_g2s(d2 + 3 * kTileP, prm.reduce_sum + p0, kTileP * 8, &bars[stage]);
     };
-    // 64 threads, one 64-byte bitmap row each (rows are words_per_row apart in global memory)
+    // threads 0..63 fetch one 64-byte bitmap row each (rows are words_per_row apart in global memory)
     auto issue_bitmap = [&](int it) {
         const int stage = it & 1;
         const i64 p0 = pod_begin + (i64)it * kTileP;
+        uint32_t* s_bm = (uint32_t*)(smem + L.bm);
         if (tid == 0) mbar_expect_tx(&bars[2 + stage], (uint32_t)(kTileP * 64));
         if (tid < kTileP) bulk_g2s(s_bm + (stage * kTileP + tid) * 16, prm.bitmap + (p0 + tid) * prm.words_per_row + word0, 64, &bars[2 + stage]);
+    };
+    auto derive = [&](int it) { // threads 0..63
+        const int stage = it & 1;
+        const i64 tile_p0 = pod_begin + (i64)it * kTileP;
+        mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
+        const int* raw = (const int*)(smem + L.raw + stage * L.raw_stage_bytes);
+        const i64* raw64 = (const i64*)(raw + 3 * kTileP);
+        PodE u;
+        u.kind = raw[0 * kTileP + tid];
+        u.nzc = raw[1 * kTileP + tid];
+        u.nzm = raw[2 * kTileP + tid];
+        u.nz100c = (int)(100u * (uint32_t)u.nzc);
+        u.nz100m = (int)(100u * (uint32_t)u.nzm);
+        u.fnzc = (float)u.nzc;
+        u.fnzm = (float)u.nzm;
+        i64 fmx = raw64[0 * kTileP + tid];
+        if (fmx < 0) fmx = 0; // maxCount starts at 0 (normalize_score.go:27)
+        if (u.kind == 2) fmx >>= prm.sh.s[DIM_FM];
+        u.fmax = (int)fmx;
+        u.finv = fmx > 0 ? (float)(1.0 / (double)fmx) : 0.f;
+        u.count = (int)raw64[3 * kTileP + tid];
+        u.alo = 0;
+        u.arange32 = 0;
+        u.ainv = 0.f;
+        if (kAlloc && u.count > 0) {
+            const i64 hi = raw64[1 * kTileP + tid], lo = -raw64[2 * kTileP + tid];
+            const i64 range = (i64)((u64)hi - (u64)lo);
+            u.alo = lo;
+            if (range >= 0 && range < (1 << 24)) {
+                u.arange32 = (int)range;
+                u.ainv = range > 0 ? (float)(100.0 / (double)range) : 0.f;
+            } else {
+                u.arange32 = -1;
+            }
+        }
+        uint32_t h = (uint32_t)(prm.seed ^ (prm.seed >> 32)) ^ ((uint32_t)(tile_p0 + tid) * 0x85EBCA6Bu);
+        h ^= h >> 15;
+        h *= 0x9E3779B1u;
+        u.hmul = h | 1u;
+        u._pad = 0;
+        ((PodE*)(smem + L.pod))[stage * kTileP + tid] = u;
     };
     if (tid == 0) {
         for (int b = 0; b < 4; ++b) mbar_init(&bars[b], 1);
@@ -389,16 +454,15 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
     if (n_tiles > 1) issue_bitmap(1);
 
     // node tile → registers
-    int capc[2], xc[2], x100c[2], capm[2], xm[2], x100m[2], g100[2], m100[2], nloc[2];
+    int capc[2], xc[2], x100c[2], capm[2], xm[2], x100m[2], g100[2], m100[2], nloc[2], inr[2], npanic[2];
     float invc[2], xqc[2], invm[2], xqm[2], g100f[2], m100f[2];
     i64 araw[2];
-    bool inrange[2], npanic[2];
     uint32_t flags_or = 0;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
         nloc[j] = warp * 64 + j * 32 + lane;
         const i64 n = node_tile0 + nloc[j];
-        inrange[j] = n < prm.n_nodes;
+        inr[j] = n < prm.n_nodes ? 1 : 0;
         auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
         if (kFit) {
             capc[j] = C(NN_CAP_C);
@@ -420,73 +484,43 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
         }
         const uint32_t fl = (uint32_t)C(NN_FLAGS);
         flags_or |= fl;
-        npanic[j] = fl & FGS_NF_REF_PANIC;
+        npanic[j] = (fl & FGS_NF_REF_PANIC) ? 1 : 0;
         araw[j] = kAlloc ? __ldg((const i64*)prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n) : 0;
     }
+    // keep the tail-tile predicates in registers (the compiler would otherwise recompute the 64-bit compare per pod)
+    asm volatile("" : "+r"(inr[0]), "+r"(inr[1]));
     const bool tile_has_panic = kFlex && __syncthreads_or((flags_or & FGS_NF_REF_PANIC) != 0);
     const bool tile_has_neg = kFlex && __syncthreads_or((flags_or & NDF_MEMSCORE_NEG) != 0);
+    if (tid < kTileP) derive(0);
+    __syncthreads();
+    if (tid == 0 && n_tiles > 2) {
+        fence_proxy_async();
+        issue_pods(2);
+    }
 
     for (int it = 0; it < n_tiles; ++it) {
         const int stage = it & 1;
-        const uint32_t parity = (uint32_t)((it >> 1) & 1);
         const i64 tile_p0 = pod_begin + (i64)it * kTileP;
         const i64 left = prm.n_pods - tile_p0;
         const int n_valid = left >= kTileP ? kTileP : (left > 0 ? (int)left : 0);
-        mbar_wait(&bars[stage], parity);
-        if (tid < kTileP) {
-            const int* raw = (const int*)(smem + L.raw + stage * L.raw_stage_bytes);
-            const i64* raw64 = (const i64*)(raw + 3 * kTileP);
-            PodE u;
-            u.kind = raw[0 * kTileP + tid];
-            u.nzc = raw[1 * kTileP + tid];
-            u.nzm = raw[2 * kTileP + tid];
-            u.nz100c = (int)(100u * (uint32_t)u.nzc);
-            u.nz100m = (int)(100u * (uint32_t)u.nzm);
-            u.fnzc = (float)u.nzc;
-            u.fnzm = (float)u.nzm;
-            i64 fmx = raw64[0 * kTileP + tid];
-            if (fmx < 0) fmx = 0; // maxCount starts at 0 (normalize_score.go:27)
-            if (u.kind == 2) fmx >>= prm.sh.s[DIM_FM];
-            u.fmax = (int)fmx;
-            u.finv = fmx > 0 ? (float)(1.0 / (double)fmx) : 0.f;
-            u.count = (int)raw64[3 * kTileP + tid];
-            u.alo = 0;
-            u.arange32 = 0;
-            u.ainv = 0.f;
-            if (kAlloc && u.count > 0) {
-                const i64 hi = raw64[1 * kTileP + tid], lo = -raw64[2 * kTileP + tid];
-                const i64 range = (i64)((u64)hi - (u64)lo);
-                u.alo = lo;
-                if (range >= 0 && range < (1 << 24)) {
-                    u.arange32 = (int)range;
-                    u.ainv = range > 0 ? (float)(100.0 / (double)range) : 0.f;
-                } else {
-                    u.arange32 = -1;
-                }
-            }
-            uint32_t h = (uint32_t)(prm.seed ^ (prm.seed >> 32)) ^ ((uint32_t)(tile_p0 + tid) * 0x85EBCA6Bu);
-            h ^= h >> 15;
-            h *= 0x9E3779B1u;
-            u.hmul = h | 1u;
-            u._pad = 0;
-            s_pod[tid] = u;
-        }
-        __syncthreads();
-        if (tid == 0 && it + 2 < n_tiles) {
-            fence_proxy_async();
-            issue_pods(it + 2);
-        }
-        mbar_wait(&bars[2 + stage], parity);
+        const PodE* s_pod = (const PodE*)(smem + L.pod) + stage * kTileP;
+        uint32_t* wkey = (uint32_t*)(smem + L.wkey) + stage * kTileP * kWarps;
+        const uint32_t* bmrow = (const uint32_t*)(smem + L.bm) + stage * kTileP * 16 + warp * 2;
+        mbar_wait(&bars[2 + stage], (uint32_t)((it >> 1) & 1));
 
-        const uint32_t* bmrow = s_bm + stage * kTileP * 16 + warp * 2;
         i64* rowp = (i64*)prm.scores + tile_p0 * prm.score_stride + node_tile0 + nloc[0];
+        // two copies of the pod loop: tiles with no panicking node and no negative MemScore (the normal case) carry
+        // none of the bookkeeping for them
+        auto pod_loop = [&](auto rare_tag) {
+        constexpr bool kRare = decltype(rare_tag)::value;
+        const uint32_t lanebit = 1u << lane;
         for (int jp = 0; jp < n_valid; ++jp, rowp += prm.score_stride) {
             const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz100c nz100m
             const float4 q3 = *(const float4*)&s_pod[jp].fnzc; // fnzc fnzm finv ainv
             const int4 q4 = *(const int4*)&s_pod[jp].fmax;     // fmax count arange32 kind
             const uint32_t hmul = s_pod[jp].hmul;
             const uint2 fw = *(const uint2*)(bmrow + jp * 16);
-            const bool feas[2] = {(bool)((fw.x >> lane) & 1u), (bool)((fw.y >> lane) & 1u)};
+            const bool feas[2] = {(fw.x & lanebit) != 0, (fw.y & lanebit) != 0};
             const int kind = q4.w;
             int tot[2];
             uint32_t key = 0;
@@ -499,12 +533,11 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
                         const int s100 = kind == 1 ? g100[j] : m100[j];
                         const float sf = kind == 1 ? g100f[j] : m100f[j];
                         v = 100 - qfix32(s100, q4.x, sf * q3.z);
-                        if (tile_has_neg && s100 < 0) {
+                        if (kRare && tile_has_neg && s100 < 0) {
                             // over-committed device: Go's '/' truncates toward zero like C++; the score leaves
                             // [0,100] and the framework aborts the cycle (runtime/framework.go:920-923)
                             v = 100 - s100 / q4.x;
-                            if (feas[j] && q4.y >= 2 && (v > 100 || v < 0))
-                                atomicMax((i64*)prm.select_key + prm.p_pad + (tile_p0 + jp), (i64)1);
+                            if (feas[j] && q4.y >= 2 && (v > 100 || v < 0)) raise_flag((i64*)prm.select_key + prm.p_pad, tile_p0 + jp);
                         }
                     }
                     t += v * prm.w_flex;
@@ -544,26 +577,31 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
                     t += v * prm.w_alloc;
                 }
                 tot[j] = t;
-                // selectHost candidate: score | 8 hash bits | node-in-tile, 0 = none (generic_scheduler.go:146-167)
+                // selectHost candidate: score+1 | 8 hash bits | node-in-tile; 0 = none (generic_scheduler.go:146-167)
                 const uint32_t low = (((uint32_t)nloc[j] * hmul) >> 15 & 0x1fe00u) | (uint32_t)nloc[j];
                 const uint32_t k = ((uint32_t)(t + 1) << 17) | low;
                 key = max(key, feas[j] ? k : 0u);
             }
-            if (inrange[0]) __stcs(rowp, (i64)(u64)(uint32_t)tot[0]);
-            if (inrange[1]) __stcs(rowp + 32, (i64)(u64)(uint32_t)tot[1]);
+            if (inr[0]) __stcs(rowp, (i64)(u64)(uint32_t)tot[0]);
+            if (inr[1]) __stcs(rowp + 32, (i64)(u64)(uint32_t)tot[1]);
             key = __reduce_max_sync(0xffffffffu, key);
             if (lane == 0) wkey[jp * kWarps + warp] = key;
-            if (tile_has_panic && q4.y >= 2) { // FlexGPU.Score → NewGPUNode panics (flex_gpu.go:148)
+            if (kRare && tile_has_panic && q4.y >= 2) { // FlexGPU.Score → NewGPUNode panics (flex_gpu.go:148)
                 const bool pz = (feas[0] && npanic[0]) || (feas[1] && npanic[1]);
-                if (__ballot_sync(0xffffffffu, pz) && lane == 0) atomicMax((i64*)prm.select_key + 2 * prm.p_pad + (tile_p0 + jp), (i64)1);
+                if (__ballot_sync(0xffffffffu, pz) && lane == 0) raise_flag((i64*)prm.select_key + 2 * prm.p_pad, tile_p0 + jp);
             }
         }
+        };
+        if (tile_has_panic || tile_has_neg) pod_loop(std::true_type{});
+        else pod_loop(std::false_type{});
+        if (tid < kTileP && it + 1 < n_tiles) derive(it + 1);
         __syncthreads();
         if (it + 2 < n_tiles) { // this stage's bitmap rows are consumed: fetch the rows of tile it+2
             if (tid < kTileP) fence_proxy_async();
             issue_bitmap(it + 2);
         }
-        if (tid < n_valid) {
+        if (tid == 0 && it + 3 < n_tiles) issue_pods(it + 3); // tile it+1's columns were consumed by derive(it+1)
+        if (tid < n_valid) { // flush tile `it` (overlaps tile it+1 of the other warps)
             const i64 p = tile_p0 + tid;
             uint32_t k = 0;
 #pragma unroll
@@ -574,43 +612,81 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
             if (k) {
                 const u64 t = (u64)(k >> 17) - 1, h8 = (k >> 9) & 0xffu, nl = k & 0x1ffu;
                 const u64 ng = (u64)(prm.node_base + node_tile0) + nl;
-                // cross-tile ties: re-hash the winner with the tile index so that no tile is favoured
-                uint32_t h16 = ((uint32_t)h8 << 8) | (((uint32_t)blockIdx.x * 0x9E3779B1u ^ s_pod[tid].hmul) >> 24);
+                // cross-tile ties: mix the tile index into the low hash byte so that no tile is favoured
+                const uint32_t h16 = ((uint32_t)h8 << 8) | (((uint32_t)blockIdx.x * 0x9E3779B1u ^ s_pod[tid].hmul) >> 24);
                 const u64 key64 = ((t << 40) | ((u64)h16 << 24) | ng) + 1; // layout shared with the int64 kernels
                 atomicMax((i64*)prm.select_key + p, (i64)key64);
             }
         }
-        __syncthreads();
     }
 }
 
+// ---- launch geometry: one wave of CTAs, each with a long run of pod tiles ------------------------------------
+int g_num_sms = 0;
+
+// CTAs per resident slot: 1 = a single wave of long CTAs; more = shorter CTAs the hardware scheduler can
+// rebalance. Measured on C2 (profiles/): see kWavesReduce / kWavesEmit. FGS_WAVES_REDUCE / FGS_WAVES_EMIT override.
+int env_waves(const char* name, int dflt) {
+    const char* v = getenv(name);
+    const int w = v ? atoi(v) : 0;
+    return w > 0 ? w : dflt;
+}
+
+template <typename K>
+int pods_per_cta_for(K kernel, int smem, const NarrowParams& p, int waves) {
+    if (!g_num_sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kThreads, smem);
+    if (occ < 1) occ = 1;
+    const i64 slots = (i64)occ * g_num_sms * waves;
+    const i64 node_tiles = p.n_pad / kTileN;
+    const i64 chunks = slots / node_tiles > 0 ? slots / node_tiles : 1;
+    i64 ppc = (p.p_pad + chunks - 1) / chunks;
+    ppc = (ppc + kTileP - 1) / kTileP * kTileP;
+    if (ppc < kTileP) ppc = kTileP;
+    return (int)ppc;
+}
+
 template <uint32_t SPEC>
-void launch_reduce_spec(const NarrowParams& p, dim3 grid, cudaStream_t st) {
+void launch_reduce_spec(NarrowParams p, cudaStream_t st) {
     const int sm = smem_reduce(SPEC & SP_SC_ALLOC).total;
-    cudaFuncSetAttribute(reduce_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    static int ready = 0;
+    if (!ready) {
+        cudaFuncSetAttribute(reduce_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+        ready = 1;
+    }
+    static const int waves = env_waves("FGS_WAVES_REDUCE", 3);
+    p.pods_per_cta = pods_per_cta_for(reduce_narrow<SPEC>, sm, p, waves);
+    const dim3 grid((unsigned)(p.n_pad / kTileN), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
     reduce_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
 }
 template <uint32_t SPEC>
-void launch_emit_spec(const NarrowParams& p, dim3 grid, cudaStream_t st) {
+void launch_emit_spec(NarrowParams p, cudaStream_t st) {
     const int sm = smem_emit().total;
-    cudaFuncSetAttribute(emit_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+    static int ready = 0;
+    if (!ready) {
+        cudaFuncSetAttribute(emit_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+        ready = 1;
+    }
+    static const int waves = env_waves("FGS_WAVES_EMIT", 4);
+    p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC>, sm, p, waves);
+    const dim3 grid((unsigned)(p.n_pad / kTileN), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
     emit_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
-}
-
-dim3 narrow_grid(const NarrowParams& p) {
-    return dim3((unsigned)(p.n_pad / kTileN), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
 }
 
 } // namespace
 
 // reduce: the SPEC bits that matter are the two filters, "needs the flex max", "needs Allocatable hi/lo"
 bool launch_reduce_narrow(const NarrowParams& p, uint32_t spec, void* stream) {
-    const dim3 g = narrow_grid(p);
     cudaStream_t st = (cudaStream_t)stream;
     switch (spec & (SP_FLEX_F | SP_FIT_F | SP_SC_FLEX | SP_SC_ALLOC)) {
-#define RCASE(v)                         \
-    case v:                              \
-        launch_reduce_spec<v>(p, g, st); \
+#define RCASE(v)                      \
+    case v:                           \
+        launch_reduce_spec<v>(p, st); \
         return true;
         RCASE(SP_FLEX_F | SP_FIT_F | SP_SC_FLEX)
         RCASE(SP_FLEX_F | SP_FIT_F | SP_SC_FLEX | SP_SC_ALLOC)
@@ -627,12 +703,11 @@ bool launch_reduce_narrow(const NarrowParams& p, uint32_t spec, void* stream) {
 }
 
 bool launch_emit_narrow(const NarrowParams& p, uint32_t spec, void* stream) {
-    const dim3 g = narrow_grid(p);
     cudaStream_t st = (cudaStream_t)stream;
     switch (spec & (SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST | SP_SC_ALLOC | SP_W_EQ)) {
-#define ECASE(v)                       \
-    case v:                            \
-        launch_emit_spec<v>(p, g, st); \
+#define ECASE(v)                    \
+    case v:                         \
+        launch_emit_spec<v>(p, st); \
         return true;
         ECASE(SP_SC_FLEX | SP_SC_FIT | SP_W_EQ) // C2 / C5: FlexGPU + LeastAllocated cpu:1 memory:1
         ECASE(SP_SC_FLEX | SP_SC_FIT)

@@ -26,7 +26,7 @@ namespace {
 typedef long long i64;
 typedef unsigned long long u64;
 constexpr i64 kI64Min = (i64)0x8000000000000000ull;
-constexpr int kPass = (int)0x80000000;  // pod-side sentinel: "<= anything"
+constexpr int kPass = (int)0x80000001;  // pod-side sentinel: "<= any node value" (INT_MIN itself is the node-side "never")
 constexpr int kNever = 0x7fffffff;      // pod-side sentinel: "<= nothing"
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
