@@ -351,7 +351,7 @@ def run_ours(args):
                          "algorithmic_bytes_per_launch": emit_bytes,
                          "path_frac": (path_bytes / ((reduce_ms + emit_ms) * 1e-3) / 1e9) / peak},
             "e2e": {"value": e2e_steps * step_evals / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pd_cols * p_pad * 8,
-                    "d2h_bytes_per_step": 10 * p_pad * 8, "steps": e2e_steps,
+                    "d2h_bytes_per_step": 4 * p_pad * 8, "steps": e2e_steps,
                     "api": "fgs_evaluate (host pod table in, per-pod selected node / count / error out)"
                     if world == 1 else "fgs_stage_pods + fgs_pass_reduce + NCCL + fgs_pass_emit + NCCL + fgs_fetch_results"},
             "gpu_launches": int(launches),

@@ -72,7 +72,7 @@ int Engine::ensure_pods(int64_t p) {
         FGS_CUDA(this, cudaMalloc(&d_pods, sizeof(int64_t) * pd_cols(S) * pp));
         FGS_CUDA(this, cudaMalloc(&d_perpod, sizeof(int64_t) * kPerPodRows * pp));
         FGS_CUDA(this, cudaMallocHost(&h_pods, sizeof(int64_t) * pd_cols(S) * pp));
-        FGS_CUDA(this, cudaMallocHost(&h_perpod, sizeof(int64_t) * kPerPodRows * pp));
+        FGS_CUDA(this, cudaMallocHost(&h_perpod, sizeof(int64_t) * 4 * pp));
     }
     if (!planes_ok) {
         if (d_bitmap) cudaFree(d_bitmap);
@@ -99,6 +99,7 @@ void Engine::free_all() {
     if (d_nn) cudaFree(d_nn);
     if (d_pn) cudaFree(d_pn);
     if (d_an) cudaFree(d_an);
+    if (d_special) cudaFree(d_special);
     if (h_raw) cudaFreeHost(h_raw);
     if (h_pods) cudaFreeHost(h_pods);
     if (h_perpod) cudaFreeHost(h_perpod);
@@ -468,7 +469,13 @@ static int run_derive(Engine* e) {
     init.araw_max = INT64_MIN;
     FGS_CUDA(e, cudaMemcpyAsync(e->d_an, &init, sizeof(init), cudaMemcpyHostToDevice, e->stream));
     FGS_CUDA(e, cudaStreamSynchronize(e->stream)); // `init` lives on this stack frame
-    launch_analyze_nodes((const int64_t*)e->d_nd, e->n_nodes, e->n_pad, e->S, (NodeAnalysis*)e->d_an, e->stream);
+    if (e->special_cap < e->n_pad) {
+        if (e->d_special) cudaFree(e->d_special);
+        e->d_special = nullptr;
+        FGS_CUDA(e, cudaMalloc(&e->d_special, sizeof(int64_t) * 2 * e->n_pad));
+        e->special_cap = e->n_pad;
+    }
+    launch_analyze_nodes((const int64_t*)e->d_nd, e->n_nodes, e->n_pad, e->S, (NodeAnalysis*)e->d_an, (int64_t*)e->d_special, e->stream);
     e->launches++;
     FGS_CUDA(e, cudaGetLastError());
     FGS_CUDA(e, cudaMemcpyAsync(&e->node_an, e->d_an, sizeof(NodeAnalysis), cudaMemcpyDeviceToHost, e->stream));
@@ -616,6 +623,11 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     if (!done) launch_eval_reduce(p, e->stream);
     e->reduce_was_narrow = done;
     e->launches++;
+    if ((e->cfg.score_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
+        launch_special_pass((const uint32_t*)e->d_bitmap, e->words_per_row, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special,
+                            (const int64_t*)e->d_pods, (int64_t*)e->d_perpod, e->n_pods, e->p_pad, e->stream);
+        e->launches++;
+    }
     FGS_CUDA(e, cudaGetLastError());
     FGS_CUDA(e, cudaEventRecord(e->events[2], e->stream));
     return FGS_OK;
@@ -651,7 +663,13 @@ extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_fetch_results before an evaluation");
     cudaSetDevice(e->device);
     const int64_t P = e->n_pods, pp = e->p_pad;
-    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, e->d_perpod, sizeof(int64_t) * kPerPodRows * pp, cudaMemcpyDeviceToHost, e->stream));
+    // per-pod epilogue on the GPU (key decode + error bits), then one compact D2H: 4 × int64 per pod
+    int64_t* d_compact = (int64_t*)e->d_perpod + (int64_t)kCompactRow0 * pp;
+    launch_finalize_pods((const int64_t*)e->d_perpod, d_compact, P, pp, e->last_key_shift, e->emitted ? 1 : 0,
+                         (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0, e->stream);
+    e->launches++;
+    FGS_CUDA(e, cudaGetLastError());
+    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, d_compact, sizeof(int64_t) * 4 * pp, cudaMemcpyDeviceToHost, e->stream));
     if (out->feasible_bitmap)
         FGS_CUDA(e, cudaMemcpyAsync(out->feasible_bitmap, e->d_bitmap, sizeof(uint32_t) * P * e->words_per_row, cudaMemcpyDeviceToHost, e->stream));
     if (out->scores && e->emitted)
@@ -659,30 +677,11 @@ extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
     FGS_CUDA(e, cudaEventRecord(e->events[4], e->stream));
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
     const int64_t* h = (const int64_t*)e->h_perpod;
-    const int64_t* filter_panic = h + (int64_t)RR_FILTER_PANIC * pp;
-    const int64_t* count = h + (int64_t)FGS_REDUCE_ROWS * pp;
-    const int64_t* key = h + (int64_t)(FGS_REDUCE_ROWS + 1) * pp;
-    const int64_t* e_range = key + pp;
-    const int64_t* e_panic = key + 2 * pp;
-    const int shift = e->last_key_shift;
-    for (int64_t p = 0; p < P; ++p) {
-        if (out->feasible_count) out->feasible_count[p] = (int32_t)count[p];
-        uint32_t err = 0;
-        if (filter_panic[p] > 0) err |= FGS_PODERR_REF_PANIC;
-        if (e->emitted) {
-            if (e_range[p] > 0) err |= FGS_PODERR_SCORE_RANGE;
-            if (e_panic[p] > 0) err |= FGS_PODERR_REF_PANIC;
-        }
-        if (out->pod_err) out->pod_err[p] = err;
-        int32_t sel = -1;
-        int64_t sc = 0;
-        if (e->emitted && key[p] > 0) {
-            const uint64_t k = (uint64_t)key[p] - 1;
-            sel = (int32_t)(k & 0xffffffu);
-            sc = (int64_t)(k >> shift);
-        }
-        if (out->selected_node) out->selected_node[p] = sel;
-        if (out->selected_score) out->selected_score[p] = sc;
+    for (int64_t p = 0; p < P; ++p) { // widths of the caller's arrays differ from the device rows: plain copies
+        if (out->feasible_count) out->feasible_count[p] = (int32_t)h[p];
+        if (out->selected_node) out->selected_node[p] = (int32_t)h[pp + p];
+        if (out->selected_score) out->selected_score[p] = h[2 * pp + p];
+        if (out->pod_err) out->pod_err[p] = (uint32_t)h[3 * pp + p];
     }
     out->words_per_row = e->words_per_row;
     out->score_row_stride = e->score_stride;

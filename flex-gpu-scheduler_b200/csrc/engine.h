@@ -11,8 +11,9 @@
 
 namespace fgs {
 
-// per-pod device block: reduce_max[FGS_REDUCE_ROWS] | reduce_sum | select_key[3]
-constexpr int kPerPodRows = FGS_REDUCE_ROWS + 1 + 3;
+// per-pod device block: reduce_max[FGS_REDUCE_ROWS] | reduce_sum | select_key[3] | compact results[4]
+constexpr int kCompactRow0 = FGS_REDUCE_ROWS + 1 + 3;
+constexpr int kPerPodRows = kCompactRow0 + 4;
 
 struct GangState; // gang_quota.cu
 
@@ -56,6 +57,8 @@ struct Engine {
     void* d_nn = nullptr;
     void* d_pn = nullptr;
     void* d_an = nullptr;
+    void* d_special = nullptr; // int64 [2][n_pad]: nodes with a negative MemScore or on which NewGPUNode panics
+    int64_t special_cap = 0;
     int64_t nn_cap = 0, pn_cap = 0;
     int decide_narrow(const fgs_pod_table* t);
     void fill_narrow_params(NarrowParams* p) const;

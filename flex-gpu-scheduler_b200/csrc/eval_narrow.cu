@@ -454,10 +454,9 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
     if (n_tiles > 1) issue_bitmap(1);
 
     // node tile → registers
-    int capc[2], xc[2], x100c[2], capm[2], xm[2], x100m[2], g100[2], m100[2], nloc[2], inr[2], npanic[2];
+    int capc[2], xc[2], x100c[2], capm[2], xm[2], x100m[2], g100[2], m100[2], nloc[2], inr[2], mneg[2];
     float invc[2], xqc[2], invm[2], xqm[2], g100f[2], m100f[2];
     i64 araw[2];
-    uint32_t flags_or = 0;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
         nloc[j] = warp * 64 + j * 32 + lane;
@@ -477,20 +476,22 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
             xqm[j] = __int_as_float(C(NN_XQ_M));
         }
         if (kFlex) {
+            // a negative MemScore (over-committed device) is kept as magnitude + sign: Go's '/' truncates toward
+            // zero, so 100 − (100·s)/max = 100 + floor(100·|s|/max). Whether that leaves [0,100] and aborts the
+            // cycle is decided per pod by special_pass / finalize_pods, not here.
+            const int ms = C(NN_MSCORE);
             g100[j] = 100 * C(NN_GSCORE);
-            m100[j] = 100 * C(NN_MSCORE);
+            m100[j] = 100 * (ms < 0 ? -ms : ms);
+            mneg[j] = ms < 0 ? 1 : 0;
             g100f[j] = __int_as_float(C(NN_GS100F));
-            m100f[j] = __int_as_float(C(NN_MS100F));
+            m100f[j] = fabsf(__int_as_float(C(NN_MS100F)));
         }
-        const uint32_t fl = (uint32_t)C(NN_FLAGS);
-        flags_or |= fl;
-        npanic[j] = (fl & FGS_NF_REF_PANIC) ? 1 : 0;
         araw[j] = kAlloc ? __ldg((const i64*)prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n) : 0;
     }
     // keep the tail-tile predicates in registers (the compiler would otherwise recompute the 64-bit compare per pod)
     asm volatile("" : "+r"(inr[0]), "+r"(inr[1]));
-    const bool tile_has_panic = kFlex && __syncthreads_or((flags_or & FGS_NF_REF_PANIC) != 0);
-    const bool tile_has_neg = kFlex && __syncthreads_or((flags_or & NDF_MEMSCORE_NEG) != 0);
+    uint32_t lanebit = 1u << lane;
+    asm volatile("" : "+r"(lanebit)); // opaque: keeps the feasibility test a single LOP3 with predicate output
     if (tid < kTileP) derive(0);
     __syncthreads();
     if (tid == 0 && n_tiles > 2) {
@@ -509,11 +510,6 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
         mbar_wait(&bars[2 + stage], (uint32_t)((it >> 1) & 1));
 
         i64* rowp = (i64*)prm.scores + tile_p0 * prm.score_stride + node_tile0 + nloc[0];
-        // two copies of the pod loop: tiles with no panicking node and no negative MemScore (the normal case) carry
-        // none of the bookkeeping for them
-        auto pod_loop = [&](auto rare_tag) {
-        constexpr bool kRare = decltype(rare_tag)::value;
-        const uint32_t lanebit = 1u << lane;
         for (int jp = 0; jp < n_valid; ++jp, rowp += prm.score_stride) {
             const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz100c nz100m
             const float4 q3 = *(const float4*)&s_pod[jp].fnzc; // fnzc fnzm finv ainv
@@ -532,13 +528,8 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
                     if (q4.x != 0 && kind != 0) {
                         const int s100 = kind == 1 ? g100[j] : m100[j];
                         const float sf = kind == 1 ? g100f[j] : m100f[j];
-                        v = 100 - qfix32(s100, q4.x, sf * q3.z);
-                        if (kRare && tile_has_neg && s100 < 0) {
-                            // over-committed device: Go's '/' truncates toward zero like C++; the score leaves
-                            // [0,100] and the framework aborts the cycle (runtime/framework.go:920-923)
-                            v = 100 - s100 / q4.x;
-                            if (feas[j] && q4.y >= 2 && (v > 100 || v < 0)) raise_flag((i64*)prm.select_key + prm.p_pad, tile_p0 + jp);
-                        }
+                        const int q = qfix32(s100, q4.x, sf * q3.z);
+                        v = (kind == 2 && mneg[j]) ? 100 + q : 100 - q;
                     }
                     t += v * prm.w_flex;
                 }
@@ -586,14 +577,7 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
             if (inr[1]) __stcs(rowp + 32, (i64)(u64)(uint32_t)tot[1]);
             key = __reduce_max_sync(0xffffffffu, key);
             if (lane == 0) wkey[jp * kWarps + warp] = key;
-            if (kRare && tile_has_panic && q4.y >= 2) { // FlexGPU.Score → NewGPUNode panics (flex_gpu.go:148)
-                const bool pz = (feas[0] && npanic[0]) || (feas[1] && npanic[1]);
-                if (__ballot_sync(0xffffffffu, pz) && lane == 0) raise_flag((i64*)prm.select_key + 2 * prm.p_pad, tile_p0 + jp);
-            }
         }
-        };
-        if (tile_has_panic || tile_has_neg) pod_loop(std::true_type{});
-        else pod_loop(std::false_type{});
         if (tid < kTileP && it + 1 < n_tiles) derive(it + 1);
         __syncthreads();
         if (it + 2 < n_tiles) { // this stage's bitmap rows are consumed: fetch the rows of tile it+2

@@ -730,6 +730,52 @@ __global__ void init_perpod(i64* perpod, i64 p_pad) {
 }
 } // namespace
 
+namespace {
+// Per-pod epilogue: decode the selectHost key and derive the cycle-error bits.
+//  * REF_PANIC: FlexGPU.Filter reached NewGPUNode on a node where it panics, or FlexGPU.Score would (it calls
+//    NewGPUNode on every feasible node, flex_gpu.go:148) — scoring only runs with >= 2 feasible nodes
+//    (generic_scheduler.go:112-127).
+//  * SCORE_RANGE: a feasible node with a negative raw score s makes 100 − (100·s)/max exceed 100 as soon as
+//    100·|s| >= max (Go's '/' truncates toward zero) — runtime/framework.go:920-923 aborts the cycle. It is the
+//    only way a normalised score on this path leaves [0,100].
+__global__ void finalize_pods(const i64* __restrict__ perpod, i64* __restrict__ compact, i64 n_pods, i64 p_pad, int key_shift, int emitted,
+                              int sc_flex) {
+    const i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    auto R = [&](int row) { return perpod[(i64)row * p_pad + p]; };
+    const i64 count = R(FGS_REDUCE_ROWS);
+    const i64 key = R(FGS_REDUCE_ROWS + 1);
+    uint32_t err = 0;
+    if (R(RR_FILTER_PANIC) > 0) err |= FGS_PODERR_REF_PANIC;
+    if (sc_flex && emitted && count >= 2) {
+        if (R(RR_SCORE_PANIC) > 0) err |= FGS_PODERR_REF_PANIC;
+        const i64 fmax = R(RR_FLEX_MAX), neg = R(RR_NEG_MAG);
+        if (fmax > 0 && neg > 0 && 100 * neg >= fmax) err |= FGS_PODERR_SCORE_RANGE;
+    }
+    if (emitted) { // flags raised inside the int64 emit kernel (same conditions, kept as a cross-check)
+        if (R(FGS_REDUCE_ROWS + 2) > 0) err |= FGS_PODERR_SCORE_RANGE;
+        if (R(FGS_REDUCE_ROWS + 3) > 0) err |= FGS_PODERR_REF_PANIC;
+    }
+    i64 sel = -1, score = 0;
+    if (emitted && key > 0) {
+        const u64 k = (u64)key - 1;
+        sel = (i64)(k & 0xffffffu);
+        score = (i64)(k >> key_shift);
+    }
+    compact[0 * p_pad + p] = count;
+    compact[1 * p_pad + p] = sel;
+    compact[2 * p_pad + p] = score;
+    compact[3 * p_pad + p] = (i64)err;
+}
+} // namespace
+
+void launch_finalize_pods(const int64_t* perpod, int64_t* compact, int64_t n_pods, int64_t p_pad, int key_shift, int emitted, int sc_flex,
+                          void* stream) {
+    if (n_pods <= 0) return;
+    finalize_pods<<<(unsigned)((n_pods + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const i64*)perpod, (i64*)compact, n_pods, p_pad, key_shift,
+                                                                                     emitted, sc_flex);
+}
+
 void launch_init_perpod(int64_t* perpod, int64_t p_pad, void* stream) {
     init_perpod<<<(unsigned)((p_pad + 255) / 256), 256, 0, (cudaStream_t)stream>>>((i64*)perpod, (i64)p_pad);
 }

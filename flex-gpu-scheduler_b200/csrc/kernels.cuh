@@ -60,7 +60,10 @@ enum PodCol : int {
 inline __host__ __device__ int pd_cols(int S) { return PD_FIXED_COLS + S; }
 
 // rows of reduce_max
-enum ReduceRow : int { RR_FLEX_MAX = 0, RR_ALLOC_HI, RR_ALLOC_NEGLO, RR_FILTER_PANIC, RR_SPARE0, RR_SPARE1 };
+// RR_NEG_MAG: largest |FlexGPU score| among feasible nodes whose score is negative (an over-committed device);
+// RR_SCORE_PANIC: a feasible node on which FlexGPU.Score's NewGPUNode would panic. Both are turned into the
+// pod's error bits by finalize_pods once the feasible count and the flex maximum are known.
+enum ReduceRow : int { RR_FLEX_MAX = 0, RR_ALLOC_HI, RR_ALLOC_NEGLO, RR_FILTER_PANIC, RR_NEG_MAG, RR_SCORE_PANIC };
 
 constexpr int kThreads = 256;       // threads per CTA of the evaluation kernels
 constexpr int kNodesPerThread = 2;
@@ -109,6 +112,10 @@ struct EvalParams {
 cudaError_t eval_setup();
 // reduce_max rows := INT64_MIN (panic row := 0), reduce_sum := 0, select_key rows := 0
 void launch_init_perpod(int64_t* perpod, int64_t p_pad, void* stream);
+// per-pod results in the form the host reads back: [0] feasible count, [1] selected node (global index, -1 none),
+// [2] selected score, [3] FGS_PODERR_* bits — int64 [4][p_pad]
+void launch_finalize_pods(const int64_t* perpod, int64_t* compact, int64_t n_pods, int64_t p_pad, int key_shift, int emitted, int sc_flex,
+                          void* stream);
 void launch_derive(const DeriveParams& p, void* stream);
 void launch_eval_reduce(const EvalParams& p, void* stream);
 void launch_eval_emit(const EvalParams& p, void* stream);

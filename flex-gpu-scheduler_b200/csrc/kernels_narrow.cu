@@ -74,7 +74,8 @@ __device__ __forceinline__ int qfix32(int x, int d, float est) {
 // ---- narrowing kernels --------------------------------------------------------------------------
 
 // OR and MAX of the derived node columns per resource dimension (valid nodes only)
-__global__ void __launch_bounds__(256) analyze_nodes(const i64* __restrict__ nd, i64 n_nodes, i64 n_pad, int S, NodeAnalysis* out) {
+__global__ void __launch_bounds__(256) analyze_nodes(const i64* __restrict__ nd, i64 n_nodes, i64 n_pad, int S, NodeAnalysis* out,
+                                                     i64* __restrict__ special) {
     const i64 n = (i64)blockIdx.x * blockDim.x + threadIdx.x;
     u64 o[ND_DIMS];
     i64 mx[ND_DIMS];
@@ -111,6 +112,11 @@ __global__ void __launch_bounds__(256) analyze_nodes(const i64* __restrict__ nd,
             const i64 ms = C(ND_MEM_SCORE);
             acc(DIM_FM, ms < 0 ? -ms : ms); // a negative MemScore (over-committed device) keeps its sign when narrowed
             if (ms < 0) negscore = 1;
+            if (ms < 0 || (fl & FGS_NF_REF_PANIC)) { // nodes the per-pod error bits depend on (special_pass)
+                const int k = atomicAdd(&out->n_special, 1);
+                special[k] = n | ((fl & FGS_NF_REF_PANIC) ? ((i64)1 << 40) : 0);
+                special[n_pad + k] = ms < 0 ? -ms : 0;
+            }
             if (C(ND_CAP_CPU) <= 0 || C(ND_CAP_MEM) <= 0) capzero = 1;
             const i64 ar = C(ND_ALLOC_RAW);
             amin = ar;
@@ -151,6 +157,30 @@ __global__ void __launch_bounds__(256) analyze_nodes(const i64* __restrict__ nd,
         atomicMax((i64*)&out->araw_max, s_amax);
         if (s_flags) atomicOr(&out->flags, s_flags);
     }
+}
+
+// The few nodes that can put a pod's cycle into an error state — a negative MemScore (over-committed device) or
+// a node NewGPUNode panics on — are handled here, outside the evaluation loops: one thread per pod looks up the
+// feasibility bit of each such node in the bitmap the reduce pass wrote (finalize_pods turns the two rows into
+// FGS_PODERR_* once the feasible count and the flex maximum are merged).
+__global__ void __launch_bounds__(128) special_pass(const uint32_t* __restrict__ bitmap, i64 words_per_row, const i64* __restrict__ special,
+                                                    i64 n_pad, int n_special, const i64* __restrict__ pods, i64* __restrict__ reduce_max,
+                                                    i64 n_pods, i64 p_pad) {
+    const i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    const uint32_t kind = (uint32_t)pods[(i64)PD_META * p_pad + p] & 3u;
+    const uint32_t* row = bitmap + p * words_per_row;
+    i64 neg = 0, panic = 0;
+    for (int k = 0; k < n_special; ++k) {
+        const i64 e = special[k];
+        const i64 n = e & 0xffffffffll;
+        if (!((row[n >> 5] >> (n & 31)) & 1u)) continue;
+        const i64 mag = special[n_pad + k];
+        if (kind == 2 && mag > neg) neg = mag; // MemScore is the raw score of fractional pods only (flex_gpu.go:160-162)
+        if (e >> 40) panic = 1;
+    }
+    if (neg) reduce_max[(i64)RR_NEG_MAG * p_pad + p] = neg;
+    if (panic) reduce_max[(i64)RR_SCORE_PANIC * p_pad + p] = 1;
 }
 
 __device__ __forceinline__ int narrow_free(i64 v, int sh) { return v < 0 ? -1 : (int)(v >> sh); }
@@ -220,9 +250,16 @@ __global__ void __launch_bounds__(256) narrow_pods(const i64* __restrict__ pods,
 
 } // namespace
 
-void launch_analyze_nodes(const int64_t* nd, int64_t n_nodes, int64_t n_pad, int S, NodeAnalysis* out, void* stream) {
+void launch_analyze_nodes(const int64_t* nd, int64_t n_nodes, int64_t n_pad, int S, NodeAnalysis* out, int64_t* special, void* stream) {
     if (n_nodes <= 0) return;
-    analyze_nodes<<<(unsigned)((n_nodes + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const i64*)nd, n_nodes, n_pad, S, out);
+    analyze_nodes<<<(unsigned)((n_nodes + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const i64*)nd, n_nodes, n_pad, S, out, (i64*)special);
+}
+
+void launch_special_pass(const uint32_t* bitmap, int64_t words_per_row, const int64_t* special, int64_t n_pad, int n_special,
+                         const int64_t* pods, int64_t* reduce_max, int64_t n_pods, int64_t p_pad, void* stream) {
+    if (n_special <= 0 || n_pods <= 0) return;
+    special_pass<<<(unsigned)((n_pods + 127) / 128), 128, 0, (cudaStream_t)stream>>>(bitmap, words_per_row, (const i64*)special, n_pad, n_special,
+                                                                                  (const i64*)pods, (i64*)reduce_max, n_pods, p_pad);
 }
 
 void launch_narrow_nodes(const int64_t* nd, int64_t n_pad, const NarrowShifts& sh, int fit_most, int* nn, void* stream) {

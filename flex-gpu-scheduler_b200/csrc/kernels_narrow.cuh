@@ -25,7 +25,7 @@ struct NodeAnalysis {
     long long max_val[ND_DIMS];
     long long araw_min, araw_max;
     int flags; // bit0: a valid node has cpu or memory capacity <= 0; bit1: a MemScore is negative
-    int _pad;
+    int n_special; // valid nodes that feed a pod's error bits: negative MemScore, or NewGPUNode panics on them
 };
 
 enum NarrowNodeCol : int {
@@ -58,7 +58,11 @@ struct NarrowParams {
     uint64_t seed;
 };
 
-void launch_analyze_nodes(const int64_t* nd, int64_t n_nodes, int64_t n_pad, int S, NodeAnalysis* out, void* stream);
+// special[0][k] = node index | (panics ? 1<<40 : 0), special[1][k] = |MemScore| when it is negative, else 0
+void launch_analyze_nodes(const int64_t* nd, int64_t n_nodes, int64_t n_pad, int S, NodeAnalysis* out, int64_t* special, void* stream);
+// per pod: RR_NEG_MAG / RR_SCORE_PANIC rows of reduce_max from the feasibility bits of the special nodes
+void launch_special_pass(const uint32_t* bitmap, int64_t words_per_row, const int64_t* special, int64_t n_pad, int n_special,
+                         const int64_t* pods, int64_t* reduce_max, int64_t n_pods, int64_t p_pad, void* stream);
 void launch_narrow_nodes(const int64_t* nd, int64_t n_pad, const NarrowShifts& sh, int fit_most, int* nn, void* stream);
 void launch_narrow_pods(const int64_t* pods, int64_t p_pad, int S, const NarrowShifts& sh, uint32_t fit_ignored, int* pn, void* stream);
 uint32_t narrow_spec_bits(bool flex_f, bool fit_f, bool sc_flex, bool sc_fit, bool fit_most, bool sc_alloc, bool w_eq);
