@@ -158,6 +158,9 @@ ABI = {
     "fgs_status_plane": (C.c_int, [C.c_void_p, C.c_uint32, p_u8]),
     "fgs_gang_check": (C.c_int, [C.c_void_p, C.POINTER(Snapshot), C.POINTER(Podset), C.POINTER(Podgroups), p_u8, p_u8, p_i32]),
     "fgs_quota_check": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(Quotas), C.POINTER(PodTable), p_i64, p_i64, p_u8]),
+    # device pointers are passed as plain integers (c_void_p): the caller owns that memory
+    "fgs_quota_check_static": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int64]),
     "fgs_get_timings": (C.c_int, [C.c_void_p, C.POINTER(Timings)]),
     "fgs_synth_create": (C.c_int, [C.POINTER(SynthParams), C.POINTER(C.c_void_p)]),
     "fgs_synth_destroy": (None, [C.c_void_p]),

@@ -737,3 +737,118 @@ extern "C" int fgs_quota_check(fgs_engine* eh, const fgs_pod_table* pods, const 
     std::memcpy(code, h + o_code, P);
     return FGS_OK;
 }
+
+// =================================================================================================
+// fgs_quota_check_static — the ElasticQuota check for callers that are not allowed to allocate
+// =================================================================================================
+//
+// Who needs this: code that runs where device allocation is off the table — a scheduler plugin called on a
+// latency-critical path that must never block on the CUDA allocator, a host that hands this library a fixed
+// arena of device memory and forbids anything beyond it, or a caller that is in the middle of recording work
+// and may not touch the allocator. fgs_quota_check sizes and grows an internal arena with cudaMalloc; this
+// variant does not: the tables and the result live in device memory the caller already owns, and the only
+// working memory the kernels need (the Σused / Σmin aggregate, its key mask, one byte per namespace) sits in
+// the fixed-size __device__ array below, which every GPU that loads libfgs carries until the process exits
+// (about 4.6 KB). It runs the same two kernels as fgs_quota_check (quota_aggregate, quota_check_pods), without
+// nominated pods.
+//
+// Rules that follow from the shared, fixed scratch:
+//   * at most FGS_STATIC_QUOTA_MAX_NS namespaces and FGS_MAX_SCALARS scalar slots — larger inputs are refused;
+//   * the FIRST call on each device looks up the device address of the scratch (cudaGetSymbolAddress) and keeps
+//     it; make that first call during start-up, before any stream capture begins on that device;
+//   * the scratch keeps whatever the previous call left in it; each call clears the part it reads before use;
+//   * all calls on one device share the scratch: two calls whose kernels may overlap on the GPU (different
+//     streams, no ordering between them) race. Order them on one stream or with events.
+#define FGS_STATIC_QUOTA_MAX_NS 4096
+
+namespace {
+constexpr size_t kStaticAggOff = 0;        // int64 agg[2][2 + FGS_MAX_SCALARS]
+constexpr size_t kStaticPresentOff = 256;  // uint32 key mask of Σused
+constexpr size_t kStaticOverOff = 512;     // uint8 ns_over_min[FGS_STATIC_QUOTA_MAX_NS]
+constexpr size_t kStaticBytes = kStaticOverOff + FGS_STATIC_QUOTA_MAX_NS;
+constexpr int kStaticMaxDevices = 64;
+
+// In host code this name is only a handle for cudaGetSymbolAddress — not an address a kernel could use.
+static __device__ __align__(256) unsigned char g_quota_static_scratch[kStaticBytes];
+static void* g_quota_static_dev_ptr[kStaticMaxDevices]; // device address of the array, per device ordinal
+
+void static_err(char* buf, int64_t len, const char* msg) {
+    if (!buf || len <= 0) return;
+    int64_t i = 0;
+    for (; msg[i] && i < len - 1; ++i) buf[i] = msg[i];
+    buf[i] = 0;
+}
+} // namespace
+
+extern "C" int fgs_quota_check_static(void* stream, int32_t n_scalars, int64_t n_ns, const uint8_t* dev_has_eq, const int64_t* dev_min,
+                                      const int64_t* dev_max, const int64_t* dev_used, const uint32_t* dev_used_present, int64_t n_pods,
+                                      const int64_t* dev_pod_req, const uint32_t* dev_pod_present, const int32_t* dev_pod_ns,
+                                      uint8_t* dev_code, char* errbuf, int64_t errbuf_len) {
+    if (n_scalars < 2 || n_scalars > FGS_MAX_SCALARS) {
+        static_err(errbuf, errbuf_len, "fgs_quota_check_static: n_scalars must be in [2, 8]");
+        return FGS_E_INVALID;
+    }
+    if (n_ns < 0 || n_ns > FGS_STATIC_QUOTA_MAX_NS) {
+        static_err(errbuf, errbuf_len, "fgs_quota_check_static: more than 4096 namespaces do not fit the fixed scratch; use fgs_quota_check");
+        return FGS_E_TOO_LARGE;
+    }
+    if (n_pods < 0 || (n_pods > 0 && (!dev_pod_req || !dev_pod_present || !dev_pod_ns || !dev_code)) ||
+        (n_ns > 0 && (!dev_has_eq || !dev_min || !dev_max || !dev_used || !dev_used_present))) {
+        static_err(errbuf, errbuf_len, "fgs_quota_check_static: null table pointer");
+        return FGS_E_INVALID;
+    }
+    if (n_pods == 0) return FGS_OK;
+    int dev = -1;
+    cudaError_t ce = cudaGetDevice(&dev);
+    if (ce != cudaSuccess || dev < 0 || dev >= kStaticMaxDevices) {
+        static_err(errbuf, errbuf_len, "fgs_quota_check_static: no current CUDA device (or ordinal >= 64)");
+        return FGS_E_CUDA;
+    }
+    // once per device, with that device current: resolve the device address of the scratch array
+    if (!g_quota_static_dev_ptr[dev]) {
+        void* ptr = nullptr;
+        ce = cudaGetSymbolAddress((void**)&ptr, g_quota_static_scratch);
+        if (ce != cudaSuccess || !ptr) {
+            static_err(errbuf, errbuf_len, cudaGetErrorString(ce));
+            return FGS_E_CUDA;
+        }
+        g_quota_static_dev_ptr[dev] = ptr;
+    }
+    unsigned char* scratch = (unsigned char*)g_quota_static_dev_ptr[dev];
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array still holds the previous call's aggregate and flags: start from zero
+    ce = cudaMemsetAsync(scratch, 0, kStaticOverOff + (size_t)n_ns, st);
+    if (ce != cudaSuccess) {
+        static_err(errbuf, errbuf_len, cudaGetErrorString(ce));
+        return FGS_E_CUDA;
+    }
+    QuotaParams qp;
+    std::memset(&qp, 0, sizeof(qp));
+    qp.has_eq = dev_has_eq;
+    qp.qmin = (const i64*)dev_min;
+    qp.qmax = (const i64*)dev_max;
+    qp.qused = (const i64*)dev_used;
+    qp.used_present = dev_used_present;
+    qp.agg = (i64*)(scratch + kStaticAggOff);
+    qp.agg_present = (uint32_t*)(scratch + kStaticPresentOff);
+    qp.ns_over_min = scratch + kStaticOverOff;
+    qp.n_ns = n_ns;
+    qp.S = n_scalars;
+    qp.W = 2 + n_scalars;
+    qp.pod_req = (const i64*)dev_pod_req;
+    qp.pod_present = dev_pod_present;
+    qp.pod_ns = dev_pod_ns;
+    qp.pod_prio = dev_pod_ns; // priorities only matter against nominated pods, and this variant has none
+    qp.pod_uid = nullptr;
+    qp.n_pods = n_pods;
+    qp.n_nom = 0;
+    qp.code = dev_code;
+    quota_aggregate<<<1, 256, 0, st>>>(qp);
+    quota_check_pods<<<(unsigned)((n_pods + 255) / 256), 256, 0, st>>>(qp);
+    ce = cudaGetLastError();
+    if (ce != cudaSuccess) {
+        static_err(errbuf, errbuf_len, cudaGetErrorString(ce));
+        return FGS_E_CUDA;
+    }
+    return FGS_OK;
+}

@@ -186,6 +186,26 @@ int fgs_quota_check(fgs_engine* e, const fgs_pod_table* pods, const fgs_quotas* 
                     const fgs_pod_table* nominated, const int64_t* pod_uid,
                     const int64_t* nominated_uid, uint8_t* code);
 
+/* The same ElasticQuota check for callers that must not allocate. This entry point has no counterpart
+ * in the reference; it exists for hosts that keep device memory in a fixed arena of their own, for code on a
+ * latency-critical path that may never wait on the CUDA allocator, and for callers that are recording work
+ * and cannot touch the allocator at that moment. It needs no engine and calls no cudaMalloc / cudaFree (or
+ * anything else that allocates): every table and the result are DEVICE pointers the caller owns, and the
+ * kernels' working memory is a fixed __device__ array inside libfgs (about 4.6 KB per GPU, held until exit).
+ *   dev_has_eq[n_ns], dev_min/max/used[n_ns][2+S] ({mcpu, mem, scalars}), dev_used_present[n_ns]: as fgs_quotas
+ *   dev_pod_req[2+S][n_pods] (column-major {mcpu, mem, scalars}), dev_pod_present[n_pods], dev_pod_ns[n_pods]
+ *   dev_code[n_pods]: 0 Success, 1 over Max, 2 aggregated used over the sum of Min (no nominated pods)
+ * Limits: n_ns <= 4096 and 2 <= n_scalars <= 8, otherwise FGS_E_TOO_LARGE / FGS_E_INVALID with the reason in
+ * errbuf (may be NULL). The first call on a device resolves the array's device address: make it at start-up,
+ * before any stream capture on that device. All calls share the array (each clears what it reads first), so
+ * two calls that can overlap on the GPU race: keep them on one stream or order them with events.
+ * Asynchronous on `stream`; the result is ready when the stream reaches that point. */
+int fgs_quota_check_static(void* stream, int32_t n_scalars, int64_t n_ns, const uint8_t* dev_has_eq,
+                           const int64_t* dev_min, const int64_t* dev_max, const int64_t* dev_used,
+                           const uint32_t* dev_used_present, int64_t n_pods, const int64_t* dev_pod_req,
+                           const uint32_t* dev_pod_present, const int32_t* dev_pod_ns, uint8_t* dev_code,
+                           char* errbuf, int64_t errbuf_len);
+
 /* ---- timings ---------------------------------------------------------------------------- */
 
 typedef struct fgs_timings {
