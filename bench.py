@@ -160,20 +160,12 @@ def run_reference(args):
     return 0
 
 
-def torch_view(ptr, nbytes_elems, dtype, torch):
-    """zero-copy torch tensor over a device pointer owned by the engine"""
-    class _A:
-        pass
-    a = _A()
-    a.__cuda_array_interface__ = {"shape": (nbytes_elems,), "typestr": "<i8", "data": (int(ptr), False), "version": 2}
-    return torch.as_tensor(a, device="cuda")
-
-
 def run_ours(args):
     import torch
     import torch.distributed as dist
     import flex_gpu_scheduler_b200 as fgs
     from flex_gpu_scheduler_b200 import _lib as L
+    from flex_gpu_scheduler_b200 import distributed as D
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -191,8 +183,7 @@ def run_ours(args):
     n_pods = args.pods or base["n_pending"]
     # every rank generates the same cluster (deterministic) and packs only its node range
     synth = fgs.config_synth(cfg_id, n_nodes=n_total, n_pending=n_pods)
-    per = (n_total + world - 1) // world
-    n0, n1 = min(n_total, rank * per), min(n_total, (rank + 1) * per)
+    n0, n1 = D.shard_bounds(n_total, world, rank)
     plugins = fgs.config_plugins(cfg_id)
     stream = torch.cuda.Stream()
     eng = fgs.Engine(device=local, n_scalars=2, node_index_base=n0, total_nodes=n_total, stream=stream.cuda_stream)
@@ -210,18 +201,13 @@ def run_ours(args):
     multi = len(batches) > 1
 
     def merges_after_reduce(view):
-        if world == 1:
-            return
-        rm = torch_view(view.reduce_max, L.FGS_REDUCE_ROWS * view.p_pad, "i8", torch)
-        rs = torch_view(view.reduce_sum, view.p_pad, "i8", torch)
-        dist.all_reduce(rm, op=dist.ReduceOp.MAX)
-        dist.all_reduce(rs, op=dist.ReduceOp.SUM)
+        if world > 1:
+            rm, rs, _ = D.device_views(torch, view)
+            D.merge_after_reduce(dist, rm, rs)
 
     def merges_after_emit(view):
-        if world == 1:
-            return
-        sk = torch_view(view.select_key, 3 * view.p_pad, "i8", torch)
-        dist.all_reduce(sk, op=dist.ReduceOp.MAX)
+        if world > 1:
+            D.merge_after_emit(dist, D.device_views(torch, view)[2])
 
     with torch.cuda.stream(stream):
         lib = L.load()
