@@ -1,0 +1,62 @@
+"""Run under torchrun with N >= 2 GPUs: node-sharded evaluation (NCCL merges) against the oracle on the whole
+cluster. Launched by tests/test_gpu_multi.py; exits non-zero on any mismatch."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    import flex_gpu_scheduler_b200 as fgs
+    from flex_gpu_scheduler_b200 import distributed as D
+    from oracle import oracle
+
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    for cfg_id, N, P in ((2, 2311, 700), (1, 1500, 300)):
+        s = fgs.config_synth(cfg_id, n_nodes=N, n_pending=P, pm_quirk_nodes=80)
+        cfg = fgs.config_plugins(cfg_id)
+        n0, n1 = D.shard_bounds(N, world, rank)
+        stream = torch.cuda.Stream()
+        eng = fgs.Engine(device=local, n_scalars=2, node_index_base=n0, total_nodes=N, stream=stream.cuda_stream)
+        eng.set_plugins(cfg)
+        eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot, n0, n1))
+        with torch.cuda.stream(stream):
+            table = fgs.Packer(2).pods(s.pending)
+            eng.stage_pods(table)
+            rm, rs, sk = D.device_views(torch, eng.device_view())
+            eng.pass_reduce()
+            D.merge_after_reduce(dist, rm, rs)
+            eng.pass_emit()
+            D.merge_after_emit(dist, sk)
+            res = eng.fetch_results(want_planes=True)
+        ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=2)
+        feas_ref = ref.status == 0
+        # this shard's planes against the oracle's columns
+        assert np.array_equal(res.feasible(n1 - n0), feas_ref[:, n0:n1]), "bitmap shard"
+        ok = (ref.pod_err == 0) & (ref.feasible_count >= 1)
+        m = feas_ref[:, n0:n1] & ok[:, None]
+        assert np.array_equal(res.scores[:, :n1 - n0][m], ref.total[:, n0:n1][m]), "score shard (normalised over ALL shards)"
+        # merged per-pod results are identical on every rank
+        assert np.array_equal(res.feasible_count, ref.feasible_count), "merged counts"
+        assert np.array_equal(res.pod_err, ref.pod_err), "merged error bits"
+        idx = np.nonzero(ok)[0]
+        sel = res.selected_node
+        assert np.all(sel[ref.feasible_count == 0] == -1)
+        assert np.all(feas_ref[idx, sel[idx]]) and np.array_equal(ref.total[idx, sel[idx]], ref.max_total[idx]), "selected node outside tie set"
+        assert np.array_equal(res.selected_score[idx], ref.max_total[idx])
+        eng.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("multi_gpu_parity ok, world", world)
+
+
+if __name__ == "__main__":
+    main()
