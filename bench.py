@@ -193,7 +193,7 @@ def run_ours(args):
     n_shard = n1 - n0
 
     # pods go through in batches when the score matrix of the whole set would not fit comfortably
-    n_pad = (max(n_shard, 1) + 511) // 512 * 512
+    n_pad = (max(n_shard, 1) + 1023) // 1024 * 1024
     batch = n_pods if n_pods * n_pad * 8 <= 48 * 2 ** 30 else BATCH
     batches = [(b, min(n_pods, b + batch)) for b in range(0, n_pods, batch)]
     packers = [fgs.Packer(2) for _ in batches]

@@ -233,7 +233,7 @@ class Engine:
         cr.selected_score = _ptr(r.selected_score, C.c_int64)
         cr.pod_err = _ptr(r.pod_err, C.c_uint32)
         if want_planes:
-            n_pad = (max(self.n_nodes, 1) + 511) // 512 * 512
+            n_pad = (max(self.n_nodes, 1) + 1023) // 1024 * 1024  # kNodePad of the engine
             r.feasible_bitmap = np.zeros((P, n_pad // 32), np.uint32)
             r.scores = np.zeros((P, n_pad), np.int64)
             cr.feasible_bitmap = _ptr(r.feasible_bitmap, C.c_uint32)

@@ -37,7 +37,7 @@ int Engine::fail(int code, const std::string& msg) {
 }
 
 int Engine::ensure_nodes(int64_t n, int D_) {
-    const int64_t np = round_up(std::max<int64_t>(n, 1), kTileN);
+    const int64_t np = round_up(std::max<int64_t>(n, 1), kNodePad);
     if (np <= n_pad_cap && D_ <= D_cap) {
         n_pad = np;
         return FGS_OK;
@@ -336,7 +336,7 @@ int Engine::decide_narrow(const fgs_pod_table* t) {
     if (sc_fit && !ep.fit_fast) return FGS_OK;                 // scoring resources beyond cpu/memory
     if (sc_fit && (node_an.flags & 1)) return FGS_OK;          // a node with zero cpu/memory capacity drops out of the average
     const int64_t wsum = (sc_flex ? ep.w_flex : 0) + (sc_fit ? ep.w_fit : 0) + (sc_alloc ? ep.w_alloc : 0);
-    if (ep.w_flex > 327 || ep.w_fit > 327 || ep.w_alloc > 327 || wsum * 100 >= (1 << 15)) return FGS_OK; // 15-bit score field of the warp key
+    if (ep.w_flex > 163 || ep.w_fit > 163 || ep.w_alloc > 163 || wsum * 100 + 1 >= (1 << 14)) return FGS_OK; // 14-bit score field of the warp key
     const int64_t P = t->n_pods;
     uint64_t o[ND_DIMS] = {0};
     int64_t mx[ND_DIMS] = {0};

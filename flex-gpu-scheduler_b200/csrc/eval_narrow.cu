@@ -75,6 +75,15 @@ __device__ __forceinline__ int qfix32(int x, int d, float est) {
     return k + (r >> 31);
 }
 
+// Nodes per thread. Each pod iteration pays a fixed cost (broadcast loads of the pod record, loop and pointer
+// bookkeeping, one REDUX, one staged store); four nodes per thread spread it over 128 evaluations per warp.
+// Measured on C2 (profiles/): four per thread is faster for the emit pass (76.7 % vs 73.5 % of HBM peak), two for
+// the reduce pass (its per-node work is nine compares: more nodes per thread only costs occupancy).
+constexpr int kNPTe = 4, kNPTr = 2;
+constexpr int kTileNe = kThreads * kNPTe, kTileNr = kThreads * kNPTr; // nodes per CTA: 1024 / 512
+constexpr int kWordsTe = kTileNe / 32, kWordsTr = kTileNr / 32;       // bitmap words per pod row per CTA
+static_assert(kNodePad % kTileNe == 0 && kNodePad % kTileNr == 0, "node padding must cover whole CTA tiles");
+
 constexpr uint32_t SP_FLEX_F = 1, SP_FIT_F = 2, SP_SC_FLEX = 4, SP_SC_FIT = 8, SP_FIT_MOST = 16, SP_SC_ALLOC = 32, SP_W_EQ = 64;
 
 // rare paths kept out of line so that they add no loop-carried address arithmetic to the pod loops
@@ -121,8 +130,8 @@ __host__ __device__ inline SmemR smem_reduce(bool alloc) {
     off += alloc ? 2 * kTileP * kWarps * 8 : 0;
     L.wnlo = off;
     off += alloc ? 2 * kTileP * kWarps * 8 : 0;
-    L.bm = off; // uint32 [2][kTileP][16]
-    off += 2 * kTileP * 16 * 4;
+    L.bm = off; // uint32 [2][kTileP][kWordsTr]
+    off += 2 * kTileP * kWordsTr * 4;
     L.total = off;
     return L;
 }
@@ -135,7 +144,7 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
     uint64_t* bars = (uint64_t*)(smem + L.bars);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const i64 node_tile0 = (i64)blockIdx.x * kTileN;
+    const i64 node_tile0 = (i64)blockIdx.x * kTileNr;
     const i64 pod_begin = (i64)blockIdx.y * prm.pods_per_cta;
     i64 pod_end = pod_begin + prm.pods_per_cta;
     if (pod_end > prm.p_pad) pod_end = prm.p_pad;
@@ -175,14 +184,14 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
         if (n_tiles > 1) issue(1);
     }
 
-    // node tile → registers (thread owns nodes 64·warp + lane and + 32, so each ballot is one bitmap word)
-    int thr_g[2], thr_m[2], fc[2], fm[2], fe[2], fs0[2], fs1[2], gsc[2], msc[2];
-    int node_ok[2], node_panic[2];
-    i64 araw[2];
+    // node tile → registers (thread owns nodes 128·warp + 32·j + lane, so each ballot is one bitmap word)
+    int thr_g[kNPTr], thr_m[kNPTr], fc[kNPTr], fm[kNPTr], fe[kNPTr], fs0[kNPTr], fs1[kNPTr], gsc[kNPTr], msc[kNPTr];
+    int node_panic[kNPTr];
+    i64 araw[kNPTr];
     uint32_t flags_or = 0;
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        const i64 n = node_tile0 + warp * 64 + j * 32 + lane;
+    for (int j = 0; j < kNPTr; ++j) {
+        const i64 n = node_tile0 + warp * (32 * kNPTr) + j * 32 + lane;
         auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
         const uint32_t fl = (uint32_t)C(NN_FLAGS);
         flags_or |= fl;
@@ -209,7 +218,7 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
         fence_proxy_async();
         issue(2);
     }
-    const i64 word0 = node_tile0 / 32; // 16 words = 64 bytes per pod row per CTA
+    const i64 word0 = node_tile0 / 32; // kWordsTr words per pod row per CTA
 
     for (int it = 0; it < n_tiles; ++it) {
         const int stage = it & 1;
@@ -220,7 +229,7 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
         int2* wred = (int2*)(smem + L.wred) + stage * kTileP * kWarps;
         i64* whi = (i64*)(smem + L.whi) + stage * kTileP * kWarps;
         i64* wnlo = (i64*)(smem + L.wnlo) + stage * kTileP * kWarps;
-        uint32_t* bm = (uint32_t*)(smem + L.bm) + stage * kTileP * 16;
+        uint32_t* bm = (uint32_t*)(smem + L.bm) + stage * kTileP * kWordsTr;
 
         // the pod loop exists twice: tiles without a node on which NewGPUNode would panic (the normal case) carry
         // none of the bookkeeping for it
@@ -230,10 +239,10 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
             const int4 a = *(const int4*)&s_pod[jp].lim_g;
             const int4 b = *(const int4*)&s_pod[jp].re;
             const int kind = b.w;
-            bool feas[2];
+            bool feas[kNPTr];
             bool fpanic = false;
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
+            for (int j = 0; j < kNPTr; ++j) {
                 // FlexGPU.Filter: kind none passes, "both" never, else limit <= per-kind threshold (flex_gpu.go:54-116)
                 const bool flex_ok = a.x <= thr_g[j] && a.y <= thr_m[j];
                 // Fit.Filter: request <= allocatable − requested per resource (fit.go:277-326)
@@ -246,26 +255,27 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
                 }
                 feas[j] = ok;
             }
-            const uint32_t b0 = __ballot_sync(0xffffffffu, feas[0]);
-            const uint32_t b1 = __ballot_sync(0xffffffffu, feas[1]);
-            int vflex = kNone;
-            if (SPEC & SP_SC_FLEX) {
-                int s0 = 0, s1 = 0;
-                if (kind == 1) {
-                    s0 = gsc[0];
-                    s1 = gsc[1];
-                } else if (kind == 2) {
-                    s0 = msc[0];
-                    s1 = msc[1];
-                }
-                vflex = __reduce_max_sync(0xffffffffu, max(feas[0] ? s0 : kNone, feas[1] ? s1 : kNone));
+            uint32_t bal[kNPTr];
+            uint32_t cnt = 0;
+#pragma unroll
+            for (int j = 0; j < kNPTr; ++j) {
+                bal[j] = __ballot_sync(0xffffffffu, feas[j]);
+                cnt += (uint32_t)__popc(bal[j]);
             }
-            uint32_t cnt = (uint32_t)(__popc(b0) + __popc(b1));
+            int vflex = kNone;
+            if (SPEC & SP_SC_FLEX) { // raw FlexGPU score by pod kind (flex_gpu.go:153-165), max over the feasible nodes
+                int sj[kNPTr];
+#pragma unroll
+                for (int j = 0; j < kNPTr; ++j) sj[j] = kind == 1 ? gsc[j] : (kind == 2 ? msc[j] : 0);
+#pragma unroll
+                for (int j = 0; j < kNPTr; ++j) vflex = max(vflex, feas[j] ? sj[j] : kNone);
+                vflex = __reduce_max_sync(0xffffffffu, vflex);
+            }
             if (kRare && __ballot_sync(0xffffffffu, fpanic)) cnt |= 0x80000000u;
             if (kAlloc) {
                 i64 vhi = kI64Min, vnlo = kI64Min;
 #pragma unroll
-                for (int j = 0; j < 2; ++j)
+                for (int j = 0; j < kNPTr; ++j)
                     if (feas[j]) {
                         vhi = araw[j] > vhi ? araw[j] : vhi;
                         vnlo = -araw[j] > vnlo ? -araw[j] : vnlo;
@@ -279,7 +289,8 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
             }
             if (lane == 0) {
                 wred[jp * kWarps + warp] = make_int2(vflex, (int)cnt);
-                *(uint2*)&bm[jp * 16 + warp * 2] = make_uint2(b0, b1);
+                static_assert(kNPTr == 2, "one 8-byte store per warp and pod");
+                *(uint2*)&bm[jp * kWordsTr + warp * kNPTr] = make_uint2(bal[0], bal[1]);
             }
         }
         };
@@ -321,8 +332,8 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
                 if (vl != kI64Min) atomicMax((i64*)prm.reduce_max + (i64)RR_ALLOC_NEGLO * prm.p_pad + p, vl);
             }
         }
-        for (int idx = tid; idx < n_valid * 16; idx += kThreads) { // bitmap rows as whole 32-byte sectors
-            const int jp = idx >> 4, w = idx & 15;
+        for (int idx = tid; idx < n_valid * kWordsTr; idx += kThreads) { // bitmap rows as whole 32-byte sectors
+            const int jp = idx / kWordsTr, w = idx % kWordsTr;
             prm.bitmap[(tile_p0 + jp) * prm.words_per_row + word0 + w] = bm[idx];
         }
     }
@@ -356,21 +367,21 @@ __host__ __device__ inline SmemE smem_emit() {
     off += 2 * kTileP * (int)sizeof(PodE);
     L.wkey = off;
     off += 2 * kTileP * kWarps * 4;
-    L.bm = off; // uint32 [2][kTileP][16]: the feasibility words of this node tile, two pod tiles deep
-    off += 2 * kTileP * 16 * 4;
+    L.bm = off; // uint32 [2][kTileP][kWordsTe]: the feasibility words of this node tile, two pod tiles deep
+    off += 2 * kTileP * kWordsTe * 4;
     L.total = off;
     return L;
 }
 
 template <uint32_t SPEC>
-__global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant__ NarrowParams prm) {
+__global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant__ NarrowParams prm) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr bool kFlex = SPEC & SP_SC_FLEX, kFit = SPEC & SP_SC_FIT, kAlloc = SPEC & SP_SC_ALLOC, kMost = SPEC & SP_FIT_MOST;
     const SmemE L = smem_emit();
     uint64_t* bars = (uint64_t*)(smem + L.bars); // [0,1] pod columns, [2,3] bitmap rows
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const i64 node_tile0 = (i64)blockIdx.x * kTileN;
+    const i64 node_tile0 = (i64)blockIdx.x * kTileNe;
     const i64 pod_begin = (i64)blockIdx.y * prm.pods_per_cta;
     i64 pod_end = pod_begin + prm.pods_per_cta;
     if (pod_end > prm.p_pad) pod_end = prm.p_pad;
@@ -392,13 +403,14 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
         bulk_g2s(d2 + 2 * kTileP, prm.reduce_max + (i64)RR_ALLOC_NEGLO * prm.p_pad + p0, kTileP * 8, &bars[stage]);
         bulk_g2s(d2 + 3 * kTileP, prm.reduce_sum + p0, kTileP * 8, &bars[stage]);
     };
-    // threads 0..63 fetch one 64-byte bitmap row each (rows are words_per_row apart in global memory)
+    // threads 0..63 fetch one 128-byte bitmap row each (rows are words_per_row apart in global memory)
     auto issue_bitmap = [&](int it) {
         const int stage = it & 1;
         const i64 p0 = pod_begin + (i64)it * kTileP;
         uint32_t* s_bm = (uint32_t*)(smem + L.bm);
-        if (tid == 0) mbar_expect_tx(&bars[2 + stage], (uint32_t)(kTileP * 64));
-        if (tid < kTileP) bulk_g2s(s_bm + (stage * kTileP + tid) * 16, prm.bitmap + (p0 + tid) * prm.words_per_row + word0, 64, &bars[2 + stage]);
+        if (tid == 0) mbar_expect_tx(&bars[2 + stage], (uint32_t)(kTileP * kWordsTe * 4));
+        if (tid < kTileP)
+            bulk_g2s(s_bm + (stage * kTileP + tid) * kWordsTe, prm.bitmap + (p0 + tid) * prm.words_per_row + word0, kWordsTe * 4, &bars[2 + stage]);
     };
     auto derive = [&](int it) { // threads 0..63
         const int stage = it & 1;
@@ -454,12 +466,12 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
     if (n_tiles > 1) issue_bitmap(1);
 
     // node tile → registers
-    int capc[2], xc[2], x100c[2], capm[2], xm[2], x100m[2], g100[2], m100[2], nloc[2], inr[2], mneg[2];
-    float invc[2], xqc[2], invm[2], xqm[2], g100f[2], m100f[2];
-    i64 araw[2];
+    int capc[kNPTe], xc[kNPTe], x100c[kNPTe], capm[kNPTe], xm[kNPTe], x100m[kNPTe], g100[kNPTe], m100[kNPTe], nloc[kNPTe], inr[kNPTe], mneg[kNPTe];
+    float invc[kNPTe], xqc[kNPTe], invm[kNPTe], xqm[kNPTe], g100f[kNPTe], m100f[kNPTe];
+    i64 araw[kNPTe];
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
-        nloc[j] = warp * 64 + j * 32 + lane;
+    for (int j = 0; j < kNPTe; ++j) {
+        nloc[j] = warp * (32 * kNPTe) + j * 32 + lane;
         const i64 n = node_tile0 + nloc[j];
         inr[j] = n < prm.n_nodes ? 1 : 0;
         auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
@@ -489,7 +501,7 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
         araw[j] = kAlloc ? __ldg((const i64*)prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n) : 0;
     }
     // keep the tail-tile predicates in registers (the compiler would otherwise recompute the 64-bit compare per pod)
-    asm volatile("" : "+r"(inr[0]), "+r"(inr[1]));
+    asm volatile("" : "+r"(inr[0]), "+r"(inr[1]), "+r"(inr[2]), "+r"(inr[3]));
     uint32_t lanebit = 1u << lane;
     asm volatile("" : "+r"(lanebit)); // opaque: keeps the feasibility test a single LOP3 with predicate output
     if (tid < kTileP) derive(0);
@@ -506,7 +518,7 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
         const int n_valid = left >= kTileP ? kTileP : (left > 0 ? (int)left : 0);
         const PodE* s_pod = (const PodE*)(smem + L.pod) + stage * kTileP;
         uint32_t* wkey = (uint32_t*)(smem + L.wkey) + stage * kTileP * kWarps;
-        const uint32_t* bmrow = (const uint32_t*)(smem + L.bm) + stage * kTileP * 16 + warp * 2;
+        const uint32_t* bmrow = (const uint32_t*)(smem + L.bm) + stage * kTileP * kWordsTe + warp * kNPTe;
         mbar_wait(&bars[2 + stage], (uint32_t)((it >> 1) & 1));
 
         i64* rowp = (i64*)prm.scores + tile_p0 * prm.score_stride + node_tile0 + nloc[0];
@@ -515,13 +527,13 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
             const float4 q3 = *(const float4*)&s_pod[jp].fnzc; // fnzc fnzm finv ainv
             const int4 q4 = *(const int4*)&s_pod[jp].fmax;     // fmax count arange32 kind
             const uint32_t hmul = s_pod[jp].hmul;
-            const uint2 fw = *(const uint2*)(bmrow + jp * 16);
-            const bool feas[2] = {(fw.x & lanebit) != 0, (fw.y & lanebit) != 0};
+            const uint4 fw = *(const uint4*)(bmrow + jp * kWordsTe);
+            const bool feas[kNPTe] = {(fw.x & lanebit) != 0, (fw.y & lanebit) != 0, (fw.z & lanebit) != 0, (fw.w & lanebit) != 0};
             const int kind = q4.w;
-            int tot[2];
+            int tot[kNPTe];
             uint32_t key = 0;
 #pragma unroll
-            for (int j = 0; j < 2; ++j) {
+            for (int j = 0; j < kNPTe; ++j) {
                 int t = 0;
                 if (kFlex) { // FlexGPU.Score + DefaultNormalizeScore(reverse) (flex_gpu.go:142-176, normalize_score.go:26-54)
                     int v = 100;
@@ -568,13 +580,15 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
                     t += v * prm.w_alloc;
                 }
                 tot[j] = t;
-                // selectHost candidate: score+1 | 8 hash bits | node-in-tile; 0 = none (generic_scheduler.go:146-167)
-                const uint32_t low = (((uint32_t)nloc[j] * hmul) >> 15 & 0x1fe00u) | (uint32_t)nloc[j];
-                const uint32_t k = ((uint32_t)(t + 1) << 17) | low;
+                // selectHost candidate: score+1 (14 bits) | 8 hash bits | node-in-tile (10 bits); 0 = none
+                // (generic_scheduler.go:146-167)
+                const uint32_t low = (((uint32_t)nloc[j] * hmul) >> 14 & 0x3fc00u) | (uint32_t)nloc[j];
+                const uint32_t k = ((uint32_t)(t + 1) << 18) | low;
                 key = max(key, feas[j] ? k : 0u);
             }
-            if (inr[0]) __stcs(rowp, (i64)(u64)(uint32_t)tot[0]);
-            if (inr[1]) __stcs(rowp + 32, (i64)(u64)(uint32_t)tot[1]);
+#pragma unroll
+            for (int j = 0; j < kNPTe; ++j)
+                if (inr[j]) __stcs(rowp + 32 * j, (i64)(u64)(uint32_t)tot[j]);
             key = __reduce_max_sync(0xffffffffu, key);
             if (lane == 0) wkey[jp * kWarps + warp] = key;
         }
@@ -594,7 +608,7 @@ __global__ void __launch_bounds__(kThreads, 3) emit_narrow(const __grid_constant
                 k = x > k ? x : k;
             }
             if (k) {
-                const u64 t = (u64)(k >> 17) - 1, h8 = (k >> 9) & 0xffu, nl = k & 0x1ffu;
+                const u64 t = (u64)(k >> 18) - 1, h8 = (k >> 10) & 0xffu, nl = k & 0x3ffu;
                 const u64 ng = (u64)(prm.node_base + node_tile0) + nl;
                 // cross-tile ties: mix the tile index into the low hash byte so that no tile is favoured
                 const uint32_t h16 = ((uint32_t)h8 << 8) | (((uint32_t)blockIdx.x * 0x9E3779B1u ^ s_pod[tid].hmul) >> 24);
@@ -617,7 +631,7 @@ int env_waves(const char* name, int dflt) {
 }
 
 template <typename K>
-int pods_per_cta_for(K kernel, int smem, const NarrowParams& p, int waves) {
+int pods_per_cta_for(K kernel, int smem, const NarrowParams& p, int waves, int tile_n) {
     if (!g_num_sms) {
         int dev = 0;
         cudaGetDevice(&dev);
@@ -627,7 +641,7 @@ int pods_per_cta_for(K kernel, int smem, const NarrowParams& p, int waves) {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kThreads, smem);
     if (occ < 1) occ = 1;
     const i64 slots = (i64)occ * g_num_sms * waves;
-    const i64 node_tiles = p.n_pad / kTileN;
+    const i64 node_tiles = p.n_pad / tile_n;
     const i64 chunks = slots / node_tiles > 0 ? slots / node_tiles : 1;
     i64 ppc = (p.p_pad + chunks - 1) / chunks;
     ppc = (ppc + kTileP - 1) / kTileP * kTileP;
@@ -644,8 +658,8 @@ void launch_reduce_spec(NarrowParams p, cudaStream_t st) {
         ready = 1;
     }
     static const int waves = env_waves("FGS_WAVES_REDUCE", 3);
-    p.pods_per_cta = pods_per_cta_for(reduce_narrow<SPEC>, sm, p, waves);
-    const dim3 grid((unsigned)(p.n_pad / kTileN), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
+    p.pods_per_cta = pods_per_cta_for(reduce_narrow<SPEC>, sm, p, waves, kTileNr);
+    const dim3 grid((unsigned)(p.n_pad / kTileNr), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
     reduce_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
 }
 template <uint32_t SPEC>
@@ -656,9 +670,9 @@ void launch_emit_spec(NarrowParams p, cudaStream_t st) {
         cudaFuncSetAttribute(emit_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
         ready = 1;
     }
-    static const int waves = env_waves("FGS_WAVES_EMIT", 4);
-    p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC>, sm, p, waves);
-    const dim3 grid((unsigned)(p.n_pad / kTileN), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
+    static const int waves = env_waves("FGS_WAVES_EMIT", 3);
+    p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC>, sm, p, waves, kTileNe);
+    const dim3 grid((unsigned)(p.n_pad / kTileNe), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
     emit_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
 }
 

@@ -70,6 +70,7 @@ constexpr int kNodesPerThread = 2;
 constexpr int kTileN = kThreads * kNodesPerThread; // 512 nodes per CTA
 constexpr int kTileP = 64;          // pods per shared-memory tile
 constexpr int kWarps = kThreads / 32;
+constexpr int kNodePad = 1024;       // node tables are padded to this (a multiple of every kernel's node tile)
 
 struct DeriveParams {
     const int64_t* raw;
