@@ -10,6 +10,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "engine.h"
@@ -252,6 +253,11 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
     {
         const char* fw = getenv("FGS_FORCE_INT64");
         e->force_wide = fw && fw[0] == '1';
+        const char* ht = getenv("FGS_HOST_THREADS");
+        int nth = ht ? atoi(ht) : 4;
+        const int hw = (int)std::thread::hardware_concurrency();
+        if (hw > 0 && nth > hw) nth = hw;
+        e->host_threads = nth < 1 ? 1 : nth;
     }
     if (c->stream) {
         e->stream = (cudaStream_t)c->stream;
@@ -337,31 +343,23 @@ int Engine::decide_narrow(const fgs_pod_table* t) {
     if (sc_fit && (node_an.flags & 1)) return FGS_OK;          // a node with zero cpu/memory capacity drops out of the average
     const int64_t wsum = (sc_flex ? ep.w_flex : 0) + (sc_fit ? ep.w_fit : 0) + (sc_alloc ? ep.w_alloc : 0);
     if (ep.w_flex > 163 || ep.w_fit > 163 || ep.w_alloc > 163 || wsum * 100 + 1 >= (1 << 14)) return FGS_OK; // 14-bit score field of the warp key
-    const int64_t P = t->n_pods;
+    (void)t;
     uint64_t o[ND_DIMS] = {0};
     int64_t mx[ND_DIMS] = {0};
-    uint32_t extra = 0;
-    auto scan = [&](int d, const int64_t* col) {
-        uint64_t oo = 0;
-        int64_t mm = 0;
-        for (int64_t i = 0; i < P; ++i) {
-            const int64_t v = col[i];
-            oo |= (uint64_t)v;
-            mm = v > mm ? v : mm;
-        }
-        o[d] |= oo;
-        mx[d] = mm > mx[d] ? mm : mx[d];
+    auto take = [&](int d, int c) { // statistics collected while the column was staged (fgs_stage_pods)
+        o[d] |= stage_or[c];
+        mx[d] = stage_max[c] > mx[d] ? stage_max[c] : mx[d];
     };
-    scan(DIM_CPU, t->req_mcpu);
-    scan(DIM_CPU, t->nz_mcpu);
-    scan(DIM_MEM, t->req_mem);
-    scan(DIM_MEM, t->nz_mem);
-    scan(DIM_EPH, t->req_eph);
-    scan(DIM_S0, t->req_scalar + 0 * P);
-    scan(DIM_S1, t->req_scalar + 1 * P);
-    scan(DIM_FG, t->flex_gpu_limit);
-    scan(DIM_FM, t->flex_mem_limit);
-    for (int64_t i = 0; i < P; ++i) extra |= t->req_scalar_present[i];
+    take(DIM_CPU, PD_REQ_CPU);
+    take(DIM_CPU, PD_NZ_CPU);
+    take(DIM_MEM, PD_REQ_MEM);
+    take(DIM_MEM, PD_NZ_MEM);
+    take(DIM_EPH, PD_REQ_EPH);
+    take(DIM_S0, PD_FIXED_COLS + 0);
+    take(DIM_S1, PD_FIXED_COLS + 1);
+    take(DIM_FG, PD_GPU_LIM);
+    take(DIM_FM, PD_MEM_LIM);
+    const uint32_t extra = stage_present_or;
     if (extra & ~3u & ~cfg.fit_ignored_scalar_mask) return FGS_OK; // a pod asks for a scalar beyond the two flex slots
     NarrowShifts sh;
     for (int d = 0; d < ND_DIMS; ++d) {
@@ -583,9 +581,23 @@ extern "C" int fgs_stage_pods(fgs_engine* eh, const fgs_pod_table* t) {
     const int S = e->S;
     int64_t* h = (int64_t*)e->h_pods;
     FGS_CUDA(e, cudaEventRecord(e->events[0], e->stream));
+    // one pass over every column: copy into the pinned staging buffer and collect the OR / MAX that the int32
+    // specialisation needs (decide_narrow); a few host threads share the work
+    const int nth = e->host_threads;
     auto col = [&](int c, const int64_t* src) {
-        std::memcpy(h + (int64_t)c * pp, src, sizeof(int64_t) * (size_t)P);
-        std::memset(h + (int64_t)c * pp + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+        int64_t* dst = h + (int64_t)c * pp;
+        uint64_t o = 0;
+        int64_t m = 0;
+#pragma omp parallel for num_threads(nth) reduction(| : o) reduction(max : m) schedule(static)
+        for (int64_t i = 0; i < P; ++i) {
+            const int64_t v = src[i];
+            dst[i] = v;
+            o |= (uint64_t)v;
+            m = v > m ? v : m;
+        }
+        std::memset(dst + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+        e->stage_or[c] = o;
+        e->stage_max[c] = m;
     };
     col(PD_GPU_LIM, t->flex_gpu_limit);
     col(PD_MEM_LIM, t->flex_mem_limit);
@@ -594,8 +606,17 @@ extern "C" int fgs_stage_pods(fgs_engine* eh, const fgs_pod_table* t) {
     col(PD_REQ_EPH, t->req_eph);
     col(PD_NZ_CPU, t->nz_mcpu);
     col(PD_NZ_MEM, t->nz_mem);
-    for (int64_t i = 0; i < P; ++i) h[(int64_t)PD_META * pp + i] = (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]);
-    std::memset(h + (int64_t)PD_META * pp + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+    {
+        int64_t* dst = h + (int64_t)PD_META * pp;
+        uint32_t pr = 0;
+#pragma omp parallel for num_threads(nth) reduction(| : pr) schedule(static)
+        for (int64_t i = 0; i < P; ++i) {
+            dst[i] = (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]);
+            pr |= t->req_scalar_present[i];
+        }
+        std::memset(dst + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+        e->stage_present_or = pr;
+    }
     for (int s = 0; s < S; ++s) col(PD_FIXED_COLS + s, t->req_scalar + (int64_t)s * P);
     FGS_CUDA(e, cudaMemcpyAsync(e->d_pods, e->h_pods, sizeof(int64_t) * pd_cols(S) * pp, cudaMemcpyHostToDevice, e->stream));
     rc = e->decide_narrow(t); // int32 tables for this batch when every value qualifies

@@ -52,6 +52,10 @@ struct Engine {
     NarrowShifts narrow_sh;
     int narrow_nodes_sig = -1; // fit strategy the narrow node table was built for (-1 = stale)
     bool narrow_batch = false; // the staged pod batch qualifies
+    int host_threads = 4;      // threads that stage the pod columns (FGS_HOST_THREADS)
+    uint64_t stage_or[PD_FIXED_COLS + FGS_MAX_SCALARS] = {0};
+    int64_t stage_max[PD_FIXED_COLS + FGS_MAX_SCALARS] = {0};
+    uint32_t stage_present_or = 0;
     bool force_wide = false;   // FGS_FORCE_INT64=1: always take the int64 kernels (tests)
     bool reduce_was_narrow = false, emit_was_narrow = false;
     void* d_nn = nullptr;
