@@ -312,10 +312,10 @@ def run_ours(args):
         emit_bytes = P * N * 8 + N * nd_cols * 8 + P * (pd_cols + 4) * 8
         path_bytes = P * N * (8 + 1 / 8) + 2 * (N * nd_cols * 8 + P * pd_cols * 8) + P * 10 * 8
         peak, peak_src = measured_peak_gbs()
-        achieved = emit_bytes / (emit_ms * 1e-3) / 1e9
+        achieved = emit_bytes / (emit_ms * 1e-3) / 1e9  # emit_ms sums the step's emit launches (one per pod batch)
         traffic = None
         tp = os.path.join(ROOT, "profiles", "r01_emit_traffic.json")
-        if os.path.exists(tp):
+        if os.path.exists(tp) and cfg_id == 2 and len(batches) == 1 and n_pods == base["n_pending"]:
             try:
                 traffic = json.load(open(tp)).get("dram_bytes_per_launch")
             except Exception:
@@ -332,9 +332,9 @@ def run_ours(args):
                        "pod_batches": len(batches)},
             "kernel_ms": {"reduce_pass": reduce_ms, "emit_pass": emit_ms},
             "scheduling_cycles_per_sec": args.steps * n_pods / (ms * 1e-3),
-            "roofline": {"bound": "hbm", "kernel": "eval_kernel<EMIT>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": "emit_narrow (int32 emit pass)" if eng.timings()["emit_int32"] else "eval_kernel<EMIT> (int64 emit pass)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": emit_bytes,
+                         "algorithmic_bytes_per_launch": emit_bytes // len(batches), "launches_per_step": len(batches),
                          "path_frac": (path_bytes / ((reduce_ms + emit_ms) * 1e-3) / 1e9) / peak},
             "e2e": {"value": e2e_steps * step_evals / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pd_cols * p_pad * 8,
                     "d2h_bytes_per_step": 4 * p_pad * 8, "steps": e2e_steps,
