@@ -86,6 +86,7 @@ class PodTable(C.Structure):
         ("flex_gpu_limit", p_i64), ("flex_mem_limit", p_i64), ("flags", p_u32),
         ("req_mcpu", p_i64), ("req_mem", p_i64), ("req_eph", p_i64), ("req_scalar", p_i64), ("req_scalar_present", p_u32),
         ("nz_mcpu", p_i64), ("nz_mem", p_i64), ("ns", p_i32), ("pg", p_i32), ("priority", p_i32),
+        ("acct_nz_mcpu", p_i64), ("acct_nz_mem", p_i64), ("index_annot", p_i32),
     ]
 
 
@@ -117,7 +118,17 @@ class DeviceView(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("reduce_ms", C.c_float), ("emit_ms", C.c_float), ("d2h_ms", C.c_float),
-                ("kernel_launches", C.c_int64), ("reduce_int32", C.c_int32), ("emit_int32", C.c_int32)]
+                ("kernel_launches", C.c_int64), ("reduce_int32", C.c_int32), ("emit_int32", C.c_int32),
+                ("seq_ms", C.c_float), ("seq_ctas", C.c_int32)]
+
+
+class SeqOpts(C.Structure):
+    _fields_ = [("reserve_flex", C.c_int32), ("_pad", C.c_int32)]
+
+
+class SeqResults(C.Structure):
+    _fields_ = [("feasible_count", p_i32), ("selected_node", p_i32), ("selected_score", p_i64), ("pod_err", p_u32),
+                ("device_index", p_i32), ("committed", p_u8)]
 
 
 class SynthParams(C.Structure):
@@ -156,6 +167,8 @@ ABI = {
     "fgs_get_device_view": (C.c_int, [C.c_void_p, C.POINTER(DeviceView)]),
     "fgs_synchronize": (C.c_int, [C.c_void_p]),
     "fgs_status_plane": (C.c_int, [C.c_void_p, C.c_uint32, p_u8]),
+    "fgs_schedule_sequential": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(SeqOpts), C.POINTER(SeqResults)]),
+    "fgs_reserve": (C.c_int, [C.c_void_p, C.POINTER(PodTable), p_i32, p_i32]),
     "fgs_gang_check": (C.c_int, [C.c_void_p, C.POINTER(Snapshot), C.POINTER(Podset), C.POINTER(Podgroups), p_u8, p_u8, p_i32]),
     "fgs_quota_check": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(Quotas), C.POINTER(PodTable), p_i64, p_i64, p_u8]),
     # device pointers are passed as plain integers (c_void_p): the caller owns that memory

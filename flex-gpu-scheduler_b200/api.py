@@ -181,6 +181,17 @@ class Results:
         return bits[:, :n_nodes].astype(bool)
 
 
+class SeqResults:
+    def __init__(self, P):
+        n = max(P, 1)
+        self.feasible_count = np.zeros(n, np.int32)[:P]
+        self.selected_node = np.zeros(n, np.int32)[:P]
+        self.selected_score = np.zeros(n, np.int64)[:P]
+        self.pod_err = np.zeros(n, np.uint32)[:P]
+        self.device_index = np.zeros(n, np.int32)[:P]
+        self.committed = np.zeros(n, np.uint8)[:P]
+
+
 class Engine:
     """One libfgs engine = one GPU's shard of the node table."""
 
@@ -287,7 +298,32 @@ class Engine:
         t = L.Timings()
         self._check(self._lib.fgs_get_timings(self._h, C.byref(t)))
         return dict(h2d_ms=t.h2d_ms, reduce_ms=t.reduce_ms, emit_ms=t.emit_ms, d2h_ms=t.d2h_ms, kernel_launches=t.kernel_launches,
-                    reduce_int32=bool(t.reduce_int32), emit_int32=bool(t.emit_int32))
+                    reduce_int32=bool(t.reduce_int32), emit_int32=bool(t.emit_int32), seq_ms=t.seq_ms, seq_ctas=int(t.seq_ctas))
+
+    # -- sequential cycles: assume + Reserve between pods -------------------------------------------------
+    def schedule_sequential(self, pod_table, reserve_flex=True):
+        """One scheduling cycle per pod of the table, in order, committing each placement (fgs_schedule_sequential)."""
+        P = int(pod_table.contents.n_pods)
+        r = SeqResults(P)
+        cr = L.SeqResults()
+        cr.feasible_count = _ptr(r.feasible_count, C.c_int32)
+        cr.selected_node = _ptr(r.selected_node, C.c_int32)
+        cr.selected_score = _ptr(r.selected_score, C.c_int64)
+        cr.pod_err = _ptr(r.pod_err, C.c_uint32)
+        cr.device_index = _ptr(r.device_index, C.c_int32)
+        cr.committed = _ptr(r.committed, C.c_uint8)
+        o = L.SeqOpts(reserve_flex=1 if reserve_flex else 0)
+        self._check(self._lib.fgs_schedule_sequential(self._h, pod_table, C.byref(o), C.byref(cr)))
+        return r
+
+    def reserve(self, pod_table, nodes):
+        """FlexGPU.Reserve's device index for pod p on nodes[p] of the current table, without committing."""
+        P = int(pod_table.contents.n_pods)
+        nodes = np.ascontiguousarray(nodes, np.int32)
+        assert nodes.shape == (P,)
+        dev = np.zeros(max(P, 1), np.int32)
+        self._check(self._lib.fgs_reserve(self._h, pod_table, _ptr(nodes, C.c_int32), _ptr(dev, C.c_int32)))
+        return dev[:P]
 
     # -- coscheduling / capacity scheduling ----------------------------------------------------------
     def gang_check(self, snapshot, pending, podgroups):

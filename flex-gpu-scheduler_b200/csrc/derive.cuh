@@ -9,26 +9,17 @@
 
 namespace fgs {
 
-__device__ __forceinline__ void derive_one_node(const DeriveParams& prm, long long n) {
+// raw row: raw[c * rs], derived row written to nd[c * ns] (global tables: pointer to the node's element, stride
+// n_pad; the sequential kernel's shared-memory copy: stride = nodes per CTA)
+__device__ __forceinline__ void derive_row(const DeriveParams& prm, const long long* __restrict__ raw, long long rs, long long* __restrict__ nd, long long ns) {
     typedef long long i64;
     typedef unsigned long long u64;
     constexpr i64 kI64Min = (i64)0x8000000000000000ull;
     constexpr i64 kI64Max = (i64)0x7fffffffffffffffull;
     auto wmul = [](i64 a, i64 b) { return (i64)((u64)a * (u64)b); };
     auto wadd = [](i64 a, i64 b) { return (i64)((u64)a + (u64)b); };
-
-    const i64 np = prm.n_pad;
     const int S = prm.S, D = prm.D;
-    const i64* raw = (const i64*)prm.raw;
-    i64* nd = (i64*)prm.nd;
-    const int ncols = nd_cols(S);
-    if (n >= prm.n_nodes) { // padding rows: never feasible, all columns zero
-        for (int c = 0; c < ncols; ++c) nd[(i64)c * np + n] = 0;
-        nd[(i64)ND_THR_GPU * np + n] = kI64Min;
-        nd[(i64)ND_THR_MEM * np + n] = kI64Min;
-        return;
-    }
-    auto R = [&](int c) { return raw[(i64)c * np + n]; };
+    auto R = [&](int c) { return raw[(i64)c * rs]; };
     const u64 meta = (u64)R(NR_META);
     uint32_t flags = (uint32_t)meta;
     const uint32_t mono = (uint32_t)(meta >> 32);
@@ -83,7 +74,7 @@ __device__ __forceinline__ void derive_one_node(const DeriveParams& prm, long lo
     }
     const i64 alloc_raw = weight_sum != 0 ? node_score / weight_sum : 0;
 
-    auto W = [&](int c, i64 v) { nd[(i64)c * np + n] = v; };
+    auto W = [&](int c, i64 v) { nd[(i64)c * ns] = v; };
     W(ND_THR_GPU, thr_gpu);
     W(ND_THR_MEM, thr_mem);
     W(ND_FREE_CPU, R(NR_ALLOC_MCPU) - R(NR_REQ_MCPU));
@@ -103,6 +94,20 @@ __device__ __forceinline__ void derive_one_node(const DeriveParams& prm, long lo
         W(nd_free_scalar(s), R(nr_alloc_scalar(s)) - R(nr_req_scalar(S, s)));
         W(nd_alloc_scalar(S, s), R(nr_alloc_scalar(s)));
     }
+}
+
+__device__ __forceinline__ void derive_one_node(const DeriveParams& prm, long long n) {
+    typedef long long i64;
+    const i64 np = prm.n_pad;
+    i64* nd = (i64*)prm.nd;
+    if (n >= prm.n_nodes) { // padding rows: never feasible, all columns zero
+        const int ncols = nd_cols(prm.S);
+        for (int c = 0; c < ncols; ++c) nd[(i64)c * np + n] = 0;
+        nd[(i64)ND_THR_GPU * np + n] = (i64)0x8000000000000000ull;
+        nd[(i64)ND_THR_MEM * np + n] = (i64)0x8000000000000000ull;
+        return;
+    }
+    derive_row(prm, (const i64*)prm.raw + n, np, nd + n, np);
 }
 
 } // namespace fgs

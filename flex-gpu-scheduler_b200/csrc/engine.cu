@@ -108,6 +108,7 @@ void Engine::free_all() {
         if (ev) cudaEventDestroy(ev);
     if (own_stream && stream) cudaStreamDestroy(stream);
     gang_free();
+    seq_free();
 }
 
 // plugin args → kernel parameters; validation mirrors the reference constructors
@@ -438,26 +439,25 @@ static uint32_t narrow_spec(const Engine* e) {
                             ep.fit_w_cpu == ep.fit_w_mem);
 }
 
-static int run_derive(Engine* e) {
-    DeriveParams dp;
-    std::memset(&dp, 0, sizeof(dp));
-    dp.raw = (const int64_t*)e->d_raw;
-    dp.nd = (int64_t*)e->d_nd;
-    dp.n_nodes = e->n_nodes;
-    dp.n_pad = e->n_pad;
-    dp.S = e->S;
-    dp.D = e->D;
-    dp.alloc_mode = e->cfg.alloc_mode;
-    dp.alloc_n_res = (e->cfg.score_mask & FGS_PL_ALLOCATABLE) ? e->cfg.alloc_n_res : 0;
-    for (int k = 0; k < dp.alloc_n_res; ++k) {
-        dp.alloc_res[k] = e->cfg.alloc_res[k];
-        dp.alloc_w[k] = e->cfg.alloc_res_w[k];
+void Engine::fill_derive_params(DeriveParams* dp) const {
+    std::memset(dp, 0, sizeof(*dp));
+    dp->raw = (const int64_t*)d_raw;
+    dp->nd = (int64_t*)d_nd;
+    dp->n_nodes = n_nodes;
+    dp->n_pad = n_pad;
+    dp->S = S;
+    dp->D = D;
+    dp->alloc_mode = cfg.alloc_mode;
+    dp->alloc_n_res = (cfg.score_mask & FGS_PL_ALLOCATABLE) ? cfg.alloc_n_res : 0;
+    for (int k = 0; k < dp->alloc_n_res; ++k) {
+        dp->alloc_res[k] = cfg.alloc_res[k];
+        dp->alloc_w[k] = cfg.alloc_res_w[k];
     }
-    launch_derive(dp, e->stream);
-    e->launches++;
-    FGS_CUDA(e, cudaGetLastError());
-    e->nodes_derived = true;
-    // node-side analysis for the int32 specialisation (upload time only; one small round trip)
+}
+
+// node-side analysis for the int32 specialisation (one small round trip)
+int Engine::analyze_nodes_now() {
+    Engine* e = this;
     e->node_an_valid = false;
     e->narrow_nodes_sig = -1;
     if (!e->d_an) FGS_CUDA(e, cudaMalloc(&e->d_an, sizeof(NodeAnalysis)));
@@ -481,6 +481,18 @@ static int run_derive(Engine* e) {
     e->node_an_valid = true;
     return FGS_OK;
 }
+
+static int run_derive(Engine* e) {
+    DeriveParams dp;
+    e->fill_derive_params(&dp);
+    launch_derive(dp, e->stream);
+    e->launches++;
+    FGS_CUDA(e, cudaGetLastError());
+    e->nodes_derived = true;
+    return e->analyze_nodes_now();
+}
+
+int Engine::derive_now() { return run_derive(this); }
 
 // copy one table row-set into the pinned column-major staging buffer
 static void stage_node_columns(Engine* e, const fgs_node_table* t, int64_t dst0, int64_t count, int64_t src0) {

@@ -16,6 +16,7 @@ constexpr int kCompactRow0 = FGS_REDUCE_ROWS + 1 + 3;
 constexpr int kPerPodRows = kCompactRow0 + 4;
 
 struct GangState; // gang_quota.cu
+struct SeqState;  // sequential.cu
 
 struct Engine {
     int device = 0;
@@ -68,8 +69,9 @@ struct Engine {
     void fill_narrow_params(NarrowParams* p) const;
 
     GangState* gang = nullptr;
+    SeqState* seq = nullptr;
 
-    fgs_timings tm = {0, 0, 0, 0, 0, 0, 0};
+    fgs_timings tm = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     int64_t launches = 0;
 
     int fail(int code, const std::string& msg);
@@ -79,6 +81,10 @@ struct Engine {
     void fill_eval_params(EvalParams* p, const fgs_eval_opts* opts) const;
     void free_all();
     void gang_free();
+    void seq_free();
+    void fill_derive_params(DeriveParams* dp) const;
+    int derive_now();        // derive_node_columns over the whole table + analysis
+    int analyze_nodes_now(); // node-side analysis for the int32 specialisation (after any change of d_nd)
 };
 
 } // namespace fgs

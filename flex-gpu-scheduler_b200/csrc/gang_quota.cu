@@ -444,6 +444,10 @@ __global__ void __launch_bounds__(256) status_plane(const __grid_constant__ Stat
         if (panic) out = 0xF0 | FGS_CODE_ERROR;
     } else if (prm.plugin == FGS_PL_FIT) {
         out = fit_code(prm, p, n);
+    } else if (!((uint32_t)prm.nd[(i64)ND_FLAGS * prm.n_pad + n] & FGS_NF_VALID)) {
+        // a NodeInfo without a Node is never in the list findNodesThatPassFilters walks (the cache keeps such
+        // entries out of the snapshot list, internal/cache/cache.go:254,290,314-325): plain Error, no plugin
+        out = FGS_CODE_ERROR;
     } else {
         // RunFilterPlugins: profile order, first failure wins (runtime/framework.go:667-693)
         const uint32_t order[2] = {prm.flex_filter_first ? FGS_PL_FLEXGPU : FGS_PL_FIT, prm.flex_filter_first ? FGS_PL_FIT : FGS_PL_FLEXGPU};

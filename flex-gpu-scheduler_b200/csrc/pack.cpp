@@ -55,6 +55,9 @@ void PackedPods::make_view() {
     view.ns = ns.data();
     view.pg = pg.data();
     view.priority = priority.data();
+    view.acct_nz_mcpu = acct_nz_mcpu.data();
+    view.acct_nz_mem = acct_nz_mem.data();
+    view.index_annot = index_annot.data();
 }
 
 static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::string* err);
@@ -211,7 +214,8 @@ int pack_pods(const fgs_podset* pods, int64_t p0, int64_t p1, PackedPods* out, s
     t.S = S;
     auto z = [&](std::vector<int64_t>& v, int64_t k) { v.assign((size_t)k, 0); };
     z(t.flex_gpu_limit, P), z(t.flex_mem_limit, P), z(t.req_mcpu, P), z(t.req_mem, P), z(t.req_eph, P);
-    z(t.req_scalar, P * S), z(t.nz_mcpu, P), z(t.nz_mem, P);
+    z(t.req_scalar, P * S), z(t.nz_mcpu, P), z(t.nz_mem, P), z(t.acct_nz_mcpu, P), z(t.acct_nz_mem, P);
+    t.index_annot.assign((size_t)P, FGS_ANNOT_NONE);
     t.flags.assign((size_t)P, 0);
     t.req_scalar_present.assign((size_t)P, 0);
     t.ns.assign((size_t)P, 0);
@@ -223,7 +227,7 @@ int pack_pods(const fgs_podset* pods, int64_t p0, int64_t p1, PackedPods* out, s
         const PodRequest r = pod_request(pods, src);
         // API validation forbids negative quantities; the kernels rely on requests and limits being >= 0
         bool ok = in_range(l.gpu) && in_range(l.mem) && in_range(r.score_mcpu) && in_range(r.score_mem) && l.gpu >= 0 && l.mem >= 0 &&
-                  r.score_mcpu >= 0 && r.score_mem >= 0;
+                  r.score_mcpu >= 0 && r.score_mem >= 0 && in_range(r.nz_mcpu) && in_range(r.nz_mem) && r.nz_mcpu >= 0 && r.nz_mem >= 0;
         for (int k = 0; k < 3 + S; ++k) ok = ok && in_range(r.v[k]) && r.v[k] >= 0;
         if (!ok) {
             *err = "pack_pods: a quantity of pod " + std::to_string(src) + " is negative or out of range";
@@ -244,6 +248,9 @@ int pack_pods(const fgs_podset* pods, int64_t p0, int64_t p1, PackedPods* out, s
         t.req_scalar_present[(size_t)i] = r.scalar_keys;
         t.nz_mcpu[(size_t)i] = r.score_mcpu;
         t.nz_mem[(size_t)i] = r.score_mem;
+        t.acct_nz_mcpu[(size_t)i] = r.nz_mcpu;
+        t.acct_nz_mem[(size_t)i] = r.nz_mem;
+        t.index_annot[(size_t)i] = pods->index_annot ? pods->index_annot[src] : FGS_ANNOT_NONE;
         t.ns[(size_t)i] = pods->ns ? pods->ns[src] : 0;
         t.pg[(size_t)i] = pods->pg ? pods->pg[src] : -1;
         t.priority[(size_t)i] = pods->priority ? pods->priority[src] : 0;

@@ -21,9 +21,10 @@ struct PackedNodes {
 struct PackedPods {
     int64_t n = 0;
     int S = 2;
-    std::vector<int64_t> flex_gpu_limit, flex_mem_limit, req_mcpu, req_mem, req_eph, req_scalar, nz_mcpu, nz_mem;
+    std::vector<int64_t> flex_gpu_limit, flex_mem_limit, req_mcpu, req_mem, req_eph, req_scalar, nz_mcpu, nz_mem, acct_nz_mcpu,
+        acct_nz_mem;
     std::vector<uint32_t> flags, req_scalar_present;
-    std::vector<int32_t> ns, pg, priority;
+    std::vector<int32_t> ns, pg, priority, index_annot;
     fgs_pod_table view;
     void make_view();
 };

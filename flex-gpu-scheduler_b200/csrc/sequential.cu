@@ -1,0 +1,918 @@
+// sequential.cu — scheduling cycles with state: Filter + Score + selectHost for ONE pod against the current node
+// table, then the reference's `assume` (NodeInfo.AddPod on the chosen node) and FlexGPU.Reserve (device index),
+// then the next pod. One persistent, cooperative kernel runs every cycle of a queue; SURVEY.md §8(f1).
+//
+//   scheduleOne            vendor/k8s.io/kubernetes/pkg/scheduler/scheduler.go:441-540 (Schedule → assume → Reserve;
+//                          a failed Reserve forgets the pod :512-521)
+//   assume / AddPod        scheduler.go:353-370; framework/types.go:583-609,715-745
+//   FlexGPU.Reserve        pkg/flexgpu/flex_gpu.go:178-223; GPUAssumeFitIndexes / MemAssumeFitIndexes
+//                          pkg/flexgpu/gpu_node.go:122-177 (first fitting device in index order)
+//   per-(pod,node) math    the same as kernels.cu (flex_gpu.go:41-166, fit.go:256-329, least/most_allocated.go,
+//                          allocatable.go:146-171, normalize_score.go:26-54, generic_scheduler.go:146-167)
+//
+// Mapping: the grid is G <= #SM CTAs of 256 threads; every thread OWNS the same nodes for the whole kernel
+// (node = cta·256·K + j·256 + tid), so a node row is only ever read and rewritten by one thread: its derived
+// columns live in that CTA's shared memory (global memory when the cluster is too large for that) and no
+// cross-thread visibility of node state is needed. What the CTAs exchange per cycle is two small reductions:
+// (A) feasible count, the maxima NormalizeScore needs and the filter-panic flag, (B) the selectHost key and the
+// score-time error bits. Each CTA posts its partial result as self-tagged 64-bit words (payload 32 bits, cycle
+// tag 32 bits) into a global mailbox and one warp per CTA polls all mailboxes — no fences, no atomics, no grid
+// barrier: a word is valid exactly when its tag equals the current cycle. Pods stream through shared memory in
+// tiles of 64 by TMA bulk copy (cp.async.bulk + mbarrier), two stages.
+//
+// Latency-bound by design (one pod × N nodes per cycle is a few hundred KB of L2/shared-memory traffic); the
+// figure of merit is cycles per second, not HBM bandwidth.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "derive.cuh"
+#include "engine.h"
+#include "kernels.cuh"
+#include "pack.h"
+
+namespace fgs {
+
+typedef long long i64;
+typedef unsigned long long u64;
+
+#define FGS_CUDA(e, call)                                                    \
+    do {                                                                     \
+        cudaError_t _err = (call);                                           \
+        if (_err != cudaSuccess) {                                           \
+            (e)->err = std::string(#call) + ": " + cudaGetErrorString(_err); \
+            return FGS_E_CUDA;                                               \
+        }                                                                    \
+    } while (0)
+
+namespace {
+
+constexpr i64 kMin64 = (i64)0x8000000000000000ull;
+constexpr int kSeqThreads = 256;
+constexpr int kSeqWarps = kSeqThreads / 32;
+constexpr int kSeqTileP = 64;
+constexpr int kMaxK = 32;        // nodes per thread (bit mask of feasible nodes)
+constexpr int kWordsA = 8;       // mailbox words per CTA, phase A (7 used)
+constexpr int kWordsB = 4;       // phase B (3 used)
+
+enum SeqExtra : int { SX_ACCT_CPU = 0, SX_ACCT_MEM, SX_ANNOT, SX_COLS };
+enum SeqOut : int { SO_COUNT = 0, SO_NODE, SO_SCORE, SO_ERR, SO_DEVICE, SO_COMMITTED, SO_COLS };
+
+struct SeqParams {
+    DeriveParams dv;       // raw + derived node tables, plugin args of the derivation
+    const i64* pods;       // [pd_cols(S)][p_pad]
+    const i64* extra;      // [SX_COLS][p_pad]
+    i64* out;              // [SO_COLS][p_pad]
+    u64* mail_a;           // [2][G][kWordsA] self-tagged words
+    u64* mail_b;           // [2][G][kWordsB]
+    u64* prof;             // [G][8] clock sums per section (FGS_SEQ_PROFILE=1), else NULL
+    int* status;           // [0]: index of the first pod whose commit left the supported range, INT_MAX none
+    i64 n_pods, p_pad;
+    int K, state_smem;
+    uint32_t filter_mask, score_mask;
+    int flex_filter_first;
+    i64 w_flex, w_fit, w_alloc;
+    int fit_strategy, fit_n_res;
+    int fit_res[FGS_MAX_SCORE_RES];
+    i64 fit_w[FGS_MAX_SCORE_RES];
+    uint32_t fit_ignored;
+    u64 seed;
+    int key_shift, reserve_flex;
+};
+
+// ---- small PTX wrappers -------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(s_u32(bar)), "r"(parity)
+            : "memory");
+    }
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s_u32(dst)),
+                 "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(s_u32(bar))
+                 : "memory");
+}
+// mailbox words: relaxed, gpu scope, never cached in L1
+__device__ __forceinline__ void st_word(u64* p, uint32_t payload, uint32_t tag) {
+    const u64 w = ((u64)tag << 32) | payload;
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ u64 ld_word(const u64* p) {
+    u64 w;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    return w;
+}
+
+__device__ __forceinline__ i64 wmul(i64 a, i64 b) { return (i64)((u64)a * (u64)b); }
+__device__ __forceinline__ i64 wadd(i64 a, i64 b) { return (i64)((u64)a + (u64)b); }
+__device__ __forceinline__ i64 wsub(i64 a, i64 b) { return (i64)((u64)a - (u64)b); }
+
+__device__ __forceinline__ i64 warp_max_i64(i64 v) {
+    const int hi = (int)(v >> 32);
+    const uint32_t lo = (uint32_t)v;
+    const int mhi = __reduce_max_sync(0xffffffffu, hi);
+    const uint32_t mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
+    return (i64)(((u64)(uint32_t)mhi << 32) | mlo);
+}
+
+__device__ __forceinline__ float u64_to_float(u64 a) {
+    return fmaf(__uint2float_rn((uint32_t)(a >> 32)), 4294967296.0f, __uint2float_rn((uint32_t)a));
+}
+
+// Go's int64 x / d (truncation toward zero, wrapping), d != 0. The common case — both positive, quotient below
+// 2^18 — avoids the 64-bit division routine: a float estimate is within 1/8 of the true quotient there, so its
+// rounding k is the quotient or one above, and the sign of the exact remainder x − k·d decides.
+__device__ __forceinline__ i64 go_div(i64 x, i64 d) {
+    if (x >= 0 && d > 0 && x < ((i64)1 << 62) && d < ((i64)1 << 62)) {
+        const float est = __fdividef(u64_to_float((u64)x), u64_to_float((u64)d));
+        if (est < 262144.0f) {
+            const int k = __float2int_rn(est);
+            const i64 r = x - (i64)((u64)(uint32_t)k * (u64)d);
+            return (i64)k + (r >> 63);
+        }
+    }
+    if (d == -1) return (i64)(0ull - (u64)x);
+    return x / d;
+}
+
+} // namespace
+
+// =================================================================================================
+// seq_kernel
+// =================================================================================================
+namespace {
+
+struct SeqSmem {
+    int bars, ring, part_a, fin_a, part_b, fin_b, state, total;
+    int npc; // pod columns per tile
+};
+
+__host__ __device__ inline SeqSmem seq_smem(int S, int D, int K, int state_smem) {
+    SeqSmem L;
+    L.npc = pd_cols(S) + SX_COLS;
+    int off = 0;
+    L.bars = off;
+    off += 64;
+    L.ring = off;
+    off += 2 * L.npc * kSeqTileP * 8;
+    L.part_a = off;
+    off += kSeqWarps * 4 * 8;
+    L.fin_a = off;
+    off += 4 * 8;
+    L.part_b = off;
+    off += kSeqWarps * 2 * 8;
+    L.fin_b = off;
+    off += 2 * 8;
+    off = (off + 127) & ~127;
+    L.state = off;
+    if (state_smem) off += (nd_cols(S) + nr_cols(S, D)) * kSeqThreads * K * 8;
+    L.total = off;
+    return L;
+}
+
+// FlexGPU.Reserve on one raw node row (flex_gpu.go:178-223): the device index, or FGS_RESERVE_*
+__device__ __forceinline__ int reserve_on_row(const i64* raw, i64 rs, int S, int D, uint32_t kind, i64 mem_limit) {
+    if (kind == 0) return FGS_RESERVE_NONE;     // :187-189
+    if (kind == 3) return FGS_RESERVE_CONFLICT; // :191-193
+    auto R = [&](int c) { return raw[(i64)c * rs]; };
+    const u64 meta = (u64)R(NR_META);
+    const uint32_t flags = (uint32_t)meta, mono = (uint32_t)(meta >> 32);
+    if (flags & FGS_NF_REF_PANIC) return FGS_RESERVE_PANIC; // NewGPUNode, :195
+    const i64 gpuCnt = R(nr_alloc_scalar(FGS_SCALAR_FLEX_GPU));
+    const i64 memCnt = (flags & FGS_NF_HAS_MEM_RES) ? R(nr_alloc_scalar(FGS_SCALAR_FLEX_MEM)) : 0;
+    const i64 memEach = memCnt / gpuCnt; // gpu_node.go:55 (gpuCnt > 0: REF_PANIC covers the rest)
+    for (int d = 0; d < D; ++d) {
+        if ((i64)d >= gpuCnt) break;
+        const i64 used = R(nr_used(S, d));
+        const bool m = (mono >> d) & 1u;
+        if (kind == 1) {
+            if (!m && used == 0) return d; // GPUAssumeFitIndexes, gpu_node.go:163-177
+        } else {
+            if (!m && memEach >= used + mem_limit) return d; // MemAssumeFitIndexes, :122-161: indexes[0] is the first fit
+        }
+    }
+    return FGS_RESERVE_FAIL;
+}
+
+__global__ void __launch_bounds__(kSeqThreads, 1) seq_kernel(const __grid_constant__ SeqParams prm) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int S = prm.dv.S, D = prm.dv.D;
+    const int K = prm.K;
+    const SeqSmem L = seq_smem(S, D, K, prm.state_smem);
+    uint64_t* bars = (uint64_t*)(smem + L.bars);
+    i64* s_ring = (i64*)(smem + L.ring);
+    i64* s_part_a = (i64*)(smem + L.part_a);
+    i64* s_fin_a = (i64*)(smem + L.fin_a);
+    u64* s_part_b = (u64*)(smem + L.part_b);
+    u64* s_fin_b = (u64*)(smem + L.fin_b);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int G = (int)gridDim.x, cta = (int)blockIdx.x;
+    const i64 np = prm.dv.n_pad, n_nodes = prm.dv.n_nodes;
+    const i64 cta_nodes = (i64)kSeqThreads * K;
+    const i64 node0 = (i64)cta * cta_nodes;
+    const int ncols = nd_cols(S);
+    const int npc = L.npc;
+    const i64 n_tiles = (prm.n_pods + kSeqTileP - 1) / kSeqTileP;
+
+    auto issue_pod_tile = [&](i64 it) { // one elected thread
+        const int stage = (int)(it & 1);
+        const i64 p0 = it * kSeqTileP;
+        i64* dst = s_ring + (size_t)stage * npc * kSeqTileP;
+        mbar_expect_tx(&bars[stage], (uint32_t)(npc * kSeqTileP * 8));
+        for (int c = 0; c < pd_cols(S); ++c) bulk_g2s(dst + c * kSeqTileP, prm.pods + (i64)c * prm.p_pad + p0, kSeqTileP * 8, &bars[stage]);
+        for (int c = 0; c < SX_COLS; ++c)
+            bulk_g2s(dst + (pd_cols(S) + c) * kSeqTileP, prm.extra + (i64)c * prm.p_pad + p0, kSeqTileP * 8, &bars[stage]);
+    };
+
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0 && n_tiles > 0) issue_pod_tile(0);
+
+    // ---- node state: the derived columns of the nodes this CTA owns ------------------------------------------
+    // st: derived columns, rw: raw columns; element (c, i) at [c * stride + i], i = node − node0
+    const int nrc = nr_cols(S, D);
+    i64 *st, *rw;
+    i64 st_stride;
+    if (prm.state_smem) {
+        st = (i64*)(smem + L.state);
+        rw = st + (i64)ncols * cta_nodes;
+        st_stride = cta_nodes;
+        for (int c = 0; c < ncols + nrc; ++c)
+            for (i64 i = tid; i < cta_nodes; i += kSeqThreads) {
+                const i64 n = node0 + i;
+                const i64* src = c < ncols ? (const i64*)prm.dv.nd + (i64)c * np : (const i64*)prm.dv.raw + (i64)(c - ncols) * np;
+                st[(i64)c * st_stride + i] = n < n_nodes ? src[n] : 0;
+            }
+    } else {
+        st = (i64*)prm.dv.nd + node0;
+        rw = (i64*)prm.dv.raw + node0;
+        st_stride = np;
+    }
+    __syncthreads();
+
+    const bool use_flex_filter = prm.filter_mask & FGS_PL_FLEXGPU;
+    const bool use_fit_filter = prm.filter_mask & FGS_PL_FIT;
+    const bool sc_flex = prm.score_mask & FGS_PL_FLEXGPU;
+    const bool sc_fit = prm.score_mask & FGS_PL_FIT;
+    const bool sc_alloc = prm.score_mask & FGS_PL_ALLOCATABLE;
+
+    long long pc[6] = {0, 0, 0, 0, 0, 0}, pt = 0;
+    const bool prof = prm.prof != nullptr && tid == 0;
+    auto tick = [&](int k) {
+        if (prof) {
+            const long long now = clock64();
+            pc[k] += now - pt;
+            pt = now;
+        }
+    };
+    if (prof) pt = clock64();
+    for (i64 p = 0; p < prm.n_pods; ++p) {
+        const i64 it = p / kSeqTileP;
+        const int jp = (int)(p % kSeqTileP), stage = (int)(it & 1);
+        if (jp == 0) mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
+        const i64* praw = s_ring + (size_t)stage * npc * kSeqTileP;
+        auto PC = [&](int c) { return praw[c * kSeqTileP + jp]; };
+        const uint32_t tag = (uint32_t)(p + 1);
+        const int par = (int)(p & 1);
+
+        // ---- per-pod values (every thread; broadcast reads) ----------------------------------------------
+        const u64 pmeta = (u64)PC(PD_META);
+        const uint32_t pf = (uint32_t)pmeta;
+        const uint32_t kind = pf & 3u;
+        const bool req_none = pf & FGS_PF_REQ_NONE;
+        const uint32_t smask = (uint32_t)(pmeta >> 32) & ~prm.fit_ignored;
+        const i64 gpu_lim = PC(PD_GPU_LIM), mem_lim = PC(PD_MEM_LIM);
+        const i64 lim = kind == 1 ? gpu_lim : mem_lim;
+        const i64 rc = PC(PD_REQ_CPU), rm = PC(PD_REQ_MEM), re = PC(PD_REQ_EPH);
+        const i64 nzc = PC(PD_NZ_CPU), nzm = PC(PD_NZ_MEM);
+
+        // ---- phase A: Filter on my nodes ---------------------------------------------------------------------
+        uint32_t feas_mask = 0, cnt = 0, fl = 0;
+        i64 vflex = kMin64, vhi = kMin64, vnlo = kMin64;
+        for (int j = 0; j < K; ++j) {
+            const i64 i = (i64)j * kSeqThreads + tid;
+            if (node0 + i >= n_nodes) break;
+            auto C = [&](int c) { return st[(i64)c * st_stride + i]; };
+            const uint32_t nf = (uint32_t)C(ND_FLAGS);
+            bool flex_ok = true; // flex_gpu.go:41-119 folded into one threshold per pod kind (derive.cuh)
+            if (use_flex_filter) {
+                if (kind == 3) flex_ok = false;
+                else if (kind == 1) flex_ok = lim <= C(ND_THR_GPU);
+                else if (kind == 2) flex_ok = lim <= C(ND_THR_MEM);
+            }
+            bool fit_ok = true; // fit.go:256-329
+            if (use_fit_filter) {
+                fit_ok = nf & NDF_PODS_OK;
+                if (!req_none) {
+                    fit_ok = fit_ok && rc <= C(ND_FREE_CPU) && rm <= C(ND_FREE_MEM) && re <= C(ND_FREE_EPH);
+                    uint32_t m = smask;
+                    while (m) {
+                        const int s = __ffs(m) - 1;
+                        m &= m - 1;
+                        if (PC(PD_FIXED_COLS + s) > C(nd_free_scalar(s))) fit_ok = false;
+                    }
+                }
+            }
+            const bool valid = nf & FGS_NF_VALID;
+            // the reference panics inside NewGPUNode (flex_gpu.go:101) when FlexGPU.Filter gets that far
+            const bool reach = use_flex_filter && (kind == 1 || kind == 2) && flex_ok && (nf & FGS_NF_REF_PANIC) &&
+                               (prm.flex_filter_first || fit_ok) && valid;
+            if (reach) fl |= 1u;
+            if (flex_ok && fit_ok && valid && !reach) {
+                feas_mask |= 1u << j;
+                cnt++;
+                const i64 s = kind == 1 ? C(ND_GPU_SCORE) : (kind == 2 ? C(ND_MEM_SCORE) : 0);
+                vflex = s > vflex ? s : vflex;
+                const i64 ar = C(ND_ALLOC_RAW);
+                vhi = ar > vhi ? ar : vhi;
+                vnlo = -ar > vnlo ? -ar : vnlo;
+            }
+        }
+        tick(0); // pod fetch + Filter on my nodes
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        fl = __reduce_or_sync(0xffffffffu, fl);
+        if (sc_flex) vflex = warp_max_i64(vflex);
+        if (sc_alloc) {
+            vhi = warp_max_i64(vhi);
+            vnlo = warp_max_i64(vnlo);
+        }
+        if (lane == 0) {
+            s_part_a[warp * 4 + 0] = (i64)(cnt | (fl << 24));
+            s_part_a[warp * 4 + 1] = vflex;
+            s_part_a[warp * 4 + 2] = vhi;
+            s_part_a[warp * 4 + 3] = vnlo;
+        }
+        __syncthreads(); // (1) partials visible; every thread is past its last read of the previous tile
+        if (tid == 0 && jp == 0 && it + 1 < n_tiles) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            issue_pod_tile(it + 1);
+        }
+        if (warp == 0) {
+            const bool w = lane < kSeqWarps;
+            const i64 cf = w ? s_part_a[lane * 4 + 0] : 0;
+            uint32_t c2 = __reduce_add_sync(0xffffffffu, (uint32_t)cf & 0xffffffu);
+            uint32_t f2 = __reduce_or_sync(0xffffffffu, (uint32_t)(cf >> 24));
+            i64 a1 = warp_max_i64(w ? s_part_a[lane * 4 + 1] : kMin64);
+            i64 a2 = warp_max_i64(w ? s_part_a[lane * 4 + 2] : kMin64);
+            i64 a3 = warp_max_i64(w ? s_part_a[lane * 4 + 3] : kMin64);
+            if (G > 1) {
+                u64* mine = prm.mail_a + ((size_t)par * G + cta) * kWordsA;
+                if (lane < 7) {
+                    uint32_t pay;
+                    if (lane == 0) pay = c2 | (f2 << 24);
+                    else {
+                        const i64 v = lane <= 2 ? a1 : (lane <= 4 ? a2 : a3);
+                        pay = (lane & 1) ? (uint32_t)v : (uint32_t)((u64)v >> 32);
+                    }
+                    st_word(mine + lane, pay, tag);
+                }
+                uint32_t tc = 0, tf = 0;
+                i64 t1 = kMin64, t2 = kMin64, t3 = kMin64;
+                for (int c = lane; c < G; c += 32) {
+                    const u64* m = prm.mail_a + ((size_t)par * G + c) * kWordsA;
+                    u64 wv[7];
+                    bool ok;
+                    do {
+                        ok = true;
+#pragma unroll
+                        for (int k = 0; k < 7; ++k) {
+                            wv[k] = ld_word(m + k);
+                            ok = ok && (uint32_t)(wv[k] >> 32) == tag;
+                        }
+                    } while (!ok);
+                    tc += (uint32_t)wv[0] & 0xffffffu;
+                    tf |= ((uint32_t)wv[0] >> 24) & 0xffu;
+                    const i64 x1 = (i64)((wv[2] << 32) | (wv[1] & 0xffffffffull));
+                    const i64 x2 = (i64)((wv[4] << 32) | (wv[3] & 0xffffffffull));
+                    const i64 x3 = (i64)((wv[6] << 32) | (wv[5] & 0xffffffffull));
+                    t1 = x1 > t1 ? x1 : t1;
+                    t2 = x2 > t2 ? x2 : t2;
+                    t3 = x3 > t3 ? x3 : t3;
+                }
+                c2 = __reduce_add_sync(0xffffffffu, tc);
+                f2 = __reduce_or_sync(0xffffffffu, tf);
+                a1 = warp_max_i64(t1);
+                a2 = warp_max_i64(t2);
+                a3 = warp_max_i64(t3);
+            }
+            if (lane == 0) {
+                s_fin_a[0] = (i64)(((u64)f2 << 32) | c2);
+                s_fin_a[1] = a1;
+                s_fin_a[2] = a2;
+                s_fin_a[3] = a3;
+            }
+        }
+        __syncthreads(); // (2)
+        tick(1); // reduction + exchange A
+        const i64 count = (i64)(uint32_t)s_fin_a[0];
+        const bool fpanic = (s_fin_a[0] >> 32) & 1;
+        const i64 g_flex = s_fin_a[1], g_hi = s_fin_a[2], g_nlo = s_fin_a[3];
+
+        // ---- phase B: Score / NormalizeScore / weights / selectHost key on my feasible nodes -----------------
+        u64 key = 0;   // 0 = no candidate
+        uint32_t eb = 0; // FGS_PODERR_* raised while scoring
+        if (count > 0) { // uniform over the grid
+            const i64 fmax = g_flex > 0 ? g_flex : 0; // maxCount starts at 0 (normalize_score.go:27)
+            const i64 alo = -g_nlo;
+            const i64 arange = wsub(g_hi, alo);
+            uint32_t ph = (uint32_t)(prm.seed ^ (prm.seed >> 32)) ^ ((uint32_t)p * 0x9E3779B1u);
+            ph ^= ph >> 16;
+            ph *= 0x85EBCA6Bu;
+            ph ^= ph >> 13;
+            uint32_t fm = feas_mask;
+            while (fm) {
+                const int j = __ffs(fm) - 1;
+                fm &= fm - 1;
+                const i64 i = (i64)j * kSeqThreads + tid;
+                auto C = [&](int c) { return st[(i64)c * st_stride + i]; };
+                const uint32_t nf = (uint32_t)C(ND_FLAGS);
+                i64 t = 0;
+                if (sc_flex) {
+                    // FlexGPU.Score (flex_gpu.go:142-166) calls NewGPUNode first, for every pod kind (:148)
+                    if (nf & FGS_NF_REF_PANIC) eb |= FGS_PODERR_REF_PANIC;
+                    const i64 s = kind == 1 ? C(ND_GPU_SCORE) : (kind == 2 ? C(ND_MEM_SCORE) : 0);
+                    // DefaultNormalizeScore, reverse (normalize_score.go:26-54)
+                    const i64 v = fmax == 0 ? 100 : 100 - go_div(wmul(100, s), fmax);
+                    if (v > 100 || v < 0) eb |= FGS_PODERR_SCORE_RANGE; // runtime/framework.go:920-923
+                    t = wadd(t, wmul(v, prm.w_flex));
+                }
+                if (sc_fit) { // least_allocated.go:29-57, most_allocated.go:29-61, resource_allocation.go:45-117
+                    i64 node_score = 0, weight_sum = 0;
+                    for (int k = 0; k < prm.fit_n_res; ++k) {
+                        const int res = prm.fit_res[k];
+                        i64 alloc = 0, req = 0;
+                        if (res == FGS_RES_CPU) {
+                            alloc = C(ND_CAP_CPU);
+                            req = C(ND_NZR_CPU) + nzc;
+                        } else if (res == FGS_RES_MEM) {
+                            alloc = C(ND_CAP_MEM);
+                            req = C(ND_NZR_MEM) + nzm;
+                        } else if (res == FGS_RES_EPH) {
+                            alloc = C(ND_ALLOC_EPH);
+                            req = (alloc - C(ND_FREE_EPH)) + re;
+                        } else if (res >= FGS_RES_SCALAR0 && res < FGS_RES_SCALAR0 + S) {
+                            const int s = res - FGS_RES_SCALAR0;
+                            const i64 pr = PC(PD_FIXED_COLS + s);
+                            if (pr != 0) { // resource_allocation.go:93-97
+                                alloc = C(nd_alloc_scalar(S, s));
+                                req = (alloc - C(nd_free_scalar(s))) + pr;
+                            }
+                        }
+                        if (alloc == 0) continue; // resource_allocation.go:64-67
+                        i64 rs;
+                        if (prm.fit_strategy == 0) rs = req > alloc ? 0 : go_div(wmul(alloc - req, 100), alloc);
+                        else rs = go_div(wmul(req > alloc ? alloc : req, 100), alloc);
+                        node_score = wadd(node_score, wmul(rs, prm.fit_w[k]));
+                        weight_sum = wadd(weight_sum, prm.fit_w[k]);
+                    }
+                    const i64 v = weight_sum == 0 ? 0 : go_div(node_score, weight_sum);
+                    if (v > 100 || v < 0) eb |= FGS_PODERR_SCORE_RANGE;
+                    t = wadd(t, wmul(v, prm.w_fit));
+                }
+                if (sc_alloc) { // allocatable.go:61-72,146-171
+                    const i64 v = arange == 0 ? 0 : go_div(wmul(wsub(C(ND_ALLOC_RAW), alo), 100), arange);
+                    if (v > 100 || v < 0) eb |= FGS_PODERR_SCORE_RANGE;
+                    t = wadd(t, wmul(v, prm.w_alloc));
+                }
+                // selectHost candidate (generic_scheduler.go:146-167): same key as the batched kernels
+                const uint32_t ng = (uint32_t)(node0 + i);
+                u64 k;
+                if (prm.key_shift == 40) {
+                    uint32_t h = (ph ^ ng) * 0x9E3779B1u;
+                    h ^= h >> 15;
+                    k = ((u64)t << 40) | ((u64)(h & 0xffffu) << 24) | ng;
+                } else {
+                    k = ((u64)t << 24) | ng;
+                }
+                k += 1;
+                key = k > key ? k : key;
+            }
+            tick(2); // Score on my feasible nodes
+            key = (u64)warp_max_i64((i64)key);
+            eb = __reduce_or_sync(0xffffffffu, eb);
+            if (lane == 0) {
+                s_part_b[warp * 2 + 0] = key;
+                s_part_b[warp * 2 + 1] = eb;
+            }
+            __syncthreads(); // (3)
+            if (warp == 0) {
+                const bool w = lane < kSeqWarps;
+                u64 k2 = (u64)warp_max_i64(w ? (i64)s_part_b[lane * 2 + 0] : 0);
+                uint32_t e2 = __reduce_or_sync(0xffffffffu, w ? (uint32_t)s_part_b[lane * 2 + 1] : 0u);
+                if (G > 1) {
+                    u64* mine = prm.mail_b + ((size_t)par * G + cta) * kWordsB;
+                    if (lane < 3) st_word(mine + lane, lane == 0 ? (uint32_t)k2 : (lane == 1 ? (uint32_t)(k2 >> 32) : e2), tag);
+                    u64 tk = 0;
+                    uint32_t te = 0;
+                    for (int c = lane; c < G; c += 32) {
+                        const u64* m = prm.mail_b + ((size_t)par * G + c) * kWordsB;
+                        u64 w0, w1, w2;
+                        do {
+                            w0 = ld_word(m + 0);
+                            w1 = ld_word(m + 1);
+                            w2 = ld_word(m + 2);
+                        } while ((uint32_t)(w0 >> 32) != tag || (uint32_t)(w1 >> 32) != tag || (uint32_t)(w2 >> 32) != tag);
+                        const u64 x = (w1 << 32) | (w0 & 0xffffffffull);
+                        tk = x > tk ? x : tk;
+                        te |= (uint32_t)w2;
+                    }
+                    k2 = (u64)warp_max_i64((i64)tk);
+                    e2 = __reduce_or_sync(0xffffffffu, te);
+                }
+                if (lane == 0) {
+                    s_fin_b[0] = k2;
+                    s_fin_b[1] = e2;
+                }
+            }
+            __syncthreads(); // (4)
+            tick(3); // reduction + exchange B
+            key = s_fin_b[0];
+            eb = (uint32_t)s_fin_b[1];
+        }
+
+        // ---- verdict of the cycle (every thread computes the same) -----------------------------------------
+        uint32_t err = fpanic ? FGS_PODERR_REF_PANIC : 0u;
+        if (count >= 2) err |= eb; // scoring only runs with >= 2 feasible nodes (generic_scheduler.go:112-127)
+        i64 sel = -1, score = 0;
+        if (key > 0) {
+            const u64 k = key - 1;
+            sel = (i64)(k & 0xffffffu);
+            score = (i64)(k >> prm.key_shift);
+        }
+        const bool mine = sel >= node0 && sel < node0 + cta_nodes && (int)((sel - node0) % kSeqThreads) == tid;
+        if (sel < 0 ? (cta == 0 && tid == 0) : mine) {
+            int dev = FGS_RESERVE_SKIPPED;
+            bool commit = sel >= 0 && err == 0;
+            if (commit && prm.reserve_flex) {
+                dev = reserve_on_row(rw + (sel - node0), st_stride, S, D, kind, mem_lim);
+                if (dev == FGS_RESERVE_PANIC) err |= FGS_PODERR_REF_PANIC;
+                commit = dev >= 0 || dev == FGS_RESERVE_NONE;
+            }
+            if (commit) {
+                // assume: NodeInfo.AddPod (framework/types.go:583-609) on the raw row, then re-derive it
+                const i64 i = sel - node0;
+                auto RW = [&](int c) -> i64& { return rw[(i64)c * st_stride + i]; };
+                bool in_range = true;
+                auto bump = [&](int c, i64 d) {
+                    const i64 v = RW(c) + d;
+                    RW(c) = v;
+                    in_range = in_range && v > -kMaxQuantity && v < kMaxQuantity;
+                };
+                bump(NR_REQ_MCPU, rc);
+                bump(NR_REQ_MEM, rm);
+                bump(NR_REQ_EPH, re);
+                for (int s = 0; s < S; ++s) bump(nr_req_scalar(S, s), PC(PD_FIXED_COLS + s));
+                bump(NR_NZ_MCPU, PC(pd_cols(S) + SX_ACCT_CPU));
+                bump(NR_NZ_MEM, PC(pd_cols(S) + SX_ACCT_MEM));
+                bump(NR_NUM_PODS, 1);
+                // what nodeResourceLimitSum (flex_gpu.go:133-140) and constructGPUs (gpu_node.go:66-120) will see
+                if (kind & 1u) bump(NR_FLEX_GPU_SUM, gpu_lim);
+                if (kind & 2u) bump(NR_FLEX_MEM_SUM, mem_lim);
+                if (kind != 0) {
+                    const i64 annot = dev >= 0 ? (i64)dev : PC(pd_cols(S) + SX_ANNOT);
+                    if (annot != (i64)FGS_ANNOT_NONE) {
+                        u64 meta = (u64)RW(NR_META);
+                        const i64 gpuCnt = ((uint32_t)meta & FGS_NF_HAS_GPU_RES) ? RW(nr_alloc_scalar(FGS_SCALAR_FLEX_GPU)) : 0;
+                        if (annot < 0 || annot >= gpuCnt) {
+                            meta |= FGS_NF_REF_PANIC; // gpus[index] out of range (gpu_node.go:110,115)
+                        } else {
+                            if (kind & 1u) meta |= 1ull << (32 + (int)annot);
+                            if (kind & 2u) bump(nr_used(S, (int)annot), mem_lim);
+                        }
+                        RW(NR_META) = (i64)meta;
+                    }
+                }
+                if (!in_range) atomicMin(prm.status, (int)(p < 0x7fffffff ? p : 0x7ffffffe));
+                derive_row(prm.dv, rw + i, st_stride, st + i, st_stride);
+                if (prm.state_smem) { // write the row through to the global tables (stores only: nothing waits on them)
+                    i64* g_nd = (i64*)prm.dv.nd + sel;
+                    i64* g_raw = (i64*)prm.dv.raw + sel;
+                    for (int c = 0; c < ncols; ++c) g_nd[(i64)c * np] = st[(i64)c * st_stride + i];
+                    for (int c = NR_REQ_MCPU; c < nrc; ++c) g_raw[(i64)c * np] = rw[(i64)c * st_stride + i];
+                }
+            }
+            prm.out[(i64)SO_COUNT * prm.p_pad + p] = count;
+            prm.out[(i64)SO_NODE * prm.p_pad + p] = sel;
+            prm.out[(i64)SO_SCORE * prm.p_pad + p] = score;
+            prm.out[(i64)SO_ERR * prm.p_pad + p] = (i64)err;
+            prm.out[(i64)SO_DEVICE * prm.p_pad + p] = (i64)dev;
+            prm.out[(i64)SO_COMMITTED * prm.p_pad + p] = commit ? 1 : 0;
+        }
+        tick(4); // verdict + commit (thread 0's own share)
+    }
+    if (prof)
+        for (int k = 0; k < 6; ++k) prm.prof[(size_t)cta * 8 + k] = (u64)pc[k];
+}
+
+// FlexGPU.Reserve for a batch of (pod, node) pairs, no commit
+__global__ void reserve_kernel(const i64* __restrict__ raw, i64 np, i64 n_nodes, int S, int D, const i64* __restrict__ pods, i64 p_pad,
+                               i64 n_pods, const int* __restrict__ node, int* __restrict__ dev) {
+    const i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    const int n = node[p];
+    if (n < 0 || n >= n_nodes) {
+        dev[p] = FGS_RESERVE_SKIPPED;
+        return;
+    }
+    const uint32_t kind = (uint32_t)pods[(i64)PD_META * p_pad + p] & 3u;
+    dev[p] = reserve_on_row(raw + n, np, S, D, kind, pods[(i64)PD_MEM_LIM * p_pad + p]);
+}
+
+} // namespace
+
+// =================================================================================================
+// host side
+// =================================================================================================
+
+struct SeqState {
+    void* d_pods = nullptr; // [(pd_cols(S) + SX_COLS)][cap]
+    void* h_pods = nullptr;
+    void* d_out = nullptr;  // [SO_COLS][cap]
+    void* h_out = nullptr;
+    int64_t cap = 0;
+    void* d_mail = nullptr; // mail_a | mail_b | status
+    size_t mail_bytes = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 0, smem_optin = 0;
+};
+
+void Engine::seq_free() {
+    if (!seq) return;
+    if (seq->d_pods) cudaFree(seq->d_pods);
+    if (seq->h_pods) cudaFreeHost(seq->h_pods);
+    if (seq->d_out) cudaFree(seq->d_out);
+    if (seq->h_out) cudaFreeHost(seq->h_out);
+    if (seq->d_mail) cudaFree(seq->d_mail);
+    if (seq->ev0) cudaEventDestroy(seq->ev0);
+    if (seq->ev1) cudaEventDestroy(seq->ev1);
+    delete seq;
+    seq = nullptr;
+}
+
+static int64_t round_up64(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+static int seq_reserve_buffers(Engine* e, int64_t pp) {
+    if (!e->seq) {
+        e->seq = new SeqState();
+        FGS_CUDA(e, cudaDeviceGetAttribute(&e->seq->sm_count, cudaDevAttrMultiProcessorCount, e->device));
+        FGS_CUDA(e, cudaDeviceGetAttribute(&e->seq->smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
+        FGS_CUDA(e, cudaEventCreate(&e->seq->ev0));
+        FGS_CUDA(e, cudaEventCreate(&e->seq->ev1));
+    }
+    SeqState* q = e->seq;
+    if (pp > q->cap) {
+        if (q->d_pods) cudaFree(q->d_pods);
+        if (q->h_pods) cudaFreeHost(q->h_pods);
+        if (q->d_out) cudaFree(q->d_out);
+        if (q->h_out) cudaFreeHost(q->h_out);
+        q->d_pods = q->h_pods = q->d_out = q->h_out = nullptr;
+        q->cap = 0;
+        const size_t in_bytes = sizeof(int64_t) * (size_t)(pd_cols(e->S) + SX_COLS) * (size_t)pp;
+        const size_t out_bytes = sizeof(int64_t) * (size_t)SO_COLS * (size_t)pp;
+        FGS_CUDA(e, cudaMalloc(&q->d_pods, in_bytes));
+        FGS_CUDA(e, cudaMallocHost(&q->h_pods, in_bytes));
+        FGS_CUDA(e, cudaMalloc(&q->d_out, out_bytes));
+        FGS_CUDA(e, cudaMallocHost(&q->h_out, out_bytes));
+        q->cap = pp;
+    }
+    return FGS_OK;
+}
+
+// pod columns → pinned staging → device, in the layout the kernels read ([column][pp])
+static int seq_stage_pods(Engine* e, const fgs_pod_table* t, int64_t pp) {
+    SeqState* q = e->seq;
+    const int64_t P = t->n_pods;
+    const int S = e->S;
+    int64_t* h = (int64_t*)q->h_pods;
+    auto col = [&](int c, const int64_t* src) {
+        std::memcpy(h + (int64_t)c * pp, src, sizeof(int64_t) * (size_t)P);
+        std::memset(h + (int64_t)c * pp + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+    };
+    col(PD_GPU_LIM, t->flex_gpu_limit);
+    col(PD_MEM_LIM, t->flex_mem_limit);
+    col(PD_REQ_CPU, t->req_mcpu);
+    col(PD_REQ_MEM, t->req_mem);
+    col(PD_REQ_EPH, t->req_eph);
+    col(PD_NZ_CPU, t->nz_mcpu);
+    col(PD_NZ_MEM, t->nz_mem);
+    for (int s = 0; s < S; ++s) col(PD_FIXED_COLS + s, t->req_scalar + (int64_t)s * P);
+    const int x0 = pd_cols(S);
+    col(x0 + SX_ACCT_CPU, t->acct_nz_mcpu);
+    col(x0 + SX_ACCT_MEM, t->acct_nz_mem);
+    int64_t* meta = h + (int64_t)PD_META * pp;
+    int64_t* ann = h + (int64_t)(x0 + SX_ANNOT) * pp;
+    for (int64_t i = 0; i < P; ++i) {
+        meta[i] = (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]);
+        ann[i] = (int64_t)t->index_annot[i];
+    }
+    std::memset(meta + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+    std::memset(ann + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+    FGS_CUDA(e, cudaMemcpyAsync(q->d_pods, q->h_pods, sizeof(int64_t) * (size_t)(x0 + SX_COLS) * (size_t)pp, cudaMemcpyHostToDevice, e->stream));
+    return FGS_OK;
+}
+
+static int seq_check_inputs(Engine* e, const fgs_pod_table* t, const char* who) {
+    if (!e->have_nodes) return e->fail(FGS_E_STATE, std::string(who) + " before fgs_upload_nodes");
+    if (!t || t->n_pods < 0) return e->fail(FGS_E_INVALID, std::string(who) + ": null pod table or negative size");
+    if (t->n_scalars != e->S) return e->fail(FGS_E_INVALID, std::string(who) + ": pod table n_scalars differs from the engine's");
+    if (t->n_pods >= ((int64_t)1 << 31) - 64) return e->fail(FGS_E_TOO_LARGE, std::string(who) + ": at most 2^31 pods per call");
+    return FGS_OK;
+}
+
+} // namespace fgs
+
+using namespace fgs;
+
+extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, const fgs_seq_opts* opts, fgs_seq_results* out) {
+    if (!eh || !out) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    int rc = seq_check_inputs(e, t, "fgs_schedule_sequential");
+    if (rc) return rc;
+    if (!t->acct_nz_mcpu || !t->acct_nz_mem || !t->index_annot)
+        return e->fail(FGS_E_INVALID, "fgs_schedule_sequential: the pod table lacks acct_nz_mcpu / acct_nz_mem / index_annot");
+    if (e->node_base != 0 || (e->total_nodes != 0 && e->total_nodes != e->n_nodes))
+        return e->fail(FGS_E_STATE, "fgs_schedule_sequential: the engine must hold the whole cluster (node_index_base 0)");
+    cudaSetDevice(e->device);
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (!e->nodes_derived) {
+        rc = e->derive_now();
+        if (rc) return rc;
+    }
+    const int64_t P = t->n_pods;
+    if (P == 0) return FGS_OK;
+    const int64_t pp = round_up64(P, kSeqTileP);
+    rc = seq_reserve_buffers(e, pp);
+    if (rc) return rc;
+    SeqState* q = e->seq;
+    rc = seq_stage_pods(e, t, pp);
+    if (rc) return rc;
+
+    // geometry: as few nodes per thread as the SM count allows; node state in shared memory when it fits
+    const int64_t N = std::max<int64_t>(e->n_nodes, 1);
+    int G = (int)std::min<int64_t>(q->sm_count, (N + kSeqThreads - 1) / kSeqThreads);
+    if (const char* s = getenv("FGS_SEQ_CTAS")) {
+        const int v = atoi(s);
+        if (v >= 1) G = std::min(v, q->sm_count);
+    }
+    const int64_t K64 = (N + (int64_t)G * kSeqThreads - 1) / ((int64_t)G * kSeqThreads);
+    if (K64 > kMaxK) return e->fail(FGS_E_TOO_LARGE, "fgs_schedule_sequential: more than 32 nodes per thread (" + std::to_string(N) + " nodes)");
+    const int K = (int)K64;
+    int state_smem = 1;
+    if (const char* s = getenv("FGS_SEQ_STATE_GLOBAL"))
+        if (s[0] == '1') state_smem = 0;
+    if (seq_smem(e->S, e->D, K, 1).total > q->smem_optin) state_smem = 0;
+    const SeqSmem L = seq_smem(e->S, e->D, K, state_smem);
+    FGS_CUDA(e, cudaFuncSetAttribute(seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+
+    const size_t a_bytes = sizeof(u64) * 2 * (size_t)G * kWordsA, b_bytes = sizeof(u64) * 2 * (size_t)G * kWordsB;
+    const bool want_prof = getenv("FGS_SEQ_PROFILE") && getenv("FGS_SEQ_PROFILE")[0] == '1';
+    const size_t prof_bytes = sizeof(u64) * 8 * (size_t)G;
+    const size_t need = a_bytes + b_bytes + 64 + prof_bytes;
+    if (need > q->mail_bytes) {
+        if (q->d_mail) cudaFree(q->d_mail);
+        q->d_mail = nullptr;
+        q->mail_bytes = 0;
+        FGS_CUDA(e, cudaMalloc(&q->d_mail, need));
+        q->mail_bytes = need;
+    }
+    FGS_CUDA(e, cudaMemsetAsync(q->d_mail, 0, need, e->stream));
+    int* d_status = (int*)((char*)q->d_mail + a_bytes + b_bytes);
+    const int none = 0x7fffffff;
+    FGS_CUDA(e, cudaMemcpyAsync(d_status, &none, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+
+    EvalParams ep;
+    e->fill_eval_params(&ep, nullptr);
+    SeqParams sp;
+    std::memset(&sp, 0, sizeof(sp));
+    e->fill_derive_params(&sp.dv);
+    sp.pods = (const i64*)q->d_pods;
+    sp.extra = (const i64*)q->d_pods + (int64_t)pd_cols(e->S) * pp;
+    sp.out = (i64*)q->d_out;
+    sp.mail_a = (u64*)q->d_mail;
+    sp.mail_b = (u64*)((char*)q->d_mail + a_bytes);
+    sp.status = d_status;
+    sp.prof = want_prof ? (u64*)((char*)q->d_mail + a_bytes + b_bytes + 64) : nullptr;
+    sp.n_pods = P;
+    sp.p_pad = pp;
+    sp.K = K;
+    sp.state_smem = state_smem;
+    sp.filter_mask = ep.filter_mask;
+    sp.score_mask = ep.score_mask;
+    sp.flex_filter_first = ep.flex_filter_first;
+    sp.w_flex = ep.w_flex;
+    sp.w_fit = ep.w_fit;
+    sp.w_alloc = ep.w_alloc;
+    sp.fit_strategy = ep.fit_strategy;
+    sp.fit_n_res = ep.fit_n_res;
+    for (int k = 0; k < FGS_MAX_SCORE_RES; ++k) {
+        sp.fit_res[k] = ep.fit_res[k];
+        sp.fit_w[k] = ep.fit_w[k];
+    }
+    sp.fit_ignored = ep.fit_ignored;
+    sp.seed = e->seed;
+    sp.key_shift = ep.key_shift;
+    sp.reserve_flex = (opts && opts->reserve_flex) ? 1 : 0;
+
+    FGS_CUDA(e, cudaEventRecord(q->ev0, e->stream));
+    void* args[] = {(void*)&sp};
+    // cooperative launch: all G CTAs must be resident at once (they wait on each other's mailbox words)
+    FGS_CUDA(e, cudaLaunchCooperativeKernel((const void*)seq_kernel, dim3((unsigned)G), dim3(kSeqThreads), args, (size_t)L.total, e->stream));
+    e->launches++;
+    FGS_CUDA(e, cudaEventRecord(q->ev1, e->stream));
+    FGS_CUDA(e, cudaMemcpyAsync(q->h_out, q->d_out, sizeof(int64_t) * SO_COLS * (size_t)pp, cudaMemcpyDeviceToHost, e->stream));
+    int status = none;
+    FGS_CUDA(e, cudaMemcpyAsync(&status, d_status, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    cudaEventElapsedTime(&e->tm.seq_ms, q->ev0, q->ev1);
+    if (want_prof) { // clock cycles per scheduling cycle and section, CTA 0 and the mean over CTAs
+        std::vector<u64> hp((size_t)G * 8);
+        FGS_CUDA(e, cudaMemcpy(hp.data(), sp.prof, prof_bytes, cudaMemcpyDeviceToHost));
+        static const char* names[5] = {"filter", "exchangeA", "score", "exchangeB", "commit"};
+        for (int k = 0; k < 5; ++k) {
+            double sum = 0;
+            for (int c = 0; c < G; ++c) sum += (double)hp[(size_t)c * 8 + k];
+            fprintf(stderr, "[fgs seq profile] %-9s cta0 %8.1f  mean %8.1f clocks/cycle\n", names[k], (double)hp[k] / (double)P, sum / G / (double)P);
+        }
+    }
+    e->tm.seq_ctas = G;
+    const int64_t* h = (const int64_t*)q->h_out;
+    for (int64_t p = 0; p < P; ++p) {
+        if (out->feasible_count) out->feasible_count[p] = (int32_t)h[(int64_t)SO_COUNT * pp + p];
+        if (out->selected_node) out->selected_node[p] = (int32_t)h[(int64_t)SO_NODE * pp + p];
+        if (out->selected_score) out->selected_score[p] = h[(int64_t)SO_SCORE * pp + p];
+        if (out->pod_err) out->pod_err[p] = (uint32_t)h[(int64_t)SO_ERR * pp + p];
+        if (out->device_index) out->device_index[p] = (int32_t)h[(int64_t)SO_DEVICE * pp + p];
+        if (out->committed) out->committed[p] = (uint8_t)h[(int64_t)SO_COMMITTED * pp + p];
+    }
+    // the derived table changed under the batched path's feet: redo its node-side analysis
+    rc = e->analyze_nodes_now();
+    if (rc) return rc;
+    if (status != none)
+        return e->fail(FGS_E_RANGE, "fgs_schedule_sequential: committing pod " + std::to_string(status) +
+                                        " took a node aggregate outside |v| < 2^53; results from that pod on are not the reference's");
+    return FGS_OK;
+}
+
+extern "C" int fgs_reserve(fgs_engine* eh, const fgs_pod_table* t, const int32_t* node, int32_t* device_index) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    int rc = seq_check_inputs(e, t, "fgs_reserve");
+    if (rc) return rc;
+    if (!node || !device_index) return e->fail(FGS_E_INVALID, "fgs_reserve: null node / device_index array");
+    cudaSetDevice(e->device);
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    const int64_t P = t->n_pods;
+    if (P == 0) return FGS_OK;
+    const int64_t pp = round_up64(P, kSeqTileP);
+    rc = seq_reserve_buffers(e, pp);
+    if (rc) return rc;
+    SeqState* q = e->seq;
+    // only the flags and the fractional limit are read
+    int64_t* h = (int64_t*)q->h_pods;
+    for (int64_t i = 0; i < P; ++i) {
+        h[(int64_t)PD_META * pp + i] = (int64_t)(uint64_t)t->flags[i];
+        h[(int64_t)PD_MEM_LIM * pp + i] = t->flex_mem_limit[i];
+    }
+    int32_t* hn = (int32_t*)q->h_out;
+    std::memcpy(hn, node, sizeof(int32_t) * (size_t)P);
+    FGS_CUDA(e, cudaMemcpyAsync((int64_t*)q->d_pods + (int64_t)PD_META * pp, h + (int64_t)PD_META * pp, sizeof(int64_t) * (size_t)P,
+                                cudaMemcpyHostToDevice, e->stream));
+    FGS_CUDA(e, cudaMemcpyAsync((int64_t*)q->d_pods + (int64_t)PD_MEM_LIM * pp, h + (int64_t)PD_MEM_LIM * pp, sizeof(int64_t) * (size_t)P,
+                                cudaMemcpyHostToDevice, e->stream));
+    int* d_node = (int*)q->d_out;
+    int* d_dev = d_node + pp;
+    FGS_CUDA(e, cudaMemcpyAsync(d_node, hn, sizeof(int32_t) * (size_t)P, cudaMemcpyHostToDevice, e->stream));
+    reserve_kernel<<<(unsigned)((P + 255) / 256), 256, 0, e->stream>>>((const i64*)e->d_raw, e->n_pad, e->n_nodes, e->S, e->D, (const i64*)q->d_pods, pp, P,
+                                                                      d_node, d_dev);
+    e->launches++;
+    FGS_CUDA(e, cudaGetLastError());
+    FGS_CUDA(e, cudaMemcpyAsync(hn + pp, d_dev, sizeof(int32_t) * (size_t)P, cudaMemcpyDeviceToHost, e->stream));
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    std::memcpy(device_index, hn + pp, sizeof(int32_t) * (size_t)P);
+    return FGS_OK;
+}

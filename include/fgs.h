@@ -167,6 +167,47 @@ int fgs_synchronize(fgs_engine* e);
  * diagnosis plane the Go Filter methods answer from (NodeToStatusMap, generic_scheduler.go:309-313). */
 int fgs_status_plane(fgs_engine* e, uint32_t plugin, uint8_t* out);
 
+/* ---- sequential scheduling cycles: assume + Reserve between pods ---------------------------- */
+
+/* device_index values that are not an index (FlexGPU.Reserve, pkg/flexgpu/flex_gpu.go:178-223) */
+#define FGS_RESERVE_FAIL (-1)     /* "allocate index fail" (:198-200,208-210): the cycle fails, the pod is forgotten */
+#define FGS_RESERVE_NONE (-2)     /* the pod has neither flex limit: nothing to reserve (:187-189) */
+#define FGS_RESERVE_CONFLICT (-3) /* both limits: UnschedulableAndUnresolvable (:191-193) */
+#define FGS_RESERVE_PANIC (-4)    /* NewGPUNode panics on the chosen node (gpu_node.go:40-58,109,115) */
+#define FGS_RESERVE_SKIPPED (-5)  /* Reserve did not run: no node chosen, cycle error, or reserve_flex == 0 */
+
+typedef struct fgs_seq_opts {
+    int32_t reserve_flex; /* 1: FlexGPU is a Reserve plugin of the profile (it is in the reference's chart) */
+    int32_t _pad;
+} fgs_seq_opts;
+
+/* Per-pod outputs of fgs_schedule_sequential (host buffers owned by the caller, each [P]; any may be NULL). */
+typedef struct fgs_seq_results {
+    int32_t* feasible_count;
+    int32_t* selected_node;  /* -1 when no node is feasible */
+    int64_t* selected_score;
+    uint32_t* pod_err;       /* FGS_PODERR_* */
+    int32_t* device_index;   /* the nvidia.flex.com/index annotation Reserve sets, or FGS_RESERVE_* */
+    uint8_t* committed;      /* 1: the pod was assumed on selected_node and the node row was updated */
+} fgs_seq_results;
+
+/* What the reference does with a queue of pods, one scheduling cycle each, in `pods` order
+ * (vendor/k8s.io/kubernetes/pkg/scheduler/scheduler.go:441-540): Filter + Score + selectHost against the
+ * CURRENT node table, then `assume` — NodeInfo.AddPod on the chosen node (scheduler.go:353-370,
+ * framework/types.go:583-609: Requested, NonZeroRequested, len(Pods)) — and FlexGPU.Reserve, which picks the
+ * device index (whole GPU: first idle non-monopoly device, gpu_node.go:163-177; fractional: first device that
+ * still fits, :122-161) that the next cycle's NewGPUNode sees as used. A pod without a feasible node, with a
+ * cycle error, or whose Reserve fails leaves the table unchanged (ForgetPod, scheduler.go:512-521).
+ * One persistent kernel runs all cycles; the node rows stay on the GPU and only the chosen row is re-derived
+ * between cycles. Afterwards the engine's node table reflects every commit (fgs_evaluate sees it).
+ * Single GPU: the engine must hold the whole cluster (node_index_base 0). */
+int fgs_schedule_sequential(fgs_engine* e, const fgs_pod_table* pods, const fgs_seq_opts* opts,
+                            fgs_seq_results* out);
+
+/* FlexGPU.Reserve alone, for callers that keep `assume` on the Go side: the device index each pod would get on
+ * node[p] of the current table (no commit). device_index[p] as above; node[p] < 0 gives FGS_RESERVE_SKIPPED. */
+int fgs_reserve(fgs_engine* e, const fgs_pod_table* pods, const int32_t* node, int32_t* device_index);
+
 /* ---- coscheduling / capacity scheduling --------------------------------------------------- */
 
 /* PodGroupManager.PreFilter for every pending pod (pkg/coscheduling/core/core.go:149-196 incl.
@@ -212,6 +253,8 @@ typedef struct fgs_timings {
     float h2d_ms, reduce_ms, emit_ms, d2h_ms; /* last fgs_evaluate, CUDA events on the stream */
     int64_t kernel_launches;                  /* kernels launched by this engine so far */
     int32_t reduce_int32, emit_int32;         /* 1: the last pass ran the int32 specialisation */
+    float seq_ms;                             /* last fgs_schedule_sequential: the persistent kernel alone */
+    int32_t seq_ctas;                         /* CTAs it ran on */
 } fgs_timings;
 int fgs_get_timings(fgs_engine* e, fgs_timings* t);
 

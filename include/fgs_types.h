@@ -207,6 +207,12 @@ typedef struct fgs_pod_table {
     const int32_t* ns;               /* namespace id */
     const int32_t* pg;               /* PodGroup id or -1 */
     const int32_t* priority;
+    /* read only by the sequential-commit path (fgs_schedule_sequential): what NodeInfo.AddPod adds to
+     * NonZeroRequested (calculateResource's non0CPU / non0Mem, framework/types.go:715-745 — unlike the
+     * scorer's figure above, the overhead is added in milli-cores) and the pod's own index annotation */
+    const int64_t* acct_nz_mcpu;
+    const int64_t* acct_nz_mem;
+    const int32_t* index_annot;      /* Atoi(nvidia.flex.com/index) or FGS_ANNOT_NONE */
 } fgs_pod_table;
 
 #ifdef __cplusplus

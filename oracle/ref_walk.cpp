@@ -550,6 +550,14 @@ extern "C" int fgs_oracle_evaluate(const fgs_snapshot* snap, const fgs_podset* p
         std::function<void(int)> checkNode = [&](int n) {
             uint8_t st = FGS_CODE_SUCCESS;
             panicked[(size_t)n] = 0;
+            // A NodeInfo whose Node() is nil is not an element of the list this loop walks: UpdateSnapshot builds
+            // nodeInfoList from the node tree and drops entries without a Node
+            // (vendor/…/scheduler/internal/cache/cache.go:254,290,314-325). The flat snapshot can still carry
+            // such rows (the gang path skips them explicitly, core.go:324-326): report Error with no plugin.
+            if (!sn.s->node_valid[n]) {
+                status[(size_t)n] = FGS_CODE_ERROR;
+                return;
+            }
             for (int k = 0; k < 2 && cfg->filter_order[k]; ++k) {
                 int pl = cfg->filter_order[k];
                 if (!(cfg->filter_mask & (uint32_t)pl)) continue;

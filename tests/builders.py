@@ -160,6 +160,9 @@ def build_snapshot(nodes, S=2):
                 present[i] |= 1 << k[1]
             else:
                 alloc[i, _slot(k)] = v
+        # aggregates that are not the sum of the listed pods (a cache that is ahead of / behind the pod list)
+        req[i] += np.array(nd.get("req_bias", [0] * RW), np.int64)
+        nz[i] += np.array(nd.get("nz_bias", [0, 0]), np.int64)
         for p in nd["pods"]:
             res, c, m = _calc_resource(p, S)
             req[i] += np.array(res, np.int64)
