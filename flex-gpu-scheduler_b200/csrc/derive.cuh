@@ -11,6 +11,9 @@ namespace fgs {
 
 // raw row: raw[c * rs], derived row written to nd[c * ns] (global tables: pointer to the node's element, stride
 // n_pad; the sequential kernel's shared-memory copy: stride = nodes per CTA)
+// DYNAMIC_ONLY: the row was derived before and only what a placement can change is redone — Allocatable and with
+// it memEach (read back from ND_MEM_EACH, saving the 64-bit division) and the Allocatable raw score stay.
+template <bool DYNAMIC_ONLY = false>
 __device__ __forceinline__ void derive_row(const DeriveParams& prm, const long long* __restrict__ raw, long long rs, long long* __restrict__ nd, long long ns) {
     typedef long long i64;
     typedef unsigned long long u64;
@@ -31,11 +34,12 @@ __device__ __forceinline__ void derive_row(const DeriveParams& prm, const long l
     const bool has_flex = flags & FGS_NF_HAS_FLEX;
     const bool panic = flags & FGS_NF_REF_PANIC;
 
-    i64 max_free = kI64Max, gpu_score = 0, mem_score = 0;
+    i64 max_free = kI64Max, gpu_score = 0, mem_score = 0, mem_each = 0;
     if (!panic) {
         const i64 gpuCnt = gpuAlloc; // > 0 here (REF_PANIC covers <= 0 and a missing key)
         const i64 memCnt = (flags & FGS_NF_HAS_MEM_RES) ? memAlloc : 0;
-        const i64 memEach = memCnt / gpuCnt; // gpu_node.go:55
+        const i64 memEach = DYNAMIC_ONLY ? nd[(i64)ND_MEM_EACH * ns] : memCnt / gpuCnt; // gpu_node.go:55
+        mem_each = memEach;
         max_free = kI64Min;
         i64 used_sum = 0;
         for (int d = 0; d < D; ++d) {
@@ -60,19 +64,22 @@ __device__ __forceinline__ void derive_row(const DeriveParams& prm, const long l
     if (R(NR_NUM_PODS) + 1 <= R(NR_ALLOC_PODS)) flags |= NDF_PODS_OK; // fit.go:259
 
     // Allocatable raw score: Σ mode(alloc_r)·w_r / Σ w_r with Go's wrapping int64 (allocatable.go:120-143)
-    i64 node_score = 0, weight_sum = 0;
-    for (int k = 0; k < prm.alloc_n_res; ++k) {
-        const int res = prm.alloc_res[k];
-        i64 a = 0;
-        if (res == FGS_RES_CPU) a = R(NR_ALLOC_MCPU);
-        else if (res == FGS_RES_MEM) a = R(NR_ALLOC_MEM);
-        else if (res == FGS_RES_EPH) a = R(NR_ALLOC_EPH);
-        else if (res >= FGS_RES_SCALAR0 && res < FGS_RES_SCALAR0 + S) a = R(nr_alloc_scalar(res - FGS_RES_SCALAR0));
-        const i64 rs = prm.alloc_mode == 0 ? wmul(-1, a) : a;
-        node_score = wadd(node_score, wmul(rs, prm.alloc_w[k]));
-        weight_sum = wadd(weight_sum, prm.alloc_w[k]);
+    i64 alloc_raw = 0;
+    if (!DYNAMIC_ONLY) {
+        i64 node_score = 0, weight_sum = 0;
+        for (int k = 0; k < prm.alloc_n_res; ++k) {
+            const int res = prm.alloc_res[k];
+            i64 a = 0;
+            if (res == FGS_RES_CPU) a = R(NR_ALLOC_MCPU);
+            else if (res == FGS_RES_MEM) a = R(NR_ALLOC_MEM);
+            else if (res == FGS_RES_EPH) a = R(NR_ALLOC_EPH);
+            else if (res >= FGS_RES_SCALAR0 && res < FGS_RES_SCALAR0 + S) a = R(nr_alloc_scalar(res - FGS_RES_SCALAR0));
+            const i64 rs_ = prm.alloc_mode == 0 ? wmul(-1, a) : a;
+            node_score = wadd(node_score, wmul(rs_, prm.alloc_w[k]));
+            weight_sum = wadd(weight_sum, prm.alloc_w[k]);
+        }
+        alloc_raw = weight_sum != 0 ? node_score / weight_sum : 0;
     }
-    const i64 alloc_raw = weight_sum != 0 ? node_score / weight_sum : 0;
 
     auto W = [&](int c, i64 v) { nd[(i64)c * ns] = v; };
     W(ND_THR_GPU, thr_gpu);
@@ -81,18 +88,19 @@ __device__ __forceinline__ void derive_row(const DeriveParams& prm, const long l
     W(ND_FREE_MEM, R(NR_ALLOC_MEM) - R(NR_REQ_MEM));
     W(ND_FREE_EPH, R(NR_ALLOC_EPH) - R(NR_REQ_EPH));
     W(ND_FLAGS, (i64)flags);
-    W(ND_CAP_CPU, R(NR_ALLOC_MCPU));
     W(ND_NZR_CPU, R(NR_NZ_MCPU));
-    W(ND_CAP_MEM, R(NR_ALLOC_MEM));
     W(ND_NZR_MEM, R(NR_NZ_MEM));
     W(ND_GPU_SCORE, gpu_score);
     W(ND_MEM_SCORE, mem_score);
-    W(ND_ALLOC_RAW, alloc_raw);
-    W(ND_ALLOC_EPH, R(NR_ALLOC_EPH));
     W(ND_LEFT_PODS, R(NR_ALLOC_PODS) - R(NR_NUM_PODS));
-    for (int s = 0; s < S; ++s) {
-        W(nd_free_scalar(s), R(nr_alloc_scalar(s)) - R(nr_req_scalar(S, s)));
-        W(nd_alloc_scalar(S, s), R(nr_alloc_scalar(s)));
+    for (int s = 0; s < S; ++s) W(nd_free_scalar(s), R(nr_alloc_scalar(s)) - R(nr_req_scalar(S, s)));
+    if (!DYNAMIC_ONLY) {
+        W(ND_CAP_CPU, R(NR_ALLOC_MCPU));
+        W(ND_CAP_MEM, R(NR_ALLOC_MEM));
+        W(ND_ALLOC_RAW, alloc_raw);
+        W(ND_ALLOC_EPH, R(NR_ALLOC_EPH));
+        W(ND_MEM_EACH, mem_each);
+        for (int s = 0; s < S; ++s) W(nd_alloc_scalar(S, s), R(nr_alloc_scalar(s)));
     }
 }
 

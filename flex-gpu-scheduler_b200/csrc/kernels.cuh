@@ -26,6 +26,7 @@ enum NodeCol : int {
     ND_ALLOC_RAW,     // Allocatable.Score raw value (allocatable.go:120-143)
     ND_ALLOC_EPH,     // Allocatable.EphemeralStorage (generic Fit scoring only)
     ND_LEFT_PODS,     // AllowedPodNumber − len(Pods) (core.go:367)
+    ND_MEM_EACH,      // memory of one device, memCnt / gpuCnt (gpu_node.go:55); 0 where NewGPUNode panics
     ND_FIXED_COLS,
     // then S columns free_scalar[s] = Allocatable[s] − Requested[s], then S columns alloc_scalar[s]
 };

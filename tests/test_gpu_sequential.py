@@ -104,9 +104,13 @@ def test_whole_gpu_passes_filter_but_reserve_fails(gpu_ok, oracle):
     eng.close()
 
 
-@pytest.mark.parametrize("env", [{}, {"FGS_SEQ_CTAS": "1"}, {"FGS_SEQ_CTAS": "3", "FGS_SEQ_STATE_GLOBAL": "1"}])
+# geometry variants: one thread-block cluster exchanging through distributed shared memory (the default for a
+# cluster this small; seq_ctas is reported negative), one CTA, global mailboxes with the node state in shared
+# memory, global mailboxes with the node state in global memory
+@pytest.mark.parametrize("env,ctas", [({}, -4), ({"FGS_SEQ_CTAS": "1"}, 1), ({"FGS_SEQ_CLUSTER": "0"}, 3),
+                                      ({"FGS_SEQ_CTAS": "3", "FGS_SEQ_STATE_GLOBAL": "1"}, 3)])
 @pytest.mark.parametrize("cfg_id", [1, 2])
-def test_synthetic_cluster_follows_the_oracle(gpu_ok, oracle, cfg_id, env):
+def test_synthetic_cluster_follows_the_oracle(gpu_ok, oracle, cfg_id, env, ctas):
     s = fgs.config_synth(cfg_id, n_nodes=700, n_pending=260, max_existing_pods=6, pm_invalid_nodes=10)
     cfg = fgs.config_plugins(cfg_id)
     nodes = SS.snapshot_to_nodes(s.snapshot.contents)
@@ -120,7 +124,7 @@ def test_synthetic_cluster_follows_the_oracle(gpu_ok, oracle, cfg_id, env):
                           np.ctypeslib.as_array(s.snapshot.contents.nonzero, shape=(N * 2,)))
     eng, res = _run(s.snapshot, s.pending, cfg, env)
     t = eng.timings()
-    assert t["seq_ctas"] == (int(env["FGS_SEQ_CTAS"]) if "FGS_SEQ_CTAS" in env else 3)
+    assert t["seq_ctas"] == ctas
     final, stats = SS.follow(oracle, nodes, queue, cfg, res)
     assert stats["committed"] > 100
     # batch evaluation of a probe against the table the commits left behind

@@ -16,8 +16,11 @@ pk_n, pk_p = fgs.Packer(2), fgs.Packer(2)
 nodes = pk_n.nodes(s.snapshot)
 table = pk_p.pods(s.pending)
 for ctas in [None] + [int(x) for x in os.environ.get("SEQ_SWEEP", "").split(",") if x]:
-    if ctas is not None:
-        os.environ["FGS_SEQ_CTAS"] = str(ctas)
+    if ctas is not None:  # 0 = automatic geometry without the cluster variant
+        if ctas == 0:
+            os.environ["FGS_SEQ_CLUSTER"] = "0"
+        else:
+            os.environ["FGS_SEQ_CTAS"] = str(ctas)
     eng = fgs.Engine(device=0)
     eng.set_plugins(cfg)
     for rep in range(2):
