@@ -123,12 +123,13 @@ class Timings(C.Structure):
 
 
 class SeqOpts(C.Structure):
-    _fields_ = [("reserve_flex", C.c_int32), ("_pad", C.c_int32)]
+    _fields_ = [("reserve_flex", C.c_int32), ("_pad", C.c_int32), ("quotas", C.c_void_p)]
 
 
 class SeqResults(C.Structure):
     _fields_ = [("feasible_count", p_i32), ("selected_node", p_i32), ("selected_score", p_i64), ("pod_err", p_u32),
-                ("device_index", p_i32), ("committed", p_u8)]
+                ("device_index", p_i32), ("committed", p_u8), ("quota_code", p_u8), ("quota_used", p_i64),
+                ("quota_used_present", p_u32)]
 
 
 class SynthParams(C.Structure):

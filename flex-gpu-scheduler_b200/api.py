@@ -190,6 +190,9 @@ class SeqResults:
         self.pod_err = np.zeros(n, np.uint32)[:P]
         self.device_index = np.zeros(n, np.int32)[:P]
         self.committed = np.zeros(n, np.uint8)[:P]
+        self.quota_code = np.zeros(n, np.uint8)[:P]
+        self.quota_used = None
+        self.quota_used_present = None
 
 
 class Engine:
@@ -301,8 +304,9 @@ class Engine:
                     reduce_int32=bool(t.reduce_int32), emit_int32=bool(t.emit_int32), seq_ms=t.seq_ms, seq_ctas=int(t.seq_ctas))
 
     # -- sequential cycles: assume + Reserve between pods -------------------------------------------------
-    def schedule_sequential(self, pod_table, reserve_flex=True):
-        """One scheduling cycle per pod of the table, in order, committing each placement (fgs_schedule_sequential)."""
+    def schedule_sequential(self, pod_table, reserve_flex=True, quotas=None):
+        """One scheduling cycle per pod of the table, in order, committing each placement (fgs_schedule_sequential).
+        quotas: POINTER(Quotas) when CapacityScheduling is in the profile (PreFilter per cycle, Reserve per commit)."""
         P = int(pod_table.contents.n_pods)
         r = SeqResults(P)
         cr = L.SeqResults()
@@ -312,7 +316,16 @@ class Engine:
         cr.pod_err = _ptr(r.pod_err, C.c_uint32)
         cr.device_index = _ptr(r.device_index, C.c_int32)
         cr.committed = _ptr(r.committed, C.c_uint8)
+        cr.quota_code = _ptr(r.quota_code, C.c_uint8)
         o = L.SeqOpts(reserve_flex=1 if reserve_flex else 0)
+        if quotas is not None:
+            q = quotas.contents
+            NS, W = int(q.n_ns), 2 + int(q.n_scalars)
+            r.quota_used = np.zeros((max(NS, 1), W), np.int64)[:NS]
+            r.quota_used_present = np.zeros(max(NS, 1), np.uint32)[:NS]
+            cr.quota_used = _ptr(r.quota_used, C.c_int64)
+            cr.quota_used_present = _ptr(r.quota_used_present, C.c_uint32)
+            o.quotas = C.cast(quotas, C.c_void_p)
         self._check(self._lib.fgs_schedule_sequential(self._h, pod_table, C.byref(o), C.byref(cr)))
         return r
 

@@ -62,8 +62,8 @@ constexpr int kWordsA = 8;       // mailbox words per CTA, phase A (7 used)
 constexpr int kWordsB = 4;       // phase B (3 used)
 constexpr int kMaxCluster = 16;  // CTAs of the single-cluster variant
 
-enum SeqExtra : int { SX_ACCT_CPU = 0, SX_ACCT_MEM, SX_ANNOT, SX_COLS };
-enum SeqOut : int { SO_COUNT = 0, SO_NODE, SO_SCORE, SO_ERR, SO_DEVICE, SO_COMMITTED, SO_COLS };
+enum SeqExtra : int { SX_ACCT_CPU = 0, SX_ACCT_MEM, SX_ANNOT, SX_NS, SX_COLS };
+enum SeqOut : int { SO_COUNT = 0, SO_NODE, SO_SCORE, SO_ERR, SO_DEVICE, SO_COMMITTED, SO_QUOTA, SO_COLS };
 
 struct SeqParams {
     DeriveParams dv;       // raw + derived node tables, plugin args of the derivation
@@ -73,6 +73,13 @@ struct SeqParams {
     u64* mail_a;           // [2][G][kWordsA] self-tagged words
     u64* mail_b;           // [2][G][kWordsB]
     u64* prof;             // [G][16] clock sums per section (FGS_SEQ_PROFILE=1), else NULL
+    // ElasticQuota tables (CapacityScheduling in the profile), device memory; q_has_eq == NULL: not in the profile
+    const uint8_t* q_has_eq; // [NS]
+    const i64* q_min;        // [NS][2+S]
+    const i64* q_max;
+    i64* q_used;             // rewritten by CapacityScheduling.Reserve
+    uint32_t* q_used_present;
+    i64 n_ns;
     int* status;           // [0]: index of the first pod whose commit left the supported range, INT_MAX none
     i64 n_pods, p_pad;
     int K, state_smem;
@@ -288,6 +295,7 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
         mbar_init(&bars[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         *s_dirty = -1;
+        s_dirty[1] = 0;
     }
     __syncthreads();
     if (tid == 0 && n_tiles > 0) issue_pod_tile(0);
@@ -358,7 +366,33 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
         }
     };
 
-    for (i64 p = 0; p < prm.n_pods; ++p) {
+    // ---- ElasticQuota state: owned by the communication warp of CTA 0 (lane c holds resource column c) ---------
+    const bool quota_on = prm.q_has_eq != nullptr;
+    const bool quota_warp = quota_on && comm && cta == 0;
+    const int QW = 2 + S;
+    i64 agg_used = 0, agg_min = 0; // Σ over namespaces with a quota (aggregatedUsedOverMinWith, elasticquota.go:40-51)
+    uint32_t agg_present = 0;
+    bool pend_has = false, pend_key = false; // the previous pod's reservation, applied once its commit is known
+    int pend_ns = -1;
+    i64 pend_v = 0;
+    uint32_t pend_keys = 0;
+    if (quota_warp) {
+        for (i64 k = 0; k < prm.n_ns; ++k) {
+            if (!prm.q_has_eq[k]) continue;
+            const uint32_t up = prm.q_used_present[k];
+            agg_present |= up;
+            if (lane < QW) {
+                if (lane < 2 || ((up >> (lane - 2)) & 1u)) agg_used += prm.q_used[k * QW + lane];
+                agg_min += prm.q_min[k * QW + lane];
+            }
+        }
+    }
+    int* s_commit = s_dirty + 1; // 1: the previous cycle's pod was committed by a thread of this CTA
+
+    // with quotas one more (drain) iteration carries the last pod's commit flag to the quota warp
+    const i64 n_iter = prm.n_pods + (quota_on ? 1 : 0);
+    for (i64 p = 0; p < n_iter; ++p) {
+        const bool drain = p >= prm.n_pods;
         const i64 it = p / kSeqTileP;
         const int jp = (int)(p % kSeqTileP), stage = (int)(it & 1);
         const uint32_t tag = (uint32_t)(p + 1);
@@ -368,8 +402,43 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
 
         if (comm) {
             // ================= the communication warp =====================================================
+            // CapacityScheduling.PreFilter of this pod (capacity_scheduling.go:201-275, no nominated pods), while
+            // the compute warps filter: once against the quota table as it is and once with the previous pod's
+            // reservation added — which of the two holds is known when that pod's commit flag arrives with (A)
+            uint32_t qbits = 0;
+            bool q_has = false, q_key = false;
+            int q_ns = -1;
+            i64 q_v = 0;
+            uint32_t q_keys = 0;
+            if (quota_warp && !drain) {
+                if (jp == 0) mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
+                q_ns = (int)PC(pd_cols(S) + SX_NS);
+                q_keys = (uint32_t)((u64)PC(PD_META) >> 32);
+                q_v = lane == 0 ? PC(PD_REQ_CPU) : (lane == 1 ? PC(PD_REQ_MEM) : (lane < QW ? PC(PD_FIXED_COLS + lane - 2) : 0));
+                q_has = q_ns >= 0 && q_ns < prm.n_ns && prm.q_has_eq[q_ns];
+                q_key = lane < 2 || (lane < QW && ((q_keys >> (lane - 2)) & 1u));
+                if (q_has) { // a namespace without an ElasticQuota passes (:210-217)
+                    const uint32_t up = *(volatile uint32_t*)(prm.q_used_present + q_ns);
+                    const bool u_key = lane < 2 || (lane < QW && ((up >> (lane - 2)) & 1u));
+                    const i64 u = u_key ? *(volatile i64*)(prm.q_used + (i64)q_ns * QW + lane) : 0;
+                    const i64 mx = lane < QW ? prm.q_max[(i64)q_ns * QW + lane] : 0;
+                    const i64 d_same = (pend_has && pend_ns == q_ns && pend_key) ? pend_v : 0;
+                    const i64 d_all = (pend_has && pend_key) ? pend_v : 0;
+                    // usedOverMaxWith = cmp2(request, Used, Max): the request's scalar keys (elasticquota.go:94-96,165-181)
+                    const uint32_t m0 = __ballot_sync(0xffffffffu, q_key && q_v + u > mx);
+                    const uint32_t m1 = __ballot_sync(0xffffffffu, q_key && q_v + u + d_same > mx);
+                    // aggregatedUsedOverMinWith: keys of Σused ∪ the request's (:40-51)
+                    const uint32_t ak0 = agg_present | q_keys, ak1 = ak0 | (pend_has ? pend_keys : 0u);
+                    const bool a0 = lane < 2 || (lane < QW && ((ak0 >> (lane - 2)) & 1u));
+                    const bool a1 = lane < 2 || (lane < QW && ((ak1 >> (lane - 2)) & 1u));
+                    const uint32_t n0 = __ballot_sync(0xffffffffu, a0 && agg_used + q_v > agg_min);
+                    const uint32_t n1 = __ballot_sync(0xffffffffu, a1 && agg_used + d_all + q_v > agg_min);
+                    const uint32_t code0 = m0 ? 1u : (n0 ? 2u : 0u), code1 = m1 ? 1u : (n1 ? 2u : 0u);
+                    qbits = (code0 << 1) | (code1 << 3);
+                }
+            }
             __syncthreads(); // (1) the compute warps' phase-A partials are in shared memory
-            if (lane == 0 && jp == 0 && it + 1 < n_tiles) { // every thread is past its last read of the previous tile
+            if (lane == 0 && !drain && jp == 0 && it + 1 < n_tiles) { // every thread is past its last read of the previous tile
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 issue_pod_tile(it + 1);
             }
@@ -379,6 +448,12 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
             ctick(0); // commit + Filter of the slowest thread of this CTA
             uint32_t c2 = __reduce_add_sync(0xffffffffu, (uint32_t)cf & 0xffffffu);
             uint32_t f2 = __reduce_or_sync(0xffffffffu, (uint32_t)(cf >> 24));
+            if (quota_on) { // bits 1-4: the two PreFilter verdicts (CTA 0); bit 5: the previous pod was committed here
+                const int cm = *(volatile int*)s_commit;
+                f2 |= qbits | (cm ? 32u : 0u);
+                __syncwarp();
+                if (lane == 0 && cm) *s_commit = 0;
+            }
             i64 a1 = warp_max_i64(w ? s_part_a[lane * 4 + 1] : kMin64);
             i64 a2 = warp_max_i64(w ? s_part_a[lane * 4 + 2] : kMin64);
             i64 a3 = warp_max_i64(w ? s_part_a[lane * 4 + 3] : kMin64);
@@ -427,6 +502,33 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
             }
             if (cprof) consume((i64)c2);
             ctick(1); // exchange A, including the wait for the slowest CTA
+            uint32_t qcode = 0;
+            if (quota_on) {
+                const bool committed_prev = (f2 >> 5) & 1u;
+                qcode = committed_prev ? (f2 >> 3) & 3u : (f2 >> 1) & 3u;
+                if (quota_warp) {
+                    if (pend_has && committed_prev) { // CapacityScheduling.Reserve → reserveResource (elasticquota.go:74-80)
+                        if (pend_key) {
+                            const uint32_t up = *(volatile uint32_t*)(prm.q_used_present + pend_ns);
+                            const bool u_key = lane < 2 || ((up >> (lane - 2)) & 1u);
+                            i64* up_ = prm.q_used + (i64)pend_ns * QW + lane;
+                            *(volatile i64*)up_ = (u_key ? *(volatile i64*)up_ : 0) + pend_v;
+                            agg_used += pend_v;
+                        }
+                        __syncwarp();
+                        if (lane == 0) *(volatile uint32_t*)(prm.q_used_present + pend_ns) |= pend_keys;
+                        __syncwarp();
+                        agg_present |= pend_keys;
+                    }
+                    pend_has = q_has && qcode == 0 && !drain;
+                    pend_ns = q_ns;
+                    pend_v = q_v;
+                    pend_keys = q_keys;
+                    pend_key = q_key;
+                }
+                if (qcode) c2 = 0; // rejected in PreFilter: no Filter/Score results, nothing to select
+                f2 = (f2 & 1u) | (qcode << 8);
+            }
             if (lane == 0) {
                 s_fin_a[0] = (i64)(((u64)f2 << 32) | c2);
                 s_fin_a[1] = a1;
@@ -479,7 +581,7 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
         }
 
         // ================= the compute warps ===============================================================
-        if (jp == 0) mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
+        if (!drain && jp == 0) mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
         // per-pod values (broadcast reads)
         const u64 pmeta = (u64)PC(PD_META);
         const uint32_t pf = (uint32_t)pmeta;
@@ -496,7 +598,8 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
         i64 vflex = kMin64, vhi = kMin64, vnlo = kMin64;
         const bool flex_pod = use_flex_filter && kind != 0;
         const bool fit_req = use_fit_filter && !req_none;
-        for (int j = 0; j < K; ++j) {
+        const int Kc = drain ? 0 : K; // the drain iteration only carries flags
+        for (int j = 0; j < Kc; ++j) {
             const i64 i = (i64)j * kSeqThreads + ct;
             if (node0 + i >= n_nodes) break;
             auto C = [&](int c) { return st[(i64)c * st_stride + i]; };
@@ -594,7 +697,8 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
         const i64 count = (i64)(uint32_t)s_fin_a[0];
         if (prof) consume(count);
         tick(2); // waiting for exchange A
-        const bool fpanic = (s_fin_a[0] >> 32) & 1;
+        const uint32_t qcode = (uint32_t)(s_fin_a[0] >> 40) & 3u; // CapacityScheduling.PreFilter: 0 pass, 1 over Max, 2 over Σmin
+        const bool fpanic = ((s_fin_a[0] >> 32) & 1) && qcode == 0;
         const i64 g_flex = s_fin_a[1], g_hi = s_fin_a[2], g_nlo = s_fin_a[3];
 
         // ---- phase B: NormalizeScore / weights / selectHost key on my feasible nodes -------------------------
@@ -672,7 +776,7 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
             score = (i64)(k >> prm.key_shift);
         }
         const bool mine = sel >= node0 && sel < node0 + cta_nodes && (int)((sel - node0) % kSeqThreads) == ct;
-        if (sel < 0 ? (cta == 0 && ct == 0) : mine) {
+        if (!drain && (sel < 0 ? (cta == 0 && ct == 0) : mine)) {
             int dev = FGS_RESERVE_SKIPPED;
             bool commit = sel >= 0 && err == 0;
             if (commit && prm.reserve_flex) {
@@ -726,6 +830,7 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
                 if (!in_range) atomicMin(prm.status, (int)(p < 0x7fffffff ? p : 0x7ffffffe));
                 derive_row<true>(prm.dv, row, st_stride, st + i, st_stride);
                 if (SMEM) *s_dirty = (int)i; // the communication warp copies the row to the global tables
+                if (quota_on) *s_commit = 1; // → CapacityScheduling.Reserve of this pod, applied by the quota warp
             }
             prm.out[(i64)SO_COUNT * prm.p_pad + p] = count;
             prm.out[(i64)SO_NODE * prm.p_pad + p] = sel;
@@ -733,6 +838,7 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
             prm.out[(i64)SO_ERR * prm.p_pad + p] = (i64)err;
             prm.out[(i64)SO_DEVICE * prm.p_pad + p] = (i64)dev;
             prm.out[(i64)SO_COMMITTED * prm.p_pad + p] = commit ? 1 : 0;
+            prm.out[(i64)SO_QUOTA * prm.p_pad + p] = (i64)qcode;
         }
         tick(5); // verdict + commit (this thread's share)
     }
@@ -771,6 +877,9 @@ struct SeqState {
     void* d_out = nullptr;  // [SO_COLS][cap]
     void* h_out = nullptr;
     int64_t cap = 0;
+    void* d_quota = nullptr; // has_eq | min | max | used | used_present
+    void* h_quota = nullptr;
+    size_t quota_bytes = 0;
     void* d_mail = nullptr; // mail_a | mail_b | status
     size_t mail_bytes = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -784,6 +893,8 @@ void Engine::seq_free() {
     if (seq->d_out) cudaFree(seq->d_out);
     if (seq->h_out) cudaFreeHost(seq->h_out);
     if (seq->d_mail) cudaFree(seq->d_mail);
+    if (seq->d_quota) cudaFree(seq->d_quota);
+    if (seq->h_quota) cudaFreeHost(seq->h_quota);
     if (seq->ev0) cudaEventDestroy(seq->ev0);
     if (seq->ev1) cudaEventDestroy(seq->ev1);
     delete seq;
@@ -842,12 +953,15 @@ static int seq_stage_pods(Engine* e, const fgs_pod_table* t, int64_t pp) {
     col(x0 + SX_ACCT_MEM, t->acct_nz_mem);
     int64_t* meta = h + (int64_t)PD_META * pp;
     int64_t* ann = h + (int64_t)(x0 + SX_ANNOT) * pp;
+    int64_t* nsc = h + (int64_t)(x0 + SX_NS) * pp;
     for (int64_t i = 0; i < P; ++i) {
         meta[i] = (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]);
         ann[i] = (int64_t)t->index_annot[i];
+        nsc[i] = t->ns ? (int64_t)t->ns[i] : -1;
     }
     std::memset(meta + P, 0, sizeof(int64_t) * (size_t)(pp - P));
     std::memset(ann + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+    std::memset(nsc + P, 0, sizeof(int64_t) * (size_t)(pp - P));
     FGS_CUDA(e, cudaMemcpyAsync(q->d_pods, q->h_pods, sizeof(int64_t) * (size_t)(x0 + SX_COLS) * (size_t)pp, cudaMemcpyHostToDevice, e->stream));
     return FGS_OK;
 }
@@ -887,6 +1001,43 @@ extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, c
     SeqState* q = e->seq;
     rc = seq_stage_pods(e, t, pp);
     if (rc) return rc;
+
+    // ElasticQuota tables (CapacityScheduling in the profile)
+    const fgs_quotas* qt = opts ? opts->quotas : nullptr;
+    size_t q_off[5] = {0, 0, 0, 0, 0}, q_total = 0;
+    if (qt) {
+        if (qt->n_scalars != e->S) return e->fail(FGS_E_INVALID, "fgs_schedule_sequential: quotas n_scalars differs from the engine's");
+        if (qt->n_ns < 0 || (qt->n_ns > 0 && (!qt->has_eq || !qt->min || !qt->max || !qt->used || !qt->used_scalar_present)))
+            return e->fail(FGS_E_INVALID, "fgs_schedule_sequential: incomplete quota tables");
+        const size_t NS = (size_t)qt->n_ns, W = (size_t)(2 + e->S);
+        auto take = [&](size_t bytes) {
+            const size_t o = q_total;
+            q_total += (bytes + 255) & ~(size_t)255;
+            return o;
+        };
+        q_off[0] = take(NS);
+        q_off[1] = take(sizeof(int64_t) * NS * W);
+        q_off[2] = take(sizeof(int64_t) * NS * W);
+        q_off[3] = take(sizeof(int64_t) * NS * W);
+        q_off[4] = take(sizeof(uint32_t) * NS);
+        q_total += 256;
+        if (q_total > q->quota_bytes) {
+            if (q->d_quota) cudaFree(q->d_quota);
+            if (q->h_quota) cudaFreeHost(q->h_quota);
+            q->d_quota = q->h_quota = nullptr;
+            q->quota_bytes = 0;
+            FGS_CUDA(e, cudaMalloc(&q->d_quota, q_total));
+            FGS_CUDA(e, cudaMallocHost(&q->h_quota, q_total));
+            q->quota_bytes = q_total;
+        }
+        char* hq = (char*)q->h_quota;
+        std::memcpy(hq + q_off[0], qt->has_eq, NS);
+        std::memcpy(hq + q_off[1], qt->min, sizeof(int64_t) * NS * W);
+        std::memcpy(hq + q_off[2], qt->max, sizeof(int64_t) * NS * W);
+        std::memcpy(hq + q_off[3], qt->used, sizeof(int64_t) * NS * W);
+        std::memcpy(hq + q_off[4], qt->used_scalar_present, sizeof(uint32_t) * NS);
+        FGS_CUDA(e, cudaMemcpyAsync(q->d_quota, q->h_quota, q_total, cudaMemcpyHostToDevice, e->stream));
+    }
 
     // geometry. Small clusters of nodes: ONE thread-block cluster (<= 16 CTAs) whose CTAs exchange through
     // distributed shared memory; otherwise up to one CTA per SM exchanging through global mailboxes. As few nodes
@@ -1000,6 +1151,15 @@ extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, c
     sp.seed = e->seed;
     sp.key_shift = ep.key_shift;
     sp.reserve_flex = (opts && opts->reserve_flex) ? 1 : 0;
+    if (qt) {
+        char* dq = (char*)q->d_quota;
+        sp.q_has_eq = (const uint8_t*)(dq + q_off[0]);
+        sp.q_min = (const i64*)(dq + q_off[1]);
+        sp.q_max = (const i64*)(dq + q_off[2]);
+        sp.q_used = (i64*)(dq + q_off[3]);
+        sp.q_used_present = (uint32_t*)(dq + q_off[4]);
+        sp.n_ns = qt->n_ns;
+    }
 
     FGS_CUDA(e, cudaEventRecord(q->ev0, e->stream));
     void* args[] = {(void*)&sp};
@@ -1028,7 +1188,14 @@ extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, c
     FGS_CUDA(e, cudaMemcpyAsync(q->h_out, q->d_out, sizeof(int64_t) * SO_COLS * (size_t)pp, cudaMemcpyDeviceToHost, e->stream));
     int status = none;
     FGS_CUDA(e, cudaMemcpyAsync(&status, d_status, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    if (qt && q_total) // ElasticQuotaInfo.Used after every CapacityScheduling.Reserve of the queue
+        FGS_CUDA(e, cudaMemcpyAsync((char*)q->h_quota + q_off[3], (char*)q->d_quota + q_off[3], q_total - q_off[3], cudaMemcpyDeviceToHost, e->stream));
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (qt) {
+        const size_t NS = (size_t)qt->n_ns, W = (size_t)(2 + e->S);
+        if (out->quota_used) std::memcpy(out->quota_used, (char*)q->h_quota + q_off[3], sizeof(int64_t) * NS * W);
+        if (out->quota_used_present) std::memcpy(out->quota_used_present, (char*)q->h_quota + q_off[4], sizeof(uint32_t) * NS);
+    }
     cudaEventElapsedTime(&e->tm.seq_ms, q->ev0, q->ev1);
     e->tm.seq_ctas = cluster ? -G : G; // negative: one thread-block cluster of that many CTAs
     if (want_prof) { // clock cycles per scheduling cycle and section, CTA 0 and the mean over CTAs
@@ -1051,6 +1218,7 @@ extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, c
         if (out->pod_err) out->pod_err[p] = (uint32_t)h[(int64_t)SO_ERR * pp + p];
         if (out->device_index) out->device_index[p] = (int32_t)h[(int64_t)SO_DEVICE * pp + p];
         if (out->committed) out->committed[p] = (uint8_t)h[(int64_t)SO_COMMITTED * pp + p];
+        if (out->quota_code) out->quota_code[p] = (uint8_t)h[(int64_t)SO_QUOTA * pp + p];
     }
     // the derived table changed under the batched path's feet: redo its node-side analysis
     rc = e->analyze_nodes_now();

@@ -179,6 +179,10 @@ int fgs_status_plane(fgs_engine* e, uint32_t plugin, uint8_t* out);
 typedef struct fgs_seq_opts {
     int32_t reserve_flex; /* 1: FlexGPU is a Reserve plugin of the profile (it is in the reference's chart) */
     int32_t _pad;
+    /* non-NULL: CapacityScheduling is in the profile. Every cycle starts with its PreFilter against the CURRENT
+     * ElasticQuotaInfos (pkg/capacityscheduling/capacity_scheduling.go:201-275, no nominated pods) and a committed
+     * pod is added to its namespace's Used (Reserve :340-353 → reserveResource, elasticquota.go:74-80). */
+    const fgs_quotas* quotas;
 } fgs_seq_opts;
 
 /* Per-pod outputs of fgs_schedule_sequential (host buffers owned by the caller, each [P]; any may be NULL). */
@@ -189,6 +193,9 @@ typedef struct fgs_seq_results {
     uint32_t* pod_err;       /* FGS_PODERR_* */
     int32_t* device_index;   /* the nvidia.flex.com/index annotation Reserve sets, or FGS_RESERVE_* */
     uint8_t* committed;      /* 1: the pod was assumed on selected_node and the node row was updated */
+    uint8_t* quota_code;     /* CapacityScheduling.PreFilter: 0 Success, 1 over Max, 2 Σused over Σmin (then no node is tried) */
+    int64_t* quota_used;     /* [n_ns][2+S] ElasticQuotaInfo.Used after the queue (opts->quotas given) */
+    uint32_t* quota_used_present; /* [n_ns] its scalar keys */
 } fgs_seq_results;
 
 /* What the reference does with a queue of pods, one scheduling cycle each, in `pods` order

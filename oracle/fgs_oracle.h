@@ -96,6 +96,10 @@ int fgs_oracle_quota_prefilter(const fgs_podset* pending, const fgs_quotas* q,
                                const int64_t* nominated_uid, int64_t p0, int64_t p1,
                                uint8_t* code);
 
+/* ElasticQuotaInfo.reserveResource (op = +1) / unreserveResource (op = -1) with pod p's request
+ * (elasticquota.go:74-88,126-147) on one namespace's Used row {mcpu, mem, scalars} and its scalar keys. */
+int fgs_oracle_quota_reserve(const fgs_podset* pods, int64_t p, int op, int64_t* used, uint32_t* used_present);
+
 #ifdef __cplusplus
 }
 #endif

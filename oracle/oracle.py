@@ -59,6 +59,8 @@ def load():
     lib.fgs_oracle_quota_prefilter.restype = C.c_int
     lib.fgs_oracle_quota_prefilter.argtypes = [C.POINTER(L.Podset), C.POINTER(L.Quotas), C.POINTER(L.Podset), L.p_i64, L.p_i64, C.c_int64,
                                                C.c_int64, L.p_u8]
+    lib.fgs_oracle_quota_reserve.restype = C.c_int
+    lib.fgs_oracle_quota_reserve.argtypes = [C.POINTER(L.Podset), C.c_int64, C.c_int, L.p_i64, L.p_u32]
     _lib = lib
     return lib
 
@@ -137,3 +139,12 @@ def quota_prefilter(pending, quotas, nominated=None, pending_uid=None, nominated
     nu = np.ascontiguousarray(nominated_uid, np.int64).ctypes.data_as(L.p_i64) if nominated_uid is not None else None
     load().fgs_oracle_quota_prefilter(pending, quotas, nominated, pu, nu, 0, P, code.ctypes.data_as(L.p_u8))
     return code[:P]
+
+
+def quota_reserve(pods, p, used_row, used_present, op=1):
+    """reserveResource (op=+1) / unreserveResource (op=-1) of pod p on one namespace's Used row (numpy int64 [2+S],
+    modified in place); returns the new scalar-key mask."""
+    assert used_row.dtype == np.int64 and used_row.flags["C_CONTIGUOUS"]
+    up = np.array([used_present], np.uint32)
+    load().fgs_oracle_quota_reserve(pods, p, op, used_row.ctypes.data_as(L.p_i64), up.ctypes.data_as(L.p_u32))
+    return int(up[0])

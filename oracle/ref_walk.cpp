@@ -895,6 +895,26 @@ void qAddQ(QRes& acc, const QRes& r, int S) {
 
 } // namespace
 
+// ElasticQuotaInfo.reserveResource / unreserveResource — pkg/capacityscheduling/elasticquota.go:74-88, with the
+// request addPodIfNotPresent / deletePodIfPresent hand them (computePodResourceRequest of the pod, :126-147):
+// Used.Memory, Used.MilliCPU and every scalar KEY of the request (SetScalar creates the key in Used).
+// used = one namespace's row {mcpu, mem, scalars}; *used_present = its scalar keys. op: +1 reserve, -1 unreserve.
+extern "C" int fgs_oracle_quota_reserve(const fgs_podset* pods, int64_t p, int op, int64_t* used,
+                                        uint32_t* used_present) {
+    const int S = pods->n_scalars;
+    Resource r = computePodResourceRequest(pods, p);
+    auto app = [&](i64 a, i64 b) { return op >= 0 ? wadd(a, b) : wsub(a, b); };
+    used[0] = app(used[0], r.mcpu);
+    used[1] = app(used[1], r.mem);
+    for (int s = 0; s < S; ++s)
+        if ((r.scalarPresent >> s) & 1u) {
+            const i64 cur = ((*used_present >> s) & 1u) ? used[2 + s] : 0; // a missing map key reads as 0
+            used[2 + s] = app(cur, r.scalar[s]);
+            *used_present |= 1u << s;
+        }
+    return 0;
+}
+
 extern "C" int fgs_oracle_quota_prefilter(const fgs_podset* pending, const fgs_quotas* q,
                                           const fgs_podset* nominated, const int64_t* pending_uid,
                                           const int64_t* nominated_uid, int64_t p0, int64_t p1,

@@ -6,6 +6,7 @@ reference's assume + Reserve are applied to the description (the pod joins the n
 annotation FlexGPU.Reserve sets — scheduler.go:496-521, flex_gpu.go:178-223) and the next pod sees it.
 NodeInfo aggregates are re-accumulated by builders.build_snapshot the way NodeInfo.AddPod does."""
 import copy
+import ctypes as C
 
 import numpy as np
 
@@ -90,13 +91,46 @@ def snapshot_to_nodes(sn):
     return nodes
 
 
-def follow(oracle, nodes, queue, cfg, res, reserve_flex=True, S=2, check_scores=True):
+class QuotaState:
+    """Mutable copy of an fgs_quotas table (ElasticQuotaInfos) for the stepped reference."""
+
+    def __init__(self, q):
+        NS, S = int(q.n_ns), int(q.n_scalars)
+        W = 2 + S
+        self.NS, self.S = NS, S
+        self.has_eq = np.array(_arr(q.has_eq, NS), np.uint8).copy()
+        self.min = np.array(_arr(q.min, NS * W), np.int64).reshape(NS, W).copy()
+        self.max = np.array(_arr(q.max, NS * W), np.int64).reshape(NS, W).copy()
+        self.used = np.array(_arr(q.used, NS * W), np.int64).reshape(NS, W).copy()
+        self.present = np.array(_arr(q.used_scalar_present, NS), np.uint32).copy()
+
+    def struct(self):
+        q = L.Quotas()
+        q.n_ns, q.n_scalars = self.NS, self.S
+        q.has_eq = self.has_eq.ctypes.data_as(L.p_u8)
+        q.min = self.min.ctypes.data_as(L.p_i64)
+        q.max = self.max.ctypes.data_as(L.p_i64)
+        q.used = self.used.ctypes.data_as(L.p_i64)
+        q.used_scalar_present = self.present.ctypes.data_as(L.p_u32)
+        return q
+
+
+def follow(oracle, nodes, queue, cfg, res, reserve_flex=True, S=2, check_scores=True, quotas=None):
     """Step the reference through `queue` following the engine's choices in `res` (api.SeqResults).
     Mutates and returns `nodes` (the cluster after every commit). Asserts parity at every cycle."""
-    stats = dict(committed=0, unschedulable=0, reserve_fail=0, errors=0)
+    stats = dict(committed=0, unschedulable=0, reserve_fail=0, errors=0, quota_rejected=0)
     for p, pd in enumerate(queue):
         snap = B.build_snapshot(nodes, S)
         pend = B.build_podset([pd], S)
+        if quotas is not None:
+            # CapacityScheduling.PreFilter against the ElasticQuotaInfos as the previous commits left them
+            qs = quotas.struct()
+            qcode = int(oracle.quota_prefilter(pend.ptr, C.pointer(qs))[0])
+            assert int(res.quota_code[p]) == qcode, (p, int(res.quota_code[p]), qcode)
+            if qcode:
+                assert int(res.feasible_count[p]) == 0 and int(res.selected_node[p]) == -1 and not res.committed[p], p
+                stats["quota_rejected"] += 1
+                continue
         ref = oracle.evaluate(snap.ptr, pend.ptr, cfg, 0, 1)
         feas = ref.status[0] == 0
         F = int(feas.sum())
@@ -132,4 +166,8 @@ def follow(oracle, nodes, queue, cfg, res, reserve_flex=True, S=2, check_scores=
             placed["index"] = want  # p.Annotations[GPUIndexAnnotationKey] = strconv.Itoa(indexes[0])
         nodes[sel]["pods"].append(placed)
         stats["committed"] += 1
+        if quotas is not None:  # CapacityScheduling.Reserve → addPodIfNotPresent → reserveResource
+            ns = pd["ns"]
+            if 0 <= ns < quotas.NS and quotas.has_eq[ns]:
+                quotas.present[ns] = oracle.quota_reserve(pend.ptr, 0, quotas.used[ns], int(quotas.present[ns]))
     return nodes, stats

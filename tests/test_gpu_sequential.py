@@ -1,6 +1,7 @@
 """Sequential scheduling cycles on the GPU (fgs_schedule_sequential) against the oracle stepped pod by pod:
 every cycle sees the node rows the previous commits left — assume/AddPod (framework/types.go:583-609) and the
 device index FlexGPU.Reserve picked (flex_gpu.go:178-223)."""
+import ctypes as C
 import os
 
 import numpy as np
@@ -29,14 +30,14 @@ def _engine(nodes_or_snapshot, cfg, env=None, S=2):
     return eng
 
 
-def _run(snapshot_ptr, pending_ptr, cfg, env=None, reserve_flex=True):
+def _run(snapshot_ptr, pending_ptr, cfg, env=None, reserve_flex=True, quotas=None):
     env = env or {}
     for k, v in env.items():
         os.environ[k] = v
     try:
         eng = _engine(snapshot_ptr, cfg)
         table = fgs.Packer(2).pods(pending_ptr)
-        res = eng.schedule_sequential(table, reserve_flex=reserve_flex)
+        res = eng.schedule_sequential(table, reserve_flex=reserve_flex, quotas=quotas)
     finally:
         for k in env:
             os.environ.pop(k, None)
@@ -163,6 +164,28 @@ def test_most_allocated_and_allocatable_scores_without_reserve_plugin(gpu_ok, or
     assert (res.device_index == SS.RESERVE_SKIPPED).all()
     final, stats = SS.follow(oracle, nodes, queue, cfg, res, reserve_flex=False)
     assert stats["committed"] > 50
+    eng.close()
+
+
+@pytest.mark.parametrize("env", [{}, {"FGS_SEQ_CLUSTER": "0"}, {"FGS_SEQ_CTAS": "1"}])
+def test_elastic_quota_prefilter_and_reserve_between_cycles(gpu_ok, oracle, env):
+    # CapacityScheduling in the profile: every cycle starts with its PreFilter against the quotas as the earlier
+    # commits left them; a committed pod is added to its namespace's Used (capacity_scheduling.go:201-275,340-353)
+    s = fgs.config_synth(4, n_nodes=600, n_pending=400, n_namespaces=12, max_existing_pods=4)
+    cfg = fgs.config_plugins(4)
+    nodes = SS.snapshot_to_nodes(s.snapshot.contents)
+    queue = SS.podset_to_pods(s.pending.contents)
+    qstate = SS.QuotaState(s.quotas.contents)
+    # tighten Max so that namespaces fill up during the queue, and Σmin so that the aggregate check bites late
+    qstate.max[:, :2] = qstate.used[:, :2] + np.array([[40000, 400 * GiB]])
+    qstate.min[:, 1] = qstate.used[:, 1] + 100 * GiB
+    qs = qstate.struct()
+    eng, res = _run(s.snapshot, s.pending, cfg, env, quotas=C.pointer(qs))
+    final, stats = SS.follow(oracle, nodes, queue, cfg, res, quotas=qstate)
+    assert stats["committed"] > 50 and stats["quota_rejected"] > 20, stats
+    assert {0, 1, 2} <= set(int(x) for x in res.quota_code)
+    assert np.array_equal(res.quota_used, qstate.used)
+    assert np.array_equal(res.quota_used_present, qstate.present)
     eng.close()
 
 

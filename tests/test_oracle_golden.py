@@ -65,3 +65,21 @@ def test_capacity_reject_reasons(oracle):
     assert oracle.quota_prefilter(pend.ptr, qs.ptr).tolist() == [0, 1]
     pend, qs = G.capacity_case(cases[1])
     assert oracle.quota_prefilter(pend.ptr, qs.ptr).tolist() == [2]
+
+
+def test_quota_reserve_golden(oracle):
+    """TestReserveResource / TestUnReserveResource (pkg/capacityscheduling/elasticquota_test.go:27-129): Used ± the
+    pods' requests for memory, cpu and an extended (scalar) resource."""
+    S = 3
+    import builders as B
+    for case in G.load("quota_reserve"):
+        pods = [B.pod([B.ctr({"cpu": pd["cpu"], "memory": pd["mem"], ("scalar", 2): pd["gpu"]})]) for pd in case["pods"]]
+        pend = B.build_podset(pods, S)
+        used = np.zeros(2 + S, np.int64)
+        used[0], used[1], used[2 + 2] = case["before"]["cpu"], case["before"]["memory"], case["before"]["scalar:2"]
+        present = 1 << 2
+        for p in range(len(pods)):
+            present = oracle.quota_reserve(pend.ptr, p, used, present, op=1 if case["op"] == "reserve" else -1)
+        got = {"cpu": int(used[0]), "memory": int(used[1]), "scalar:2": int(used[2 + 2])}
+        assert got == case["expected"], case["name"]
+        assert present == 1 << 2
