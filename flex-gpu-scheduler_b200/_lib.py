@@ -101,11 +101,13 @@ class Results(C.Structure):
     _fields_ = [
         ("feasible_count", p_i32), ("selected_node", p_i32), ("selected_score", p_i64), ("pod_err", p_u32),
         ("feasible_bitmap", p_u32), ("scores", p_i64), ("words_per_row", C.c_int64), ("score_row_stride", C.c_int64),
+        ("next_start_node_index", C.c_int64), ("processed_nodes", p_i32),
     ]
 
 
 class EvalOpts(C.Structure):
-    _fields_ = [("emit_mask", C.c_uint32), ("emit_raw", C.c_uint32), ("skip_pass_b", C.c_uint32), ("_pad", C.c_uint32)]
+    _fields_ = [("emit_mask", C.c_uint32), ("emit_raw", C.c_uint32), ("skip_pass_b", C.c_uint32), ("sample", C.c_uint32),
+                ("percentage_of_nodes_to_score", C.c_int32), ("_pad", C.c_int32), ("start_node_index", C.c_int64)]
 
 
 class DeviceView(C.Structure):

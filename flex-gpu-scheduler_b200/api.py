@@ -170,6 +170,8 @@ class Results:
         self.selected_node = np.zeros(P, np.int32)
         self.selected_score = np.zeros(P, np.int64)
         self.pod_err = np.zeros(P, np.uint32)
+        self.processed_nodes = np.zeros(max(P, 1), np.int32)[:P]  # node sampling: nodes each pod's walk counted
+        self.next_start_node_index = -1
         self.feasible_bitmap = None
         self.scores = None
         self.words_per_row = 0
@@ -246,6 +248,7 @@ class Engine:
         cr.selected_node = _ptr(r.selected_node, C.c_int32)
         cr.selected_score = _ptr(r.selected_score, C.c_int64)
         cr.pod_err = _ptr(r.pod_err, C.c_uint32)
+        cr.processed_nodes = _ptr(r.processed_nodes, C.c_int32)
         if want_planes:
             n_pad = (max(self.n_nodes, 1) + 1023) // 1024 * 1024  # kNodePad of the engine
             r.feasible_bitmap = np.zeros((P, n_pad // 32), np.uint32)
@@ -255,8 +258,9 @@ class Engine:
         return r, cr
 
     @staticmethod
-    def _opts(emit_mask=0, emit_raw=0, skip_pass_b=0):
-        return L.EvalOpts(emit_mask=emit_mask, emit_raw=emit_raw, skip_pass_b=skip_pass_b)
+    def _opts(emit_mask=0, emit_raw=0, skip_pass_b=0, sample=0, percentage_of_nodes_to_score=0, start_node_index=0):
+        return L.EvalOpts(emit_mask=emit_mask, emit_raw=emit_raw, skip_pass_b=skip_pass_b, sample=1 if sample else 0,
+                          percentage_of_nodes_to_score=percentage_of_nodes_to_score, start_node_index=start_node_index)
 
     def evaluate(self, pod_table, want_planes=False, **opts):
         P = int(pod_table.contents.n_pods)
@@ -265,6 +269,7 @@ class Engine:
         o = self._opts(**opts)
         self._check(self._lib.fgs_evaluate(self._h, pod_table, C.byref(o), C.byref(cr)))
         r.words_per_row, r.score_row_stride = int(cr.words_per_row), int(cr.score_row_stride)
+        r.next_start_node_index = int(cr.next_start_node_index)
         return r
 
     def stage_pods(self, pod_table):
@@ -282,6 +287,7 @@ class Engine:
         r, cr = self._results(self.n_pods, want_planes)
         self._check(self._lib.fgs_fetch_results(self._h, C.byref(cr)))
         r.words_per_row, r.score_row_stride = int(cr.words_per_row), int(cr.score_row_stride)
+        r.next_start_node_index = int(cr.next_start_node_index)
         return r
 
     def device_view(self):

@@ -16,6 +16,7 @@
 #include "engine.h"
 #include "kernels.cuh"
 #include "pack.h"
+#include "sample.cuh"
 
 namespace fgs {
 
@@ -101,6 +102,8 @@ void Engine::free_all() {
     if (d_pn) cudaFree(d_pn);
     if (d_an) cudaFree(d_an);
     if (d_special) cudaFree(d_special);
+    if (d_walk) cudaFree(d_walk);
+    if (h_walk) cudaFreeHost(h_walk);
     if (h_raw) cudaFreeHost(h_raw);
     if (h_pods) cudaFreeHost(h_pods);
     if (h_perpod) cudaFreeHost(h_perpod);
@@ -201,6 +204,7 @@ void Engine::fill_eval_params(EvalParams* p, const fgs_eval_opts* opts) const {
     if (cfg.score_mask & FGS_PL_FIT) max_total += 100 * p->w_fit;
     if (cfg.score_mask & FGS_PL_ALLOCATABLE) max_total += 100 * p->w_alloc;
     p->key_shift = (max_total < ((int64_t)1 << 23) && !p->emit_raw) ? 40 : 24;
+    p->feas_from_bitmap = sampled ? 1 : 0;
     // pods per CTA: enough CTAs for a few waves of 148 SMs × 2 resident CTAs
     const int64_t node_tiles = n_pad / kTileN;
     const int64_t target_ctas = 148 * 2 * 4;
@@ -638,11 +642,56 @@ extern "C" int fgs_stage_pods(fgs_engine* eh, const fgs_pod_table* t) {
     return FGS_OK;
 }
 
+// The reference's node sampling on top of the reduce pass's full bitmap (sample.cu): walk, truncate, re-reduce.
+int Engine::run_sampling(const fgs_eval_opts* opts) {
+    Engine* e = this;
+    if (e->sampled) return FGS_OK;
+    if (e->node_base != 0 || (e->total_nodes != 0 && e->total_nodes != e->n_nodes))
+        return e->fail(FGS_E_STATE, "node sampling needs the whole cluster on one engine (node_index_base 0)");
+    if (e->n_pods == 0 || e->n_nodes == 0) return FGS_OK;
+    if (e->p_pad > e->walk_cap) {
+        if (e->d_walk) cudaFree(e->d_walk);
+        if (e->h_walk) cudaFreeHost(e->h_walk);
+        e->d_walk = e->h_walk = nullptr;
+        e->walk_cap = 0;
+        FGS_CUDA(e, cudaMalloc(&e->d_walk, sizeof(int64_t) * (size_t)(e->p_pad + 1)));
+        FGS_CUDA(e, cudaMallocHost(&e->h_walk, sizeof(int64_t) * (size_t)(e->p_pad + 1)));
+        e->walk_cap = e->p_pad;
+    }
+    SampleParams sp;
+    std::memset(&sp, 0, sizeof(sp));
+    sp.bitmap = (uint32_t*)e->d_bitmap;
+    sp.nd = (const int64_t*)e->d_nd;
+    sp.pods = (const int64_t*)e->d_pods;
+    sp.reduce_max = (int64_t*)e->d_perpod;
+    sp.reduce_sum = (int64_t*)e->d_perpod + (int64_t)FGS_REDUCE_ROWS * e->p_pad;
+    sp.walk = e->d_walk;
+    sp.next_start = (int64_t*)e->d_walk + e->p_pad; // int2 [p_pad] = int64 [p_pad], then the scalar
+    sp.words_per_row = e->words_per_row;
+    sp.n_nodes = e->n_nodes;
+    sp.n_pad = e->n_pad;
+    sp.n_pods = e->n_pods;
+    sp.p_pad = e->p_pad;
+    sp.k = num_feasible_nodes_to_find(e->n_nodes, opts->percentage_of_nodes_to_score);
+    sp.start = opts->start_node_index;
+    FGS_CUDA(e, launch_sampling(sp, e->stream));
+    e->launches += 3;
+    if ((e->cfg.score_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
+        launch_special_pass((const uint32_t*)e->d_bitmap, e->words_per_row, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special,
+                            (const int64_t*)e->d_pods, (int64_t*)e->d_perpod, e->n_pods, e->p_pad, e->stream);
+        e->launches++;
+        FGS_CUDA(e, cudaGetLastError());
+    }
+    e->sampled = true;
+    return FGS_OK;
+}
+
 extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_reduce before fgs_stage_pods");
     cudaSetDevice(e->device);
+    e->sampled = false;
     EvalParams p;
     e->fill_eval_params(&p, nullptr);
     launch_init_perpod((int64_t*)e->d_perpod, e->p_pad, e->stream);
@@ -671,6 +720,10 @@ extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
     Engine* e = (Engine*)eh;
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_emit before fgs_stage_pods");
     cudaSetDevice(e->device);
+    if (opts && opts->sample) { // keep only the nodes the reference's walk would have found
+        const int rc = e->run_sampling(opts);
+        if (rc) return rc;
+    }
     EvalParams p;
     e->fill_eval_params(&p, opts);
     e->last_key_shift = p.key_shift;
@@ -707,8 +760,18 @@ extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
         FGS_CUDA(e, cudaMemcpyAsync(out->feasible_bitmap, e->d_bitmap, sizeof(uint32_t) * P * e->words_per_row, cudaMemcpyDeviceToHost, e->stream));
     if (out->scores && e->emitted)
         FGS_CUDA(e, cudaMemcpyAsync(out->scores, e->d_scores, sizeof(int64_t) * P * e->score_stride, cudaMemcpyDeviceToHost, e->stream));
+    if (e->sampled) // the walks: int2 {start, processed} per pod, then nextStartNodeIndex
+        FGS_CUDA(e, cudaMemcpyAsync(e->h_walk, e->d_walk, sizeof(int64_t) * (size_t)(pp + 1), cudaMemcpyDeviceToHost, e->stream));
     FGS_CUDA(e, cudaEventRecord(e->events[4], e->stream));
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    out->next_start_node_index = -1;
+    if (e->sampled) {
+        out->next_start_node_index = ((const int64_t*)e->h_walk)[pp];
+        if (out->processed_nodes)
+            for (int64_t p = 0; p < P; ++p) out->processed_nodes[p] = ((const int32_t*)e->h_walk)[2 * p + 1];
+    } else if (out->processed_nodes) {
+        for (int64_t p = 0; p < P; ++p) out->processed_nodes[p] = (int32_t)e->n_nodes;
+    }
     const int64_t* h = (const int64_t*)e->h_perpod;
     for (int64_t p = 0; p < P; ++p) { // widths of the caller's arrays differ from the device rows: plain copies
         if (out->feasible_count) out->feasible_count[p] = (int32_t)h[p];
@@ -740,6 +803,9 @@ extern "C" int fgs_evaluate(fgs_engine* eh, const fgs_pod_table* pods, const fgs
     if (rc) return rc;
     if (!(opts && opts->skip_pass_b)) {
         rc = fgs_pass_emit(eh, opts);
+        if (rc) return rc;
+    } else if (opts->sample) { // Filter only, truncated as the reference's walk would
+        rc = e->run_sampling(opts);
         if (rc) return rc;
     }
     return fgs_fetch_results(eh, out);

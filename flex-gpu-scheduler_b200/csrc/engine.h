@@ -68,6 +68,13 @@ struct Engine {
     int decide_narrow(const fgs_pod_table* t);
     void fill_narrow_params(NarrowParams* p) const;
 
+    // node sampling (sample.cu): per-pod walks of the current batch
+    void* d_walk = nullptr;    // int2 [p_pad] + one int64 (nextStartNodeIndex)
+    void* h_walk = nullptr;
+    int64_t walk_cap = 0;
+    bool sampled = false;      // the current batch's bitmap was truncated by the walk
+    int run_sampling(const fgs_eval_opts* opts);
+
     GangState* gang = nullptr;
     SeqState* seq = nullptr;
 

@@ -380,6 +380,10 @@ __global__ void __launch_bounds__(kThreads, 2) eval_kernel(const __grid_constant
                                    (prm.flex_filter_first || fit_ok) && valid;
                 fpanic = fpanic || reach;
                 feas[j] = flex_ok && fit_ok && valid && !reach;
+                if (MODE == MODE_EMIT && prm.feas_from_bitmap) { // node sampling kept a subset of the feasible nodes
+                    const uint32_t word = __ldg(prm.bitmap + p * prm.words_per_row + (node_tile0 >> 5) + warp * kNodesPerThread + j);
+                    feas[j] = feas[j] && ((word >> lane) & 1u);
+                }
             }
 
             if (MODE == MODE_REDUCE) {

@@ -108,6 +108,7 @@ struct EvalParams {
     float fit_inv_wsum;
     uint64_t seed;
     int key_shift;         // bits below the score field of the select key (40, or 24 without hash)
+    int feas_from_bitmap;  // EMIT: AND the recomputed Filter verdict with the bitmap (node sampling truncated it)
 };
 
 // sets the dynamic shared memory limits of the evaluation kernels on the current device

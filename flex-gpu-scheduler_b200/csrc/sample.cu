@@ -1,0 +1,243 @@
+// sample.cu — the reference's node sampling on top of the full feasibility bitmap.
+//
+//   numFeasibleNodesToFind        vendor/k8s.io/kubernetes/pkg/scheduler/generic_scheduler.go:171-191
+//   findNodesThatPassFilters      :266-338 — pod p visits nodes[(nextStartNodeIndex + i) % N], i = 0,1,…, keeps the
+//                                 first K feasible ones, stops at the node that would be the (K+1)-th, and advances
+//                                 nextStartNodeIndex by the nodes it counted (:329-330)
+//
+// With the reference's 16 workers WHICH K nodes are kept is a race (:302-308); this is the walk as ONE worker does
+// it, which is deterministic. The reduce pass has already evaluated Filter on every node, so the walk is a
+// rank/select problem on each pod's bitmap row:
+//   sample_chain        one warp, pods in order (pod p+1 starts where pod p stopped — a true dependency chain):
+//                       popcount prefix over the row, rank of the start position, select of the (K+1)-th set bit
+//                       in rotated order; rows stream through shared memory by TMA bulk copy, 4 stages
+//   sample_truncate     pods × words in parallel: clear the feasible bits outside the walked interval
+//   reduce_from_bitmap  one warp per pod: the maxima NormalizeScore needs, over the KEPT nodes only
+// Score / NormalizeScore / selectHost then run on the kept nodes (the emit pass reads feasibility from the bitmap).
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "kernels.cuh"
+#include "sample.cuh"
+
+namespace fgs {
+namespace {
+
+typedef long long i64;
+typedef unsigned long long u64;
+constexpr i64 kMin64 = (i64)0x8000000000000000ull;
+constexpr int kStages = 4;
+
+__device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(s_u32(bar)), "r"(parity)
+            : "memory");
+    }
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s_u32(dst)),
+                 "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(s_u32(bar))
+                 : "memory");
+}
+
+// ---- the walk: one warp, one pod after the other ------------------------------------------------------------
+__global__ void __launch_bounds__(32, 1) sample_chain(const uint32_t* __restrict__ bitmap, i64 W, i64 n_nodes, i64 n_pods, i64 K, i64 start0,
+                                                      int2* __restrict__ walk, i64* __restrict__ reduce_sum, i64* __restrict__ next_start) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint64_t* bars = (uint64_t*)smem;                // [kStages]
+    uint32_t* rows = (uint32_t*)(smem + 64);         // [kStages][W]
+    const int lane = threadIdx.x;
+    const uint32_t row_bytes = (uint32_t)(W * 4);
+    if (lane == 0) {
+        for (int k = 0; k < kStages; ++k) mbar_init(&bars[k], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    auto issue = [&](i64 p) {
+        const int st = (int)(p % kStages);
+        mbar_expect_tx(&bars[st], row_bytes);
+        bulk_g2s(rows + (size_t)st * W, bitmap + p * W, row_bytes, &bars[st]);
+    };
+    if (lane == 0)
+        for (i64 p = 0; p < kStages - 1 && p < n_pods; ++p) issue(p);
+
+    const int cpl = (int)((W + 31) / 32); // words per lane, consecutive
+    const i64 N = n_nodes;
+    i64 s = ((start0 % N) + N) % N;
+    for (i64 p = 0; p < n_pods; ++p) {
+        const int st = (int)(p % kStages);
+        if (lane == 0 && p + kStages - 1 < n_pods) {
+            // the stage being refilled held row p-1: every lane finished with it before the __syncwarp below
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            issue(p + kStages - 1);
+        }
+        mbar_wait(&bars[st], (uint32_t)((p / kStages) & 1));
+        const uint32_t* row = rows + (size_t)st * W;
+        const i64 w0 = (i64)lane * cpl;
+        const i64 sw = s >> 5;
+        const uint32_t below = (1u << (s & 31)) - 1u; // bits of word sw that lie before s
+        int c = 0, b = 0;
+        for (int k = 0; k < cpl; ++k) {
+            const i64 w = w0 + k;
+            if (w >= W) break;
+            const uint32_t x = row[w];
+            const int pc = __popc(x);
+            c += pc;
+            b += w < sw ? pc : (w == sw ? __popc(x & below) : 0);
+        }
+        // exclusive prefix of the lanes' counts
+        int incl = c;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) incl += v;
+        }
+        const int excl = incl - c;
+        const int T = __shfl_sync(0xffffffffu, incl, 31);
+        const int before = __reduce_add_sync(0xffffffffu, b);
+        const int after = T - before;
+        i64 processed = N, kept = T, nxt = s;
+        if ((i64)T >= K + 1) {
+            // 0-based rank, in row order, of the (K+1)-th feasible node of the rotated walk
+            const int r = (i64)after >= K + 1 ? before + (int)K : (int)K - after;
+            const uint32_t owner = __ballot_sync(0xffffffffu, excl <= r && r < excl + c);
+            const int ol = __ffs(owner) - 1;
+            int pos = -1;
+            if (lane == ol) {
+                int rem = r - excl;
+                for (int k = 0; k < cpl; ++k) {
+                    const uint32_t x = row[w0 + k];
+                    const int pc = __popc(x);
+                    if (rem < pc) {
+                        pos = (int)((w0 + k) * 32) + (int)__fns(x, 0, rem + 1);
+                        break;
+                    }
+                    rem -= pc;
+                }
+            }
+            pos = __shfl_sync(0xffffffffu, pos, ol);
+            processed = ((i64)pos - s + N) % N; // kept + failed; the (K+1)-th itself is dropped
+            kept = K;
+            nxt = pos;
+        }
+        if (lane == 0) {
+            walk[p] = make_int2((int)s, (int)processed);
+            reduce_sum[p] = kept; // len(feasibleNodes)
+        }
+        s = nxt;
+        __syncwarp();
+    }
+    if (lane == 0) *next_start = s;
+}
+
+// ---- clear what the walk did not keep ----------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sample_truncate(uint32_t* __restrict__ bitmap, i64 W, i64 n_nodes, i64 n_pods, const int2* __restrict__ walk) {
+    const i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n_pods * W) return;
+    const i64 p = idx / W, w = idx % W;
+    const int2 wk = walk[p];
+    const i64 s = wk.x, L = wk.y, N = n_nodes;
+    if (L >= N) return; // everything was walked
+    // kept: rotated position (n − s) mod N < L  ⇔  n in [s, s+L) or, wrapped, n in [0, s+L−N)
+    const i64 lo = w * 32;
+    auto range_mask = [&](i64 a, i64 b) -> uint32_t { // bits of this word with a <= n < b
+        i64 x = a > lo ? a - lo : 0, y = b - lo;
+        if (y <= 0 || x >= 32) return 0u;
+        if (y > 32) y = 32;
+        const uint32_t hi_m = y == 32 ? 0xffffffffu : ((1u << y) - 1u);
+        return hi_m & ~((1u << x) - 1u);
+    };
+    uint32_t m = range_mask(s, s + L < N ? s + L : N);
+    if (s + L > N) m |= range_mask(0, s + L - N);
+    const uint32_t x = bitmap[idx];
+    if (x & ~m) bitmap[idx] = x & m;
+}
+
+// ---- NormalizeScore's reductions over the kept nodes ---------------------------------------------------------------
+__global__ void __launch_bounds__(256) reduce_from_bitmap(const uint32_t* __restrict__ bitmap, i64 W, i64 n_pods, i64 p_pad, i64 n_pad,
+                                                          const i64* __restrict__ nd, const i64* __restrict__ pods, i64* __restrict__ reduce_max) {
+    const i64 p = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (p >= n_pods) return;
+    const uint32_t kind = (uint32_t)pods[(i64)PD_META * p_pad + p] & 3u;
+    const i64* sc = nd + (i64)(kind == 1 ? ND_GPU_SCORE : ND_MEM_SCORE) * n_pad;
+    const i64* ar = nd + (i64)ND_ALLOC_RAW * n_pad;
+    i64 vflex = kMin64, vhi = kMin64, vnlo = kMin64;
+    for (i64 w = lane; w < W; w += 32) {
+        uint32_t x = bitmap[p * W + w];
+        while (x) {
+            const int bit = __ffs(x) - 1;
+            x &= x - 1;
+            const i64 n = w * 32 + bit;
+            const i64 s = (kind == 1 || kind == 2) ? sc[n] : 0; // FlexGPU.Score, flex_gpu.go:150-165
+            const i64 a = ar[n];
+            vflex = s > vflex ? s : vflex;
+            vhi = a > vhi ? a : vhi;
+            vnlo = -a > vnlo ? -a : vnlo;
+        }
+    }
+    auto wmax = [&](i64 v) {
+        const int hi = (int)(v >> 32);
+        const int mhi = __reduce_max_sync(0xffffffffu, hi);
+        const uint32_t mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? (uint32_t)v : 0u);
+        return (i64)(((u64)(uint32_t)mhi << 32) | mlo);
+    };
+    vflex = wmax(vflex);
+    vhi = wmax(vhi);
+    vnlo = wmax(vnlo);
+    if (lane == 0) {
+        reduce_max[(i64)RR_FLEX_MAX * p_pad + p] = vflex;
+        reduce_max[(i64)RR_ALLOC_HI * p_pad + p] = vhi;
+        reduce_max[(i64)RR_ALLOC_NEGLO * p_pad + p] = vnlo;
+        reduce_max[(i64)RR_NEG_MAG * p_pad + p] = 0;     // rewritten by special_pass over the kept nodes
+        reduce_max[(i64)RR_SCORE_PANIC * p_pad + p] = 0;
+    }
+}
+
+} // namespace
+
+int64_t num_feasible_nodes_to_find(int64_t n_nodes, int32_t percentage) {
+    // generic_scheduler.go:43-53,171-191; int32 arithmetic as in Go
+    const int32_t n = (int32_t)n_nodes;
+    if (n < 100 || percentage >= 100) return n;
+    int32_t adaptive = percentage;
+    if (adaptive <= 0) {
+        adaptive = 50 - n / 125;
+        if (adaptive < 5) adaptive = 5;
+    }
+    const int32_t k = n * adaptive / 100;
+    return k < 100 ? 100 : k;
+}
+
+cudaError_t launch_sampling(const SampleParams& sp, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (sp.n_pods <= 0 || sp.n_nodes <= 0) return cudaSuccess;
+    const size_t smem = 64 + (size_t)kStages * (size_t)sp.words_per_row * 4;
+    cudaError_t ce = cudaFuncSetAttribute(sample_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (ce != cudaSuccess) return ce;
+    sample_chain<<<1, 32, smem, stream>>>(sp.bitmap, sp.words_per_row, sp.n_nodes, sp.n_pods, sp.k, sp.start, (int2*)sp.walk, (i64*)sp.reduce_sum,
+                                           (i64*)sp.next_start);
+    const i64 total = sp.n_pods * sp.words_per_row;
+    sample_truncate<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(sp.bitmap, sp.words_per_row, sp.n_nodes, sp.n_pods, (const int2*)sp.walk);
+    reduce_from_bitmap<<<(unsigned)((sp.n_pods * 32 + 255) / 256), 256, 0, stream>>>(sp.bitmap, sp.words_per_row, sp.n_pods, sp.p_pad, sp.n_pad,
+                                                                                    (const i64*)sp.nd, (const i64*)sp.pods, (i64*)sp.reduce_max);
+    return cudaGetLastError();
+}
+
+} // namespace fgs

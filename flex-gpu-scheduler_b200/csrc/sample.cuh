@@ -1,0 +1,26 @@
+// sample.cuh — launch parameters of the node-sampling stage (sample.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+namespace fgs {
+
+struct SampleParams {
+    uint32_t* bitmap;        // [P][words_per_row], truncated in place
+    const int64_t* nd;       // derived node table
+    const int64_t* pods;     // device pod table
+    int64_t* reduce_max;     // [FGS_REDUCE_ROWS][p_pad]
+    int64_t* reduce_sum;     // [p_pad] ← len(feasibleNodes) after the walk
+    void* walk;              // int2 [P]: {start index, processed nodes} of every pod's walk
+    int64_t* next_start;     // device scalar: nextStartNodeIndex after the last pod
+    int64_t words_per_row, n_nodes, n_pad, n_pods, p_pad;
+    int64_t k;               // numFeasibleNodesToFind
+    int64_t start;           // nextStartNodeIndex before the first pod
+};
+
+int64_t num_feasible_nodes_to_find(int64_t n_nodes, int32_t percentage);
+// sample_chain + sample_truncate + reduce_from_bitmap (3 launches)
+cudaError_t launch_sampling(const SampleParams& p, void* stream);
+
+} // namespace fgs

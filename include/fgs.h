@@ -61,6 +61,10 @@ typedef struct fgs_results {
     int64_t* scores;           /* [P][score_row_stride] total weighted score per node */
     int64_t words_per_row;     /* filled in by the engine */
     int64_t score_row_stride;  /* filled in by the engine */
+    /* node sampling (fgs_eval_opts.sample): g.nextStartNodeIndex after the last pod, and per pod the nodes its
+     * walk counted (optional, [P]); without sampling next_start_node_index is -1 */
+    int64_t next_start_node_index;
+    int32_t* processed_nodes;
 } fgs_results;
 
 typedef struct fgs_eval_opts {
@@ -69,7 +73,16 @@ typedef struct fgs_eval_opts {
                              answers) */
     uint32_t emit_raw;    /* 1: emit the plugin's raw Score instead of the normalised×weight value */
     uint32_t skip_pass_b; /* 1: Filter only (bitmap + counts come from the reduce pass) */
-    uint32_t _pad;
+    /* 1: the reference's node sampling (findNodesThatPassFilters, sched/generic_scheduler.go:266-338, as ONE
+     * worker runs it — with 16 workers which nodes are found is a race, :302-308): pod p walks
+     * nodes[(start + i) % N], keeps the first K = numFeasibleNodesToFind(N) feasible nodes (:171-191), stops at
+     * the node that would be the (K+1)-th and moves `start` on by the nodes it counted (:329-330); the next pod
+     * of the batch starts there. Bitmap, counts, NormalizeScore and selectHost then cover the kept nodes only.
+     * 0 (default): every node is evaluated for every pod (percentageOfNodesToScore = 100). Single engine only. */
+    uint32_t sample;
+    int32_t percentage_of_nodes_to_score; /* with sample: KubeSchedulerConfiguration's field; 0 = adaptive */
+    int32_t _pad;
+    int64_t start_node_index;             /* with sample: g.nextStartNodeIndex before the first pod */
 } fgs_eval_opts;
 
 /* device-side buffers of the current batch, for callers that keep results in HBM or that run

@@ -55,6 +55,19 @@ int fgs_oracle_evaluate(const fgs_snapshot* snap, const fgs_podset* pending,
                         const fgs_plugin_cfg* cfg, int64_t p0, int64_t p1, int workers,
                         fgs_oracle_out* out);
 
+/* numFeasibleNodesToFind (generic_scheduler.go:171-191): percentage 0 = adaptive, >= 100 = all nodes. */
+int32_t fgs_oracle_num_feasible_nodes_to_find(int32_t numAllNodes, int32_t percentageOfNodesToScore);
+
+/* fgs_oracle_evaluate with the reference's node sampling as it runs with ONE worker (findNodesThatPassFilters,
+ * generic_scheduler.go:266-338): pod p visits nodes[(start+i) % N], i = 0,1,…, keeps the first
+ * K = numFeasibleNodesToFind(N) feasible ones and stops at the node that would be the (K+1)-th; then
+ * start = (start + processed) % N with processed = kept + failed (:329-330). *start_index carries
+ * g.nextStartNodeIndex in and out; processed[p - p0] may be NULL. status of a node the walk did not reach (or
+ * reached last and dropped) is 0xEE. Scores / NormalizeScore / selectHost run on the kept nodes only. */
+int fgs_oracle_evaluate_sampled(const fgs_snapshot* snap, const fgs_podset* pending,
+                                const fgs_plugin_cfg* cfg, int64_t p0, int64_t p1, int percentage,
+                                int64_t* start_index, int32_t* processed, fgs_oracle_out* out);
+
 /* FlexGPU.Reserve's device choice (flex_gpu.go:178-223) for pod p on node n:
  * returns the index written into the annotation, -1 when no index fits (Unschedulable),
  * -2 when the pod has neither limit (nothing to reserve), -3 both limits, -4 reference panic. */

@@ -59,6 +59,11 @@ def load():
     lib.fgs_oracle_quota_prefilter.restype = C.c_int
     lib.fgs_oracle_quota_prefilter.argtypes = [C.POINTER(L.Podset), C.POINTER(L.Quotas), C.POINTER(L.Podset), L.p_i64, L.p_i64, C.c_int64,
                                                C.c_int64, L.p_u8]
+    lib.fgs_oracle_num_feasible_nodes_to_find.restype = C.c_int32
+    lib.fgs_oracle_num_feasible_nodes_to_find.argtypes = [C.c_int32, C.c_int32]
+    lib.fgs_oracle_evaluate_sampled.restype = C.c_int
+    lib.fgs_oracle_evaluate_sampled.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64, C.c_int64,
+                                                C.c_int, C.POINTER(C.c_int64), L.p_i32, C.POINTER(OracleOut)]
     lib.fgs_oracle_quota_reserve.restype = C.c_int
     lib.fgs_oracle_quota_reserve.argtypes = [C.POINTER(L.Podset), C.c_int64, C.c_int, L.p_i64, L.p_u32]
     _lib = lib
@@ -69,8 +74,14 @@ class EvalResult:
     pass
 
 
-def evaluate(snapshot, pending, cfg, p0=0, p1=None, workers=1, planes=("status", "total"), per_plugin=False):
-    """Run the oracle on pods [p0,p1). Returns numpy arrays; planes are [p1-p0][N]."""
+def num_feasible_nodes_to_find(n_nodes, percentage=0):
+    return int(load().fgs_oracle_num_feasible_nodes_to_find(n_nodes, percentage))
+
+
+def evaluate(snapshot, pending, cfg, p0=0, p1=None, workers=1, planes=("status", "total"), per_plugin=False, sample=None):
+    """Run the oracle on pods [p0,p1). Returns numpy arrays; planes are [p1-p0][N].
+    sample=(percentage, start_index): the reference's node sampling at one worker; adds r.processed [P] and
+    r.next_start (status 0xEE = node not visited)."""
     lib = load()
     N = int(snapshot.contents.n_nodes)
     if p1 is None:
@@ -96,7 +107,15 @@ def evaluate(snapshot, pending, cfg, p0=0, p1=None, workers=1, planes=("status",
     out.max_total = r.max_total.ctypes.data_as(L.p_i64)
     out.tie_count = r.tie_count.ctypes.data_as(L.p_i32)
     out.first_max = r.first_max.ctypes.data_as(L.p_i32)
-    rc = lib.fgs_oracle_evaluate(snapshot, pending, C.byref(cfg), p0, p1, workers, C.byref(out))
+    if sample is not None:
+        start = C.c_int64(int(sample[1]))
+        r.processed = np.zeros(max(P, 1), np.int32)
+        rc = lib.fgs_oracle_evaluate_sampled(snapshot, pending, C.byref(cfg), p0, p1, int(sample[0]), C.byref(start),
+                                             r.processed.ctypes.data_as(L.p_i32), C.byref(out))
+        r.processed = r.processed[:P]
+        r.next_start = int(start.value)
+    else:
+        rc = lib.fgs_oracle_evaluate(snapshot, pending, C.byref(cfg), p0, p1, workers, C.byref(out))
     if rc != 0:
         raise RuntimeError(f"fgs_oracle_evaluate rc={rc}")
     return r

@@ -518,9 +518,55 @@ class Pool {
 
 // =============================================================================================
 
+// numFeasibleNodesToFind — vendor/k8s.io/kubernetes/pkg/scheduler/generic_scheduler.go:171-191
+// (minFeasibleNodesToFind = 100, minFeasibleNodesPercentageToFind = 5, :43-53); int32 arithmetic as in Go.
+extern "C" int32_t fgs_oracle_num_feasible_nodes_to_find(int32_t numAllNodes, int32_t percentageOfNodesToScore) {
+    const int32_t minFeasibleNodesToFind = 100, minFeasibleNodesPercentageToFind = 5;
+    if (numAllNodes < minFeasibleNodesToFind || percentageOfNodesToScore >= 100) return numAllNodes;
+    int32_t adaptivePercentage = percentageOfNodesToScore;
+    if (adaptivePercentage <= 0) {
+        const int32_t basePercentageOfNodesToScore = 50;
+        adaptivePercentage = basePercentageOfNodesToScore - numAllNodes / 125;
+        if (adaptivePercentage < minFeasibleNodesPercentageToFind) adaptivePercentage = minFeasibleNodesPercentageToFind;
+    }
+    const int32_t numNodes = numAllNodes * adaptivePercentage / 100;
+    if (numNodes < minFeasibleNodesToFind) return minFeasibleNodesToFind;
+    return numNodes;
+}
+
+namespace {
+// sampling state of one evaluation call (percentage < 0: every node is evaluated)
+struct Sampling {
+    int percentage = -1;
+    int64_t* start = nullptr;   // g.nextStartNodeIndex, advanced per pod
+    int32_t* processed = nullptr;
+};
+int evaluateImpl(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg, int64_t p0,
+                 int64_t p1, int workers, fgs_oracle_out* out, const Sampling& smp);
+} // namespace
+
 extern "C" int fgs_oracle_evaluate(const fgs_snapshot* snap, const fgs_podset* pending,
                                    const fgs_plugin_cfg* cfg, int64_t p0, int64_t p1, int workers,
                                    fgs_oracle_out* out) {
+    return evaluateImpl(snap, pending, cfg, p0, p1, workers, out, Sampling());
+}
+
+// findNodesThatPassFilters with the reference's node sampling, as it runs with ONE worker
+// (generic_scheduler.go:266-338; with 16 workers which nodes are found is racy, :302-308)
+extern "C" int fgs_oracle_evaluate_sampled(const fgs_snapshot* snap, const fgs_podset* pending,
+                                           const fgs_plugin_cfg* cfg, int64_t p0, int64_t p1, int percentage,
+                                           int64_t* start_index, int32_t* processed, fgs_oracle_out* out) {
+    if (!start_index || percentage < 0) return -1;
+    Sampling smp;
+    smp.percentage = percentage;
+    smp.start = start_index;
+    smp.processed = processed;
+    return evaluateImpl(snap, pending, cfg, p0, p1, 1, out, smp);
+}
+
+namespace {
+int evaluateImpl(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg, int64_t p0,
+                 int64_t p1, int workers, fgs_oracle_out* out, const Sampling& smp) {
     Snap sn(snap);
     const i64 N = snap->n_nodes;
     if (workers < 1) workers = 1;
@@ -579,7 +625,34 @@ extern "C" int fgs_oracle_evaluate(const fgs_snapshot* snap, const fgs_podset* p
             }
             status[(size_t)n] = st;
         };
-        pool.until((int)N, checkNode);
+        if (smp.percentage < 0) {
+            pool.until((int)N, checkNode);
+        } else if (N > 0) {
+            // one worker: nodes[(nextStartNodeIndex+i) % len] for i = 0,1,…; the (K+1)-th success cancels the walk
+            // and is itself dropped (:296-308); processedNodes = len(feasible) + len(NodeToStatusMap) (:329-330)
+            const i64 K = fgs_oracle_num_feasible_nodes_to_find((int32_t)N, smp.percentage);
+            const i64 start = ((*smp.start % N) + N) % N;
+            std::fill(status.begin(), status.end(), (uint8_t)0xEE); // not visited
+            std::fill(panicked.begin(), panicked.end(), (uint8_t)0);
+            i64 found = 0, failed = 0;
+            for (i64 i = 0; i < N; ++i) {
+                const i64 n = (start + i) % N;
+                checkNode((int)n);
+                if (panicked[(size_t)n]) break; // status.Code() == Error: SendErrorWithCancel (:290-293)
+                if (status[(size_t)n] == FGS_CODE_SUCCESS) {
+                    if (found + 1 > K) {
+                        status[(size_t)n] = 0xEE; // found but not kept: neither feasible nor in the status map
+                        break;
+                    }
+                    found++;
+                } else {
+                    failed++;
+                }
+            }
+            const i64 proc = found + failed;
+            if (smp.processed) smp.processed[row] = (int32_t)proc;
+            *smp.start = (start + proc) % N;
+        }
 
         feasible.clear();
         for (i64 n = 0; n < N; ++n) {
@@ -667,6 +740,7 @@ extern "C" int fgs_oracle_evaluate(const fgs_snapshot* snap, const fgs_podset* p
     }
     return 0;
 }
+} // namespace
 
 // FlexGPU.Reserve — pkg/flexgpu/flex_gpu.go:178-223
 extern "C" int fgs_oracle_reserve_index(const fgs_snapshot* snap, const fgs_podset* pending, int64_t p,

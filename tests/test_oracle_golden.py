@@ -83,3 +83,14 @@ def test_quota_reserve_golden(oracle):
         got = {"cpu": int(used[0]), "memory": int(used[1]), "scalar:2": int(used[2 + 2])}
         assert got == case["expected"], case["name"]
         assert present == 1 << 2
+
+
+def test_num_feasible_nodes_to_find(oracle):
+    """numFeasibleNodesToFind (vendor/k8s.io/kubernetes/pkg/scheduler/generic_scheduler.go:171-191). The vendored
+    tree carries no _test.go files; these are the cases of upstream's TestNumFeasibleNodesToFind (kubernetes
+    v1.22 pkg/scheduler/generic_scheduler_test.go) plus the K of the five BASELINE configs."""
+    cases = [(10, 0, 10), (10, 40, 10), (1000, 0, 420), (1000, 40, 400), (6000, 0, 300), (6000, 40, 2400),
+             (1000, 0, 420), (5000, 0, 500), (10000, 0, 500), (20000, 0, 1000), (50000, 0, 2500), (99, 10, 99), (5000, 100, 5000),
+             (150, 10, 100)]
+    for n, pct, want in cases:
+        assert oracle.num_feasible_nodes_to_find(n, pct) == want, (n, pct)
