@@ -170,6 +170,7 @@ ABI = {
     "fgs_get_device_view": (C.c_int, [C.c_void_p, C.POINTER(DeviceView)]),
     "fgs_synchronize": (C.c_int, [C.c_void_p]),
     "fgs_status_plane": (C.c_int, [C.c_void_p, C.c_uint32, p_u8]),
+    "fgs_reason_plane": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint16)]),
     "fgs_schedule_sequential": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(SeqOpts), C.POINTER(SeqResults)]),
     "fgs_reserve": (C.c_int, [C.c_void_p, C.POINTER(PodTable), p_i32, p_i32]),
     "fgs_gang_check": (C.c_int, [C.c_void_p, C.POINTER(Snapshot), C.POINTER(Podset), C.POINTER(Podgroups), p_u8, p_u8, p_i32]),

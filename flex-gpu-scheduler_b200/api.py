@@ -303,6 +303,12 @@ class Engine:
         self._check(self._lib.fgs_status_plane(self._h, plugin, _ptr(out, C.c_uint8)))
         return out
 
+    def reason_plane(self, plugin):
+        """uint16 [P][N]: FGS_FLEX_REASON_* ids (plugin FlexGPU) or FGS_FIT_REASON_* bit masks (plugin Fit)."""
+        out = np.zeros((self.n_pods, self.n_nodes), np.uint16)
+        self._check(self._lib.fgs_reason_plane(self._h, plugin, _ptr(out, C.c_uint16)))
+        return out
+
     def timings(self):
         t = L.Timings()
         self._check(self._lib.fgs_get_timings(self._h, C.byref(t)))

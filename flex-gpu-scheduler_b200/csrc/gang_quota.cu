@@ -397,6 +397,10 @@ struct StatusParams {
     uint32_t filter_mask, fit_ignored;
     int flex_filter_first;
     uint8_t* out; // [P][n_nodes]
+    // reason plane only
+    const i64* raw;
+    int D;
+    uint16_t* out16;
 };
 
 __device__ __forceinline__ uint8_t flex_code(const StatusParams& prm, i64 p, i64 n, bool* panic) {
@@ -472,12 +476,104 @@ __global__ void __launch_bounds__(256) status_plane(const __grid_constant__ Stat
     prm.out[p * prm.n_nodes + n] = out;
 }
 
+// WHY a plugin rejected the node — what the reference puts into the Status message (NodeToStatusMap,
+// generic_scheduler.go:309-313): FlexGPU's five messages (flex_gpu.go:60,67,73,92,97,114) as FGS_FLEX_REASON_*, and
+// Fit's list of InsufficientResource entries (fit.go:256-329: every failing dimension is reported) as a bit mask.
+__global__ void __launch_bounds__(256) reason_plane(const __grid_constant__ StatusParams prm) {
+    const i64 n = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const i64 p = blockIdx.y;
+    if (n >= prm.n_nodes || p >= prm.n_pods) return;
+    auto P = [&](int c) { return prm.pods[(i64)c * prm.p_pad + p]; };
+    auto N = [&](int c) { return prm.nd[(i64)c * prm.n_pad + n]; };
+    auto R = [&](int c) { return prm.raw[(i64)c * prm.n_pad + n]; };
+    const u64 meta = (u64)P(PD_META);
+    const uint32_t pf = (uint32_t)meta, kind = pf & 3u;
+    const uint32_t fl = (uint32_t)N(ND_FLAGS);
+    uint16_t out = 0;
+    if (prm.plugin == FGS_PL_FLEXGPU) {
+        const int S = prm.S;
+        if (kind == 0) out = FGS_FLEX_REASON_NONE;
+        else if (kind == 3) out = FGS_FLEX_REASON_CONFLICT;
+        else if (!(fl & FGS_NF_HAS_FLEX)) out = FGS_FLEX_REASON_UNKNOWN_RESOURCE;
+        else {
+            const i64 gl = kind == 1 ? P(PD_GPU_LIM) : 0, ml = kind == 2 ? P(PD_MEM_LIM) : 0;
+            const i64 gpu_head = R(nr_alloc_scalar(FGS_SCALAR_FLEX_GPU)) - R(NR_FLEX_GPU_SUM);
+            const i64 mem_head = R(nr_alloc_scalar(FGS_SCALAR_FLEX_MEM)) - R(NR_FLEX_MEM_SUM);
+            if (gl > gpu_head) out = FGS_FLEX_REASON_INSUFFICIENT_GPU;       // :90-93
+            else if (ml > mem_head) out = FGS_FLEX_REASON_INSUFFICIENT_MEM;  // :95-98
+            else if (fl & FGS_NF_REF_PANIC) out = FGS_FLEX_REASON_PANIC;     // NewGPUNode, :101
+            else if (kind == 2) {                                            // MemAssumeFitIndexes empty, :109-116
+                const i64 each = N(ND_MEM_EACH), cnt = R(nr_alloc_scalar(FGS_SCALAR_FLEX_GPU));
+                const uint32_t mono = (uint32_t)((u64)R(NR_META) >> 32);
+                bool fits = false;
+                for (int d = 0; d < prm.D && (i64)d < cnt; ++d)
+                    if (!((mono >> d) & 1u) && each >= R(nr_used(S, d)) + ml) fits = true;
+                if (!fits) out = FGS_FLEX_REASON_NO_FIT_INDEX;
+            }
+        }
+    } else {
+        if (!(fl & NDF_PODS_OK)) out |= FGS_FIT_REASON_PODS; // "Too many pods", fit.go:259-268
+        if (!(pf & FGS_PF_REQ_NONE)) {
+            if (P(PD_REQ_CPU) > N(ND_FREE_CPU)) out |= FGS_FIT_REASON_CPU;
+            if (P(PD_REQ_MEM) > N(ND_FREE_MEM)) out |= FGS_FIT_REASON_MEM;
+            if (P(PD_REQ_EPH) > N(ND_FREE_EPH)) out |= FGS_FIT_REASON_EPH;
+            uint32_t m = (uint32_t)(meta >> 32) & ~prm.fit_ignored;
+            while (m) {
+                const int s = __ffs(m) - 1;
+                m &= m - 1;
+                if (P(PD_FIXED_COLS + s) > N(nd_free_scalar(s))) out |= (uint16_t)(FGS_FIT_REASON_SCALAR0 << s);
+            }
+        }
+    }
+    prm.out16[p * prm.n_nodes + n] = out;
+}
+
 } // namespace
 } // namespace fgs
 
 using namespace fgs;
 
 // =================================================================================================
+
+extern "C" int fgs_reason_plane(fgs_engine* eh, uint32_t plugin, uint16_t* out) {
+    if (!eh || !out) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_reason_plane before an evaluation");
+    if (plugin != FGS_PL_FLEXGPU && plugin != FGS_PL_FIT) return e->fail(FGS_E_INVALID, "fgs_reason_plane: plugin must be FlexGPU or Fit");
+    cudaSetDevice(e->device);
+    const size_t cells = (size_t)e->n_pods * (size_t)e->n_nodes;
+    if (cells == 0) return FGS_OK;
+    uint16_t* d = nullptr;
+    FGS_CUDA(e, cudaMalloc(&d, cells * sizeof(uint16_t)));
+    StatusParams sp;
+    std::memset(&sp, 0, sizeof(sp));
+    sp.nd = (const i64*)e->d_nd;
+    sp.raw = (const i64*)e->d_raw;
+    sp.pods = (const i64*)e->d_pods;
+    sp.n_nodes = e->n_nodes;
+    sp.n_pad = e->n_pad;
+    sp.p_pad = e->p_pad;
+    sp.S = e->S;
+    sp.D = e->D;
+    sp.plugin = plugin;
+    sp.fit_ignored = e->cfg.fit_ignored_scalar_mask;
+    for (int64_t p0 = 0; p0 < e->n_pods; p0 += 32768) { // grid.y is limited to 65535
+        StatusParams s2 = sp;
+        const int64_t cnt = std::min<int64_t>(32768, e->n_pods - p0);
+        s2.pods = sp.pods + p0;
+        s2.n_pods = cnt;
+        s2.out16 = d + p0 * e->n_nodes;
+        dim3 grid((unsigned)((e->n_nodes + 255) / 256), (unsigned)cnt);
+        reason_plane<<<grid, 256, 0, e->stream>>>(s2);
+        e->launches++;
+    }
+    cudaError_t ce = cudaGetLastError();
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(out, d, cells * sizeof(uint16_t), cudaMemcpyDeviceToHost, e->stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->stream);
+    cudaFree(d);
+    if (ce != cudaSuccess) return e->fail(FGS_E_CUDA, std::string("fgs_reason_plane: ") + cudaGetErrorString(ce));
+    return FGS_OK;
+}
 
 extern "C" int fgs_status_plane(fgs_engine* eh, uint32_t plugin, uint8_t* out) {
     if (!eh || !out) return FGS_E_INVALID;

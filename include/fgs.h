@@ -180,6 +180,12 @@ int fgs_synchronize(fgs_engine* e);
  * diagnosis plane the Go Filter methods answer from (NodeToStatusMap, generic_scheduler.go:309-313). */
 int fgs_status_plane(fgs_engine* e, uint32_t plugin, uint8_t* out);
 
+/* The REASON behind each non-success verdict of the last staged batch, out[P][n_nodes] — what the reference
+ * writes into the Status message that ends up in the pod's FitError / events (sched/framework/types.go:221-250):
+ *   plugin == FGS_PL_FLEXGPU  one of FGS_FLEX_REASON_* (FlexGPU.Filter returns at its first failing step)
+ *   plugin == FGS_PL_FIT      OR of FGS_FIT_REASON_* (fitsRequest reports every insufficient resource) */
+int fgs_reason_plane(fgs_engine* e, uint32_t plugin, uint16_t* out);
+
 /* ---- sequential scheduling cycles: assume + Reserve between pods ---------------------------- */
 
 /* device_index values that are not an index (FlexGPU.Reserve, pkg/flexgpu/flex_gpu.go:178-223) */

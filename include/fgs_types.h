@@ -68,6 +68,21 @@ extern "C" {
 #define FGS_PODERR_SCORE_RANGE 1u /* a normalised score left [0,100]: runtime/framework.go:920-923 */
 #define FGS_PODERR_REF_PANIC 2u   /* the reference would panic here (gpu_node.go:40-58,109,115) */
 
+/* fgs_reason_plane: why FlexGPU.Filter rejected the node = which of its messages the Status carries */
+#define FGS_FLEX_REASON_NONE 0
+#define FGS_FLEX_REASON_CONFLICT 1         /* "pod conflict resources"                         flex_gpu.go:60 */
+#define FGS_FLEX_REASON_UNKNOWN_RESOURCE 2 /* "unknown resource type"                          :67,73 */
+#define FGS_FLEX_REASON_INSUFFICIENT_GPU 3 /* "insufficient resource nvidia.flex.com/gpu"      :92 */
+#define FGS_FLEX_REASON_INSUFFICIENT_MEM 4 /* "insufficient resource nvidia.flex.com/memory"   :97 */
+#define FGS_FLEX_REASON_NO_FIT_INDEX 5     /* "no fit indexes resource nvidia.flex.com/memory" :114 */
+#define FGS_FLEX_REASON_PANIC 0xF1         /* NewGPUNode panics on the node (gpu_node.go:40-58,109,115) */
+/* … and Fit.Filter's InsufficientResource list as bits (fit.go:256-329; every failing dimension is listed) */
+#define FGS_FIT_REASON_PODS 1u     /* "Too many pods" */
+#define FGS_FIT_REASON_CPU 2u      /* "Insufficient cpu" */
+#define FGS_FIT_REASON_MEM 4u      /* "Insufficient memory" */
+#define FGS_FIT_REASON_EPH 8u      /* "Insufficient ephemeral-storage" */
+#define FGS_FIT_REASON_SCALAR0 16u /* << s: "Insufficient <scalar resource s>" */
+
 /* ---------------------------------------------------------------- object level ---------- */
 
 typedef struct fgs_podset {

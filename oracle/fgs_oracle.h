@@ -55,6 +55,12 @@ int fgs_oracle_evaluate(const fgs_snapshot* snap, const fgs_podset* pending,
                         const fgs_plugin_cfg* cfg, int64_t p0, int64_t p1, int workers,
                         fgs_oracle_out* out);
 
+/* The reason inside each plugin's Filter status of pod p, per node: flex[n] = FGS_FLEX_REASON_* (the message
+ * FlexGPU.Filter returns, flex_gpu.go:60-114), fit[n] = FGS_FIT_REASON_* bits (fitsRequest's InsufficientResource
+ * list, fit.go:256-329). Either may be NULL. */
+int fgs_oracle_filter_reasons(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg,
+                              int64_t p, uint16_t* flex, uint16_t* fit);
+
 /* numFeasibleNodesToFind (generic_scheduler.go:171-191): percentage 0 = adaptive, >= 100 = all nodes. */
 int32_t fgs_oracle_num_feasible_nodes_to_find(int32_t numAllNodes, int32_t percentageOfNodesToScore);
 

@@ -64,6 +64,9 @@ def load():
     lib.fgs_oracle_evaluate_sampled.restype = C.c_int
     lib.fgs_oracle_evaluate_sampled.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64, C.c_int64,
                                                 C.c_int, C.POINTER(C.c_int64), L.p_i32, C.POINTER(OracleOut)]
+    lib.fgs_oracle_filter_reasons.restype = C.c_int
+    lib.fgs_oracle_filter_reasons.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64,
+                                              C.POINTER(C.c_uint16), C.POINTER(C.c_uint16)]
     lib.fgs_oracle_quota_reserve.restype = C.c_int
     lib.fgs_oracle_quota_reserve.argtypes = [C.POINTER(L.Podset), C.c_int64, C.c_int, L.p_i64, L.p_u32]
     _lib = lib
@@ -167,3 +170,12 @@ def quota_reserve(pods, p, used_row, used_present, op=1):
     up = np.array([used_present], np.uint32)
     load().fgs_oracle_quota_reserve(pods, p, op, used_row.ctypes.data_as(L.p_i64), up.ctypes.data_as(L.p_u32))
     return int(up[0])
+
+
+def filter_reasons(snapshot, pending, cfg, p):
+    """(flex reason ids [N], fit reason bit masks [N]) of pod p"""
+    N = int(snapshot.contents.n_nodes)
+    flex, fit = np.zeros(max(N, 1), np.uint16), np.zeros(max(N, 1), np.uint16)
+    load().fgs_oracle_filter_reasons(snapshot, pending, C.byref(cfg), p, flex.ctypes.data_as(C.POINTER(C.c_uint16)),
+                                     fit.ctypes.data_as(C.POINTER(C.c_uint16)))
+    return flex[:N], fit[:N]

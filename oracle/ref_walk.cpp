@@ -293,23 +293,27 @@ struct PodCtx {
 };
 
 // FlexGPU.Filter — pkg/flexgpu/flex_gpu.go:41-119. Returns a framework.Code.
-int flexFilter(const Snap& sn, const PodCtx& pc, i64 n) {
+// reason (optional): which of FlexGPU.Filter's messages the Status carries (FGS_FLEX_REASON_*)
+int flexFilter(const Snap& sn, const PodCtx& pc, i64 n, int* reason = nullptr) {
+    int dummy;
+    if (!reason) reason = &dummy;
+    *reason = FGS_FLEX_REASON_NONE;
     bool gpuExist, memExist;
     i64 gpuLimit = podResourceLimit(pc.ps, pc.i, FGS_SCALAR_FLEX_GPU, gpuExist); // :52
     i64 memLimit = podResourceLimit(pc.ps, pc.i, FGS_SCALAR_FLEX_MEM, memExist); // :53
     if (!gpuExist && !memExist) return FGS_CODE_SUCCESS;                         // :54-56
-    if (gpuExist && memExist) return FGS_CODE_UNRESOLVABLE;                      // :58-61
-    if (!sn.allocHasScalar(n, FGS_SCALAR_FLEX_GPU)) return FGS_CODE_UNRESOLVABLE; // :64-68
-    if (!sn.allocHasScalar(n, FGS_SCALAR_FLEX_MEM)) return FGS_CODE_UNRESOLVABLE; // :70-74
+    if (gpuExist && memExist) return *reason = FGS_FLEX_REASON_CONFLICT, FGS_CODE_UNRESOLVABLE; // :58-61
+    if (!sn.allocHasScalar(n, FGS_SCALAR_FLEX_GPU)) return *reason = FGS_FLEX_REASON_UNKNOWN_RESOURCE, FGS_CODE_UNRESOLVABLE; // :64-68
+    if (!sn.allocHasScalar(n, FGS_SCALAR_FLEX_MEM)) return *reason = FGS_FLEX_REASON_UNKNOWN_RESOURCE, FGS_CODE_UNRESOLVABLE; // :70-74
     i64 gpuAllocatable = sn.alloc(n)[4 + FGS_SCALAR_FLEX_GPU];
     i64 memAllocatable = sn.alloc(n)[4 + FGS_SCALAR_FLEX_MEM];
     i64 gpuAssume = wadd(nodeResourceLimitSum(sn, n, FGS_SCALAR_FLEX_GPU), gpuLimit); // :82-87
     i64 memAssume = wadd(nodeResourceLimitSum(sn, n, FGS_SCALAR_FLEX_MEM), memLimit);
-    if (gpuAssume > gpuAllocatable) return FGS_CODE_UNSCHEDULABLE; // :90-93
-    if (memAssume > memAllocatable) return FGS_CODE_UNSCHEDULABLE; // :95-98
+    if (gpuAssume > gpuAllocatable) return *reason = FGS_FLEX_REASON_INSUFFICIENT_GPU, FGS_CODE_UNSCHEDULABLE; // :90-93
+    if (memAssume > memAllocatable) return *reason = FGS_FLEX_REASON_INSUFFICIENT_MEM, FGS_CODE_UNSCHEDULABLE; // :95-98
     GpuNode no = newGPUNode(sn, n);                                // :101 (may panic)
     if (memExist) {                                                // :109-116
-        if (memAssumeFitIndexes(no, memLimit).empty()) return FGS_CODE_UNSCHEDULABLE;
+        if (memAssumeFitIndexes(no, memLimit).empty()) return *reason = FGS_FLEX_REASON_NO_FIT_INDEX, FGS_CODE_UNSCHEDULABLE;
     }
     return FGS_CODE_SUCCESS;
 }
@@ -326,21 +330,25 @@ i64 flexScore(const Snap& sn, const PodCtx& pc, i64 n) {
 }
 
 // fitsRequest — vendor/…/plugins/noderesources/fit.go:256-329. Returns #insufficient resources.
-int fitsRequest(const Snap& sn, const PodCtx& pc, i64 n, uint32_t ignoredScalarMask) {
+// mask (optional): the InsufficientResource list as FGS_FIT_REASON_* bits
+int fitsRequest(const Snap& sn, const PodCtx& pc, i64 n, uint32_t ignoredScalarMask, uint32_t* mask = nullptr) {
     int insufficient = 0;
+    uint32_t dummy;
+    if (!mask) mask = &dummy;
+    *mask = 0;
     const i64* al = sn.alloc(n);
     const i64* rq = sn.req(n);
     i64 numPods = sn.podEnd(n) - sn.podBegin(n);
-    if (numPods + 1 > al[3]) insufficient++; // :259-268
+    if (numPods + 1 > al[3]) insufficient++, *mask |= FGS_FIT_REASON_PODS; // :259-268
     const Resource& r = pc.fitReq;
     if (r.mcpu == 0 && r.mem == 0 && r.eph == 0 && r.scalarPresent == 0) return insufficient; // :270-275
-    if (r.mcpu > wsub(al[0], rq[0])) insufficient++; // :277-285
-    if (r.mem > wsub(al[1], rq[1])) insufficient++;  // :286-294
-    if (r.eph > wsub(al[2], rq[2])) insufficient++;  // :295-303
+    if (r.mcpu > wsub(al[0], rq[0])) insufficient++, *mask |= FGS_FIT_REASON_CPU; // :277-285
+    if (r.mem > wsub(al[1], rq[1])) insufficient++, *mask |= FGS_FIT_REASON_MEM; // :286-294
+    if (r.eph > wsub(al[2], rq[2])) insufficient++, *mask |= FGS_FIT_REASON_EPH; // :295-303
     for (int s = 0; s < sn.S; ++s) {                 // :305-326
         if (!((r.scalarPresent >> s) & 1u)) continue;
         if ((ignoredScalarMask >> s) & 1u) continue;
-        if (r.scalar[s] > wsub(al[4 + s], rq[3 + s])) insufficient++;
+        if (r.scalar[s] > wsub(al[4 + s], rq[3 + s])) insufficient++, *mask |= FGS_FIT_REASON_SCALAR0 << s;
     }
     return insufficient;
 }
@@ -741,6 +749,34 @@ int evaluateImpl(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_
     return 0;
 }
 } // namespace
+
+// The reason inside each plugin's Filter status for pod p on every node: flex[n] = FGS_FLEX_REASON_* (0xF1 where
+// NewGPUNode panics), fit[n] = FGS_FIT_REASON_* bits. Either may be NULL.
+extern "C" int fgs_oracle_filter_reasons(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg,
+                                         int64_t p, uint16_t* flex, uint16_t* fit) {
+    Snap sn(snap);
+    PodCtx pc;
+    pc.ps = pending;
+    pc.i = p;
+    pc.fitReq = computePodResourceRequest(pending, p);
+    for (i64 n = 0; n < snap->n_nodes; ++n) {
+        if (flex) {
+            int reason = 0;
+            try {
+                flexFilter(sn, pc, n, &reason);
+            } catch (const RefPanic&) {
+                reason = FGS_FLEX_REASON_PANIC;
+            }
+            flex[n] = (uint16_t)reason;
+        }
+        if (fit) {
+            uint32_t mask = 0;
+            fitsRequest(sn, pc, n, cfg->fit_ignored_scalar_mask, &mask);
+            fit[n] = (uint16_t)mask;
+        }
+    }
+    return 0;
+}
 
 // FlexGPU.Reserve — pkg/flexgpu/flex_gpu.go:178-223
 extern "C" int fgs_oracle_reserve_index(const fgs_snapshot* snap, const fgs_podset* pending, int64_t p,

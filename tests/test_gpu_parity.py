@@ -6,6 +6,7 @@ import os
 import numpy as np
 import pytest
 
+import builders as B
 import golden_cases as G
 import flex_gpu_scheduler_b200 as fgs
 from flex_gpu_scheduler_b200 import _lib as L
@@ -300,4 +301,42 @@ def test_dirty_row_update(gpu_ok, oracle):
     exp = ra.status == 0
     exp[:, dirty] = (rb.status == 0)[:, dirty]
     assert np.array_equal(feas, exp)
+    eng.close()
+
+
+def test_reason_planes_match_the_oracle(gpu_ok, oracle):
+    """fgs_reason_plane: the message inside each Filter status (flex_gpu.go:60-114) and Fit's InsufficientResource
+    list (fit.go:256-329), against the oracle's walk."""
+    s = fgs.config_synth(2, n_nodes=900, n_pending=96, pm_panic_nodes=15, pm_nongpu_nodes=60, pm_extra_scalar=200, n_scalars=3)
+    cfg = fgs.config_plugins(2)
+    eng = fgs.Engine(device=0, n_scalars=3)
+    eng.set_plugins(cfg)
+    eng.upload_nodes(fgs.Packer(3).nodes(s.snapshot))
+    eng.evaluate(fgs.Packer(3).pods(s.pending))
+    flex = eng.reason_plane(L.FGS_PL_FLEXGPU)
+    fit = eng.reason_plane(L.FGS_PL_FIT)
+    seen_flex, seen_fit = set(), set()
+    for p in range(s.n_pending):
+        rf, rt = oracle.filter_reasons(s.snapshot, s.pending, cfg, p)
+        assert np.array_equal(flex[p], rf), p
+        assert np.array_equal(fit[p], rt), p
+        seen_flex |= set(int(x) for x in rf)
+        seen_fit |= set(int(x) for x in rt)
+    assert {0, 1, 2, 3, 4, 5, 0xF1} <= seen_flex, seen_flex
+    # cpu, memory and all three scalar slots occur, alone and combined
+    assert all(any(x & b for x in seen_fit) for b in (2, 4, 16, 32, 64)) and any(bin(x).count("1") >= 3 for x in seen_fit)
+    eng.close()
+    # "Too many pods" (fit.go:259-268), alone and together with another dimension
+    full = B.node(alloc={"cpu": 4000, "memory": 8 << 30, "pods": 1}, pods=[B.pod([B.ctr({"cpu": 100})], node_name=True)])
+    free = B.node(alloc={"cpu": 4000, "memory": 8 << 30, "pods": 110})
+    snap = B.build_snapshot([full, free])
+    pend = B.build_podset([B.pod([B.ctr({"cpu": 100})]), B.pod([B.ctr({"cpu": 8000})]), B.pod([B.ctr({})])])
+    eng = fgs.Engine(device=0)
+    eng.set_plugins(cfg)
+    eng.upload_nodes(fgs.Packer(2).nodes(snap.ptr))
+    eng.evaluate(fgs.Packer(2).pods(pend.ptr))
+    fit = eng.reason_plane(L.FGS_PL_FIT)
+    assert fit.tolist() == [[1, 0], [3, 2], [1, 0]]
+    for p in range(3):
+        assert np.array_equal(fit[p], oracle.filter_reasons(snap.ptr, pend.ptr, cfg, p)[1])
     eng.close()
