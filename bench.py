@@ -194,7 +194,7 @@ def run_ours(args):
 
     # pods go through in batches when the score matrix of the whole set would not fit comfortably
     n_pad = (max(n_shard, 1) + 1023) // 1024 * 1024
-    batch = n_pods if n_pods * n_pad * 8 <= 48 * 2 ** 30 else BATCH
+    batch = n_pods if n_pods * n_pad * 8 <= 100 * 2 ** 30 else BATCH  # 180 GB of HBM3e per GPU
     batches = [(b, min(n_pods, b + batch)) for b in range(0, n_pods, batch)]
     packers = [fgs.Packer(2) for _ in batches]
     tables = [pk.pods(synth.pending, b0, b1) for pk, (b0, b1) in zip(packers, batches)]
