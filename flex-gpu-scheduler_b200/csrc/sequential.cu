@@ -50,822 +50,8 @@ typedef unsigned long long u64;
         }                                                                    \
     } while (0)
 
-namespace {
+#include "seq_kernel.cuh"
 
-constexpr i64 kMin64 = (i64)0x8000000000000000ull;
-constexpr int kSeqThreads = 256;              // node-owning threads per CTA
-constexpr int kSeqWarps = kSeqThreads / 32;  // node-owning warps
-constexpr int kSeqBlock = kSeqThreads + 32;   // + the communication warp (warp 0)
-constexpr int kSeqTileP = 64;
-constexpr int kMaxK = 32;        // nodes per thread (bit mask of feasible nodes)
-constexpr int kWordsA = 8;       // mailbox words per CTA, phase A (7 used)
-constexpr int kWordsB = 4;       // phase B (3 used)
-constexpr int kMaxCluster = 16;  // CTAs of the single-cluster variant
-
-enum SeqExtra : int { SX_ACCT_CPU = 0, SX_ACCT_MEM, SX_ANNOT, SX_NS, SX_COLS };
-enum SeqOut : int { SO_COUNT = 0, SO_NODE, SO_SCORE, SO_ERR, SO_DEVICE, SO_COMMITTED, SO_QUOTA, SO_COLS };
-
-struct SeqParams {
-    DeriveParams dv;       // raw + derived node tables, plugin args of the derivation
-    const i64* pods;       // [pd_cols(S)][p_pad]
-    const i64* extra;      // [SX_COLS][p_pad]
-    i64* out;              // [SO_COLS][p_pad]
-    u64* mail_a;           // [2][G][kWordsA] self-tagged words
-    u64* mail_b;           // [2][G][kWordsB]
-    u64* prof;             // [G][16] clock sums per section (FGS_SEQ_PROFILE=1), else NULL
-    // ElasticQuota tables (CapacityScheduling in the profile), device memory; q_has_eq == NULL: not in the profile
-    const uint8_t* q_has_eq; // [NS]
-    const i64* q_min;        // [NS][2+S]
-    const i64* q_max;
-    i64* q_used;             // rewritten by CapacityScheduling.Reserve
-    uint32_t* q_used_present;
-    i64 n_ns;
-    int* status;           // [0]: index of the first pod whose commit left the supported range, INT_MAX none
-    i64 n_pods, p_pad;
-    int K, state_smem;
-    uint32_t filter_mask, score_mask;
-    int flex_filter_first;
-    i64 w_flex, w_fit, w_alloc;
-    int fit_strategy, fit_n_res;
-    int fit_res[FGS_MAX_SCORE_RES];
-    i64 fit_w[FGS_MAX_SCORE_RES];
-    uint32_t fit_ignored;
-    u64 seed;
-    int key_shift, reserve_flex;
-};
-
-// ---- small PTX wrappers -------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    uint32_t ok = 0;
-    while (!ok) {
-        asm volatile(
-            "{\n"
-            ".reg .pred p;\n"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-            "selp.u32 %0, 1, 0, p;\n"
-            "}\n"
-            : "=r"(ok)
-            : "r"(s_u32(bar)), "r"(parity)
-            : "memory");
-    }
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s_u32(dst)),
-                 "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(s_u32(bar))
-                 : "memory");
-}
-// mailbox words: relaxed, gpu scope, never cached in L1
-__device__ __forceinline__ void st_word(u64* p, uint32_t payload, uint32_t tag) {
-    const u64 w = ((u64)tag << 32) | payload;
-    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
-}
-__device__ __forceinline__ u64 ld_word(const u64* p) {
-    u64 w;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
-    return w;
-}
-
-// the same words through distributed shared memory (one thread-block cluster): remote store into a peer CTA's
-// mailbox, local polling
-__device__ __forceinline__ uint32_t mapa_u32(uint32_t saddr, uint32_t rank) {
-    uint32_t r;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
-    return r;
-}
-__device__ __forceinline__ void st_word_peer(uint32_t raddr, uint32_t payload, uint32_t tag) {
-    const u64 w = ((u64)tag << 32) | payload;
-    asm volatile("st.relaxed.cluster.shared::cluster.u64 [%0], %1;" ::"r"(raddr), "l"(w) : "memory");
-}
-__device__ __forceinline__ u64 ld_word_local(const u64* p) {
-    u64 w;
-    asm volatile("ld.relaxed.cluster.shared::cta.u64 %0, [%1];" : "=l"(w) : "r"(s_u32(p)) : "memory");
-    return w;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// a real consumer of `v` that cannot be removed: the clock read after it cannot issue before v has arrived
-__device__ __forceinline__ void consume(i64 v) {
-    asm volatile("{\n.reg .pred q;\nsetp.eq.s64 q, %0, 0x7ff0123456789abc;\n@q trap;\n}\n" ::"l"(v));
-}
-
-__device__ __forceinline__ i64 wmul(i64 a, i64 b) { return (i64)((u64)a * (u64)b); }
-__device__ __forceinline__ i64 wadd(i64 a, i64 b) { return (i64)((u64)a + (u64)b); }
-__device__ __forceinline__ i64 wsub(i64 a, i64 b) { return (i64)((u64)a - (u64)b); }
-
-__device__ __forceinline__ i64 warp_max_i64(i64 v) {
-    const int hi = (int)(v >> 32);
-    const uint32_t lo = (uint32_t)v;
-    const int mhi = __reduce_max_sync(0xffffffffu, hi);
-    const uint32_t mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
-    return (i64)(((u64)(uint32_t)mhi << 32) | mlo);
-}
-
-__device__ __forceinline__ float u64_to_float(u64 a) {
-    return fmaf(__uint2float_rn((uint32_t)(a >> 32)), 4294967296.0f, __uint2float_rn((uint32_t)a));
-}
-
-// Go's int64 x / d (truncation toward zero, wrapping), d != 0. The common case — both positive, quotient below
-// 2^18 — avoids the 64-bit division routine: a float estimate is within 1/8 of the true quotient there, so its
-// rounding k is the quotient or one above, and the sign of the exact remainder x − k·d decides.
-__device__ __forceinline__ i64 go_div(i64 x, i64 d) {
-    if (x >= 0 && d > 0 && x < ((i64)1 << 62) && d < ((i64)1 << 62)) {
-        const float est = __fdividef(u64_to_float((u64)x), u64_to_float((u64)d));
-        if (est < 262144.0f) {
-            const int k = __float2int_rn(est);
-            const i64 r = x - (i64)((u64)(uint32_t)k * (u64)d);
-            return (i64)k + (r >> 63);
-        }
-    }
-    if (d == -1) return (i64)(0ull - (u64)x);
-    return x / d;
-}
-
-} // namespace
-
-// =================================================================================================
-// seq_kernel
-// =================================================================================================
-namespace {
-
-struct SeqSmem {
-    int bars, ring, part_a, fin_a, part_b, fin_b, mail_a, mail_b, fit, state, total;
-    int npc; // pod columns per tile
-};
-
-__host__ __device__ inline SeqSmem seq_smem(int S, int D, int K, int state_smem) {
-    SeqSmem L;
-    L.npc = pd_cols(S) + SX_COLS;
-    int off = 0;
-    L.bars = off;
-    off += 64;
-    L.ring = off;
-    off += 2 * L.npc * kSeqTileP * 8;
-    L.part_a = off;
-    off += kSeqWarps * 4 * 8;
-    L.fin_a = off;
-    off += 4 * 8;
-    L.part_b = off;
-    off += kSeqWarps * 2 * 8;
-    L.fin_b = off;
-    off += 2 * 8;
-    L.mail_a = off; // cluster variant: u64 [2][kMaxCluster][kWordsA]
-    off += 2 * kMaxCluster * kWordsA * 8;
-    L.mail_b = off;
-    off += 2 * kMaxCluster * kWordsB * 8;
-    L.fit = off;
-    off += K * kSeqThreads * 8;
-    off = (off + 127) & ~127;
-    L.state = off;
-    if (state_smem) off += (nd_cols(S) + nr_cols(S, D)) * kSeqThreads * K * 8;
-    L.total = off;
-    return L;
-}
-
-// FlexGPU.Reserve on one raw node row (flex_gpu.go:178-223): the device index, or FGS_RESERVE_*.
-// mem_each = memCnt / gpuCnt as NewGPUNode computes it (gpu_node.go:55), taken from the derived row.
-__device__ __forceinline__ int reserve_on_row(const i64* raw, i64 rs, i64 mem_each, int S, int D, uint32_t kind, i64 mem_limit) {
-    if (kind == 0) return FGS_RESERVE_NONE;     // :187-189
-    if (kind == 3) return FGS_RESERVE_CONFLICT; // :191-193
-    auto R = [&](int c) { return raw[(i64)c * rs]; };
-    const u64 meta = (u64)R(NR_META);
-    const uint32_t flags = (uint32_t)meta, mono = (uint32_t)(meta >> 32);
-    if (flags & FGS_NF_REF_PANIC) return FGS_RESERVE_PANIC; // NewGPUNode, :195
-    const i64 gpuCnt = R(nr_alloc_scalar(FGS_SCALAR_FLEX_GPU)); // > 0: REF_PANIC covers the rest
-    int dev = FGS_RESERVE_FAIL;
-    for (int d = D - 1; d >= 0; --d) { // lowest fitting index wins; no early exit so that the loads overlap
-        const i64 used = R(nr_used(S, d));
-        const bool m = (mono >> d) & 1u;
-        // GPUAssumeFitIndexes, gpu_node.go:163-177 / MemAssumeFitIndexes, :122-161 (indexes[0] is the first fit)
-        const bool fit = kind == 1 ? (!m && used == 0) : (!m && mem_each >= used + mem_limit);
-        if (fit && (i64)d < gpuCnt) dev = d;
-    }
-    return dev;
-}
-
-template <bool SMEM, bool CLUSTER>
-__global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant__ SeqParams prm) {
-    extern __shared__ __align__(128) unsigned char smem[];
-    const int S = prm.dv.S, D = prm.dv.D;
-    const int K = prm.K;
-    const SeqSmem L = seq_smem(S, D, K, SMEM ? 1 : 0);
-    uint64_t* bars = (uint64_t*)(smem + L.bars);
-    i64* s_ring = (i64*)(smem + L.ring);
-    i64* s_part_a = (i64*)(smem + L.part_a);
-    i64* s_fin_a = (i64*)(smem + L.fin_a);
-    u64* s_part_b = (u64*)(smem + L.part_b);
-    u64* s_fin_b = (u64*)(smem + L.fin_b);
-    i64* s_fit = (i64*)(smem + L.fit);
-    u64* s_mail_a = (u64*)(smem + L.mail_a);
-    u64* s_mail_b = (u64*)(smem + L.mail_b);
-    int* s_dirty = (int*)(smem + L.bars + 32); // local index of the node whose row the last commit rewrote, -1 none
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const bool comm = warp == 0;        // warp 0 talks to the other CTAs; warps 1..8 own the nodes
-    const int ct = tid - 32, cw = warp - 1;
-    const int G = (int)gridDim.x, cta = (int)blockIdx.x;
-    const i64 np = prm.dv.n_pad, n_nodes = prm.dv.n_nodes;
-    const i64 cta_nodes = (i64)kSeqThreads * K;
-    const i64 node0 = (i64)cta * cta_nodes;
-    const int ncols = nd_cols(S);
-    const int nrc = nr_cols(S, D);
-    const int npc = L.npc;
-    const i64 n_tiles = (prm.n_pods + kSeqTileP - 1) / kSeqTileP;
-
-    auto issue_pod_tile = [&](i64 it) { // one elected thread
-        const int stage = (int)(it & 1);
-        const i64 p0 = it * kSeqTileP;
-        i64* dst = s_ring + (size_t)stage * npc * kSeqTileP;
-        mbar_expect_tx(&bars[stage], (uint32_t)(npc * kSeqTileP * 8));
-        for (int c = 0; c < pd_cols(S); ++c) bulk_g2s(dst + c * kSeqTileP, prm.pods + (i64)c * prm.p_pad + p0, kSeqTileP * 8, &bars[stage]);
-        for (int c = 0; c < SX_COLS; ++c)
-            bulk_g2s(dst + (pd_cols(S) + c) * kSeqTileP, prm.extra + (i64)c * prm.p_pad + p0, kSeqTileP * 8, &bars[stage]);
-    };
-
-    if (tid == 0) {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        *s_dirty = -1;
-        s_dirty[1] = 0;
-    }
-    __syncthreads();
-    if (tid == 0 && n_tiles > 0) issue_pod_tile(0);
-
-    // ---- node state of the nodes this CTA owns: st = derived columns, rw = raw columns; element (c, i) at
-    // [c * stride + i], i = node − node0 ----------------------------------------------------------------------
-    i64 *st, *rw;
-    i64 st_stride;
-    if (SMEM) {
-        st = (i64*)(smem + L.state);
-        rw = st + (i64)ncols * cta_nodes;
-        st_stride = cta_nodes;
-        for (int c = 0; c < ncols + nrc; ++c)
-            for (i64 i = tid; i < cta_nodes; i += kSeqBlock) {
-                const i64 n = node0 + i;
-                const i64* src = c < ncols ? (const i64*)prm.dv.nd + (i64)c * np : (const i64*)prm.dv.raw + (i64)(c - ncols) * np;
-                st[(i64)c * st_stride + i] = n < n_nodes ? src[n] : 0;
-            }
-    } else {
-        st = (i64*)prm.dv.nd + node0;
-        rw = (i64*)prm.dv.raw + node0;
-        st_stride = np;
-    }
-    if (CLUSTER) {
-        for (int k = tid; k < 2 * kMaxCluster * (kWordsA + kWordsB); k += kSeqBlock) s_mail_a[k] = 0; // mail_b follows mail_a
-        cluster_sync_all(); // no peer writes into a mailbox that is not cleared yet
-    }
-    __syncthreads();
-
-    const bool use_flex_filter = prm.filter_mask & FGS_PL_FLEXGPU;
-    const bool use_fit_filter = prm.filter_mask & FGS_PL_FIT;
-    const bool sc_flex = prm.score_mask & FGS_PL_FLEXGPU;
-    const bool sc_fit = prm.score_mask & FGS_PL_FIT;
-    const bool sc_alloc = prm.score_mask & FGS_PL_ALLOCATABLE;
-
-    long long pc[6] = {0, 0, 0, 0, 0, 0}, pt = 0;
-    const bool prof = prm.prof != nullptr && tid == 32;
-    auto tick = [&](int k) {
-        if (prof) {
-            const long long now = clock64();
-            pc[k] += now - pt;
-            pt = now;
-        }
-    };
-    const bool cprof = prm.prof != nullptr && tid == 0;
-    long long cc[4] = {0, 0, 0, 0}, cpt = 0;
-    auto ctick = [&](int k) {
-        if (cprof) {
-            const long long now = clock64();
-            cc[k] += now - cpt;
-            cpt = now;
-        }
-    };
-    if (prof) pt = clock64();
-    if (cprof) cpt = clock64();
-    // communication warp, shared-memory state only: copy the row the last commit rewrote to the global tables
-    // (off the critical path: the owner thread only flags it)
-    auto flush_dirty = [&]() {
-        const int di = *(volatile int*)s_dirty;
-        if (di >= 0) {
-            const i64 n = node0 + di;
-            for (int c = lane; c < ncols + nrc; c += 32) {
-                if (c < ncols) ((i64*)prm.dv.nd)[(i64)c * np + n] = st[(i64)c * st_stride + di];
-                else ((i64*)prm.dv.raw)[(i64)(c - ncols) * np + n] = rw[(i64)(c - ncols) * st_stride + di];
-            }
-            __syncwarp();
-            if (lane == 0) *s_dirty = -1;
-        }
-    };
-
-    // ---- ElasticQuota state: owned by the communication warp of CTA 0 (lane c holds resource column c) ---------
-    const bool quota_on = prm.q_has_eq != nullptr;
-    const bool quota_warp = quota_on && comm && cta == 0;
-    const int QW = 2 + S;
-    i64 agg_used = 0, agg_min = 0; // Σ over namespaces with a quota (aggregatedUsedOverMinWith, elasticquota.go:40-51)
-    uint32_t agg_present = 0;
-    bool pend_has = false, pend_key = false; // the previous pod's reservation, applied once its commit is known
-    int pend_ns = -1;
-    i64 pend_v = 0;
-    uint32_t pend_keys = 0;
-    if (quota_warp) {
-        for (i64 k = 0; k < prm.n_ns; ++k) {
-            if (!prm.q_has_eq[k]) continue;
-            const uint32_t up = prm.q_used_present[k];
-            agg_present |= up;
-            if (lane < QW) {
-                if (lane < 2 || ((up >> (lane - 2)) & 1u)) agg_used += prm.q_used[k * QW + lane];
-                agg_min += prm.q_min[k * QW + lane];
-            }
-        }
-    }
-    int* s_commit = s_dirty + 1; // 1: the previous cycle's pod was committed by a thread of this CTA
-
-    // with quotas one more (drain) iteration carries the last pod's commit flag to the quota warp
-    const i64 n_iter = prm.n_pods + (quota_on ? 1 : 0);
-    for (i64 p = 0; p < n_iter; ++p) {
-        const bool drain = p >= prm.n_pods;
-        const i64 it = p / kSeqTileP;
-        const int jp = (int)(p % kSeqTileP), stage = (int)(it & 1);
-        const uint32_t tag = (uint32_t)(p + 1);
-        const int par = (int)(p & 1);
-        const i64* praw = s_ring + (size_t)stage * npc * kSeqTileP;
-        auto PC = [&](int c) { return praw[c * kSeqTileP + jp]; };
-
-        if (comm) {
-            // ================= the communication warp =====================================================
-            // CapacityScheduling.PreFilter of this pod (capacity_scheduling.go:201-275, no nominated pods), while
-            // the compute warps filter: once against the quota table as it is and once with the previous pod's
-            // reservation added — which of the two holds is known when that pod's commit flag arrives with (A)
-            uint32_t qbits = 0;
-            bool q_has = false, q_key = false;
-            int q_ns = -1;
-            i64 q_v = 0;
-            uint32_t q_keys = 0;
-            if (quota_warp && !drain) {
-                if (jp == 0) mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
-                q_ns = (int)PC(pd_cols(S) + SX_NS);
-                q_keys = (uint32_t)((u64)PC(PD_META) >> 32);
-                q_v = lane == 0 ? PC(PD_REQ_CPU) : (lane == 1 ? PC(PD_REQ_MEM) : (lane < QW ? PC(PD_FIXED_COLS + lane - 2) : 0));
-                q_has = q_ns >= 0 && q_ns < prm.n_ns && prm.q_has_eq[q_ns];
-                q_key = lane < 2 || (lane < QW && ((q_keys >> (lane - 2)) & 1u));
-                if (q_has) { // a namespace without an ElasticQuota passes (:210-217)
-                    const uint32_t up = *(volatile uint32_t*)(prm.q_used_present + q_ns);
-                    const bool u_key = lane < 2 || (lane < QW && ((up >> (lane - 2)) & 1u));
-                    const i64 u = u_key ? *(volatile i64*)(prm.q_used + (i64)q_ns * QW + lane) : 0;
-                    const i64 mx = lane < QW ? prm.q_max[(i64)q_ns * QW + lane] : 0;
-                    const i64 d_same = (pend_has && pend_ns == q_ns && pend_key) ? pend_v : 0;
-                    const i64 d_all = (pend_has && pend_key) ? pend_v : 0;
-                    // usedOverMaxWith = cmp2(request, Used, Max): the request's scalar keys (elasticquota.go:94-96,165-181)
-                    const uint32_t m0 = __ballot_sync(0xffffffffu, q_key && q_v + u > mx);
-                    const uint32_t m1 = __ballot_sync(0xffffffffu, q_key && q_v + u + d_same > mx);
-                    // aggregatedUsedOverMinWith: keys of Σused ∪ the request's (:40-51)
-                    const uint32_t ak0 = agg_present | q_keys, ak1 = ak0 | (pend_has ? pend_keys : 0u);
-                    const bool a0 = lane < 2 || (lane < QW && ((ak0 >> (lane - 2)) & 1u));
-                    const bool a1 = lane < 2 || (lane < QW && ((ak1 >> (lane - 2)) & 1u));
-                    const uint32_t n0 = __ballot_sync(0xffffffffu, a0 && agg_used + q_v > agg_min);
-                    const uint32_t n1 = __ballot_sync(0xffffffffu, a1 && agg_used + d_all + q_v > agg_min);
-                    const uint32_t code0 = m0 ? 1u : (n0 ? 2u : 0u), code1 = m1 ? 1u : (n1 ? 2u : 0u);
-                    qbits = (code0 << 1) | (code1 << 3);
-                }
-            }
-            __syncthreads(); // (1) the compute warps' phase-A partials are in shared memory
-            if (lane == 0 && !drain && jp == 0 && it + 1 < n_tiles) { // every thread is past its last read of the previous tile
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                issue_pod_tile(it + 1);
-            }
-            const bool w = lane < kSeqWarps;
-            const i64 cf = w ? s_part_a[lane * 4 + 0] : 0;
-            if (cprof) consume(cf);
-            ctick(0); // commit + Filter of the slowest thread of this CTA
-            uint32_t c2 = __reduce_add_sync(0xffffffffu, (uint32_t)cf & 0xffffffu);
-            uint32_t f2 = __reduce_or_sync(0xffffffffu, (uint32_t)(cf >> 24));
-            if (quota_on) { // bits 1-4: the two PreFilter verdicts (CTA 0); bit 5: the previous pod was committed here
-                const int cm = *(volatile int*)s_commit;
-                f2 |= qbits | (cm ? 32u : 0u);
-                __syncwarp();
-                if (lane == 0 && cm) *s_commit = 0;
-            }
-            i64 a1 = warp_max_i64(w ? s_part_a[lane * 4 + 1] : kMin64);
-            i64 a2 = warp_max_i64(w ? s_part_a[lane * 4 + 2] : kMin64);
-            i64 a3 = warp_max_i64(w ? s_part_a[lane * 4 + 3] : kMin64);
-            if (G > 1) {
-                uint32_t pay = 0;
-                if (lane == 0) pay = c2 | (f2 << 24);
-                else if (lane < 7) {
-                    const i64 v = lane <= 2 ? a1 : (lane <= 4 ? a2 : a3);
-                    pay = (lane & 1) ? (uint32_t)v : (uint32_t)((u64)v >> 32);
-                }
-                if (CLUSTER) {
-                    const uint32_t slot = s_u32(s_mail_a + ((size_t)par * kMaxCluster + cta) * kWordsA + lane);
-                    if (lane < 7)
-                        for (int dst = 0; dst < G; ++dst) st_word_peer(mapa_u32(slot, (uint32_t)dst), pay, tag);
-                } else if (lane < 7) {
-                    st_word(prm.mail_a + ((size_t)par * G + cta) * kWordsA + lane, pay, tag);
-                }
-                uint32_t tc = 0, tf = 0;
-                i64 t1 = kMin64, t2 = kMin64, t3 = kMin64;
-                for (int c = lane; c < G; c += 32) {
-                    const u64* m = CLUSTER ? s_mail_a + ((size_t)par * kMaxCluster + c) * kWordsA : prm.mail_a + ((size_t)par * G + c) * kWordsA;
-                    u64 wv[7];
-                    bool ok;
-                    do {
-                        ok = true;
-#pragma unroll
-                        for (int k = 0; k < 7; ++k) {
-                            wv[k] = CLUSTER ? ld_word_local(m + k) : ld_word(m + k);
-                            ok = ok && (uint32_t)(wv[k] >> 32) == tag;
-                        }
-                    } while (!ok);
-                    tc += (uint32_t)wv[0] & 0xffffffu;
-                    tf |= ((uint32_t)wv[0] >> 24) & 0xffu;
-                    const i64 x1 = (i64)((wv[2] << 32) | (wv[1] & 0xffffffffull));
-                    const i64 x2 = (i64)((wv[4] << 32) | (wv[3] & 0xffffffffull));
-                    const i64 x3 = (i64)((wv[6] << 32) | (wv[5] & 0xffffffffull));
-                    t1 = x1 > t1 ? x1 : t1;
-                    t2 = x2 > t2 ? x2 : t2;
-                    t3 = x3 > t3 ? x3 : t3;
-                }
-                c2 = __reduce_add_sync(0xffffffffu, tc);
-                f2 = __reduce_or_sync(0xffffffffu, tf);
-                a1 = warp_max_i64(t1);
-                a2 = warp_max_i64(t2);
-                a3 = warp_max_i64(t3);
-            }
-            if (cprof) consume((i64)c2);
-            ctick(1); // exchange A, including the wait for the slowest CTA
-            uint32_t qcode = 0;
-            if (quota_on) {
-                const bool committed_prev = (f2 >> 5) & 1u;
-                qcode = committed_prev ? (f2 >> 3) & 3u : (f2 >> 1) & 3u;
-                if (quota_warp) {
-                    if (pend_has && committed_prev) { // CapacityScheduling.Reserve → reserveResource (elasticquota.go:74-80)
-                        if (pend_key) {
-                            const uint32_t up = *(volatile uint32_t*)(prm.q_used_present + pend_ns);
-                            const bool u_key = lane < 2 || ((up >> (lane - 2)) & 1u);
-                            i64* up_ = prm.q_used + (i64)pend_ns * QW + lane;
-                            *(volatile i64*)up_ = (u_key ? *(volatile i64*)up_ : 0) + pend_v;
-                            agg_used += pend_v;
-                        }
-                        __syncwarp();
-                        if (lane == 0) *(volatile uint32_t*)(prm.q_used_present + pend_ns) |= pend_keys;
-                        __syncwarp();
-                        agg_present |= pend_keys;
-                    }
-                    pend_has = q_has && qcode == 0 && !drain;
-                    pend_ns = q_ns;
-                    pend_v = q_v;
-                    pend_keys = q_keys;
-                    pend_key = q_key;
-                }
-                if (qcode) c2 = 0; // rejected in PreFilter: no Filter/Score results, nothing to select
-                f2 = (f2 & 1u) | (qcode << 8);
-            }
-            if (lane == 0) {
-                s_fin_a[0] = (i64)(((u64)f2 << 32) | c2);
-                s_fin_a[1] = a1;
-                s_fin_a[2] = a2;
-                s_fin_a[3] = a3;
-            }
-            __syncthreads(); // (2)
-            if (SMEM) flush_dirty();
-            if (c2 > 0) {    // uniform over the grid: phase B runs
-                __syncthreads(); // (3) the compute warps' keys are in shared memory
-                u64 k2 = (u64)warp_max_i64(w ? (i64)s_part_b[lane * 2 + 0] : 0);
-                if (cprof) consume((i64)k2);
-                ctick(2); // Fit score + NormalizeScore of the slowest thread of this CTA
-                uint32_t e2 = __reduce_or_sync(0xffffffffu, w ? (uint32_t)s_part_b[lane * 2 + 1] : 0u);
-                if (G > 1) {
-                    const uint32_t pay = lane == 0 ? (uint32_t)k2 : (lane == 1 ? (uint32_t)(k2 >> 32) : e2);
-                    if (CLUSTER) {
-                        const uint32_t slot = s_u32(s_mail_b + ((size_t)par * kMaxCluster + cta) * kWordsB + lane);
-                        if (lane < 3)
-                            for (int dst = 0; dst < G; ++dst) st_word_peer(mapa_u32(slot, (uint32_t)dst), pay, tag);
-                    } else if (lane < 3) {
-                        st_word(prm.mail_b + ((size_t)par * G + cta) * kWordsB + lane, pay, tag);
-                    }
-                    u64 tk = 0;
-                    uint32_t te = 0;
-                    for (int c = lane; c < G; c += 32) {
-                        const u64* m = CLUSTER ? s_mail_b + ((size_t)par * kMaxCluster + c) * kWordsB : prm.mail_b + ((size_t)par * G + c) * kWordsB;
-                        u64 w0, w1, w2;
-                        do {
-                            w0 = CLUSTER ? ld_word_local(m + 0) : ld_word(m + 0);
-                            w1 = CLUSTER ? ld_word_local(m + 1) : ld_word(m + 1);
-                            w2 = CLUSTER ? ld_word_local(m + 2) : ld_word(m + 2);
-                        } while ((uint32_t)(w0 >> 32) != tag || (uint32_t)(w1 >> 32) != tag || (uint32_t)(w2 >> 32) != tag);
-                        const u64 x = (w1 << 32) | (w0 & 0xffffffffull);
-                        tk = x > tk ? x : tk;
-                        te |= (uint32_t)w2;
-                    }
-                    k2 = (u64)warp_max_i64((i64)tk);
-                    e2 = __reduce_or_sync(0xffffffffu, te);
-                }
-                if (cprof) consume((i64)k2);
-                ctick(3); // exchange B
-                if (lane == 0) {
-                    s_fin_b[0] = k2;
-                    s_fin_b[1] = e2;
-                }
-                __syncthreads(); // (4)
-            }
-            continue;
-        }
-
-        // ================= the compute warps ===============================================================
-        if (!drain && jp == 0) mbar_wait(&bars[stage], (uint32_t)((it >> 1) & 1));
-        // per-pod values (broadcast reads)
-        const u64 pmeta = (u64)PC(PD_META);
-        const uint32_t pf = (uint32_t)pmeta;
-        const uint32_t kind = pf & 3u;
-        const bool req_none = pf & FGS_PF_REQ_NONE;
-        const uint32_t smask = (uint32_t)(pmeta >> 32) & ~prm.fit_ignored;
-        const i64 gpu_lim = PC(PD_GPU_LIM), mem_lim = PC(PD_MEM_LIM);
-        const i64 lim = kind == 1 ? gpu_lim : mem_lim;
-        const i64 rc = PC(PD_REQ_CPU), rm = PC(PD_REQ_MEM), re = PC(PD_REQ_EPH);
-        const i64 nzc = PC(PD_NZ_CPU), nzm = PC(PD_NZ_MEM);
-
-        // ---- phase A: Filter on my nodes ---------------------------------------------------------------------
-        uint32_t feas_mask = 0, cnt = 0, fl = 0;
-        i64 vflex = kMin64, vhi = kMin64, vnlo = kMin64;
-        const bool flex_pod = use_flex_filter && kind != 0;
-        const bool fit_req = use_fit_filter && !req_none;
-        const int Kc = drain ? 0 : K; // the drain iteration only carries flags
-        for (int j = 0; j < Kc; ++j) {
-            const i64 i = (i64)j * kSeqThreads + ct;
-            if (node0 + i >= n_nodes) break;
-            auto C = [&](int c) { return st[(i64)c * st_stride + i]; };
-            // every column the verdict can need, loaded before any of them is used (one shared-memory latency)
-            const uint32_t nf = (uint32_t)C(ND_FLAGS);
-            const i64 thr = C(kind == 1 ? ND_THR_GPU : ND_THR_MEM);
-            const i64 fc = C(ND_FREE_CPU), fm_ = C(ND_FREE_MEM), fe = C(ND_FREE_EPH);
-            const i64 sflex = C(kind == 1 ? ND_GPU_SCORE : ND_MEM_SCORE);
-            const i64 ar = C(ND_ALLOC_RAW);
-            // FlexGPU.Filter, flex_gpu.go:41-119, folded into one threshold per pod kind (derive.cuh)
-            const bool flex_ok = !flex_pod || (kind != 3 && lim <= thr);
-            // Fit.Filter, fit.go:256-329
-            bool fit_ok = !use_fit_filter || (nf & NDF_PODS_OK);
-            if (fit_req) {
-                fit_ok = fit_ok & (rc <= fc) & (rm <= fm_) & (re <= fe);
-                uint32_t m = smask;
-                while (m) {
-                    const int s = __ffs(m) - 1;
-                    m &= m - 1;
-                    if (PC(PD_FIXED_COLS + s) > C(nd_free_scalar(s))) fit_ok = false;
-                }
-            }
-            const bool valid = nf & FGS_NF_VALID;
-            // the reference panics inside NewGPUNode (flex_gpu.go:101) when FlexGPU.Filter gets that far
-            const bool reach = flex_pod && kind != 3 && flex_ok && (nf & FGS_NF_REF_PANIC) && (prm.flex_filter_first || fit_ok) && valid;
-            if (reach) fl |= 1u;
-            if (flex_ok && fit_ok && valid && !reach) {
-                feas_mask |= 1u << j;
-                cnt++;
-                const i64 s = (kind == 1 || kind == 2) ? sflex : 0;
-                vflex = s > vflex ? s : vflex;
-                vhi = ar > vhi ? ar : vhi;
-                vnlo = -ar > vnlo ? -ar : vnlo;
-            }
-        }
-        cnt = __reduce_add_sync(0xffffffffu, cnt);
-        fl = __reduce_or_sync(0xffffffffu, fl);
-        if (sc_flex) vflex = warp_max_i64(vflex);
-        if (sc_alloc) {
-            vhi = warp_max_i64(vhi);
-            vnlo = warp_max_i64(vnlo);
-        }
-        if (lane == 0) {
-            s_part_a[cw * 4 + 0] = (i64)(cnt | (fl << 24));
-            s_part_a[cw * 4 + 1] = vflex;
-            s_part_a[cw * 4 + 2] = vhi;
-            s_part_a[cw * 4 + 3] = vnlo;
-        }
-        tick(0); // pod fetch + Filter on my nodes
-        __syncthreads(); // (1)
-
-        // ---- while the communication warp exchanges the phase-A results: the part of Score that needs none of
-        // them — Fit's Least/MostAllocated (least_allocated.go:29-57, most_allocated.go:29-61,
-        // resource_allocation.go:45-117) on my feasible nodes -----------------------------------------------
-        if (sc_fit) {
-            uint32_t fm = feas_mask;
-            while (fm) {
-                const int j = __ffs(fm) - 1;
-                fm &= fm - 1;
-                const i64 i = (i64)j * kSeqThreads + ct;
-                auto C = [&](int c) { return st[(i64)c * st_stride + i]; };
-                i64 node_score = 0, weight_sum = 0;
-                for (int k = 0; k < prm.fit_n_res; ++k) {
-                    const int res = prm.fit_res[k];
-                    i64 alloc = 0, req = 0;
-                    if (res == FGS_RES_CPU) {
-                        alloc = C(ND_CAP_CPU);
-                        req = C(ND_NZR_CPU) + nzc;
-                    } else if (res == FGS_RES_MEM) {
-                        alloc = C(ND_CAP_MEM);
-                        req = C(ND_NZR_MEM) + nzm;
-                    } else if (res == FGS_RES_EPH) {
-                        alloc = C(ND_ALLOC_EPH);
-                        req = (alloc - C(ND_FREE_EPH)) + re;
-                    } else if (res >= FGS_RES_SCALAR0 && res < FGS_RES_SCALAR0 + S) {
-                        const int s = res - FGS_RES_SCALAR0;
-                        const i64 pr = PC(PD_FIXED_COLS + s);
-                        if (pr != 0) { // resource_allocation.go:93-97
-                            alloc = C(nd_alloc_scalar(S, s));
-                            req = (alloc - C(nd_free_scalar(s))) + pr;
-                        }
-                    }
-                    if (alloc == 0) continue; // resource_allocation.go:64-67
-                    i64 rs;
-                    if (prm.fit_strategy == 0) rs = req > alloc ? 0 : go_div(wmul(alloc - req, 100), alloc);
-                    else rs = go_div(wmul(req > alloc ? alloc : req, 100), alloc);
-                    node_score = wadd(node_score, wmul(rs, prm.fit_w[k]));
-                    weight_sum = wadd(weight_sum, prm.fit_w[k]);
-                }
-                s_fit[j * kSeqThreads + ct] = weight_sum == 0 ? 0 : go_div(node_score, weight_sum);
-            }
-        }
-        tick(1); // Fit score, overlapped with exchange A
-        __syncthreads(); // (2)
-        const i64 count = (i64)(uint32_t)s_fin_a[0];
-        if (prof) consume(count);
-        tick(2); // waiting for exchange A
-        const uint32_t qcode = (uint32_t)(s_fin_a[0] >> 40) & 3u; // CapacityScheduling.PreFilter: 0 pass, 1 over Max, 2 over Σmin
-        const bool fpanic = ((s_fin_a[0] >> 32) & 1) && qcode == 0;
-        const i64 g_flex = s_fin_a[1], g_hi = s_fin_a[2], g_nlo = s_fin_a[3];
-
-        // ---- phase B: NormalizeScore / weights / selectHost key on my feasible nodes -------------------------
-        u64 key = 0;     // 0 = no candidate
-        uint32_t eb = 0; // FGS_PODERR_* raised while scoring
-        if (count > 0) { // uniform over the grid
-            const i64 fmax = g_flex > 0 ? g_flex : 0; // maxCount starts at 0 (normalize_score.go:27)
-            const i64 alo = -g_nlo;
-            const i64 arange = wsub(g_hi, alo);
-            uint32_t ph = (uint32_t)(prm.seed ^ (prm.seed >> 32)) ^ ((uint32_t)p * 0x9E3779B1u);
-            ph ^= ph >> 16;
-            ph *= 0x85EBCA6Bu;
-            ph ^= ph >> 13;
-            uint32_t fm = feas_mask;
-            while (fm) {
-                const int j = __ffs(fm) - 1;
-                fm &= fm - 1;
-                const i64 i = (i64)j * kSeqThreads + ct;
-                auto C = [&](int c) { return st[(i64)c * st_stride + i]; };
-                i64 t = 0;
-                if (sc_flex) {
-                    // FlexGPU.Score (flex_gpu.go:142-166) calls NewGPUNode first, for every pod kind (:148)
-                    if ((uint32_t)C(ND_FLAGS) & FGS_NF_REF_PANIC) eb |= FGS_PODERR_REF_PANIC;
-                    const i64 s = kind == 1 ? C(ND_GPU_SCORE) : (kind == 2 ? C(ND_MEM_SCORE) : 0);
-                    // DefaultNormalizeScore, reverse (normalize_score.go:26-54)
-                    const i64 v = fmax == 0 ? 100 : 100 - go_div(wmul(100, s), fmax);
-                    if (v > 100 || v < 0) eb |= FGS_PODERR_SCORE_RANGE; // runtime/framework.go:920-923
-                    t = wadd(t, wmul(v, prm.w_flex));
-                }
-                if (sc_fit) {
-                    const i64 v = s_fit[j * kSeqThreads + ct];
-                    if (v > 100 || v < 0) eb |= FGS_PODERR_SCORE_RANGE;
-                    t = wadd(t, wmul(v, prm.w_fit));
-                }
-                if (sc_alloc) { // allocatable.go:61-72,146-171
-                    const i64 v = arange == 0 ? 0 : go_div(wmul(wsub(C(ND_ALLOC_RAW), alo), 100), arange);
-                    if (v > 100 || v < 0) eb |= FGS_PODERR_SCORE_RANGE;
-                    t = wadd(t, wmul(v, prm.w_alloc));
-                }
-                // selectHost candidate (generic_scheduler.go:146-167): same key as the batched kernels
-                const uint32_t ng = (uint32_t)(node0 + i);
-                u64 k;
-                if (prm.key_shift == 40) {
-                    uint32_t h = (ph ^ ng) * 0x9E3779B1u;
-                    h ^= h >> 15;
-                    k = ((u64)t << 40) | ((u64)(h & 0xffffu) << 24) | ng;
-                } else {
-                    k = ((u64)t << 24) | ng;
-                }
-                k += 1;
-                key = k > key ? k : key;
-            }
-            key = (u64)warp_max_i64((i64)key);
-            eb = __reduce_or_sync(0xffffffffu, eb);
-            if (lane == 0) {
-                s_part_b[cw * 2 + 0] = key;
-                s_part_b[cw * 2 + 1] = eb;
-            }
-            tick(3); // NormalizeScore + key on my feasible nodes
-            __syncthreads(); // (3)
-            __syncthreads(); // (4)
-            key = s_fin_b[0];
-            if (prof) consume((i64)key);
-            tick(4); // waiting for exchange B
-            eb = (uint32_t)s_fin_b[1];
-        }
-
-        // ---- verdict of the cycle (every compute thread computes the same) ------------------------------------
-        uint32_t err = fpanic ? FGS_PODERR_REF_PANIC : 0u;
-        if (count >= 2) err |= eb; // scoring only runs with >= 2 feasible nodes (generic_scheduler.go:112-127)
-        i64 sel = -1, score = 0;
-        if (key > 0) {
-            const u64 k = key - 1;
-            sel = (i64)(k & 0xffffffu);
-            score = (i64)(k >> prm.key_shift);
-        }
-        const bool mine = sel >= node0 && sel < node0 + cta_nodes && (int)((sel - node0) % kSeqThreads) == ct;
-        if (!drain && (sel < 0 ? (cta == 0 && ct == 0) : mine)) {
-            int dev = FGS_RESERVE_SKIPPED;
-            bool commit = sel >= 0 && err == 0;
-            if (commit && prm.reserve_flex) {
-                dev = reserve_on_row(rw + (sel - node0), st_stride, st[(i64)ND_MEM_EACH * st_stride + (sel - node0)], S, D, kind, mem_lim);
-                if (dev == FGS_RESERVE_PANIC) err |= FGS_PODERR_REF_PANIC;
-                commit = dev >= 0 || dev == FGS_RESERVE_NONE;
-            }
-            if (commit) {
-                // assume: NodeInfo.AddPod (framework/types.go:583-609) on the raw row, then re-derive what a
-                // placement can change. All loads first, then the sums, then the stores.
-                const i64 i = sel - node0;
-                i64* row = rw + i;
-                auto A = [&](int c) -> i64& { return row[(i64)c * st_stride]; };
-                const i64 o_rc = A(NR_REQ_MCPU), o_rm = A(NR_REQ_MEM), o_re = A(NR_REQ_EPH), o_nzc = A(NR_NZ_MCPU), o_nzm = A(NR_NZ_MEM);
-                const i64 o_np = A(NR_NUM_PODS), o_gs = A(NR_FLEX_GPU_SUM), o_ms = A(NR_FLEX_MEM_SUM);
-                u64 meta = (u64)A(NR_META);
-                const i64 gpuCnt = ((uint32_t)meta & FGS_NF_HAS_GPU_RES) ? A(nr_alloc_scalar(FGS_SCALAR_FLEX_GPU)) : 0;
-                // the annotation constructGPUs (gpu_node.go:66-120) will read on the next cycle
-                const i64 annot = kind == 0 ? (i64)FGS_ANNOT_NONE : (dev >= 0 ? (i64)dev : PC(pd_cols(S) + SX_ANNOT));
-                const bool annot_ok = annot != (i64)FGS_ANNOT_NONE && annot >= 0 && annot < gpuCnt;
-                const i64 o_used = (annot_ok && (kind & 2u)) ? A(nr_used(S, (int)annot)) : 0;
-                i64 o_sc[FGS_MAX_SCALARS];
-#pragma unroll
-                for (int s = 0; s < FGS_MAX_SCALARS; ++s) o_sc[s] = s < S ? A(nr_req_scalar(S, s)) : 0;
-                bool in_range = true;
-                auto put = [&](int c, i64 v) {
-                    A(c) = v;
-                    in_range = in_range && v > -kMaxQuantity && v < kMaxQuantity;
-                };
-                put(NR_REQ_MCPU, o_rc + rc);
-                put(NR_REQ_MEM, o_rm + rm);
-                put(NR_REQ_EPH, o_re + re);
-#pragma unroll
-                for (int s = 0; s < FGS_MAX_SCALARS; ++s)
-                    if (s < S) put(nr_req_scalar(S, s), o_sc[s] + PC(PD_FIXED_COLS + s));
-                put(NR_NZ_MCPU, o_nzc + PC(pd_cols(S) + SX_ACCT_CPU));
-                put(NR_NZ_MEM, o_nzm + PC(pd_cols(S) + SX_ACCT_MEM));
-                put(NR_NUM_PODS, o_np + 1);
-                // what nodeResourceLimitSum (flex_gpu.go:133-140) will see
-                if (kind & 1u) put(NR_FLEX_GPU_SUM, o_gs + gpu_lim);
-                if (kind & 2u) put(NR_FLEX_MEM_SUM, o_ms + mem_lim);
-                if (annot != (i64)FGS_ANNOT_NONE) {
-                    if (!annot_ok) {
-                        meta |= FGS_NF_REF_PANIC; // gpus[index] out of range (gpu_node.go:110,115)
-                    } else {
-                        if (kind & 1u) meta |= 1ull << (32 + (int)annot);
-                        if (kind & 2u) put(nr_used(S, (int)annot), o_used + mem_lim);
-                    }
-                    A(NR_META) = (i64)meta;
-                }
-                if (!in_range) atomicMin(prm.status, (int)(p < 0x7fffffff ? p : 0x7ffffffe));
-                derive_row<true>(prm.dv, row, st_stride, st + i, st_stride);
-                if (SMEM) *s_dirty = (int)i; // the communication warp copies the row to the global tables
-                if (quota_on) *s_commit = 1; // → CapacityScheduling.Reserve of this pod, applied by the quota warp
-            }
-            prm.out[(i64)SO_COUNT * prm.p_pad + p] = count;
-            prm.out[(i64)SO_NODE * prm.p_pad + p] = sel;
-            prm.out[(i64)SO_SCORE * prm.p_pad + p] = score;
-            prm.out[(i64)SO_ERR * prm.p_pad + p] = (i64)err;
-            prm.out[(i64)SO_DEVICE * prm.p_pad + p] = (i64)dev;
-            prm.out[(i64)SO_COMMITTED * prm.p_pad + p] = commit ? 1 : 0;
-            prm.out[(i64)SO_QUOTA * prm.p_pad + p] = (i64)qcode;
-        }
-        tick(5); // verdict + commit (this thread's share)
-    }
-    __syncthreads();
-    if (SMEM && comm) flush_dirty();
-    if (prof)
-        for (int k = 0; k < 6; ++k) prm.prof[(size_t)cta * 16 + k] = (u64)pc[k];
-    if (cprof)
-        for (int k = 0; k < 4; ++k) prm.prof[(size_t)cta * 16 + 8 + k] = (u64)cc[k];
-    if (CLUSTER) cluster_sync_all(); // no CTA leaves while a peer could still address its shared memory
-}
-
-// FlexGPU.Reserve for a batch of (pod, node) pairs, no commit
-__global__ void reserve_kernel(const i64* __restrict__ raw, const i64* __restrict__ nd, i64 np, i64 n_nodes, int S, int D, const i64* __restrict__ pods, i64 p_pad,
-                               i64 n_pods, const int* __restrict__ node, int* __restrict__ dev) {
-    const i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n_pods) return;
-    const int n = node[p];
-    if (n < 0 || n >= n_nodes) {
-        dev[p] = FGS_RESERVE_SKIPPED;
-        return;
-    }
-    const uint32_t kind = (uint32_t)pods[(i64)PD_META * p_pad + p] & 3u;
-    dev[p] = reserve_on_row(raw + n, np, nd[(i64)ND_MEM_EACH * np + n], S, D, kind, pods[(i64)PD_MEM_LIM * p_pad + p]);
-}
-
-} // namespace
 
 // =================================================================================================
 // host side
@@ -1049,20 +235,27 @@ extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, c
     const char* env_cluster = getenv("FGS_SEQ_CLUSTER");
     const bool cluster_off = env_cluster && env_cluster[0] == '0';
     const bool state_global = getenv("FGS_SEQ_STATE_GLOBAL") && getenv("FGS_SEQ_STATE_GLOBAL")[0] == '1';
+    // speculative commit (two versions of every row in shared memory): one node per thread only
+    const bool spec_off = getenv("FGS_SEQ_SPEC") && getenv("FGS_SEQ_SPEC")[0] == '0';
+    const bool spec_fits = !spec_off && !state_global && seq_smem(e->S, e->D, 1, 2).total <= q->smem_optin;
+    auto pick = [&](bool cl, bool ssm, bool sp) -> const void* {
+        if (cl) return sp ? (const void*)seq_kernel<true, true, true> : (const void*)seq_kernel<true, true, false>;
+        if (ssm) return sp ? (const void*)seq_kernel<true, false, true> : (const void*)seq_kernel<true, false, false>;
+        return (const void*)seq_kernel<false, false, false>;
+    };
     int G = 0, K = 0, cluster = 0;
-    if (!cluster_off && !state_global && !env_ctas) {
-        for (int k = 1; k <= k_smem_max && !G; ++k)
-            for (int g = 1; g <= kMaxCluster; g *= 2)
-                if ((int64_t)g * kSeqThreads * k >= N) {
-                    G = g;
-                    K = k;
-                    cluster = g > 1;
-                    break;
-                }
+    if (!cluster_off && !state_global && !env_ctas && k_smem_max >= 1) {
+        for (int g = 1; g <= kMaxCluster; g *= 2) // one node per thread, or the single-cluster variant does not pay
+            if ((int64_t)g * kSeqThreads >= N) {
+                G = g;
+                K = 1;
+                cluster = g > 1;
+                break;
+            }
     }
     if (cluster) { // can a cluster of that size be resident at all? (16 is above the portable limit of 8)
-        const SeqSmem Lc = seq_smem(e->S, e->D, K, 1);
-        const void* kc = (const void*)seq_kernel<true, true>;
+        const SeqSmem Lc = seq_smem(e->S, e->D, K, spec_fits ? 2 : 1);
+        const void* kc = pick(true, true, spec_fits);
         cudaError_t ce = cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, Lc.total);
         if (ce == cudaSuccess && G > 8) ce = cudaFuncSetAttribute(kc, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         int n_clusters = 0;
@@ -1098,10 +291,11 @@ extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, c
         K = (int)K64;
     }
     const int state_smem = (!state_global && K <= k_smem_max) ? 1 : 0;
-    const SeqSmem L = seq_smem(e->S, e->D, K, state_smem);
-    const void* kfn = cluster ? (const void*)seq_kernel<true, true>
-                              : (state_smem ? (const void*)seq_kernel<true, false> : (const void*)seq_kernel<false, false>);
+    const bool spec = state_smem && K == 1 && spec_fits;
+    const SeqSmem L = seq_smem(e->S, e->D, K, state_smem ? (spec ? 2 : 1) : 0);
+    const void* kfn = pick(cluster != 0, state_smem != 0, spec);
     FGS_CUDA(e, cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+    if (cluster && G > 8) FGS_CUDA(e, cudaFuncSetAttribute(kfn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
 
     const size_t a_bytes = sizeof(u64) * 2 * (size_t)G * kWordsA, b_bytes = sizeof(u64) * 2 * (size_t)G * kWordsB;
     const bool want_prof = getenv("FGS_SEQ_PROFILE") && getenv("FGS_SEQ_PROFILE")[0] == '1';

@@ -108,8 +108,10 @@ def test_whole_gpu_passes_filter_but_reserve_fails(gpu_ok, oracle):
 # geometry variants: one thread-block cluster exchanging through distributed shared memory (the default for a
 # cluster this small; seq_ctas is reported negative), one CTA, global mailboxes with the node state in shared
 # memory, global mailboxes with the node state in global memory
+# ... and the same with the commit applied after the verdict instead of being built ahead of it (FGS_SEQ_SPEC=0)
 @pytest.mark.parametrize("env,ctas", [({}, -4), ({"FGS_SEQ_CTAS": "1"}, 1), ({"FGS_SEQ_CLUSTER": "0"}, 3),
-                                      ({"FGS_SEQ_CTAS": "3", "FGS_SEQ_STATE_GLOBAL": "1"}, 3)])
+                                      ({"FGS_SEQ_CTAS": "3", "FGS_SEQ_STATE_GLOBAL": "1"}, 3), ({"FGS_SEQ_SPEC": "0"}, -4),
+                                      ({"FGS_SEQ_CTAS": "2"}, 2)])
 @pytest.mark.parametrize("cfg_id", [1, 2])
 def test_synthetic_cluster_follows_the_oracle(gpu_ok, oracle, cfg_id, env, ctas):
     s = fgs.config_synth(cfg_id, n_nodes=700, n_pending=260, max_existing_pods=6, pm_invalid_nodes=10)
@@ -167,7 +169,7 @@ def test_most_allocated_and_allocatable_scores_without_reserve_plugin(gpu_ok, or
     eng.close()
 
 
-@pytest.mark.parametrize("env", [{}, {"FGS_SEQ_CLUSTER": "0"}, {"FGS_SEQ_CTAS": "1"}])
+@pytest.mark.parametrize("env", [{}, {"FGS_SEQ_CLUSTER": "0"}, {"FGS_SEQ_CTAS": "1"}, {"FGS_SEQ_SPEC": "0"}])
 def test_elastic_quota_prefilter_and_reserve_between_cycles(gpu_ok, oracle, env):
     # CapacityScheduling in the profile: every cycle starts with its PreFilter against the quotas as the earlier
     # commits left them; a committed pod is added to its namespace's Used (capacity_scheduling.go:201-275,340-353)
