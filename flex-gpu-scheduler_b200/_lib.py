@@ -163,6 +163,8 @@ ABI = {
     "fgs_upload_nodes": (C.c_int, [C.c_void_p, C.POINTER(NodeTable)]),
     "fgs_update_nodes": (C.c_int, [C.c_void_p, C.POINTER(NodeTable), p_i64]),
     "fgs_evaluate": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts), C.POINTER(Results)]),
+    "fgs_submit": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts)]),
+    "fgs_collect": (C.c_int, [C.c_void_p, C.POINTER(Results)]),
     "fgs_stage_pods": (C.c_int, [C.c_void_p, C.POINTER(PodTable)]),
     "fgs_pass_reduce": (C.c_int, [C.c_void_p]),
     "fgs_pass_emit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),

@@ -272,6 +272,20 @@ class Engine:
         r.next_start_node_index = int(cr.next_start_node_index)
         return r
 
+    def submit(self, pod_table, **opts):
+        """Enqueue one batch (fgs_submit); at most two may be in flight. Pair every submit with a collect()."""
+        P = int(pod_table.contents.n_pods)
+        o = self._opts(**opts)
+        self._check(self._lib.fgs_submit(self._h, pod_table, C.byref(o)))
+        self._pending = getattr(self, "_pending", []) + [P]
+
+    def collect(self):
+        """Per-pod results of the oldest submitted batch (blocks until it is done)."""
+        P = self._pending.pop(0)
+        r, cr = self._results(P, False)
+        self._check(self._lib.fgs_collect(self._h, C.byref(cr)))
+        return r
+
     def stage_pods(self, pod_table):
         self.n_pods = int(pod_table.contents.n_pods)
         self._check(self._lib.fgs_stage_pods(self._h, pod_table))

@@ -104,6 +104,18 @@ void Engine::free_all() {
     if (d_special) cudaFree(d_special);
     if (d_walk) cudaFree(d_walk);
     if (h_walk) cudaFreeHost(h_walk);
+    { // the pipeline slot the members do not alias right now
+        Slot& o = slots[cur_slot ^ 1];
+        if (o.d_pods) cudaFree(o.d_pods);
+        if (o.d_perpod) cudaFree(o.d_perpod);
+        if (o.d_pn) cudaFree(o.d_pn);
+        if (o.h_pods) cudaFreeHost(o.h_pods);
+        if (o.h_perpod) cudaFreeHost(o.h_perpod);
+        for (auto& sl : slots)
+            if (sl.ev_done) cudaEventDestroy(sl.ev_done);
+        if (ev_h2d) cudaEventDestroy(ev_h2d);
+        if (copy_stream) cudaStreamDestroy(copy_stream);
+    }
     if (h_raw) cudaFreeHost(h_raw);
     if (h_pods) cudaFreeHost(h_pods);
     if (h_perpod) cudaFreeHost(h_perpod);
@@ -578,14 +590,14 @@ extern "C" int fgs_update_nodes(fgs_engine* eh, const fgs_node_table* rows, cons
     return run_derive(e);
 }
 
-extern "C" int fgs_stage_pods(fgs_engine* eh, const fgs_pod_table* t) {
-    if (!eh) return FGS_E_INVALID;
-    Engine* e = (Engine*)eh;
+// async: called by fgs_submit — the staging buffers belong to a pipeline slot that is known to be free, so the
+// compute stream is not drained, and the H2D copy runs on the copy stream (it overlaps the previous batch's kernels)
+static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
     if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_stage_pods before fgs_upload_nodes");
     if (!t || t->n_pods < 0) return e->fail(FGS_E_INVALID, "pod table: null or negative size");
     if (t->n_scalars != e->S) return e->fail(FGS_E_INVALID, "pod table: n_scalars differs from the engine's");
     cudaSetDevice(e->device);
-    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (!async) FGS_CUDA(e, cudaStreamSynchronize(e->stream));
     int rc = e->ensure_pods(t->n_pods);
     if (rc) return rc;
     if (!e->nodes_derived) {
@@ -634,12 +646,25 @@ extern "C" int fgs_stage_pods(fgs_engine* eh, const fgs_pod_table* t) {
         e->stage_present_or = pr;
     }
     for (int s = 0; s < S; ++s) col(PD_FIXED_COLS + s, t->req_scalar + (int64_t)s * P);
-    FGS_CUDA(e, cudaMemcpyAsync(e->d_pods, e->h_pods, sizeof(int64_t) * pd_cols(S) * pp, cudaMemcpyHostToDevice, e->stream));
+    if (async) {
+        FGS_CUDA(e, cudaMemcpyAsync(e->d_pods, e->h_pods, sizeof(int64_t) * pd_cols(S) * pp, cudaMemcpyHostToDevice, e->copy_stream));
+        FGS_CUDA(e, cudaEventRecord(e->ev_h2d, e->copy_stream));
+        FGS_CUDA(e, cudaStreamWaitEvent(e->stream, e->ev_h2d, 0));
+    } else {
+        FGS_CUDA(e, cudaMemcpyAsync(e->d_pods, e->h_pods, sizeof(int64_t) * pd_cols(S) * pp, cudaMemcpyHostToDevice, e->stream));
+    }
     rc = e->decide_narrow(t); // int32 tables for this batch when every value qualifies
     if (rc) return rc;
     FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
     e->have_pods = true;
     return FGS_OK;
+}
+
+extern "C" int fgs_stage_pods(fgs_engine* eh, const fgs_pod_table* t) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_stage_pods while submitted batches are in flight: fgs_collect them first");
+    return stage_pods_impl(e, t, false);
 }
 
 // The reference's node sampling on top of the reduce pass's full bitmap (sample.cu): walk, truncate, re-reduce.
@@ -842,5 +867,87 @@ extern "C" int fgs_get_timings(fgs_engine* eh, fgs_timings* t) {
     t->kernel_launches = e->launches;
     t->reduce_int32 = e->reduce_was_narrow ? 1 : 0;
     t->emit_int32 = e->emit_was_narrow ? 1 : 0;
+    return FGS_OK;
+}
+
+// =================================================================================================
+// fgs_submit / fgs_collect — the same evaluation with two batches in flight
+// =================================================================================================
+// A stream of batches through fgs_evaluate serialises, per batch, the host-side staging, the H2D copy, the two
+// passes, the D2H of the results and their unpacking. Here the per-batch buffers exist twice (slots): while the
+// kernels of batch k run, the host already stages batch k+1 into the other slot, its H2D copy runs on a copy
+// stream, and batch k-1's results are unpacked. The bitmap / score planes are shared (the kernels of consecutive
+// batches are ordered on the compute stream), so a submitted batch returns per-pod results only.
+
+void Engine::bind_slot(int k) {
+    Slot& o = slots[cur_slot];
+    o.d_pods = d_pods, o.h_pods = h_pods, o.d_perpod = d_perpod, o.h_perpod = h_perpod, o.d_pn = d_pn;
+    o.p_pad_cap = p_pad_cap, o.pn_cap = pn_cap, o.n_pods = n_pods, o.p_pad = p_pad;
+    o.narrow_batch = narrow_batch, o.emitted = emitted, o.sampled = sampled, o.have_pods = have_pods, o.key_shift = last_key_shift;
+    const Slot& n = slots[k];
+    d_pods = n.d_pods, h_pods = n.h_pods, d_perpod = n.d_perpod, h_perpod = n.h_perpod, d_pn = n.d_pn;
+    p_pad_cap = n.p_pad_cap, pn_cap = n.pn_cap, n_pods = n.n_pods, p_pad = n.p_pad;
+    narrow_batch = n.narrow_batch, emitted = n.emitted, sampled = n.sampled, have_pods = n.have_pods, last_key_shift = n.key_shift;
+    cur_slot = k;
+}
+
+extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (e->in_flight >= 2) return e->fail(FGS_E_STATE, "fgs_submit: two batches are in flight already; fgs_collect one first");
+    if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_submit: sample / skip_pass_b need fgs_evaluate");
+    cudaSetDevice(e->device);
+    if (!e->copy_stream) {
+        FGS_CUDA(e, cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+        FGS_CUDA(e, cudaEventCreateWithFlags(&e->ev_h2d, cudaEventDisableTiming));
+        for (auto& sl : e->slots) FGS_CUDA(e, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
+    }
+    // the slot that is not in flight (in_flight == 1: the other one; 0: keep the current one)
+    const int k = e->in_flight == 0 ? e->cur_slot : (e->oldest_slot ^ 1);
+    if (k != e->cur_slot) e->bind_slot(k);
+    if (e->in_flight == 0) e->oldest_slot = k;
+    int rc = stage_pods_impl(e, pods, true);
+    if (rc) return rc;
+    e->emitted = false;
+    rc = fgs_pass_reduce(eh);
+    if (rc) return rc;
+    rc = fgs_pass_emit(eh, opts);
+    if (rc) return rc;
+    const int64_t P = e->n_pods, pp = e->p_pad;
+    int64_t* d_compact = (int64_t*)e->d_perpod + (int64_t)kCompactRow0 * pp;
+    launch_finalize_pods((const int64_t*)e->d_perpod, d_compact, P, pp, e->last_key_shift, 1, (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0, e->stream);
+    e->launches++;
+    FGS_CUDA(e, cudaGetLastError());
+    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, d_compact, sizeof(int64_t) * 4 * pp, cudaMemcpyDeviceToHost, e->stream));
+    FGS_CUDA(e, cudaEventRecord(e->slots[k].ev_done, e->stream));
+    e->slots[k].busy = true;
+    e->in_flight++;
+    return FGS_OK;
+}
+
+extern "C" int fgs_collect(fgs_engine* eh, fgs_results* out) {
+    if (!eh || !out) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (e->in_flight == 0) return e->fail(FGS_E_STATE, "fgs_collect: nothing was submitted");
+    cudaSetDevice(e->device);
+    const int k = e->oldest_slot;
+    FGS_CUDA(e, cudaEventSynchronize(e->slots[k].ev_done));
+    // the oldest batch's host buffer: the members alias slot cur_slot, the other slot keeps its own copy
+    const bool is_cur = k == e->cur_slot;
+    const int64_t P = is_cur ? e->n_pods : e->slots[k].n_pods, pp = is_cur ? e->p_pad : e->slots[k].p_pad;
+    const int64_t* h = (const int64_t*)(is_cur ? e->h_perpod : e->slots[k].h_perpod);
+    for (int64_t p = 0; p < P; ++p) {
+        if (out->feasible_count) out->feasible_count[p] = (int32_t)h[p];
+        if (out->selected_node) out->selected_node[p] = (int32_t)h[pp + p];
+        if (out->selected_score) out->selected_score[p] = h[2 * pp + p];
+        if (out->pod_err) out->pod_err[p] = (uint32_t)h[3 * pp + p];
+        if (out->processed_nodes) out->processed_nodes[p] = (int32_t)e->n_nodes;
+    }
+    out->words_per_row = e->words_per_row;
+    out->score_row_stride = e->score_stride;
+    out->next_start_node_index = -1;
+    e->slots[k].busy = false;
+    e->in_flight--;
+    e->oldest_slot = k ^ 1;
     return FGS_OK;
 }

@@ -68,6 +68,23 @@ struct Engine {
     int decide_narrow(const fgs_pod_table* t);
     void fill_narrow_params(NarrowParams* p) const;
 
+    // fgs_submit / fgs_collect: two batches in flight. A slot owns the per-batch buffers; the engine's members
+    // above (d_pods, h_pods, d_perpod, h_perpod, d_pn, …) always alias the slot being filled.
+    struct Slot {
+        void *d_pods = nullptr, *h_pods = nullptr, *d_perpod = nullptr, *h_perpod = nullptr, *d_pn = nullptr;
+        int64_t p_pad_cap = 0, pn_cap = 0, n_pods = 0, p_pad = 0;
+        bool narrow_batch = false, emitted = false, sampled = false, have_pods = false, busy = false;
+        int key_shift = 40;
+        cudaEvent_t ev_done = nullptr;
+    };
+    Slot slots[2];
+    int cur_slot = 0;       // slot whose buffers the members alias
+    int in_flight = 0;      // submitted, not yet collected
+    int oldest_slot = 0;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_h2d = nullptr;
+    void bind_slot(int k);  // save the members into slots[cur_slot], load slots[k]
+
     // node sampling (sample.cu): per-pod walks of the current batch
     void* d_walk = nullptr;    // int2 [p_pad] + one int64 (nextStartNodeIndex)
     void* h_walk = nullptr;

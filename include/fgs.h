@@ -159,6 +159,16 @@ int fgs_update_nodes(fgs_engine* e, const fgs_node_table* rows, const int64_t* d
 int fgs_evaluate(fgs_engine* e, const fgs_pod_table* pods, const fgs_eval_opts* opts,
                  fgs_results* out);
 
+/* fgs_evaluate for a STREAM of batches, two in flight: fgs_submit stages the batch (into the buffers the
+ * previous-but-one batch has released), copies it on a copy stream and enqueues both passes and the D2H of the
+ * per-pod results, then returns; fgs_collect blocks until the OLDEST submitted batch is done and unpacks its
+ * per-pod results. While the kernels of one batch run, the host stages the next and unpacks the previous one.
+ * At most two batches may be in flight (a third fgs_submit before fgs_collect → FGS_E_STATE). The bitmap / score
+ * planes are shared by consecutive batches, so `out` receives per-pod results only; fgs_evaluate, the staged
+ * calls and the plane getters are refused while batches are in flight. No sampling / skip_pass_b here. */
+int fgs_submit(fgs_engine* e, const fgs_pod_table* pods, const fgs_eval_opts* opts);
+int fgs_collect(fgs_engine* e, fgs_results* out);
+
 /* The same evaluation in stages, for node-sharded multi-GPU runs (one engine per GPU/process):
  *   fgs_stage_pods → fgs_pass_reduce → [merge reduce_max / reduce_sum across shards]
  *   → fgs_pass_emit → [merge select_key across shards] → fgs_fetch_results.

@@ -340,3 +340,40 @@ def test_reason_planes_match_the_oracle(gpu_ok, oracle):
     for p in range(3):
         assert np.array_equal(fit[p], oracle.filter_reasons(snap.ptr, pend.ptr, cfg, p)[1])
     eng.close()
+
+
+def test_submit_collect_pipeline_equals_evaluate(gpu_ok):
+    """fgs_submit / fgs_collect (two batches in flight, double-buffered staging) returns what fgs_evaluate returns,
+    batch after batch, including batches of different sizes."""
+    s = fgs.config_synth(2, n_nodes=3000, n_pending=5000, pm_extra_scalar=0)
+    cfg = fgs.config_plugins(2)
+    eng = fgs.Engine(device=0)
+    eng.set_plugins(cfg)
+    eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot))
+    bounds = [(0, 700), (700, 2048), (2048, 2049), (2049, 4000), (4000, 5000), (0, 5000), (100, 164)]
+    packers = [fgs.Packer(2) for _ in bounds]
+    tables = [pk.pods(s.pending, a, b) for pk, (a, b) in zip(packers, bounds)]
+    want = [eng.evaluate(t) for t in tables]
+    got = []
+    eng.submit(tables[0])
+    for t in tables[1:]:
+        eng.submit(t)
+        got.append(eng.collect())
+    got.append(eng.collect())
+    for w, g in zip(want, got):
+        assert np.array_equal(w.feasible_count, g.feasible_count)
+        assert np.array_equal(w.selected_node, g.selected_node)
+        assert np.array_equal(w.selected_score, g.selected_score)
+        assert np.array_equal(w.pod_err, g.pod_err)
+    # a third submit without a collect is refused, and so is the synchronous path while batches are in flight
+    eng.submit(tables[0])
+    eng.submit(tables[1])
+    with pytest.raises(fgs.FgsError):
+        eng.submit(tables[2])
+    with pytest.raises(fgs.FgsError):
+        eng.evaluate(tables[2])
+    a, b = eng.collect(), eng.collect()
+    assert np.array_equal(a.selected_node, want[0].selected_node) and np.array_equal(b.selected_node, want[1].selected_node)
+    again = eng.evaluate(tables[3])  # the synchronous path works again once everything is collected
+    assert np.array_equal(again.selected_node, want[3].selected_node)
+    eng.close()
