@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
             if (SPEC & SP_SC_FLEX) { // raw FlexGPU score by pod kind (flex_gpu.go:153-165), max over the feasible nodes
                 int sj[kNPTr];
 #pragma unroll
-                for (int j = 0; j < kNPTr; ++j) sj[j] = kind == 1 ? gsc[j] : (kind == 2 ? msc[j] : 0);
+                for (int j = 0; j < kNPTr; ++j) sj[j] = (kind & 1) ? gsc[j] : (kind == 2 ? msc[j] : 0); // a gpu limit wins over a memory limit (:157-159)
 #pragma unroll
                 for (int j = 0; j < kNPTr; ++j) vflex = max(vflex, feas[j] ? sj[j] : kNone);
                 vflex = __reduce_max_sync(0xffffffffu, vflex);
@@ -538,8 +538,8 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                 if (kFlex) { // FlexGPU.Score + DefaultNormalizeScore(reverse) (flex_gpu.go:142-176, normalize_score.go:26-54)
                     int v = 100;
                     if (q4.x != 0 && kind != 0) {
-                        const int s100 = kind == 1 ? g100[j] : m100[j];
-                        const float sf = kind == 1 ? g100f[j] : m100f[j];
+                        const int s100 = (kind & 1) ? g100[j] : m100[j]; // a gpu limit wins over a memory limit (flex_gpu.go:157-159)
+                        const float sf = (kind & 1) ? g100f[j] : m100f[j];
                         const int q = qfix32(s100, q4.x, sf * q3.z);
                         v = (kind == 2 && mneg[j]) ? 100 + q : 100 - q;
                     }

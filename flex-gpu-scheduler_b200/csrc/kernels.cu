@@ -394,7 +394,8 @@ __global__ void __launch_bounds__(kThreads, 2) eval_kernel(const __grid_constant
 #pragma unroll
                 for (int j = 0; j < kNodesPerThread; ++j) {
                     if (feas[j]) {
-                        const i64 s = kind == 1 ? nr[j].gscore : (kind == 2 ? nr[j].mscore : 0);
+                        // a gpu limit wins over a memory limit (flex_gpu.go:157-159)
+                        const i64 s = (kind & 1u) ? nr[j].gscore : (kind == 2 ? nr[j].mscore : 0);
                         vflex = s > vflex ? s : vflex;
                         vhi = nr[j].araw > vhi ? nr[j].araw : vhi;
                         const i64 nl = -nr[j].araw;
@@ -426,14 +427,14 @@ __global__ void __launch_bounds__(kThreads, 2) eval_kernel(const __grid_constant
                     i64 t = 0;
                     // FlexGPU.Score (flex_gpu.go:142-166) + DefaultNormalizeScore reverse (normalize_score.go:26-54)
                     if (sc_flex && (prm.emit_mask & FGS_PL_FLEXGPU)) {
-                        const i64 s = kind == 1 ? r.gscore : (kind == 2 ? r.mscore : 0);
+                        const i64 s = (kind & 1u) ? r.gscore : (kind == 2 ? r.mscore : 0);
                         i64 v;
                         if (prm.emit_raw) {
                             v = s;
                         } else if (u.fmax == 0) {
                             v = 100;
                         } else if (s >= 0) {
-                            const float sf = kind == 1 ? r.gs100f : r.ms100f;
+                            const float sf = (kind & 1u) ? r.gs100f : r.ms100f;
                             v = 100 - qfix(100 * s, u.fmax, sf * u.finv);
                         } else {
                             v = 100 - wmul(100, s) / u.fmax; // Go '/' truncates toward zero, as does C++

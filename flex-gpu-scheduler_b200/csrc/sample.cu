@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(256) reduce_from_bitmap(const uint32_t* __rest
     const int lane = threadIdx.x & 31;
     if (p >= n_pods) return;
     const uint32_t kind = (uint32_t)pods[(i64)PD_META * p_pad + p] & 3u;
-    const i64* sc = nd + (i64)(kind == 1 ? ND_GPU_SCORE : ND_MEM_SCORE) * n_pad;
+    const i64* sc = nd + (i64)((kind & 1u) ? ND_GPU_SCORE : ND_MEM_SCORE) * n_pad; // a gpu limit wins (flex_gpu.go:157-159)
     const i64* ar = nd + (i64)ND_ALLOC_RAW * n_pad;
     i64 vflex = kMin64, vhi = kMin64, vnlo = kMin64;
     for (i64 w = lane; w < W; w += 32) {
@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(256) reduce_from_bitmap(const uint32_t* __rest
             const int bit = __ffs(x) - 1;
             x &= x - 1;
             const i64 n = w * 32 + bit;
-            const i64 s = (kind == 1 || kind == 2) ? sc[n] : 0; // FlexGPU.Score, flex_gpu.go:150-165
+            const i64 s = kind != 0 ? sc[n] : 0; // FlexGPU.Score, flex_gpu.go:150-165
             const i64 a = ar[n];
             vflex = s > vflex ? s : vflex;
             vhi = a > vhi ? a : vhi;

@@ -746,7 +746,7 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
             const uint32_t nf = (uint32_t)C(ND_FLAGS);
             const i64 thr = C(kind == 1 ? ND_THR_GPU : ND_THR_MEM);
             const i64 fc = C(ND_FREE_CPU), fm_ = C(ND_FREE_MEM), fe = C(ND_FREE_EPH);
-            const i64 sflex = C(kind == 1 ? ND_GPU_SCORE : ND_MEM_SCORE);
+            const i64 sflex = C((kind & 1u) ? ND_GPU_SCORE : ND_MEM_SCORE); // a gpu limit wins over a memory limit (flex_gpu.go:157-159)
             const i64 ar = C(ND_ALLOC_RAW);
             // FlexGPU.Filter, flex_gpu.go:41-119, folded into one threshold per pod kind (derive.cuh)
             const bool flex_ok = !flex_pod || (kind != 3 && lim <= thr);
@@ -768,7 +768,7 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
             if (flex_ok && fit_ok && valid && !reach) {
                 feas_mask |= 1u << j;
                 cnt++;
-                const i64 s = (kind == 1 || kind == 2) ? sflex : 0;
+                const i64 s = kind != 0 ? sflex : 0;
                 vflex = s > vflex ? s : vflex;
                 vhi = ar > vhi ? ar : vhi;
                 vnlo = -ar > vnlo ? -ar : vnlo;
@@ -865,7 +865,7 @@ __global__ void __launch_bounds__(kSeqBlock, 1) seq_kernel(const __grid_constant
                 if (sc_flex) {
                     // FlexGPU.Score (flex_gpu.go:142-166) calls NewGPUNode first, for every pod kind (:148)
                     if ((uint32_t)C(ND_FLAGS) & FGS_NF_REF_PANIC) eb |= FGS_PODERR_REF_PANIC;
-                    const i64 s = kind == 1 ? C(ND_GPU_SCORE) : (kind == 2 ? C(ND_MEM_SCORE) : 0);
+                    const i64 s = (kind & 1u) ? C(ND_GPU_SCORE) : (kind == 2 ? C(ND_MEM_SCORE) : 0);
                     // DefaultNormalizeScore, reverse (normalize_score.go:26-54)
                     const i64 v = fmax == 0 ? 100 : 100 - go_div(wmul(100, s), fmax);
                     if (v > 100 || v < 0) eb |= FGS_PODERR_SCORE_RANGE; // runtime/framework.go:920-923

@@ -110,6 +110,9 @@ CONFIG_CASES = [
     ("filter-only-flex", dict(cfg=2, n_nodes=300, n_pending=200), dict(filter_plugins=("FlexGPU",), score_plugins=(("FlexGPU", 1),))),
     ("ignored-scalar", dict(cfg=2, n_nodes=300, n_pending=200, n_scalars=3, pm_extra_scalar=500), dict(fit_ignored_scalar_mask=0b100)),
     ("huge-weight-keys", dict(cfg=2, n_nodes=300, n_pending=200), dict(score_plugins=(("FlexGPU", 50000), ("NodeResourcesFit", 70000)))),
+    # FlexGPU scores without filtering: pods with BOTH limits stay feasible and are scored by GPUScore (flex_gpu.go:157-159)
+    ("flex-score-without-flex-filter", dict(cfg=2, n_nodes=400, n_pending=300, pm_degenerate=300, pm_invalid_nodes=20),
+     dict(filter_plugins=("NodeResourcesFit",), score_plugins=(("FlexGPU", 2), ("NodeResourcesFit", 1)))),
 ]
 
 
