@@ -171,6 +171,9 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
         u.rs0 = raw[PN_RS0 * kTileP + tid];
         u.rs1 = raw[PN_RS1 * kTileP + tid];
         u.kind = raw[PN_KIND * kTileP + tid];
+        // both limits: the Filter side never passes (its limit columns hold kNever) and Score takes GPUScore — a gpu
+        // limit wins over a memory limit (flex_gpu.go:157-159) — so from here on the pod is a whole-GPU pod
+        if (u.kind == 3) u.kind = 1;
         ((PodR*)(smem + L.pod))[stage * kTileP + tid] = u;
     };
     if (tid == 0) {
@@ -266,7 +269,7 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
             if (SPEC & SP_SC_FLEX) { // raw FlexGPU score by pod kind (flex_gpu.go:153-165), max over the feasible nodes
                 int sj[kNPTr];
 #pragma unroll
-                for (int j = 0; j < kNPTr; ++j) sj[j] = (kind & 1) ? gsc[j] : (kind == 2 ? msc[j] : 0); // a gpu limit wins over a memory limit (:157-159)
+                for (int j = 0; j < kNPTr; ++j) sj[j] = kind == 1 ? gsc[j] : (kind == 2 ? msc[j] : 0);
 #pragma unroll
                 for (int j = 0; j < kNPTr; ++j) vflex = max(vflex, feas[j] ? sj[j] : kNone);
                 vflex = __reduce_max_sync(0xffffffffu, vflex);
@@ -347,8 +350,8 @@ struct __align__(16) PodE { // 64 bytes: four broadcast LDS.128 per pod
     int nzc, nzm, nz100c, nz100m;
     float fnzc, fnzm, finv, ainv;
     int fmax, count, arange32, kind; // arange32 < 0: exact 64-bit path for Allocatable
-    uint32_t hmul;
-    int _pad;
+    uint32_t hmul; // per-pod hash (cross-tile tie mixing in the flush)
+    int hpos;      // 8 of its bits at positions 10..17: XORed with the node's bits in the key
     i64 alo;
 };
 
@@ -450,7 +453,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         h ^= h >> 15;
         h *= 0x9E3779B1u;
         u.hmul = h | 1u;
-        u._pad = 0;
+        u.hpos = (int)(((h >> 20) & 0xffu) << 10);
         ((PodE*)(smem + L.pod))[stage * kTileP + tid] = u;
     };
     if (tid == 0) {
@@ -468,10 +471,13 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     // node tile → registers
     int capc[kNPTe], xc[kNPTe], x100c[kNPTe], capm[kNPTe], xm[kNPTe], x100m[kNPTe], g100[kNPTe], m100[kNPTe], nloc[kNPTe], inr[kNPTe], mneg[kNPTe];
     float invc[kNPTe], xqc[kNPTe], invm[kNPTe], xqm[kNPTe], g100f[kNPTe], m100f[kNPTe];
+    uint32_t nbase[kNPTe], nh[kNPTe];
     i64 araw[kNPTe];
 #pragma unroll
     for (int j = 0; j < kNPTe; ++j) {
         nloc[j] = warp * (32 * kNPTe) + j * 32 + lane;
+        nbase[j] = (1u << 18) | (uint32_t)nloc[j];
+        nh[j] = (((uint32_t)nloc[j] * 0x9E3779B1u) >> 24) << 10; // the node's 8 tie-break bits, at bits 10..17
         const i64 n = node_tile0 + nloc[j];
         inr[j] = n < prm.n_nodes ? 1 : 0;
         auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
@@ -526,71 +532,81 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
             const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz100c nz100m
             const float4 q3 = *(const float4*)&s_pod[jp].fnzc; // fnzc fnzm finv ainv
             const int4 q4 = *(const int4*)&s_pod[jp].fmax;     // fmax count arange32 kind
-            const uint32_t hmul = s_pod[jp].hmul;
             const uint4 fw = *(const uint4*)(bmrow + jp * kWordsTe);
             const bool feas[kNPTe] = {(fw.x & lanebit) != 0, (fw.y & lanebit) != 0, (fw.z & lanebit) != 0, (fw.w & lanebit) != 0};
             const int kind = q4.w;
-            int tot[kNPTe];
-            uint32_t key = 0;
+            const uint32_t ph = (uint32_t)s_pod[jp].hpos; // the pod's 8 tie-break bits, already at bits 10..17
+            // The pod kind and "max flex score == 0" are uniform over the tile: one copy of the node loop per case
+            // instead of per-node selects. KS = 0: the FlexGPU term is the constant 100 (no limit, or max == 0);
+            // 1: GPUScore (a gpu limit wins over a memory limit, flex_gpu.go:157-159); 2: MemScore.
+            auto pod_body = [&](auto KSEL) {
+                constexpr int KS = decltype(KSEL)::value;
+                int tot[kNPTe];
+                uint32_t key = 0;
 #pragma unroll
-            for (int j = 0; j < kNPTe; ++j) {
-                int t = 0;
-                if (kFlex) { // FlexGPU.Score + DefaultNormalizeScore(reverse) (flex_gpu.go:142-176, normalize_score.go:26-54)
-                    int v = 100;
-                    if (q4.x != 0 && kind != 0) {
-                        const int s100 = (kind & 1) ? g100[j] : m100[j]; // a gpu limit wins over a memory limit (flex_gpu.go:157-159)
-                        const float sf = (kind & 1) ? g100f[j] : m100f[j];
-                        const int q = qfix32(s100, q4.x, sf * q3.z);
-                        v = (kind == 2 && mneg[j]) ? 100 + q : 100 - q;
+                for (int j = 0; j < kNPTe; ++j) {
+                    int t = 0;
+                    if (kFlex) { // FlexGPU.Score + DefaultNormalizeScore(reverse) (flex_gpu.go:142-176, normalize_score.go:26-54)
+                        int v = 100;
+                        if (KS == 1) {
+                            v = 100 - qfix32(g100[j], q4.x, g100f[j] * q3.z);
+                        } else if (KS == 2) { // magnitude and sign: Go's '/' truncates toward zero
+                            const int q = qfix32(m100[j], q4.x, m100f[j] * q3.z);
+                            v = mneg[j] ? 100 + q : 100 - q;
+                        }
+                        t += v * prm.w_flex;
                     }
-                    t += v * prm.w_flex;
+                    if (kFit) { // Least/MostAllocated over cpu and memory, non-zero requests (least_allocated.go:29-57, most_allocated.go:29-61)
+                        int sc, sm;
+                        if (!kMost) {
+                            sc = qfix32(x100c[j] - q2.z, capc[j], fmaf(-q3.x, invc[j], xqc[j]));
+                            sm = qfix32(x100m[j] - q2.w, capm[j], fmaf(-q3.y, invm[j], xqm[j]));
+                            sc = q2.x > xc[j] ? 0 : sc; // requested > capacity → 0
+                            sm = q2.y > xm[j] ? 0 : sm;
+                        } else {
+                            sc = qfix32(x100c[j] + q2.z, capc[j], fmaf(q3.x, invc[j], xqc[j]));
+                            sm = qfix32(x100m[j] + q2.w, capm[j], fmaf(q3.y, invm[j], xqm[j]));
+                            sc = q2.x > capc[j] - xc[j] ? 100 : sc; // requested clamps to capacity
+                            sm = q2.y > capm[j] - xm[j] ? 100 : sm;
+                        }
+                        int v;
+                        if (SPEC & SP_W_EQ) {
+                            v = (sc + sm) >> 1;
+                        } else { // Σ score·w / Σ w, w in [1,100]: exact through a float floor
+                            const int num = sc * prm.fit_w_cpu + sm * prm.fit_w_mem;
+                            v = __float_as_int(__fadd_rd(((float)num + 0.5f) * prm.fit_inv_wsum, 8388608.0f)) & 0x7fffff;
+                        }
+                        t += v * prm.w_fit;
+                    }
+                    if (kAlloc) { // Allocatable.NormalizeScore (allocatable.go:146-171)
+                        int v = 0;
+                        if (q4.z > 0) {
+                            const int a = (int)(uint32_t)((u64)araw[j] - (u64)s_pod[jp].alo);
+                            v = qfix32((int)(100u * (uint32_t)a), q4.z, (float)a * q3.w);
+                        } else if (q4.z < 0) {
+                            const i64 alo = s_pod[jp].alo;
+                            const i64 range = (i64)((u64)__ldg((const i64*)prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + tile_p0 + jp) - (u64)alo);
+                            v = (int)((i64)((u64)((i64)((u64)araw[j] - (u64)alo)) * 100ull) / range);
+                        }
+                        t += v * prm.w_alloc;
+                    }
+                    tot[j] = t;
+                    // selectHost candidate: score+1 (14 bits) | 8 tie-break bits | node-in-tile (10 bits); 0 = none
+                    // (generic_scheduler.go:146-167). nbase = 1<<18 | node-in-tile, nh = the node's 8 hash bits in place:
+                    // one LOP3 and one IMAD per node
+                    const uint32_t k = (uint32_t)t * 262144u + ((nh[j] ^ ph) | nbase[j]);
+                    key = max(key, feas[j] ? k : 0u);
                 }
-                if (kFit) { // Least/MostAllocated over cpu and memory, non-zero requests (least_allocated.go:29-57, most_allocated.go:29-61)
-                    int sc, sm;
-                    if (!kMost) {
-                        sc = qfix32(x100c[j] - q2.z, capc[j], fmaf(-q3.x, invc[j], xqc[j]));
-                        sm = qfix32(x100m[j] - q2.w, capm[j], fmaf(-q3.y, invm[j], xqm[j]));
-                        sc = q2.x > xc[j] ? 0 : sc; // requested > capacity → 0
-                        sm = q2.y > xm[j] ? 0 : sm;
-                    } else {
-                        sc = qfix32(x100c[j] + q2.z, capc[j], fmaf(q3.x, invc[j], xqc[j]));
-                        sm = qfix32(x100m[j] + q2.w, capm[j], fmaf(q3.y, invm[j], xqm[j]));
-                        sc = q2.x > capc[j] - xc[j] ? 100 : sc; // requested clamps to capacity
-                        sm = q2.y > capm[j] - xm[j] ? 100 : sm;
-                    }
-                    int v;
-                    if (SPEC & SP_W_EQ) {
-                        v = (sc + sm) >> 1;
-                    } else { // Σ score·w / Σ w, w in [1,100]: exact through a float floor
-                        const int num = sc * prm.fit_w_cpu + sm * prm.fit_w_mem;
-                        v = __float_as_int(__fadd_rd(((float)num + 0.5f) * prm.fit_inv_wsum, 8388608.0f)) & 0x7fffff;
-                    }
-                    t += v * prm.w_fit;
-                }
-                if (kAlloc) { // Allocatable.NormalizeScore (allocatable.go:146-171)
-                    int v = 0;
-                    if (q4.z > 0) {
-                        const int a = (int)(uint32_t)((u64)araw[j] - (u64)s_pod[jp].alo);
-                        v = qfix32((int)(100u * (uint32_t)a), q4.z, (float)a * q3.w);
-                    } else if (q4.z < 0) {
-                        const i64 alo = s_pod[jp].alo;
-                        const i64 range = (i64)((u64)__ldg((const i64*)prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + tile_p0 + jp) - (u64)alo);
-                        v = (int)((i64)((u64)((i64)((u64)araw[j] - (u64)alo)) * 100ull) / range);
-                    }
-                    t += v * prm.w_alloc;
-                }
-                tot[j] = t;
-                // selectHost candidate: score+1 (14 bits) | 8 hash bits | node-in-tile (10 bits); 0 = none
-                // (generic_scheduler.go:146-167)
-                const uint32_t low = (((uint32_t)nloc[j] * hmul) >> 14 & 0x3fc00u) | (uint32_t)nloc[j];
-                const uint32_t k = ((uint32_t)(t + 1) << 18) | low;
-                key = max(key, feas[j] ? k : 0u);
-            }
 #pragma unroll
-            for (int j = 0; j < kNPTe; ++j)
-                if (inr[j]) __stcs(rowp + 32 * j, (i64)(u64)(uint32_t)tot[j]);
-            key = __reduce_max_sync(0xffffffffu, key);
-            if (lane == 0) wkey[jp * kWarps + warp] = key;
+                for (int j = 0; j < kNPTe; ++j)
+                    if (inr[j]) __stcs(rowp + 32 * j, (i64)(u64)(uint32_t)tot[j]);
+                key = __reduce_max_sync(0xffffffffu, key);
+                if (lane == 0) wkey[jp * kWarps + warp] = key;
+            };
+            const int ks = (kFlex && q4.x != 0) ? ((kind & 1) ? 1 : (kind == 2 ? 2 : 0)) : 0;
+            if (ks == 2) pod_body(std::integral_constant<int, 2>{});
+            else if (ks == 1) pod_body(std::integral_constant<int, 1>{});
+            else pod_body(std::integral_constant<int, 0>{});
         }
         if (tid < kTileP && it + 1 < n_tiles) derive(it + 1);
         __syncthreads();
