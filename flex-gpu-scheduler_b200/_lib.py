@@ -86,7 +86,7 @@ class PodTable(C.Structure):
         ("flex_gpu_limit", p_i64), ("flex_mem_limit", p_i64), ("flags", p_u32),
         ("req_mcpu", p_i64), ("req_mem", p_i64), ("req_eph", p_i64), ("req_scalar", p_i64), ("req_scalar_present", p_u32),
         ("nz_mcpu", p_i64), ("nz_mem", p_i64), ("ns", p_i32), ("pg", p_i32), ("priority", p_i32),
-        ("acct_nz_mcpu", p_i64), ("acct_nz_mem", p_i64), ("index_annot", p_i32),
+        ("acct_nz_mcpu", p_i64), ("acct_nz_mem", p_i64), ("index_annot", p_i32), ("uid", p_i64),
     ]
 
 
@@ -163,6 +163,7 @@ ABI = {
     "fgs_upload_nodes": (C.c_int, [C.c_void_p, C.POINTER(NodeTable)]),
     "fgs_update_nodes": (C.c_int, [C.c_void_p, C.POINTER(NodeTable), p_i64]),
     "fgs_evaluate": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts), C.POINTER(Results)]),
+    "fgs_set_nominated": (C.c_int, [C.c_void_p, C.POINTER(PodTable), p_i32, p_i64]),
     "fgs_submit": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts)]),
     "fgs_collect": (C.c_int, [C.c_void_p, C.POINTER(Results)]),
     "fgs_stage_pods": (C.c_int, [C.c_void_p, C.POINTER(PodTable)]),

@@ -272,6 +272,24 @@ class Engine:
         r.next_start_node_index = int(cr.next_start_node_index)
         return r
 
+    def set_nominated(self, pod_table=None, nodes=None, uid=None):
+        """The PodNominator's content (fgs_set_nominated): pod_table = packed nominated pods, nodes[q] = snapshot index
+        of pod q's nominated node. No arguments: clear."""
+        if pod_table is None:
+            self._check(self._lib.fgs_set_nominated(self._h, None, None, None))
+            return
+        nodes = np.ascontiguousarray(nodes, np.int32)
+        u = _ptr(np.ascontiguousarray(uid, np.int64), C.c_int64) if uid is not None else None
+        self._check(self._lib.fgs_set_nominated(self._h, pod_table, _ptr(nodes, C.c_int32), u))
+
+    @staticmethod
+    def with_uids(pod_table, uid):
+        """Attach pod UIDs to a packed pod table (fgs_pod_table.uid); returns the table."""
+        arr = np.ascontiguousarray(uid, np.int64)
+        pod_table.contents.uid = _ptr(arr, C.c_int64)
+        pod_table._uid_keep = arr
+        return pod_table
+
     def submit(self, pod_table, **opts):
         """Enqueue one batch (fgs_submit); at most two may be in flight. Pair every submit with a collect()."""
         P = int(pod_table.contents.n_pods)

@@ -104,6 +104,9 @@ void Engine::free_all() {
     if (d_special) cudaFree(d_special);
     if (d_walk) cudaFree(d_walk);
     if (h_walk) cudaFreeHost(h_walk);
+    if (d_nom) cudaFree(d_nom);
+    if (d_pod_aux) cudaFree(d_pod_aux);
+    if (h_pod_aux) cudaFreeHost(h_pod_aux);
     { // the pipeline slot the members do not alias right now
         Slot& o = slots[cur_slot ^ 1];
         if (o.d_pods) cudaFree(o.d_pods);
@@ -655,6 +658,8 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
     }
     rc = e->decide_narrow(t); // int32 tables for this batch when every value qualifies
     if (rc) return rc;
+    rc = e->stage_nominated_aux(t); // priority / uid columns for the nominated-pod filter pass, if any are set
+    if (rc) return rc;
     FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
     e->have_pods = true;
     return FGS_OK;
@@ -736,6 +741,10 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
         e->launches++;
     }
     FGS_CUDA(e, cudaGetLastError());
+    {
+        const int rc = e->run_nominated_pass(); // RunFilterPluginsWithNominatedPods' first pass, where pods are nominated
+        if (rc) return rc;
+    }
     FGS_CUDA(e, cudaEventRecord(e->events[2], e->stream));
     return FGS_OK;
 }
@@ -896,6 +905,7 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
     Engine* e = (Engine*)eh;
     if (e->in_flight >= 2) return e->fail(FGS_E_STATE, "fgs_submit: two batches are in flight already; fgs_collect one first");
     if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_submit: sample / skip_pass_b need fgs_evaluate");
+    if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_submit: nominated pods are set (their per-batch columns are not double-buffered): use fgs_evaluate");
     cudaSetDevice(e->device);
     if (!e->copy_stream) {
         FGS_CUDA(e, cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));

@@ -85,6 +85,17 @@ struct Engine {
     cudaEvent_t ev_h2d = nullptr;
     void bind_slot(int k);  // save the members into slots[cur_slot], load slots[k]
 
+    // nominated pods (nominated.cu): the PodNominator's content, grouped by node, and the per-batch columns
+    // (priority, uid, dirty flag) the second filter pass needs
+    void* d_nom = nullptr;      // int64 [NQ_COLS][nom_q] | int64 nodes[nom_m] | int64 off[nom_m + 1]
+    int64_t nom_q = 0, nom_m = 0, nom_cap_bytes = 0;
+    void* d_pod_aux = nullptr;  // int64 [3][aux_cap]: priority, uid, dirty
+    void* h_pod_aux = nullptr;
+    int64_t aux_cap = 0;
+    bool aux_has_uid = false;
+    int stage_nominated_aux(const fgs_pod_table* t); // called by the pod staging when nominated pods are set
+    int run_nominated_pass();                        // after the reduce pass, before the merges
+
     // node sampling (sample.cu): per-pod walks of the current batch
     void* d_walk = nullptr;    // int2 [p_pad] + one int64 (nextStartNodeIndex)
     void* h_walk = nullptr;

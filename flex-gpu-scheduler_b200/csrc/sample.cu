@@ -171,10 +171,12 @@ __global__ void __launch_bounds__(256) sample_truncate(uint32_t* __restrict__ bi
 
 // ---- NormalizeScore's reductions over the kept nodes ---------------------------------------------------------------
 __global__ void __launch_bounds__(256) reduce_from_bitmap(const uint32_t* __restrict__ bitmap, i64 W, i64 n_pods, i64 p_pad, i64 n_pad,
-                                                          const i64* __restrict__ nd, const i64* __restrict__ pods, i64* __restrict__ reduce_max) {
+                                                          const i64* __restrict__ nd, const i64* __restrict__ pods, i64* __restrict__ reduce_max,
+                                                          const i64* __restrict__ only /* NULL, or only[p] != 0 selects the pods */) {
     const i64 p = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (p >= n_pods) return;
+    if (only && only[p] == 0) return;
     const uint32_t kind = (uint32_t)pods[(i64)PD_META * p_pad + p] & 3u;
     const i64* sc = nd + (i64)((kind & 1u) ? ND_GPU_SCORE : ND_MEM_SCORE) * n_pad; // a gpu limit wins (flex_gpu.go:157-159)
     const i64* ar = nd + (i64)ND_ALLOC_RAW * n_pad;
@@ -236,7 +238,14 @@ cudaError_t launch_sampling(const SampleParams& sp, void* stream_) {
     const i64 total = sp.n_pods * sp.words_per_row;
     sample_truncate<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(sp.bitmap, sp.words_per_row, sp.n_nodes, sp.n_pods, (const int2*)sp.walk);
     reduce_from_bitmap<<<(unsigned)((sp.n_pods * 32 + 255) / 256), 256, 0, stream>>>(sp.bitmap, sp.words_per_row, sp.n_pods, sp.p_pad, sp.n_pad,
-                                                                                    (const i64*)sp.nd, (const i64*)sp.pods, (i64*)sp.reduce_max);
+                                                                                    (const i64*)sp.nd, (const i64*)sp.pods, (i64*)sp.reduce_max, nullptr);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_reduce_from_bitmap(const SampleParams& sp, const int64_t* only, void* stream_) {
+    if (sp.n_pods <= 0) return cudaSuccess;
+    reduce_from_bitmap<<<(unsigned)((sp.n_pods * 32 + 255) / 256), 256, 0, (cudaStream_t)stream_>>>(
+        sp.bitmap, sp.words_per_row, sp.n_pods, sp.p_pad, sp.n_pad, (const i64*)sp.nd, (const i64*)sp.pods, (i64*)sp.reduce_max, (const i64*)only);
     return cudaGetLastError();
 }
 

@@ -22,5 +22,7 @@ struct SampleParams {
 int64_t num_feasible_nodes_to_find(int64_t n_nodes, int32_t percentage);
 // sample_chain + sample_truncate + reduce_from_bitmap (3 launches)
 cudaError_t launch_sampling(const SampleParams& p, void* stream);
+// reduce_from_bitmap alone (bitmap, nd, pods, reduce_max, sizes of `p` are read), for the pods with only[p] != 0
+cudaError_t launch_reduce_from_bitmap(const SampleParams& p, const int64_t* only, void* stream);
 
 } // namespace fgs

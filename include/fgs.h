@@ -159,6 +159,16 @@ int fgs_update_nodes(fgs_engine* e, const fgs_node_table* rows, const int64_t* d
 int fgs_evaluate(fgs_engine* e, const fgs_pod_table* pods, const fgs_eval_opts* opts,
                  fgs_results* out);
 
+/* The PodNominator's content: pods an earlier preemption nominated to nodes (Status.NominatedNodeName).
+ * While it is set, every evaluation filters a node that has such pods the way RunFilterPluginsWithNominatedPods
+ * does (sched/framework/runtime/framework.go:752-823): once with the nominated pods whose priority is >= the
+ * evaluated pod's added to the node (addNominatedPods: Requested, pod count, flex limit sums, devices by index
+ * annotation), and — only if that passed — once without them; feasible = both pass. Scores are not affected
+ * (Score plugins read the snapshot's NodeInfo). node[q] = snapshot index of pod q's nominated node (global index;
+ * < 0 or outside this engine's shard: ignored); uid (optional) with fgs_pod_table.uid of the evaluated batch keeps
+ * a pod from yielding to itself. pods == NULL or empty clears. The tables are copied. */
+int fgs_set_nominated(fgs_engine* e, const fgs_pod_table* pods, const int32_t* node, const int64_t* uid);
+
 /* fgs_evaluate for a STREAM of batches, two in flight: fgs_submit stages the batch (into the buffers the
  * previous-but-one batch has released), copies it on a copy stream and enqueues both passes and the D2H of the
  * per-pod results, then returns; fgs_collect blocks until the OLDEST submitted batch is done and unpacks its

@@ -228,6 +228,9 @@ typedef struct fgs_pod_table {
     const int64_t* acct_nz_mcpu;
     const int64_t* acct_nz_mem;
     const int32_t* index_annot;      /* Atoi(nvidia.flex.com/index) or FGS_ANNOT_NONE */
+    /* optional (the packer leaves it NULL): pod UIDs, so that a pod that is itself nominated does not yield to
+     * itself in the nominated-pod filter pass (runtime/framework.go:812) */
+    const int64_t* uid;
 } fgs_pod_table;
 
 #ifdef __cplusplus

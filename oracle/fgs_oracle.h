@@ -61,6 +61,15 @@ int fgs_oracle_evaluate(const fgs_snapshot* snap, const fgs_podset* pending,
 int fgs_oracle_filter_reasons(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg,
                               int64_t p, uint16_t* flex, uint16_t* fit);
 
+/* fgs_oracle_evaluate with nominated pods: every node is filtered as RunFilterPluginsWithNominatedPods does
+ * (runtime/framework.go:752-823) — first with the nominated pods of equal or higher priority added to the node
+ * (addNominatedPods), then, if that passed, once more without them. nom_node[q] = snapshot index of pod q's
+ * NominatedNodeName (< 0: none); nom_uid / pending_uid (optional) keep a pod from yielding to itself (:812). */
+int fgs_oracle_evaluate_nominated(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg,
+                                  int64_t p0, int64_t p1, int workers, const fgs_podset* nominated,
+                                  const int32_t* nom_node, const int64_t* nom_uid, const int64_t* pending_uid,
+                                  fgs_oracle_out* out);
+
 /* numFeasibleNodesToFind (generic_scheduler.go:171-191): percentage 0 = adaptive, >= 100 = all nodes. */
 int32_t fgs_oracle_num_feasible_nodes_to_find(int32_t numAllNodes, int32_t percentageOfNodesToScore);
 

@@ -64,6 +64,9 @@ def load():
     lib.fgs_oracle_evaluate_sampled.restype = C.c_int
     lib.fgs_oracle_evaluate_sampled.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64, C.c_int64,
                                                 C.c_int, C.POINTER(C.c_int64), L.p_i32, C.POINTER(OracleOut)]
+    lib.fgs_oracle_evaluate_nominated.restype = C.c_int
+    lib.fgs_oracle_evaluate_nominated.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64, C.c_int64,
+                                                  C.c_int, C.POINTER(L.Podset), L.p_i32, L.p_i64, L.p_i64, C.POINTER(OracleOut)]
     lib.fgs_oracle_filter_reasons.restype = C.c_int
     lib.fgs_oracle_filter_reasons.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64,
                                               C.POINTER(C.c_uint16), C.POINTER(C.c_uint16)]
@@ -81,7 +84,8 @@ def num_feasible_nodes_to_find(n_nodes, percentage=0):
     return int(load().fgs_oracle_num_feasible_nodes_to_find(n_nodes, percentage))
 
 
-def evaluate(snapshot, pending, cfg, p0=0, p1=None, workers=1, planes=("status", "total"), per_plugin=False, sample=None):
+def evaluate(snapshot, pending, cfg, p0=0, p1=None, workers=1, planes=("status", "total"), per_plugin=False, sample=None,
+             nominated=None):
     """Run the oracle on pods [p0,p1). Returns numpy arrays; planes are [p1-p0][N].
     sample=(percentage, start_index): the reference's node sampling at one worker; adds r.processed [P] and
     r.next_start (status 0xEE = node not visited)."""
@@ -110,7 +114,14 @@ def evaluate(snapshot, pending, cfg, p0=0, p1=None, workers=1, planes=("status",
     out.max_total = r.max_total.ctypes.data_as(L.p_i64)
     out.tie_count = r.tie_count.ctypes.data_as(L.p_i32)
     out.first_max = r.first_max.ctypes.data_as(L.p_i32)
-    if sample is not None:
+    if nominated is not None:  # (podset pointer, node index array, uid array or None, pending uid array or None)
+        nps, nnode, nuid, puid = nominated
+        nnode = np.ascontiguousarray(nnode, np.int32)
+        nu = np.ascontiguousarray(nuid, np.int64).ctypes.data_as(L.p_i64) if nuid is not None else None
+        pu = np.ascontiguousarray(puid, np.int64).ctypes.data_as(L.p_i64) if puid is not None else None
+        rc = lib.fgs_oracle_evaluate_nominated(snapshot, pending, C.byref(cfg), p0, p1, workers, nps, nnode.ctypes.data_as(L.p_i32), nu, pu,
+                                               C.byref(out))
+    elif sample is not None:
         start = C.c_int64(int(sample[1]))
         r.processed = np.zeros(max(P, 1), np.int32)
         rc = lib.fgs_oracle_evaluate_sampled(snapshot, pending, C.byref(cfg), p0, p1, int(sample[0]), C.byref(start),

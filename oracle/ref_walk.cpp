@@ -185,6 +185,12 @@ struct Snap {
     const i64* alloc(i64 n) const { return s->alloc + n * AW; }
     const i64* req(i64 n) const { return s->requested + n * RW; }
     bool allocHasScalar(i64 n, int sc) const { return (s->alloc_scalar_present[n] >> sc) & 1u; }
+    // addNominatedPods (vendor/…/framework/runtime/framework.go:795-823): nodeInfo.Clone() + AddPodInfo for the
+    // nominated pods the evaluated pod must yield to — modelled as extra pods of ONE node, taken from another podset
+    i64 ovNode = -1;
+    const fgs_podset* ovPs = nullptr;
+    std::vector<i64> ovPods;
+    bool overlaid(i64 n) const { return n == ovNode && !ovPods.empty(); }
 };
 
 // nodeResourceLimitSum — pkg/flexgpu/flex_gpu.go:133-140
@@ -194,6 +200,11 @@ i64 nodeResourceLimitSum(const Snap& sn, i64 n, int flexSlot) {
         bool e;
         sum = wadd(sum, podResourceLimit(&sn.s->pods, q, flexSlot, e));
     }
+    if (sn.overlaid(n))
+        for (i64 q : sn.ovPods) {
+            bool e;
+            sum = wadd(sum, podResourceLimit(sn.ovPs, q, flexSlot, e));
+        }
     return sum;
 }
 
@@ -221,15 +232,14 @@ GpuNode newGPUNode(const Snap& sn, i64 n) {
     g.memEachShared = memEach;
     g.gpus.resize((size_t)gpuCnt);
     for (i64 i = 0; i < gpuCnt; ++i) g.gpus[(size_t)i] = Gpu{(int)i, false, 0};
-    const fgs_podset* ps = &sn.s->pods;
-    for (i64 q = sn.podBegin(n); q < sn.podEnd(n); ++q) {
+    auto visit = [&](const fgs_podset* ps, i64 q) {
         bool gpuExist, memExist;
         podResourceLimit(ps, q, FGS_SCALAR_FLEX_GPU, gpuExist);
         i64 memLimit = podResourceLimit(ps, q, FGS_SCALAR_FLEX_MEM, memExist);
-        if (!gpuExist && !memExist) continue; // :85-88
+        if (!gpuExist && !memExist) return; // :85-88
         // :90-96 Atoi of a missing ("") or malformed annotation errors → pod skipped
         int32_t idx = ps->index_annot[q];
-        if (idx == FGS_ANNOT_NONE) continue;
+        if (idx == FGS_ANNOT_NONE) return;
         if (gpuExist) {
             if (idx < 0 || idx >= gpuCnt) throw RefPanic{"index out of range (gpu_node.go:110)"};
             g.gpus[(size_t)idx].monopoly = true;
@@ -238,7 +248,10 @@ GpuNode newGPUNode(const Snap& sn, i64 n) {
             if (idx < 0 || idx >= gpuCnt) throw RefPanic{"index out of range (gpu_node.go:115)"};
             g.gpus[(size_t)idx].usedMemory = wadd(g.gpus[(size_t)idx].usedMemory, memLimit);
         }
-    }
+    };
+    for (i64 q = sn.podBegin(n); q < sn.podEnd(n); ++q) visit(&sn.s->pods, q);
+    if (sn.overlaid(n))
+        for (i64 q : sn.ovPods) visit(sn.ovPs, q);
     return g;
 }
 
@@ -337,8 +350,22 @@ int fitsRequest(const Snap& sn, const PodCtx& pc, i64 n, uint32_t ignoredScalarM
     if (!mask) mask = &dummy;
     *mask = 0;
     const i64* al = sn.alloc(n);
-    const i64* rq = sn.req(n);
+    i64 rqv[3 + FGS_MAX_SCALARS];
+    for (int k = 0; k < sn.RW; ++k) rqv[k] = sn.req(n)[k];
     i64 numPods = sn.podEnd(n) - sn.podBegin(n);
+    if (sn.overlaid(n)) // NodeInfo.AddPodInfo of the nominated pods: Requested += calculateResource, one more pod each
+        for (i64 q : sn.ovPods) {
+            Resource res;
+            i64 a, b;
+            calculateResource(sn.ovPs, q, res, a, b);
+            rqv[0] = wadd(rqv[0], res.mcpu);
+            rqv[1] = wadd(rqv[1], res.mem);
+            rqv[2] = wadd(rqv[2], res.eph);
+            for (int sc = 0; sc < sn.S; ++sc)
+                if ((res.scalarPresent >> sc) & 1u) rqv[3 + sc] = wadd(rqv[3 + sc], res.scalar[sc]);
+            numPods++;
+        }
+    const i64* rq = rqv;
     if (numPods + 1 > al[3]) insufficient++, *mask |= FGS_FIT_REASON_PODS; // :259-268
     const Resource& r = pc.fitReq;
     if (r.mcpu == 0 && r.mem == 0 && r.eph == 0 && r.scalarPresent == 0) return insufficient; // :270-275
@@ -548,6 +575,11 @@ struct Sampling {
     int percentage = -1;
     int64_t* start = nullptr;   // g.nextStartNodeIndex, advanced per pod
     int32_t* processed = nullptr;
+    // the PodNominator's content (nil = none): pods nominated to nodes by an earlier preemption
+    const fgs_podset* nominated = nullptr;
+    const int32_t* nomNode = nullptr;   // [Q] snapshot index of NominatedNodeName, < 0 none
+    const int64_t* nomUid = nullptr;    // [Q] optional
+    const int64_t* pendingUid = nullptr; // [P] optional
 };
 int evaluateImpl(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg, int64_t p0,
                  int64_t p1, int workers, fgs_oracle_out* out, const Sampling& smp);
@@ -557,6 +589,21 @@ extern "C" int fgs_oracle_evaluate(const fgs_snapshot* snap, const fgs_podset* p
                                    const fgs_plugin_cfg* cfg, int64_t p0, int64_t p1, int workers,
                                    fgs_oracle_out* out) {
     return evaluateImpl(snap, pending, cfg, p0, p1, workers, out, Sampling());
+}
+
+// fgs_oracle_evaluate with a PodNominator: RunFilterPluginsWithNominatedPods (runtime/framework.go:752-823)
+extern "C" int fgs_oracle_evaluate_nominated(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg,
+                                             int64_t p0, int64_t p1, int workers, const fgs_podset* nominated,
+                                             const int32_t* nom_node, const int64_t* nom_uid, const int64_t* pending_uid,
+                                             fgs_oracle_out* out) {
+    Sampling smp;
+    if (nominated && nominated->n_pods > 0 && nom_node) {
+        smp.nominated = nominated;
+        smp.nomNode = nom_node;
+        smp.nomUid = nom_uid;
+        smp.pendingUid = pending_uid;
+    }
+    return evaluateImpl(snap, pending, cfg, p0, p1, workers, out, smp);
 }
 
 // findNodesThatPassFilters with the reference's node sampling, as it runs with ONE worker
@@ -612,25 +659,54 @@ int evaluateImpl(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_
                 status[(size_t)n] = FGS_CODE_ERROR;
                 return;
             }
-            for (int k = 0; k < 2 && cfg->filter_order[k]; ++k) {
-                int pl = cfg->filter_order[k];
-                if (!(cfg->filter_mask & (uint32_t)pl)) continue;
-                int code = FGS_CODE_SUCCESS;
-                if (pl == FGS_PL_FLEXGPU) {
-                    try {
-                        code = flexFilter(sn, pc, n);
-                    } catch (const RefPanic&) {
-                        panicked[(size_t)n] = 1;
-                        code = FGS_CODE_ERROR;
+            // RunFilterPlugins — runtime/framework.go:667-693 — on a node view
+            auto runFilters = [&](const Snap& view) {
+                uint8_t r = FGS_CODE_SUCCESS;
+                for (int k = 0; k < 2 && cfg->filter_order[k]; ++k) {
+                    int pl = cfg->filter_order[k];
+                    if (!(cfg->filter_mask & (uint32_t)pl)) continue;
+                    int code = FGS_CODE_SUCCESS;
+                    bool pan = false;
+                    if (pl == FGS_PL_FLEXGPU) {
+                        try {
+                            code = flexFilter(view, pc, n);
+                        } catch (const RefPanic&) {
+                            pan = true;
+                            panicked[(size_t)n] = 1;
+                            code = FGS_CODE_ERROR;
+                        }
+                    } else if (pl == FGS_PL_FIT) {
+                        code = fitsRequest(view, pc, n, cfg->fit_ignored_scalar_mask) ? FGS_CODE_UNSCHEDULABLE : FGS_CODE_SUCCESS;
                     }
-                } else if (pl == FGS_PL_FIT) {
-                    code = fitsRequest(sn, pc, n, cfg->fit_ignored_scalar_mask) ? FGS_CODE_UNSCHEDULABLE : FGS_CODE_SUCCESS;
+                    if (code != FGS_CODE_SUCCESS) {
+                        r = (uint8_t)(((pan ? 0xF : pl) << 4) | code);
+                        break;
+                    }
                 }
-                if (code != FGS_CODE_SUCCESS) {
-                    st = (uint8_t)(((panicked[(size_t)n] ? 0xF : pl) << 4) | code);
-                    break;
+                return r;
+            };
+            // RunFilterPluginsWithNominatedPods — runtime/framework.go:752-793: first with the nominated pods of equal
+            // or higher priority added to the node (addNominatedPods :795-823), and only if that passes once more
+            // without them; the status of the last pass that ran is the node's status
+            bool podsAdded = false;
+            if (smp.nominated) {
+                Snap view = sn;
+                view.ovNode = n;
+                view.ovPs = smp.nominated;
+                const int32_t myPrio = pending->priority ? pending->priority[p] : 0;
+                for (i64 q = 0; q < smp.nominated->n_pods; ++q) {
+                    if (smp.nomNode[q] != n) continue;
+                    const int32_t pr = smp.nominated->priority ? smp.nominated->priority[q] : 0;
+                    if (pr < myPrio) continue;
+                    if (smp.nomUid && smp.pendingUid && smp.nomUid[q] == smp.pendingUid[p]) continue; // :812
+                    view.ovPods.push_back(q);
+                }
+                if (!view.ovPods.empty()) {
+                    podsAdded = true;
+                    st = runFilters(view);
                 }
             }
+            if (!podsAdded || st == FGS_CODE_SUCCESS) st = runFilters(sn);
             status[(size_t)n] = st;
         };
         if (smp.percentage < 0) {
