@@ -117,7 +117,9 @@ void Engine::free_all() {
         for (auto& sl : slots)
             if (sl.ev_done) cudaEventDestroy(sl.ev_done);
         if (ev_h2d) cudaEventDestroy(ev_h2d);
+        if (ev_kernels) cudaEventDestroy(ev_kernels);
         if (copy_stream) cudaStreamDestroy(copy_stream);
+        if (d2h_stream) cudaStreamDestroy(d2h_stream);
     }
     if (h_raw) cudaFreeHost(h_raw);
     if (h_pods) cudaFreeHost(h_pods);
@@ -909,7 +911,9 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
     cudaSetDevice(e->device);
     if (!e->copy_stream) {
         FGS_CUDA(e, cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+        FGS_CUDA(e, cudaStreamCreateWithFlags(&e->d2h_stream, cudaStreamNonBlocking));
         FGS_CUDA(e, cudaEventCreateWithFlags(&e->ev_h2d, cudaEventDisableTiming));
+        FGS_CUDA(e, cudaEventCreateWithFlags(&e->ev_kernels, cudaEventDisableTiming));
         for (auto& sl : e->slots) FGS_CUDA(e, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
     }
     // the slot that is not in flight (in_flight == 1: the other one; 0: keep the current one)
@@ -928,8 +932,11 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
     launch_finalize_pods((const int64_t*)e->d_perpod, d_compact, P, pp, e->last_key_shift, 1, (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0, e->stream);
     e->launches++;
     FGS_CUDA(e, cudaGetLastError());
-    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, d_compact, sizeof(int64_t) * 4 * pp, cudaMemcpyDeviceToHost, e->stream));
-    FGS_CUDA(e, cudaEventRecord(e->slots[k].ev_done, e->stream));
+    // the D2H of the per-pod results runs on its own stream: the next batch's kernels do not wait for it
+    FGS_CUDA(e, cudaEventRecord(e->ev_kernels, e->stream));
+    FGS_CUDA(e, cudaStreamWaitEvent(e->d2h_stream, e->ev_kernels, 0));
+    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, d_compact, sizeof(int64_t) * 4 * pp, cudaMemcpyDeviceToHost, e->d2h_stream));
+    FGS_CUDA(e, cudaEventRecord(e->slots[k].ev_done, e->d2h_stream));
     e->slots[k].busy = true;
     e->in_flight++;
     return FGS_OK;

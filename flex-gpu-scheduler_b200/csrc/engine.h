@@ -81,8 +81,8 @@ struct Engine {
     int cur_slot = 0;       // slot whose buffers the members alias
     int in_flight = 0;      // submitted, not yet collected
     int oldest_slot = 0;
-    cudaStream_t copy_stream = nullptr;
-    cudaEvent_t ev_h2d = nullptr;
+    cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
+    cudaEvent_t ev_h2d = nullptr, ev_kernels = nullptr;
     void bind_slot(int k);  // save the members into slots[cur_slot], load slots[k]
 
     // nominated pods (nominated.cu): the PodNominator's content, grouped by node, and the per-batch columns
