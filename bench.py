@@ -200,14 +200,27 @@ def run_ours(args):
     tables = [pk.pods(synth.pending, b0, b1) for pk, (b0, b1) in zip(packers, batches)]
     multi = len(batches) > 1
 
+    # without NodeResourcesAllocatable among the score plugins the emit pass does not read the merged counts: their
+    # all-reduce overlaps it (distributed.merge_after_reduce) and is waited for at the end of the step
+    defer_counts = not (plugins.score_mask & L.FGS_PL_ALLOCATABLE)
+
+    views = {}  # torch views of the engine's per-pod buffers, made once per buffer (not per step)
+
+    def tensors(view):
+        key = (int(view.reduce_max), int(view.p_pad))
+        if key not in views:
+            views[key] = D.device_views(torch, view)
+        return views[key]
+
     def merges_after_reduce(view):
         if world > 1:
-            rm, rs, _ = D.device_views(torch, view)
-            D.merge_after_reduce(dist, rm, rs)
+            rm, rs, _ = tensors(view)
+            return D.merge_after_reduce(dist, rm, rs, defer_counts)
+        return None
 
     def merges_after_emit(view):
         if world > 1:
-            D.merge_after_emit(dist, D.device_views(torch, view)[2])
+            D.merge_after_emit(dist, tensors(view)[2])
 
     with torch.cuda.stream(stream):
         lib = L.load()
@@ -225,13 +238,15 @@ def run_ours(args):
                 eng.pass_reduce()
                 if ev is not None:
                     e[1].record(stream)
-                merges_after_reduce(v)
+                pending = merges_after_reduce(v)
                 if ev is not None:
                     e[2].record(stream)
                 eng.pass_emit()
                 if ev is not None:
                     e[3].record(stream)
                 merges_after_emit(v)
+                if pending is not None:
+                    pending.wait()
 
         eng.stage_pods(tables[0])
         view = eng.device_view()
@@ -277,9 +292,11 @@ def run_ours(args):
                     eng.stage_pods(t)
                     v = eng.device_view()
                     eng.pass_reduce()
-                    merges_after_reduce(v)
+                    pending = merges_after_reduce(v)
                     eng.pass_emit()
                     merges_after_emit(v)
+                    if pending is not None:
+                        pending.wait()
                     res_holder[0] = eng.fetch_results()
 
         e2e_steps = max(1, min(args.steps, 5))

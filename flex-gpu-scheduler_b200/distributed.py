@@ -36,12 +36,18 @@ def device_views(torch, view):
             torch.as_tensor(_CudaArray(view.select_key, KEY_ROWS * p), device="cuda"))
 
 
-def merge_after_reduce(dist, reduce_max, reduce_sum):
-    """cross-shard merge between the two passes; tensors are modified in place"""
+def merge_after_reduce(dist, reduce_max, reduce_sum, defer_counts=False):
+    """cross-shard merge between the two passes; tensors are modified in place.
+    defer_counts: the emit pass needs the merged maxima but, unless NodeResourcesAllocatable is scored, not the
+    merged feasible counts (only the per-pod epilogue does): their all-reduce is then issued asynchronously AFTER the
+    MAX one, overlaps the emit pass, and the returned handle must be wait()ed before fgs_fetch_results."""
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
-        return
+        return None
     dist.all_reduce(reduce_max, op=dist.ReduceOp.MAX)
+    if defer_counts:
+        return dist.all_reduce(reduce_sum, op=dist.ReduceOp.SUM, async_op=True)
     dist.all_reduce(reduce_sum, op=dist.ReduceOp.SUM)
+    return None
 
 
 def merge_after_emit(dist, select_key):
@@ -59,14 +65,17 @@ def decode_keys(keys, key_shift=40):
     return node, score
 
 
-def evaluate_sharded(torch, dist, engine, pod_table):
+def evaluate_sharded(torch, dist, engine, pod_table, defer_counts=False):
     """One full evaluation of `pod_table` on this rank's shard with the cross-shard merges in place.
-    Must run with the engine's stream current (torch.cuda.stream(...)) so that the collectives are ordered."""
+    Must run with the engine's stream current (torch.cuda.stream(...)) so that the collectives are ordered.
+    defer_counts: see merge_after_reduce (only valid when NodeResourcesAllocatable is not a score plugin)."""
     engine.stage_pods(pod_table)
     view = engine.device_view()
     rm, rs, sk = device_views(torch, view)
     engine.pass_reduce()
-    merge_after_reduce(dist, rm, rs)
+    pending = merge_after_reduce(dist, rm, rs, defer_counts)
     engine.pass_emit()
     merge_after_emit(dist, sk)
+    if pending is not None:
+        pending.wait()
     return engine.fetch_results()

@@ -32,9 +32,12 @@ def main():
             eng.stage_pods(table)
             rm, rs, sk = D.device_views(torch, eng.device_view())
             eng.pass_reduce()
-            D.merge_after_reduce(dist, rm, rs)
+            # config 2 does not score NodeResourcesAllocatable: the count all-reduce may overlap the emit pass
+            pending = D.merge_after_reduce(dist, rm, rs, defer_counts=(cfg_id == 2))
             eng.pass_emit()
             D.merge_after_emit(dist, sk)
+            if pending is not None:
+                pending.wait()
             res = eng.fetch_results(want_planes=True)
         ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=2)
         feas_ref = ref.status == 0
