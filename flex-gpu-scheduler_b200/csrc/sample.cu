@@ -56,6 +56,24 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  : "memory");
 }
 
+// position of the r-th (0-based) set bit of x: five popcount halvings (the library's __fns is a long software loop)
+__device__ __forceinline__ int select_bit(uint32_t x, int r) {
+    int pos = 0;
+#pragma unroll
+    for (int w = 16; w >= 1; w >>= 1) {
+        const uint32_t low = x & ((1u << w) - 1u);
+        const int c = __popc(low);
+        if (r >= c) {
+            r -= c;
+            x >>= w;
+            pos += w;
+        } else {
+            x = low;
+        }
+    }
+    return pos;
+}
+
 // ---- the walk: one warp, one pod after the other ------------------------------------------------------------
 __global__ void __launch_bounds__(32, 1) sample_chain(const uint32_t* __restrict__ bitmap, i64 W, i64 n_nodes, i64 n_pods, i64 K, i64 start0,
                                                       int2* __restrict__ walk, i64* __restrict__ reduce_sum, i64* __restrict__ next_start) {
@@ -89,13 +107,13 @@ __global__ void __launch_bounds__(32, 1) sample_chain(const uint32_t* __restrict
         }
         mbar_wait(&bars[st], (uint32_t)((p / kStages) & 1));
         const uint32_t* row = rows + (size_t)st * W;
-        const i64 w0 = (i64)lane * cpl;
-        const i64 sw = s >> 5;
+        const int w0 = lane * cpl;
+        const int sw = (int)(s >> 5), Wi = (int)W;
         const uint32_t below = (1u << (s & 31)) - 1u; // bits of word sw that lie before s
         int c = 0, b = 0;
         for (int k = 0; k < cpl; ++k) {
-            const i64 w = w0 + k;
-            if (w >= W) break;
+            const int w = w0 + k;
+            if (w >= Wi) break;
             const uint32_t x = row[w];
             const int pc = __popc(x);
             c += pc;
@@ -125,14 +143,15 @@ __global__ void __launch_bounds__(32, 1) sample_chain(const uint32_t* __restrict
                     const uint32_t x = row[w0 + k];
                     const int pc = __popc(x);
                     if (rem < pc) {
-                        pos = (int)((w0 + k) * 32) + (int)__fns(x, 0, rem + 1);
+                        pos = (int)((w0 + k) * 32) + select_bit(x, rem);
                         break;
                     }
                     rem -= pc;
                 }
             }
             pos = __shfl_sync(0xffffffffu, pos, ol);
-            processed = ((i64)pos - s + N) % N; // kept + failed; the (K+1)-th itself is dropped
+            processed = (i64)pos - s; // kept + failed; the (K+1)-th itself is dropped
+            if (processed < 0) processed += N;
             kept = K;
             nxt = pos;
         }
