@@ -16,6 +16,8 @@ FGS_MAX_SCORE_RES = 8
 FGS_RES_CPU, FGS_RES_MEM, FGS_RES_EPH, FGS_RES_SCALAR0, FGS_RES_UNKNOWN = 0, 1, 2, 3, -1
 FGS_ANNOT_NONE = -(2 ** 31)
 FGS_PL_FLEXGPU, FGS_PL_FIT, FGS_PL_ALLOCATABLE = 1, 2, 4
+(FGS_PREEMPT_CANDIDATE, FGS_PREEMPT_NO_VICTIMS, FGS_PREEMPT_STILL_UNFIT, FGS_PREEMPT_QUOTA, FGS_PREEMPT_ERROR, FGS_PREEMPT_NOT_A_NODE,
+ FGS_PREEMPT_PANIC) = range(7)
 FGS_CODE_SUCCESS, FGS_CODE_ERROR, FGS_CODE_UNSCHEDULABLE, FGS_CODE_UNRESOLVABLE, FGS_CODE_WAIT = 0, 1, 2, 3, 4
 FGS_PODERR_SCORE_RANGE, FGS_PODERR_REF_PANIC = 1, 2
 FGS_REDUCE_ROWS = 6
@@ -33,6 +35,7 @@ class Podset(C.Structure):
         ("ns", p_i32), ("pg", p_i32), ("priority", p_i32), ("has_node_name", p_u8), ("index_annot", p_i32),
         ("ctr_off", p_i64), ("n_init", p_i32), ("overhead_present", p_u32), ("overhead", p_i64),
         ("n_ctrs", C.c_int64), ("c_req", p_i64), ("c_req_present", p_u32), ("c_lim_flex", p_i64), ("c_lim_present", p_u32),
+        ("start_time", p_i64),
     ]
 
 

@@ -83,6 +83,15 @@ extern "C" {
 #define FGS_FIT_REASON_EPH 8u      /* "Insufficient ephemeral-storage" */
 #define FGS_FIT_REASON_SCALAR0 16u /* << s: "Insufficient <scalar resource s>" */
 
+/* fgs_select_victims: what SelectVictimsOnNode returns for a node (pkg/capacityscheduling/capacity_scheduling.go:465-644) */
+#define FGS_PREEMPT_CANDIDATE 0   /* Success with at least one victim: the node is a preemption candidate */
+#define FGS_PREEMPT_NO_VICTIMS 1  /* "No victims found on node …", UnschedulableAndUnresolvable (:560-565) */
+#define FGS_PREEMPT_STILL_UNFIT 2 /* the pod fails the filters even with every potential victim removed (:573-575) */
+#define FGS_PREEMPT_QUOTA 3       /* "global quota max exceeded" (:580-585) */
+#define FGS_PREEMPT_ERROR 4       /* reprieve removes a pod it has just removed: RemovePod errors (:598-612) */
+#define FGS_PREEMPT_NOT_A_NODE 5  /* a row without a Node is not in the list DryRunPreemption walks */
+#define FGS_PREEMPT_PANIC 6       /* NewGPUNode panics in one of the filter runs */
+
 /* ---------------------------------------------------------------- object level ---------- */
 
 typedef struct fgs_podset {
@@ -103,6 +112,9 @@ typedef struct fgs_podset {
     const uint32_t* c_req_present;   /* [C] bit r: Requests has the key of slot r */
     const int64_t* c_lim_flex;       /* [C][2] Resources.Limits of flex gpu / flex memory */
     const uint32_t* c_lim_present;   /* [C] bit0 flex gpu limit key present, bit1 flex memory */
+    /* optional (NULL = all equal): Status.StartTime, any monotone int64 — the tie-break of util.MoreImportantPod
+     * (same priority: the pod that started earlier is more important), read by the dry-run preemption only */
+    const int64_t* start_time;
 } fgs_podset;
 
 typedef struct fgs_snapshot {

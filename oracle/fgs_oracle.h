@@ -128,6 +128,16 @@ int fgs_oracle_quota_prefilter(const fgs_podset* pending, const fgs_quotas* q,
  * (elasticquota.go:74-88,126-147) on one namespace's Used row {mcpu, mem, scalars} and its scalar keys. */
 int fgs_oracle_quota_reserve(const fgs_podset* pods, int64_t p, int op, int64_t* used, uint32_t* used_present);
 
+/* preemptor.SelectVictimsOnNode (capacity_scheduling.go:465-644) for pending pod p on EVERY node, as
+ * DryRunPreemption runs it (per-node clones; no PodDisruptionBudgets; empty PodNominator). q may be NULL (no
+ * ElasticQuota anywhere). tracks_pods: 1 = assigned pods are members of their quota's pod set, so removing / re-adding
+ * one moves its request out of / into Used (production); 0 = they are not (the reference's unit-test fixtures).
+ * node_status[n] = FGS_PREEMPT_*; victim[a] = 1 for rows of snap->pods chosen as victims on a CANDIDATE node;
+ * n_victims[n] (may be NULL). */
+int fgs_oracle_select_victims(const fgs_snapshot* snap, const fgs_podset* pending, int64_t p, const fgs_plugin_cfg* cfg,
+                              const fgs_quotas* q, int tracks_pods, uint8_t* node_status, uint8_t* victim,
+                              int32_t* n_victims);
+
 #ifdef __cplusplus
 }
 #endif

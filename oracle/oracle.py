@@ -67,6 +67,9 @@ def load():
     lib.fgs_oracle_evaluate_nominated.restype = C.c_int
     lib.fgs_oracle_evaluate_nominated.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64, C.c_int64,
                                                   C.c_int, C.POINTER(L.Podset), L.p_i32, L.p_i64, L.p_i64, C.POINTER(OracleOut)]
+    lib.fgs_oracle_select_victims.restype = C.c_int
+    lib.fgs_oracle_select_victims.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.c_int64, C.POINTER(L.PluginCfg),
+                                              C.POINTER(L.Quotas), C.c_int, L.p_u8, L.p_u8, L.p_i32]
     lib.fgs_oracle_filter_reasons.restype = C.c_int
     lib.fgs_oracle_filter_reasons.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64,
                                               C.POINTER(C.c_uint16), C.POINTER(C.c_uint16)]
@@ -190,3 +193,13 @@ def filter_reasons(snapshot, pending, cfg, p):
     load().fgs_oracle_filter_reasons(snapshot, pending, C.byref(cfg), p, flex.ctypes.data_as(C.POINTER(C.c_uint16)),
                                      fit.ctypes.data_as(C.POINTER(C.c_uint16)))
     return flex[:N], fit[:N]
+
+
+def select_victims(snapshot, pending, p, cfg, quotas=None, tracks_pods=True):
+    """SelectVictimsOnNode for pod p on every node: (status [N], victim flags [pods in the snapshot], victims per node [N])"""
+    N = int(snapshot.contents.n_nodes)
+    T = int(snapshot.contents.pods.n_pods)
+    st, vic, cnt = np.zeros(max(N, 1), np.uint8), np.zeros(max(T, 1), np.uint8), np.zeros(max(N, 1), np.int32)
+    load().fgs_oracle_select_victims(snapshot, pending, p, C.byref(cfg), quotas, 1 if tracks_pods else 0, st.ctypes.data_as(L.p_u8),
+                                     vic.ctypes.data_as(L.p_u8), cnt.ctypes.data_as(L.p_i32))
+    return st[:N], vic[:T], cnt[:N]

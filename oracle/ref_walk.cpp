@@ -191,12 +191,17 @@ struct Snap {
     const fgs_podset* ovPs = nullptr;
     std::vector<i64> ovPods;
     bool overlaid(i64 n) const { return n == ovNode && !ovPods.empty(); }
+    // NodeInfo.RemovePod of the dry-run preemption (capacity_scheduling.go:486-495): pods of the snapshot marked as
+    // removed (indexed by their row in s->pods); nullptr = none
+    const std::vector<uint8_t>* removed = nullptr;
+    bool gone(i64 q) const { return removed && (*removed)[(size_t)q]; }
 };
 
 // nodeResourceLimitSum — pkg/flexgpu/flex_gpu.go:133-140
 i64 nodeResourceLimitSum(const Snap& sn, i64 n, int flexSlot) {
     i64 sum = 0;
     for (i64 q = sn.podBegin(n); q < sn.podEnd(n); ++q) {
+        if (sn.gone(q)) continue;
         bool e;
         sum = wadd(sum, podResourceLimit(&sn.s->pods, q, flexSlot, e));
     }
@@ -249,7 +254,8 @@ GpuNode newGPUNode(const Snap& sn, i64 n) {
             g.gpus[(size_t)idx].usedMemory = wadd(g.gpus[(size_t)idx].usedMemory, memLimit);
         }
     };
-    for (i64 q = sn.podBegin(n); q < sn.podEnd(n); ++q) visit(&sn.s->pods, q);
+    for (i64 q = sn.podBegin(n); q < sn.podEnd(n); ++q)
+        if (!sn.gone(q)) visit(&sn.s->pods, q);
     if (sn.overlaid(n))
         for (i64 q : sn.ovPods) visit(sn.ovPs, q);
     return g;
@@ -353,6 +359,19 @@ int fitsRequest(const Snap& sn, const PodCtx& pc, i64 n, uint32_t ignoredScalarM
     i64 rqv[3 + FGS_MAX_SCALARS];
     for (int k = 0; k < sn.RW; ++k) rqv[k] = sn.req(n)[k];
     i64 numPods = sn.podEnd(n) - sn.podBegin(n);
+    if (sn.removed) // NodeInfo.RemovePod (framework/types.go:640-690): Requested -= calculateResource, one pod fewer
+        for (i64 q = sn.podBegin(n); q < sn.podEnd(n); ++q) {
+            if (!sn.gone(q)) continue;
+            Resource res;
+            i64 a, b;
+            calculateResource(&sn.s->pods, q, res, a, b);
+            rqv[0] = wsub(rqv[0], res.mcpu);
+            rqv[1] = wsub(rqv[1], res.mem);
+            rqv[2] = wsub(rqv[2], res.eph);
+            for (int sc = 0; sc < sn.S; ++sc)
+                if ((res.scalarPresent >> sc) & 1u) rqv[3 + sc] = wsub(rqv[3 + sc], res.scalar[sc]);
+            numPods--;
+        }
     if (sn.overlaid(n)) // NodeInfo.AddPodInfo of the nominated pods: Requested += calculateResource, one more pod each
         for (i64 q : sn.ovPods) {
             Resource res;
@@ -1152,6 +1171,180 @@ extern "C" int fgs_oracle_quota_prefilter(const fgs_podset* pending, const fgs_q
         }
         qAddQ(aggUsed, all, S);
         code[p - p0] = cmp2(aggUsed, QRes(), aggMin, S) ? 2 : 0; // :270-272
+    }
+    return 0;
+}
+
+// ---- dry-run preemption ----------------------------------------------------------------------------------------
+//
+// preemptor.SelectVictimsOnNode — pkg/capacityscheduling/capacity_scheduling.go:465-644, for every node of the
+// snapshot (preemption.Evaluator.DryRunPreemption, vendor/…/framework/preemption/preemption.go:546-597, clones the
+// NodeInfo and the CycleState per node, so nodes are independent). No PodDisruptionBudgets (every victim is
+// "non-violating", :593) and an empty PodNominator (PreFilterState.nominatedPodsReq* == podReq, as in the
+// reference's TestDryRunPreemption :311-318).
+// tracks_pods: the CapacityScheduling PreFilterExtensions AddPod / RemovePod (:277-318) move a pod's request in and
+// out of its quota's Used — only when the pod is in the quota's pod set, which is the case for every assigned pod
+// in production and for none in the reference's unit test (its ElasticQuotaInfo literals carry no pod set and the
+// test framework registers no CapacityScheduling PreFilter plugin).
+// sort.Slice is restated as insertion sort (what Go runs below 12 elements); with more pods per node Go's
+// quicksort may order EQUALLY important pods differently — pods of distinct (priority, start time) are unaffected.
+extern "C" int fgs_oracle_select_victims(const fgs_snapshot* snap, const fgs_podset* pending, int64_t p,
+                                         const fgs_plugin_cfg* cfg, const fgs_quotas* q, int tracks_pods,
+                                         uint8_t* node_status, uint8_t* victim, int32_t* n_victims) {
+    Snap sn(snap);
+    const i64 N = snap->n_nodes;
+    const int S = snap->n_scalars, W = 2 + S;
+    const fgs_podset* ps = &snap->pods;
+    const uint32_t allScalars = (S >= 32) ? 0xffffffffu : ((1u << S) - 1u);
+    PodCtx pc;
+    pc.ps = pending;
+    pc.i = p;
+    pc.fitReq = computePodResourceRequest(pending, p);
+    QRes podReq;
+    qAdd(podReq, pc.fitReq, S);
+    const int32_t podNs = pending->ns[p], podPrio = pending->priority ? pending->priority[p] : 0;
+    auto hasEQ = [&](int32_t ns) { return q && ns >= 0 && ns < q->n_ns && q->has_eq[ns]; };
+    auto prio = [&](i64 a) { return ps->priority ? ps->priority[a] : 0; };
+    auto start = [&](i64 a) { return ps->start_time ? ps->start_time[a] : (i64)0; };
+    // util.MoreImportantPod (vendor/…/scheduler/util/utils.go): higher priority, then the earlier start time
+    auto moreImportant = [&](i64 a, i64 b) { return prio(a) != prio(b) ? prio(a) > prio(b) : start(a) < start(b); };
+    auto insertionSort = [](std::vector<i64>& d, const std::function<bool(i64, i64)>& less) {
+        for (size_t i = 1; i < d.size(); ++i)
+            for (size_t j = i; j > 0 && less(d[j], d[j - 1]); --j) std::swap(d[j], d[j - 1]);
+    };
+    std::vector<uint8_t> removed((size_t)std::max<i64>(ps->n_pods, 1), 0);
+    if (victim) std::memset(victim, 0, (size_t)ps->n_pods);
+    for (i64 n = 0; n < N; ++n) {
+        if (n_victims) n_victims[n] = 0;
+        if (!snap->node_valid[n]) {
+            node_status[n] = FGS_PREEMPT_NOT_A_NODE;
+            continue;
+        }
+        // the per-node clone of the ElasticQuotaSnapshotState
+        std::vector<i64> used;
+        std::vector<uint32_t> present;
+        if (q) {
+            used.assign(q->used, q->used + q->n_ns * W);
+            present.assign(q->used_scalar_present, q->used_scalar_present + q->n_ns);
+        }
+        auto usedQ = [&](int32_t ns) { return rowToQRes(used.data() + (i64)ns * W, present[(size_t)ns], S); };
+        auto quotaMove = [&](i64 a, int op) { // RemovePod / AddPod extensions → unreserveResource / reserveResource
+            const int32_t ns = ps->ns[a];
+            if (!tracks_pods || !hasEQ(ns)) return;
+            fgs_oracle_quota_reserve(ps, a, op, used.data() + (i64)ns * W, &present[(size_t)ns]);
+        };
+        auto removePod = [&](i64 a) {
+            removed[(size_t)a] = 1;
+            quotaMove(a, -1);
+        };
+        auto addPod = [&](i64 a) {
+            removed[(size_t)a] = 0;
+            quotaMove(a, +1);
+        };
+        Snap view = sn;
+        view.removed = &removed;
+        bool panicked = false;
+        auto fits = [&]() { // RunFilterPluginsWithNominatedPods with an empty nominator = RunFilterPlugins (:667-693)
+            for (int k = 0; k < 2 && cfg->filter_order[k]; ++k) {
+                const int pl = cfg->filter_order[k];
+                if (!(cfg->filter_mask & (uint32_t)pl)) continue;
+                int code = FGS_CODE_SUCCESS;
+                if (pl == FGS_PL_FLEXGPU) {
+                    try {
+                        code = flexFilter(view, pc, n);
+                    } catch (const RefPanic&) {
+                        panicked = true;
+                        return false;
+                    }
+                } else if (pl == FGS_PL_FIT) {
+                    code = fitsRequest(view, pc, n, cfg->fit_ignored_scalar_mask) ? FGS_CODE_UNSCHEDULABLE : FGS_CODE_SUCCESS;
+                }
+                if (code != FGS_CODE_SUCCESS) return false;
+            }
+            return true;
+        };
+        auto overQuota = [&]() { // usedOverMaxWith(podReq) || aggregatedUsedOverMinWith(podReq) (:580-585, :606-607)
+            if (cmp2(podReq, usedQ(podNs), rowToQRes(q->max + (i64)podNs * W, allScalars, S), S)) return true;
+            QRes aggUsed, aggMin;
+            for (i64 k = 0; k < q->n_ns; ++k) {
+                if (!q->has_eq[k]) continue;
+                qAddQ(aggUsed, usedQ((int32_t)k), S);
+                qAddQ(aggMin, rowToQRes(q->min + k * W, allScalars, S), S);
+            }
+            qAddQ(aggUsed, podReq, S);
+            return cmp2(aggUsed, QRes(), aggMin, S);
+        };
+
+        // :505 sort the pods in node by the priority class (least important first)
+        std::vector<i64> pods;
+        for (i64 a = sn.podBegin(n); a < sn.podEnd(n); ++a) pods.push_back(a);
+        insertionSort(pods, [&](i64 a, i64 b) { return !moreImportant(a, b); });
+        std::vector<i64> potential;
+        const bool withEQ = hasEQ(podNs);
+        if (withEQ) { // :508-543
+            const bool moreThanMin = cmp2(podReq, usedQ(podNs), rowToQRes(q->min + (i64)podNs * W, allScalars, S), S);
+            for (i64 a : pods) {
+                const int32_t ns = ps->ns[a];
+                if (!hasEQ(ns)) continue;
+                if (moreThanMin) {
+                    if (ns == podNs && prio(a) < podPrio) potential.push_back(a), removePod(a);
+                } else {
+                    const bool overMin = cmp2(usedQ(ns), QRes(), rowToQRes(q->min + (i64)ns * W, allScalars, S), S); // usedOverMin()
+                    if (ns != podNs && overMin) potential.push_back(a), removePod(a);
+                }
+            }
+        } else { // :544-557
+            for (i64 a : pods) {
+                if (hasEQ(ps->ns[a])) continue;
+                if (prio(a) < podPrio) potential.push_back(a), removePod(a);
+            }
+        }
+        auto finish = [&](uint8_t st, const std::vector<i64>& victims) {
+            node_status[n] = st;
+            if (st == FGS_PREEMPT_CANDIDATE) {
+                if (victim)
+                    for (i64 a : victims) victim[a] = 1;
+                if (n_victims) n_victims[n] = (int32_t)victims.size();
+            }
+            for (i64 a : pods) removed[(size_t)a] = 0;
+        };
+        if (potential.empty()) {
+            finish(FGS_PREEMPT_NO_VICTIMS, {});
+            continue;
+        }
+        if (!fits()) { // :573-575
+            finish(panicked ? FGS_PREEMPT_PANIC : FGS_PREEMPT_STILL_UNFIT, {});
+            continue;
+        }
+        if (withEQ && overQuota()) { // :580-585
+            finish(FGS_PREEMPT_QUOTA, {});
+            continue;
+        }
+        insertionSort(potential, [&](i64 a, i64 b) { return moreImportant(a, b); }); // :589-591 most important first
+        std::vector<i64> victims;
+        uint8_t st = FGS_PREEMPT_CANDIDATE;
+        for (i64 a : potential) { // reprievePod :595-615
+            addPod(a);
+            const bool ok = fits();
+            if (panicked) {
+                st = FGS_PREEMPT_PANIC;
+                break;
+            }
+            if (!ok) {
+                removePod(a);
+                victims.push_back(a);
+            }
+            if (withEQ && overQuota()) {
+                if (!ok) { // NodeInfo.RemovePod of a pod that is no longer on the node: "no corresponding pod …"
+                    st = FGS_PREEMPT_ERROR;
+                    break;
+                }
+                removePod(a);
+                victims.push_back(a);
+            }
+        }
+        if (st == FGS_PREEMPT_CANDIDATE && victims.empty()) st = FGS_PREEMPT_ERROR; // preemption.go:578-580 "expected at least one victim pod"
+        finish(st, victims);
     }
     return 0;
 }

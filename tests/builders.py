@@ -27,10 +27,10 @@ def _slot(key):
     raise KeyError(key)
 
 
-def pod(containers=None, init_containers=None, overhead=None, ns=0, pg=-1, priority=0, node_name=False, index=None, uid=None):
+def pod(containers=None, init_containers=None, overhead=None, ns=0, pg=-1, priority=0, node_name=False, index=None, uid=None, start=0):
     """containers: list of {"requests": {...}, "limits": {"gpu": v, "mem": v}}"""
     return dict(containers=containers or [], init_containers=init_containers or [], overhead=overhead, ns=ns, pg=pg,
-                priority=priority, node_name=node_name, index=index, uid=uid)
+                priority=priority, node_name=node_name, index=index, uid=uid, start=start)
 
 
 def ctr(requests=None, gpu_limit=None, mem_limit=None):
@@ -61,6 +61,7 @@ def build_podset(pods, S=2):
     prio = np.array([p["priority"] for p in pods] or [0], np.int32)
     named = np.array([1 if p["node_name"] else 0 for p in pods] or [0], np.uint8)
     annot = np.array([ANNOT_NONE if p["index"] is None else p["index"] for p in pods] or [0], np.int32)
+    start = np.array([p.get("start", 0) for p in pods] or [0], np.int64)
     ctr_off = [0]
     n_init = []
     c_req, c_pres, c_lim, c_lpres = [], [], [], []
@@ -110,7 +111,8 @@ def build_podset(pods, S=2):
     ps.n_ctrs = len(c_pres) if pods and any(p["containers"] or p["init_containers"] for p in pods) else 0
     ps.c_req, ps.c_req_present = _p(c_req, C.c_int64), _p(c_pres, C.c_uint32)
     ps.c_lim_flex, ps.c_lim_present = _p(c_lim, C.c_int64), _p(c_lpres, C.c_uint32)
-    return Built(ps, [ns, pg, prio, named, annot, ctr_off, n_init, ovh, ovh_p, c_req, c_pres, c_lim, c_lpres])
+    ps.start_time = _p(start, C.c_int64)
+    return Built(ps, [ns, pg, prio, named, annot, ctr_off, n_init, ovh, ovh_p, c_req, c_pres, c_lim, c_lpres, start])
 
 
 def _calc_resource(p, S):

@@ -140,9 +140,32 @@ quota_reserve = [
 ]
 
 
+# pkg/capacityscheduling/capacity_scheduling_test.go:166-282 (TestDryRunPreemption): one node with memory 150 (and the
+# wrapper's 32 pods, vendor/…/scheduler/testing/wrappers.go:483-492), three assigned pods of memory 50, a preemptor of
+# memory 50 and highPriority (1000; midPriority = 100, :49). The fixtures' ElasticQuotaInfos carry no pod sets and the
+# test framework registers no CapacityScheduling PreFilter extensions, so Used does not move while pods are removed.
+dry_run_preemption = [
+    dict(name="in-namespace preemption", src="capacity_scheduling_test.go:178-230",
+         node=dict(memory=150, pods=32), preemptor=dict(ns=1, mem=50, priority=1000),
+         assigned=[dict(name="t1-p1", ns=1, mem=50, priority=100), dict(name="t1-p2", ns=2, mem=50, priority=100),
+                   dict(name="t1-p3", ns=2, mem=50, priority=100)],
+         quotas={"1": dict(min={"memory": 50}, max={"memory": 200}, used={"memory": 50}),
+                 "2": dict(min={"memory": 200}, max={"memory": 200}, used={"memory": 100})},
+         want_victims=["t1-p1"]),
+    dict(name="cross-namespace preemption", src=":231-282",
+         node=dict(memory=150, pods=32), preemptor=dict(ns=1, mem=50, priority=1000),
+         assigned=[dict(name="t1-p1", ns=1, mem=50, priority=100), dict(name="t1-p2", ns=2, mem=50, priority=1000),
+                   dict(name="t1-p3", ns=2, mem=50, priority=100)],
+         quotas={"1": dict(min={"memory": 150}, max={"memory": 200}, used={"memory": 50}),
+                 "2": dict(min={"memory": 50}, max={"memory": 200}, used={"memory": 100})},
+         want_victims=["t1-p3"]),
+]
+
+
 def main():
     out = dict(allocatable=allocatable, gang_prefilter=gang_prefilter, gang_permit=gang_permit,
-               check_cluster_resource=check_cluster_resource, capacity_prefilter=capacity_prefilter, quota_reserve=quota_reserve)
+               check_cluster_resource=check_cluster_resource, capacity_prefilter=capacity_prefilter, quota_reserve=quota_reserve,
+               dry_run_preemption=dry_run_preemption)
     for name, obj in out.items():
         with open(os.path.join(HERE, name + ".json"), "w") as f:
             json.dump(obj, f, indent=1, sort_keys=True)

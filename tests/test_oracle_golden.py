@@ -94,3 +94,23 @@ def test_num_feasible_nodes_to_find(oracle):
              (150, 10, 100)]
     for n, pct, want in cases:
         assert oracle.num_feasible_nodes_to_find(n, pct) == want, (n, pct)
+
+
+def test_dry_run_preemption_golden(oracle):
+    """TestDryRunPreemption (pkg/capacityscheduling/capacity_scheduling_test.go:166-282): the victims SelectVictimsOnNode
+    picks for the in-namespace and the cross-namespace case."""
+    import builders as B
+    S = 3
+    for case in G.load("dry_run_preemption"):
+        def mk(d, **kw):
+            return B.pod([B.ctr({"memory": d["mem"], "cpu": 0, ("scalar", 2): 0})], ns=d["ns"], priority=d["priority"], **kw)
+        nodes = [B.node({"memory": case["node"]["memory"], "pods": case["node"]["pods"]}, [mk(d, node_name=True) for d in case["assigned"]])]
+        snap = B.build_snapshot(nodes, S)
+        pend = B.build_podset([mk(case["preemptor"])], S)
+        n_ns = 1 + max(int(k) for k in case["quotas"])
+        qs = B.build_quotas({int(k): v for k, v in case["quotas"].items()}, n_ns, S)
+        cfg = fgs.plugin_cfg(filter_plugins=("NodeResourcesFit",), score_plugins=(("NodeResourcesFit", 1),))
+        st, vic, cnt = oracle.select_victims(snap.ptr, pend.ptr, 0, cfg, qs.ptr, tracks_pods=False)
+        assert int(st[0]) == L.FGS_PREEMPT_CANDIDATE, case["name"]
+        got = [d["name"] for d, v in zip(case["assigned"], vic) if v]
+        assert got == case["want_victims"] and int(cnt[0]) == len(got), (case["name"], got)
