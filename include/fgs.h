@@ -273,6 +273,23 @@ int fgs_quota_check(fgs_engine* e, const fgs_pod_table* pods, const fgs_quotas* 
                     const fgs_pod_table* nominated, const int64_t* pod_uid,
                     const int64_t* nominated_uid, uint8_t* code);
 
+/* Batched dry-run preemption: preemptor.SelectVictimsOnNode (pkg/capacityscheduling/capacity_scheduling.go:465-644)
+ * for pending pod p on EVERY node of the uploaded snapshot at once — what preemption.Evaluator.DryRunPreemption
+ * (sched/framework/preemption/preemption.go:546-597) runs node by node on clones. Per node: the potential victims by the
+ * ElasticQuota rules, the filters with all of them removed, the quota bounds, then the reprieve loop from the most
+ * important victim down. No PodDisruptionBudgets, empty PodNominator. q may be NULL (no ElasticQuota anywhere).
+ * tracks_pods: 1 = assigned pods are members of their quota's pod set, so removing / re-adding one moves its request
+ * out of / into Used (production); 0 = they are not (the reference's unit-test fixtures).
+ *   node_status[n_nodes]  FGS_PREEMPT_*
+ *   victim[snap->pods.n_pods]  1 for the pods chosen as victims on a CANDIDATE node (may be NULL)
+ *   n_victims[n_nodes]    (may be NULL)
+ * `snap` must be the snapshot the node table was packed from; single engine holding the whole cluster; at most 128
+ * pods per node. The caller filters the nodes by nodesWherePreemptionMightHelp (status plane code != 3) and picks
+ * a candidate (pickOneNodeForPreemption) on the host. */
+int fgs_select_victims(fgs_engine* e, const fgs_snapshot* snap, const fgs_podset* pending, int64_t p,
+                       const fgs_quotas* q, int32_t tracks_pods, uint8_t* node_status, uint8_t* victim,
+                       int32_t* n_victims);
+
 /* The same ElasticQuota check for callers that must not allocate. This entry point has no counterpart
  * in the reference; it exists for hosts that keep device memory in a fixed arena of their own, for code on a
  * latency-critical path that may never wait on the CUDA allocator, and for callers that are recording work
