@@ -121,6 +121,14 @@ class DeviceView(C.Structure):
     ]
 
 
+FGS_PEER_MAX_RANKS = 8
+
+
+class PeerGroup(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("world", C.c_int32), ("buffers", C.c_void_p * FGS_PEER_MAX_RANKS), ("multicast", C.c_void_p),
+                ("bytes", C.c_uint64)]
+
+
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("reduce_ms", C.c_float), ("emit_ms", C.c_float), ("d2h_ms", C.c_float),
                 ("kernel_launches", C.c_int64), ("reduce_int32", C.c_int32), ("emit_int32", C.c_int32),
@@ -176,6 +184,11 @@ ABI = {
     "fgs_pass_emit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
     "fgs_fetch_results": (C.c_int, [C.c_void_p, C.POINTER(Results)]),
     "fgs_get_device_view": (C.c_int, [C.c_void_p, C.POINTER(DeviceView)]),
+    "fgs_peer_bytes": (C.c_uint64, [C.c_int64]),
+    "fgs_peer_attach": (C.c_int, [C.c_void_p, C.POINTER(PeerGroup)]),
+    "fgs_peer_merge_reduce": (C.c_int, [C.c_void_p]),
+    "fgs_peer_merge_select": (C.c_int, [C.c_void_p]),
+    "fgs_peer_status": (C.c_int, [C.c_void_p, p_i32]),
     "fgs_synchronize": (C.c_int, [C.c_void_p]),
     "fgs_status_plane": (C.c_int, [C.c_void_p, C.c_uint32, p_u8]),
     "fgs_reason_plane": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint16)]),

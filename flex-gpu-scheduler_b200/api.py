@@ -337,6 +337,33 @@ class Engine:
         self._check(self._lib.fgs_get_device_view(self._h, C.byref(v)))
         return v
 
+    def peer_bytes(self, max_pods):
+        return int(self._lib.fgs_peer_bytes(int(max_pods)))
+
+    def peer_attach(self, rank, world, buffer_ptrs, multicast_ptr, nbytes):
+        """fgs_peer_attach: the exchange buffers of all shards (device addresses as mapped in this process)."""
+        g = L.PeerGroup()
+        g.rank, g.world, g.bytes = int(rank), int(world), int(nbytes)
+        for r, p in enumerate(buffer_ptrs):
+            g.buffers[r] = int(p)
+        g.multicast = int(multicast_ptr) if multicast_ptr else None
+        self._check(self._lib.fgs_peer_attach(self._h, C.byref(g)))
+
+    def peer_detach(self):
+        self._check(self._lib.fgs_peer_attach(self._h, None))
+
+    def peer_merge_reduce(self):
+        self._check(self._lib.fgs_peer_merge_reduce(self._h))
+
+    def peer_merge_select(self):
+        self._check(self._lib.fgs_peer_merge_select(self._h))
+
+    def peer_status(self):
+        """waits for the engine stream; raises if a merge timed out; True when the multicast path is in use"""
+        mc = C.c_int32(0)
+        self._check(self._lib.fgs_peer_status(self._h, C.byref(mc)))
+        return bool(mc.value)
+
     def synchronize(self):
         self._check(self._lib.fgs_synchronize(self._h))
 

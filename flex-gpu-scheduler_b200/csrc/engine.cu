@@ -129,6 +129,7 @@ void Engine::free_all() {
     if (own_stream && stream) cudaStreamDestroy(stream);
     gang_free();
     seq_free();
+    peer_free();
 }
 
 // plugin args → kernel parameters; validation mirrors the reference constructors

@@ -105,6 +105,7 @@ struct Engine {
 
     GangState* gang = nullptr;
     SeqState* seq = nullptr;
+    struct PeerState* peer = nullptr; // peer_merge.cu: the other shards' exchange buffers
 
     fgs_timings tm = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     int64_t launches = 0;
@@ -117,6 +118,7 @@ struct Engine {
     void free_all();
     void gang_free();
     void seq_free();
+    void peer_free();
     void fill_derive_params(DeriveParams* dp) const;
     int derive_now();        // derive_node_columns over the whole table + analysis
     int analyze_nodes_now(); // node-side analysis for the int32 specialisation (after any change of d_nd)

@@ -1,0 +1,292 @@
+// peer_merge.cu — the two cross-shard merges of the node-sharded path as ONE kernel each over NVLink
+// peer memory, in place of the NCCL all-reduces of flex-gpu-scheduler_b200/distributed.py.
+//
+// What crosses the shards is per-pod only: after the reduce pass the NormalizeScore maxima (DefaultNormalizeScore's
+// maxCount, pkg/flexgpu/flex_gpu.go:126 → vendor/…/plugins/helper/normalize_score.go:27-35; the Allocatable hi/lo of
+// pkg/noderesources/allocatable.go:121-153) and len(feasibleNodes); after the emit pass the selectHost key
+// (schedule_one.go:783-806). Each rank owns one engine and one exchange buffer in symmetric memory; every rank maps all
+// of them (and, where the NVSwitch offers it, one multicast address over all).
+//
+//   multicast (NVLS)      part := my partials            — local stores
+//                         barrier
+//                         my slice := multimem.ld_reduce  — the switch reduces the R copies on the way in
+//                         multimem.st → every rank's out  — the switch replicates on the way out
+//                         barrier;  d_perpod := out
+//   peer pointers         inbox[me] of rank s := my partials of slice s   (stores over NVLink, for every s)
+//                         barrier
+//                         my slice := reduce over inbox[0..R); out slice of every rank := it
+//                         barrier;  d_perpod := out
+//
+// The barrier is per CTA: CTA b of every rank works on sub-range b of every slice, so it only has to meet CTA b of
+// the peers (flag[b][src] := epoch with st.release.sys, spin with ld.acquire.sys). Epochs only grow, flags are never
+// reset. The grid is at most one CTA per SM so that all CTAs are resident (a CTA spins on a peer, never on a CTA of
+// its own GPU). A spin that lasts longer than kSpinLimitNs gives up and raises the error word instead of hanging.
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <string>
+
+#include "engine.h"
+
+namespace fgs {
+
+typedef long long i64;
+typedef unsigned long long u64;
+
+#define FGS_CUDA(e, call)                                                    \
+    do {                                                                     \
+        cudaError_t _err = (call);                                           \
+        if (_err != cudaSuccess) {                                           \
+            (e)->err = std::string(#call) + ": " + cudaGetErrorString(_err); \
+            return FGS_E_CUDA;                                               \
+        }                                                                    \
+    } while (0)
+
+namespace {
+
+constexpr int kMaxRanks = FGS_PEER_MAX_RANKS;
+constexpr int kPeerMaxCtas = 64;
+constexpr int kPeerThreads = 512;
+constexpr u64 kSpinLimitNs = 10ull * 1000 * 1000 * 1000;
+constexpr i64 kHeaderBytes = 4096 + (i64)kPeerMaxCtas * kMaxRanks * 8; // error word page + flags
+
+struct PeerParams {
+    i64* local;          // the engine's per-pod block (first row of the merge)
+    i64 len;             // int64 elements to merge
+    i64 sum_begin, sum_end; // elements merged with SUM; the rest with MAX
+    i64 per;             // slice length per rank (even)
+    i64 region;          // int64 elements per region (inbox / part, out)
+    char* buf[kMaxRanks]; // every rank's exchange buffer as mapped here
+    char* mc;            // multicast mapping of the same buffer, or NULL
+    int rank, world;
+    u64 epoch;           // barrier values of this launch: epoch + 1, epoch + 2
+};
+
+__device__ __forceinline__ void st_release_sys(u64* p, u64 v) { asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+__device__ __forceinline__ u64 ld_acquire_sys(const u64* p) {
+    u64 v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ u64 globaltimer_ns() {
+    u64 t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ i64 mc_ld_max(const i64* p) {
+    i64 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.max.s64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ i64 mc_ld_add(const i64* p) {
+    u64 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return (i64)v;
+}
+__device__ __forceinline__ void mc_st(i64* p, i64 v) { asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
+
+__device__ __forceinline__ u64* flag_of(char* base, int cta, int src) { return (u64*)(base + 4096) + (i64)cta * kMaxRanks + src; }
+__device__ __forceinline__ i64* region_of(char* base, i64 region, int k) { return (i64*)(base + kHeaderBytes) + (i64)k * region; }
+
+// all writes of this CTA → visible to CTA `blockIdx.x` of every peer once it has seen `value`; and the converse
+__device__ __forceinline__ void cta_barrier(const PeerParams& prm, u64 value) {
+    __syncthreads();
+    if ((int)threadIdx.x < prm.world) {
+        const int peer = threadIdx.x;
+        __threadfence_system();
+        st_release_sys(flag_of(prm.buf[peer], blockIdx.x, prm.rank), value);
+        const u64* mine = flag_of(prm.buf[prm.rank], blockIdx.x, peer);
+        const u64 t0 = globaltimer_ns();
+        while (ld_acquire_sys(mine) < value) {
+            if (globaltimer_ns() - t0 > kSpinLimitNs) {
+                *(volatile int*)prm.buf[prm.rank] = 1 + peer; // error word: the peer that never arrived
+                break;
+            }
+        }
+    }
+    __syncthreads();
+}
+
+template <bool MC>
+__global__ void __launch_bounds__(kPeerThreads) peer_merge_kernel(const PeerParams prm) {
+    const int R = prm.world, me = prm.rank;
+    const i64 per = prm.per;
+    const i64 sub = ((per + gridDim.x - 1) / gridDim.x + 1) & ~1ll; // this CTA's share of every slice (even)
+    const i64 s0 = (i64)blockIdx.x * sub;
+    const i64 s1 = s0 + sub < per ? s0 + sub : per;
+
+    // 1. hand the partials over
+    if (MC) {
+        i64* part = region_of(prm.buf[me], prm.region, 0);
+        for (int s = 0; s < R; s++) {
+            const i64 base = (i64)s * per;
+            for (i64 i = s0 + 2 * threadIdx.x; i < s1; i += 2 * kPeerThreads) {
+                const i64 g = base + i;
+                if (g + 1 < prm.len) *(longlong2*)(part + g) = *(const longlong2*)(prm.local + g);
+                else if (g < prm.len) part[g] = prm.local[g];
+            }
+        }
+    } else {
+        for (int k = 1; k < R; k++) {
+            const int s = (me + k) % R; // stagger the targets
+            const i64 base = (i64)s * per;
+            i64* inbox = region_of(prm.buf[s], prm.region, 0) + (i64)me * per;
+            for (i64 i = s0 + 2 * threadIdx.x; i < s1; i += 2 * kPeerThreads) {
+                const i64 g = base + i;
+                if (g + 1 < prm.len) *(longlong2*)(inbox + i) = *(const longlong2*)(prm.local + g);
+                else if (g < prm.len) inbox[i] = prm.local[g];
+            }
+        }
+    }
+    cta_barrier(prm, prm.epoch + 1);
+
+    // 2. reduce my slice, hand the result to everyone
+    {
+        const i64 base = (i64)me * per;
+        if (MC) {
+            const i64* part_mc = region_of(prm.mc, prm.region, 0);
+            i64* out_mc = region_of(prm.mc, prm.region, 1);
+            for (i64 i = s0 + threadIdx.x; i < s1; i += kPeerThreads) {
+                const i64 g = base + i;
+                if (g >= prm.len) break;
+                const i64 v = (g >= prm.sum_begin && g < prm.sum_end) ? mc_ld_add(part_mc + g) : mc_ld_max(part_mc + g);
+                mc_st(out_mc + g, v);
+            }
+        } else {
+            const i64* inbox = region_of(prm.buf[me], prm.region, 0);
+            for (i64 i = s0 + threadIdx.x; i < s1; i += kPeerThreads) {
+                const i64 g = base + i;
+                if (g >= prm.len) break;
+                const bool sum = g >= prm.sum_begin && g < prm.sum_end;
+                i64 v = prm.local[g];
+                for (int k = 1; k < R; k++) {
+                    const i64 w = inbox[(i64)((me + k) % R) * per + i];
+                    v = sum ? (i64)((u64)v + (u64)w) : (w > v ? w : v);
+                }
+                prm.local[g] = v;
+                for (int k = 1; k < R; k++) region_of(prm.buf[(me + k) % R], prm.region, 1)[g] = v;
+            }
+        }
+    }
+    cta_barrier(prm, prm.epoch + 2);
+
+    // 3. the merged vector → the engine's block (the own slice is already in place without multicast)
+    {
+        const i64* out = region_of(prm.buf[me], prm.region, 1);
+        for (int s = 0; s < R; s++) {
+            if (!MC && s == me) continue;
+            const i64 base = (i64)s * per;
+            for (i64 i = s0 + 2 * threadIdx.x; i < s1; i += 2 * kPeerThreads) {
+                const i64 g = base + i;
+                if (g + 1 < prm.len) *(longlong2*)(prm.local + g) = *(const longlong2*)(out + g);
+                else if (g < prm.len) prm.local[g] = out[g];
+            }
+        }
+    }
+}
+
+} // namespace
+
+struct PeerState {
+    fgs_peer_group g;
+    u64 epoch = 0;
+    int ctas = 32;
+    bool use_mc = false;
+};
+
+void Engine::peer_free() {
+    delete peer;
+    peer = nullptr;
+}
+
+} // namespace fgs
+
+using namespace fgs;
+
+extern "C" uint64_t fgs_peer_bytes(int64_t max_pods) {
+    const i64 p_pad = (max_pods + 63) / 64 * 64 + 64;
+    const i64 region = (i64)(FGS_REDUCE_ROWS + 1) * p_pad + 2 * kMaxRanks;
+    return (uint64_t)(kHeaderBytes + 2 * region * 8);
+}
+
+extern "C" int fgs_peer_attach(fgs_engine* eh, const fgs_peer_group* g) {
+    Engine* e = (Engine*)eh;
+    if (!e) return FGS_E_INVALID;
+    if (!g) { // detach
+        e->peer_free();
+        return FGS_OK;
+    }
+    if (g->world < 2 || g->world > kMaxRanks || g->rank < 0 || g->rank >= g->world) return e->fail(FGS_E_INVALID, "fgs_peer_attach: world must be 2.." + std::to_string(kMaxRanks));
+    for (int r = 0; r < g->world; r++)
+        if (!g->buffers[r]) return e->fail(FGS_E_INVALID, "fgs_peer_attach: missing buffer of rank " + std::to_string(r));
+    if (g->bytes < (uint64_t)kHeaderBytes + 64) return e->fail(FGS_E_INVALID, "fgs_peer_attach: exchange buffer too small");
+    FGS_CUDA(e, cudaSetDevice(e->device));
+    // header (error word, flags) := 0 once; the caller synchronises the ranks between attach and the first merge
+    FGS_CUDA(e, cudaMemsetAsync(g->buffers[g->rank], 0, (size_t)kHeaderBytes, e->stream));
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (!e->peer) e->peer = new PeerState();
+    e->peer->g = *g;
+    e->peer->epoch = 0;
+    e->peer->use_mc = g->multicast != nullptr;
+    if (const char* s = getenv("FGS_PEER_NO_MULTICAST"))
+        if (*s == '1') e->peer->use_mc = false;
+    if (const char* s = getenv("FGS_PEER_CTAS")) {
+        int v = atoi(s);
+        if (v >= 1 && v <= kPeerMaxCtas) e->peer->ctas = v;
+    }
+    return FGS_OK;
+}
+
+static int peer_launch(Engine* e, i64 row0, i64 rows, i64 sum_row) {
+    PeerState* ps = e->peer;
+    if (!ps) return e->fail(FGS_E_STATE, "fgs_peer_merge_* before fgs_peer_attach");
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_peer_merge_* before fgs_stage_pods");
+    PeerParams prm;
+    memset(&prm, 0, sizeof prm);
+    prm.local = (i64*)e->d_perpod + row0 * e->p_pad;
+    prm.len = rows * e->p_pad;
+    prm.sum_begin = sum_row >= 0 ? sum_row * e->p_pad : 0;
+    prm.sum_end = sum_row >= 0 ? (sum_row + 1) * e->p_pad : 0;
+    prm.world = ps->g.world;
+    prm.rank = ps->g.rank;
+    prm.per = ((prm.len + prm.world - 1) / prm.world + 1) & ~1ll;
+    prm.region = (i64)((ps->g.bytes - (uint64_t)kHeaderBytes) / 16) & ~1ll;
+    if (prm.per * prm.world > prm.region) return e->fail(FGS_E_INVALID, "fgs_peer_merge_*: exchange buffer smaller than fgs_peer_bytes(max_pods)");
+    for (int r = 0; r < prm.world; r++) prm.buf[r] = (char*)ps->g.buffers[r];
+    prm.mc = (char*)ps->g.multicast;
+    prm.epoch = ps->epoch;
+    ps->epoch += 2;
+    FGS_CUDA(e, cudaSetDevice(e->device));
+    if (ps->use_mc)
+        peer_merge_kernel<true><<<ps->ctas, kPeerThreads, 0, e->stream>>>(prm);
+    else
+        peer_merge_kernel<false><<<ps->ctas, kPeerThreads, 0, e->stream>>>(prm);
+    FGS_CUDA(e, cudaGetLastError());
+    e->launches++;
+    return FGS_OK;
+}
+
+extern "C" int fgs_peer_merge_reduce(fgs_engine* eh) {
+    Engine* e = (Engine*)eh;
+    if (!e) return FGS_E_INVALID;
+    return peer_launch(e, 0, FGS_REDUCE_ROWS + 1, FGS_REDUCE_ROWS); // reduce_max rows: MAX, reduce_sum row: SUM
+}
+
+extern "C" int fgs_peer_merge_select(fgs_engine* eh) {
+    Engine* e = (Engine*)eh;
+    if (!e) return FGS_E_INVALID;
+    return peer_launch(e, FGS_REDUCE_ROWS + 1, 3, -1);
+}
+
+extern "C" int fgs_peer_status(fgs_engine* eh, int32_t* uses_multicast) {
+    Engine* e = (Engine*)eh;
+    if (!e) return FGS_E_INVALID;
+    if (!e->peer) return e->fail(FGS_E_STATE, "fgs_peer_status before fgs_peer_attach");
+    FGS_CUDA(e, cudaSetDevice(e->device));
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    int word = 0;
+    FGS_CUDA(e, cudaMemcpy(&word, e->peer->g.buffers[e->peer->g.rank], sizeof word, cudaMemcpyDeviceToHost));
+    if (uses_multicast) *uses_multicast = e->peer->use_mc ? 1 : 0;
+    if (word) return e->fail(FGS_E_STATE, "peer merge: rank " + std::to_string(word - 1) + " never reached the barrier (timed out)");
+    return FGS_OK;
+}

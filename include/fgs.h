@@ -188,6 +188,32 @@ int fgs_pass_reduce(fgs_engine* e);
 int fgs_pass_emit(fgs_engine* e, const fgs_eval_opts* opts);
 int fgs_fetch_results(fgs_engine* e, fgs_results* out);
 int fgs_get_device_view(fgs_engine* e, fgs_device_view* v);
+
+/* ---- the cross-shard merges over NVLink peer memory --------------------------------------- */
+
+/* The two merges of the sharded sequence above as one kernel each, over exchange buffers every rank maps
+ * (CUDA IPC / fabric handles / torch symmetric memory — the caller's plumbing) instead of NCCL all-reduces:
+ * DefaultNormalizeScore's maxCount and Allocatable's hi / lo are maxima over ALL nodes (vendor/…/plugins/helper/
+ * normalize_score.go:27-35, pkg/noderesources/allocatable.go:121-153), len(feasibleNodes) a sum, selectHost a
+ * maximum of keys (schedule_one.go:783-806). With `multicast` set the NVSwitch reduces and replicates
+ * (multimem.ld_reduce / multimem.st); without, slices are pushed to their owner and the results pushed back.
+ * Every rank must call the same merges in the same order; a peer that does not show up within 10 s raises an
+ * error (fgs_peer_status) instead of hanging the GPU. */
+#define FGS_PEER_MAX_RANKS 8
+typedef struct fgs_peer_group {
+    int32_t rank, world;               /* 2 ≤ world ≤ FGS_PEER_MAX_RANKS */
+    void* buffers[FGS_PEER_MAX_RANKS]; /* every rank's exchange buffer as mapped in THIS process; [rank] = own */
+    void* multicast;                   /* multicast mapping of the same buffers, or NULL */
+    uint64_t bytes;                    /* size of each buffer, ≥ fgs_peer_bytes(max pods per batch) */
+} fgs_peer_group;
+uint64_t fgs_peer_bytes(int64_t max_pods);
+/* Zeroes the own buffer's header; synchronise the ranks (a host barrier) between attach and the first merge.
+ * g == NULL detaches. */
+int fgs_peer_attach(fgs_engine* e, const fgs_peer_group* g);
+int fgs_peer_merge_reduce(fgs_engine* e); /* after fgs_pass_reduce: reduce_max (MAX) and reduce_sum (SUM) */
+int fgs_peer_merge_select(fgs_engine* e); /* after fgs_pass_emit: select_key (MAX) */
+/* Waits for the engine stream; FGS_E_STATE if a merge timed out. uses_multicast (optional) ← 1 / 0. */
+int fgs_peer_status(fgs_engine* e, int32_t* uses_multicast);
 int fgs_synchronize(fgs_engine* e);
 
 /* Filter verdicts of the last staged batch as framework.Code bytes, out[P][n_nodes]:

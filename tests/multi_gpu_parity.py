@@ -1,5 +1,6 @@
-"""Run under torchrun with N >= 2 GPUs: node-sharded evaluation (NCCL merges) against the oracle on the whole
-cluster. Launched by tests/test_gpu_multi.py; exits non-zero on any mismatch."""
+"""Run under torchrun with N >= 2 GPUs: node-sharded evaluation against the oracle on the whole cluster, with the
+merges as NCCL all-reduces, as the engine's peer-memory kernels through NVSwitch multicast, and as the same kernels
+over plain peer pointers. Launched by tests/test_gpu_multi.py; exits non-zero on any mismatch."""
 import os
 import sys
 
@@ -19,7 +20,8 @@ def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    for cfg_id, N, P in ((2, 2311, 700), (1, 1500, 300)):
+    modes_run = []
+    for mode, (cfg_id, N, P) in [(m, c) for m in ("nccl", "multicast", "peer") for c in ((2, 2311, 700), (1, 1500, 300), (2, 900, 4001))]:
         s = fgs.config_synth(cfg_id, n_nodes=N, n_pending=P, pm_quirk_nodes=80)
         cfg = fgs.config_plugins(cfg_id)
         n0, n1 = D.shard_bounds(N, world, rank)
@@ -27,18 +29,41 @@ def main():
         eng = fgs.Engine(device=local, n_scalars=2, node_index_base=n0, total_nodes=N, stream=stream.cuda_stream)
         eng.set_plugins(cfg)
         eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot, n0, n1))
-        with torch.cuda.stream(stream):
+        px = None
+        if mode != "nccl":
+            px, why = D.try_peer_exchange(torch, dist, eng, P, multicast=(mode == "multicast"))
+            if px is None or (mode == "multicast" and not px.multicast):
+                if rank == 0:
+                    print("mode", mode, "unavailable:", why or "no multicast address")
+                if px is not None:
+                    px.close()
+                eng.close()
+                continue
+        if px is not None:
             table = fgs.Packer(2).pods(s.pending)
+            for _ in range(3):  # repeated merges: epochs and buffer reuse
+                res = D.evaluate_sharded(torch, dist, eng, table, peer=px)
+            assert eng.peer_status() == (mode == "multicast")
             eng.stage_pods(table)
-            rm, rs, sk = D.device_views(torch, eng.device_view())
             eng.pass_reduce()
-            # config 2 does not score NodeResourcesAllocatable: the count all-reduce may overlap the emit pass
-            pending = D.merge_after_reduce(dist, rm, rs, defer_counts=(cfg_id == 2))
+            eng.peer_merge_reduce()
             eng.pass_emit()
-            D.merge_after_emit(dist, sk)
-            if pending is not None:
-                pending.wait()
+            eng.peer_merge_select()
             res = eng.fetch_results(want_planes=True)
+            eng.peer_status()
+        else:
+          with torch.cuda.stream(stream):
+              table = fgs.Packer(2).pods(s.pending)
+              eng.stage_pods(table)
+              rm, rs, sk = D.device_views(torch, eng.device_view())
+              eng.pass_reduce()
+              # config 2 does not score NodeResourcesAllocatable: the count all-reduce may overlap the emit pass
+              pending = D.merge_after_reduce(dist, rm, rs, defer_counts=(cfg_id == 2))
+              eng.pass_emit()
+              D.merge_after_emit(dist, sk)
+              if pending is not None:
+                  pending.wait()
+              res = eng.fetch_results(want_planes=True)
         ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=2)
         feas_ref = ref.status == 0
         # this shard's planes against the oracle's columns
@@ -54,11 +79,14 @@ def main():
         assert np.all(sel[ref.feasible_count == 0] == -1)
         assert np.all(feas_ref[idx, sel[idx]]) and np.array_equal(ref.total[idx, sel[idx]], ref.max_total[idx]), "selected node outside tie set"
         assert np.array_equal(res.selected_score[idx], ref.max_total[idx])
+        if px is not None:
+            px.close()
         eng.close()
+        modes_run.append(mode)
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0:
-        print("multi_gpu_parity ok, world", world)
+        print("multi_gpu_parity ok, world", world, "modes", sorted(set(modes_run)))
 
 
 if __name__ == "__main__":
