@@ -11,8 +11,9 @@ pod tables resident in HBM. Prints ONE JSON line on rank 0.
   N = 1   workload = config 2 (5k nodes × 8 GPUs, 100k mixed pods, FlexGPU + Fit filter,
           FlexGPU + LeastAllocated scores) — BASELINE.json configs[1]
   N > 1   weak scaling: every rank holds a config-2-sized node shard (5k nodes) of a 5k·N-node
-          cluster, all ranks see the same 100k pods; per-pod reductions are merged with NCCL
-          all-reduce (MAX / SUM) over NVLink. `--config 5` runs the 50k-node / 1M-pod config
+          cluster, all ranks see the same 100k pods; per-pod reductions are merged (MAX / SUM) by
+          the engine's peer-memory kernels over NVLink / NVSwitch multicast (--merge nccl: NCCL
+          all-reduces instead). `--config 5` runs the 50k-node / 1M-pod config
           node-sharded instead (strong scaling).
 
 --impl reference times the reference's own algorithm on the host cores: the Go plugins cannot be built
@@ -212,14 +213,31 @@ def run_ours(args):
             views[key] = D.device_views(torch, view)
         return views[key]
 
+    # cross-shard merges: the engine's own kernels over NVLink peer memory (NVSwitch multicast where the box has
+    # it), NCCL all-reduces only if symmetric memory cannot be set up (or --merge nccl)
+    px, merge_name = None, "none (single GPU)"
+    if world > 1:
+        merge_name = "NCCL all-reduce"
+        if args.merge != "nccl":
+            px, why = D.try_peer_exchange(torch, dist, eng, max(b1 - b0 for b0, b1 in batches), multicast=(args.merge != "peer"))
+            if px is not None:
+                merge_name = ("peer-memory kernel, NVSwitch multicast (multimem.ld_reduce / multimem.st)" if px.multicast
+                              else "peer-memory kernel, pushed slices over NVLink peer pointers")
+            else:
+                merge_name += " (peer memory unavailable: %s)" % why
+
     def merges_after_reduce(view):
-        if world > 1:
+        if px is not None:
+            eng.peer_merge_reduce()
+        elif world > 1:
             rm, rs, _ = tensors(view)
             return D.merge_after_reduce(dist, rm, rs, defer_counts)
         return None
 
     def merges_after_emit(view):
-        if world > 1:
+        if px is not None:
+            eng.peer_merge_select()
+        elif world > 1:
             D.merge_after_emit(dist, tensors(view)[2])
 
     with torch.cuda.stream(stream):
@@ -232,7 +250,7 @@ def run_ours(args):
                     eng.stage_pods(t)
                 v = eng.device_view() if multi else view
                 if ev is not None:
-                    e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+                    e = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
                     ev.append(e)
                     e[0].record(stream)
                 eng.pass_reduce()
@@ -245,6 +263,8 @@ def run_ours(args):
                 if ev is not None:
                     e[3].record(stream)
                 merges_after_emit(v)
+                if ev is not None:
+                    e[4].record(stream)
                 if pending is not None:
                     pending.wait()
 
@@ -270,14 +290,18 @@ def run_ours(args):
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
+        if px is not None:
+            eng.peer_status()  # raises if a merge gave up waiting for a peer
         ms = e_start.elapsed_time(e_end)
         launches = eng.timings()["kernel_launches"] - launches0
         reduce_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
         emit_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / args.steps
+        merge1_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
+        merge2_ms = sum(e[3].elapsed_time(e[4]) for e in evs) / args.steps
         if world > 1:
-            t = torch.tensor([ms, reduce_ms, emit_ms], device="cuda", dtype=torch.float64)
+            t = torch.tensor([ms, reduce_ms, emit_ms, merge1_ms, merge2_ms], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms, reduce_ms, emit_ms = [float(x) for x in t.tolist()]
+            ms, reduce_ms, emit_ms, merge1_ms, merge2_ms = [float(x) for x in t.tolist()]
 
         # ---- end to end through the public C-ABI call with HOST buffers ---------------------------------
         # fgs_evaluate: H2D of the pod table from pinned staging + both passes + D2H of the per-pod results.
@@ -387,8 +411,9 @@ def run_ours(args):
                        "l2": "outputs (8 B per eval, %.1f GB per step per GPU) exceed the 126 MB L2; node and pod tables "
                              "(%.1f MB) are L2-resident by design" % (P * N * 8 / 1e9, (N * nd_cols * 8 + P * pd_cols * 8) / 1e6),
                        "parity": "all nodes evaluated for every pod (percentageOfNodesToScore=100)",
-                       "pod_batches": len(batches)},
-            "kernel_ms": {"reduce_pass": reduce_ms, "emit_pass": emit_ms},
+                       "pod_batches": len(batches), "merge": merge_name},
+            "kernel_ms": dict({"reduce_pass": reduce_ms, "emit_pass": emit_ms},
+                              **({"merge_after_reduce": merge1_ms, "merge_after_emit": merge2_ms} if world > 1 else {})),
             "scheduling_cycles_per_sec": args.steps * n_pods / (ms * 1e-3),
             "scheduling_cycles_note": "batched: every pod against the same snapshot, no commit between pods; "
                                       "'sequential' below commits each placement before the next pod",
@@ -407,7 +432,7 @@ def run_ours(args):
                     {"value": e2e_steps * step_evals / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pd_cols * p_pad * 8,
                      "d2h_bytes_per_step": 4 * p_pad * 8, "steps": e2e_steps,
                      "api": "fgs_evaluate (host pod table in, per-pod selected node / count / error out)"
-                     if world == 1 else "fgs_stage_pods + fgs_pass_reduce + NCCL + fgs_pass_emit + NCCL + fgs_fetch_results"}),
+                     if world == 1 else "fgs_stage_pods + fgs_pass_reduce + merge + fgs_pass_emit + merge + fgs_fetch_results (merge: see config)"}),
             "gpu_launches": int(launches),
             "clocks": clocks,
             "selected_nodes_checksum": int(res.selected_node.astype("int64").sum()) if res is not None else None,
@@ -431,6 +456,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sequential", action="store_true")
+    ap.add_argument("--merge", default="auto", choices=["auto", "peer", "nccl"],
+                    help="N > 1: cross-shard merges through the engine's peer-memory kernels (auto: NVSwitch multicast if there is one; "
+                         "peer: plain peer pointers) or through NCCL all-reduces")
     ap.add_argument("--seq-pods", type=int, default=20000, help="pods of the sequential (commit between pods) measurement")
     args = ap.parse_args()
     if args.warmup < 3:

@@ -45,7 +45,7 @@ typedef unsigned long long u64;
 namespace {
 
 constexpr int kMaxRanks = FGS_PEER_MAX_RANKS;
-constexpr int kPeerMaxCtas = 64;
+constexpr int kPeerMaxCtas = 128;
 constexpr int kPeerThreads = 512;
 constexpr u64 kSpinLimitNs = 10ull * 1000 * 1000 * 1000;
 constexpr i64 kHeaderBytes = 4096 + (i64)kPeerMaxCtas * kMaxRanks * 8; // error word page + flags
@@ -146,11 +146,20 @@ __global__ void __launch_bounds__(kPeerThreads) peer_merge_kernel(const PeerPara
         if (MC) {
             const i64* part_mc = region_of(prm.mc, prm.region, 0);
             i64* out_mc = region_of(prm.mc, prm.region, 1);
-            for (i64 i = s0 + threadIdx.x; i < s1; i += kPeerThreads) {
-                const i64 g = base + i;
-                if (g >= prm.len) break;
-                const i64 v = (g >= prm.sum_begin && g < prm.sum_end) ? mc_ld_add(part_mc + g) : mc_ld_max(part_mc + g);
-                mc_st(out_mc + g, v);
+            // a multimem load is a round trip through the switch: keep kIlp of them in flight per thread
+            constexpr int kIlp = 8;
+            for (i64 i0 = s0 + threadIdx.x; i0 < s1; i0 += (i64)kIlp * kPeerThreads) {
+                i64 v[kIlp];
+#pragma unroll
+                for (int u = 0; u < kIlp; u++) {
+                    const i64 i = i0 + (i64)u * kPeerThreads, g = base + i;
+                    if (i < s1 && g < prm.len) v[u] = (g >= prm.sum_begin && g < prm.sum_end) ? mc_ld_add(part_mc + g) : mc_ld_max(part_mc + g);
+                }
+#pragma unroll
+                for (int u = 0; u < kIlp; u++) {
+                    const i64 i = i0 + (i64)u * kPeerThreads, g = base + i;
+                    if (i < s1 && g < prm.len) mc_st(out_mc + g, v[u]);
+                }
             }
         } else {
             const i64* inbox = region_of(prm.buf[me], prm.region, 0);
@@ -190,7 +199,7 @@ __global__ void __launch_bounds__(kPeerThreads) peer_merge_kernel(const PeerPara
 struct PeerState {
     fgs_peer_group g;
     u64 epoch = 0;
-    int ctas = 32;
+    int ctas = 128;
     bool use_mc = false;
 };
 
