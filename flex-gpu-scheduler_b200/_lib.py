@@ -179,6 +179,7 @@ ABI = {
     "fgs_set_nominated": (C.c_int, [C.c_void_p, C.POINTER(PodTable), p_i32, p_i64]),
     "fgs_submit": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts)]),
     "fgs_collect": (C.c_int, [C.c_void_p, C.POINTER(Results)]),
+    "fgs_resubmit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
     "fgs_stage_pods": (C.c_int, [C.c_void_p, C.POINTER(PodTable)]),
     "fgs_pass_reduce": (C.c_int, [C.c_void_p]),
     "fgs_pass_emit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),

@@ -307,6 +307,12 @@ class Engine:
         self._check(self._lib.fgs_submit(self._h, pod_table, C.byref(o)))
         self._pending = getattr(self, "_pending", []) + [P]
 
+    def resubmit(self, n_pods, **opts):
+        """fgs_resubmit: the batch already resident in the next pipeline slot again (sharded engines only)."""
+        o = self._opts(**opts)
+        self._check(self._lib.fgs_resubmit(self._h, C.byref(o)))
+        self._pending = getattr(self, "_pending", []) + [int(n_pods)]
+
     def collect(self):
         """Per-pod results of the oldest submitted batch (blocks until it is done)."""
         P = self._pending.pop(0)

@@ -114,8 +114,13 @@ void Engine::free_all() {
         if (o.d_pn) cudaFree(o.d_pn);
         if (o.h_pods) cudaFreeHost(o.h_pods);
         if (o.h_perpod) cudaFreeHost(o.h_perpod);
-        for (auto& sl : slots)
+        for (auto& sl : slots) {
             if (sl.ev_done) cudaEventDestroy(sl.ev_done);
+            for (cudaEvent_t ev : {sl.ev_reduce, sl.ev_merge1, sl.ev_emit, sl.ev_merge2})
+                if (ev) cudaEventDestroy(ev);
+        }
+        if (merge_stream) cudaStreamDestroy(merge_stream);
+        if (d_bitmap_alt) cudaFree(d_bitmap_alt);
         if (ev_h2d) cudaEventDestroy(ev_h2d);
         if (ev_kernels) cudaEventDestroy(ev_kernels);
         if (copy_stream) cudaStreamDestroy(copy_stream);
@@ -836,11 +841,20 @@ extern "C" int fgs_evaluate(fgs_engine* eh, const fgs_pod_table* pods, const fgs
     int rc = fgs_stage_pods(eh, pods);
     if (rc) return rc;
     e->emitted = false;
+    if (e->peer && opts && opts->sample) return e->fail(FGS_E_INVALID, "fgs_evaluate: node sampling walks ONE node list (single engine only)");
     rc = fgs_pass_reduce(eh);
     if (rc) return rc;
+    if (e->peer) { // node-sharded engine: the other shards' maxima and counts
+        rc = e->peer_merge(0, e->stream);
+        if (rc) return rc;
+    }
     if (!(opts && opts->skip_pass_b)) {
         rc = fgs_pass_emit(eh, opts);
         if (rc) return rc;
+        if (e->peer) { // … and their selectHost keys
+            rc = e->peer_merge(1, e->stream);
+            if (rc) return rc;
+        }
     } else if (opts->sample) { // Filter only, truncated as the reference's walk would
         rc = e->run_sampling(opts);
         if (rc) return rc;
@@ -903,13 +917,7 @@ void Engine::bind_slot(int k) {
     cur_slot = k;
 }
 
-extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts) {
-    if (!eh) return FGS_E_INVALID;
-    Engine* e = (Engine*)eh;
-    if (e->in_flight >= 2) return e->fail(FGS_E_STATE, "fgs_submit: two batches are in flight already; fgs_collect one first");
-    if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_submit: sample / skip_pass_b need fgs_evaluate");
-    if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_submit: nominated pods are set (their per-batch columns are not double-buffered): use fgs_evaluate");
-    cudaSetDevice(e->device);
+static int ensure_pipeline(Engine* e) {
     if (!e->copy_stream) {
         FGS_CUDA(e, cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
         FGS_CUDA(e, cudaStreamCreateWithFlags(&e->d2h_stream, cudaStreamNonBlocking));
@@ -917,6 +925,134 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
         FGS_CUDA(e, cudaEventCreateWithFlags(&e->ev_kernels, cudaEventDisableTiming));
         for (auto& sl : e->slots) FGS_CUDA(e, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
     }
+    if (e->peer && !e->merge_stream) {
+        int lo = 0, hi = 0;
+        FGS_CUDA(e, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        FGS_CUDA(e, cudaStreamCreateWithPriority(&e->merge_stream, cudaStreamNonBlocking, hi)); // its few CTAs go first
+        for (auto& sl : e->slots)
+            for (cudaEvent_t* ev : {&sl.ev_reduce, &sl.ev_merge1, &sl.ev_emit, &sl.ev_merge2}) FGS_CUDA(e, cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+    }
+    return FGS_OK;
+}
+
+namespace {
+// slot 1 of the sharded pipeline evaluates into its own bitmap
+struct BitmapFor {
+    Engine* e;
+    void* saved;
+    BitmapFor(Engine* e_, int slot) : e(e_), saved(e_->d_bitmap) {
+        if (slot == 1 && e->d_bitmap_alt) e->d_bitmap = e->d_bitmap_alt;
+    }
+    ~BitmapFor() { e->d_bitmap = saved; }
+};
+} // namespace
+
+// The sharded pipeline (a peer group is attached): per batch k
+//     compute stream   reduce(k)              emit(k-1)               reduce(k+1)   …
+//     merge stream            merge1(k)              merge2(k-1), epilogue(k-1)   merge1(k+1) …
+// so every cross-shard merge overlaps a pass of the other batch. The emit pass of batch k is therefore issued by the
+// NEXT submit (after that batch's reduce pass) or, when nothing follows, by fgs_collect. Every rank must make the same
+// sequence of submit / collect calls: the merge kernels meet their peers in issue order.
+int Engine::issue_emit_sharded(int j) {
+    const int cur = cur_slot;
+    if (j != cur) bind_slot(j);
+    Slot& sl = slots[j];
+    auto body = [&]() -> int {
+        Engine* e = this;
+        FGS_CUDA(e, cudaStreamWaitEvent(stream, sl.ev_merge1, 0));
+        {
+            BitmapFor bm(this, j);
+            const int rc = fgs_pass_emit((fgs_engine*)this, sl.have_opts ? &sl.opts : nullptr);
+            if (rc) return rc;
+        }
+        FGS_CUDA(e, cudaEventRecord(sl.ev_emit, stream));
+        FGS_CUDA(e, cudaStreamWaitEvent(merge_stream, sl.ev_emit, 0));
+        const int rc = peer_merge(1, merge_stream);
+        if (rc) return rc;
+        int64_t* d_compact = (int64_t*)d_perpod + (int64_t)kCompactRow0 * p_pad;
+        launch_finalize_pods((const int64_t*)d_perpod, d_compact, n_pods, p_pad, last_key_shift, 1, (cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0, merge_stream);
+        launches++;
+        FGS_CUDA(e, cudaGetLastError());
+        FGS_CUDA(e, cudaEventRecord(sl.ev_merge2, merge_stream));
+        FGS_CUDA(e, cudaStreamWaitEvent(d2h_stream, sl.ev_merge2, 0));
+        FGS_CUDA(e, cudaMemcpyAsync(h_perpod, d_compact, sizeof(int64_t) * 4 * p_pad, cudaMemcpyDeviceToHost, d2h_stream));
+        FGS_CUDA(e, cudaEventRecord(sl.ev_done, d2h_stream));
+        sl.emit_pending = false;
+        return FGS_OK;
+    };
+    const int rc = body();
+    if (j != cur) bind_slot(cur);
+    return rc;
+}
+
+int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident) {
+    Engine* e = this;
+    const int k = in_flight == 0 ? cur_slot : (oldest_slot ^ 1);
+    if (k != cur_slot) bind_slot(k);
+    if (in_flight == 0) oldest_slot = k;
+    if (resident) {
+        if (!have_pods) return fail(FGS_E_STATE, "fgs_resubmit: no batch is resident in this pipeline slot (fgs_submit fills the slots in turn)");
+    } else {
+        const int rc = stage_pods_impl(e, pods, true);
+        if (rc) return rc;
+    }
+    emitted = false;
+    if (k == 1) { // its own bitmap, as large as the shared one
+        const size_t need = sizeof(uint32_t) * (size_t)p_plane_cap * (size_t)words_per_row;
+        if (need > bitmap_alt_bytes) {
+            FGS_CUDA(e, cudaDeviceSynchronize());
+            if (d_bitmap_alt) cudaFree(d_bitmap_alt);
+            d_bitmap_alt = nullptr;
+            FGS_CUDA(e, cudaMalloc(&d_bitmap_alt, need));
+            bitmap_alt_bytes = need;
+        }
+    }
+    Slot& sl = slots[k];
+    {
+        BitmapFor bm(this, k);
+        const int rc = fgs_pass_reduce((fgs_engine*)this);
+        if (rc) return rc;
+    }
+    FGS_CUDA(e, cudaEventRecord(sl.ev_reduce, stream));
+    FGS_CUDA(e, cudaStreamWaitEvent(merge_stream, sl.ev_reduce, 0));
+    {
+        const int rc = peer_merge(0, merge_stream);
+        if (rc) return rc;
+    }
+    FGS_CUDA(e, cudaEventRecord(sl.ev_merge1, merge_stream));
+    sl.emit_pending = true;
+    sl.have_opts = opts != nullptr;
+    if (opts) sl.opts = *opts;
+    sl.busy = true;
+    in_flight++;
+    if (in_flight == 2 && slots[oldest_slot].emit_pending) return issue_emit_sharded(oldest_slot);
+    return FGS_OK;
+}
+
+extern "C" int fgs_resubmit(fgs_engine* eh, const fgs_eval_opts* opts) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->peer) return e->fail(FGS_E_STATE, "fgs_resubmit: only with a peer group attached (fgs_peer_attach)");
+    if (e->in_flight >= 2) return e->fail(FGS_E_STATE, "fgs_resubmit: two batches are in flight already; fgs_collect one first");
+    if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_resubmit: sample / skip_pass_b need fgs_evaluate");
+    cudaSetDevice(e->device);
+    const int rc = ensure_pipeline(e);
+    if (rc) return rc;
+    return e->submit_sharded(nullptr, opts, true);
+}
+
+extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (e->in_flight >= 2) return e->fail(FGS_E_STATE, "fgs_submit: two batches are in flight already; fgs_collect one first");
+    if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_submit: sample / skip_pass_b need fgs_evaluate");
+    if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_submit: nominated pods are set (their per-batch columns are not double-buffered): use fgs_evaluate");
+    cudaSetDevice(e->device);
+    {
+        const int rc = ensure_pipeline(e);
+        if (rc) return rc;
+    }
+    if (e->peer) return e->submit_sharded(pods, opts, false);
     // the slot that is not in flight (in_flight == 1: the other one; 0: keep the current one)
     const int k = e->in_flight == 0 ? e->cur_slot : (e->oldest_slot ^ 1);
     if (k != e->cur_slot) e->bind_slot(k);
@@ -949,6 +1085,10 @@ extern "C" int fgs_collect(fgs_engine* eh, fgs_results* out) {
     if (e->in_flight == 0) return e->fail(FGS_E_STATE, "fgs_collect: nothing was submitted");
     cudaSetDevice(e->device);
     const int k = e->oldest_slot;
+    if (e->slots[k].emit_pending) { // sharded pipeline, nothing was submitted after this batch: finish it now
+        const int rc = e->issue_emit_sharded(k);
+        if (rc) return rc;
+    }
     FGS_CUDA(e, cudaEventSynchronize(e->slots[k].ev_done));
     // the oldest batch's host buffer: the members alias slot cur_slot, the other slot keeps its own copy
     const bool is_cur = k == e->cur_slot;

@@ -76,6 +76,11 @@ struct Engine {
         bool narrow_batch = false, emitted = false, sampled = false, have_pods = false, busy = false;
         int key_shift = 40;
         cudaEvent_t ev_done = nullptr;
+        // sharded pipeline (peer attached): the emit pass of a batch is issued with the NEXT submit (or by collect)
+        bool emit_pending = false;
+        fgs_eval_opts opts;
+        bool have_opts = false;
+        cudaEvent_t ev_reduce = nullptr, ev_merge1 = nullptr, ev_emit = nullptr, ev_merge2 = nullptr;
     };
     Slot slots[2];
     int cur_slot = 0;       // slot whose buffers the members alias
@@ -84,6 +89,14 @@ struct Engine {
     cudaStream_t copy_stream = nullptr, d2h_stream = nullptr;
     cudaEvent_t ev_h2d = nullptr, ev_kernels = nullptr;
     void bind_slot(int k);  // save the members into slots[cur_slot], load slots[k]
+    // sharded pipeline: merges on their own (high-priority) stream so that they overlap the other batch's pass;
+    // slot 1 has its own bitmap (the emit pass of batch k-1 reads its bitmap while the reduce pass of batch k writes)
+    cudaStream_t merge_stream = nullptr;
+    void* d_bitmap_alt = nullptr;
+    size_t bitmap_alt_bytes = 0;
+    int peer_merge(int which, cudaStream_t on); // peer_merge.cu
+    int submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident);
+    int issue_emit_sharded(int slot);
 
     // nominated pods (nominated.cu): the PodNominator's content, grouped by node, and the per-batch columns
     // (priority, uid, dirty flag) the second filter pass needs

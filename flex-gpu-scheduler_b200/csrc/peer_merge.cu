@@ -96,11 +96,15 @@ __device__ __forceinline__ void cta_barrier(const PeerParams& prm, u64 value) {
         __threadfence_system();
         st_release_sys(flag_of(prm.buf[peer], blockIdx.x, prm.rank), value);
         const u64* mine = flag_of(prm.buf[prm.rank], blockIdx.x, peer);
-        const u64 t0 = globaltimer_ns();
-        while (ld_acquire_sys(mine) < value) {
-            if (globaltimer_ns() - t0 > kSpinLimitNs) {
-                *(volatile int*)prm.buf[prm.rank] = 1 + peer; // error word: the peer that never arrived
-                break;
+        u64 t0 = 0;
+        for (unsigned polls = 1; ld_acquire_sys(mine) < value; polls++) {
+            if ((polls & 4095u) == 0) { // the timer is slow to read: look at it now and then
+                const u64 t = globaltimer_ns();
+                if (t0 == 0) t0 = t;
+                if (t - t0 > kSpinLimitNs) {
+                    *(volatile int*)prm.buf[prm.rank] = 1 + peer; // error word: the peer that never arrived
+                    break;
+                }
             }
         }
     }
@@ -246,7 +250,11 @@ extern "C" int fgs_peer_attach(fgs_engine* eh, const fgs_peer_group* g) {
     return FGS_OK;
 }
 
-static int peer_launch(Engine* e, i64 row0, i64 rows, i64 sum_row) {
+// which = 0: after the reduce pass (reduce_max rows: MAX, reduce_sum row: SUM); 1: after the emit pass (select_key: MAX).
+// Works on the per-pod block the engine's members alias at the time of the call.
+int fgs::Engine::peer_merge(int which, cudaStream_t on) {
+    Engine* e = this;
+    const i64 row0 = which == 0 ? 0 : FGS_REDUCE_ROWS + 1, rows = which == 0 ? FGS_REDUCE_ROWS + 1 : 3, sum_row = which == 0 ? FGS_REDUCE_ROWS : -1;
     PeerState* ps = e->peer;
     if (!ps) return e->fail(FGS_E_STATE, "fgs_peer_merge_* before fgs_peer_attach");
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_peer_merge_* before fgs_stage_pods");
@@ -267,9 +275,9 @@ static int peer_launch(Engine* e, i64 row0, i64 rows, i64 sum_row) {
     ps->epoch += 2;
     FGS_CUDA(e, cudaSetDevice(e->device));
     if (ps->use_mc)
-        peer_merge_kernel<true><<<ps->ctas, kPeerThreads, 0, e->stream>>>(prm);
+        peer_merge_kernel<true><<<ps->ctas, kPeerThreads, 0, on>>>(prm);
     else
-        peer_merge_kernel<false><<<ps->ctas, kPeerThreads, 0, e->stream>>>(prm);
+        peer_merge_kernel<false><<<ps->ctas, kPeerThreads, 0, on>>>(prm);
     FGS_CUDA(e, cudaGetLastError());
     e->launches++;
     return FGS_OK;
@@ -278,13 +286,13 @@ static int peer_launch(Engine* e, i64 row0, i64 rows, i64 sum_row) {
 extern "C" int fgs_peer_merge_reduce(fgs_engine* eh) {
     Engine* e = (Engine*)eh;
     if (!e) return FGS_E_INVALID;
-    return peer_launch(e, 0, FGS_REDUCE_ROWS + 1, FGS_REDUCE_ROWS); // reduce_max rows: MAX, reduce_sum row: SUM
+    return e->peer_merge(0, e->stream);
 }
 
 extern "C" int fgs_peer_merge_select(fgs_engine* eh) {
     Engine* e = (Engine*)eh;
     if (!e) return FGS_E_INVALID;
-    return peer_launch(e, FGS_REDUCE_ROWS + 1, 3, -1);
+    return e->peer_merge(1, e->stream);
 }
 
 extern "C" int fgs_peer_status(fgs_engine* eh, int32_t* uses_multicast) {

@@ -178,6 +178,13 @@ int fgs_set_nominated(fgs_engine* e, const fgs_pod_table* pods, const int32_t* n
  * calls and the plane getters are refused while batches are in flight. No sampling / skip_pass_b here. */
 int fgs_submit(fgs_engine* e, const fgs_pod_table* pods, const fgs_eval_opts* opts);
 int fgs_collect(fgs_engine* e, fgs_results* out);
+/* Node-sharded engines (fgs_peer_attach): fgs_evaluate, fgs_submit and fgs_collect include the two cross-shard
+ * merges; every rank must make the same sequence of calls. In the submit / collect pipeline the merges run on their
+ * own stream and overlap a pass of the OTHER batch in flight: the emit pass of a batch is issued by the next
+ * fgs_submit, or by fgs_collect when nothing follows. fgs_resubmit evaluates again the batch that an earlier
+ * fgs_submit left resident in the next pipeline slot (no staging, no H2D): steady-state measurements with the
+ * tables already in HBM. */
+int fgs_resubmit(fgs_engine* e, const fgs_eval_opts* opts);
 
 /* The same evaluation in stages, for node-sharded multi-GPU runs (one engine per GPU/process):
  *   fgs_stage_pods → fgs_pass_reduce → [merge reduce_max / reduce_sum across shards]

@@ -10,6 +10,43 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def check_calls_with_merges(fgs, eng, s, ref, P):
+    """fgs_evaluate and the submit / collect pipeline of a sharded engine include the merges (every rank makes the
+    same calls): per-pod results against the oracle's, with batches of different sizes alternating in the two slots"""
+    def same(r, b0, b1):
+        ok = (ref.pod_err[b0:b1] == 0) & (ref.feasible_count[b0:b1] >= 1)
+        assert np.array_equal(r.feasible_count, ref.feasible_count[b0:b1]), "counts"
+        assert np.array_equal(r.pod_err, ref.pod_err[b0:b1]), "error bits"
+        assert np.array_equal(r.selected_score[ok], ref.max_total[b0:b1][ok]), "selected score"
+        idx = np.nonzero(ok)[0]
+        feas = ref.status[b0:b1] == 0
+        assert np.all(feas[idx, r.selected_node[idx]]), "selected node infeasible"
+        assert np.array_equal(ref.total[b0:b1][idx, r.selected_node[idx]], ref.max_total[b0:b1][idx]), "selected node outside tie set"
+        assert np.all(r.selected_node[ref.feasible_count[b0:b1] == 0] == -1)
+
+    h = P // 3
+    cuts = [(0, h), (h, P), (0, P)]
+    packers = [fgs.Packer(2) for _ in cuts]
+    tabs = [pk.pods(s.pending, b0, b1) for pk, (b0, b1) in zip(packers, cuts)]
+    same(eng.evaluate(tabs[2]), 0, P)
+    same(eng.evaluate(tabs[0]), 0, h)
+    order = [0, 1, 2, 1, 0, 0, 2]
+    eng.submit(tabs[order[0]])
+    for i in range(1, len(order)):
+        eng.submit(tabs[order[i]])
+        same(eng.collect(), *cuts[order[i - 1]])
+    same(eng.collect(), *cuts[order[-1]])
+    # the two batches left resident in the slots again, without staging: the slot of the LAST batch comes first
+    last, prev = cuts[order[-1]], cuts[order[-2]]
+    eng.resubmit(last[1] - last[0])
+    eng.resubmit(prev[1] - prev[0])
+    same(eng.collect(), *last)
+    eng.resubmit(last[1] - last[0])
+    same(eng.collect(), *prev)
+    same(eng.collect(), *last)
+    eng.peer_status()
+
+
 def main():
     import torch
     import torch.distributed as dist
@@ -65,6 +102,8 @@ def main():
                   pending.wait()
               res = eng.fetch_results(want_planes=True)
         ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=2)
+        if px is not None:
+            check_calls_with_merges(fgs, eng, s, ref, P)
         feas_ref = ref.status == 0
         # this shard's planes against the oracle's columns
         assert np.array_equal(res.feasible(n1 - n0), feas_ref[:, n0:n1]), "bitmap shard"
