@@ -107,13 +107,16 @@ void Engine::free_all() {
     if (d_nom) cudaFree(d_nom);
     if (d_pod_aux) cudaFree(d_pod_aux);
     if (h_pod_aux) cudaFreeHost(h_pod_aux);
-    { // the pipeline slot the members do not alias right now
-        Slot& o = slots[cur_slot ^ 1];
-        if (o.d_pods) cudaFree(o.d_pods);
-        if (o.d_perpod) cudaFree(o.d_perpod);
-        if (o.d_pn) cudaFree(o.d_pn);
-        if (o.h_pods) cudaFreeHost(o.h_pods);
-        if (o.h_perpod) cudaFreeHost(o.h_perpod);
+    { // the pipeline slots the members do not alias right now
+        for (int j = 0; j < kSlots; j++) {
+            if (j == cur_slot) continue;
+            Slot& o = slots[j];
+            if (o.d_pods) cudaFree(o.d_pods);
+            if (o.d_perpod) cudaFree(o.d_perpod);
+            if (o.d_pn) cudaFree(o.d_pn);
+            if (o.h_pods) cudaFreeHost(o.h_pods);
+            if (o.h_perpod) cudaFreeHost(o.h_perpod);
+        }
         for (auto& sl : slots) {
             if (sl.ev_done) cudaEventDestroy(sl.ev_done);
             for (cudaEvent_t ev : {sl.ev_reduce, sl.ev_merge1, sl.ev_emit, sl.ev_merge2})
@@ -936,12 +939,12 @@ static int ensure_pipeline(Engine* e) {
 }
 
 namespace {
-// slot 1 of the sharded pipeline evaluates into its own bitmap
+// every other batch of the sharded pipeline evaluates into the second bitmap
 struct BitmapFor {
     Engine* e;
     void* saved;
-    BitmapFor(Engine* e_, int slot) : e(e_), saved(e_->d_bitmap) {
-        if (slot == 1 && e->d_bitmap_alt) e->d_bitmap = e->d_bitmap_alt;
+    BitmapFor(Engine* e_, int sel) : e(e_), saved(e_->d_bitmap) {
+        if (sel == 1 && e->d_bitmap_alt) e->d_bitmap = e->d_bitmap_alt;
     }
     ~BitmapFor() { e->d_bitmap = saved; }
 };
@@ -951,8 +954,11 @@ struct BitmapFor {
 //     compute stream   reduce(k)              emit(k-1)               reduce(k+1)   …
 //     merge stream            merge1(k)              merge2(k-1), epilogue(k-1)   merge1(k+1) …
 // so every cross-shard merge overlaps a pass of the other batch. The emit pass of batch k is therefore issued by the
-// NEXT submit (after that batch's reduce pass) or, when nothing follows, by fgs_collect. Every rank must make the same
-// sequence of submit / collect calls: the merge kernels meet their peers in issue order.
+// NEXT submit (after that batch's reduce pass) or, when nothing follows, by fgs_collect. Up to THREE batches are in
+// flight here (k-1 being read back and unpacked, k waiting for its emit pass, k+1 just submitted): with two, the
+// compute stream would run dry while the host collects. The bitmap exists twice (the emit pass of batch k-1 reads its
+// rows while the reduce pass of batch k writes). Every rank must make the same sequence of submit / collect calls:
+// the merge kernels meet their peers in issue order.
 int Engine::issue_emit_sharded(int j) {
     const int cur = cur_slot;
     if (j != cur) bind_slot(j);
@@ -961,7 +967,7 @@ int Engine::issue_emit_sharded(int j) {
         Engine* e = this;
         FGS_CUDA(e, cudaStreamWaitEvent(stream, sl.ev_merge1, 0));
         {
-            BitmapFor bm(this, j);
+            BitmapFor bm(this, sl.bitmap_sel);
             const int rc = fgs_pass_emit((fgs_engine*)this, sl.have_opts ? &sl.opts : nullptr);
             if (rc) return rc;
         }
@@ -987,7 +993,8 @@ int Engine::issue_emit_sharded(int j) {
 
 int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident) {
     Engine* e = this;
-    const int k = in_flight == 0 ? cur_slot : (oldest_slot ^ 1);
+    const int k = in_flight == 0 ? cur_slot : (oldest_slot + in_flight) % ring();
+    const int newest = in_flight == 0 ? -1 : (oldest_slot + in_flight - 1) % ring();
     if (k != cur_slot) bind_slot(k);
     if (in_flight == 0) oldest_slot = k;
     if (resident) {
@@ -997,7 +1004,8 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
         if (rc) return rc;
     }
     emitted = false;
-    if (k == 1) { // its own bitmap, as large as the shared one
+    slots[k].bitmap_sel = (int)(submit_seq++ & 1);
+    if (slots[k].bitmap_sel == 1) { // the second bitmap, as large as the first
         const size_t need = sizeof(uint32_t) * (size_t)p_plane_cap * (size_t)words_per_row;
         if (need > bitmap_alt_bytes) {
             FGS_CUDA(e, cudaDeviceSynchronize());
@@ -1009,7 +1017,7 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
     }
     Slot& sl = slots[k];
     {
-        BitmapFor bm(this, k);
+        BitmapFor bm(this, sl.bitmap_sel);
         const int rc = fgs_pass_reduce((fgs_engine*)this);
         if (rc) return rc;
     }
@@ -1025,7 +1033,7 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
     if (opts) sl.opts = *opts;
     sl.busy = true;
     in_flight++;
-    if (in_flight == 2 && slots[oldest_slot].emit_pending) return issue_emit_sharded(oldest_slot);
+    if (newest >= 0 && slots[newest].emit_pending) return issue_emit_sharded(newest);
     return FGS_OK;
 }
 
@@ -1033,7 +1041,8 @@ extern "C" int fgs_resubmit(fgs_engine* eh, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
     if (!e->peer) return e->fail(FGS_E_STATE, "fgs_resubmit: only with a peer group attached (fgs_peer_attach)");
-    if (e->in_flight >= 2) return e->fail(FGS_E_STATE, "fgs_resubmit: two batches are in flight already; fgs_collect one first");
+    if (e->in_flight >= 3) return e->fail(FGS_E_STATE, "fgs_resubmit: three batches are in flight already; fgs_collect one first");
+    if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_resubmit: nominated pods are set: use fgs_evaluate");
     if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_resubmit: sample / skip_pass_b need fgs_evaluate");
     cudaSetDevice(e->device);
     const int rc = ensure_pipeline(e);
@@ -1044,7 +1053,9 @@ extern "C" int fgs_resubmit(fgs_engine* eh, const fgs_eval_opts* opts) {
 extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
-    if (e->in_flight >= 2) return e->fail(FGS_E_STATE, "fgs_submit: two batches are in flight already; fgs_collect one first");
+    if (e->in_flight >= (e->peer ? 3 : 2))
+        return e->fail(FGS_E_STATE, e->peer ? "fgs_submit: three batches are in flight already; fgs_collect one first"
+                                            : "fgs_submit: two batches are in flight already; fgs_collect one first");
     if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_submit: sample / skip_pass_b need fgs_evaluate");
     if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_submit: nominated pods are set (their per-batch columns are not double-buffered): use fgs_evaluate");
     cudaSetDevice(e->device);
@@ -1054,7 +1065,7 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
     }
     if (e->peer) return e->submit_sharded(pods, opts, false);
     // the slot that is not in flight (in_flight == 1: the other one; 0: keep the current one)
-    const int k = e->in_flight == 0 ? e->cur_slot : (e->oldest_slot ^ 1);
+    const int k = e->in_flight == 0 ? e->cur_slot : (e->oldest_slot + e->in_flight) % e->ring();
     if (k != e->cur_slot) e->bind_slot(k);
     if (e->in_flight == 0) e->oldest_slot = k;
     int rc = stage_pods_impl(e, pods, true);
@@ -1106,6 +1117,6 @@ extern "C" int fgs_collect(fgs_engine* eh, fgs_results* out) {
     out->next_start_node_index = -1;
     e->slots[k].busy = false;
     e->in_flight--;
-    e->oldest_slot = k ^ 1;
+    e->oldest_slot = (k + 1) % e->ring();
     return FGS_OK;
 }

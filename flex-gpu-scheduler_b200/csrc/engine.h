@@ -78,11 +78,15 @@ struct Engine {
         cudaEvent_t ev_done = nullptr;
         // sharded pipeline (peer attached): the emit pass of a batch is issued with the NEXT submit (or by collect)
         bool emit_pending = false;
+        int bitmap_sel = 0;
         fgs_eval_opts opts;
         bool have_opts = false;
         cudaEvent_t ev_reduce = nullptr, ev_merge1 = nullptr, ev_emit = nullptr, ev_merge2 = nullptr;
     };
-    Slot slots[2];
+    static constexpr int kSlots = 3; // two in flight on one GPU; three in the sharded pipeline (see submit_sharded)
+    Slot slots[kSlots];
+    int ring() const { return peer ? 3 : 2; }
+    uint64_t submit_seq = 0; // batches submitted so far: the sharded pipeline alternates two bitmaps by its parity
     int cur_slot = 0;       // slot whose buffers the members alias
     int in_flight = 0;      // submitted, not yet collected
     int oldest_slot = 0;
@@ -90,7 +94,7 @@ struct Engine {
     cudaEvent_t ev_h2d = nullptr, ev_kernels = nullptr;
     void bind_slot(int k);  // save the members into slots[cur_slot], load slots[k]
     // sharded pipeline: merges on their own (high-priority) stream so that they overlap the other batch's pass;
-    // slot 1 has its own bitmap (the emit pass of batch k-1 reads its bitmap while the reduce pass of batch k writes)
+    // every other batch uses a second bitmap (the emit pass of batch k-1 reads its rows while the reduce pass of batch k writes)
     cudaStream_t merge_stream = nullptr;
     void* d_bitmap_alt = nullptr;
     size_t bitmap_alt_bytes = 0;

@@ -225,6 +225,7 @@ extern "C" uint64_t fgs_peer_bytes(int64_t max_pods) {
 extern "C" int fgs_peer_attach(fgs_engine* eh, const fgs_peer_group* g) {
     Engine* e = (Engine*)eh;
     if (!e) return FGS_E_INVALID;
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_peer_attach while submitted batches are in flight: fgs_collect them first");
     if (!g) { // detach
         e->peer_free();
         return FGS_OK;

@@ -31,19 +31,24 @@ def check_calls_with_merges(fgs, eng, s, ref, P):
     same(eng.evaluate(tabs[2]), 0, P)
     same(eng.evaluate(tabs[0]), 0, h)
     order = [0, 1, 2, 1, 0, 0, 2]
-    eng.submit(tabs[order[0]])
-    for i in range(1, len(order)):
-        eng.submit(tabs[order[i]])
-        same(eng.collect(), *cuts[order[i - 1]])
-    same(eng.collect(), *cuts[order[-1]])
-    # the two batches left resident in the slots again, without staging: the slot of the LAST batch comes first
-    last, prev = cuts[order[-1]], cuts[order[-2]]
-    eng.resubmit(last[1] - last[0])
-    eng.resubmit(prev[1] - prev[0])
-    same(eng.collect(), *last)
-    eng.resubmit(last[1] - last[0])
-    same(eng.collect(), *prev)
-    same(eng.collect(), *last)
+    for depth in (1, 2, 3):  # batches in flight (a sharded engine takes up to three)
+        q = []
+        for i in order:
+            eng.submit(tabs[i])
+            q.append(i)
+            if len(q) == depth:
+                same(eng.collect(), *cuts[q.pop(0)])
+        while q:
+            same(eng.collect(), *cuts[q.pop(0)])
+    # the three batches left resident in the ring of slots again, without staging: the slot of the LAST batch comes
+    # first, then the ring goes on (third to last, second to last)
+    ring = [cuts[order[-1]], cuts[order[-3]], cuts[order[-2]]]
+    for c in ring:
+        eng.resubmit(c[1] - c[0])
+    same(eng.collect(), *ring[0])
+    eng.resubmit(ring[0][1] - ring[0][0])
+    for c in ring[1:] + ring[:1]:
+        same(eng.collect(), *c)
     eng.peer_status()
 
 

@@ -10,7 +10,7 @@ for m in auto peer nccl; do
 import json
 try:
     d = json.loads(open("gpurun_out/merge_${N}_$m.json").read().strip().splitlines()[-1])
-    print(d["n_gpus"], round(d["ms_per_step"], 4), "%.3e" % d["value"], {k: round(v, 4) for k, v in d["kernel_ms"].items()}, d["config"]["merge"], d["e2e"]["value"])
+    print(d["n_gpus"], round(d["ms_per_step"], 4), "%.3e" % d["value"], {k: round(v, 4) for k, v in d["kernel_ms"].items() if not isinstance(v, str)}, d["config"]["merge"], d["e2e"]["value"])
 except Exception as ex:
     print("no line:", ex)
 PY
