@@ -973,7 +973,7 @@ int Engine::issue_emit_sharded(int j) {
         }
         FGS_CUDA(e, cudaEventRecord(sl.ev_emit, stream));
         FGS_CUDA(e, cudaStreamWaitEvent(merge_stream, sl.ev_emit, 0));
-        const int rc = peer_merge(1, merge_stream);
+        const int rc = peer_merge(1, merge_stream, true);
         if (rc) return rc;
         int64_t* d_compact = (int64_t*)d_perpod + (int64_t)kCompactRow0 * p_pad;
         launch_finalize_pods((const int64_t*)d_perpod, d_compact, n_pods, p_pad, last_key_shift, 1, (cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0, merge_stream);
@@ -1024,7 +1024,7 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
     FGS_CUDA(e, cudaEventRecord(sl.ev_reduce, stream));
     FGS_CUDA(e, cudaStreamWaitEvent(merge_stream, sl.ev_reduce, 0));
     {
-        const int rc = peer_merge(0, merge_stream);
+        const int rc = peer_merge(0, merge_stream, true);
         if (rc) return rc;
     }
     FGS_CUDA(e, cudaEventRecord(sl.ev_merge1, merge_stream));

@@ -98,7 +98,7 @@ struct Engine {
     cudaStream_t merge_stream = nullptr;
     void* d_bitmap_alt = nullptr;
     size_t bitmap_alt_bytes = 0;
-    int peer_merge(int which, cudaStream_t on); // peer_merge.cu
+    int peer_merge(int which, cudaStream_t on, bool overlapped = false); // peer_merge.cu
     int submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident);
     int issue_emit_sharded(int slot);
 

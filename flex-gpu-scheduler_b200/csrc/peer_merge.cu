@@ -203,7 +203,8 @@ __global__ void __launch_bounds__(kPeerThreads) peer_merge_kernel(const PeerPara
 struct PeerState {
     fgs_peer_group g;
     u64 epoch = 0;
-    int ctas = 128;
+    int ctas = 128;        // merge alone on the GPU: latency matters, take many CTAs
+    int ctas_overlap = 16; // merge beside a pass of another batch (pipeline): it is hidden anyway, leave the SMs to the pass
     bool use_mc = false;
 };
 
@@ -248,12 +249,16 @@ extern "C" int fgs_peer_attach(fgs_engine* eh, const fgs_peer_group* g) {
         int v = atoi(s);
         if (v >= 1 && v <= kPeerMaxCtas) e->peer->ctas = v;
     }
+    if (const char* s = getenv("FGS_PEER_CTAS_OVERLAP")) {
+        int v = atoi(s);
+        if (v >= 1 && v <= kPeerMaxCtas) e->peer->ctas_overlap = v;
+    }
     return FGS_OK;
 }
 
 // which = 0: after the reduce pass (reduce_max rows: MAX, reduce_sum row: SUM); 1: after the emit pass (select_key: MAX).
 // Works on the per-pod block the engine's members alias at the time of the call.
-int fgs::Engine::peer_merge(int which, cudaStream_t on) {
+int fgs::Engine::peer_merge(int which, cudaStream_t on, bool overlapped) {
     Engine* e = this;
     const i64 row0 = which == 0 ? 0 : FGS_REDUCE_ROWS + 1, rows = which == 0 ? FGS_REDUCE_ROWS + 1 : 3, sum_row = which == 0 ? FGS_REDUCE_ROWS : -1;
     PeerState* ps = e->peer;
@@ -275,10 +280,11 @@ int fgs::Engine::peer_merge(int which, cudaStream_t on) {
     prm.epoch = ps->epoch;
     ps->epoch += 2;
     FGS_CUDA(e, cudaSetDevice(e->device));
+    const int ctas = overlapped ? ps->ctas_overlap : ps->ctas;
     if (ps->use_mc)
-        peer_merge_kernel<true><<<ps->ctas, kPeerThreads, 0, on>>>(prm);
+        peer_merge_kernel<true><<<ctas, kPeerThreads, 0, on>>>(prm);
     else
-        peer_merge_kernel<false><<<ps->ctas, kPeerThreads, 0, on>>>(prm);
+        peer_merge_kernel<false><<<ctas, kPeerThreads, 0, on>>>(prm);
     FGS_CUDA(e, cudaGetLastError());
     e->launches++;
     return FGS_OK;
