@@ -2,7 +2,7 @@
 # tools/merge_bench.sh N — the node-sharded bench with each kind of cross-shard merge, one JSON line each in gpurun_out/
 N=${1:-2}
 mkdir -p gpurun_out
-for m in auto peer nccl; do
+for m in ${MODES:-auto peer nccl}; do
   timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node=$N --master-addr 127.0.0.1 --master-port $((29600 + RANDOM % 200)) \
     bench.py --gpus $N --steps 20 --warmup 3 --merge $m > gpurun_out/merge_${N}_$m.json 2> gpurun_out/merge_${N}_$m.err
   echo "rc=$? merge=$m"
