@@ -47,19 +47,60 @@ class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, device):
+    def __init__(self, device, uuid=None):
         self.device = device
+        self.uuid = uuid
         self.rows = []
+        self.source = "nvidia-smi"
+        self.window = None  # (t0, t1) in time.perf_counter() terms: the timed region
         self._stop = threading.Event()
         self._t = None
 
+    def _nvml_handle(self):
+        """NVML handle of the CUDA device (by UUID: CUDA_VISIBLE_DEVICES may renumber), or None"""
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            if self.uuid:
+                for u in ("GPU-" + self.uuid, self.uuid):
+                    try:
+                        return pynvml, pynvml.nvmlDeviceGetHandleByUUID(u)
+                    except Exception:
+                        pass
+            if os.environ.get("CUDA_VISIBLE_DEVICES"):
+                return None  # the index may be renumbered: leave it to nvidia-smi's view of the same index
+            return pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.device)
+        except Exception:
+            return None
+
+    def _run_nvml(self, nv, h):
+        """the same counters as the nvidia-smi query through NVML: a sample every few ms, so that the short timed region
+        (tens of ms) is covered by more than one"""
+        mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        bits = (("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown), ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown), ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap))
+        while not self._stop.is_set():
+            sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+            self.rows.append([str(self.device), str(sm), str(mx), "", hex(r)] + ["Active" if r & b else "Not Active" for _, b in bits]
+                             + [time.perf_counter()])
+            self._stop.wait(0.004)
+
     def _run(self):
+        got = self._nvml_handle()
+        if got is not None:
+            try:
+                self.source = "nvml"
+                self._run_nvml(*got)
+                return
+            except Exception:
+                self.source = "nvidia-smi"
         while not self._stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.device)],
                                      capture_output=True, text=True, timeout=5).stdout.strip()
                 if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                    self.rows.append([x.strip() for x in out.split(",")] + [time.perf_counter()])
             except Exception:
                 pass
             self._stop.wait(0.2)
@@ -73,7 +114,11 @@ class ClockSampler:
         if self._t:
             self._t.join(timeout=6)
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        rows = self.rows
+        if self.window is not None:  # the samples taken while the device-timed loop ran, if any fell inside
+            inside = [r for r in rows if self.window[0] <= r[-1] <= self.window[1]]
+            rows = inside or rows
+        for r in rows:
             try:
                 sm.append(float(r[1]))
                 mx.append(float(r[2]))
@@ -84,9 +129,10 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(nm)
         if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": self.source}
         sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm), "source": self.source,
+                "window": "timed region" if self.window is not None and rows is not self.rows else "warm-up to end of the device-timed loops"}
 
 
 def measured_peak_gbs():
@@ -277,17 +323,23 @@ def run_ours(args):
         if world > 1:
             dist.barrier()
         launches0 = eng.timings()["kernel_launches"]
-        sampler = ClockSampler(local)
+        try:
+            dev_uuid = str(torch.cuda.get_device_properties(local).uuid)
+        except Exception:
+            dev_uuid = None
+        sampler = ClockSampler(local, dev_uuid)
         if rank == 0:
             sampler.start()
         evs = []
         e_start, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
+        t_w0 = time.perf_counter()
         e_start.record(stream)
         for k in range(args.steps):
             one_step(evs)
         e_end.record(stream)
         torch.cuda.synchronize()
+        sampler.window = (t_w0, time.perf_counter())
         if world > 1:
             dist.barrier()
         if px is not None:
@@ -348,7 +400,7 @@ def run_ours(args):
         pipe_ms, pipe_steps = None, 0
         if (world == 1 or px is not None) and not multi:
             pipe_steps = max(10, args.steps)
-            depth = 2 if world == 1 else 3  # batches in flight (the sharded pipeline defers a batch's emit pass by one submit)
+            depth = (3 if os.environ.get("FGS_PIPE_SLOTS") == "3" else 2) if world == 1 else 3  # batches in flight (the sharded pipeline defers a batch's emit pass by one submit)
 
             def pipe_loop(k, sub):
                 inflight = 0
@@ -362,17 +414,6 @@ def run_ours(args):
                     res_holder[0] = eng.collect()
 
             pipe_loop(depth, lambda: eng.submit(tables[0]))  # every pipeline slot now holds the batch
-            torch.cuda.synchronize()
-            if world > 1:
-                dist.barrier()
-            t0 = time.perf_counter()
-            pipe_loop(pipe_steps, lambda: eng.submit(tables[0]))
-            torch.cuda.synchronize()
-            pipe_ms = 1e3 * (time.perf_counter() - t0)
-            if world > 1:
-                t = torch.tensor([pipe_ms], device="cuda", dtype=torch.float64)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                pipe_ms = float(t.item())
         # N > 1, tables resident in HBM (both pipeline slots hold the batch after the loop above): the headline loop
         # again with two batches in flight, so that every merge overlaps a pass of the other batch. Each step still runs
         # both passes, both merges, the per-pod epilogue and the D2H of the per-pod results.
@@ -389,13 +430,28 @@ def run_ours(args):
             ov_loop(args.steps)
             o_e.record(stream)  # after the last collect returned: every stream of the pipeline has drained
             torch.cuda.synchronize()
+            sampler.window = (sampler.window[0], time.perf_counter())  # both device-timed loops
             dist.barrier()
             eng.peer_status()
             ov_launches = eng.timings()["kernel_launches"] - launches0
             t = torch.tensor([o_s.elapsed_time(o_e)], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ov_ms = float(t.item())
+        # the clock sampler (an nvidia-smi process every 200 ms) has covered the device-timed loops; it stops here: its
+        # driver queries delay kernel launches, which the host-paced pipeline below would feel
         clocks = sampler.stop() if rank == 0 else None
+        if (world == 1 or px is not None) and not multi:
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            pipe_loop(pipe_steps, lambda: eng.submit(tables[0]))
+            torch.cuda.synchronize()
+            pipe_ms = 1e3 * (time.perf_counter() - t0)
+            if world > 1:
+                t = torch.tensor([pipe_ms], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                pipe_ms = float(t.item())
 
     # ---- true scheduling cycles: one pod at a time with assume + Reserve between pods ----------
     # A second engine on the same cluster (the sequence rewrites node rows); a bounded prefix of the queue.

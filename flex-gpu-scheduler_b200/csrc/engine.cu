@@ -289,6 +289,8 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
         const int hw = (int)std::thread::hardware_concurrency();
         if (hw > 0 && nth > hw) nth = hw;
         e->host_threads = nth < 1 ? 1 : nth;
+        const char* ps = getenv("FGS_PIPE_SLOTS");
+        if (ps && ps[0] == '3') e->pipe_slots = 3;
     }
     if (c->stream) {
         e->stream = (cudaStream_t)c->stream;
@@ -1053,9 +1055,9 @@ extern "C" int fgs_resubmit(fgs_engine* eh, const fgs_eval_opts* opts) {
 extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
-    if (e->in_flight >= (e->peer ? 3 : 2))
-        return e->fail(FGS_E_STATE, e->peer ? "fgs_submit: three batches are in flight already; fgs_collect one first"
-                                            : "fgs_submit: two batches are in flight already; fgs_collect one first");
+    if (e->in_flight >= e->ring())
+        return e->fail(FGS_E_STATE, e->ring() == 3 ? "fgs_submit: three batches are in flight already; fgs_collect one first"
+                                                   : "fgs_submit: two batches are in flight already; fgs_collect one first");
     if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_submit: sample / skip_pass_b need fgs_evaluate");
     if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_submit: nominated pods are set (their per-batch columns are not double-buffered): use fgs_evaluate");
     cudaSetDevice(e->device);
