@@ -54,6 +54,7 @@ class ClockSampler:
         self.source = "nvidia-smi"
         self.window = None  # (t0, t1) in time.perf_counter() terms: the timed region
         self._stop = threading.Event()
+        self.ready = threading.Event()  # set once the first sample is in
         self._t = None
 
     def _nvml_handle(self):
@@ -84,6 +85,7 @@ class ClockSampler:
             r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
             self.rows.append([str(self.device), str(sm), str(mx), "", hex(r)] + ["Active" if r & b else "Not Active" for _, b in bits]
                              + [time.perf_counter()])
+            self.ready.set()
             self._stop.wait(0.004)
 
     def _run(self):
@@ -101,6 +103,7 @@ class ClockSampler:
                                      capture_output=True, text=True, timeout=5).stdout.strip()
                 if out:
                     self.rows.append([x.strip() for x in out.split(",")] + [time.perf_counter()])
+                    self.ready.set()
             except Exception:
                 pass
             self._stop.wait(0.2)
@@ -317,19 +320,21 @@ def run_ours(args):
         eng.stage_pods(tables[0])
         view = eng.device_view()
         eng.synchronize()
-        for _ in range(args.warmup):
-            one_step()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        launches0 = eng.timings()["kernel_launches"]
         try:
             dev_uuid = str(torch.cuda.get_device_properties(local).uuid)
         except Exception:
             dev_uuid = None
         sampler = ClockSampler(local, dev_uuid)
         if rank == 0:
-            sampler.start()
+            sampler.start()  # before the warm-up: NVML takes some ms to come up, the timed region is short
+        for _ in range(args.warmup):
+            one_step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        if rank == 0:
+            sampler.ready.wait(2.0)
+        launches0 = eng.timings()["kernel_launches"]
         evs = []
         e_start, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
@@ -400,7 +405,7 @@ def run_ours(args):
         pipe_ms, pipe_steps = None, 0
         if (world == 1 or px is not None) and not multi:
             pipe_steps = max(10, args.steps)
-            depth = (3 if os.environ.get("FGS_PIPE_SLOTS") == "3" else 2) if world == 1 else 3  # batches in flight (the sharded pipeline defers a batch's emit pass by one submit)
+            depth = 2 if world == 1 else 3  # batches in flight (the sharded pipeline defers a batch's emit pass by one submit)
 
             def pipe_loop(k, sub):
                 inflight = 0

@@ -289,8 +289,6 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
         const int hw = (int)std::thread::hardware_concurrency();
         if (hw > 0 && nth > hw) nth = hw;
         e->host_threads = nth < 1 ? 1 : nth;
-        const char* ps = getenv("FGS_PIPE_SLOTS");
-        if (ps && ps[0] == '3') e->pipe_slots = 3;
     }
     if (c->stream) {
         e->stream = (cudaStream_t)c->stream;

@@ -85,8 +85,7 @@ struct Engine {
     };
     static constexpr int kSlots = 3; // two in flight on one GPU; three in the sharded pipeline (see submit_sharded)
     Slot slots[kSlots];
-    int pipe_slots = 2; // FGS_PIPE_SLOTS: batches in flight on a single engine (2 or 3)
-    int ring() const { return peer ? 3 : pipe_slots; }
+    int ring() const { return peer ? 3 : 2; } // a third batch in flight buys nothing on one GPU (tools/pipe_breakdown.py)
     uint64_t submit_seq = 0; // batches submitted so far: the sharded pipeline alternates two bitmaps by its parity
     int cur_slot = 0;       // slot whose buffers the members alias
     int in_flight = 0;      // submitted, not yet collected
