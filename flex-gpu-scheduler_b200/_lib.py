@@ -175,7 +175,7 @@ ABI = {
     "fgs_update_nodes": (C.c_int, [C.c_void_p, C.POINTER(NodeTable), p_i64]),
     "fgs_evaluate": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts), C.POINTER(Results)]),
     "fgs_select_victims": (C.c_int, [C.c_void_p, C.POINTER(Snapshot), C.POINTER(Podset), C.c_int64, C.POINTER(Quotas), C.c_int32, p_u8, p_u8,
-                                     p_i32]),
+                                     p_i32, p_i32]),
     "fgs_set_nominated": (C.c_int, [C.c_void_p, C.POINTER(PodTable), p_i32, p_i64]),
     "fgs_submit": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts)]),
     "fgs_collect": (C.c_int, [C.c_void_p, C.POINTER(Results)]),

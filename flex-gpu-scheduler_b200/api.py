@@ -272,14 +272,18 @@ class Engine:
         r.next_start_node_index = int(cr.next_start_node_index)
         return r
 
-    def select_victims(self, snapshot, pending, p, quotas=None, tracks_pods=True):
+    def select_victims(self, snapshot, pending, p, quotas=None, tracks_pods=True, pick=False):
         """Dry-run preemption of pending pod p on every node (fgs_select_victims):
-        (status [N] FGS_PREEMPT_*, victim flags [pods in the snapshot], victims per node [N])"""
+        (status [N] FGS_PREEMPT_*, victim flags [pods in the snapshot], victims per node [N]);
+        pick=True appends the node pickOneNodeForPreemption chooses among the candidates (-1: none)"""
         N = int(snapshot.contents.n_nodes)
         T = int(snapshot.contents.pods.n_pods)
         st, vic, cnt = np.zeros(max(N, 1), np.uint8), np.zeros(max(T, 1), np.uint8), np.zeros(max(N, 1), np.int32)
+        picked = C.c_int32(-1)
         self._check(self._lib.fgs_select_victims(self._h, snapshot, pending, p, quotas, 1 if tracks_pods else 0, _ptr(st, C.c_uint8),
-                                                 _ptr(vic, C.c_uint8), _ptr(cnt, C.c_int32)))
+                                                 _ptr(vic, C.c_uint8), _ptr(cnt, C.c_int32), C.byref(picked) if pick else None))
+        if pick:
+            return st[:N], vic[:T], cnt[:N], int(picked.value)
         return st[:N], vic[:T], cnt[:N]
 
     def set_nominated(self, pod_table=None, nodes=None, uid=None):

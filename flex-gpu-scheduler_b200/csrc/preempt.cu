@@ -71,6 +71,9 @@ struct PreemptParams {
     uint8_t* status;  // [N]
     uint8_t* victim;  // [T]
     int* n_victims;   // [N]
+    i64* cand;        // [4][N] per candidate node: highest victim priority, Σ (priority + 2^31), victims, earliest start
+                      // time among the victims of the highest priority — what pickOneNodeForPreemption compares
+    int* picked;      // the chosen candidate, -1 if there is none
 };
 
 struct Mask128 {
@@ -327,9 +330,54 @@ __global__ void __launch_bounds__(64) select_victims_kernel(const __grid_constan
     prm.status[n] = st;
     if (st == FGS_PREEMPT_CANDIDATE) {
         prm.n_victims[n] = n_vic;
+        i64 hi = INT64_MIN, sum = 0, earliest = 0;
         for (int a = 0; a < cnt; ++a)
-            if (removed.get(a)) prm.victim[q0 + a] = 1; // what is still removed at the end is exactly the victim list
+            if (removed.get(a)) {
+                prm.victim[q0 + a] = 1; // what is still removed at the end is exactly the victim list
+                const i64 pr = V(VP_PRIO, a), t0 = V(VP_START, a);
+                sum += pr + 2147483648ll;
+                if (pr > hi) hi = pr, earliest = t0; // util.GetEarliestPodStartTime (scheduler/util/utils.go:56-78)
+                else if (pr == hi && t0 < earliest) earliest = t0;
+            }
+        prm.cand[n] = hi;
+        prm.cand[prm.n_nodes + n] = sum;
+        prm.cand[2 * prm.n_nodes + n] = n_vic;
+        prm.cand[3 * prm.n_nodes + n] = earliest;
     }
+}
+
+// pickOneNodeForPreemption (vendor/k8s.io/kubernetes/pkg/scheduler/framework/preemption/preemption.go:386-505) over the
+// candidates: no PodDisruptionBudgets here, so criterion 1 ties everywhere; then the lowest "highest victim priority",
+// the smallest sum of priorities, the fewest victims, the LATEST earliest-start-time of the highest-priority victims.
+// The reference breaks what is left by Go map order ("sort of randomly"); here the lowest node index wins.
+struct PickKey {
+    i64 hi, sum, cnt, start;
+    int node;
+};
+__device__ __forceinline__ bool pick_better(const PickKey& a, const PickKey& b) { // is a a better choice than b?
+    if (b.node < 0) return a.node >= 0;
+    if (a.node < 0) return false;
+    if (a.hi != b.hi) return a.hi < b.hi;
+    if (a.sum != b.sum) return a.sum < b.sum;
+    if (a.cnt != b.cnt) return a.cnt < b.cnt;
+    if (a.start != b.start) return a.start > b.start;
+    return a.node < b.node;
+}
+__global__ void __launch_bounds__(1024) pick_candidate_kernel(const uint8_t* __restrict__ status, const i64* __restrict__ cand, i64 N, int* __restrict__ picked) {
+    __shared__ PickKey sh[1024];
+    PickKey best = {0, 0, 0, 0, -1};
+    for (i64 n = threadIdx.x; n < N; n += blockDim.x) {
+        if (status[n] != FGS_PREEMPT_CANDIDATE) continue;
+        const PickKey k = {cand[n], cand[N + n], cand[2 * N + n], cand[3 * N + n], (int)n};
+        if (pick_better(k, best)) best = k;
+    }
+    sh[threadIdx.x] = best;
+    __syncthreads();
+    for (int w = blockDim.x / 2; w > 0; w >>= 1) {
+        if ((int)threadIdx.x < w && pick_better(sh[threadIdx.x + w], sh[threadIdx.x])) sh[threadIdx.x] = sh[threadIdx.x + w];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *picked = sh[0].node;
 }
 
 } // namespace
@@ -339,7 +387,7 @@ __global__ void __launch_bounds__(64) select_victims_kernel(const __grid_constan
 using namespace fgs;
 
 extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, const fgs_podset* pending, int64_t p, const fgs_quotas* q,
-                                  int32_t tracks_pods, uint8_t* node_status, uint8_t* victim, int32_t* n_victims) {
+                                  int32_t tracks_pods, uint8_t* node_status, uint8_t* victim, int32_t* n_victims, int32_t* picked_node) {
     if (!eh || !snap || !pending || !node_status) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
     if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_select_victims before fgs_upload_nodes");
@@ -348,6 +396,7 @@ extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, cons
     if (p < 0 || p >= pending->n_pods) return e->fail(FGS_E_INVALID, "fgs_select_victims: pod index out of range");
     const int64_t N = snap->n_nodes, T = snap->pods.n_pods;
     const int S = e->S, W = 2 + S;
+    if (picked_node) *picked_node = -1;
     if (N == 0) return FGS_OK;
     for (int64_t n = 0; n < N; ++n)
         if (snap->pod_off[n + 1] - snap->pod_off[n] > kMaxPodsPerNode)
@@ -400,7 +449,7 @@ extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, cons
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
     const size_t in_bytes = h.size() * sizeof(int64_t);
     const size_t small_bytes = NS + sizeof(uint32_t) * NS + 64;                    // has_eq, used_scalar_present
-    const size_t out_bytes = (size_t)N + Tn + sizeof(int) * (size_t)N + 64;          // status, victim, n_victims
+    const size_t out_bytes = (size_t)N + Tn + sizeof(int) * (size_t)N + 4 * sizeof(int64_t) * (size_t)N + 256; // status, victim, n_victims, cand, picked
     char* d = nullptr;
     FGS_CUDA(e, cudaMalloc(&d, in_bytes + small_bytes + out_bytes + 256));
     char* d_small = d + ((in_bytes + 63) / 64) * 64;
@@ -445,11 +494,19 @@ extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, cons
     prm.status = (uint8_t*)d_out;
     prm.victim = prm.status + ((N + 15) / 16) * 16;
     prm.n_victims = (int*)(prm.victim + ((Tn + 15) / 16) * 16);
+    prm.cand = (i64*)((char*)prm.n_victims + ((sizeof(int) * (size_t)N + 15) / 16) * 16);
+    prm.picked = (int*)(prm.cand + 4 * (size_t)N);
     if (ce == cudaSuccess) {
         select_victims_kernel<<<(unsigned)((N + 63) / 64), 64, 0, e->stream>>>(prm);
         e->launches++;
+        if (picked_node) {
+            pick_candidate_kernel<<<1, 1024, 0, e->stream>>>(prm.status, prm.cand, N, prm.picked);
+            e->launches++;
+        }
         ce = cudaGetLastError();
     }
+    int h_picked = -1;
+    if (ce == cudaSuccess && picked_node) ce = cudaMemcpyAsync(&h_picked, prm.picked, sizeof(int), cudaMemcpyDeviceToHost, e->stream);
     std::vector<int> h_cnt((size_t)N);
     if (ce == cudaSuccess) ce = cudaMemcpyAsync(node_status, prm.status, (size_t)N, cudaMemcpyDeviceToHost, e->stream);
     if (ce == cudaSuccess && victim && T) ce = cudaMemcpyAsync(victim, prm.victim, (size_t)T, cudaMemcpyDeviceToHost, e->stream);
@@ -459,5 +516,6 @@ extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, cons
     if (ce != cudaSuccess) return e->fail(FGS_E_CUDA, std::string("fgs_select_victims: ") + cudaGetErrorString(ce));
     if (n_victims)
         for (int64_t n = 0; n < N; ++n) n_victims[n] = h_cnt[(size_t)n];
+    if (picked_node) *picked_node = h_picked;
     return FGS_OK;
 }

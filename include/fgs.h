@@ -316,12 +316,19 @@ int fgs_quota_check(fgs_engine* e, const fgs_pod_table* pods, const fgs_quotas* 
  *   node_status[n_nodes]  FGS_PREEMPT_*
  *   victim[snap->pods.n_pods]  1 for the pods chosen as victims on a CANDIDATE node (may be NULL)
  *   n_victims[n_nodes]    (may be NULL)
+ *   picked_node           (may be NULL) the candidate pickOneNodeForPreemption (preemption.go:386-505) chooses among
+ *                         ALL candidate nodes, -1 if there is none: lowest highest-victim-priority, then smallest sum
+ *                         of victim priorities, then fewest victims, then the latest earliest-start-time of the
+ *                         highest-priority victims (a pod without a start time counts as 0; the reference takes
+ *                         time.Now()); what is left the reference breaks by Go map order, here the lowest node index
+ *                         wins. The reference dry-runs a random window of the nodes (GetOffsetAndNumCandidates) and
+ *                         picks among those; this is the pick over the whole cluster.
  * `snap` must be the snapshot the node table was packed from; single engine holding the whole cluster; at most 128
- * pods per node. The caller filters the nodes by nodesWherePreemptionMightHelp (status plane code != 3) and picks
- * a candidate (pickOneNodeForPreemption) on the host. */
+ * pods per node. The caller filters the nodes by nodesWherePreemptionMightHelp (status plane code != 3) — a node it
+ * drops must not be picked: pass picked_node = NULL then and choose among node_status / n_victims on the host. */
 int fgs_select_victims(fgs_engine* e, const fgs_snapshot* snap, const fgs_podset* pending, int64_t p,
                        const fgs_quotas* q, int32_t tracks_pods, uint8_t* node_status, uint8_t* victim,
-                       int32_t* n_victims);
+                       int32_t* n_victims, int32_t* picked_node);
 
 /* The same ElasticQuota check for callers that must not allocate. This entry point has no counterpart
  * in the reference; it exists for hosts that keep device memory in a fixed arena of their own, for code on a

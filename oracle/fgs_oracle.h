@@ -138,6 +138,14 @@ int fgs_oracle_select_victims(const fgs_snapshot* snap, const fgs_podset* pendin
                               const fgs_quotas* q, int tracks_pods, uint8_t* node_status, uint8_t* victim,
                               int32_t* n_victims);
 
+/* pickOneNodeForPreemption (vendor/k8s.io/kubernetes/pkg/scheduler/framework/preemption/preemption.go:386-505) over
+ * the candidates a dry run produced (node_status / victim as fgs_oracle_select_victims wrote them; no
+ * PodDisruptionBudgets, so NumPDBViolations is 0 everywhere). The reference's last tie-break is the iteration order of
+ * a Go map: tie_set[n] = 1 for EVERY node it may return (the nodes still level after criterion 5). Returns their
+ * number (0: no candidate). */
+int64_t fgs_oracle_pick_preemption_node(const fgs_snapshot* snap, const uint8_t* node_status, const uint8_t* victim,
+                                        uint8_t* tie_set);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,6 +67,8 @@ def load():
     lib.fgs_oracle_evaluate_nominated.restype = C.c_int
     lib.fgs_oracle_evaluate_nominated.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64, C.c_int64,
                                                   C.c_int, C.POINTER(L.Podset), L.p_i32, L.p_i64, L.p_i64, C.POINTER(OracleOut)]
+    lib.fgs_oracle_pick_preemption_node.restype = C.c_int64
+    lib.fgs_oracle_pick_preemption_node.argtypes = [C.POINTER(L.Snapshot), L.p_u8, L.p_u8, L.p_u8]
     lib.fgs_oracle_select_victims.restype = C.c_int
     lib.fgs_oracle_select_victims.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.c_int64, C.POINTER(L.PluginCfg),
                                               C.POINTER(L.Quotas), C.c_int, L.p_u8, L.p_u8, L.p_i32]
@@ -203,3 +205,14 @@ def select_victims(snapshot, pending, p, cfg, quotas=None, tracks_pods=True):
     load().fgs_oracle_select_victims(snapshot, pending, p, C.byref(cfg), quotas, 1 if tracks_pods else 0, st.ctypes.data_as(L.p_u8),
                                      vic.ctypes.data_as(L.p_u8), cnt.ctypes.data_as(L.p_i32))
     return st[:N], vic[:T], cnt[:N]
+
+
+def pick_preemption_node(snapshot, node_status, victim):
+    """pickOneNodeForPreemption over the candidates of a dry run: the mask [N] of the nodes the reference may return
+    (its last tie-break is Go map order)"""
+    N = int(snapshot.contents.n_nodes)
+    st = np.ascontiguousarray(node_status, np.uint8)
+    vic = np.ascontiguousarray(victim if len(victim) else np.zeros(1, np.uint8), np.uint8)
+    ties = np.zeros(max(N, 1), np.uint8)
+    load().fgs_oracle_pick_preemption_node(snapshot, st.ctypes.data_as(L.p_u8), vic.ctypes.data_as(L.p_u8), ties.ctypes.data_as(L.p_u8))
+    return ties[:N].astype(bool)

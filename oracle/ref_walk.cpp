@@ -1348,3 +1348,88 @@ extern "C" int fgs_oracle_select_victims(const fgs_snapshot* snap, const fgs_pod
     }
     return 0;
 }
+
+// pickOneNodeForPreemption, preemption.go:397-505, stage by stage as the reference narrows minNodes1 / minNodes2.
+// victims.Pods is in reprieve order (most important first), so Pods[0] is the victim with the highest priority — taken
+// here as the maximum, which is the same pod's priority.
+extern "C" int64_t fgs_oracle_pick_preemption_node(const fgs_snapshot* snap, const uint8_t* node_status, const uint8_t* victim,
+                                                   uint8_t* tie_set) {
+    const i64 N = snap->n_nodes;
+    const fgs_podset* ps = &snap->pods;
+    auto prio = [&](i64 a) { return (i64)(ps->priority ? ps->priority[a] : 0); };
+    auto start = [&](i64 a) { return ps->start_time ? ps->start_time[a] : (i64)0; };
+    std::memset(tie_set, 0, (size_t)N);
+    std::vector<i64> nodes1, nodes2;
+    for (i64 n = 0; n < N; ++n) // :404-415 — NumPDBViolations == 0 on every candidate
+        if (node_status[n] == FGS_PREEMPT_CANDIDATE) nodes1.push_back(n);
+    if (nodes1.empty()) return 0;
+    auto victimsOf = [&](i64 n) {
+        std::vector<i64> v;
+        for (i64 a = snap->pod_off[n]; a < snap->pod_off[n + 1]; ++a)
+            if (victim[a]) v.push_back(a);
+        return v;
+    };
+    auto finish = [&](const std::vector<i64>& set) {
+        for (i64 n : set) tie_set[n] = 1;
+        return (i64)set.size();
+    };
+    if (nodes1.size() == 1) return finish(nodes1);
+    // :422-440 minimum highest-priority victim
+    i64 minHighest = INT64_MAX;
+    for (i64 n : nodes1) {
+        i64 hi = INT64_MIN;
+        for (i64 a : victimsOf(n)) hi = std::max(hi, prio(a));
+        if (hi < minHighest) {
+            minHighest = hi;
+            nodes2.clear();
+        }
+        if (hi == minHighest) nodes2.push_back(n);
+    }
+    if (nodes2.size() == 1) return finish(nodes2);
+    // :444-466 smallest sum of (priority + MaxInt32 + 1)
+    i64 minSum = INT64_MAX;
+    nodes1.clear();
+    for (i64 n : nodes2) {
+        i64 sum = 0;
+        for (i64 a : victimsOf(n)) sum += prio(a) + ((i64)INT32_MAX + 1);
+        if (sum < minSum) {
+            minSum = sum;
+            nodes1.clear();
+        }
+        if (sum == minSum) nodes1.push_back(n);
+    }
+    if (nodes1.size() == 1) return finish(nodes1);
+    // :470-486 fewest victims
+    i64 minPods = INT64_MAX;
+    nodes2.clear();
+    for (i64 n : nodes1) {
+        const i64 c = (i64)victimsOf(n).size();
+        if (c < minPods) {
+            minPods = c;
+            nodes2.clear();
+        }
+        if (c == minPods) nodes2.push_back(n);
+    }
+    if (nodes2.size() == 1) return finish(nodes2);
+    // :490-511 latest earliest-start-time of the highest-priority victims (util.GetEarliestPodStartTime, utils.go:56-78);
+    // a node is replaced only by a strictly later one, so every node with the latest time may be the one returned
+    auto earliestStart = [&](i64 n) {
+        const std::vector<i64> v = victimsOf(n);
+        i64 earliest = start(v[0]), maxPrio = prio(v[0]);
+        for (i64 a : v) {
+            if (prio(a) == maxPrio) {
+                if (start(a) < earliest) earliest = start(a);
+            } else if (prio(a) > maxPrio) {
+                maxPrio = prio(a);
+                earliest = start(a);
+            }
+        }
+        return earliest;
+    };
+    i64 latest = INT64_MIN;
+    for (i64 n : nodes2) latest = std::max(latest, earliestStart(n));
+    nodes1.clear();
+    for (i64 n : nodes2)
+        if (earliestStart(n) == latest) nodes1.push_back(n);
+    return finish(nodes1);
+}

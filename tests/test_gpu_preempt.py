@@ -49,15 +49,20 @@ def test_synthetic_cluster_matches_the_oracle(gpu_ok, oracle, tracks, with_quota
     cfg = fgs.config_plugins(4)
     eng = _engine(s.snapshot, cfg)
     q = s.quotas if with_quotas else None
-    seen = set()
+    seen, picks = set(), []
     for p in range(0, s.n_pending, 2):
-        st, vic, cnt = eng.select_victims(s.snapshot, s.pending, p, q, tracks_pods=tracks)
+        st, vic, cnt, picked = eng.select_victims(s.snapshot, s.pending, p, q, tracks_pods=tracks, pick=True)
         rst, rvic, rcnt = oracle.select_victims(s.snapshot, s.pending, p, cfg, q, tracks_pods=tracks)
         assert np.array_equal(st, rst), (p, np.nonzero(st != rst)[0][:5], st[st != rst][:5], rst[st != rst][:5])
         assert np.array_equal(vic, rvic), p
         assert np.array_equal(cnt, rcnt), p
+        # pickOneNodeForPreemption: the reference may return any node of the oracle's tie set; the engine the lowest
+        ties = np.nonzero(oracle.pick_preemption_node(s.snapshot, rst, rvic))[0]
+        assert picked == (int(ties[0]) if len(ties) else -1), (p, picked, ties[:5])
+        picks.append(picked)
         seen |= set(int(x) for x in st)
     assert {L.FGS_PREEMPT_CANDIDATE, L.FGS_PREEMPT_NO_VICTIMS, L.FGS_PREEMPT_NOT_A_NODE} <= seen, seen
+    assert any(x >= 0 for x in picks)
     eng.close()
 
 
@@ -102,3 +107,36 @@ def test_handmade_devices_priorities_and_reprieve(gpu_ok, oracle):
         if p == 3:
             assert (st == L.FGS_PREEMPT_NO_VICTIMS).all()
     eng.close()
+
+
+def test_pick_one_node_criteria_on_the_gpu(gpu_ok, oracle):
+    """every criterion of pickOneNodeForPreemption decides once: nodes that differ only in what that criterion looks at"""
+    def n(pods):
+        return B.node({"cpu": 1000, "memory": 64 * GiB, "pods": 110}, pods)
+
+    def v(prio, start=0, cpu=600):
+        return B.pod([B.ctr({"cpu": cpu})], priority=prio, node_name=True, start=start)
+
+    pend = B.build_podset([B.pod([B.ctr({"cpu": 900})], priority=1000)])
+    cfg = fgs.plugin_cfg(filter_plugins=("NodeResourcesFit",), score_plugins=(("NodeResourcesFit", 1),))
+    INT32_MIN = -2147483648
+    cases = [
+        ([n([v(50)]), n([v(40)]), n([v(60)])], [1]),                                            # lowest highest-priority victim
+        ([n([v(50, cpu=300), v(50, cpu=300)]), n([v(50, cpu=300), v(10, cpu=300)]), n([v(50, cpu=300), v(20, cpu=300)])], [1]),  # sum
+        ([n([v(-1, cpu=300), v(-1, cpu=300)]), n([v(-1)])], [1]),                               # the +2^31 shift: fewer pods win
+        ([n([v(7, cpu=300), v(INT32_MIN, cpu=300)]), n([v(7)])], [1]),                          # equal sums, fewer victims
+        ([n([v(5, start=10)]), n([v(5, start=30)]), n([v(5, start=20)])], [1]),                 # latest start time
+        ([n([v(5, start=9, cpu=300), v(5, start=30, cpu=300)]), n([v(5, start=10, cpu=300), v(5, start=11, cpu=300)])], [1]),  # EARLIEST of the top pods
+        ([n([v(5, start=7)]), n([v(3)], ), n([v(5, start=7)]), n([v(3)])], [1, 3]),              # level to the end: a tie set
+        ([n([v(2000)]), n([])], []),                                                            # nobody to evict
+    ]
+    for nodes, want in cases:
+        snap = B.build_snapshot(nodes)
+        eng = _engine(snap.ptr, cfg)
+        st, vic, cnt, picked = eng.select_victims(snap.ptr, pend.ptr, 0, pick=True)
+        rst, rvic, rcnt = oracle.select_victims(snap.ptr, pend.ptr, 0, cfg)
+        assert np.array_equal(st, rst) and np.array_equal(vic, rvic)
+        ties = np.nonzero(oracle.pick_preemption_node(snap.ptr, rst, rvic))[0].tolist()
+        assert ties == want, (want, ties, st.tolist(), vic.tolist())
+        assert picked == (want[0] if want else -1)
+        eng.close()

@@ -114,3 +114,37 @@ def test_dry_run_preemption_golden(oracle):
         assert int(st[0]) == L.FGS_PREEMPT_CANDIDATE, case["name"]
         got = [d["name"] for d, v in zip(case["assigned"], vic) if v]
         assert got == case["want_victims"] and int(cnt[0]) == len(got), (case["name"], got)
+
+
+def test_pick_one_node_for_preemption(oracle):
+    """pickOneNodeForPreemption (preemption.go:386-505) criterion by criterion; the vendored package carries no tests, so
+    the expectations are the function's documented order: highest victim priority, sum of priorities (+2^31 each),
+    number of victims, latest earliest-start-time of the highest-priority victims, then any of the rest"""
+    import numpy as np
+    import builders as B
+    from flex_gpu_scheduler_b200 import _lib as L
+
+    def run(per_node, status=None):
+        """per_node: for every node a list of (priority, start, is_victim)"""
+        nodes = [B.node({"cpu": 1000, "pods": 110}, [B.pod([B.ctr({"cpu": 1})], priority=pr, start=st, node_name=True) for pr, st, _ in pods])
+                 for pods in per_node]
+        snap = B.build_snapshot(nodes)
+        vic = np.array([int(v) for pods in per_node for _, _, v in pods] or [0], np.uint8)
+        st = np.array(status if status is not None else
+                      [L.FGS_PREEMPT_CANDIDATE if any(v for _, _, v in pods) else L.FGS_PREEMPT_NO_VICTIMS for pods in per_node], np.uint8)
+        return np.nonzero(oracle.pick_preemption_node(snap.ptr, st, vic))[0].tolist()
+
+    V, K = True, False
+    assert run([[(5, 0, V)]]) == [0]
+    assert run([[(5, 0, K)], [(9, 0, K)]]) == []
+    assert run([[(50, 0, V)], [(40, 0, V), (40, 0, V), (40, 0, V)], [(60, 0, V)]]) == [1]           # criterion 2 before 3 and 4
+    assert run([[(50, 0, V), (50, 0, V)], [(50, 0, V), (10, 0, V)], [(50, 0, V), (20, 0, V)]]) == [1]
+    assert run([[(-1, 0, V), (-1, 0, V)], [(-1, 0, V)]]) == [1]
+    assert run([[(7, 0, V), (-2147483648, 0, V)], [(7, 0, V)]]) == [1]                              # equal sums: fewer victims
+    assert run([[(5, 10, V)], [(5, 30, V)], [(5, 20, V)]]) == [1]
+    assert run([[(5, 9, V), (5, 30, V)], [(5, 10, V), (5, 11, V)]]) == [1]
+    assert run([[(5, 9, V), (4, 1, V)], [(5, 8, V), (4, 50, V)]]) == [0]                            # only the top-priority victims' times count
+    assert run([[(5, 7, V)], [(3, 0, V)], [(5, 7, V)], [(3, 0, V)]]) == [1, 3]
+    assert run([[(5, 7, V), (1, 0, K)], [(5, 7, V)]]) == [0, 1]                                     # pods that stay do not count
+    # a node that is not a candidate is never picked, whatever its victim flags say
+    assert run([[(1, 0, V)], [(9, 0, V)]], status=[L.FGS_PREEMPT_STILL_UNFIT, L.FGS_PREEMPT_CANDIDATE]) == [1]
