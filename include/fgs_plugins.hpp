@@ -9,7 +9,7 @@
 //   Fit                Name, Filter, Score                                      vendor/…/plugins/noderesources/fit.go:42,221-339
 //   Allocatable        Name, New (args validation), Score, NormalizeScore       pkg/noderesources/allocatable.go:43-171
 //   Coscheduling       Name, PreFilter, Permit                                  pkg/coscheduling/coscheduling.go:58,124-215
-//   CapacityScheduling Name, PreFilter                                          pkg/capacityscheduling/capacity_scheduling.go:103,201-275
+//   CapacityScheduling Name, PreFilter, PostFilter (dry-run preemption + pick)    pkg/capacityscheduling/capacity_scheduling.go:103,201-275,320-338,465-644
 //   Framework          RunPreFilterPlugins (the new pack + evaluate stage), RunFilterPlugins, RunScorePlugins, selectHost
 //
 // A "node" is its index in the fgs_snapshot (the reference keys by node name), a "pod" an index into an
@@ -485,7 +485,69 @@ class CapacityScheduling {
         }
     }
 
+
+    // PostFilter — :320-338 → preemption.Evaluator.Preempt (vendor/…/framework/preemption/preemption.go:138-195) up to and
+    // including SelectCandidate: the nodes where preemption might help (nodesWherePreemptionMightHelp, :335-350: not
+    // UnschedulableAndUnresolvable in the filter pass), SelectVictimsOnNode on every one of them in ONE call, and
+    // pickOneNodeForPreemption. prepareCandidate (evictions, clearing nominations: API-server work) stays with the caller,
+    // who gets the victims. `eval` is the pod's PreFilter result (nullptr: every node might help). No PodDisruptionBudgets,
+    // no extenders; every potential node is dry-run (the reference stops after GetOffsetAndNumCandidates' quota).
+    struct PostFilterResult {
+        int64_t NominatedNode = -1;       // framework.PostFilterResult.NominatedNodeName as a snapshot index; -1 = ""
+        std::vector<int64_t> Victims;     // rows of snapshot->pods to evict on that node, most important first is NOT implied
+        int64_t Candidates = 0;           // nodes on which preemption would work
+    };
+    std::pair<PostFilterResult, framework::Status> PostFilter(const fgs_podset* pending, int64_t pod, const fgs_quotas* q,
+                                                             const PodEvaluation* eval = nullptr, bool tracks_pods = true) const {
+        using framework::Code;
+        using framework::Status;
+        const fgs_snapshot* snap = h_.snapshot();
+        if (!snap || snap->n_nodes == 0) return {PostFilterResult{}, Status(Code::Error, "no nodes available")}; // :199-201
+        const int64_t N = snap->n_nodes, T = snap->pods.n_pods;
+        std::vector<uint8_t> st((size_t)N), vic((size_t)std::max<int64_t>(T, 1));
+        std::vector<int32_t> cnt((size_t)N);
+        int32_t picked = -1;
+        h_.Check(fgs_select_victims(h_.engine(), snap, pending, pod, q, tracks_pods ? 1 : 0, st.data(), vic.data(), cnt.data(), &picked));
+        auto mightHelp = [&](int64_t n) { return !eval || eval->merged_code[(size_t)n] != (uint8_t)Code::UnschedulableAndUnresolvable; };
+        PostFilterResult r;
+        bool dropped_candidate = false;
+        for (int64_t n = 0; n < N; ++n)
+            if (st[(size_t)n] == FGS_PREEMPT_CANDIDATE) {
+                if (mightHelp(n)) r.Candidates++;
+                else dropped_candidate = true;
+            }
+        if (r.Candidates == 0) // :162-173 — the FitError text needs the per-node reasons; the code and the cleared nomination are the contract
+            return {r, Status(Code::Unschedulable, "preemption: 0/" + std::to_string(N) + " nodes are available")};
+        if (dropped_candidate && !mightHelp(picked)) picked = (int32_t)PickOnHost(snap, st, vic, mightHelp);
+        r.NominatedNode = picked;
+        for (int64_t a = snap->pod_off[picked]; a < snap->pod_off[picked + 1]; ++a)
+            if (vic[(size_t)a]) r.Victims.push_back(a);
+        return {r, Status()};
+    }
+
   private:
+    // pickOneNodeForPreemption (:386-505) among the candidates `keep` lets through — only when the device's pick over
+    // all candidates landed on a node the filter pass had ruled out for good
+    template <typename Keep>
+    static int64_t PickOnHost(const fgs_snapshot* snap, const std::vector<uint8_t>& st, const std::vector<uint8_t>& vic, Keep keep) {
+        const fgs_podset& ps = snap->pods;
+        int64_t best = -1, bhi = 0, bsum = 0, bcnt = 0, bstart = 0;
+        for (int64_t n = 0; n < snap->n_nodes; ++n) {
+            if (st[(size_t)n] != FGS_PREEMPT_CANDIDATE || !keep(n)) continue;
+            int64_t hi = INT64_MIN, sum = 0, c = 0, start = 0;
+            for (int64_t a = snap->pod_off[n]; a < snap->pod_off[n + 1]; ++a) {
+                if (!vic[(size_t)a]) continue;
+                const int64_t pr = ps.priority ? ps.priority[a] : 0, t0 = ps.start_time ? ps.start_time[a] : 0;
+                sum += pr + 2147483648ll;
+                c++;
+                if (pr > hi) hi = pr, start = t0;
+                else if (pr == hi && t0 < start) start = t0;
+            }
+            const bool better = best < 0 || (hi != bhi ? hi < bhi : sum != bsum ? sum < bsum : c != bcnt ? c < bcnt : start > bstart);
+            if (better) best = n, bhi = hi, bsum = sum, bcnt = c, bstart = start;
+        }
+        return best;
+    }
     Handle& h_;
     std::vector<uint8_t> code_;
 };

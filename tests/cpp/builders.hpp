@@ -40,6 +40,7 @@ struct Pod {
     std::vector<Ctr> containers, init_containers;
     int32_t ns = 0, pg = -1, priority = 0, index = FGS_ANNOT_NONE;
     bool node_name = false;
+    int64_t start = 0; // pod.Status.StartTime
 };
 inline Pod MakePod(std::vector<Ctr> ctrs, int32_t ns = 0, int32_t pg = -1, int32_t priority = 0) {
     Pod p;
@@ -81,6 +82,7 @@ class Podset {
             prio_.push_back(p.priority);
             named_.push_back(p.node_name ? 1 : 0);
             annot_.push_back(p.index);
+            start_.push_back(p.start);
             ovp_.push_back(0);
         }
         ov_.assign(std::max<size_t>(pods.size(), 1) * (size_t)W, 0);
@@ -90,11 +92,13 @@ class Podset {
         pad(ns_), pad(pg_), pad(prio_), pad(named_), pad(annot_), pad(n_init_), pad(ovp_), pad(c_pres_), pad(c_lpres_);
         if (c_req_.empty()) c_req_.assign((size_t)W, 0);
         if (c_lim_.empty()) c_lim_.assign(2, 0);
+        if (start_.empty()) start_.push_back(0);
         ps_ = fgs_podset{};
         ps_.n_pods = (int64_t)pods.size();
         ps_.n_scalars = S;
         ps_.ns = ns_.data(), ps_.pg = pg_.data(), ps_.priority = prio_.data();
         ps_.has_node_name = named_.data(), ps_.index_annot = annot_.data();
+        ps_.start_time = start_.data();
         ps_.ctr_off = ctr_off_.data(), ps_.n_init = n_init_.data();
         ps_.overhead_present = ovp_.data(), ps_.overhead = ov_.data();
         ps_.n_ctrs = pods.empty() ? 0 : ctr_off_.back();
@@ -109,7 +113,7 @@ class Podset {
     std::vector<int32_t> ns_, pg_, prio_, annot_, n_init_;
     std::vector<uint8_t> named_;
     std::vector<uint32_t> ovp_, c_pres_, c_lpres_;
-    std::vector<int64_t> ctr_off_, ov_, c_req_, c_lim_;
+    std::vector<int64_t> ctr_off_, ov_, c_req_, c_lim_, start_;
     fgs_podset ps_;
 };
 

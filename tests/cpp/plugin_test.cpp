@@ -236,6 +236,42 @@ static void TestCapacityPreFilter(Handle& h) {
     }
 }
 
+// ---- CapacityScheduling.PostFilter: dry-run preemption on every node + pickOneNodeForPreemption ----------------------------------
+static void TestCapacityPostFilter(Handle& h) {
+    auto victim = [](int32_t prio, int64_t start) {
+        Pod p = MakePod({MakeCtr({{0, 600}})}, 0, -1, prio);
+        p.node_name = true;
+        p.start = start;
+        return p;
+    };
+    std::vector<Node> nodes = {makeNode(1000, 1 << 30), makeNode(1000, 1 << 30), makeNode(1000, 1 << 30), makeNode(1000, 1 << 30), makeNode(500, 1 << 30)};
+    nodes[0].on = {victim(50, 0)};
+    nodes[1].on = {victim(40, 5)};
+    nodes[2].on = {victim(40, 9)}; // as node 1, but its victim started later: the one to evict (preemption.go:393)
+    nodes[3].on = {victim(2000, 0)}; // more important than the preemptor
+    Snapshot snap(nodes);
+    h.UpdateSnapshot(snap.get());
+    Profile prof;
+    prof.Filter = {Fit::Name};
+    prof.Score = {{Fit::Name, 1}};
+    Framework fw(h, prof);
+    CapacityScheduling cs(h);
+    Podset pods({MakePod({MakeCtr({{0, 900}})}, 0, -1, 1000), MakePod({MakeCtr({{0, 900}})}, 0, -1, 10)}, 2);
+    CycleState st;
+    CHECK(fw.RunPreFilterPlugins(st, pods.get(), 0).IsSuccess());
+    CHECK(st.Read(Framework::kStateKey)->feasible_count == 0); // nothing fits: PostFilter's turn
+    auto r = cs.PostFilter(pods.get(), 0, nullptr, st.Read(Framework::kStateKey).get());
+    CHECK(r.second.IsSuccess());
+    CHECK(r.first.Candidates == 3 && r.first.NominatedNode == 2);
+    CHECK(r.first.Victims.size() == 1 && r.first.Victims[0] == snap.get()->pod_off[2]);
+    // a preemptor less important than everybody: no candidates, the nomination is cleared (preemption.go:162-173)
+    CycleState st2;
+    CHECK(fw.RunPreFilterPlugins(st2, pods.get(), 1).IsSuccess());
+    auto r2 = cs.PostFilter(pods.get(), 1, nullptr, st2.Read(Framework::kStateKey).get());
+    CHECK(r2.second.GetCode() == Code::Unschedulable && r2.first.NominatedNode == -1 && r2.first.Candidates == 0);
+    CHECK(r2.second.Message() == "preemption: 0/5 nodes are available");
+}
+
 // ---- Coscheduling PreFilter / Permit (core_test.go) ------------------------------------------------------------------------------
 static void TestCoscheduling(Handle& h) {
     // 3 nodes of 1 cpu each; PodGroup 0: MinMember 2, MinResources cpu 2 (enough) — PodGroup 1: MinMember 2,
@@ -276,6 +312,7 @@ int main() {
         TestNodeResourcesAllocatable(h);
         TestFlexGPU(h);
         TestCapacityPreFilter(h);
+        TestCapacityPostFilter(h);
         TestCoscheduling(h);
     } catch (const std::exception& e) {
         std::fprintf(stderr, "exception: %s\n", e.what());
