@@ -16,6 +16,7 @@ FGS_MAX_SCORE_RES = 8
 FGS_RES_CPU, FGS_RES_MEM, FGS_RES_EPH, FGS_RES_SCALAR0, FGS_RES_UNKNOWN = 0, 1, 2, 3, -1
 FGS_ANNOT_NONE = -(2 ** 31)
 FGS_PL_FLEXGPU, FGS_PL_FIT, FGS_PL_ALLOCATABLE = 1, 2, 4
+FGS_DIAG_FLEX0, FGS_DIAG_FLEX_PANIC, FGS_DIAG_FIT0, FGS_DIAG_NOT_A_NODE, FGS_DIAG_SLOTS = 0, 5, 6, 30, 32
 (FGS_PREEMPT_CANDIDATE, FGS_PREEMPT_NO_VICTIMS, FGS_PREEMPT_STILL_UNFIT, FGS_PREEMPT_QUOTA, FGS_PREEMPT_ERROR, FGS_PREEMPT_NOT_A_NODE,
  FGS_PREEMPT_PANIC) = range(7)
 FGS_CODE_SUCCESS, FGS_CODE_ERROR, FGS_CODE_UNSCHEDULABLE, FGS_CODE_UNRESOLVABLE, FGS_CODE_WAIT = 0, 1, 2, 3, 4
@@ -193,6 +194,7 @@ ABI = {
     "fgs_synchronize": (C.c_int, [C.c_void_p]),
     "fgs_status_plane": (C.c_int, [C.c_void_p, C.c_uint32, p_u8]),
     "fgs_reason_plane": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint16)]),
+    "fgs_fit_error_histogram": (C.c_int, [C.c_void_p, p_i32]),
     "fgs_schedule_sequential": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(SeqOpts), C.POINTER(SeqResults)]),
     "fgs_reserve": (C.c_int, [C.c_void_p, C.POINTER(PodTable), p_i32, p_i32]),
     "fgs_gang_check": (C.c_int, [C.c_void_p, C.POINTER(Snapshot), C.POINTER(Podset), C.POINTER(Podgroups), p_u8, p_u8, p_i32]),

@@ -388,6 +388,13 @@ class Engine:
         self._check(self._lib.fgs_reason_plane(self._h, plugin, _ptr(out, C.c_uint16)))
         return out
 
+    def fit_error_histogram(self):
+        """int32 [P][FGS_DIAG_SLOTS]: per pod without a feasible node, nodes per reason of its NodeToStatusMap
+        (fgs_fit_error_histogram — the numbers in FitError.Error())"""
+        out = np.zeros((max(self.n_pods, 1), L.FGS_DIAG_SLOTS), np.int32)
+        self._check(self._lib.fgs_fit_error_histogram(self._h, _ptr(out, C.c_int32)))
+        return out[:self.n_pods]
+
     def timings(self):
         t = L.Timings()
         self._check(self._lib.fgs_get_timings(self._h, C.byref(t)))

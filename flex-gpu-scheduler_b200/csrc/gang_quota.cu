@@ -479,10 +479,7 @@ __global__ void __launch_bounds__(256) status_plane(const __grid_constant__ Stat
 // WHY a plugin rejected the node — what the reference puts into the Status message (NodeToStatusMap,
 // generic_scheduler.go:309-313): FlexGPU's five messages (flex_gpu.go:60,67,73,92,97,114) as FGS_FLEX_REASON_*, and
 // Fit's list of InsufficientResource entries (fit.go:256-329: every failing dimension is reported) as a bit mask.
-__global__ void __launch_bounds__(256) reason_plane(const __grid_constant__ StatusParams prm) {
-    const i64 n = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-    const i64 p = blockIdx.y;
-    if (n >= prm.n_nodes || p >= prm.n_pods) return;
+__device__ __forceinline__ uint16_t reason_of(const StatusParams& prm, uint32_t plugin, i64 p, i64 n) {
     auto P = [&](int c) { return prm.pods[(i64)c * prm.p_pad + p]; };
     auto N = [&](int c) { return prm.nd[(i64)c * prm.n_pad + n]; };
     auto R = [&](int c) { return prm.raw[(i64)c * prm.n_pad + n]; };
@@ -490,7 +487,7 @@ __global__ void __launch_bounds__(256) reason_plane(const __grid_constant__ Stat
     const uint32_t pf = (uint32_t)meta, kind = pf & 3u;
     const uint32_t fl = (uint32_t)N(ND_FLAGS);
     uint16_t out = 0;
-    if (prm.plugin == FGS_PL_FLEXGPU) {
+    if (plugin == FGS_PL_FLEXGPU) {
         const int S = prm.S;
         if (kind == 0) out = FGS_FLEX_REASON_NONE;
         else if (kind == 3) out = FGS_FLEX_REASON_CONFLICT;
@@ -525,7 +522,55 @@ __global__ void __launch_bounds__(256) reason_plane(const __grid_constant__ Stat
             }
         }
     }
-    prm.out16[p * prm.n_nodes + n] = out;
+    return out;
+}
+
+__global__ void __launch_bounds__(256) reason_plane(const __grid_constant__ StatusParams prm) {
+    const i64 n = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const i64 p = blockIdx.y;
+    if (n >= prm.n_nodes || p >= prm.n_pods) return;
+    prm.out16[p * prm.n_nodes + n] = reason_of(prm, prm.plugin, p, n);
+}
+
+// FitError (vendor/k8s.io/kubernetes/pkg/scheduler/framework/types.go:221-250): the histogram of the reasons in the
+// NodeToStatusMap of a pod no node took — per pod, how many nodes carry each reason string. A node's status is the
+// status of the FIRST filter plugin that rejected it (RunFilterPlugins, profile order, early exit); Fit lists every
+// insufficient resource, so one node may count under several Fit reasons. One CTA per (pod, 2048 nodes), counts in
+// shared memory, one atomicAdd per non-zero slot. Pods with a feasible node are skipped: there is no FitError for them.
+__global__ void __launch_bounds__(256) fit_error_histogram(const __grid_constant__ StatusParams prm, const i64* __restrict__ feasible_count,
+                                                           int* __restrict__ counts) {
+    __shared__ int sh[FGS_DIAG_SLOTS];
+    const i64 p = blockIdx.y;
+    if (p >= prm.n_pods || feasible_count[p] > 0) return;
+    if (threadIdx.x < FGS_DIAG_SLOTS) sh[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t order[2] = {prm.flex_filter_first ? FGS_PL_FLEXGPU : FGS_PL_FIT, prm.flex_filter_first ? FGS_PL_FIT : FGS_PL_FLEXGPU};
+    for (int it = 0; it < 8; ++it) {
+        const i64 n = ((i64)blockIdx.x * 8 + it) * blockDim.x + threadIdx.x;
+        if (n >= prm.n_nodes) break;
+        if (!((uint32_t)prm.nd[(i64)ND_FLAGS * prm.n_pad + n] & FGS_NF_VALID)) {
+            atomicAdd(&sh[FGS_DIAG_NOT_A_NODE], 1);
+            continue;
+        }
+        for (int k = 0; k < 2; ++k) {
+            if (!(prm.filter_mask & order[k])) continue;
+            const uint16_t r = reason_of(prm, order[k], p, n);
+            if (!r) continue;
+            if (order[k] == FGS_PL_FLEXGPU) {
+                atomicAdd(&sh[r == FGS_FLEX_REASON_PANIC ? FGS_DIAG_FLEX_PANIC : FGS_DIAG_FLEX0 + (int)r - 1], 1);
+            } else {
+                uint32_t m = r;
+                while (m) {
+                    const int b = __ffs(m) - 1;
+                    m &= m - 1;
+                    atomicAdd(&sh[FGS_DIAG_FIT0 + b], 1);
+                }
+            }
+            break; // the first rejecting plugin's status is the node's status
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < FGS_DIAG_SLOTS && sh[threadIdx.x]) atomicAdd(&counts[p * FGS_DIAG_SLOTS + threadIdx.x], sh[threadIdx.x]);
 }
 
 } // namespace
@@ -950,5 +995,50 @@ extern "C" int fgs_quota_check_static(void* stream, int32_t n_scalars, int64_t n
         static_err(errbuf, errbuf_len, cudaGetErrorString(ce));
         return FGS_E_CUDA;
     }
+    return FGS_OK;
+}
+
+extern "C" int fgs_fit_error_histogram(fgs_engine* eh, int32_t* counts) {
+    if (!eh || !counts) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_fit_error_histogram before an evaluation");
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_fit_error_histogram while submitted batches are in flight");
+    cudaSetDevice(e->device);
+    const int64_t P = e->n_pods;
+    if (P == 0) return FGS_OK;
+    int* d = nullptr;
+    const size_t bytes = sizeof(int) * (size_t)P * FGS_DIAG_SLOTS;
+    FGS_CUDA(e, cudaMalloc(&d, bytes));
+    cudaError_t ce = cudaMemsetAsync(d, 0, bytes, e->stream);
+    EvalParams ep;
+    e->fill_eval_params(&ep, nullptr);
+    StatusParams sp;
+    std::memset(&sp, 0, sizeof(sp));
+    sp.nd = (const i64*)e->d_nd;
+    sp.raw = (const i64*)e->d_raw;
+    sp.pods = (const i64*)e->d_pods;
+    sp.n_nodes = e->n_nodes;
+    sp.n_pad = e->n_pad;
+    sp.p_pad = e->p_pad;
+    sp.S = e->S;
+    sp.D = e->D;
+    sp.filter_mask = ep.filter_mask;
+    sp.fit_ignored = ep.fit_ignored;
+    sp.flex_filter_first = ep.flex_filter_first;
+    const i64* d_count = (const i64*)e->d_perpod + (int64_t)FGS_REDUCE_ROWS * e->p_pad; // merged over the shards when there are any
+    for (int64_t p0 = 0; p0 < P && ce == cudaSuccess; p0 += 32768) { // grid.y is limited to 65535
+        StatusParams s2 = sp;
+        const int64_t cnt = std::min<int64_t>(32768, P - p0);
+        s2.pods = sp.pods + p0;
+        s2.n_pods = cnt;
+        dim3 grid((unsigned)((e->n_nodes + 2047) / 2048), (unsigned)cnt);
+        fit_error_histogram<<<grid, 256, 0, e->stream>>>(s2, d_count + p0, d + p0 * FGS_DIAG_SLOTS);
+        e->launches++;
+        ce = cudaGetLastError();
+    }
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(counts, d, bytes, cudaMemcpyDeviceToHost, e->stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->stream);
+    cudaFree(d);
+    if (ce != cudaSuccess) return e->fail(FGS_E_CUDA, std::string("fgs_fit_error_histogram: ") + cudaGetErrorString(ce));
     return FGS_OK;
 }

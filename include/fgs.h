@@ -239,6 +239,15 @@ int fgs_status_plane(fgs_engine* e, uint32_t plugin, uint8_t* out);
  *   plugin == FGS_PL_FIT      OR of FGS_FIT_REASON_* (fitsRequest reports every insufficient resource) */
 int fgs_reason_plane(fgs_engine* e, uint32_t plugin, uint16_t* out);
 
+/* FitError.Error() (sched/framework/types.go:221-250) without moving the planes to the host: for every pod of the
+ * last evaluated batch that NO node took, counts[p][FGS_DIAG_*] = how many nodes carry each reason in the pod's
+ * NodeToStatusMap — a node's status being that of the first filter plugin (profile order) that rejected it
+ * (runtime/framework.go:667-693), with every insufficient resource Fit lists counted. Rows of pods with a feasible
+ * node stay 0. counts is int32 [n_pods][FGS_DIAG_SLOTS]. The host sorts "<count> <reason>" and joins:
+ * "0/<N> nodes are available: 3 Insufficient cpu, 2 insufficient resource nvidia.flex.com/gpu." Call after the
+ * evaluation (on a sharded engine: after the merges; each shard reports its own nodes, the host adds the rows up). */
+int fgs_fit_error_histogram(fgs_engine* e, int32_t* counts);
+
 /* ---- sequential scheduling cycles: assume + Reserve between pods ---------------------------- */
 
 /* device_index values that are not an index (FlexGPU.Reserve, pkg/flexgpu/flex_gpu.go:178-223) */

@@ -296,6 +296,32 @@ class Framework {
     // selectHost (generic_scheduler.go:146-167): the node libfgs picked out of the max-score tie set
     int64_t SelectHost(const CycleState& state) const { return state.Read(kStateKey)->selected_node; }
 
+    // framework.FitError.Error() (framework/types.go:221-250) for the pod RunPreFilterPlugins evaluated last, when no node
+    // took it: "0/<N> nodes are available: <count> <reason>, … ." — the histogram over the NodeToStatusMap comes from the
+    // device (fgs_fit_error_histogram), the "<count> <reason>" strings are sorted as sort.Strings sorts them
+    std::string FitError() const {
+        int32_t c[FGS_DIAG_SLOTS] = {0};
+        h_.Check(fgs_fit_error_histogram(h_.engine(), c));
+        std::vector<std::string> parts;
+        auto add = [&](int slot, const std::string& reason) {
+            if (c[slot]) parts.push_back(std::to_string(c[slot]) + " " + reason);
+        };
+        add(FGS_DIAG_FLEX0 + FGS_FLEX_REASON_CONFLICT - 1, "pod conflict resources");                                   // flex_gpu.go:60
+        add(FGS_DIAG_FLEX0 + FGS_FLEX_REASON_UNKNOWN_RESOURCE - 1, "unknown resource type");                            // :67,73
+        add(FGS_DIAG_FLEX0 + FGS_FLEX_REASON_INSUFFICIENT_GPU - 1, "insufficient resource nvidia.flex.com/gpu");        // :92
+        add(FGS_DIAG_FLEX0 + FGS_FLEX_REASON_INSUFFICIENT_MEM - 1, "insufficient resource nvidia.flex.com/memory");     // :97
+        add(FGS_DIAG_FLEX0 + FGS_FLEX_REASON_NO_FIT_INDEX - 1, "no fit indexes resource nvidia.flex.com/memory");       // :114
+        add(FGS_DIAG_FIT0 + 0, "Too many pods");                                                                        // fit.go:259-268
+        add(FGS_DIAG_FIT0 + 1, "Insufficient cpu");
+        add(FGS_DIAG_FIT0 + 2, "Insufficient memory");
+        add(FGS_DIAG_FIT0 + 3, "Insufficient ephemeral-storage");
+        for (int s = 0; s < FGS_MAX_SCALARS; ++s) add(FGS_DIAG_FIT0 + 4 + s, "Insufficient " + h_.names.Scalar(s));
+        std::sort(parts.begin(), parts.end());
+        std::string msg = "0/" + std::to_string(h_.snapshot() ? h_.snapshot()->n_nodes : 0) + " nodes are available: ";
+        for (size_t i = 0; i < parts.size(); ++i) msg += (i ? ", " : "") + parts[i];
+        return msg + ".";
+    }
+
   private:
     Handle& h_;
     Profile profile_;

@@ -83,6 +83,13 @@ extern "C" {
 #define FGS_FIT_REASON_EPH 8u      /* "Insufficient ephemeral-storage" */
 #define FGS_FIT_REASON_SCALAR0 16u /* << s: "Insufficient <scalar resource s>" */
 
+/* fgs_fit_error_histogram: slots of the per-pod reason histogram (FitError, framework/types.go:221-250) */
+#define FGS_DIAG_FLEX0 0       /* + (FGS_FLEX_REASON_x - 1): the five FlexGPU messages */
+#define FGS_DIAG_FLEX_PANIC 5  /* nodes on which NewGPUNode panics */
+#define FGS_DIAG_FIT0 6        /* + bit index of FGS_FIT_REASON_x: Too many pods, cpu, memory, ephemeral-storage, scalar s */
+#define FGS_DIAG_NOT_A_NODE 30 /* rows that are not nodes of the list (NodeInfo without a Node) */
+#define FGS_DIAG_SLOTS 32
+
 /* fgs_select_victims: what SelectVictimsOnNode returns for a node (pkg/capacityscheduling/capacity_scheduling.go:465-644) */
 #define FGS_PREEMPT_CANDIDATE 0   /* Success with at least one victim: the node is a preemption candidate */
 #define FGS_PREEMPT_NO_VICTIMS 1  /* "No victims found on node …", UnschedulableAndUnresolvable (:560-565) */

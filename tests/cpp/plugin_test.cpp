@@ -260,6 +260,7 @@ static void TestCapacityPostFilter(Handle& h) {
     CycleState st;
     CHECK(fw.RunPreFilterPlugins(st, pods.get(), 0).IsSuccess());
     CHECK(st.Read(Framework::kStateKey)->feasible_count == 0); // nothing fits: PostFilter's turn
+    CHECK(fw.FitError() == "0/5 nodes are available: 5 Insufficient cpu."); // framework/types.go:221-250
     auto r = cs.PostFilter(pods.get(), 0, nullptr, st.Read(Framework::kStateKey).get());
     CHECK(r.second.IsSuccess());
     CHECK(r.first.Candidates == 3 && r.first.NominatedNode == 2);

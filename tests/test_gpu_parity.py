@@ -380,3 +380,68 @@ def test_submit_collect_pipeline_equals_evaluate(gpu_ok):
     again = eng.evaluate(tables[3])  # the synchronous path works again once everything is collected
     assert np.array_equal(again.selected_node, want[3].selected_node)
     eng.close()
+
+
+def _expected_fit_error_histogram(oracle, snapshot, pending, cfg, ref, n_nodes, node_valid):
+    """FitError's reason counts from the oracle's walk: per unschedulable pod, every node's status is the status of the
+    first filter plugin (profile order) that rejected it"""
+    order = [int(x) for x in cfg.filter_order if int(x)]
+    exp = np.zeros((len(ref.feasible_count), L.FGS_DIAG_SLOTS), np.int32)
+    for p in np.nonzero(ref.feasible_count == 0)[0]:
+        rf, rt = oracle.filter_reasons(snapshot, pending, cfg, int(p))
+        for n in range(n_nodes):
+            if not node_valid[n]:
+                exp[p, L.FGS_DIAG_NOT_A_NODE] += 1
+                continue
+            for pl in order:
+                if pl == L.FGS_PL_FLEXGPU and rf[n]:
+                    exp[p, L.FGS_DIAG_FLEX_PANIC if rf[n] == 0xF1 else L.FGS_DIAG_FLEX0 + int(rf[n]) - 1] += 1
+                    break
+                if pl == L.FGS_PL_FIT and rt[n]:
+                    for b in range(16):
+                        if (int(rt[n]) >> b) & 1:
+                            exp[p, L.FGS_DIAG_FIT0 + b] += 1
+                    break
+    return exp
+
+
+def test_fit_error_histogram_matches_the_oracle(gpu_ok, oracle):
+    """fgs_fit_error_histogram: the counts FitError.Error() prints (framework/types.go:221-250), per unschedulable pod"""
+    for order in (("NodeResourcesFit", "FlexGPU"), ("FlexGPU", "NodeResourcesFit")):
+        s = fgs.config_synth(2, n_nodes=300, n_pending=400, pm_panic_nodes=15, pm_nongpu_nodes=200, pm_extra_scalar=200, pm_invalid_nodes=20,
+                             n_scalars=3, max_existing_pods=60)
+        cfg = fgs.plugin_cfg(filter_plugins=order, score_plugins=(("FlexGPU", 1), ("NodeResourcesFit", 1)))
+        eng = fgs.Engine(device=0, n_scalars=3)
+        eng.set_plugins(cfg)
+        eng.upload_nodes(fgs.Packer(3).nodes(s.snapshot))
+        res = eng.evaluate(fgs.Packer(3).pods(s.pending))
+        got = eng.fit_error_histogram()
+        ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=4)
+        assert np.array_equal(res.feasible_count, ref.feasible_count)
+        valid = np.ctypeslib.as_array(s.snapshot.contents.node_valid, shape=(s.n_nodes,))
+        exp = _expected_fit_error_histogram(oracle, s.snapshot, s.pending, cfg, ref, s.n_nodes, valid)
+        assert int((ref.feasible_count == 0).sum()) >= 10
+        assert np.array_equal(got, exp), np.nonzero((got != exp).any(axis=1))[0][:5]
+        used = set(np.nonzero(exp.sum(axis=0))[0].tolist())
+        assert {L.FGS_DIAG_FLEX0, L.FGS_DIAG_NOT_A_NODE} <= used and len(used) >= 5, used
+        eng.close()
+    # by hand: 3 nodes, nothing fits. Fit first: node 0 lacks cpu AND memory (both are listed), node 1 cpu, node 2 has
+    # no flex resources but Fit already said no for its pod count
+    GiB = 1 << 30
+    nodes = [B.node({"cpu": 1000, "memory": GiB, "pods": 110, ("scalar", 0): 8, ("scalar", 1): 64 * GiB}),
+             B.node({"cpu": 1000, "memory": 64 * GiB, "pods": 110, ("scalar", 0): 8, ("scalar", 1): 64 * GiB}),
+             B.node({"cpu": 64000, "memory": 64 * GiB, "pods": 1}, [B.pod([B.ctr({"cpu": 1})], node_name=True)])]
+    pend = [B.pod([B.ctr({"cpu": 2000, "memory": 2 * GiB}, mem_limit=GiB)]), B.pod([B.ctr({"cpu": 10})])]
+    snap, ps = B.build_snapshot(nodes), B.build_podset(pend)
+    for order, want in ((("NodeResourcesFit", "FlexGPU"), {L.FGS_DIAG_FIT0 + 1: 2, L.FGS_DIAG_FIT0 + 2: 1, L.FGS_DIAG_FIT0 + 0: 1}),
+                        (("FlexGPU", "NodeResourcesFit"), {L.FGS_DIAG_FIT0 + 1: 2, L.FGS_DIAG_FIT0 + 2: 1, L.FGS_DIAG_FLEX0 + 1: 1})):
+        cfg = fgs.plugin_cfg(filter_plugins=order, score_plugins=(("NodeResourcesFit", 1),))
+        eng = fgs.Engine(device=0)
+        eng.set_plugins(cfg)
+        eng.upload_nodes(fgs.Packer(2).nodes(snap.ptr))
+        res = eng.evaluate(fgs.Packer(2).pods(ps.ptr))
+        assert res.feasible_count.tolist() == [0, 2]
+        got = eng.fit_error_histogram()
+        assert {k: int(v) for k, v in enumerate(got[0]) if v} == want, (order, got[0])
+        assert not got[1].any()  # a pod some node took has no FitError
+        eng.close()
