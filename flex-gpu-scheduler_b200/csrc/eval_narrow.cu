@@ -65,15 +65,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
-__device__ __forceinline__ int rn_small(float x) { return __float_as_int(x + 12582912.0f) - 0x4B400000; }
-
-// floor(x / d) for 0 <= x < 2^31, 0 < d < 2^24 given a float estimate within 0.5 of x/d (quotient < 2^22):
-// k = round(est) is the quotient or one above it; the sign of the exact remainder x − k·d decides.
-__device__ __forceinline__ int qfix32(int x, int d, float est) {
-    const int k = rn_small(est);
-    const int r = (int)((uint32_t)x - (uint32_t)k * (uint32_t)d); // wraps harmlessly on don't-care lanes
-    return k + (r >> 31);
-}
+// floor(x / d) for 0 <= x < 2^31 and the divisor's magic pair (narrow_magic, kernels_narrow.cuh), given 2·x:
+// one IMAD.HI and one shift — the quotient is exact, no estimate to repair.
+__device__ __forceinline__ int qmagic(uint32_t x2, uint32_t m, int l) { return (int)(__umulhi(x2, m) >> l); }
 
 // Nodes per thread. Each pod iteration pays a fixed cost (broadcast loads of the pod record, loop and pointer
 // bookkeeping, one REDUX, one staged store); four nodes per thread spread it over 128 evaluations per warp.
@@ -347,8 +341,9 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
 // =================================================================================================
 
 struct __align__(16) PodE { // 64 bytes: four broadcast LDS.128 per pod
-    int nzc, nzm, nz100c, nz100m;
-    float fnzc, fnzm, finv, ainv;
+    int nzc, nzm, nz200c, nz200m;      // non-zero requests and 200 × them (the dividends are kept doubled, see qmagic)
+    uint32_t fmag, amag;               // magic multipliers of the pod's two divisors: flex max, Allocatable range
+    int fsh, ash;                      // … and their shifts
     int fmax, count, arange32, kind; // arange32 < 0: exact 64-bit path for Allocatable
     uint32_t hmul; // per-pod hash (cross-tile tie mixing in the flush)
     int hpos;      // 8 of its bits at positions 10..17: XORed with the node's bits in the key
@@ -425,26 +420,25 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         u.kind = raw[0 * kTileP + tid];
         u.nzc = raw[1 * kTileP + tid];
         u.nzm = raw[2 * kTileP + tid];
-        u.nz100c = (int)(100u * (uint32_t)u.nzc);
-        u.nz100m = (int)(100u * (uint32_t)u.nzm);
-        u.fnzc = (float)u.nzc;
-        u.fnzm = (float)u.nzm;
+        u.nz200c = (int)(200u * (uint32_t)u.nzc);
+        u.nz200m = (int)(200u * (uint32_t)u.nzm);
         i64 fmx = raw64[0 * kTileP + tid];
         if (fmx < 0) fmx = 0; // maxCount starts at 0 (normalize_score.go:27)
         if (u.kind == 2) fmx >>= prm.sh.s[DIM_FM];
         u.fmax = (int)fmx;
-        u.finv = fmx > 0 ? (float)(1.0 / (double)fmx) : 0.f;
+        u.fmag = narrow_magic((uint32_t)u.fmax, &u.fsh);
         u.count = (int)raw64[3 * kTileP + tid];
         u.alo = 0;
         u.arange32 = 0;
-        u.ainv = 0.f;
+        u.amag = 0;
+        u.ash = 0;
         if (kAlloc && u.count > 0) {
             const i64 hi = raw64[1 * kTileP + tid], lo = -raw64[2 * kTileP + tid];
             const i64 range = (i64)((u64)hi - (u64)lo);
             u.alo = lo;
             if (range >= 0 && range < (1 << 24)) {
                 u.arange32 = (int)range;
-                u.ainv = range > 0 ? (float)(100.0 / (double)range) : 0.f;
+                u.amag = narrow_magic((uint32_t)range, &u.ash);
             } else {
                 u.arange32 = -1;
             }
@@ -469,8 +463,8 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     if (n_tiles > 1) issue_bitmap(1);
 
     // node tile → registers
-    int capc[kNPTe], xc[kNPTe], x100c[kNPTe], capm[kNPTe], xm[kNPTe], x100m[kNPTe], g100[kNPTe], m100[kNPTe], nloc[kNPTe], inr[kNPTe], mneg[kNPTe];
-    float invc[kNPTe], xqc[kNPTe], invm[kNPTe], xqm[kNPTe], g100f[kNPTe], m100f[kNPTe];
+    int capc[kNPTe], xc[kNPTe], capm[kNPTe], xm[kNPTe], nloc[kNPTe], inr[kNPTe], mneg[kNPTe], shc[kNPTe], shm[kNPTe];
+    uint32_t x200c[kNPTe], x200m[kNPTe], g200[kNPTe], m200[kNPTe], magc[kNPTe], magm[kNPTe];
     uint32_t nbase[kNPTe], nh[kNPTe];
     i64 araw[kNPTe];
 #pragma unroll
@@ -486,23 +480,22 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
             xc[j] = C(NN_X_C);
             capm[j] = C(NN_CAP_M);
             xm[j] = C(NN_X_M);
-            x100c[j] = 100 * xc[j];
-            x100m[j] = 100 * xm[j];
-            invc[j] = __int_as_float(C(NN_INV_C));
-            xqc[j] = __int_as_float(C(NN_XQ_C));
-            invm[j] = __int_as_float(C(NN_INV_M));
-            xqm[j] = __int_as_float(C(NN_XQ_M));
+            x200c[j] = 200u * (uint32_t)xc[j];
+            x200m[j] = 200u * (uint32_t)xm[j];
+            magc[j] = (uint32_t)C(NN_MAG_C);
+            magm[j] = (uint32_t)C(NN_MAG_M);
+            const int shs = C(NN_MAG_SH);
+            shc[j] = shs & 0xff;
+            shm[j] = (shs >> 8) & 0xff;
         }
         if (kFlex) {
             // a negative MemScore (over-committed device) is kept as magnitude + sign: Go's '/' truncates toward
             // zero, so 100 − (100·s)/max = 100 + floor(100·|s|/max). Whether that leaves [0,100] and aborts the
             // cycle is decided per pod by special_pass / finalize_pods, not here.
             const int ms = C(NN_MSCORE);
-            g100[j] = 100 * C(NN_GSCORE);
-            m100[j] = 100 * (ms < 0 ? -ms : ms);
+            g200[j] = 200u * (uint32_t)C(NN_GSCORE);
+            m200[j] = 200u * (uint32_t)(ms < 0 ? -ms : ms);
             mneg[j] = ms < 0 ? 1 : 0;
-            g100f[j] = __int_as_float(C(NN_GS100F));
-            m100f[j] = fabsf(__int_as_float(C(NN_MS100F)));
         }
         araw[j] = kAlloc ? __ldg((const i64*)prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n) : 0;
     }
@@ -529,8 +522,8 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
 
         i64* rowp = (i64*)prm.scores + tile_p0 * prm.score_stride + node_tile0 + nloc[0];
         for (int jp = 0; jp < n_valid; ++jp, rowp += prm.score_stride) {
-            const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz100c nz100m
-            const float4 q3 = *(const float4*)&s_pod[jp].fnzc; // fnzc fnzm finv ainv
+            const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz200c nz200m
+            const uint4 q3 = *(const uint4*)&s_pod[jp].fmag;   // fmag amag fsh ash
             const int4 q4 = *(const int4*)&s_pod[jp].fmax;     // fmax count arange32 kind
             const uint4 fw = *(const uint4*)(bmrow + jp * kWordsTe);
             const bool feas[kNPTe] = {(fw.x & lanebit) != 0, (fw.y & lanebit) != 0, (fw.z & lanebit) != 0, (fw.w & lanebit) != 0};
@@ -549,9 +542,9 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                     if (kFlex) { // FlexGPU.Score + DefaultNormalizeScore(reverse) (flex_gpu.go:142-176, normalize_score.go:26-54)
                         int v = 100;
                         if (KS == 1) {
-                            v = 100 - qfix32(g100[j], q4.x, g100f[j] * q3.z);
+                            v = 100 - qmagic(g200[j], q3.x, (int)q3.z);
                         } else if (KS == 2) { // magnitude and sign: Go's '/' truncates toward zero
-                            const int q = qfix32(m100[j], q4.x, m100f[j] * q3.z);
+                            const int q = qmagic(m200[j], q3.x, (int)q3.z);
                             v = mneg[j] ? 100 + q : 100 - q;
                         }
                         t += v * prm.w_flex;
@@ -559,13 +552,13 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                     if (kFit) { // Least/MostAllocated over cpu and memory, non-zero requests (least_allocated.go:29-57, most_allocated.go:29-61)
                         int sc, sm;
                         if (!kMost) {
-                            sc = qfix32(x100c[j] - q2.z, capc[j], fmaf(-q3.x, invc[j], xqc[j]));
-                            sm = qfix32(x100m[j] - q2.w, capm[j], fmaf(-q3.y, invm[j], xqm[j]));
+                            sc = qmagic(x200c[j] - (uint32_t)q2.z, magc[j], shc[j]);
+                            sm = qmagic(x200m[j] - (uint32_t)q2.w, magm[j], shm[j]);
                             sc = q2.x > xc[j] ? 0 : sc; // requested > capacity → 0
                             sm = q2.y > xm[j] ? 0 : sm;
                         } else {
-                            sc = qfix32(x100c[j] + q2.z, capc[j], fmaf(q3.x, invc[j], xqc[j]));
-                            sm = qfix32(x100m[j] + q2.w, capm[j], fmaf(q3.y, invm[j], xqm[j]));
+                            sc = qmagic(x200c[j] + (uint32_t)q2.z, magc[j], shc[j]);
+                            sm = qmagic(x200m[j] + (uint32_t)q2.w, magm[j], shm[j]);
                             sc = q2.x > capc[j] - xc[j] ? 100 : sc; // requested clamps to capacity
                             sm = q2.y > capm[j] - xm[j] ? 100 : sm;
                         }
@@ -582,7 +575,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                         int v = 0;
                         if (q4.z > 0) {
                             const int a = (int)(uint32_t)((u64)araw[j] - (u64)s_pod[jp].alo);
-                            v = qfix32((int)(100u * (uint32_t)a), q4.z, (float)a * q3.w);
+                            v = qmagic(200u * (uint32_t)a, q3.y, (int)q3.w);
                         } else if (q4.z < 0) {
                             const i64 alo = s_pod[jp].alo;
                             const i64 range = (i64)((u64)__ldg((const i64*)prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + tile_p0 + jp) - (u64)alo);

@@ -218,12 +218,10 @@ __global__ void __launch_bounds__(256) narrow_nodes(const i64* __restrict__ nd, 
     const int gs = (int)C(ND_GPU_SCORE), ms = ms64 < 0 ? -(int)((-ms64) >> sh.s[DIM_FM]) : (int)(ms64 >> sh.s[DIM_FM]);
     W(NN_GSCORE, gs);
     W(NN_MSCORE, ms);
-    WF(NN_INV_C, capc > 0 ? (float)(100.0 / (double)capc) : 0.f);
-    WF(NN_XQ_C, capc > 0 ? (float)(100.0 * (double)xc / (double)capc) : 0.f);
-    WF(NN_INV_M, capm > 0 ? (float)(100.0 / (double)capm) : 0.f);
-    WF(NN_XQ_M, capm > 0 ? (float)(100.0 * (double)xm / (double)capm) : 0.f);
-    WF(NN_GS100F, (float)(100.0 * (double)gs));
-    WF(NN_MS100F, (float)(100.0 * (double)ms));
+    int lc = 0, lm = 0;
+    W(NN_MAG_C, (int)narrow_magic(capc > 0 ? (uint32_t)capc : 0u, &lc));
+    W(NN_MAG_M, (int)narrow_magic(capm > 0 ? (uint32_t)capm : 0u, &lm));
+    W(NN_MAG_SH, lc | (lm << 8));
 }
 
 __global__ void __launch_bounds__(256) narrow_pods(const i64* __restrict__ pods, i64 p_pad, int S, NarrowShifts sh, uint32_t fit_ignored,

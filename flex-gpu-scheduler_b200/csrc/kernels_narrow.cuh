@@ -28,10 +28,29 @@ struct NodeAnalysis {
     int n_special; // valid nodes that feed a pod's error bits: negative MemScore, or NewGPUNode panics on them
 };
 
+// Division by an invariant (Granlund–Montgomery, round-up variant) for dividends x < 2^31 and divisors 1 <= d < 2^31:
+// with l = ceil(log2 d) and m = floor(2^(31+l) / d) + 1 (m < 2^32), floor(x / d) = floor(x·m / 2^(31+l)) because
+// m·d = 2^(31+l) + e with 0 < e <= d <= 2^l and x·e < 2^(31+l). The kernels keep 2·x (< 2^32) and take
+// umulhi(2x, m) >> l: two instructions per exact quotient. d == 0 → m = 0: the quotient reads 0, as the reference's
+// "capacity == 0 → score 0" (least_allocated.go:48-50, most_allocated.go:52-54).
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline uint32_t narrow_magic(uint32_t d, int* l) {
+    if (d == 0) {
+        *l = 0;
+        return 0;
+    }
+    int lg = 0;
+    while ((1ull << lg) < (unsigned long long)d) ++lg;
+    *l = lg;
+    return (uint32_t)((1ull << (31 + lg)) / d + 1ull);
+}
+
 enum NarrowNodeCol : int {
     NN_THR_GPU = 0, NN_THR_MEM, NN_FREE_CPU, NN_FREE_MEM, NN_FREE_EPH, NN_FS0, NN_FS1, NN_FLAGS,
     NN_CAP_C, NN_X_C, NN_CAP_M, NN_X_M, NN_GSCORE, NN_MSCORE,
-    NN_INV_C, NN_XQ_C, NN_INV_M, NN_XQ_M, NN_GS100F, NN_MS100F, // float bits
+    NN_MAG_C, NN_MAG_M, NN_MAG_SH, // division by the node's cpu / memory capacity: magic multipliers, shifts (cpu | mem << 8)
     NN_COLS
 };
 
