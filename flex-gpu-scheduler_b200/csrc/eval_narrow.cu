@@ -472,6 +472,8 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         nloc[j] = warp * (32 * kNPTe) + j * 32 + lane;
         nbase[j] = (1u << 18) | (uint32_t)nloc[j];
         nh[j] = (((uint32_t)nloc[j] * 0x9E3779B1u) >> 24) << 10; // the node's 8 tie-break bits, at bits 10..17
+        nh[j] |= nbase[j];                                        // … with the marker bit 18 and the node-in-tile: the pod's
+                                                                  // hash bits (10..17 only) are XORed into this word
         const i64 n = node_tile0 + nloc[j];
         inr[j] = n < prm.n_nodes ? 1 : 0;
         auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
@@ -501,6 +503,8 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     }
     // keep the tail-tile predicates in registers (the compiler would otherwise recompute the 64-bit compare per pod)
     asm volatile("" : "+r"(inr[0]), "+r"(inr[1]), "+r"(inr[2]), "+r"(inr[3]));
+    asm volatile("" : "+r"(nh[0]), "+r"(nh[1]), "+r"(nh[2]), "+r"(nh[3])); // opaque: one register per node instead of rebuilding it per pod
+
     uint32_t lanebit = 1u << lane;
     asm volatile("" : "+r"(lanebit)); // opaque: keeps the feasibility test a single LOP3 with predicate output
     if (tid < kTileP) derive(0);
@@ -587,7 +591,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                     // selectHost candidate: score+1 (14 bits) | 8 tie-break bits | node-in-tile (10 bits); 0 = none
                     // (generic_scheduler.go:146-167). nbase = 1<<18 | node-in-tile, nh = the node's 8 hash bits in place:
                     // one LOP3 and one IMAD per node
-                    const uint32_t k = (uint32_t)t * 262144u + ((nh[j] ^ ph) | nbase[j]);
+                    const uint32_t k = (uint32_t)t * 262144u + (nh[j] ^ ph);
                     key = max(key, feas[j] ? k : 0u);
                 }
 #pragma unroll
@@ -679,7 +683,7 @@ void launch_emit_spec(NarrowParams p, cudaStream_t st) {
         cudaFuncSetAttribute(emit_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
         ready = 1;
     }
-    static const int waves = env_waves("FGS_WAVES_EMIT", 3);
+    static const int waves = env_waves("FGS_WAVES_EMIT", 6);
     p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC>, sm, p, waves, kTileNe);
     const dim3 grid((unsigned)(p.n_pad / kTileNe), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
     emit_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
