@@ -293,6 +293,8 @@ def run_ours(args):
         lib = L.load()
         step_evals = n_pods * n_total  # whole job: all pods x all nodes of all shards
 
+        fused = False
+
         def one_step(ev=None):
             for t in tables:
                 if multi:  # only one batch is resident at a time: restaging is part of the step
@@ -302,13 +304,19 @@ def run_ours(args):
                     e = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
                     ev.append(e)
                     e[0].record(stream)
-                eng.pass_reduce()
+                if fused:  # one engine, nothing between Filter and Score: per-pod prepass, then ONE pass over pod x node
+                    eng.pass_fused_prepass()
+                else:
+                    eng.pass_reduce()
                 if ev is not None:
                     e[1].record(stream)
                 pending = merges_after_reduce(v)
                 if ev is not None:
                     e[2].record(stream)
-                eng.pass_emit()
+                if fused:
+                    eng.pass_fused_main()
+                else:
+                    eng.pass_emit()
                 if ev is not None:
                     e[3].record(stream)
                 merges_after_emit(v)
@@ -320,6 +328,7 @@ def run_ours(args):
         eng.stage_pods(tables[0])
         view = eng.device_view()
         eng.synchronize()
+        fused = (not args.two_pass) and eng.fused_eligible()
         try:
             dev_uuid = str(torch.cuda.get_device_properties(local).uuid)
         except Exception:
@@ -491,10 +500,13 @@ def run_ours(args):
         nd_cols, pd_cols = 15 + 2 * S, 8 + S
         emit_bytes = P * N * 8 + N * nd_cols * 8 + P * (pd_cols + 4) * 8
         path_bytes = P * N * (8 + 1 / 8) + 2 * (N * nd_cols * 8 + P * pd_cols * 8) + P * 10 * 8
+        if fused:  # the one pass writes the score AND the feasibility bit of every (pod,node): SURVEY.md §8d's B_alg
+            emit_bytes = int(P * N * (8 + 1 / 8)) + N * nd_cols * 8 + P * (pd_cols + 4) * 8
+            path_bytes = emit_bytes + P * pd_cols * 8
         peak, peak_src = measured_peak_gbs()
         achieved = emit_bytes / (emit_ms * 1e-3) / 1e9  # emit_ms sums the step's emit launches (one per pod batch)
         traffic = None
-        tp = os.path.join(ROOT, "profiles", "r01_emit_traffic.json")
+        tp = os.path.join(ROOT, "profiles", "r01_fused_traffic.json" if fused else "r01_emit_traffic.json")
         if os.path.exists(tp) and cfg_id == 2 and len(batches) == 1 and n_pods == base["n_pending"]:
             try:
                 traffic = json.load(open(tp)).get("dram_bytes_per_launch")
@@ -513,7 +525,7 @@ def run_ours(args):
                              "(%.1f MB) are L2-resident by design" % (P * N * 8 / 1e9, (N * nd_cols * 8 + P * pd_cols * 8) / 1e6),
                        "parity": "all nodes evaluated for every pod (percentageOfNodesToScore=100)",
                        "pod_batches": len(batches), "merge": merge_name},
-            "kernel_ms": dict({"reduce_pass": reduce_ms, "emit_pass": emit_ms},
+            "kernel_ms": dict({"flexmax_prepass": reduce_ms, "fused_pass": emit_ms} if fused else {"reduce_pass": reduce_ms, "emit_pass": emit_ms},
                               **({"merge_after_reduce": merge1_ms, "merge_after_emit": merge2_ms, "one_batch_at_a_time_ms_per_step": sync_ms_per_step,
                                   "note": "kernel_ms: measured with one batch at a time (pass, merge, pass, merge in sequence); "
                                           "ms_per_step / value: " + ("up to three batches in flight (fgs_resubmit / fgs_collect), merges overlap the other "
@@ -522,7 +534,8 @@ def run_ours(args):
             "scheduling_cycles_note": "batched: every pod against the same snapshot, no commit between pods; "
                                       "'sequential' below commits each placement before the next pod",
             "sequential": seq,
-            "roofline": {"bound": "hbm", "kernel": "emit_narrow (int32 emit pass)" if eng.timings()["emit_int32"] else "eval_kernel<EMIT> (int64 emit pass)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"bound": "hbm", "kernel": ("emit_narrow<SPEC, fused> (Filter + Score + NormalizeScore + selectHost key in one pass, int32)" if fused else
+                                                    "emit_narrow (int32 emit pass)" if eng.timings()["emit_int32"] else "eval_kernel<EMIT> (int64 emit pass)"), "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": emit_bytes // len(batches), "launches_per_step": len(batches),
                          "path_frac": (path_bytes / ((reduce_ms + emit_ms) * 1e-3) / 1e9) / peak},
@@ -562,6 +575,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sequential", action="store_true")
+    ap.add_argument("--two-pass", action="store_true", help="N = 1: reduce pass + emit pass even where Filter and Score can run in one pass")
     ap.add_argument("--merge", default="auto", choices=["auto", "peer", "nccl"],
                     help="N > 1: cross-shard merges through the engine's peer-memory kernels (auto: NVSwitch multicast if there is one; "
                          "peer: plain peer pointers) or through NCCL all-reduces")

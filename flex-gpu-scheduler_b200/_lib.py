@@ -133,7 +133,7 @@ class PeerGroup(C.Structure):
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("reduce_ms", C.c_float), ("emit_ms", C.c_float), ("d2h_ms", C.c_float),
                 ("kernel_launches", C.c_int64), ("reduce_int32", C.c_int32), ("emit_int32", C.c_int32),
-                ("seq_ms", C.c_float), ("seq_ctas", C.c_int32)]
+                ("seq_ms", C.c_float), ("seq_ctas", C.c_int32), ("fused", C.c_int32), ("_pad", C.c_int32)]
 
 
 class SeqOpts(C.Structure):
@@ -183,6 +183,10 @@ ABI = {
     "fgs_resubmit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
     "fgs_stage_pods": (C.c_int, [C.c_void_p, C.POINTER(PodTable)]),
     "fgs_pass_reduce": (C.c_int, [C.c_void_p]),
+    "fgs_fused_eligible": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
+    "fgs_pass_fused": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
+    "fgs_pass_fused_prepass": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
+    "fgs_pass_fused_main": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
     "fgs_pass_emit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
     "fgs_fetch_results": (C.c_int, [C.c_void_p, C.POINTER(Results)]),
     "fgs_get_device_view": (C.c_int, [C.c_void_p, C.POINTER(DeviceView)]),

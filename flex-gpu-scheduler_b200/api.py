@@ -331,6 +331,23 @@ class Engine:
     def pass_reduce(self):
         self._check(self._lib.fgs_pass_reduce(self._h))
 
+    def fused_eligible(self, **opts):
+        o = self._opts(**opts)
+        return bool(self._lib.fgs_fused_eligible(self._h, C.byref(o)))
+
+    def pass_fused(self, **opts):
+        """Filter and Score in one pass over pod × node (fgs_pass_fused) instead of pass_reduce + pass_emit"""
+        o = self._opts(**opts)
+        self._check(self._lib.fgs_pass_fused(self._h, C.byref(o)))
+
+    def pass_fused_prepass(self, **opts):
+        o = self._opts(**opts)
+        self._check(self._lib.fgs_pass_fused_prepass(self._h, C.byref(o)))
+
+    def pass_fused_main(self, **opts):
+        o = self._opts(**opts)
+        self._check(self._lib.fgs_pass_fused_main(self._h, C.byref(o)))
+
     def pass_emit(self, **opts):
         o = self._opts(**opts)
         self._check(self._lib.fgs_pass_emit(self._h, C.byref(o)))
@@ -399,7 +416,8 @@ class Engine:
         t = L.Timings()
         self._check(self._lib.fgs_get_timings(self._h, C.byref(t)))
         return dict(h2d_ms=t.h2d_ms, reduce_ms=t.reduce_ms, emit_ms=t.emit_ms, d2h_ms=t.d2h_ms, kernel_launches=t.kernel_launches,
-                    reduce_int32=bool(t.reduce_int32), emit_int32=bool(t.emit_int32), seq_ms=t.seq_ms, seq_ctas=int(t.seq_ctas))
+                    reduce_int32=bool(t.reduce_int32), emit_int32=bool(t.emit_int32), seq_ms=t.seq_ms, seq_ctas=int(t.seq_ctas),
+                    fused=bool(t.fused))
 
     # -- sequential cycles: assume + Reserve between pods -------------------------------------------------
     def schedule_sequential(self, pod_table, reserve_flex=True, quotas=None):

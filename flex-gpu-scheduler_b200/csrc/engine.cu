@@ -102,6 +102,8 @@ void Engine::free_all() {
     if (d_pn) cudaFree(d_pn);
     if (d_an) cudaFree(d_an);
     if (d_special) cudaFree(d_special);
+    if (d_order) cudaFree(d_order);
+    if (d_order_scratch) cudaFree(d_order_scratch);
     if (d_walk) cudaFree(d_walk);
     if (h_walk) cudaFreeHost(h_walk);
     if (d_nom) cudaFree(d_nom);
@@ -284,6 +286,10 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
     {
         const char* fw = getenv("FGS_FORCE_INT64");
         e->force_wide = fw && fw[0] == '1';
+        // the fused pass is opt-in: on C2 it is slower than the two passes (1.19 vs 1.10 ms per step: 109 registers per
+        // thread leave two CTAs per SM, and the loop does not hide its latencies with 16 warps) — DESIGN.md §3
+        const char* nf = getenv("FGS_FUSED");
+        e->no_fused = !(nf && nf[0] == '1');
         const char* ht = getenv("FGS_HOST_THREADS");
         int nth = ht ? atoi(ht) : 4;
         const int hw = (int)std::thread::hardware_concurrency();
@@ -364,6 +370,8 @@ extern "C" int fgs_set_plugins(fgs_engine* eh, const fgs_plugin_cfg* c) {
 // by 100, 2^30 where it is only compared). Anything else runs on the int64 kernels.
 static int tz64(uint64_t v) { return v ? __builtin_ctzll(v) : 62; }
 
+static uint32_t narrow_spec(const Engine* e);
+
 int Engine::decide_narrow(const fgs_pod_table* t) {
     narrow_batch = false;
     if (force_wide || !node_an_valid || S < 2) return FGS_OK;
@@ -422,6 +430,7 @@ int Engine::decide_narrow(const fgs_pod_table* t) {
         launches++;
         narrow_nodes_sig = sig;
         narrow_sh = sh;
+        orders_valid = false; // the fused pass's node orders follow the narrow node table
     }
     launch_narrow_pods((const int64_t*)d_pods, p_pad, S, sh, cfg.fit_ignored_scalar_mask, (int*)d_pn, stream);
     launches++;
@@ -467,6 +476,76 @@ static uint32_t narrow_spec(const Engine* e) {
     return narrow_spec_bits(e->cfg.filter_mask & FGS_PL_FLEXGPU, e->cfg.filter_mask & FGS_PL_FIT, e->cfg.score_mask & FGS_PL_FLEXGPU,
                             e->cfg.score_mask & FGS_PL_FIT, e->cfg.fit_strategy == 1, e->cfg.score_mask & FGS_PL_ALLOCATABLE,
                             ep.fit_w_cpu == ep.fit_w_mem);
+}
+
+// ---- the fused pass -----------------------------------------------------------------------------------------------
+// One pass over pod × node instead of two when nothing has to happen between Filter and Score: a single engine holding
+// the whole cluster (no cross-shard merge), no node sampling, no nominated pods, default outputs, and no
+// NodeResourcesAllocatable among the score plugins (its normaliser needs the feasible set first).
+bool Engine::fused_eligible(const fgs_eval_opts* opts) const {
+    if (no_fused || !narrow_batch || peer || nom_q > 0 || n_pods <= 0) return false;
+    if (node_base != 0 || (total_nodes != 0 && total_nodes != n_nodes)) return false;
+    if (opts && (opts->sample || opts->skip_pass_b || opts->emit_raw || (opts->emit_mask != 0 && opts->emit_mask != cfg.score_mask))) return false;
+    if (cfg.score_mask & FGS_PL_ALLOCATABLE) return false;
+    EvalParams ep;
+    fill_eval_params(&ep, opts);
+    if (ep.key_shift != 40) return false;
+    return narrow_fused_available(narrow_spec(this));
+}
+
+int Engine::run_fused(const fgs_eval_opts* opts, int part) { // part: 1 = prepass, 2 = the pass itself, 3 = both
+    cudaSetDevice(device);
+    sampled = false;
+    if (part == 2 && !fused_prepass_done) return fail(FGS_E_STATE, "fgs_pass_fused_main before fgs_pass_fused_prepass");
+    if (!orders_valid) {
+        if (n_pad > order_cap) {
+            if (d_order) cudaFree(d_order);
+            if (d_order_scratch) cudaFree(d_order_scratch);
+            d_order = d_order_scratch = nullptr;
+            order_scratch_bytes = narrow_orders_scratch_bytes(n_pad);
+            FGS_CUDA(this, cudaMalloc(&d_order, sizeof(int) * 2 * (size_t)n_pad));
+            FGS_CUDA(this, cudaMalloc(&d_order_scratch, order_scratch_bytes));
+            order_cap = n_pad;
+        }
+        launch_narrow_orders((const int*)d_nn, n_nodes, n_pad, (int*)d_order, d_order_scratch, order_scratch_bytes, stream);
+        launches += 3;
+        FGS_CUDA(this, cudaGetLastError());
+        orders_valid = true;
+    }
+    EvalParams ep;
+    fill_eval_params(&ep, opts);
+    last_key_shift = ep.key_shift;
+    if (part & 1) {
+        launch_init_perpod((int64_t*)d_perpod, p_pad, stream);
+        launches++;
+    }
+    NarrowParams np;
+    fill_narrow_params(&np);
+    if (!launch_fused_narrow(np, narrow_spec(this), (const int*)d_order, (const int*)d_order + n_pad, stream, events[2], part))
+        return fail(FGS_E_STATE, "fused pass: no instantiation for this plugin set");
+    if ((part & 1) && (cfg.score_mask & FGS_PL_FLEXGPU)) launches++;
+    if (part & 2) launches++;
+    fused_prepass_done = part == 1;
+    if (part == 1) {
+        FGS_CUDA(this, cudaGetLastError());
+        return FGS_OK;
+    }
+    if ((cfg.filter_mask & FGS_PL_FLEXGPU) && node_an_valid && node_an.n_special > 0) {
+        launch_filter_panic_pass((const int*)d_nn, (const int*)d_pn, (const int64_t*)d_special, n_pad, node_an.n_special, n_pods, p_pad,
+                                 (cfg.filter_mask & FGS_PL_FIT) ? 1 : 0, ep.flex_filter_first, (int64_t*)d_perpod, stream);
+        launches++;
+    }
+    if ((cfg.score_mask & FGS_PL_FLEXGPU) && node_an_valid && node_an.n_special > 0) { // reads the bitmap the pass has just written
+        launch_special_pass((const uint32_t*)d_bitmap, words_per_row, (const int64_t*)d_special, n_pad, node_an.n_special,
+                            (const int64_t*)d_pods, (int64_t*)d_perpod, n_pods, p_pad, stream);
+        launches++;
+    }
+    FGS_CUDA(this, cudaGetLastError());
+    FGS_CUDA(this, cudaEventRecord(events[3], stream));
+    reduce_was_narrow = emit_was_narrow = true;
+    emitted = true;
+    was_fused = true;
+    return FGS_OK;
 }
 
 void Engine::fill_derive_params(DeriveParams* dp) const {
@@ -733,6 +812,7 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_reduce before fgs_stage_pods");
     cudaSetDevice(e->device);
     e->sampled = false;
+    e->was_fused = false;
     EvalParams p;
     e->fill_eval_params(&p, nullptr);
     launch_init_perpod((int64_t*)e->d_perpod, e->p_pad, e->stream);
@@ -746,6 +826,11 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     if (!done) launch_eval_reduce(p, e->stream);
     e->reduce_was_narrow = done;
     e->launches++;
+    if (done && (e->cfg.filter_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) { // the narrow loop leaves this flag to a side pass
+        launch_filter_panic_pass((const int*)e->d_nn, (const int*)e->d_pn, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special, e->n_pods, e->p_pad,
+                                 (e->cfg.filter_mask & FGS_PL_FIT) ? 1 : 0, p.flex_filter_first, (int64_t*)e->d_perpod, e->stream);
+        e->launches++;
+    }
     if ((e->cfg.score_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
         launch_special_pass((const uint32_t*)e->d_bitmap, e->words_per_row, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special,
                             (const int64_t*)e->d_pods, (int64_t*)e->d_perpod, e->n_pods, e->p_pad, e->stream);
@@ -758,6 +843,36 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     }
     FGS_CUDA(e, cudaEventRecord(e->events[2], e->stream));
     return FGS_OK;
+}
+
+extern "C" int fgs_fused_eligible(fgs_engine* eh, const fgs_eval_opts* opts) {
+    if (!eh) return 0;
+    Engine* e = (Engine*)eh;
+    return e->have_pods && e->fused_eligible(opts) ? 1 : 0;
+}
+
+extern "C" int fgs_pass_fused(fgs_engine* eh, const fgs_eval_opts* opts) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_fused before fgs_stage_pods");
+    if (!e->fused_eligible(opts)) return e->fail(FGS_E_STATE, "fgs_pass_fused: this batch / configuration needs the two passes (see fgs_fused_eligible)");
+    return e->run_fused(opts, 3);
+}
+
+extern "C" int fgs_pass_fused_prepass(fgs_engine* eh, const fgs_eval_opts* opts) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_fused_prepass before fgs_stage_pods");
+    if (!e->fused_eligible(opts)) return e->fail(FGS_E_STATE, "fgs_pass_fused_prepass: this batch / configuration needs the two passes (see fgs_fused_eligible)");
+    return e->run_fused(opts, 1);
+}
+
+extern "C" int fgs_pass_fused_main(fgs_engine* eh, const fgs_eval_opts* opts) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_fused_main before fgs_stage_pods");
+    if (!e->fused_eligible(opts)) return e->fail(FGS_E_STATE, "fgs_pass_fused_main: this batch / configuration needs the two passes (see fgs_fused_eligible)");
+    return e->run_fused(opts, 2);
 }
 
 extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
@@ -845,6 +960,12 @@ extern "C" int fgs_evaluate(fgs_engine* eh, const fgs_pod_table* pods, const fgs
     if (rc) return rc;
     e->emitted = false;
     if (e->peer && opts && opts->sample) return e->fail(FGS_E_INVALID, "fgs_evaluate: node sampling walks ONE node list (single engine only)");
+    e->was_fused = false;
+    if (e->fused_eligible(opts)) { // Filter and Score in one pass over pod × node
+        rc = e->run_fused(opts, 3);
+        if (rc) return rc;
+        return fgs_fetch_results(eh, out);
+    }
     rc = fgs_pass_reduce(eh);
     if (rc) return rc;
     if (e->peer) { // node-sharded engine: the other shards' maxima and counts
@@ -896,6 +1017,7 @@ extern "C" int fgs_get_timings(fgs_engine* eh, fgs_timings* t) {
     t->kernel_launches = e->launches;
     t->reduce_int32 = e->reduce_was_narrow ? 1 : 0;
     t->emit_int32 = e->emit_was_narrow ? 1 : 0;
+    t->fused = e->was_fused ? 1 : 0;
     return FGS_OK;
 }
 
@@ -1071,10 +1193,16 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
     int rc = stage_pods_impl(e, pods, true);
     if (rc) return rc;
     e->emitted = false;
-    rc = fgs_pass_reduce(eh);
-    if (rc) return rc;
-    rc = fgs_pass_emit(eh, opts);
-    if (rc) return rc;
+    e->was_fused = false;
+    if (e->fused_eligible(opts)) {
+        rc = e->run_fused(opts, 3);
+        if (rc) return rc;
+    } else {
+        rc = fgs_pass_reduce(eh);
+        if (rc) return rc;
+        rc = fgs_pass_emit(eh, opts);
+        if (rc) return rc;
+    }
     const int64_t P = e->n_pods, pp = e->p_pad;
     int64_t* d_compact = (int64_t*)e->d_perpod + (int64_t)kCompactRow0 * pp;
     launch_finalize_pods((const int64_t*)e->d_perpod, d_compact, P, pp, e->last_key_shift, 1, (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0, e->stream);

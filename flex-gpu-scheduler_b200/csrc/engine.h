@@ -67,6 +67,18 @@ struct Engine {
     int64_t nn_cap = 0, pn_cap = 0;
     int decide_narrow(const fgs_pod_table* t);
     void fill_narrow_params(NarrowParams* p) const;
+    // the fused pass (eval_narrow.cu: filters + scores in ONE pass over pod × node, after a per-pod prepass for the
+    // FlexGPU maximum): node orders by GPUScore / MemScore, rebuilt whenever the narrow node table is
+    void* d_order = nullptr;          // int [2][n_pad]
+    void* d_order_scratch = nullptr;
+    size_t order_scratch_bytes = 0;
+    int64_t order_cap = 0;
+    bool orders_valid = false;
+    bool no_fused = true;             // FGS_FUSED=1 turns the fused pass on (opt-in: slower than the two passes on C2)
+    bool was_fused = false;           // the last evaluation took the fused pass
+    bool fused_eligible(const fgs_eval_opts* opts) const;
+    bool fused_prepass_done = false;
+    int run_fused(const fgs_eval_opts* opts, int part); // init + prepass (1), fused kernel + special pass (2): what pass_reduce + pass_emit do
 
     // fgs_submit / fgs_collect: two batches in flight. A slot owns the per-batch buffers; the engine's members
     // above (d_pods, h_pods, d_perpod, h_perpod, d_pn, …) always alias the slot being filled.
@@ -124,7 +136,7 @@ struct Engine {
     SeqState* seq = nullptr;
     struct PeerState* peer = nullptr; // peer_merge.cu: the other shards' exchange buffers
 
-    fgs_timings tm = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    fgs_timings tm = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     int64_t launches = 0;
 
     int fail(int code, const std::string& msg);

@@ -30,6 +30,7 @@ typedef unsigned long long u64;
 constexpr i64 kI64Min = (i64)0x8000000000000000ull;
 constexpr int kNone = (int)0x80000000; // node side: below every pod value, sentinels included; also 'no feasible node'
 constexpr int kNever = 0x7fffffff;
+constexpr int kPass = (int)0x80000001; // pod side: "no limit / no request" — below every real node value, above kNone
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -205,10 +206,16 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
         araw[j] = kAlloc ? __ldg((const i64*)prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n) : 0;
         // node-only verdicts folded into the compares (every pod value, sentinels included, is > kNone):
         // a row that is not a node fails FlexGPU's side, "too many pods" (fit.go:259) fails Fit's side
+        // a node on which NewGPUNode would panic (flex_gpu.go:101) takes no pod that carries a flex limit — their limits
+        // are >= 0 — but every pod without one (kPass): the threshold kPass says exactly that. WHICH pods reach the panic
+        // (pod_err) is found outside the loop, over the few such nodes (filter_panic_pass).
+        if ((SPEC & SP_FLEX_F) && (fl & FGS_NF_REF_PANIC)) thr_g[j] = thr_m[j] = kPass;
         if (!(fl & FGS_NF_VALID)) thr_g[j] = thr_m[j] = kNone;
         if ((SPEC & SP_FIT_F) && !(fl & NDF_PODS_OK)) fc[j] = kNone;
     }
-    const bool tile_has_panic = (SPEC & SP_FLEX_F) && __syncthreads_or((flags_or & FGS_NF_REF_PANIC) != 0);
+    (void)flags_or;
+    (void)node_panic;
+    const bool tile_has_panic = false;
     if (tid < kTileP) derive(0);
     __syncthreads();
     if (tid == 0 && n_tiles > 2) {
@@ -353,29 +360,35 @@ struct __align__(16) PodE { // 64 bytes: four broadcast LDS.128 per pod
 struct SmemE {
     int bars, raw, pod, wkey, bm, total, raw_stage_bytes;
 };
-__host__ __device__ inline SmemE smem_emit() {
+// fused: the pass also runs the filters (one pass over pod × node instead of two). Its tiles carry the pod's filter
+// columns too, and the 'bm' area holds the per-warp feasible counts instead of staged bitmap rows.
+__host__ __device__ inline SmemE smem_emit(bool fused) {
     SmemE L;
     int off = 0;
     L.bars = off;
     off += 64;
     L.raw = off;
     L.raw_stage_bytes = 3 * kTileP * 4 + 4 * kTileP * 8; // kind, nzc, nzm + flex max, alloc hi, alloc −lo, count
+    if (fused) L.raw_stage_bytes += 7 * kTileP * 4;     // + limits and requests (PN_LIM_G … PN_RS1)
     off += 2 * L.raw_stage_bytes;
     L.pod = off;
-    off += 2 * kTileP * (int)sizeof(PodE);
+    off += 2 * kTileP * (int)(sizeof(PodE) + (fused ? sizeof(PodR) : 0));
     L.wkey = off;
     off += 2 * kTileP * kWarps * 4;
     L.bm = off; // uint32 [2][kTileP][kWordsTe]: the feasibility words of this node tile, two pod tiles deep
-    off += 2 * kTileP * kWordsTe * 4;
+                // (fused: uint32 [2][kTileP][kWarps] feasible nodes per warp, bit 31 = "NewGPUNode would panic")
+    off += 2 * kTileP * (fused ? kWarps : kWordsTe) * 4;
     L.total = off;
     return L;
 }
 
-template <uint32_t SPEC>
+template <uint32_t SPEC, bool FUSED>
 __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant__ NarrowParams prm) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr bool kFlex = SPEC & SP_SC_FLEX, kFit = SPEC & SP_SC_FIT, kAlloc = SPEC & SP_SC_ALLOC, kMost = SPEC & SP_FIT_MOST;
-    const SmemE L = smem_emit();
+    static_assert(!(FUSED && kAlloc), "the fused pass has no Allocatable hi/lo (they would need the feasible set first)");
+    const SmemE L = smem_emit(FUSED);
+    PodR* const s_podf_base = (PodR*)(smem + L.pod + 2 * kTileP * (int)sizeof(PodE)); // fused: the pods' filter records
     uint64_t* bars = (uint64_t*)(smem + L.bars); // [0,1] pod columns, [2,3] bitmap rows
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -400,6 +413,10 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         bulk_g2s(d2 + 1 * kTileP, prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + p0, kTileP * 8, &bars[stage]);
         bulk_g2s(d2 + 2 * kTileP, prm.reduce_max + (i64)RR_ALLOC_NEGLO * prm.p_pad + p0, kTileP * 8, &bars[stage]);
         bulk_g2s(d2 + 3 * kTileP, prm.reduce_sum + p0, kTileP * 8, &bars[stage]);
+        if (FUSED) {
+            int* d3 = (int*)(d2 + 4 * kTileP);
+            for (int c = 0; c < 7; ++c) bulk_g2s(d3 + c * kTileP, prm.pn + (i64)(PN_LIM_G + c) * prm.p_pad + p0, kTileP * 4, &bars[stage]);
+        }
     };
     // threads 0..63 fetch one 128-byte bitmap row each (rows are words_per_row apart in global memory)
     auto issue_bitmap = [&](int it) {
@@ -449,9 +466,23 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         u.hmul = h | 1u;
         u.hpos = (int)(((h >> 20) & 0xffu) << 10);
         ((PodE*)(smem + L.pod))[stage * kTileP + tid] = u;
+        if (FUSED) {
+            const int* f = (const int*)(raw64 + 4 * kTileP);
+            PodR r;
+            r.lim_g = f[0 * kTileP + tid];
+            r.lim_m = f[1 * kTileP + tid];
+            r.rc = f[2 * kTileP + tid];
+            r.rm = f[3 * kTileP + tid];
+            r.re = f[4 * kTileP + tid];
+            r.rs0 = f[5 * kTileP + tid];
+            r.rs1 = f[6 * kTileP + tid];
+            r.kind = u.kind;
+            s_podf_base[stage * kTileP + tid] = r;
+        }
     };
     if (tid == 0) {
         for (int b = 0; b < 4; ++b) mbar_init(&bars[b], 1);
+        static_assert(PN_LIM_G + 6 == PN_RS1, "the fused pass copies seven consecutive pod columns");
         fence_mbar_init();
     }
     __syncthreads();
@@ -459,17 +490,41 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         issue_pods(0);
         if (n_tiles > 1) issue_pods(1);
     }
-    issue_bitmap(0);
-    if (n_tiles > 1) issue_bitmap(1);
+    if (!FUSED) {
+        issue_bitmap(0);
+        if (n_tiles > 1) issue_bitmap(1);
+    }
 
     // node tile → registers
     int capc[kNPTe], xc[kNPTe], capm[kNPTe], xm[kNPTe], nloc[kNPTe], inr[kNPTe], mneg[kNPTe], shc[kNPTe], shm[kNPTe];
     uint32_t x200c[kNPTe], x200m[kNPTe], g200[kNPTe], m200[kNPTe], magc[kNPTe], magm[kNPTe];
     uint32_t nbase[kNPTe], nh[kNPTe];
     i64 araw[kNPTe];
+    // fused: the node side of the two filters, as in reduce_narrow (which filters run is a run-time choice here: a
+    // disabled one compares against kNever)
+    int thr_g[kNPTe], thr_m[kNPTe], fc[kNPTe], fm[kNPTe], fe[kNPTe], fs0[kNPTe], fs1[kNPTe], node_panic[kNPTe];
+    uint32_t flags_or = 0;
 #pragma unroll
     for (int j = 0; j < kNPTe; ++j) {
         nloc[j] = warp * (32 * kNPTe) + j * 32 + lane;
+        if (FUSED) {
+            const i64 n = node_tile0 + nloc[j];
+            auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
+            const uint32_t fl = (uint32_t)C(NN_FLAGS);
+            const bool flex_f = prm.fused_spec & SP_FLEX_F, fit_f = prm.fused_spec & SP_FIT_F;
+            flags_or |= fl;
+            thr_g[j] = flex_f ? C(NN_THR_GPU) : kNever;
+            thr_m[j] = flex_f ? C(NN_THR_MEM) : kNever;
+            fc[j] = fit_f ? C(NN_FREE_CPU) : kNever;
+            fm[j] = fit_f ? C(NN_FREE_MEM) : kNever;
+            fe[j] = fit_f ? C(NN_FREE_EPH) : kNever;
+            fs0[j] = fit_f ? C(NN_FS0) : kNever;
+            fs1[j] = fit_f ? C(NN_FS1) : kNever;
+            node_panic[j] = (fl & FGS_NF_REF_PANIC) ? 1 : 0;
+            if (flex_f && (fl & FGS_NF_REF_PANIC)) thr_g[j] = thr_m[j] = kPass; // see reduce_narrow
+            if (!(fl & FGS_NF_VALID)) thr_g[j] = thr_m[j] = kNone; // a row that is not a node fails FlexGPU's side
+            if (fit_f && !(fl & NDF_PODS_OK)) fc[j] = kNone;       // "Too many pods" (fit.go:259) fails Fit's side
+        }
         nbase[j] = (1u << 18) | (uint32_t)nloc[j];
         nh[j] = (((uint32_t)nloc[j] * 0x9E3779B1u) >> 24) << 10; // the node's 8 tie-break bits, at bits 10..17
         nh[j] |= nbase[j];                                        // … with the marker bit 18 and the node-in-tile: the pod's
@@ -507,6 +562,9 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
 
     uint32_t lanebit = 1u << lane;
     asm volatile("" : "+r"(lanebit)); // opaque: keeps the feasibility test a single LOP3 with predicate output
+    (void)flags_or;
+    (void)node_panic;
+    constexpr bool tile_has_panic = false; // panic nodes are handled through the thresholds (see reduce_narrow)
     if (tid < kTileP) derive(0);
     __syncthreads();
     if (tid == 0 && n_tiles > 2) {
@@ -522,16 +580,59 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         const PodE* s_pod = (const PodE*)(smem + L.pod) + stage * kTileP;
         uint32_t* wkey = (uint32_t*)(smem + L.wkey) + stage * kTileP * kWarps;
         const uint32_t* bmrow = (const uint32_t*)(smem + L.bm) + stage * kTileP * kWordsTe + warp * kNPTe;
-        mbar_wait(&bars[2 + stage], (uint32_t)((it >> 1) & 1));
+        const PodR* s_podf = s_podf_base + stage * kTileP;
+        uint32_t* wcnt = (uint32_t*)(smem + L.bm) + stage * kTileP * kWarps; // fused only
+        uint32_t* bm_out = prm.bitmap + tile_p0 * prm.words_per_row + word0 + warp * kNPTe; // fused: this warp's four words
+        if (!FUSED) mbar_wait(&bars[2 + stage], (uint32_t)((it >> 1) & 1));
 
         i64* rowp = (i64*)prm.scores + tile_p0 * prm.score_stride + node_tile0 + nloc[0];
-        for (int jp = 0; jp < n_valid; ++jp, rowp += prm.score_stride) {
+        for (int jp = 0; jp < n_valid; ++jp, rowp += prm.score_stride, bm_out += prm.words_per_row) {
             const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz200c nz200m
             const uint4 q3 = *(const uint4*)&s_pod[jp].fmag;   // fmag amag fsh ash
             const int4 q4 = *(const int4*)&s_pod[jp].fmax;     // fmax count arange32 kind
-            const uint4 fw = *(const uint4*)(bmrow + jp * kWordsTe);
-            const bool feas[kNPTe] = {(fw.x & lanebit) != 0, (fw.y & lanebit) != 0, (fw.z & lanebit) != 0, (fw.w & lanebit) != 0};
             const int kind = q4.w;
+            bool feas[kNPTe] = {false, false, false, false};
+            if (!FUSED) {
+                const uint4 fw = *(const uint4*)(bmrow + jp * kWordsTe);
+                feas[0] = (fw.x & lanebit) != 0, feas[1] = (fw.y & lanebit) != 0, feas[2] = (fw.z & lanebit) != 0, feas[3] = (fw.w & lanebit) != 0;
+            }
+            // fused: the two filters, exactly as reduce_narrow runs them (flex_gpu.go:54-116, fit.go:277-326). As there, the
+            // code exists twice: tiles without a node on which NewGPUNode would panic (the normal case) carry none of the
+            // bookkeeping for it.
+            auto run_filters = [&](auto rare_tag) {
+                constexpr bool kRare = decltype(rare_tag)::value;
+                const int4 a = *(const int4*)&s_podf[jp].lim_g; // lim_g lim_m rc rm
+                const int4 b = *(const int4*)&s_podf[jp].re;    // re rs0 rs1 kind
+                bool fpanic = false;
+#pragma unroll
+                for (int j = 0; j < kNPTe; ++j) {
+                    const bool flex_ok = a.x <= thr_g[j] && a.y <= thr_m[j];
+                    const bool fit_ok = a.z <= fc[j] && a.w <= fm[j] && b.x <= fe[j] && b.y <= fs0[j] && b.z <= fs1[j];
+                    bool ok = flex_ok && fit_ok;
+                    if (kRare) { // NewGPUNode would panic inside FlexGPU.Filter (flex_gpu.go:101)
+                        const bool reach = kind != 0 && flex_ok && node_panic[j] && (prm.flex_filter_first || fit_ok);
+                        fpanic = fpanic || reach;
+                        ok = ok && !reach;
+                    }
+                    feas[j] = ok;
+                }
+                uint32_t bal[kNPTe], cnt = 0;
+#pragma unroll
+                for (int j = 0; j < kNPTe; ++j) {
+                    bal[j] = __ballot_sync(0xffffffffu, feas[j]);
+                    cnt += (uint32_t)__popc(bal[j]);
+                }
+                if (kRare && __ballot_sync(0xffffffffu, fpanic)) cnt |= 0x80000000u;
+                if (lane == 0) {
+                    static_assert(kNPTe == 4, "one 16-byte store per warp and pod");
+                    *(uint4*)bm_out = make_uint4(bal[0], bal[1], bal[2], bal[3]); // the bitmap row's words of this warp's 128 nodes
+                    wcnt[jp * kWarps + warp] = cnt;
+                }
+            };
+            if (FUSED) {
+                if (tile_has_panic) run_filters(std::true_type{});
+                else run_filters(std::false_type{});
+            }
             const uint32_t ph = (uint32_t)s_pod[jp].hpos; // the pod's 8 tie-break bits, already at bits 10..17
             // The pod kind and "max flex score == 0" are uniform over the tile: one copy of the node loop per case
             // instead of per-node selects. KS = 0: the FlexGPU term is the constant 100 (no limit, or max == 0);
@@ -607,7 +708,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         }
         if (tid < kTileP && it + 1 < n_tiles) derive(it + 1);
         __syncthreads();
-        if (it + 2 < n_tiles) { // this stage's bitmap rows are consumed: fetch the rows of tile it+2
+        if (!FUSED && it + 2 < n_tiles) { // this stage's bitmap rows are consumed: fetch the rows of tile it+2
             if (tid < kTileP) fence_proxy_async();
             issue_bitmap(it + 2);
         }
@@ -627,6 +728,17 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                 const uint32_t h16 = ((uint32_t)h8 << 8) | (((uint32_t)blockIdx.x * 0x9E3779B1u ^ s_pod[tid].hmul) >> 24);
                 const u64 key64 = ((t << 40) | ((u64)h16 << 24) | ng) + 1; // layout shared with the int64 kernels
                 atomicMax((i64*)prm.select_key + p, (i64)key64);
+            }
+            if (FUSED) { // what reduce_narrow's flush does for the count and the panic flag
+                uint32_t c = 0, pn = 0;
+#pragma unroll
+                for (int w = 0; w < kWarps; ++w) {
+                    const uint32_t x = wcnt[tid * kWarps + w];
+                    c += x & 0x7fffffffu;
+                    pn |= x >> 31;
+                }
+                if (c) atomicAdd((u64*)prm.reduce_sum + p, (u64)c);
+                if (pn) raise_flag((i64*)prm.reduce_max + (i64)RR_FILTER_PANIC * prm.p_pad, p);
             }
         }
     }
@@ -675,18 +787,60 @@ void launch_reduce_spec(NarrowParams p, cudaStream_t st) {
     const dim3 grid((unsigned)(p.n_pad / kTileNr), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
     reduce_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
 }
-template <uint32_t SPEC>
+template <uint32_t SPEC, bool FUSED>
 void launch_emit_spec(NarrowParams p, cudaStream_t st) {
-    const int sm = smem_emit().total;
+    const int sm = smem_emit(FUSED).total;
     static int ready = 0;
     if (!ready) {
-        cudaFuncSetAttribute(emit_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+        cudaFuncSetAttribute(emit_narrow<SPEC, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
         ready = 1;
     }
-    static const int waves = env_waves("FGS_WAVES_EMIT", 6);
-    p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC>, sm, p, waves, kTileNe);
+    static const int waves = env_waves(FUSED ? "FGS_WAVES_FUSED" : "FGS_WAVES_EMIT", 6);
+    p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC, FUSED>, sm, p, waves, kTileNe);
     const dim3 grid((unsigned)(p.n_pad / kTileNe), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
-    emit_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
+    emit_narrow<SPEC, FUSED><<<grid, kThreads, sm, st>>>(p);
+}
+
+// ---- the maxima the fused pass needs up front --------------------------------------------------------------------
+// DefaultNormalizeScore divides by the highest raw FlexGPU score among the pod's feasible nodes (normalize_score.go:27-35).
+// That raw score does not depend on the pod beyond its kind — GPUScore(node) for a whole-GPU pod, MemScore(node) for a
+// fractional one (gpu_node.go:179-199) — so with the nodes sorted by it, the maximum is the score of the FIRST feasible
+// node in that order: one warp per pod walks the order 32 nodes at a time and almost always stops after the first step.
+__global__ void __launch_bounds__(256) flexmax_prepass(const __grid_constant__ NarrowParams prm, const int* __restrict__ ord_g,
+                                                       const int* __restrict__ ord_m) {
+    const i64 p = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (p >= prm.n_pods) return;
+    auto P = [&](int c) { return __ldg(prm.pn + (i64)c * prm.p_pad + p); };
+    int kind = P(PN_KIND);
+    const bool flex_f = prm.fused_spec & SP_FLEX_F, fit_f = prm.fused_spec & SP_FIT_F;
+    if (kind == 3) {
+        if (flex_f) return; // both limits: FlexGPU.Filter rejects every node (flex_gpu.go:58-61)
+        kind = 1;           // a gpu limit wins over a memory limit (flex_gpu.go:157-159)
+    }
+    if (kind != 1 && kind != 2) return; // no limit: the raw score is 0 on every node
+    const int lim_g = P(PN_LIM_G), lim_m = P(PN_LIM_M), rc = P(PN_RC), rm = P(PN_RM), re = P(PN_RE), rs0 = P(PN_RS0), rs1 = P(PN_RS1);
+    const int* ord = kind == 2 ? ord_m : ord_g;
+    for (i64 base = 0; base < prm.n_nodes; base += 32) {
+        const i64 k = base + lane;
+        bool ok = false;
+        int score = 0;
+        if (k < prm.n_nodes) {
+            const i64 n = ord[k];
+            auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
+            const uint32_t fl = (uint32_t)C(NN_FLAGS);
+            ok = (fl & FGS_NF_VALID) != 0;
+            if (flex_f) ok = ok && lim_g <= C(NN_THR_GPU) && lim_m <= C(NN_THR_MEM) && !(fl & FGS_NF_REF_PANIC);
+            if (fit_f) ok = ok && (fl & NDF_PODS_OK) && rc <= C(NN_FREE_CPU) && rm <= C(NN_FREE_MEM) && re <= C(NN_FREE_EPH) && rs0 <= C(NN_FS0) && rs1 <= C(NN_FS1);
+            score = C(kind == 2 ? NN_MSCORE : NN_GSCORE);
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+        if (bal) {
+            const int v = __shfl_sync(0xffffffffu, score, __ffs(bal) - 1);
+            if (lane == 0) prm.reduce_max[(i64)RR_FLEX_MAX * prm.p_pad + p] = kind == 2 ? (i64)v * ((i64)1 << prm.sh.s[DIM_FM]) : (i64)v;
+            return;
+        }
+    }
 }
 
 } // namespace
@@ -713,12 +867,57 @@ bool launch_reduce_narrow(const NarrowParams& p, uint32_t spec, void* stream) {
     }
 }
 
+bool narrow_fused_available(uint32_t spec) {
+    switch (spec & (SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST | SP_SC_ALLOC | SP_W_EQ)) {
+        case SP_SC_FLEX | SP_SC_FIT | SP_W_EQ:
+        case SP_SC_FLEX | SP_SC_FIT:
+        case SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST | SP_W_EQ:
+        case SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST:
+        case SP_SC_FLEX:
+        case SP_SC_FIT | SP_W_EQ:
+        case SP_SC_FIT:
+            return true;
+        default:
+            return false;
+    }
+}
+
+// One pass over pod × node: flexmax_prepass, then emit_narrow<SPEC, true> (filters + bitmap + count + scores + key).
+// ord_g / ord_m: the node indices sorted by GPUScore / MemScore, highest first (launch_narrow_orders).
+bool launch_fused_narrow(const NarrowParams& p0, uint32_t spec, const int* ord_g, const int* ord_m, void* stream, void* ev_between, int part) {
+    cudaStream_t st = (cudaStream_t)stream;
+    NarrowParams p = p0;
+    p.fused_spec = spec;
+    if (!narrow_fused_available(spec)) return false;
+    if (part & 1) {
+        if (spec & SP_SC_FLEX) flexmax_prepass<<<(unsigned)((p.n_pods * 32 + 255) / 256), 256, 0, st>>>(p, ord_g, ord_m);
+        if (ev_between) cudaEventRecord((cudaEvent_t)ev_between, st);
+    }
+    if (!(part & 2)) return true;
+    switch (spec & (SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST | SP_SC_ALLOC | SP_W_EQ)) {
+#define FCASE(v)                          \
+    case v:                               \
+        launch_emit_spec<v, true>(p, st); \
+        return true;
+        FCASE(SP_SC_FLEX | SP_SC_FIT | SP_W_EQ)
+        FCASE(SP_SC_FLEX | SP_SC_FIT)
+        FCASE(SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST | SP_W_EQ)
+        FCASE(SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST)
+        FCASE(SP_SC_FLEX)
+        FCASE(SP_SC_FIT | SP_W_EQ)
+        FCASE(SP_SC_FIT)
+#undef FCASE
+        default:
+            return false;
+    }
+}
+
 bool launch_emit_narrow(const NarrowParams& p, uint32_t spec, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     switch (spec & (SP_SC_FLEX | SP_SC_FIT | SP_FIT_MOST | SP_SC_ALLOC | SP_W_EQ)) {
-#define ECASE(v)                    \
-    case v:                         \
-        launch_emit_spec<v>(p, st); \
+#define ECASE(v)                           \
+    case v:                                \
+        launch_emit_spec<v, false>(p, st); \
         return true;
         ECASE(SP_SC_FLEX | SP_SC_FIT | SP_W_EQ) // C2 / C5: FlexGPU + LeastAllocated cpu:1 memory:1
         ECASE(SP_SC_FLEX | SP_SC_FIT)

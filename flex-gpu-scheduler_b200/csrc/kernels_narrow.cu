@@ -12,6 +12,7 @@
 //
 // Plugin configuration is a template parameter (SPEC bits) so that the inner loop carries no
 // configuration branches.
+#include <cub/device/device_radix_sort.cuh>
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -262,6 +263,71 @@ void launch_special_pass(const uint32_t* bitmap, int64_t words_per_row, const in
 
 void launch_narrow_nodes(const int64_t* nd, int64_t n_pad, const NarrowShifts& sh, int fit_most, int* nn, void* stream) {
     narrow_nodes<<<(unsigned)((n_pad + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const i64*)nd, n_pad, sh, fit_most, nn);
+}
+
+// Which pods would make the reference panic inside FlexGPU.Filter: a pod with a flex limit that gets as far as
+// NewGPUNode (flex_gpu.go:101) on a node whose device state is inconsistent (gpu_node.go:40-58,109,115) — it passed the
+// limit-sum checks (:85-98) and, when NodeResourcesFit runs first, Fit as well (RunFilterPlugins stops at the first
+// failure, runtime/framework.go:667-693). The evaluation loops keep such nodes infeasible for these pods through their
+// thresholds; this pass, over the few such nodes only, raises the pods' error flag.
+__global__ void __launch_bounds__(128) filter_panic_pass(const int* __restrict__ nn, const int* __restrict__ pn, const i64* __restrict__ special,
+                                                         i64 n_pad, int n_special, i64 n_pods, i64 p_pad, int fit_f, int flex_first,
+                                                         i64* __restrict__ reduce_max) {
+    const i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    auto P = [&](int c) { return pn[(i64)c * p_pad + p]; };
+    const int kind = P(PN_KIND);
+    if (kind != 1 && kind != 2) return; // no limit: Success before NewGPUNode (:54-56); both: rejected before it (:58-61)
+    const int lim_g = P(PN_LIM_G), lim_m = P(PN_LIM_M), rc = P(PN_RC), rm = P(PN_RM), re = P(PN_RE), rs0 = P(PN_RS0), rs1 = P(PN_RS1);
+    for (int k = 0; k < n_special; ++k) {
+        const i64 e = special[k];
+        if (!(e >> 40)) continue;
+        const i64 n = e & 0xffffffffll;
+        auto C = [&](int c) { return nn[(i64)c * n_pad + n]; };
+        const uint32_t fl = (uint32_t)C(NN_FLAGS);
+        if (!(fl & FGS_NF_VALID)) continue;
+        if (!(lim_g <= C(NN_THR_GPU) && lim_m <= C(NN_THR_MEM))) continue;
+        if (fit_f && !flex_first) {
+            const bool fit_ok = (fl & NDF_PODS_OK) && rc <= C(NN_FREE_CPU) && rm <= C(NN_FREE_MEM) && re <= C(NN_FREE_EPH) && rs0 <= C(NN_FS0) && rs1 <= C(NN_FS1);
+            if (!fit_ok) continue;
+        }
+        reduce_max[(i64)RR_FILTER_PANIC * p_pad + p] = 1;
+        return;
+    }
+}
+
+void launch_filter_panic_pass(const int* nn, const int* pn, const int64_t* special, int64_t n_pad, int n_special, int64_t n_pods, int64_t p_pad,
+                              int fit_f, int flex_first, int64_t* reduce_max, void* stream) {
+    if (n_special <= 0 || n_pods <= 0) return;
+    filter_panic_pass<<<(unsigned)((n_pods + 127) / 128), 128, 0, (cudaStream_t)stream>>>(nn, pn, (const i64*)special, n_pad, n_special, n_pods, p_pad, fit_f,
+                                                                                       flex_first, (i64*)reduce_max);
+}
+
+// ---- node orders for the fused pass: indices sorted by GPUScore / MemScore, highest first ---------------------------------
+__global__ void iota_kernel(int* v, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = i;
+}
+
+size_t narrow_orders_scratch_bytes(int64_t n_nodes) {
+    size_t tmp = 0;
+    cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp, (const int*)nullptr, (int*)nullptr, (const int*)nullptr, (int*)nullptr, (int)n_nodes);
+    return ((tmp + 255) / 256) * 256 + 2 * sizeof(int) * (size_t)((n_nodes + 63) / 64 * 64);
+}
+
+// ord[0][n_pad] ← by NN_GSCORE, ord[1][n_pad] ← by NN_MSCORE (ties in any order: only the score of the first feasible
+// node is used). scratch: narrow_orders_scratch_bytes(n_nodes).
+void launch_narrow_orders(const int* nn, int64_t n_nodes, int64_t n_pad, int* ord, void* scratch, size_t scratch_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t nn64 = (size_t)((n_nodes + 63) / 64 * 64);
+    int* iota = (int*)scratch;
+    int* keys_out = iota + nn64;
+    void* tmp = (void*)(keys_out + nn64);
+    size_t tmp_bytes = scratch_bytes - 2 * sizeof(int) * nn64;
+    if (n_nodes <= 0) return;
+    iota_kernel<<<(unsigned)((n_nodes + 255) / 256), 256, 0, st>>>(iota, (int)n_nodes);
+    cub::DeviceRadixSort::SortPairsDescending(tmp, tmp_bytes, nn + (i64)NN_GSCORE * n_pad, keys_out, iota, ord, (int)n_nodes, 0, 32, st);
+    cub::DeviceRadixSort::SortPairsDescending(tmp, tmp_bytes, nn + (i64)NN_MSCORE * n_pad, keys_out, iota, ord + n_pad, (int)n_nodes, 0, 32, st);
 }
 
 void launch_narrow_pods(const int64_t* pods, int64_t p_pad, int S, const NarrowShifts& sh, uint32_t fit_ignored, int* pn, void* stream) {

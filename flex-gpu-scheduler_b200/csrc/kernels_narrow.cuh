@@ -75,6 +75,7 @@ struct NarrowParams {
     int fit_w_cpu, fit_w_mem;
     float fit_inv_wsum;
     uint64_t seed;
+    uint32_t fused_spec; // fused pass only: which filters run (SP_FLEX_F / SP_FIT_F), a run-time choice there
 };
 
 // special[0][k] = node index | (panics ? 1<<40 : 0), special[1][k] = |MemScore| when it is negative, else 0
@@ -82,11 +83,21 @@ void launch_analyze_nodes(const int64_t* nd, int64_t n_nodes, int64_t n_pad, int
 // per pod: RR_NEG_MAG / RR_SCORE_PANIC rows of reduce_max from the feasibility bits of the special nodes
 void launch_special_pass(const uint32_t* bitmap, int64_t words_per_row, const int64_t* special, int64_t n_pad, int n_special,
                          const int64_t* pods, int64_t* reduce_max, int64_t n_pods, int64_t p_pad, void* stream);
+// the pods that reach NewGPUNode's panic inside FlexGPU.Filter → RR_FILTER_PANIC (narrow tables; after either filter pass)
+void launch_filter_panic_pass(const int* nn, const int* pn, const int64_t* special, int64_t n_pad, int n_special, int64_t n_pods, int64_t p_pad,
+                              int fit_f, int flex_first, int64_t* reduce_max, void* stream);
 void launch_narrow_nodes(const int64_t* nd, int64_t n_pad, const NarrowShifts& sh, int fit_most, int* nn, void* stream);
 void launch_narrow_pods(const int64_t* pods, int64_t p_pad, int S, const NarrowShifts& sh, uint32_t fit_ignored, int* pn, void* stream);
 uint32_t narrow_spec_bits(bool flex_f, bool fit_f, bool sc_flex, bool sc_fit, bool fit_most, bool sc_alloc, bool w_eq);
 // false = no instantiation for that plugin combination (the caller falls back to the int64 kernels)
 bool launch_reduce_narrow(const NarrowParams& p, uint32_t spec, void* stream);
 bool launch_emit_narrow(const NarrowParams& p, uint32_t spec, void* stream);
+// The fused pass (one pass over pod × node; no Allocatable among the score plugins): node orders, then prepass + kernel.
+// ev_between (cudaEvent_t, optional) is recorded between the prepass and the main kernel.
+size_t narrow_orders_scratch_bytes(int64_t n_nodes);
+void launch_narrow_orders(const int* nn, int64_t n_nodes, int64_t n_pad, int* ord, void* scratch, size_t scratch_bytes, void* stream);
+bool narrow_fused_available(uint32_t spec);
+// part: 1 = the prepass only, 2 = the main kernel only, 3 = both
+bool launch_fused_narrow(const NarrowParams& p, uint32_t spec, const int* ord_g, const int* ord_m, void* stream, void* ev_between, int part);
 
 } // namespace fgs

@@ -191,6 +191,20 @@ int fgs_resubmit(fgs_engine* e, const fgs_eval_opts* opts);
  *   → fgs_pass_emit → [merge select_key across shards] → fgs_fetch_results.
  * All stages are asynchronous on the engine stream except fgs_fetch_results. */
 int fgs_stage_pods(fgs_engine* e, const fgs_pod_table* pods);
+/* Filter AND Score in one pass over pod × node (opt-in, FGS_FUSED=1 in the environment when the engine is created:
+ * fgs_evaluate / fgs_submit then take it by themselves when they can; measured slower than the two passes on config 2,
+ * DESIGN.md §3): a
+ * per-pod prepass finds DefaultNormalizeScore's maxCount — the raw FlexGPU score depends on the node and the pod's kind
+ * only, so it is the score of the first feasible node in score order — then one kernel runs the filters, writes the
+ * bitmap and the counts, scores, normalises, sums and keeps the selectHost key. Needs: one engine holding the whole
+ * cluster (nothing to merge between Filter and Score), no sampling, no nominated pods, default outputs, no
+ * NodeResourcesAllocatable among the score plugins, the int32 specialisation. fgs_fused_eligible: 1 / 0 for the staged
+ * batch; fgs_pass_fused replaces fgs_pass_reduce + fgs_pass_emit (FGS_E_STATE when not eligible). */
+int fgs_fused_eligible(fgs_engine* e, const fgs_eval_opts* opts);
+int fgs_pass_fused(fgs_engine* e, const fgs_eval_opts* opts);
+/* the same in its two steps (for callers that time them apart): per-pod prepass, then the pass over pod × node */
+int fgs_pass_fused_prepass(fgs_engine* e, const fgs_eval_opts* opts);
+int fgs_pass_fused_main(fgs_engine* e, const fgs_eval_opts* opts);
 int fgs_pass_reduce(fgs_engine* e);
 int fgs_pass_emit(fgs_engine* e, const fgs_eval_opts* opts);
 int fgs_fetch_results(fgs_engine* e, fgs_results* out);
@@ -367,6 +381,9 @@ typedef struct fgs_timings {
     int32_t reduce_int32, emit_int32;         /* 1: the last pass ran the int32 specialisation */
     float seq_ms;                             /* last fgs_schedule_sequential: the persistent kernel alone */
     int32_t seq_ctas;                         /* CTAs it ran on */
+    int32_t fused;                            /* 1: the last evaluation ran Filter and Score in one pass (then reduce_ms =
+                                                 the per-pod prepass, emit_ms = the fused kernel) */
+    int32_t _pad;
 } fgs_timings;
 int fgs_get_timings(fgs_engine* e, fgs_timings* t);
 

@@ -445,3 +445,48 @@ def test_fit_error_histogram_matches_the_oracle(gpu_ok, oracle):
         assert {k: int(v) for k, v in enumerate(got[0]) if v} == want, (order, got[0])
         assert not got[1].any()  # a pod some node took has no FitError
         eng.close()
+
+
+def test_fused_pass_equals_the_two_passes(gpu_ok, oracle, monkeypatch):
+    """Filter + Score in one pass (flexmax prepass + fused kernel) gives bit for bit what reduce + emit give — bitmap,
+    counts, error bits, every score, the selected node — over plugin sets, strategies, filter orders and quirk nodes;
+    and both equal the oracle."""
+    s = fgs.config_synth(2, n_nodes=1700, n_pending=900, pm_panic_nodes=20, pm_nongpu_nodes=80, pm_invalid_nodes=15, pm_quirk_nodes=40,
+                         max_existing_pods=40)
+    variants = [
+        dict(),
+        dict(filter_plugins=("FlexGPU", "NodeResourcesFit")),
+        dict(filter_plugins=("FlexGPU",), score_plugins=(("FlexGPU", 3),)),
+        dict(filter_plugins=("NodeResourcesFit",), score_plugins=(("NodeResourcesFit", 2),)),
+        dict(fit_strategy="MostAllocated", score_plugins=(("FlexGPU", 2), ("NodeResourcesFit", 5))),
+        dict(fit_resources=(("cpu", 3), ("memory", 1))),
+        dict(filter_plugins=("NodeResourcesFit",), score_plugins=(("FlexGPU", 1), ("NodeResourcesFit", 1))),
+    ]
+    for kw in variants:
+        cfg = fgs.plugin_cfg(**kw)
+        out = []
+        for no_fused in ("0", "1"):
+            monkeypatch.setenv("FGS_FUSED", "1" if no_fused == "0" else "0")
+            eng = fgs.Engine(device=0)
+            eng.set_plugins(cfg)
+            eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot))
+            r = eng.evaluate(fgs.Packer(2).pods(s.pending), want_planes=True)
+            t = eng.timings()
+            assert t["fused"] == (no_fused == "0"), (kw, t)
+            assert t["emit_int32"]
+            out.append(r)
+            eng.close()
+        a, b = out
+        assert np.array_equal(a.feasible_bitmap, b.feasible_bitmap), kw
+        assert np.array_equal(a.feasible_count, b.feasible_count), kw
+        assert np.array_equal(a.pod_err, b.pod_err), kw
+        assert np.array_equal(a.selected_node, b.selected_node) and np.array_equal(a.selected_score, b.selected_score), kw
+        feas = a.feasible(s.n_nodes)
+        assert np.array_equal(a.scores[:, :s.n_nodes][feas], b.scores[:, :s.n_nodes][feas]), kw
+        ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=4)
+        assert np.array_equal(feas, ref.status == 0), kw
+        assert np.array_equal(a.feasible_count, ref.feasible_count) and np.array_equal(a.pod_err, ref.pod_err), kw
+        ok = (ref.pod_err == 0) & (ref.feasible_count >= 1)
+        m = feas & ok[:, None]
+        assert np.array_equal(a.scores[:, :s.n_nodes][m], ref.total[m]), kw
+    monkeypatch.delenv("FGS_FUSED")
