@@ -53,6 +53,7 @@ class ClockSampler:
         self.rows = []
         self.source = "nvidia-smi"
         self.window = None  # (t0, t1) in time.perf_counter() terms: the timed region
+        self.period_s = float(os.environ.get("BENCH_CLOCK_PERIOD_MS", "4")) * 1e-3  # NVML sampling period
         self._stop = threading.Event()
         self.ready = threading.Event()  # set once the first sample is in
         self._t = None
@@ -86,7 +87,7 @@ class ClockSampler:
             self.rows.append([str(self.device), str(sm), str(mx), "", hex(r)] + ["Active" if r & b else "Not Active" for _, b in bits]
                              + [time.perf_counter()])
             self.ready.set()
-            self._stop.wait(0.004)
+            self._stop.wait(self.period_s)
 
     def _run(self):
         got = self._nvml_handle()
@@ -334,6 +335,8 @@ def run_ours(args):
         except Exception:
             dev_uuid = None
         sampler = ClockSampler(local, dev_uuid)
+        if world > 1 and "BENCH_CLOCK_PERIOD_MS" not in os.environ:
+            sampler.period_s = 0.02  # NVML queries share a driver lock with kernel launches; the ranks run in lockstep here
         if rank == 0:
             sampler.start()  # before the warm-up: NVML takes some ms to come up, the timed region is short
         for _ in range(args.warmup):
@@ -362,8 +365,9 @@ def run_ours(args):
         launches = eng.timings()["kernel_launches"] - launches0
         reduce_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
         emit_ms = sum(e[2].elapsed_time(e[3]) for e in evs) / args.steps
-        merge1_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
-        merge2_ms = sum(e[3].elapsed_time(e[4]) for e in evs) / args.steps
+        # medians: a merge also waits for the slowest rank's previous pass, so one host hiccup on any rank lands here
+        merge1_ms = sorted(e[1].elapsed_time(e[2]) for e in evs)[len(evs) // 2]
+        merge2_ms = sorted(e[3].elapsed_time(e[4]) for e in evs)[len(evs) // 2]
         if world > 1:
             t = torch.tensor([ms, reduce_ms, emit_ms, merge1_ms, merge2_ms], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -526,7 +530,7 @@ def run_ours(args):
                        "parity": "all nodes evaluated for every pod (percentageOfNodesToScore=100)",
                        "pod_batches": len(batches), "merge": merge_name},
             "kernel_ms": dict({"flexmax_prepass": reduce_ms, "fused_pass": emit_ms} if fused else {"reduce_pass": reduce_ms, "emit_pass": emit_ms},
-                              **({"merge_after_reduce": merge1_ms, "merge_after_emit": merge2_ms, "one_batch_at_a_time_ms_per_step": sync_ms_per_step,
+                              **({"merge_after_reduce_median": merge1_ms, "merge_after_emit_median": merge2_ms, "one_batch_at_a_time_ms_per_step": sync_ms_per_step,
                                   "note": "kernel_ms: measured with one batch at a time (pass, merge, pass, merge in sequence); "
                                           "ms_per_step / value: " + ("up to three batches in flight (fgs_resubmit / fgs_collect), merges overlap the other "
                                                                      "batch's pass" if ov_ms is not None else "the same sequence")} if world > 1 else {})),

@@ -9,7 +9,7 @@ for c in ${CTAS:-8 16 32}; do
 import json
 try:
     d = json.loads(open("gpurun_out/ctas_${N}_$c.json").read().strip().splitlines()[-1])
-    print("ctas $c", d["n_gpus"], round(d["ms_per_step"], 4), "%.3e" % d["value"], round(d["kernel_ms"]["one_batch_at_a_time_ms_per_step"], 4), "e2e %.3e" % d["e2e"]["value"])
+    print("ctas $c", d["n_gpus"], round(d["ms_per_step"], 4), "%.3e" % d["value"], round(d["kernel_ms"].get("one_batch_at_a_time_ms_per_step", 0), 4), "e2e %.3e" % d["e2e"]["value"])
 except Exception as ex:
     print("no line:", ex)
 PY
