@@ -1,6 +1,7 @@
 // engine.cu — host side of libfgs: device memory, H2D/D2H staging, kernel sequencing and the
 // extern "C" entry points declared in include/fgs.h. There is no CPU evaluation path in this file:
 // every verdict and score comes from the kernels in kernels.cu / gang_quota.cu.
+#include <omp.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -704,41 +705,66 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
     FGS_CUDA(e, cudaEventRecord(e->events[0], e->stream));
     // one pass over every column: copy into the pinned staging buffer and collect the OR / MAX that the int32
     // specialisation needs (decide_narrow); a few host threads share the work
+    // ONE parallel region: every thread takes a contiguous range of pods through all the columns (one fork / join per
+    // batch instead of one per column — with one engine per GPU and several GPUs per host the joins were the cost)
     const int nth = e->host_threads;
-    auto col = [&](int c, const int64_t* src) {
-        int64_t* dst = h + (int64_t)c * pp;
-        uint64_t o = 0;
-        int64_t m = 0;
-#pragma omp parallel for num_threads(nth) reduction(| : o) reduction(max : m) schedule(static)
-        for (int64_t i = 0; i < P; ++i) {
-            const int64_t v = src[i];
-            dst[i] = v;
-            o |= (uint64_t)v;
-            m = v > m ? v : m;
-        }
-        std::memset(dst + P, 0, sizeof(int64_t) * (size_t)(pp - P));
-        e->stage_or[c] = o;
-        e->stage_max[c] = m;
-    };
-    col(PD_GPU_LIM, t->flex_gpu_limit);
-    col(PD_MEM_LIM, t->flex_mem_limit);
-    col(PD_REQ_CPU, t->req_mcpu);
-    col(PD_REQ_MEM, t->req_mem);
-    col(PD_REQ_EPH, t->req_eph);
-    col(PD_NZ_CPU, t->nz_mcpu);
-    col(PD_NZ_MEM, t->nz_mem);
+    constexpr int kMaxCols = PD_FIXED_COLS + FGS_MAX_SCALARS;
+    const int64_t* src[kMaxCols] = {nullptr};
+    src[PD_GPU_LIM] = t->flex_gpu_limit;
+    src[PD_MEM_LIM] = t->flex_mem_limit;
+    src[PD_REQ_CPU] = t->req_mcpu;
+    src[PD_REQ_MEM] = t->req_mem;
+    src[PD_REQ_EPH] = t->req_eph;
+    src[PD_NZ_CPU] = t->nz_mcpu;
+    src[PD_NZ_MEM] = t->nz_mem;
+    for (int s = 0; s < S; ++s) src[PD_FIXED_COLS + s] = t->req_scalar + (int64_t)s * P;
+    const int ncols = pd_cols(S);
+    uint64_t acc_or[kMaxCols] = {0};
+    int64_t acc_max[kMaxCols] = {0};
+    uint32_t acc_pr = 0;
+#pragma omp parallel num_threads(nth)
     {
-        int64_t* dst = h + (int64_t)PD_META * pp;
-        uint32_t pr = 0;
-#pragma omp parallel for num_threads(nth) reduction(| : pr) schedule(static)
-        for (int64_t i = 0; i < P; ++i) {
-            dst[i] = (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]);
-            pr |= t->req_scalar_present[i];
+        const int tn = omp_get_num_threads(), ti = omp_get_thread_num();
+        const int64_t i0 = P * ti / tn, i1 = P * (ti + 1) / tn;
+        uint64_t lo[kMaxCols] = {0};
+        int64_t lm[kMaxCols] = {0};
+        uint32_t lpr = 0;
+        for (int c = 0; c < ncols; ++c) {
+            int64_t* dst = h + (int64_t)c * pp;
+            if (c == PD_META) {
+                for (int64_t i = i0; i < i1; ++i) {
+                    dst[i] = (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]);
+                    lpr |= t->req_scalar_present[i];
+                }
+                continue;
+            }
+            const int64_t* sc = src[c];
+            uint64_t o = 0;
+            int64_t m = 0;
+            for (int64_t i = i0; i < i1; ++i) {
+                const int64_t v = sc[i];
+                dst[i] = v;
+                o |= (uint64_t)v;
+                m = v > m ? v : m;
+            }
+            lo[c] = o;
+            lm[c] = m;
         }
-        std::memset(dst + P, 0, sizeof(int64_t) * (size_t)(pp - P));
-        e->stage_present_or = pr;
+#pragma omp critical
+        {
+            for (int c = 0; c < ncols; ++c) {
+                acc_or[c] |= lo[c];
+                acc_max[c] = lm[c] > acc_max[c] ? lm[c] : acc_max[c];
+            }
+            acc_pr |= lpr;
+        }
     }
-    for (int s = 0; s < S; ++s) col(PD_FIXED_COLS + s, t->req_scalar + (int64_t)s * P);
+    for (int c = 0; c < ncols; ++c) {
+        std::memset(h + (int64_t)c * pp + P, 0, sizeof(int64_t) * (size_t)(pp - P));
+        e->stage_or[c] = acc_or[c];
+        e->stage_max[c] = acc_max[c];
+    }
+    e->stage_present_or = acc_pr;
     if (async) {
         FGS_CUDA(e, cudaMemcpyAsync(e->d_pods, e->h_pods, sizeof(int64_t) * pd_cols(S) * pp, cudaMemcpyHostToDevice, e->copy_stream));
         FGS_CUDA(e, cudaEventRecord(e->ev_h2d, e->copy_stream));
