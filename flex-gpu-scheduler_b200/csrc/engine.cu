@@ -141,6 +141,7 @@ void Engine::free_all() {
     gang_free();
     seq_free();
     peer_free();
+    preempt_free();
 }
 
 // plugin args → kernel parameters; validation mirrors the reference constructors
@@ -570,6 +571,7 @@ int Engine::analyze_nodes_now() {
     Engine* e = this;
     e->node_an_valid = false;
     e->narrow_nodes_sig = -1;
+    e->node_gen++; // every change of the node table comes through here (upload, patch, sequential commits)
     if (!e->d_an) FGS_CUDA(e, cudaMalloc(&e->d_an, sizeof(NodeAnalysis)));
     NodeAnalysis init;
     std::memset(&init, 0, sizeof(init));

@@ -135,6 +135,8 @@ struct Engine {
     GangState* gang = nullptr;
     SeqState* seq = nullptr;
     struct PeerState* peer = nullptr; // peer_merge.cu: the other shards' exchange buffers
+    struct PreemptCache* pcache = nullptr; // preempt.cu: the snapshot's pods as device columns, kept between calls
+    uint64_t node_gen = 0;                 // bumped whenever the node table changes (upload, patch, sequential commits)
 
     fgs_timings tm = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     int64_t launches = 0;
@@ -148,6 +150,7 @@ struct Engine {
     void gang_free();
     void seq_free();
     void peer_free();
+    void preempt_free();
     void fill_derive_params(DeriveParams* dp) const;
     int derive_now();        // derive_node_columns over the whole table + analysis
     int analyze_nodes_now(); // node-side analysis for the int32 specialisation (after any change of d_nd)

@@ -386,31 +386,46 @@ __global__ void __launch_bounds__(1024) pick_candidate_kernel(const uint8_t* __r
 
 using namespace fgs;
 
-extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, const fgs_podset* pending, int64_t p, const fgs_quotas* q,
-                                  int32_t tracks_pods, uint8_t* node_status, uint8_t* victim, int32_t* n_victims, int32_t* picked_node) {
-    if (!eh || !snap || !pending || !node_status) return FGS_E_INVALID;
-    Engine* e = (Engine*)eh;
-    if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_select_victims before fgs_upload_nodes");
-    if (snap->n_nodes != e->n_nodes || e->node_base != 0) return e->fail(FGS_E_INVALID, "fgs_select_victims: the snapshot is not the uploaded node table (whole cluster, one engine)");
-    if (snap->n_scalars != e->S || pending->n_scalars != e->S || (q && q->n_scalars != e->S)) return e->fail(FGS_E_INVALID, "fgs_select_victims: n_scalars mismatch");
-    if (p < 0 || p >= pending->n_pods) return e->fail(FGS_E_INVALID, "fgs_select_victims: pod index out of range");
+// The snapshot's pods as device columns, kept between calls: a PostFilter storm asks about many pods against ONE
+// snapshot, and packing ~10 pods per node on the host dwarfs the kernel. Valid for the same fgs_snapshot object as long
+// as the node table has not been uploaded or patched again (Engine::node_gen).
+namespace fgs {
+struct PreemptCache {
+    const fgs_snapshot* snap = nullptr;
+    uint64_t node_gen = 0;
+    bool valid = false;
+    int64_t N = 0, T = 0;
+    int64_t* d_vp = nullptr; // [ncols][Tn] | pod_off [N + 1]
+    size_t vp_bytes = 0;
+    char* d_work = nullptr;  // quota tables + outputs of one call
+    size_t work_bytes = 0;
+};
+void Engine::preempt_free() {
+    if (!pcache) return;
+    if (pcache->d_vp) cudaFree(pcache->d_vp);
+    if (pcache->d_work) cudaFree(pcache->d_work);
+    delete pcache;
+    pcache = nullptr;
+}
+} // namespace fgs
+
+static int preempt_prepare(Engine* e, const fgs_snapshot* snap) {
+    if (!e->pcache) e->pcache = new PreemptCache();
+    PreemptCache* pc = e->pcache;
+    if (pc->valid && pc->snap == snap && pc->node_gen == e->node_gen && pc->N == snap->n_nodes && pc->T == snap->pods.n_pods) return FGS_OK;
+    pc->valid = false;
     const int64_t N = snap->n_nodes, T = snap->pods.n_pods;
-    const int S = e->S, W = 2 + S;
-    if (picked_node) *picked_node = -1;
-    if (N == 0) return FGS_OK;
+    const int S = e->S;
     for (int64_t n = 0; n < N; ++n)
         if (snap->pod_off[n + 1] - snap->pod_off[n] > kMaxPodsPerNode)
             return e->fail(FGS_E_TOO_LARGE, "fgs_select_victims: node " + std::to_string(n) + " has more than 128 pods");
-    // the pods of the snapshot and the preemptor, through the packer's arithmetic
-    PackedPods vp, pp;
+    PackedPods vp; // the pods of the snapshot through the packer's arithmetic
     std::string err;
-    int rc = pack_pods(&snap->pods, 0, T, &vp, &err);
-    if (rc == FGS_OK) rc = pack_pods(pending, p, p + 1, &pp, &err);
+    const int rc = pack_pods(&snap->pods, 0, T, &vp, &err);
     if (rc) return e->fail(rc, err);
     const int ncols = VP_FIXED + S;
-    const size_t Tn = (size_t)std::max<int64_t>(T, 1), NS = q ? (size_t)q->n_ns : 0;
-    // one staging buffer: columns | pod_off | quota tables
-    std::vector<int64_t> h((size_t)ncols * Tn + (size_t)N + 1 + 3 * NS * (size_t)W);
+    const size_t Tn = (size_t)std::max<int64_t>(T, 1);
+    std::vector<int64_t> h((size_t)ncols * Tn + (size_t)N + 1);
     auto col = [&](int c, int64_t a) -> int64_t& { return h[(size_t)c * Tn + (size_t)a]; };
     for (int64_t a = 0; a < T; ++a) {
         col(VP_NS, a) = vp.ns[(size_t)a];
@@ -426,15 +441,54 @@ extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, cons
         col(VP_REQ_EPH, a) = vp.req_eph[(size_t)a];
         for (int s = 0; s < S; ++s) col(VP_FIXED + s, a) = vp.req_scalar[(size_t)((int64_t)s * T + a)];
     }
-    int64_t* h_off = h.data() + (size_t)ncols * Tn;
-    std::memcpy(h_off, snap->pod_off, sizeof(int64_t) * (size_t)(N + 1));
-    int64_t* h_q = h_off + N + 1;
+    std::memcpy(h.data() + (size_t)ncols * Tn, snap->pod_off, sizeof(int64_t) * (size_t)(N + 1));
+    const size_t bytes = h.size() * sizeof(int64_t);
+    FGS_CUDA(e, cudaSetDevice(e->device));
+    FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (bytes > pc->vp_bytes) {
+        if (pc->d_vp) cudaFree(pc->d_vp);
+        pc->d_vp = nullptr;
+        pc->vp_bytes = 0;
+        FGS_CUDA(e, cudaMalloc(&pc->d_vp, bytes));
+        pc->vp_bytes = bytes;
+    }
+    FGS_CUDA(e, cudaMemcpy(pc->d_vp, h.data(), bytes, cudaMemcpyHostToDevice));
+    pc->snap = snap;
+    pc->node_gen = e->node_gen;
+    pc->N = N;
+    pc->T = T;
+    pc->valid = true;
+    return FGS_OK;
+}
+
+extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, const fgs_podset* pending, int64_t p, const fgs_quotas* q,
+                                  int32_t tracks_pods, uint8_t* node_status, uint8_t* victim, int32_t* n_victims, int32_t* picked_node) {
+    if (!eh || !snap || !pending || !node_status) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_select_victims before fgs_upload_nodes");
+    if (snap->n_nodes != e->n_nodes || e->node_base != 0) return e->fail(FGS_E_INVALID, "fgs_select_victims: the snapshot is not the uploaded node table (whole cluster, one engine)");
+    if (snap->n_scalars != e->S || pending->n_scalars != e->S || (q && q->n_scalars != e->S)) return e->fail(FGS_E_INVALID, "fgs_select_victims: n_scalars mismatch");
+    if (p < 0 || p >= pending->n_pods) return e->fail(FGS_E_INVALID, "fgs_select_victims: pod index out of range");
+    const int64_t N = snap->n_nodes, T = snap->pods.n_pods;
+    const int S = e->S, W = 2 + S;
+    if (picked_node) *picked_node = -1;
+    if (N == 0) return FGS_OK;
+    int rc = preempt_prepare(e, snap);
+    if (rc) return rc;
+    PreemptCache* pc = e->pcache;
+    PackedPods pp; // the preemptor
+    std::string err;
+    rc = pack_pods(pending, p, p + 1, &pp, &err);
+    if (rc) return e->fail(rc, err);
+    const int ncols = VP_FIXED + S;
+    const size_t Tn = (size_t)std::max<int64_t>(T, 1), NS = q ? (size_t)q->n_ns : 0;
+    std::vector<int64_t> hq(3 * NS * (size_t)W + 1);
     PreemptParams prm;
     std::memset(&prm, 0, sizeof(prm));
     if (q && NS) {
-        std::memcpy(h_q, q->min, sizeof(int64_t) * NS * W);
-        std::memcpy(h_q + NS * W, q->max, sizeof(int64_t) * NS * W);
-        std::memcpy(h_q + 2 * NS * W, q->used, sizeof(int64_t) * NS * W);
+        std::memcpy(hq.data(), q->min, sizeof(int64_t) * NS * W);
+        std::memcpy(hq.data() + NS * W, q->max, sizeof(int64_t) * NS * W);
+        std::memcpy(hq.data() + 2 * NS * W, q->used, sizeof(int64_t) * NS * W);
         for (size_t k = 0; k < NS; ++k) { // Σ Used and Σ Min over the namespaces with a quota (elasticquota.go:40-51)
             if (!q->has_eq[k]) continue;
             const uint32_t up = q->used_scalar_present[k];
@@ -447,20 +501,28 @@ extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, cons
     }
     cudaSetDevice(e->device);
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
-    const size_t in_bytes = h.size() * sizeof(int64_t);
-    const size_t small_bytes = NS + sizeof(uint32_t) * NS + 64;                    // has_eq, used_scalar_present
+    const size_t q_bytes = ((sizeof(int64_t) * 3 * NS * (size_t)W + 63) / 64) * 64;
+    const size_t small_bytes = ((NS + sizeof(uint32_t) * NS + 64 + 63) / 64) * 64;      // has_eq, used_scalar_present
     const size_t out_bytes = (size_t)N + Tn + sizeof(int) * (size_t)N + 4 * sizeof(int64_t) * (size_t)N + 256; // status, victim, n_victims, cand, picked
-    char* d = nullptr;
-    FGS_CUDA(e, cudaMalloc(&d, in_bytes + small_bytes + out_bytes + 256));
-    char* d_small = d + ((in_bytes + 63) / 64) * 64;
-    char* d_out = d_small + ((small_bytes + 63) / 64) * 64;
-    cudaError_t ce = cudaMemcpyAsync(d, h.data(), in_bytes, cudaMemcpyHostToDevice, e->stream);
+    const size_t need = q_bytes + small_bytes + out_bytes + 256;
+    if (need > pc->work_bytes) {
+        if (pc->d_work) cudaFree(pc->d_work);
+        pc->d_work = nullptr;
+        pc->work_bytes = 0;
+        FGS_CUDA(e, cudaMalloc(&pc->d_work, need));
+        pc->work_bytes = need;
+    }
+    char* d_q = pc->d_work;
+    char* d_small = d_q + q_bytes;
+    char* d_out = d_small + small_bytes;
+    cudaError_t ce = cudaSuccess;
+    if (NS) ce = cudaMemcpyAsync(d_q, hq.data(), sizeof(int64_t) * 3 * NS * (size_t)W, cudaMemcpyHostToDevice, e->stream);
     if (ce == cudaSuccess && NS) ce = cudaMemcpyAsync(d_small, q->has_eq, NS, cudaMemcpyHostToDevice, e->stream);
     char* d_pres = d_small + ((NS + 15) / 16) * 16;
     if (ce == cudaSuccess && NS) ce = cudaMemcpyAsync(d_pres, q->used_scalar_present, sizeof(uint32_t) * NS, cudaMemcpyHostToDevice, e->stream);
     if (ce == cudaSuccess) ce = cudaMemsetAsync(d_out, 0, out_bytes, e->stream);
     prm.raw = (const i64*)e->d_raw;
-    prm.vp = (const i64*)d;
+    prm.vp = (const i64*)pc->d_vp;
     prm.pod_off = prm.vp + (size_t)ncols * Tn;
     prm.n_nodes = N;
     prm.n_pad = e->n_pad;
@@ -469,7 +531,7 @@ extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, cons
     prm.D = e->D;
     if (q && NS) {
         prm.has_eq = (const uint8_t*)d_small;
-        prm.qmin = prm.pod_off + N + 1;
+        prm.qmin = (const i64*)d_q;
         prm.qmax = prm.qmin + NS * W;
         prm.qused = prm.qmax + NS * W;
         prm.qpresent = (const uint32_t*)d_pres;
@@ -511,8 +573,7 @@ extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, cons
     if (ce == cudaSuccess) ce = cudaMemcpyAsync(node_status, prm.status, (size_t)N, cudaMemcpyDeviceToHost, e->stream);
     if (ce == cudaSuccess && victim && T) ce = cudaMemcpyAsync(victim, prm.victim, (size_t)T, cudaMemcpyDeviceToHost, e->stream);
     if (ce == cudaSuccess && n_victims) ce = cudaMemcpyAsync(h_cnt.data(), prm.n_victims, sizeof(int) * (size_t)N, cudaMemcpyDeviceToHost, e->stream);
-    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->stream);
-    cudaFree(d);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->stream); // (the host copies above come from pageable memory: already staged)
     if (ce != cudaSuccess) return e->fail(FGS_E_CUDA, std::string("fgs_select_victims: ") + cudaGetErrorString(ce));
     if (n_victims)
         for (int64_t n = 0; n < N; ++n) n_victims[n] = h_cnt[(size_t)n];

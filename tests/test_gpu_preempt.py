@@ -140,3 +140,29 @@ def test_pick_one_node_criteria_on_the_gpu(gpu_ok, oracle):
         assert ties == want, (want, ties, st.tolist(), vic.tolist())
         assert picked == (want[0] if want else -1)
         eng.close()
+
+
+def test_snapshot_pods_are_cached_until_the_node_table_changes(gpu_ok, oracle):
+    """fgs_select_victims keeps the snapshot's pods on the device between calls; uploading the node table again (the
+    snapshot object may be the same one, edited in place) makes it pack them afresh"""
+    def n(pods):
+        return B.node({"cpu": 1000, "memory": 64 * GiB, "pods": 110}, pods)
+
+    def v(prio):
+        return B.pod([B.ctr({"cpu": 600})], priority=prio, node_name=True)
+
+    snap = B.build_snapshot([n([v(50)]), n([v(40)]), n([v(60)])])
+    pend = B.build_podset([B.pod([B.ctr({"cpu": 900})], priority=1000), B.pod([B.ctr({"cpu": 900})], priority=45)])
+    cfg = fgs.plugin_cfg(filter_plugins=("NodeResourcesFit",), score_plugins=(("NodeResourcesFit", 1),))
+    eng = _engine(snap.ptr, cfg)
+    for p, want in ((0, 1), (1, 1), (0, 1)):  # repeated calls, two preemptors: same cached columns
+        st, vic, cnt, picked = eng.select_victims(snap.ptr, pend.ptr, p, pick=True)
+        rst, rvic, rcnt = oracle.select_victims(snap.ptr, pend.ptr, p, cfg)
+        assert np.array_equal(st, rst) and np.array_equal(vic, rvic) and picked == want
+    # the same snapshot object, edited in place: node 2's pod becomes the least important one
+    snap.ptr.contents.pods.priority[2] = 5
+    eng.upload_nodes(fgs.Packer(2).nodes(snap.ptr))
+    st, vic, cnt, picked = eng.select_victims(snap.ptr, pend.ptr, 0, pick=True)
+    rst, rvic, rcnt = oracle.select_victims(snap.ptr, pend.ptr, 0, cfg)
+    assert np.array_equal(st, rst) and np.array_equal(vic, rvic) and picked == 2
+    eng.close()
