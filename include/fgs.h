@@ -347,7 +347,9 @@ int fgs_quota_check(fgs_engine* e, const fgs_pod_table* pods, const fgs_quotas* 
  *                         wins. The reference dry-runs a random window of the nodes (GetOffsetAndNumCandidates) and
  *                         picks among those; this is the pick over the whole cluster.
  * `snap` must be the snapshot the node table was packed from; single engine holding the whole cluster; at most 128
- * pods per node. The caller filters the nodes by nodesWherePreemptionMightHelp (status plane code != 3) — a node it
+ * pods per node. The engine keeps the snapshot's pods on the device between calls and packs them again only when it
+ * is handed another fgs_snapshot object or the node table has been uploaded / patched since: a snapshot edited in
+ * place goes through fgs_upload_nodes before the next call. The caller filters the nodes by nodesWherePreemptionMightHelp (status plane code != 3) — a node it
  * drops must not be picked: pass picked_node = NULL then and choose among node_status / n_victims on the host. */
 int fgs_select_victims(fgs_engine* e, const fgs_snapshot* snap, const fgs_podset* pending, int64_t p,
                        const fgs_quotas* q, int32_t tracks_pods, uint8_t* node_status, uint8_t* victim,
