@@ -1,6 +1,9 @@
 // engine.cu — host side of libfgs: device memory, H2D/D2H staging, kernel sequencing and the
 // extern "C" entry points declared in include/fgs.h. There is no CPU evaluation path in this file:
 // every verdict and score comes from the kernels in kernels.cu / gang_quota.cu.
+#if defined(__x86_64__)
+#include <emmintrin.h>
+#endif
 #include <omp.h>
 #include <cuda_runtime.h>
 
@@ -688,6 +691,17 @@ extern "C" int fgs_update_nodes(fgs_engine* eh, const fgs_node_table* rows, cons
 
 // async: called by fgs_submit — the staging buffers belong to a pipeline slot that is known to be free, so the
 // compute stream is not drained, and the H2D copy runs on the copy stream (it overlaps the previous batch's kernels)
+// The pinned staging buffer is written once and read by the DMA engine only: a streaming store keeps it out of the
+// caches and spares the read-for-ownership (with one engine per GPU and several GPUs per host the staging passes share
+// the host's memory bandwidth).
+static inline void stream_store(int64_t* p, int64_t v) {
+#if defined(__x86_64__)
+    _mm_stream_si64((long long*)p, (long long)v);
+#else
+    *p = v;
+#endif
+}
+
 static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
     if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_stage_pods before fgs_upload_nodes");
     if (!t || t->n_pods < 0) return e->fail(FGS_E_INVALID, "pod table: null or negative size");
@@ -735,7 +749,7 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
             int64_t* dst = h + (int64_t)c * pp;
             if (c == PD_META) {
                 for (int64_t i = i0; i < i1; ++i) {
-                    dst[i] = (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]);
+                    stream_store(dst + i, (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]));
                     lpr |= t->req_scalar_present[i];
                 }
                 continue;
@@ -745,13 +759,16 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
             int64_t m = 0;
             for (int64_t i = i0; i < i1; ++i) {
                 const int64_t v = sc[i];
-                dst[i] = v;
+                stream_store(dst + i, v);
                 o |= (uint64_t)v;
                 m = v > m ? v : m;
             }
             lo[c] = o;
             lm[c] = m;
         }
+#if defined(__x86_64__)
+        _mm_sfence(); // this thread's streaming stores are globally visible before the region ends
+#endif
 #pragma omp critical
         {
             for (int c = 0; c < ncols; ++c) {
