@@ -8,10 +8,13 @@
 //                        bitmap (staged per pod tile by TMA), not recomputed; an external mask can be
 //                        substituted (the feasible list the framework hands to PreScore).
 //
-// One CTA = 512 nodes in registers (2 per thread) × a range of pods; pod tiles of 64 arrive through a
-// two-stage cp.async.bulk + mbarrier ring. SPEC (plugin set, strategy, weights equal) is a template
-// parameter, so the pod loop has no configuration branches. HBM-write bound by design; the inner loop is
-// integer ALU work, ~45 lane-instructions per (pod,node).
+//   emit_narrow<SPEC, true> + flexmax_prepass: both passes in one (opt-in, FGS_FUSED=1).
+//
+// One CTA = 256 threads × a tile of nodes in registers (reduce: 2 per thread, emit: 4) × a range of pods; pod tiles
+// of 64 arrive through a two-stage cp.async.bulk + mbarrier ring (loads from this GPU's own tables). SPEC (plugin
+// set, strategy, weights equal) is a template parameter, so the pod loops have no configuration branches. The emit
+// pass is HBM-write bound (91.7 % of the copy peak on C2, ~36 lane-instructions per (pod,node)), the reduce pass
+// integer-issue bound (~20).
 #include <cuda_runtime.h>
 
 #include <cstdint>
