@@ -785,7 +785,7 @@ void launch_reduce_spec(NarrowParams p, cudaStream_t st) {
         cudaFuncSetAttribute(reduce_narrow<SPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
         ready = 1;
     }
-    static const int waves = env_waves("FGS_WAVES_REDUCE", 3);
+    static const int waves = env_waves("FGS_WAVES_REDUCE", 12);
     p.pods_per_cta = pods_per_cta_for(reduce_narrow<SPEC>, sm, p, waves, kTileNr);
     const dim3 grid((unsigned)(p.n_pad / kTileNr), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
     reduce_narrow<SPEC><<<grid, kThreads, sm, st>>>(p);
@@ -798,7 +798,7 @@ void launch_emit_spec(NarrowParams p, cudaStream_t st) {
         cudaFuncSetAttribute(emit_narrow<SPEC, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
         ready = 1;
     }
-    static const int waves = env_waves(FUSED ? "FGS_WAVES_FUSED" : "FGS_WAVES_EMIT", 6);
+    static const int waves = env_waves(FUSED ? "FGS_WAVES_FUSED" : "FGS_WAVES_EMIT", FUSED ? 6 : 24);
     p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC, FUSED>, sm, p, waves, kTileNe);
     const dim3 grid((unsigned)(p.n_pad / kTileNe), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
     emit_narrow<SPEC, FUSED><<<grid, kThreads, sm, st>>>(p);
