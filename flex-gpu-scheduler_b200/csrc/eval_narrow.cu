@@ -238,8 +238,9 @@ __global__ void __launch_bounds__(kThreads, 4) reduce_narrow(const __grid_consta
         i64* wnlo = (i64*)(smem + L.wnlo) + stage * kTileP * kWarps;
         uint32_t* bm = (uint32_t*)(smem + L.bm) + stage * kTileP * kWordsTr;
 
-        // the pod loop exists twice: tiles without a node on which NewGPUNode would panic (the normal case) carry
-        // none of the bookkeeping for it
+        // The pod loop used to exist twice (tiles with / without a node on which NewGPUNode would panic); panic nodes now go
+        // through the thresholds and only the plain instance runs. The generic-lambda form is kept on purpose: written as
+        // a bare loop the same body compiles to a slower schedule (0.432 vs 0.403 ms on C2, measured).
         auto pod_loop = [&](auto rare_tag) {
         constexpr bool kRare = decltype(rare_tag)::value;
         for (int jp = 0; jp < n_valid; ++jp) {
