@@ -1,0 +1,48 @@
+// Exactness of the division by invariant multipliers the int32 emit pass uses (kernels_narrow.cuh: narrow_magic;
+// eval_narrow.cu: qmagic = umulhi(2x, m) >> l): floor(x / d) for every dividend 0 <= x < 2^31 and divisor 1 <= d < 2^31.
+// Host-only: the same header function computes the pairs for the device tables.
+#include <cstdint>
+#include <cstdio>
+#include <random>
+
+#include "kernels_narrow.cuh"
+
+static inline uint32_t umulhi(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * b) >> 32); }
+
+int main() {
+    long long checks = 0, bad = 0;
+    auto check = [&](uint32_t x, uint32_t d, uint32_t m, int l) {
+        if (x >= (1u << 31)) return;
+        const uint32_t q = umulhi(2u * x, m) >> l;
+        ++checks;
+        if (q != x / d) {
+            if (bad < 10) std::printf("x=%u d=%u m=%u l=%d: %u != %u\n", x, d, m, l, q, x / d);
+            ++bad;
+        }
+    };
+    auto divisor = [&](uint32_t d, std::mt19937_64& rng) {
+        int l = 0;
+        const uint32_t m = fgs::narrow_magic(d, &l);
+        const uint32_t top = 0x7fffffffu;
+        for (uint32_t x : {0u, 1u, d - 1, d, d + 1, 2 * d - 1, 2 * d, top, top - 1, top - d, top / d * d, top / d * d - 1}) check(x, d, m, l);
+        for (int k = 0; k < 64; ++k) {
+            const uint32_t x = (uint32_t)(rng() & top);
+            check(x, d, m, l);
+            const uint32_t y = x / d * d; // multiples and their neighbours: where a wrong multiplier shows
+            check(y, d, m, l);
+            if (y) check(y - 1, d, m, l);
+        }
+    };
+    std::mt19937_64 rng(0xF65);
+    for (uint32_t d = 1; d <= 200000; ++d) divisor(d, rng);                       // every small divisor (capacities, maxima)
+    for (int e = 1; e < 31; ++e)                                                    // around every power of two
+        for (int o = -3; o <= 3; ++o) {
+            const int64_t d = ((int64_t)1 << e) + o;
+            if (d >= 1 && d < ((int64_t)1 << 31)) divisor((uint32_t)d, rng);
+        }
+    for (int k = 0; k < 200000; ++k) divisor((uint32_t)(rng() % 0x7fffffffu) + 1, rng); // random divisors up to 2^31 - 1
+    int l = 7;
+    if (fgs::narrow_magic(0, &l) != 0 || l != 0) ++bad; // capacity 0 → quotient 0 (least_allocated.go:48-50)
+    std::printf("%lld checks, %lld failed\n", checks, bad);
+    return bad ? 1 : 0;
+}

@@ -151,3 +151,17 @@ def test_pod_table_matches_reference_request_rules():
     assert t.flags[1] == PF_NONE and t.nz_mcpu[1] == 100 and t.nz_mem[1] == 200 * Mi
     assert t.flags[2] == PF_GPU                              # a zero-valued scalar key still makes the request non-empty
     assert t.req_scalar_present[2] == 1
+
+
+def test_division_by_invariant_multipliers_is_exact(tmp_path):
+    """The int32 emit pass divides by multiplication (kernels_narrow.cuh: narrow_magic): the host-side function that fills
+    the device tables, checked against '/' over every small divisor, the neighbours of every power of two and random
+    31-bit divisors (tests/cpp/magic_test.cpp, ~7.5e7 quotients)."""
+    import subprocess
+    exe = str(tmp_path / "magic_test")
+    cmd = ["g++", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "flex-gpu-scheduler_b200", "csrc"), "-I", os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "cpp", "magic_test.cpp"), "-o", exe]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "0 failed" in r.stdout, r.stdout[-2000:]
