@@ -165,3 +165,34 @@ def test_division_by_invariant_multipliers_is_exact(tmp_path):
     assert r.returncode == 0, r.stderr[-2000:]
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "0 failed" in r.stdout, r.stdout[-2000:]
+
+
+def test_ctypes_mirrors_match_the_c_headers(tmp_path):
+    """Every struct that crosses the C ABI exists twice: in include/*.h and as a ctypes.Structure in _lib.py. A C program
+    prints sizeof and the offset of every field of the header's version; both must agree with the Python mirror."""
+    import subprocess
+    from flex_gpu_scheduler_b200 import _lib as L
+    pairs = {"fgs_podset": L.Podset, "fgs_snapshot": L.Snapshot, "fgs_podgroups": L.Podgroups, "fgs_quotas": L.Quotas,
+             "fgs_plugin_cfg": L.PluginCfg, "fgs_node_table": L.NodeTable, "fgs_pod_table": L.PodTable, "fgs_config": L.Config,
+             "fgs_results": L.Results, "fgs_eval_opts": L.EvalOpts, "fgs_device_view": L.DeviceView, "fgs_peer_group": L.PeerGroup,
+             "fgs_timings": L.Timings, "fgs_seq_opts": L.SeqOpts, "fgs_seq_results": L.SeqResults, "fgs_synth_params": L.SynthParams}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "fgs.h"', 'int main(void) {']
+    for cname, py in pairs.items():
+        lines.append(f'  printf("{cname} size %zu\\n", sizeof({cname}));')
+        for fname, *_ in py._fields_:
+            lines.append(f'  printf("{cname} {fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = str(tmp_path / "layout")
+    r = subprocess.run(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), str(src), "-o", exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-3000:]  # a field the header does not have fails here
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout
+    for line in out.splitlines():
+        cname, what, val = line.split()
+        py = pairs[cname]
+        if what == "size":
+            assert C.sizeof(py) == int(val), (cname, C.sizeof(py), val)
+        else:
+            assert getattr(py, what).offset == int(val), (cname, what, getattr(py, what).offset, val)
+    # … and the header has no field the mirror lacks (sizes equal and every mirrored offset matches ⇒ same layout)
