@@ -196,3 +196,14 @@ def test_ctypes_mirrors_match_the_c_headers(tmp_path):
         else:
             assert getattr(py, what).offset == int(val), (cname, what, getattr(py, what).offset, val)
     # … and the header has no field the mirror lacks (sizes equal and every mirrored offset matches ⇒ same layout)
+
+
+def test_cpp_host_layer_compiles():
+    """include/fgs_plugins.hpp (the C++ mirror of the Go plugin interface) and its test program compile without a GPU;
+    tests/test_gpu_cpp_plugins.py builds and RUNS them on one."""
+    import subprocess
+    cmd = ["g++", "-std=c++17", "-fsyntax-only", "-Wall", "-Wextra", "-I", os.path.join(ROOT, "include"),
+           "-I", os.path.join(ROOT, "flex-gpu-scheduler_b200", "csrc"), "-I", os.path.join(ROOT, "tests", "cpp"),
+           os.path.join(ROOT, "tests", "cpp", "plugin_test.cpp")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "warning" not in r.stderr, r.stderr[-3000:]
