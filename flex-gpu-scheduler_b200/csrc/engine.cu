@@ -18,6 +18,7 @@
 #include <vector>
 
 #include "engine.h"
+#include "filter_tables.cuh"
 #include "kernels.cuh"
 #include "pack.h"
 #include "sample.cuh"
@@ -36,6 +37,30 @@ static std::string g_create_error;
     } while (0)
 
 static int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+static uint64_t this_thread_tag() {
+    static thread_local const char tag = 0; // its address is unique among the live threads and never 0
+    return (uint64_t)(uintptr_t)&tag;
+}
+
+EngineEntry::EngineEntry(Engine* e_) : e(e_), ok(false) {
+    const uint64_t me = this_thread_tag();
+    uint64_t cur = e->owner.load(std::memory_order_acquire);
+    if (cur == me) {
+        e->owner_depth++;
+        ok = true;
+        return;
+    }
+    uint64_t expect = 0;
+    if (e->owner.compare_exchange_strong(expect, me, std::memory_order_acq_rel)) {
+        e->owner_depth = 1;
+        ok = true;
+    }
+}
+
+EngineEntry::~EngineEntry() {
+    if (ok && --e->owner_depth == 0) e->owner.store(0, std::memory_order_release);
+}
 
 int Engine::fail(int code, const std::string& msg) {
     err = msg;
@@ -141,6 +166,7 @@ void Engine::free_all() {
     for (auto& ev : events)
         if (ev) cudaEventDestroy(ev);
     if (own_stream && stream) cudaStreamDestroy(stream);
+    ft_free();
     gang_free();
     seq_free();
     peer_free();
@@ -269,6 +295,10 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
         g_create_error = "fgs_create: n_scalars must be in [2, 8]";
         return FGS_E_INVALID;
     }
+    if (c->node_index_base < 0 || c->node_index_base > ((int64_t)1 << 24) - 2 || c->total_nodes < 0 || c->total_nodes > ((int64_t)1 << 24) - 2) {
+        g_create_error = "fgs_create: node_index_base / total_nodes must be in [0, 2^24-2] (the selectHost key carries the global node index in 24 bits)";
+        return FGS_E_TOO_LARGE;
+    }
     int ndev = 0;
     cudaError_t ce = cudaGetDeviceCount(&ndev);
     if (ce != cudaSuccess || ndev <= 0 || c->device < 0 || c->device >= ndev) {
@@ -295,6 +325,8 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
         // thread leave two CTAs per SM, and the loop does not hide its latencies with 16 warps) — DESIGN.md §3
         const char* nf = getenv("FGS_FUSED");
         e->no_fused = !(nf && nf[0] == '1');
+        const char* fm = getenv("FGS_FILTER");
+        e->filter_mode = fm ? (fm[0] == 'c' ? 1 : (fm[0] == 'l' ? 2 : 0)) : 0;
         const char* ht = getenv("FGS_HOST_THREADS");
         int nth = ht ? atoi(ht) : 4;
         const int hw = (int)std::thread::hardware_concurrency();
@@ -364,7 +396,10 @@ extern "C" void fgs_destroy(fgs_engine* eh) {
 
 extern "C" int fgs_set_plugins(fgs_engine* eh, const fgs_plugin_cfg* c) {
     if (!eh) return FGS_E_INVALID;
-    return ((Engine*)eh)->set_plugins(c);
+    Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_set_plugins while submitted batches are in flight: fgs_collect them first");
+    return e->set_plugins(c);
 }
 
 // ---- int32 specialisation: can this (node table, pod batch) pair run on the narrow kernels? --------------
@@ -548,8 +583,55 @@ int Engine::run_fused(const fgs_eval_opts* opts, int part) { // part: 1 = prepas
     FGS_CUDA(this, cudaGetLastError());
     FGS_CUDA(this, cudaEventRecord(events[3], stream));
     reduce_was_narrow = emit_was_narrow = true;
+    reduce_was_lookup = false;
     emitted = true;
     was_fused = true;
+    return FGS_OK;
+}
+
+// ---- pass A as table look-ups ----------------------------------------------------------------------------------------
+void Engine::ft_free() {
+    if (ft) {
+        ft->free_all();
+        delete ft;
+        ft = nullptr;
+    }
+}
+
+// *use ← the level tables are current for this node table and profile (built here when they are not) and the batch's
+// rows fit the look-up kernel; false → the compare kernels run
+int Engine::ensure_filter_tables(bool* use) {
+    *use = false;
+    if (filter_mode == 1 || n_nodes <= 0) return FGS_OK;
+    if (!ft) {
+        ft = new (std::nothrow) FilterTables();
+        if (!ft) return fail(FGS_E_INVALID, "out of host memory");
+        const char* lim = getenv("FGS_FILTER_TABLE_MB");
+        if (lim && atoll(lim) > 0) ft->limit_bytes = (size_t)atoll(lim) << 20;
+    }
+    const uint32_t fmask = cfg.filter_mask;
+    const bool current = ft->node_gen == node_gen && ft->filter_mask == fmask && ft->n_pad == n_pad && ft->v.n_dims == 5 + S;
+    if (!current || (!ft->valid && !ft->refused)) {
+        FtBuildParams bp;
+        bp.nd = (const int64_t*)d_nd;
+        bp.n_nodes = n_nodes;
+        bp.n_pad = n_pad;
+        bp.S = S;
+        bp.filter_mask = fmask;
+        ft->v.n_dims = 5 + S;
+        ft->n_pad = n_pad;
+        const cudaError_t ce = ft_build(ft, bp, stream, &launches);
+        if (ce != cudaSuccess) {
+            cudaGetLastError();
+            ft->valid = false;
+            if (ce != cudaErrorMemoryAllocation) return fail(FGS_E_CUDA, std::string("filter tables: ") + cudaGetErrorString(ce));
+            ft->refused = true; // no room for the tables: the compare kernels need none
+        }
+        ft->node_gen = node_gen;
+        ft->filter_mask = fmask;
+    }
+    *use = ft->valid && ft_rows_fit(ft->v.W);
+    if (!*use && filter_mode == 2) return fail(FGS_E_STATE, "FGS_FILTER=lookup: the level tables exceed their memory limit for this node table");
     return FGS_OK;
 }
 
@@ -646,12 +728,16 @@ static int validate_node_table(Engine* e, const fgs_node_table* t) {
     if (t->n_scalars != e->S) return e->fail(FGS_E_INVALID, "node table: n_scalars differs from the engine's");
     if (t->n_devices < 1 || t->n_devices > FGS_MAX_DEVICES) return e->fail(FGS_E_TOO_LARGE, "node table: n_devices must be in [1, 16]");
     if (t->n_nodes >= ((int64_t)1 << 24) - 1) return e->fail(FGS_E_TOO_LARGE, "node table: at most 2^24-2 nodes per engine");
+    // the selectHost key carries the GLOBAL node index in 24 bits
+    if (e->node_base + t->n_nodes > ((int64_t)1 << 24) - 2) return e->fail(FGS_E_TOO_LARGE, "node table: node_index_base + n_nodes exceeds 2^24-2");
     return FGS_OK;
 }
 
 extern "C" int fgs_upload_nodes(fgs_engine* eh, const fgs_node_table* t) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_upload_nodes while submitted batches are in flight: fgs_collect them first");
     int rc = validate_node_table(e, t);
     if (rc) return rc;
     cudaSetDevice(e->device);
@@ -670,7 +756,9 @@ extern "C" int fgs_upload_nodes(fgs_engine* eh, const fgs_node_table* t) {
 extern "C" int fgs_update_nodes(fgs_engine* eh, const fgs_node_table* rows, const int64_t* dirty_idx) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_update_nodes before fgs_upload_nodes");
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_update_nodes while submitted batches are in flight: fgs_collect them first");
     int rc = validate_node_table(e, rows);
     if (rc) return rc;
     if (rows->n_devices > e->D) return e->fail(FGS_E_INVALID, "fgs_update_nodes: more device slots than the uploaded table; re-upload");
@@ -803,6 +891,7 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
 extern "C" int fgs_stage_pods(fgs_engine* eh, const fgs_pod_table* t) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_stage_pods while submitted batches are in flight: fgs_collect them first");
     return stage_pods_impl(e, t, false);
 }
@@ -854,23 +943,57 @@ int Engine::run_sampling(const fgs_eval_opts* opts) {
 extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_reduce before fgs_stage_pods");
     cudaSetDevice(e->device);
     e->sampled = false;
     e->was_fused = false;
     EvalParams p;
     e->fill_eval_params(&p, nullptr);
+    bool lookup = false;
+    {
+        const int rc = e->ensure_filter_tables(&lookup);
+        if (rc) return rc;
+    }
     launch_init_perpod((int64_t*)e->d_perpod, e->p_pad, e->stream);
     e->launches++;
     bool done = false;
+    e->reduce_was_lookup = lookup;
+    if (lookup) { // Filter by table look-up: one warp per pod ANDs the level rows of its values (filter_tables.cu)
+        FtRowsParams rp;
+        std::memset(&rp, 0, sizeof(rp));
+        rp.v = e->ft->v;
+        rp.pods = (const int64_t*)e->d_pods;
+        rp.nd = (const int64_t*)e->d_nd;
+        rp.n_pods = e->n_pods;
+        rp.p_pad = e->p_pad;
+        rp.n_nodes = e->n_nodes;
+        rp.n_pad = e->n_pad;
+        rp.S = e->S;
+        rp.fit_ignored = e->cfg.fit_ignored_scalar_mask;
+        rp.bitmap = (uint32_t*)e->d_bitmap;
+        rp.reduce_max = p.reduce_max;
+        rp.reduce_sum = p.reduce_sum;
+        rp.sc_flex = (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0;
+        rp.sc_alloc = (e->cfg.score_mask & FGS_PL_ALLOCATABLE) ? 1 : 0;
+        FGS_CUDA(e, ft_launch_rows(rp, e->stream));
+        e->launches++;
+        if ((e->cfg.filter_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
+            ft_launch_filter_panic((const int64_t*)e->d_nd, (const int64_t*)e->d_pods, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special,
+                                   e->n_pods, e->p_pad, e->S, e->cfg.filter_mask, e->cfg.fit_ignored_scalar_mask, p.flex_filter_first,
+                                   (int64_t*)e->d_perpod, e->stream);
+            e->launches++;
+        }
+    } else {
     if (e->narrow_batch) {
         NarrowParams np;
         e->fill_narrow_params(&np);
         done = launch_reduce_narrow(np, narrow_spec(e), e->stream);
     }
     if (!done) launch_eval_reduce(p, e->stream);
-    e->reduce_was_narrow = done;
     e->launches++;
+    }
+    e->reduce_was_narrow = done;
     if (done && (e->cfg.filter_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) { // the narrow loop leaves this flag to a side pass
         launch_filter_panic_pass((const int*)e->d_nn, (const int*)e->d_pn, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special, e->n_pods, e->p_pad,
                                  (e->cfg.filter_mask & FGS_PL_FIT) ? 1 : 0, p.flex_filter_first, (int64_t*)e->d_perpod, e->stream);
@@ -893,12 +1016,14 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
 extern "C" int fgs_fused_eligible(fgs_engine* eh, const fgs_eval_opts* opts) {
     if (!eh) return 0;
     Engine* e = (Engine*)eh;
+    FGS_ENTER_RET(e, 0);
     return e->have_pods && e->fused_eligible(opts) ? 1 : 0;
 }
 
 extern "C" int fgs_pass_fused(fgs_engine* eh, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_fused before fgs_stage_pods");
     if (!e->fused_eligible(opts)) return e->fail(FGS_E_STATE, "fgs_pass_fused: this batch / configuration needs the two passes (see fgs_fused_eligible)");
     return e->run_fused(opts, 3);
@@ -907,6 +1032,7 @@ extern "C" int fgs_pass_fused(fgs_engine* eh, const fgs_eval_opts* opts) {
 extern "C" int fgs_pass_fused_prepass(fgs_engine* eh, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_fused_prepass before fgs_stage_pods");
     if (!e->fused_eligible(opts)) return e->fail(FGS_E_STATE, "fgs_pass_fused_prepass: this batch / configuration needs the two passes (see fgs_fused_eligible)");
     return e->run_fused(opts, 1);
@@ -915,6 +1041,7 @@ extern "C" int fgs_pass_fused_prepass(fgs_engine* eh, const fgs_eval_opts* opts)
 extern "C" int fgs_pass_fused_main(fgs_engine* eh, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_fused_main before fgs_stage_pods");
     if (!e->fused_eligible(opts)) return e->fail(FGS_E_STATE, "fgs_pass_fused_main: this batch / configuration needs the two passes (see fgs_fused_eligible)");
     return e->run_fused(opts, 2);
@@ -923,6 +1050,7 @@ extern "C" int fgs_pass_fused_main(fgs_engine* eh, const fgs_eval_opts* opts) {
 extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_emit before fgs_stage_pods");
     cudaSetDevice(e->device);
     if (opts && opts->sample) { // keep only the nodes the reference's walk would have found
@@ -951,6 +1079,7 @@ extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
 extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
     if (!eh || !out) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_fetch_results before an evaluation");
     cudaSetDevice(e->device);
     const int64_t P = e->n_pods, pp = e->p_pad;
@@ -967,8 +1096,16 @@ extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
         FGS_CUDA(e, cudaMemcpyAsync(out->scores, e->d_scores, sizeof(int64_t) * P * e->score_stride, cudaMemcpyDeviceToHost, e->stream));
     if (e->sampled) // the walks: int2 {start, processed} per pod, then nextStartNodeIndex
         FGS_CUDA(e, cudaMemcpyAsync(e->h_walk, e->d_walk, sizeof(int64_t) * (size_t)(pp + 1), cudaMemcpyDeviceToHost, e->stream));
+    if (e->peer) {
+        const int rc = e->peer_fetch_error(Engine::kSlots, e->stream);
+        if (rc) return rc;
+    }
     FGS_CUDA(e, cudaEventRecord(e->events[4], e->stream));
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    {
+        const int rc = e->peer_check_error(Engine::kSlots); // a merge of this batch timed out: nothing to hand back
+        if (rc) return rc;
+    }
     out->next_start_node_index = -1;
     if (e->sampled) {
         out->next_start_node_index = ((const int64_t*)e->h_walk)[pp];
@@ -1001,6 +1138,7 @@ extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
 extern "C" int fgs_evaluate(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts, fgs_results* out) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     int rc = fgs_stage_pods(eh, pods);
     if (rc) return rc;
     e->emitted = false;
@@ -1034,6 +1172,7 @@ extern "C" int fgs_evaluate(fgs_engine* eh, const fgs_pod_table* pods, const fgs
 extern "C" int fgs_get_device_view(fgs_engine* eh, fgs_device_view* v) {
     if (!eh || !v) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_get_device_view before fgs_stage_pods");
     v->reduce_max = e->d_perpod;
     v->reduce_sum = (int64_t*)e->d_perpod + (int64_t)FGS_REDUCE_ROWS * e->p_pad;
@@ -1050,6 +1189,7 @@ extern "C" int fgs_get_device_view(fgs_engine* eh, fgs_device_view* v) {
 extern "C" int fgs_synchronize(fgs_engine* eh) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     cudaSetDevice(e->device);
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
     return FGS_OK;
@@ -1063,6 +1203,7 @@ extern "C" int fgs_get_timings(fgs_engine* eh, fgs_timings* t) {
     t->reduce_int32 = e->reduce_was_narrow ? 1 : 0;
     t->emit_int32 = e->emit_was_narrow ? 1 : 0;
     t->fused = e->was_fused ? 1 : 0;
+    t->reduce_lookup = e->reduce_was_lookup ? 1 : 0;
     return FGS_OK;
 }
 
@@ -1149,6 +1290,10 @@ int Engine::issue_emit_sharded(int j) {
         FGS_CUDA(e, cudaEventRecord(sl.ev_merge2, merge_stream));
         FGS_CUDA(e, cudaStreamWaitEvent(d2h_stream, sl.ev_merge2, 0));
         FGS_CUDA(e, cudaMemcpyAsync(h_perpod, d_compact, sizeof(int64_t) * 4 * p_pad, cudaMemcpyDeviceToHost, d2h_stream));
+        {
+            const int rc2 = peer_fetch_error(j, d2h_stream);
+            if (rc2) return rc2;
+        }
         FGS_CUDA(e, cudaEventRecord(sl.ev_done, d2h_stream));
         sl.emit_pending = false;
         return FGS_OK;
@@ -1167,6 +1312,15 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
     if (resident) {
         if (!have_pods) return fail(FGS_E_STATE, "fgs_resubmit: no batch is resident in this pipeline slot (fgs_submit fills the slots in turn)");
     } else {
+        // A batch larger than any before makes ensure_pods replace the bitmap / score planes, which the emit pass of the
+        // previous batch has still to read: issue that pass first and let everything in flight drain.
+        if (pods && in_flight > 0 && round_up(std::max<int64_t>(pods->n_pods, 1), kTileP) > p_plane_cap) {
+            if (newest >= 0 && slots[newest].emit_pending) {
+                const int rc = issue_emit_sharded(newest);
+                if (rc) return rc;
+            }
+            FGS_CUDA(e, cudaDeviceSynchronize());
+        }
         const int rc = stage_pods_impl(e, pods, true);
         if (rc) return rc;
     }
@@ -1207,6 +1361,7 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
 extern "C" int fgs_resubmit(fgs_engine* eh, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->peer) return e->fail(FGS_E_STATE, "fgs_resubmit: only with a peer group attached (fgs_peer_attach)");
     if (e->in_flight >= 3) return e->fail(FGS_E_STATE, "fgs_resubmit: three batches are in flight already; fgs_collect one first");
     if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_resubmit: nominated pods are set: use fgs_evaluate");
@@ -1220,6 +1375,7 @@ extern "C" int fgs_resubmit(fgs_engine* eh, const fgs_eval_opts* opts) {
 extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (e->in_flight >= e->ring())
         return e->fail(FGS_E_STATE, e->ring() == 3 ? "fgs_submit: three batches are in flight already; fgs_collect one first"
                                                    : "fgs_submit: two batches are in flight already; fgs_collect one first");
@@ -1266,6 +1422,7 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
 extern "C" int fgs_collect(fgs_engine* eh, fgs_results* out) {
     if (!eh || !out) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (e->in_flight == 0) return e->fail(FGS_E_STATE, "fgs_collect: nothing was submitted");
     cudaSetDevice(e->device);
     const int k = e->oldest_slot;
@@ -1274,6 +1431,15 @@ extern "C" int fgs_collect(fgs_engine* eh, fgs_results* out) {
         if (rc) return rc;
     }
     FGS_CUDA(e, cudaEventSynchronize(e->slots[k].ev_done));
+    if (e->peer) { // a merge of this batch timed out: drop the batch, report
+        const int rc = e->peer_check_error(k);
+        if (rc) {
+            e->slots[k].busy = false;
+            e->in_flight--;
+            e->oldest_slot = (k + 1) % e->ring();
+            return rc;
+        }
+    }
     // the oldest batch's host buffer: the members alias slot cur_slot, the other slot keeps its own copy
     const bool is_cur = k == e->cur_slot;
     const int64_t P = is_cur ? e->n_pods : e->slots[k].n_pods, pp = is_cur ? e->p_pad : e->slots[k].p_pad;

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <string>
 
 #include "../../include/fgs.h"
@@ -16,6 +17,7 @@ constexpr int kCompactRow0 = FGS_REDUCE_ROWS + 1 + 3;
 constexpr int kPerPodRows = kCompactRow0 + 4;
 
 struct GangState; // gang_quota.cu
+struct FilterTables; // filter_tables.cuh
 struct SeqState;  // sequential.cu
 
 struct Engine {
@@ -111,6 +113,8 @@ struct Engine {
     void* d_bitmap_alt = nullptr;
     size_t bitmap_alt_bytes = 0;
     int peer_merge(int which, cudaStream_t on, bool overlapped = false); // peer_merge.cu
+    int peer_fetch_error(int slot, cudaStream_t on); // copy of the merge error word, behind the merges on `on`
+    int peer_check_error(int slot);                  // FGS_E_STATE when that copy says a merge timed out
     int submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident);
     int issue_emit_sharded(int slot);
 
@@ -132,6 +136,14 @@ struct Engine {
     bool sampled = false;      // the current batch's bitmap was truncated by the walk
     int run_sampling(const fgs_eval_opts* opts);
 
+    // pass A as table look-ups (filter_tables.cu): level tables of the node side of the filters, rebuilt lazily when the
+    // node table or the filter plugins change. FGS_FILTER=compare forces the compare kernels, =lookup refuses to fall back.
+    FilterTables* ft = nullptr;
+    int filter_mode = 0; // 0 auto (look-up when the tables fit), 1 compare kernels only, 2 look-up only (tests)
+    bool reduce_was_lookup = false;
+    int ensure_filter_tables(bool* use);
+    void ft_free();
+
     GangState* gang = nullptr;
     SeqState* seq = nullptr;
     struct PeerState* peer = nullptr; // peer_merge.cu: the other shards' exchange buffers
@@ -140,6 +152,11 @@ struct Engine {
 
     fgs_timings tm = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     int64_t launches = 0;
+
+    // one caller at a time: the thread inside an entry point owns the engine (entry points call each other, so the
+    // ownership nests); a second thread gets FGS_E_STATE instead of corrupting the staging slots
+    std::atomic<uint64_t> owner{0};
+    int owner_depth = 0;
 
     int fail(int code, const std::string& msg);
     int ensure_nodes(int64_t n, int D);
@@ -155,5 +172,17 @@ struct Engine {
     int derive_now();        // derive_node_columns over the whole table + analysis
     int analyze_nodes_now(); // node-side analysis for the int32 specialisation (after any change of d_nd)
 };
+
+// first statement of every entry point that takes an engine
+struct EngineEntry {
+    Engine* e;
+    bool ok;
+    explicit EngineEntry(Engine* e_);
+    ~EngineEntry();
+};
+#define FGS_ENTER_RET(e, ret)      \
+    fgs::EngineEntry _entry(e);    \
+    if (!_entry.ok) return (ret)
+#define FGS_ENTER(e) FGS_ENTER_RET(e, FGS_E_STATE)
 
 } // namespace fgs

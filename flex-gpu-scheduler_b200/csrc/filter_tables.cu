@@ -1,0 +1,481 @@
+// filter_tables.cu — pass A by table look-up (see filter_tables.cuh for the idea).
+//
+//   ft_build            node side, once per change of the node table: effective thresholds per dimension →
+//                       radix sort → distinct levels + the rank of every node → bit rows T_d[r]; node orders by
+//                       GPUScore / MemScore / Allocatable raw score.
+//   filter_rows         pod side, per batch, ONE WARP PER POD: rank of the pod's value in every dimension (binary search
+//                       in the levels), AND of the 5+S rows → the pod's bitmap row, popcount → len(feasibleNodes);
+//                       DefaultNormalizeScore's maximum (normalize_score.go:27-35) and Allocatable's hi / lo
+//                       (allocatable.go:146-159) are the score of the FIRST feasible node in score order — a raw score
+//                       depends on the node and the pod's kind only (flex_gpu.go:153-165, gpu_node.go:179-199).
+//
+// The verdicts are those of eval_kernel<REDUCE> (kernels.cu) bit for bit: the same int64 thresholds, compared through
+// their ranks. Reads of the tables are this GPU's own memory only.
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdint>
+
+#include "filter_tables.cuh"
+#include "kernels.cuh"
+
+namespace fgs {
+
+namespace {
+
+typedef int64_t i64;
+typedef uint64_t u64;
+constexpr i64 kMin = (i64)0x8000000000000000ull;
+constexpr i64 kMax = (i64)0x7fffffffffffffffull;
+// sentinels below every real quantity (|v| < 2^53, fgs_types.h):
+constexpr i64 kLow0 = kMin;     // node side: the row takes no pod at all
+constexpr i64 kLow1 = kMin + 1; // pod side: "no limit / no request" — passes wherever the node takes anything
+constexpr i64 kLow2 = kMin + 2; // node side: takes only the pods without a value in this dimension
+
+// ---- node side ---------------------------------------------------------------------------------------------------
+
+// thr[d][n]: what a pod's value in dimension d must not exceed on node n; keys of the three score orders behind them
+__global__ void __launch_bounds__(256) ft_thresholds(const i64* __restrict__ nd, i64 n_nodes, i64 n_pad, int S, uint32_t filter_mask,
+                                                     i64* __restrict__ thr, i64 stride) {
+    const i64 n = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= n_pad) return;
+    const int n_dims = 5 + S;
+    auto C = [&](int c) { return nd[(i64)c * n_pad + n]; };
+    const uint32_t fl = (uint32_t)C(ND_FLAGS);
+    const bool valid = n < n_nodes && (fl & FGS_NF_VALID);
+    const bool flex_f = filter_mask & FGS_PL_FLEXGPU, fit_f = filter_mask & FGS_PL_FIT;
+    // FlexGPU.Filter: limit <= per-kind threshold; a node on which NewGPUNode would panic takes no pod that carries a
+    // flex limit (which pods REACH the panic is ft_filter_panic's business) but every pod without one
+    auto flex_thr = [&](i64 t) -> i64 {
+        if (!valid) return kLow0; // a row that is not a node takes nothing, whichever filters run
+        if (!flex_f) return kMax;
+        if ((fl & FGS_NF_REF_PANIC) || t == kMin) return kLow2;
+        return t;
+    };
+    thr[(i64)FT_GPU * stride + n] = flex_thr(C(ND_THR_GPU));
+    thr[(i64)FT_FMEM * stride + n] = flex_thr(C(ND_THR_MEM));
+    // Fit.Filter: "Too many pods" (fit.go:259) rejects every pod, then request <= Allocatable − Requested per resource
+    thr[(i64)FT_CPU * stride + n] = !fit_f ? kMax : (!(fl & NDF_PODS_OK) ? kLow0 : C(ND_FREE_CPU));
+    thr[(i64)FT_MEM * stride + n] = !fit_f ? kMax : C(ND_FREE_MEM);
+    thr[(i64)FT_EPH * stride + n] = !fit_f ? kMax : C(ND_FREE_EPH);
+    for (int s = 0; s < S; ++s) thr[(i64)(FT_SCALAR0 + s) * stride + n] = !fit_f ? kMax : C(nd_free_scalar(s));
+    thr[(i64)(n_dims + FT_ORD_GSCORE) * stride + n] = C(ND_GPU_SCORE);
+    thr[(i64)(n_dims + FT_ORD_MSCORE) * stride + n] = C(ND_MEM_SCORE);
+    thr[(i64)(n_dims + FT_ORD_ARAW) * stride + n] = C(ND_ALLOC_RAW);
+}
+
+__global__ void __launch_bounds__(256) ft_iota(int* v, i64 n) {
+    const i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = (int)i;
+}
+
+__global__ void __launch_bounds__(256) ft_heads(const i64* __restrict__ ks, i64 n, int* __restrict__ head) {
+    const i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) head[i] = (i == 0 || ks[i] != ks[i - 1]) ? 1 : 0;
+}
+
+// sorted position i → rank = (number of distinct keys up to i) − 1; levels[rank] = the key; node_rank[node] = rank
+__global__ void __launch_bounds__(256) ft_scatter(const i64* __restrict__ ks, const int* __restrict__ perm, const int* __restrict__ head,
+                                                  const int* __restrict__ scan, i64 n, i64* __restrict__ levels, int* __restrict__ node_rank,
+                                                  int* __restrict__ count) {
+    const i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int r = scan[i] - 1;
+    node_rank[perm[i]] = r;
+    if (head[i]) levels[r] = ks[i];
+    if (i == n - 1) *count = scan[i];
+}
+
+// T_d[r][w] = bits of the nodes 32w..32w+31 whose rank in dimension d is >= r, for r = 0..R_d (row R_d is empty).
+// One CTA = 32 consecutive words × 8 rows at a time; a thread keeps the 32 ranks of its word in registers.
+constexpr int kFtRowsPerCta = 64;
+struct FtTabParams {
+    uint32_t* table;
+    const int* node_rank; // [n_dims][stride]
+    i64 stride, W;
+    i64 row0[kFtMaxDims];
+    int R[kFtMaxDims];
+};
+__global__ void __launch_bounds__(256) ft_fill_rows(const __grid_constant__ FtTabParams prm) {
+    const int d = blockIdx.z;
+    const int R = prm.R[d];
+    const int r_begin = blockIdx.y * kFtRowsPerCta;
+    if (r_begin > R) return;
+    const i64 w = (i64)blockIdx.x * 32 + (threadIdx.x & 31);
+    if (w >= prm.W) return;
+    int rk[32];
+    const int4* src = (const int4*)(prm.node_rank + (i64)d * prm.stride + w * 32);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const int4 v = __ldg(src + q);
+        rk[4 * q] = v.x, rk[4 * q + 1] = v.y, rk[4 * q + 2] = v.z, rk[4 * q + 3] = v.w;
+    }
+    const int r_end = min(R, r_begin + kFtRowsPerCta - 1);
+    for (int r = r_begin + (threadIdx.x >> 5); r <= r_end; r += 8) {
+        uint32_t word = 0;
+#pragma unroll
+        for (int b = 0; b < 32; ++b) word |= (rk[b] >= r ? 1u : 0u) << b;
+        prm.table[(prm.row0[d] + r) * prm.W + w] = word;
+    }
+}
+
+// ---- pod side ----------------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ i64 warp_max_i64(i64 v) {
+    const int hi = (int)(v >> 32);
+    const int mhi = __reduce_max_sync(0xffffffffu, hi);
+    const uint32_t mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? (uint32_t)v : 0u);
+    return (i64)(((u64)(uint32_t)mhi << 32) | mlo);
+}
+
+constexpr int kWalkChunks = 24; // order walk: 32 nodes per step; after this many empty steps the set bits are scanned instead
+
+// value of the first feasible node in an order (front) or of the last one (back); `row` = the pod's bitmap row in shared memory
+__device__ __forceinline__ bool walk_order(const int* __restrict__ ord, const i64* __restrict__ val, i64 n_nodes, const uint32_t* row, int lane,
+                                           bool from_back, i64* out) {
+    for (int step = 0; step < kWalkChunks; ++step) {
+        const i64 k0 = (i64)step * 32 + lane;
+        if ((i64)step * 32 >= n_nodes) return false;
+        const i64 k = from_back ? n_nodes - 1 - k0 : k0;
+        bool ok = false;
+        if (k0 < n_nodes) {
+            const int n = __ldg(ord + k);
+            ok = (row[n >> 5] >> (n & 31)) & 1u;
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+        if (bal) {
+            const i64 kf = (i64)step * 32 + (__ffs(bal) - 1);
+            *out = __ldg(val + (from_back ? n_nodes - 1 - kf : kf));
+            return true;
+        }
+    }
+    return false;
+}
+
+// the slow way round, bounded by the number of feasible nodes: max of col[n] (or of −col[n]) over the set bits
+__device__ __forceinline__ i64 scan_bits(const uint32_t* row, i64 W, const i64* __restrict__ col, int lane, bool negate) {
+    i64 best = kMin;
+    for (i64 w = lane; w < W; w += 32) {
+        uint32_t x = row[w];
+        while (x) {
+            const int bit = __ffs(x) - 1;
+            x &= x - 1;
+            const i64 v = __ldg(col + w * 32 + bit);
+            const i64 c = negate ? -v : v;
+            best = c > best ? c : best;
+        }
+    }
+    return warp_max_i64(best);
+}
+
+constexpr int kRowsWarps = 8;
+
+template <int NDIMS> // 0 = any number of dimensions (S > 2)
+__global__ void __launch_bounds__(kRowsWarps * 32) filter_rows(const __grid_constant__ FtRowsParams prm) {
+    extern __shared__ __align__(16) uint32_t s_rows[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const i64 p = (i64)blockIdx.x * kRowsWarps + warp;
+    if (p >= prm.n_pods) return;
+    const int n_dims = NDIMS ? NDIMS : prm.v.n_dims;
+    const i64 W = prm.v.W;
+    uint32_t* row = s_rows + (size_t)warp * W;
+
+    // ---- the pod's value and its rank in every dimension: lane d owns dimension d ---------------------------------
+    const u64 meta = (u64)__ldg(prm.pods + (i64)PD_META * prm.p_pad + p);
+    const uint32_t pf = (uint32_t)meta, kind = pf & 3u;
+    const bool none = pf & FGS_PF_REQ_NONE;
+    const uint32_t smask = (uint32_t)(meta >> 32) & ~prm.fit_ignored;
+    i64 rowoff = 0; // (row0[d] + rank) · W
+    if (lane < n_dims) {
+        const int d = lane;
+        auto P = [&](int c) { return __ldg(prm.pods + (i64)c * prm.p_pad + p); };
+        i64 v;
+        if (d == FT_GPU) v = kind == 1 ? P(PD_GPU_LIM) : (kind == 3 ? kMax : kLow1);      // both limits: flex_gpu.go:58-61
+        else if (d == FT_FMEM) v = kind == 2 ? P(PD_MEM_LIM) : (kind == 3 ? kMax : kLow1);
+        else if (d == FT_CPU) v = none ? kLow1 : P(PD_REQ_CPU);                            // fit.go:270-275
+        else if (d == FT_MEM) v = none ? kLow1 : P(PD_REQ_MEM);
+        else if (d == FT_EPH) v = none ? kLow1 : P(PD_REQ_EPH);
+        else v = (none || !((smask >> (d - FT_SCALAR0)) & 1u)) ? kLow1 : P(PD_FIXED_COLS + (d - FT_SCALAR0));
+        const i64* lev = prm.v.levels + (i64)d * prm.v.lev_stride;
+        int lo = 0, hi = prm.v.R[d];
+        while (lo < hi) { // lower bound: the number of levels below v
+            const int mid = (lo + hi) >> 1;
+            if (__ldg(lev + mid) < v) lo = mid + 1;
+            else hi = mid;
+        }
+        rowoff = (prm.v.row0[d] + lo) * W;
+    }
+
+    // ---- the row: AND over the dimensions, 32 words per step ------------------------------------------------------
+    uint32_t cnt = 0;
+    uint32_t* out = prm.bitmap + p * W;
+    if (NDIMS) {
+        const uint32_t* rp[NDIMS ? NDIMS : 1];
+#pragma unroll
+        for (int d = 0; d < NDIMS; ++d) rp[d] = prm.v.table + __shfl_sync(0xffffffffu, rowoff, d);
+        for (i64 w = lane; w < W; w += 32) {
+            uint32_t x[NDIMS ? NDIMS : 1];
+#pragma unroll
+            for (int d = 0; d < NDIMS; ++d) x[d] = __ldg(rp[d] + w);
+            uint32_t a = x[0];
+#pragma unroll
+            for (int d = 1; d < NDIMS; ++d) a &= x[d];
+            row[w] = a;
+            out[w] = a;
+            cnt += (uint32_t)__popc(a);
+        }
+    } else {
+        for (i64 w = lane; w < W; w += 32) {
+            uint32_t a = 0xffffffffu;
+            for (int d = 0; d < n_dims; ++d) a &= __ldg(prm.v.table + __shfl_sync(0xffffffffu, rowoff, d) + w);
+            row[w] = a;
+            out[w] = a;
+            cnt += (uint32_t)__popc(a);
+        }
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    __syncwarp();
+
+    // ---- what NormalizeScore needs: the best raw scores among the feasible nodes ------------------------------------
+    i64 vflex = kMin, vhi = kMin, vnlo = kMin;
+    if (cnt > 0) {
+        if (prm.sc_flex) { // raw FlexGPU score by pod kind (flex_gpu.go:153-165); a gpu limit wins over a memory limit
+            if (kind == 0) {
+                vflex = 0;
+            } else {
+                const int o = (kind & 1u) ? FT_ORD_GSCORE : FT_ORD_MSCORE;
+                if (!walk_order(prm.v.ord + (i64)o * prm.n_pad, prm.v.ord_val + (i64)o * prm.n_pad, prm.n_nodes, row, lane, false, &vflex))
+                    vflex = scan_bits(row, W, prm.nd + (i64)((kind & 1u) ? ND_GPU_SCORE : ND_MEM_SCORE) * prm.n_pad, lane, false);
+            }
+        }
+        if (prm.sc_alloc) {
+            const int* ord = prm.v.ord + (i64)FT_ORD_ARAW * prm.n_pad;
+            const i64* val = prm.v.ord_val + (i64)FT_ORD_ARAW * prm.n_pad;
+            const i64* col = prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad;
+            if (!walk_order(ord, val, prm.n_nodes, row, lane, false, &vhi)) vhi = scan_bits(row, W, col, lane, false);
+            i64 lo;
+            if (walk_order(ord, val, prm.n_nodes, row, lane, true, &lo)) vnlo = -lo;
+            else vnlo = scan_bits(row, W, col, lane, true);
+        }
+    }
+    if (lane == 0) {
+        prm.reduce_sum[p] = (i64)cnt;
+        prm.reduce_max[(i64)RR_FLEX_MAX * prm.p_pad + p] = vflex;
+        prm.reduce_max[(i64)RR_ALLOC_HI * prm.p_pad + p] = vhi;
+        prm.reduce_max[(i64)RR_ALLOC_NEGLO * prm.p_pad + p] = vnlo;
+    }
+}
+
+// Which pods would make the reference panic inside FlexGPU.Filter (see filter_panic_pass in kernels_narrow.cu): a pod
+// with ONE flex limit that passes the limit-sum checks (flex_gpu.go:85-98) on a node whose device state makes NewGPUNode
+// panic (:101, gpu_node.go:40-58,109,115) and, when NodeResourcesFit runs first, passes Fit too (runtime/framework.go:667-693).
+__global__ void __launch_bounds__(128) ft_filter_panic(const i64* __restrict__ nd, const i64* __restrict__ pods, const i64* __restrict__ special,
+                                                       i64 n_pad, int n_special, i64 n_pods, i64 p_pad, int S, uint32_t filter_mask,
+                                                       uint32_t fit_ignored, int flex_first, i64* __restrict__ reduce_max) {
+    const i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    auto P = [&](int c) { return pods[(i64)c * p_pad + p]; };
+    const u64 meta = (u64)P(PD_META);
+    const uint32_t pf = (uint32_t)meta, kind = pf & 3u;
+    if (kind != 1 && kind != 2) return;
+    const i64 lim = kind == 1 ? P(PD_GPU_LIM) : P(PD_MEM_LIM);
+    const bool none = pf & FGS_PF_REQ_NONE;
+    const uint32_t smask = (uint32_t)(meta >> 32) & ~fit_ignored;
+    const bool fit_first = (filter_mask & FGS_PL_FIT) && !flex_first;
+    for (int k = 0; k < n_special; ++k) {
+        const i64 e = special[k];
+        if (!(e >> 40)) continue;
+        const i64 n = e & 0xffffffffll;
+        auto C = [&](int c) { return nd[(i64)c * n_pad + n]; };
+        const uint32_t fl = (uint32_t)C(ND_FLAGS);
+        if (!(fl & FGS_NF_VALID)) continue;
+        if (!(lim <= C(kind == 1 ? ND_THR_GPU : ND_THR_MEM))) continue;
+        if (fit_first) {
+            bool fit_ok = fl & NDF_PODS_OK;
+            if (fit_ok && !none) {
+                fit_ok = P(PD_REQ_CPU) <= C(ND_FREE_CPU) && P(PD_REQ_MEM) <= C(ND_FREE_MEM) && P(PD_REQ_EPH) <= C(ND_FREE_EPH);
+                for (int s = 0; s < S && fit_ok; ++s)
+                    if (((smask >> s) & 1u) && P(PD_FIXED_COLS + s) > C(nd_free_scalar(s))) fit_ok = false;
+            }
+            if (!fit_ok) continue;
+        }
+        reduce_max[(i64)RR_FILTER_PANIC * p_pad + p] = 1;
+        return;
+    }
+}
+
+cudaError_t grow(void** p, size_t bytes) {
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    return cudaMalloc(p, bytes);
+}
+
+} // namespace
+
+void FilterTables::free_all() {
+    for (void** p : {&d_table, &d_levels, &d_node_rank, &d_ord, &d_ord_val, &d_thr, &d_sort, &d_counts})
+        if (*p) {
+            cudaFree(*p);
+            *p = nullptr;
+        }
+    table_bytes = sort_bytes = 0;
+    n_cap = 0;
+    dims_cap = 0;
+    valid = false;
+}
+
+#define FT_TRY(call)                      \
+    do {                                  \
+        cudaError_t _e = (call);          \
+        if (_e != cudaSuccess) return _e; \
+    } while (0)
+
+cudaError_t ft_build(FilterTables* ft, const FtBuildParams& bp, cudaStream_t st, int64_t* launches) {
+    ft->valid = false;
+    ft->refused = false;
+    const i64 n = bp.n_pad, n_nodes = bp.n_nodes;
+    const int n_dims = 5 + bp.S;
+    if (n <= 0 || n_nodes <= 0) return cudaSuccess;
+    if (n > ((i64)1 << 22)) { // (R+1) · n/8 bytes per dimension: beyond any sensible table long before this
+        ft->refused = true;
+        return cudaSuccess;
+    }
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEventCreate(&ev0);
+    cudaEventCreate(&ev1);
+    cudaEventRecord(ev0, st);
+    // ---- buffers --------------------------------------------------------------------------------------------------
+    size_t tmp_sort = 0, tmp_scan = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp_sort, (const i64*)nullptr, (i64*)nullptr, (const int*)nullptr, (int*)nullptr, (int)n);
+    cub::DeviceScan::InclusiveSum(nullptr, tmp_scan, (const int*)nullptr, (int*)nullptr, (int)n);
+    const size_t tmp_bytes = (std::max(tmp_sort, tmp_scan) + 255) / 256 * 256;
+    const size_t n8 = (size_t)n * 8, n4 = ((size_t)n * 4 + 255) / 256 * 256;
+    const size_t need_sort = n8 /*keys out*/ + 4 * n4 /*iota, perm, head, scan*/ + tmp_bytes;
+    if (n > ft->n_cap || n_dims > ft->dims_cap) {
+        ft->n_cap = std::max(n, ft->n_cap);
+        ft->dims_cap = std::max(n_dims, ft->dims_cap);
+        const size_t nc = (size_t)ft->n_cap, dc = (size_t)ft->dims_cap;
+        FT_TRY(grow(&ft->d_levels, sizeof(i64) * dc * (nc + 1)));
+        FT_TRY(grow(&ft->d_node_rank, sizeof(int) * dc * nc));
+        FT_TRY(grow(&ft->d_ord, sizeof(int) * FT_ORDERS * nc));
+        FT_TRY(grow(&ft->d_ord_val, sizeof(i64) * FT_ORDERS * nc));
+        FT_TRY(grow(&ft->d_thr, sizeof(i64) * (dc + FT_ORDERS) * nc));
+        if (!ft->d_counts) FT_TRY(cudaMalloc(&ft->d_counts, sizeof(int) * kFtMaxDims));
+    }
+    if (need_sort > ft->sort_bytes) {
+        FT_TRY(grow(&ft->d_sort, need_sort));
+        ft->sort_bytes = need_sort;
+    }
+    const i64 stride = ft->n_cap;
+    i64* thr = (i64*)ft->d_thr;
+    char* sp = (char*)ft->d_sort;
+    i64* keys_out = (i64*)sp;
+    int* iota = (int*)(sp + n8);
+    int* perm = (int*)(sp + n8 + n4);
+    int* head = (int*)(sp + n8 + 2 * n4);
+    int* scan = (int*)(sp + n8 + 3 * n4);
+    void* tmp = sp + n8 + 4 * n4;
+    size_t tb = tmp_bytes;
+    const unsigned nb = (unsigned)((n + 255) / 256);
+
+    ft_thresholds<<<nb, 256, 0, st>>>(bp.nd, n_nodes, n, bp.S, bp.filter_mask, thr, stride);
+    ft_iota<<<nb, 256, 0, st>>>(iota, n);
+    *launches += 2;
+    for (int d = 0; d < n_dims; ++d) {
+        FT_TRY(cub::DeviceRadixSort::SortPairs(tmp, tb, (const i64*)(thr + (i64)d * stride), keys_out, (const int*)iota, perm, (int)n, 0, 64, st));
+        ft_heads<<<nb, 256, 0, st>>>(keys_out, n, head);
+        FT_TRY(cub::DeviceScan::InclusiveSum(tmp, tb, (const int*)head, scan, (int)n, st));
+        ft_scatter<<<nb, 256, 0, st>>>(keys_out, perm, head, scan, n, (i64*)ft->d_levels + (i64)d * (stride + 1), (int*)ft->d_node_rank + (i64)d * stride,
+                                       (int*)ft->d_counts + d);
+        *launches += 2;
+    }
+    // node orders, highest score first (nodes only: padding rows are never feasible)
+    for (int o = 0; o < FT_ORDERS; ++o) {
+        FT_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tb, (const i64*)(thr + (i64)(n_dims + o) * stride), (i64*)ft->d_ord_val + (i64)o * stride,
+                                                         (const int*)iota, (int*)ft->d_ord + (i64)o * stride, (int)n_nodes, 0, 64, st));
+    }
+    int counts[kFtMaxDims] = {0};
+    FT_TRY(cudaMemcpyAsync(counts, ft->d_counts, sizeof(int) * n_dims, cudaMemcpyDeviceToHost, st));
+    FT_TRY(cudaStreamSynchronize(st));
+    // ---- the table ------------------------------------------------------------------------------------------------------
+    FtView& v = ft->v;
+    v.n_dims = n_dims;
+    v.W = n / 32;
+    v.lev_stride = stride + 1;
+    i64 rows = 0;
+    int rmax = 0;
+    for (int d = 0; d < n_dims; ++d) {
+        v.R[d] = counts[d];
+        v.row0[d] = rows;
+        rows += (i64)counts[d] + 1;
+        rmax = std::max(rmax, counts[d]);
+    }
+    ft->rows_total = rows;
+    const size_t need = (size_t)rows * (size_t)v.W * 4;
+    if (need > ft->limit_bytes) {
+        ft->refused = true;
+        cudaEventDestroy(ev0);
+        cudaEventDestroy(ev1);
+        return cudaSuccess;
+    }
+    if (need > ft->table_bytes) {
+        FT_TRY(grow(&ft->d_table, need));
+        ft->table_bytes = need;
+    }
+    FtTabParams tp;
+    tp.table = (uint32_t*)ft->d_table;
+    tp.node_rank = (const int*)ft->d_node_rank;
+    tp.stride = stride;
+    tp.W = v.W;
+    for (int d = 0; d < kFtMaxDims; ++d) {
+        tp.row0[d] = d < n_dims ? v.row0[d] : 0;
+        tp.R[d] = d < n_dims ? v.R[d] : -1;
+    }
+    const dim3 grid((unsigned)((v.W + 31) / 32), (unsigned)(rmax / kFtRowsPerCta + 1), (unsigned)n_dims);
+    ft_fill_rows<<<grid, 256, 0, st>>>(tp);
+    *launches += 1;
+    FT_TRY(cudaGetLastError());
+    v.table = (const uint32_t*)ft->d_table;
+    v.levels = (const i64*)ft->d_levels;
+    v.ord = (const int*)ft->d_ord;
+    v.ord_val = (const i64*)ft->d_ord_val;
+    ft->n_pad = n;
+    ft->n_nodes = n_nodes;
+    cudaEventRecord(ev1, st);
+    cudaEventSynchronize(ev1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    ft->build_ms = ms;
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    ft->valid = true;
+    return cudaSuccess;
+}
+
+bool ft_rows_fit(int64_t W) { return (size_t)W * 4 * kRowsWarps <= 200 * 1024; }
+
+cudaError_t ft_launch_rows(const FtRowsParams& p, cudaStream_t st) {
+    if (p.n_pods <= 0) return cudaSuccess;
+    const size_t smem = (size_t)p.v.W * 4 * kRowsWarps;
+    const unsigned grid = (unsigned)((p.n_pods + kRowsWarps - 1) / kRowsWarps);
+    if (p.v.n_dims == 7) {
+        if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(filter_rows<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        filter_rows<7><<<grid, kRowsWarps * 32, smem, st>>>(p);
+    } else {
+        if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(filter_rows<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        filter_rows<0><<<grid, kRowsWarps * 32, smem, st>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+void ft_launch_filter_panic(const int64_t* nd, const int64_t* pods, const int64_t* special, int64_t n_pad, int n_special, int64_t n_pods,
+                            int64_t p_pad, int S, uint32_t filter_mask, uint32_t fit_ignored, int flex_first, int64_t* reduce_max,
+                            cudaStream_t st) {
+    if (n_special <= 0 || n_pods <= 0) return;
+    ft_filter_panic<<<(unsigned)((n_pods + 127) / 128), 128, 0, st>>>((const i64*)nd, (const i64*)pods, (const i64*)special, n_pad, n_special, n_pods,
+                                                                     p_pad, S, filter_mask, fit_ignored, flex_first, (i64*)reduce_max);
+}
+
+} // namespace fgs

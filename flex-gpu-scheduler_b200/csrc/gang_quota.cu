@@ -583,6 +583,7 @@ using namespace fgs;
 extern "C" int fgs_reason_plane(fgs_engine* eh, uint32_t plugin, uint16_t* out) {
     if (!eh || !out) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_reason_plane before an evaluation");
     if (plugin != FGS_PL_FLEXGPU && plugin != FGS_PL_FIT) return e->fail(FGS_E_INVALID, "fgs_reason_plane: plugin must be FlexGPU or Fit");
     cudaSetDevice(e->device);
@@ -623,6 +624,7 @@ extern "C" int fgs_reason_plane(fgs_engine* eh, uint32_t plugin, uint16_t* out) 
 extern "C" int fgs_status_plane(fgs_engine* eh, uint32_t plugin, uint8_t* out) {
     if (!eh || !out) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_status_plane before an evaluation");
     if (plugin != 0 && plugin != FGS_PL_FLEXGPU && plugin != FGS_PL_FIT) return e->fail(FGS_E_INVALID, "fgs_status_plane: plugin must be 0, FlexGPU or Fit");
     cudaSetDevice(e->device);
@@ -670,6 +672,7 @@ extern "C" int fgs_gang_check(fgs_engine* eh, const fgs_snapshot* snap, const fg
                               uint8_t* prefilter_code, uint8_t* permit_status, int32_t* assigned) {
     if (!eh || !snap || !pending || !pgs) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_gang_check before fgs_upload_nodes");
     if (snap->n_nodes != e->n_nodes) return e->fail(FGS_E_INVALID, "fgs_gang_check: snapshot does not match the uploaded node table");
     if (snap->n_scalars != e->S || pgs->n_scalars != e->S) return e->fail(FGS_E_INVALID, "fgs_gang_check: n_scalars mismatch");
@@ -804,6 +807,7 @@ extern "C" int fgs_quota_check(fgs_engine* eh, const fgs_pod_table* pods, const 
                                const int64_t* pod_uid, const int64_t* nominated_uid, uint8_t* code) {
     if (!eh || !pods || !q || !code) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (pods->n_scalars != e->S || q->n_scalars != e->S) return e->fail(FGS_E_INVALID, "fgs_quota_check: n_scalars mismatch");
     if (nominated && nominated->n_scalars != e->S) return e->fail(FGS_E_INVALID, "fgs_quota_check: nominated n_scalars mismatch");
     cudaSetDevice(e->device);
@@ -1001,6 +1005,7 @@ extern "C" int fgs_quota_check_static(void* stream, int32_t n_scalars, int64_t n
 extern "C" int fgs_fit_error_histogram(fgs_engine* eh, int32_t* counts) {
     if (!eh || !counts) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_fit_error_histogram before an evaluation");
     if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_fit_error_histogram while submitted batches are in flight");
     cudaSetDevice(e->device);

@@ -250,6 +250,8 @@ using namespace fgs;
 extern "C" int fgs_set_nominated(fgs_engine* eh, const fgs_pod_table* pods, const int32_t* node, const int64_t* uid) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_set_nominated while submitted batches are in flight: fgs_collect them first");
     cudaSetDevice(e->device);
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
     e->nom_q = e->nom_m = 0;

@@ -88,8 +88,12 @@ __device__ __forceinline__ void mc_st(i64* p, i64 v) { asm volatile("multimem.st
 __device__ __forceinline__ u64* flag_of(char* base, int cta, int src) { return (u64*)(base + 4096) + (i64)cta * kMaxRanks + src; }
 __device__ __forceinline__ i64* region_of(char* base, i64 region, int k) { return (i64*)(base + kHeaderBytes) + (i64)k * region; }
 
-// all writes of this CTA → visible to CTA `blockIdx.x` of every peer once it has seen `value`; and the converse
-__device__ __forceinline__ void cta_barrier(const PeerParams& prm, u64 value) {
+// all writes of this CTA → visible to CTA `blockIdx.x` of every peer once it has seen `value`; and the converse.
+// false: a peer did not arrive within kSpinLimitNs (or an earlier merge on this rank already gave up): the error word of
+// the own buffer is set and the caller must stop — what the peers would have written is not there.
+__device__ __forceinline__ bool cta_barrier(const PeerParams& prm, u64 value) {
+    __shared__ int s_failed;
+    if (threadIdx.x == 0) s_failed = 0;
     __syncthreads();
     if ((int)threadIdx.x < prm.world) {
         const int peer = threadIdx.x;
@@ -101,14 +105,16 @@ __device__ __forceinline__ void cta_barrier(const PeerParams& prm, u64 value) {
             if ((polls & 4095u) == 0) { // the timer is slow to read: look at it now and then
                 const u64 t = globaltimer_ns();
                 if (t0 == 0) t0 = t;
-                if (t - t0 > kSpinLimitNs) {
-                    *(volatile int*)prm.buf[prm.rank] = 1 + peer; // error word: the peer that never arrived
+                if (t - t0 > kSpinLimitNs || *(volatile int*)prm.buf[prm.rank] != 0) {
+                    atomicCAS((int*)prm.buf[prm.rank], 0, 1 + peer); // error word: the (first) peer that never arrived
+                    s_failed = 1;
                     break;
                 }
             }
         }
     }
     __syncthreads();
+    return s_failed == 0;
 }
 
 template <bool MC>
@@ -118,6 +124,7 @@ __global__ void __launch_bounds__(kPeerThreads) peer_merge_kernel(const PeerPara
     const i64 sub = ((per + gridDim.x - 1) / gridDim.x + 1) & ~1ll; // this CTA's share of every slice (even)
     const i64 s0 = (i64)blockIdx.x * sub;
     const i64 s1 = s0 + sub < per ? s0 + sub : per;
+    if (*(volatile int*)prm.buf[me] != 0) return; // an earlier merge timed out: the ranks are out of step, publish nothing more
 
     // 1. hand the partials over
     if (MC) {
@@ -142,7 +149,7 @@ __global__ void __launch_bounds__(kPeerThreads) peer_merge_kernel(const PeerPara
             }
         }
     }
-    cta_barrier(prm, prm.epoch + 1);
+    if (!cta_barrier(prm, prm.epoch + 1)) return;
 
     // 2. reduce my slice, hand the result to everyone
     {
@@ -181,7 +188,7 @@ __global__ void __launch_bounds__(kPeerThreads) peer_merge_kernel(const PeerPara
             }
         }
     }
-    cta_barrier(prm, prm.epoch + 2);
+    if (!cta_barrier(prm, prm.epoch + 2)) return;
 
     // 3. the merged vector → the engine's block (the own slice is already in place without multicast)
     {
@@ -206,6 +213,10 @@ struct PeerState {
     int ctas = 128;        // merge alone on the GPU: latency matters, take many CTAs
     int ctas_overlap = 16; // merge beside a pass of another batch (pipeline): it is hidden anyway, leave the SMs to the pass
     bool use_mc = false;
+    int* h_err = nullptr;  // pinned: the error word as read back with each batch's per-pod results (one per pipeline slot + 1)
+    ~PeerState() {
+        if (h_err) cudaFreeHost(h_err);
+    }
 };
 
 void Engine::peer_free() {
@@ -226,6 +237,7 @@ extern "C" uint64_t fgs_peer_bytes(int64_t max_pods) {
 extern "C" int fgs_peer_attach(fgs_engine* eh, const fgs_peer_group* g) {
     Engine* e = (Engine*)eh;
     if (!e) return FGS_E_INVALID;
+    FGS_ENTER(e);
     if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_peer_attach while submitted batches are in flight: fgs_collect them first");
     if (!g) { // detach
         e->peer_free();
@@ -240,6 +252,8 @@ extern "C" int fgs_peer_attach(fgs_engine* eh, const fgs_peer_group* g) {
     FGS_CUDA(e, cudaMemsetAsync(g->buffers[g->rank], 0, (size_t)kHeaderBytes, e->stream));
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
     if (!e->peer) e->peer = new PeerState();
+    if (!e->peer->h_err) FGS_CUDA(e, cudaMallocHost((void**)&e->peer->h_err, sizeof(int) * (Engine::kSlots + 1)));
+    memset(e->peer->h_err, 0, sizeof(int) * (Engine::kSlots + 1));
     e->peer->g = *g;
     e->peer->epoch = 0;
     e->peer->use_mc = g->multicast != nullptr;
@@ -293,21 +307,40 @@ int fgs::Engine::peer_merge(int which, cudaStream_t on, bool overlapped) {
 extern "C" int fgs_peer_merge_reduce(fgs_engine* eh) {
     Engine* e = (Engine*)eh;
     if (!e) return FGS_E_INVALID;
+    FGS_ENTER(e);
     return e->peer_merge(0, e->stream);
 }
 
 extern "C" int fgs_peer_merge_select(fgs_engine* eh) {
     Engine* e = (Engine*)eh;
     if (!e) return FGS_E_INVALID;
+    FGS_ENTER(e);
     return e->peer_merge(1, e->stream);
+}
+
+// the error word travels to the host with every batch's results: enqueue its copy behind the merge on `on` …
+int fgs::Engine::peer_fetch_error(int slot, cudaStream_t on) {
+    Engine* e = this;
+    if (!e->peer) return FGS_OK;
+    FGS_CUDA(e, cudaMemcpyAsync(e->peer->h_err + slot, e->peer->g.buffers[e->peer->g.rank], sizeof(int), cudaMemcpyDeviceToHost, on));
+    return FGS_OK;
+}
+// … and look at it once that stream has been waited for
+int fgs::Engine::peer_check_error(int slot) {
+    if (!peer || !peer->h_err) return FGS_OK;
+    const int word = peer->h_err[slot];
+    if (word) return fail(FGS_E_STATE, "peer merge: rank " + std::to_string(word - 1) + " never reached the barrier (timed out); this batch's results are not merged");
+    return FGS_OK;
 }
 
 extern "C" int fgs_peer_status(fgs_engine* eh, int32_t* uses_multicast) {
     Engine* e = (Engine*)eh;
     if (!e) return FGS_E_INVALID;
+    FGS_ENTER(e);
     if (!e->peer) return e->fail(FGS_E_STATE, "fgs_peer_status before fgs_peer_attach");
     FGS_CUDA(e, cudaSetDevice(e->device));
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (e->merge_stream) FGS_CUDA(e, cudaStreamSynchronize(e->merge_stream)); // the pipeline's merges run there
     int word = 0;
     FGS_CUDA(e, cudaMemcpy(&word, e->peer->g.buffers[e->peer->g.rank], sizeof word, cudaMemcpyDeviceToHost));
     if (uses_multicast) *uses_multicast = e->peer->use_mc ? 1 : 0;

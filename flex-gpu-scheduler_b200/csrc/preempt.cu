@@ -465,6 +465,7 @@ extern "C" int fgs_select_victims(fgs_engine* eh, const fgs_snapshot* snap, cons
                                   int32_t tracks_pods, uint8_t* node_status, uint8_t* victim, int32_t* n_victims, int32_t* picked_node) {
     if (!eh || !snap || !pending || !node_status) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_select_victims before fgs_upload_nodes");
     if (snap->n_nodes != e->n_nodes || e->node_base != 0) return e->fail(FGS_E_INVALID, "fgs_select_victims: the snapshot is not the uploaded node table (whole cluster, one engine)");
     if (snap->n_scalars != e->S || pending->n_scalars != e->S || (q && q->n_scalars != e->S)) return e->fail(FGS_E_INVALID, "fgs_select_victims: n_scalars mismatch");

@@ -167,6 +167,8 @@ using namespace fgs;
 extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, const fgs_seq_opts* opts, fgs_seq_results* out) {
     if (!eh || !out) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_schedule_sequential while submitted batches are in flight (it rewrites the node table): fgs_collect them first");
     int rc = seq_check_inputs(e, t, "fgs_schedule_sequential");
     if (rc) return rc;
     if (!t->acct_nz_mcpu || !t->acct_nz_mem || !t->index_annot)
@@ -426,6 +428,7 @@ extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, c
 extern "C" int fgs_reserve(fgs_engine* eh, const fgs_pod_table* t, const int32_t* node, int32_t* device_index) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
     int rc = seq_check_inputs(e, t, "fgs_reserve");
     if (rc) return rc;
     if (!node || !device_index) return e->fail(FGS_E_INVALID, "fgs_reserve: null node / device_index array");

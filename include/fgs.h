@@ -385,7 +385,8 @@ typedef struct fgs_timings {
     int32_t seq_ctas;                         /* CTAs it ran on */
     int32_t fused;                            /* 1: the last evaluation ran Filter and Score in one pass (then reduce_ms =
                                                  the per-pod prepass, emit_ms = the fused kernel) */
-    int32_t _pad;
+    int32_t reduce_lookup;                    /* 1: the last reduce pass ran Filter as table look-ups (level tables of the node
+                                                 side) instead of the compare kernels (then reduce_int32 = 0) */
 } fgs_timings;
 int fgs_get_timings(fgs_engine* e, fgs_timings* t);
 

@@ -28,10 +28,12 @@ def _planes(torch, eng, P):
 
 def _run(force_int64, s, cfg):
     os.environ["FGS_FORCE_INT64"] = "1" if force_int64 else "0"
+    os.environ["FGS_FILTER"] = "compare" if force_int64 else "lookup"  # the int64 family with its own Filter loop: an independent bitmap
     try:
         eng = fgs.Engine(device=0, n_scalars=2, total_nodes=s.n_nodes)
     finally:
         os.environ.pop("FGS_FORCE_INT64", None)
+        os.environ.pop("FGS_FILTER", None)
     eng.set_plugins(cfg)
     pk = fgs.Packer(2)
     eng.upload_nodes(pk.nodes(s.snapshot))
@@ -47,7 +49,7 @@ def test_config2_full_size_properties(gpu_ok, oracle):
     N, P = s.n_nodes, s.n_pending
     eng, table, res = _run(False, s, cfg)
     t = eng.timings()
-    assert t["reduce_int32"] and t["emit_int32"]  # the benchmark configuration runs the int32 kernels
+    assert t["reduce_lookup"] and t["emit_int32"]  # the benchmark configuration: Filter by table look-up, int32 emit kernel
     bm, sc = _planes(torch, eng, P)
     # feasibility as a [P][N] mask, in row chunks to bound memory
     shifts = torch.arange(32, device="cuda", dtype=torch.int32)

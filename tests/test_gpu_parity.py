@@ -34,18 +34,28 @@ def check_against_oracle(oracle, snapshot, pending, cfg, S=2, per_plugin=True, t
     qualifies) and a run with FGS_FORCE_INT64=1 (always the int64 kernels)."""
     ref = oracle.evaluate(snapshot, pending, cfg, workers=4, per_plugin=per_plugin)
     res = None
-    for force in ("0", "1"):
-        os.environ["FGS_FORCE_INT64"] = force
-        try:
-            res_i, took = _check_one(ref, snapshot, pending, cfg, S, per_plugin)
-        finally:
-            os.environ.pop("FGS_FORCE_INT64", None)
-        if force == "0":
-            res = res_i
-            if tag:
-                PATHS_TAKEN[tag] = took
-        else:
-            assert took == (False, False)
+    # … and both forms of pass A: Filter as table look-ups (the default) and the compare kernels
+    for filt in ("lookup", "compare"):
+        for force in ("0", "1"):
+            os.environ["FGS_FORCE_INT64"] = force
+            os.environ["FGS_FILTER"] = filt
+            try:
+                res_i, took, looked_up = _check_one(ref, snapshot, pending, cfg, S, per_plugin)
+            finally:
+                os.environ.pop("FGS_FORCE_INT64", None)
+                os.environ.pop("FGS_FILTER", None)
+            assert looked_up == (filt == "lookup")
+            if filt == "lookup":
+                assert not took[0]
+                if force == "0":
+                    res = res_i
+                    if tag:
+                        PATHS_TAKEN[tag + "/lookup"] = took
+            elif force == "0":
+                if tag:
+                    PATHS_TAKEN[tag] = took
+            else:
+                assert took == (False, False)
     return ref, res
 
 
@@ -54,6 +64,7 @@ def _check_one(ref, snapshot, pending, cfg, S, per_plugin):
     eng, pk, res = run_engine((snapshot, pending), cfg, S=S)
     t = eng.timings()
     took = (t["reduce_int32"], t["emit_int32"])
+    looked_up = t["reduce_lookup"]
     feas_ref = ref.status == 0
     # identical feasible set, counts and error flags
     feas = res.feasible(N)
@@ -88,7 +99,7 @@ def _check_one(ref, snapshot, pending, cfg, S, per_plugin):
             r_norm = eng.evaluate(pend_table, want_planes=True, emit_mask=bit)
             assert np.array_equal(r_norm.scores[:, :N][m], norm_ref[m] * (w if w else 1))
     eng.close()
-    return res, took
+    return res, took, looked_up
 
 
 CONFIG_CASES = [
