@@ -976,8 +976,16 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
         rp.reduce_sum = p.reduce_sum;
         rp.sc_flex = (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0;
         rp.sc_alloc = (e->cfg.score_mask & FGS_PL_ALLOCATABLE) ? 1 : 0;
-        FGS_CUDA(e, ft_launch_rows(rp, e->stream));
-        e->launches++;
+        const int64_t need_idx = (int64_t)rp.v.n_dims * e->p_pad;
+        if (need_idx > e->ft->rowidx_cap) {
+            if (e->ft->d_rowidx) cudaFree(e->ft->d_rowidx);
+            e->ft->d_rowidx = nullptr;
+            e->ft->rowidx_cap = 0;
+            FGS_CUDA(e, cudaMalloc(&e->ft->d_rowidx, sizeof(int) * (size_t)need_idx));
+            e->ft->rowidx_cap = need_idx;
+        }
+        FGS_CUDA(e, ft_launch_rows(rp, (int*)e->ft->d_rowidx, e->stream));
+        e->launches += 2;
         if ((e->cfg.filter_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
             ft_launch_filter_panic((const int64_t*)e->d_nd, (const int64_t*)e->d_pods, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special,
                                    e->n_pods, e->p_pad, e->S, e->cfg.filter_mask, e->cfg.fit_ignored_scalar_mask, p.flex_filter_first,

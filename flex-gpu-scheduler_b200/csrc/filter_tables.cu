@@ -133,7 +133,7 @@ __device__ __forceinline__ i64 warp_max_i64(i64 v) {
 constexpr int kWalkChunks = 24; // order walk: 32 nodes per step; after this many empty steps the set bits are scanned instead
 
 // value of the first feasible node in an order (front) or of the last one (back); `row` = the pod's bitmap row in shared memory
-__device__ __forceinline__ bool walk_order(const int* __restrict__ ord, const i64* __restrict__ val, i64 n_nodes, const uint32_t* row, int lane,
+__device__ __noinline__ bool walk_order(const int* __restrict__ ord, const i64* __restrict__ val, i64 n_nodes, const uint32_t* row, int lane,
                                            bool from_back, i64* out) {
     for (int step = 0; step < kWalkChunks; ++step) {
         const i64 k0 = (i64)step * 32 + lane;
@@ -155,7 +155,7 @@ __device__ __forceinline__ bool walk_order(const int* __restrict__ ord, const i6
 }
 
 // the slow way round, bounded by the number of feasible nodes: max of col[n] (or of −col[n]) over the set bits
-__device__ __forceinline__ i64 scan_bits(const uint32_t* row, i64 W, const i64* __restrict__ col, int lane, bool negate) {
+__device__ __noinline__ i64 scan_bits(const uint32_t* row, i64 W, const i64* __restrict__ col, int lane, bool negate) {
     i64 best = kMin;
     for (i64 w = lane; w < W; w += 32) {
         uint32_t x = row[w];
@@ -172,8 +172,54 @@ __device__ __forceinline__ i64 scan_bits(const uint32_t* row, i64 W, const i64* 
 
 constexpr int kRowsWarps = 8;
 
+// The row of every (pod, dimension): thread per pair — the pod's value in that dimension, its rank among the levels
+// (lower bound: the number of levels below it), → row index in the table, or the all-ones row when the row cannot
+// clear a bit: rank 0 (every node's threshold is at least the value), or the flex dimension the pod's kind does not
+// use (its row is "every valid node", which the other flex row already implies).
+__global__ void __launch_bounds__(256) ft_pod_rows(const __grid_constant__ FtRowsParams prm, int* __restrict__ rowidx) {
+    const i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    const int d = blockIdx.y;
+    if (p >= prm.p_pad) return;
+    const int ones = (int)prm.v.ones_row;
+    if (p >= prm.n_pods) {
+        rowidx[(i64)d * prm.p_pad + p] = ones;
+        return;
+    }
+    auto P = [&](int c) { return __ldg(prm.pods + (i64)c * prm.p_pad + p); };
+    const u64 meta = (u64)P(PD_META);
+    const uint32_t pf = (uint32_t)meta, kind = pf & 3u;
+    const bool none = pf & FGS_PF_REQ_NONE;
+    const uint32_t smask = (uint32_t)(meta >> 32) & ~prm.fit_ignored;
+    i64 v;
+    bool skip = false;
+    if (d == FT_GPU) {
+        v = kind == 1 ? P(PD_GPU_LIM) : (kind == 3 ? kMax : kLow1); // both limits: flex_gpu.go:58-61
+        skip = kind == 2;
+    } else if (d == FT_FMEM) {
+        v = kind == 2 ? P(PD_MEM_LIM) : kLow1;
+        skip = kind != 2;
+    } else if (d == FT_CPU) v = none ? kLow1 : P(PD_REQ_CPU); // fit.go:270-275
+    else if (d == FT_MEM) v = none ? kLow1 : P(PD_REQ_MEM);
+    else if (d == FT_EPH) v = none ? kLow1 : P(PD_REQ_EPH);
+    else v = (none || !((smask >> (d - FT_SCALAR0)) & 1u)) ? kLow1 : P(PD_FIXED_COLS + (d - FT_SCALAR0));
+    int out = ones;
+    if (!skip) {
+        const i64* lev = prm.v.levels + (i64)d * prm.v.lev_stride;
+        int lo = 0, hi = prm.v.R[d];
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (__ldg(lev + mid) < v) lo = mid + 1;
+            else hi = mid;
+        }
+        const bool flex_dim = d == FT_GPU || d == FT_FMEM; // never dropped: it also keeps rows that are not nodes out
+        if (lo > 0 || flex_dim) out = (int)(prm.v.row0[d] + lo);
+    }
+    rowidx[(i64)d * prm.p_pad + p] = out;
+}
+
+// ONE WARP PER POD: AND of the pod's rows → bitmap row + count; first feasible node in score order → the maxima.
 template <int NDIMS> // 0 = any number of dimensions (S > 2)
-__global__ void __launch_bounds__(kRowsWarps * 32) filter_rows(const __grid_constant__ FtRowsParams prm) {
+__global__ void __launch_bounds__(kRowsWarps * 32, NDIMS ? 5 : 4) filter_rows(const __grid_constant__ FtRowsParams prm, const int* __restrict__ rowidx) {
     extern __shared__ __align__(16) uint32_t s_rows[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const i64 p = (i64)blockIdx.x * kRowsWarps + warp;
@@ -182,57 +228,62 @@ __global__ void __launch_bounds__(kRowsWarps * 32) filter_rows(const __grid_cons
     const i64 W = prm.v.W;
     uint32_t* row = s_rows + (size_t)warp * W;
 
-    // ---- the pod's value and its rank in every dimension: lane d owns dimension d ---------------------------------
-    const u64 meta = (u64)__ldg(prm.pods + (i64)PD_META * prm.p_pad + p);
-    const uint32_t pf = (uint32_t)meta, kind = pf & 3u;
-    const bool none = pf & FGS_PF_REQ_NONE;
-    const uint32_t smask = (uint32_t)(meta >> 32) & ~prm.fit_ignored;
-    i64 rowoff = 0; // (row0[d] + rank) · W
-    if (lane < n_dims) {
-        const int d = lane;
-        auto P = [&](int c) { return __ldg(prm.pods + (i64)c * prm.p_pad + p); };
-        i64 v;
-        if (d == FT_GPU) v = kind == 1 ? P(PD_GPU_LIM) : (kind == 3 ? kMax : kLow1);      // both limits: flex_gpu.go:58-61
-        else if (d == FT_FMEM) v = kind == 2 ? P(PD_MEM_LIM) : (kind == 3 ? kMax : kLow1);
-        else if (d == FT_CPU) v = none ? kLow1 : P(PD_REQ_CPU);                            // fit.go:270-275
-        else if (d == FT_MEM) v = none ? kLow1 : P(PD_REQ_MEM);
-        else if (d == FT_EPH) v = none ? kLow1 : P(PD_REQ_EPH);
-        else v = (none || !((smask >> (d - FT_SCALAR0)) & 1u)) ? kLow1 : P(PD_FIXED_COLS + (d - FT_SCALAR0));
-        const i64* lev = prm.v.levels + (i64)d * prm.v.lev_stride;
-        int lo = 0, hi = prm.v.R[d];
-        while (lo < hi) { // lower bound: the number of levels below v
-            const int mid = (lo + hi) >> 1;
-            if (__ldg(lev + mid) < v) lo = mid + 1;
-            else hi = mid;
+    // row offset of lane d's dimension in 16-byte units (rows are multiples of 128 bytes)
+    const uint32_t my_off = lane < n_dims ? (uint32_t)(((i64)__ldg(rowidx + (i64)lane * prm.p_pad + p) * W) >> 2) : 0u;
+    const uint32_t kind = (uint32_t)__ldg(prm.pods + (i64)PD_META * prm.p_pad + p) & 3u;
+    // the first step of the order walks does not depend on the row: have its loads in flight now
+    const int o_flex = (kind & 1u) ? FT_ORD_GSCORE : FT_ORD_MSCORE; // a gpu limit wins over a memory limit (flex_gpu.go:157-159)
+    int n_f = 0, n_a = 0, n_b = 0;
+    i64 v_f = 0, v_a = 0, v_b = 0;
+    const bool want_flex = prm.sc_flex && kind != 0;
+    if (lane < prm.n_nodes) {
+        if (want_flex) {
+            n_f = __ldg(prm.v.ord + (i64)o_flex * prm.n_pad + lane);
+            v_f = __ldg(prm.v.ord_val + (i64)o_flex * prm.n_pad + lane);
         }
-        rowoff = (prm.v.row0[d] + lo) * W;
+        if (prm.sc_alloc) {
+            n_a = __ldg(prm.v.ord + (i64)FT_ORD_ARAW * prm.n_pad + lane);
+            v_a = __ldg(prm.v.ord_val + (i64)FT_ORD_ARAW * prm.n_pad + lane);
+            n_b = __ldg(prm.v.ord + (i64)FT_ORD_ARAW * prm.n_pad + prm.n_nodes - 1 - lane);
+            v_b = __ldg(prm.v.ord_val + (i64)FT_ORD_ARAW * prm.n_pad + prm.n_nodes - 1 - lane);
+        }
     }
 
-    // ---- the row: AND over the dimensions, 32 words per step ------------------------------------------------------
+    // ---- the row: AND over the dimensions, 4 words per lane and step (one 16-byte load per dimension) ---------------
     uint32_t cnt = 0;
-    uint32_t* out = prm.bitmap + p * W;
+    const uint4* T = (const uint4*)prm.v.table;
+    uint4* out4 = (uint4*)(prm.bitmap + p * W);
+    uint4* row4 = (uint4*)row;
+    const int W4 = (int)(W >> 2);
+    uint32_t off[NDIMS ? NDIMS : 1];
     if (NDIMS) {
-        const uint32_t* rp[NDIMS ? NDIMS : 1];
 #pragma unroll
-        for (int d = 0; d < NDIMS; ++d) rp[d] = prm.v.table + __shfl_sync(0xffffffffu, rowoff, d);
-        for (i64 w = lane; w < W; w += 32) {
-            uint32_t x[NDIMS ? NDIMS : 1];
+        for (int d = 0; d < NDIMS; ++d) off[d] = __shfl_sync(0xffffffffu, my_off, d);
+    }
+    for (int c0 = 0; c0 < W4; c0 += 32) {
+        const int c = c0 + lane;
+        uint4 a = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+        if (NDIMS) {
+            if (c < W4) {
+                uint4 x[NDIMS ? NDIMS : 1];
 #pragma unroll
-            for (int d = 0; d < NDIMS; ++d) x[d] = __ldg(rp[d] + w);
-            uint32_t a = x[0];
+                for (int d = 0; d < NDIMS; ++d) x[d] = __ldg(T + (size_t)off[d] + c);
 #pragma unroll
-            for (int d = 1; d < NDIMS; ++d) a &= x[d];
-            row[w] = a;
-            out[w] = a;
-            cnt += (uint32_t)__popc(a);
+                for (int d = 0; d < NDIMS; ++d) a.x &= x[d].x, a.y &= x[d].y, a.z &= x[d].z, a.w &= x[d].w;
+            }
+        } else {
+            for (int d = 0; d < n_dims; ++d) {
+                const uint32_t o = __shfl_sync(0xffffffffu, my_off, d);
+                if (c < W4) {
+                    const uint4 x = __ldg(T + (size_t)o + c);
+                    a.x &= x.x, a.y &= x.y, a.z &= x.z, a.w &= x.w;
+                }
+            }
         }
-    } else {
-        for (i64 w = lane; w < W; w += 32) {
-            uint32_t a = 0xffffffffu;
-            for (int d = 0; d < n_dims; ++d) a &= __ldg(prm.v.table + __shfl_sync(0xffffffffu, rowoff, d) + w);
-            row[w] = a;
-            out[w] = a;
-            cnt += (uint32_t)__popc(a);
+        if (c < W4) {
+            row4[c] = a;
+            out4[c] = a;
+            cnt += (uint32_t)(__popc(a.x) + __popc(a.y) + __popc(a.z) + __popc(a.w));
         }
     }
     cnt = __reduce_add_sync(0xffffffffu, cnt);
@@ -241,12 +292,19 @@ __global__ void __launch_bounds__(kRowsWarps * 32) filter_rows(const __grid_cons
     // ---- what NormalizeScore needs: the best raw scores among the feasible nodes ------------------------------------
     i64 vflex = kMin, vhi = kMin, vnlo = kMin;
     if (cnt > 0) {
-        if (prm.sc_flex) { // raw FlexGPU score by pod kind (flex_gpu.go:153-165); a gpu limit wins over a memory limit
+        auto bit = [&](int n) { return (row[n >> 5] >> (n & 31)) & 1u; };
+        auto first_of = [&](int n, i64 v, bool* found) -> i64 { // step 0 of a walk from the values loaded above
+            const uint32_t bal = __ballot_sync(0xffffffffu, lane < prm.n_nodes && bit(n));
+            *found = bal != 0;
+            return __shfl_sync(0xffffffffu, v, bal ? __ffs(bal) - 1 : 0);
+        };
+        if (prm.sc_flex) { // raw FlexGPU score by pod kind (flex_gpu.go:153-165)
             if (kind == 0) {
                 vflex = 0;
             } else {
-                const int o = (kind & 1u) ? FT_ORD_GSCORE : FT_ORD_MSCORE;
-                if (!walk_order(prm.v.ord + (i64)o * prm.n_pad, prm.v.ord_val + (i64)o * prm.n_pad, prm.n_nodes, row, lane, false, &vflex))
+                bool found;
+                vflex = first_of(n_f, v_f, &found);
+                if (!found && !walk_order(prm.v.ord + (i64)o_flex * prm.n_pad, prm.v.ord_val + (i64)o_flex * prm.n_pad, prm.n_nodes, row, lane, false, &vflex))
                     vflex = scan_bits(row, W, prm.nd + (i64)((kind & 1u) ? ND_GPU_SCORE : ND_MEM_SCORE) * prm.n_pad, lane, false);
             }
         }
@@ -254,9 +312,11 @@ __global__ void __launch_bounds__(kRowsWarps * 32) filter_rows(const __grid_cons
             const int* ord = prm.v.ord + (i64)FT_ORD_ARAW * prm.n_pad;
             const i64* val = prm.v.ord_val + (i64)FT_ORD_ARAW * prm.n_pad;
             const i64* col = prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad;
-            if (!walk_order(ord, val, prm.n_nodes, row, lane, false, &vhi)) vhi = scan_bits(row, W, col, lane, false);
-            i64 lo;
-            if (walk_order(ord, val, prm.n_nodes, row, lane, true, &lo)) vnlo = -lo;
+            bool found;
+            vhi = first_of(n_a, v_a, &found);
+            if (!found && !walk_order(ord, val, prm.n_nodes, row, lane, false, &vhi)) vhi = scan_bits(row, W, col, lane, false);
+            i64 lo = first_of(n_b, v_b, &found);
+            if (found || walk_order(ord, val, prm.n_nodes, row, lane, true, &lo)) vnlo = -lo;
             else vnlo = scan_bits(row, W, col, lane, true);
         }
     }
@@ -315,12 +375,13 @@ cudaError_t grow(void** p, size_t bytes) {
 } // namespace
 
 void FilterTables::free_all() {
-    for (void** p : {&d_table, &d_levels, &d_node_rank, &d_ord, &d_ord_val, &d_thr, &d_sort, &d_counts})
+    for (void** p : {&d_table, &d_levels, &d_node_rank, &d_ord, &d_ord_val, &d_thr, &d_sort, &d_counts, &d_rowidx})
         if (*p) {
             cudaFree(*p);
             *p = nullptr;
         }
     table_bytes = sort_bytes = 0;
+    rowidx_cap = 0;
     n_cap = 0;
     dims_cap = 0;
     valid = false;
@@ -413,7 +474,8 @@ cudaError_t ft_build(FilterTables* ft, const FtBuildParams& bp, cudaStream_t st,
         rmax = std::max(rmax, counts[d]);
     }
     ft->rows_total = rows;
-    const size_t need = (size_t)rows * (size_t)v.W * 4;
+    v.ones_row = rows; // one more row, all ones: what a dimension that cannot clear a bit reads
+    const size_t need = (size_t)(rows + 1) * (size_t)v.W * 4;
     if (need > ft->limit_bytes) {
         ft->refused = true;
         cudaEventDestroy(ev0);
@@ -435,6 +497,7 @@ cudaError_t ft_build(FilterTables* ft, const FtBuildParams& bp, cudaStream_t st,
     }
     const dim3 grid((unsigned)((v.W + 31) / 32), (unsigned)(rmax / kFtRowsPerCta + 1), (unsigned)n_dims);
     ft_fill_rows<<<grid, 256, 0, st>>>(tp);
+    FT_TRY(cudaMemsetAsync((uint32_t*)ft->d_table + (size_t)rows * (size_t)v.W, 0xff, (size_t)v.W * 4, st));
     *launches += 1;
     FT_TRY(cudaGetLastError());
     v.table = (const uint32_t*)ft->d_table;
@@ -456,16 +519,18 @@ cudaError_t ft_build(FilterTables* ft, const FtBuildParams& bp, cudaStream_t st,
 
 bool ft_rows_fit(int64_t W) { return (size_t)W * 4 * kRowsWarps <= 200 * 1024; }
 
-cudaError_t ft_launch_rows(const FtRowsParams& p, cudaStream_t st) {
+cudaError_t ft_launch_rows(const FtRowsParams& p, int* rowidx, cudaStream_t st) {
     if (p.n_pods <= 0) return cudaSuccess;
+    const dim3 rgrid((unsigned)((p.p_pad + 255) / 256), (unsigned)p.v.n_dims);
+    ft_pod_rows<<<rgrid, 256, 0, st>>>(p, rowidx);
     const size_t smem = (size_t)p.v.W * 4 * kRowsWarps;
     const unsigned grid = (unsigned)((p.n_pods + kRowsWarps - 1) / kRowsWarps);
     if (p.v.n_dims == 7) {
         if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(filter_rows<7>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        filter_rows<7><<<grid, kRowsWarps * 32, smem, st>>>(p);
+        filter_rows<7><<<grid, kRowsWarps * 32, smem, st>>>(p, rowidx);
     } else {
         if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(filter_rows<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        filter_rows<0><<<grid, kRowsWarps * 32, smem, st>>>(p);
+        filter_rows<0><<<grid, kRowsWarps * 32, smem, st>>>(p, rowidx);
     }
     return cudaGetLastError();
 }

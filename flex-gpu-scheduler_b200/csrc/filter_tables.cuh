@@ -30,6 +30,7 @@ struct FtView {
     const int64_t* ord_val;  // [FT_ORDERS][n_pad]: the sorted values
     int64_t lev_stride;
     int64_t W;               // words per row = n_pad / 32
+    int64_t ones_row;         // index of the all-ones row behind the last dimension
     int64_t row0[kFtMaxDims]; // first row of dimension d
     int32_t R[kFtMaxDims];    // levels of dimension d (its rows are 0..R[d]: row R[d] is empty)
     int32_t n_dims;
@@ -53,6 +54,8 @@ struct FilterTables {
     void* d_sort = nullptr;         // sort scratch: keys out, values in / out, scan, cub temp
     size_t sort_bytes = 0;
     void* d_counts = nullptr;       // int32 [kFtMaxDims]
+    void* d_rowidx = nullptr;       // int32 [n_dims][p_cap]: per batch, the table row of every (pod, dimension)
+    int64_t rowidx_cap = 0;
     int64_t n_cap = 0;
     int dims_cap = 0;
     int64_t rows_total = 0;
@@ -84,8 +87,9 @@ struct FtRowsParams {
     int64_t* reduce_sum;     // [p_pad]
     int sc_flex, sc_alloc;
 };
-// pass A: bitmap rows, feasible counts, max FlexGPU score, Allocatable hi / −lo of every pod (one warp per pod)
-cudaError_t ft_launch_rows(const FtRowsParams& p, cudaStream_t stream);
+// pass A: bitmap rows, feasible counts, max FlexGPU score, Allocatable hi / −lo of every pod — two launches: the row of
+// every (pod, dimension) into rowidx (int32 [n_dims][p_pad], caller's scratch), then one warp per pod
+cudaError_t ft_launch_rows(const FtRowsParams& p, int* rowidx, cudaStream_t stream);
 bool ft_rows_fit(int64_t W); // the row of one pod fits the kernel's shared memory
 
 // the pods that reach NewGPUNode's panic inside FlexGPU.Filter → RR_FILTER_PANIC, from the int64 tables (any S)
