@@ -84,13 +84,18 @@ class NodeTable(C.Structure):
     ]
 
 
+class PodStats(C.Structure):
+    _fields_ = [("or_bits", C.c_uint64 * (8 + FGS_MAX_SCALARS)), ("max_val", C.c_int64 * (8 + FGS_MAX_SCALARS)), ("present_or", C.c_uint32),
+                ("flags", C.c_uint32)]
+
+
 class PodTable(C.Structure):
     _fields_ = [
         ("n_pods", C.c_int64), ("n_scalars", C.c_int32), ("_pad0", C.c_int32),
         ("flex_gpu_limit", p_i64), ("flex_mem_limit", p_i64), ("flags", p_u32),
         ("req_mcpu", p_i64), ("req_mem", p_i64), ("req_eph", p_i64), ("req_scalar", p_i64), ("req_scalar_present", p_u32),
         ("nz_mcpu", p_i64), ("nz_mem", p_i64), ("ns", p_i32), ("pg", p_i32), ("priority", p_i32),
-        ("acct_nz_mcpu", p_i64), ("acct_nz_mem", p_i64), ("index_annot", p_i32), ("uid", p_i64),
+        ("acct_nz_mcpu", p_i64), ("acct_nz_mem", p_i64), ("index_annot", p_i32), ("uid", p_i64), ("stats", C.POINTER(PodStats)),
     ]
 
 
@@ -180,7 +185,9 @@ ABI = {
     "fgs_set_nominated": (C.c_int, [C.c_void_p, C.POINTER(PodTable), p_i32, p_i64]),
     "fgs_submit": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts)]),
     "fgs_collect": (C.c_int, [C.c_void_p, C.POINTER(Results)]),
+    "fgs_packer_pin": (C.c_int, [C.c_void_p]),
     "fgs_resubmit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
+    "fgs_set_resident_batches": (C.c_int, [C.c_void_p, C.c_int32]),
     "fgs_stage_pods": (C.c_int, [C.c_void_p, C.POINTER(PodTable)]),
     "fgs_pass_reduce": (C.c_int, [C.c_void_p]),
     "fgs_fused_eligible": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),

@@ -124,13 +124,17 @@ class Packer:
     """Host-side packer (no GPU needed): object snapshot → SoA tables. A table stays valid until the
     next call of the same kind on the same Packer, so use one Packer per table you keep."""
 
-    def __init__(self, n_scalars=2):
+    def __init__(self, n_scalars=2, pin=False):
+        """pin=True: page-lock the pod tables this packer makes (fgs_packer_pin), so that the engine copies them to the
+        GPU by DMA without a staging pass; needs a CUDA device"""
         self._lib = L.load()
         h = C.c_void_p()
         rc = self._lib.fgs_packer_create(n_scalars, C.byref(h))
         if rc != 0:
             raise FgsError(rc, "fgs_packer_create")
         self._h = h
+        if pin:
+            self._check(self._lib.fgs_packer_pin(self._h))
 
     def _check(self, rc):
         if rc != 0:
@@ -312,10 +316,14 @@ class Engine:
         self._pending = getattr(self, "_pending", []) + [P]
 
     def resubmit(self, n_pods, **opts):
-        """fgs_resubmit: the batch already resident in the next pipeline slot again (sharded engines only)."""
+        """fgs_resubmit: the batch already resident in the next pipeline slot again (no staging, no H2D)."""
         o = self._opts(**opts)
         self._check(self._lib.fgs_resubmit(self._h, C.byref(o)))
         self._pending = getattr(self, "_pending", []) + [int(n_pods)]
+
+    def set_resident_batches(self, n):
+        """fgs_set_resident_batches: a ring of n pipeline slots, so that a job of n batches stays resident for resubmit()"""
+        self._check(self._lib.fgs_set_resident_batches(self._h, int(n)))
 
     def collect(self):
         """Per-pod results of the oldest submitted batch (blocks until it is done)."""

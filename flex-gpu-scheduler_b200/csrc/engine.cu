@@ -100,7 +100,7 @@ int Engine::ensure_pods(int64_t p) {
         d_pods = d_perpod = nullptr;
         h_pods = h_perpod = nullptr;
         p_pad_cap = pp;
-        FGS_CUDA(this, cudaMalloc(&d_pods, sizeof(int64_t) * pd_cols(S) * pp));
+        FGS_CUDA(this, cudaMalloc(&d_pods, sizeof(int64_t) * (pd_cols(S) + 1) * pp)); // + one column of scratch (flags / present words on the DMA path)
         FGS_CUDA(this, cudaMalloc(&d_perpod, sizeof(int64_t) * kPerPodRows * pp));
         FGS_CUDA(this, cudaMallocHost(&h_pods, sizeof(int64_t) * pd_cols(S) * pp));
         FGS_CUDA(this, cudaMallocHost(&h_perpod, sizeof(int64_t) * 4 * pp));
@@ -325,6 +325,8 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
         // thread leave two CTAs per SM, and the loop does not hide its latencies with 16 warps) — DESIGN.md §3
         const char* nf = getenv("FGS_FUSED");
         e->no_fused = !(nf && nf[0] == '1');
+        const char* nd_ = getenv("FGS_NO_DMA");
+        e->no_dma = nd_ && nd_[0] == '1';
         const char* fm = getenv("FGS_FILTER");
         e->filter_mode = fm ? (fm[0] == 'c' ? 1 : (fm[0] == 'l' ? 2 : 0)) : 0;
         const char* ht = getenv("FGS_HOST_THREADS");
@@ -807,6 +809,46 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
     const int S = e->S;
     int64_t* h = (int64_t*)e->h_pods;
     FGS_CUDA(e, cudaEventRecord(e->events[0], e->stream));
+    // DMA path: the table brings its column statistics and lies in page-locked memory (fgs_pod_stats, fgs_packer_pin) —
+    // every column goes to the GPU straight from the caller's arrays: no host pass, no staging copy
+    if (t->stats && (t->stats->flags & FGS_POD_STATS_PINNED) && P > 0 && !e->no_dma) {
+        cudaStream_t st = async ? e->copy_stream : e->stream;
+        int64_t* d = (int64_t*)e->d_pods;
+        const int64_t* cols[PD_FIXED_COLS] = {nullptr};
+        cols[PD_GPU_LIM] = t->flex_gpu_limit, cols[PD_MEM_LIM] = t->flex_mem_limit, cols[PD_REQ_CPU] = t->req_mcpu, cols[PD_REQ_MEM] = t->req_mem;
+        cols[PD_REQ_EPH] = t->req_eph, cols[PD_NZ_CPU] = t->nz_mcpu, cols[PD_NZ_MEM] = t->nz_mem;
+        for (int c = 0; c < PD_FIXED_COLS; ++c)
+            if (cols[c]) FGS_CUDA(e, cudaMemcpyAsync(d + (int64_t)c * pp, cols[c], sizeof(int64_t) * (size_t)P, cudaMemcpyHostToDevice, st));
+        // the S scalar columns are one [S][P] block in the table and [S][pp] on the device
+        FGS_CUDA(e, cudaMemcpy2DAsync(d + (int64_t)PD_FIXED_COLS * pp, sizeof(int64_t) * (size_t)pp, t->req_scalar, sizeof(int64_t) * (size_t)P,
+                                      sizeof(int64_t) * (size_t)P, (size_t)S, cudaMemcpyHostToDevice, st));
+        uint32_t* scratch = (uint32_t*)(d + (int64_t)pd_cols(S) * pp);
+        FGS_CUDA(e, cudaMemcpyAsync(scratch, t->flags, sizeof(uint32_t) * (size_t)P, cudaMemcpyHostToDevice, st));
+        FGS_CUDA(e, cudaMemcpyAsync(scratch + pp, t->req_scalar_present, sizeof(uint32_t) * (size_t)P, cudaMemcpyHostToDevice, st));
+        if (pp > P) // the padding pods of every column
+            FGS_CUDA(e, cudaMemset2DAsync(d + P, sizeof(int64_t) * (size_t)pp, 0, sizeof(int64_t) * (size_t)(pp - P), (size_t)pd_cols(S), st));
+        launch_make_pod_meta(scratch, scratch + pp, d + (int64_t)PD_META * pp, P, pp, st);
+        e->launches++;
+        FGS_CUDA(e, cudaGetLastError());
+        for (int c = 0; c < pd_cols(S); ++c) {
+            e->stage_or[c] = t->stats->or_bits[c];
+            e->stage_max[c] = t->stats->max_val[c];
+        }
+        e->stage_present_or = t->stats->present_or;
+        if (async) {
+            FGS_CUDA(e, cudaEventRecord(e->ev_h2d, e->copy_stream));
+            FGS_CUDA(e, cudaStreamWaitEvent(e->stream, e->ev_h2d, 0));
+        }
+        int rc2 = e->decide_narrow(t);
+        if (rc2) return rc2;
+        rc2 = e->stage_nominated_aux(t);
+        if (rc2) return rc2;
+        FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
+        e->have_pods = true;
+        e->staged_by_dma = true;
+        return FGS_OK;
+    }
+    e->staged_by_dma = false;
     // one pass over every column: copy into the pinned staging buffer and collect the OR / MAX that the int32
     // specialisation needs (decide_narrow); a few host threads share the work
     // ONE parallel region: every thread takes a contiguous range of pods through all the columns (one fork / join per
@@ -1313,12 +1355,14 @@ int Engine::issue_emit_sharded(int j) {
 
 int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident) {
     Engine* e = this;
-    const int k = in_flight == 0 ? cur_slot : (oldest_slot + in_flight) % ring();
+    const int k = in_flight == 0 ? (next_slot >= 0 && next_slot < ring() ? next_slot : cur_slot) : (oldest_slot + in_flight) % ring();
     const int newest = in_flight == 0 ? -1 : (oldest_slot + in_flight - 1) % ring();
     if (k != cur_slot) bind_slot(k);
     if (in_flight == 0) oldest_slot = k;
+    next_slot = (k + 1) % ring();
     if (resident) {
         if (!have_pods) return fail(FGS_E_STATE, "fgs_resubmit: no batch is resident in this pipeline slot (fgs_submit fills the slots in turn)");
+        if (slots[k].node_gen != node_gen) return fail(FGS_E_STATE, "fgs_resubmit: the node table changed since this batch was staged: fgs_submit it again");
     } else {
         // A batch larger than any before makes ensure_pods replace the bitmap / score planes, which the emit pass of the
         // previous batch has still to read: issue that pass first and let everything in flight drain.
@@ -1333,6 +1377,7 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
         if (rc) return rc;
     }
     emitted = false;
+    slots[k].node_gen = node_gen;
     slots[k].bitmap_sel = (int)(submit_seq++ & 1);
     if (slots[k].bitmap_sel == 1) { // the second bitmap, as large as the first
         const size_t need = sizeof(uint32_t) * (size_t)p_plane_cap * (size_t)words_per_row;
@@ -1370,23 +1415,40 @@ extern "C" int fgs_resubmit(fgs_engine* eh, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
     FGS_ENTER(e);
-    if (!e->peer) return e->fail(FGS_E_STATE, "fgs_resubmit: only with a peer group attached (fgs_peer_attach)");
-    if (e->in_flight >= 3) return e->fail(FGS_E_STATE, "fgs_resubmit: three batches are in flight already; fgs_collect one first");
+    if (e->in_flight >= e->max_in_flight())
+        return e->fail(FGS_E_STATE, e->peer ? "fgs_resubmit: three batches are in flight already; fgs_collect one first"
+                                            : "fgs_resubmit: two batches are in flight already; fgs_collect one first");
     if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_resubmit: nominated pods are set: use fgs_evaluate");
     if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_resubmit: sample / skip_pass_b need fgs_evaluate");
     cudaSetDevice(e->device);
     const int rc = ensure_pipeline(e);
     if (rc) return rc;
-    return e->submit_sharded(nullptr, opts, true);
+    if (e->peer) return e->submit_sharded(nullptr, opts, true);
+    return e->submit_single(nullptr, opts, true);
+}
+
+// More pipeline slots than batches in flight: every slot keeps the batch it was last handed resident on the device
+// (pod tables, int32 tables, per-pod rows), so that fgs_resubmit can walk a whole job of n batches again and again
+// without staging. 0 restores the default (as many slots as batches in flight).
+extern "C" int fgs_set_resident_batches(fgs_engine* eh, int32_t n) {
+    if (!eh) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_set_resident_batches while submitted batches are in flight: fgs_collect them first");
+    if (n != 0 && (n < 3 || n > Engine::kSlots)) return e->fail(FGS_E_TOO_LARGE, "fgs_set_resident_batches: 0 (default) or 3.." + std::to_string(Engine::kSlots));
+    e->resident_cfg = n;
+    e->next_slot = -1;
+    if (e->cur_slot >= e->ring()) e->bind_slot(0);
+    return FGS_OK;
 }
 
 extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
     FGS_ENTER(e);
-    if (e->in_flight >= e->ring())
-        return e->fail(FGS_E_STATE, e->ring() == 3 ? "fgs_submit: three batches are in flight already; fgs_collect one first"
-                                                   : "fgs_submit: two batches are in flight already; fgs_collect one first");
+    if (e->in_flight >= e->max_in_flight())
+        return e->fail(FGS_E_STATE, e->peer ? "fgs_submit: three batches are in flight already; fgs_collect one first"
+                                            : "fgs_submit: two batches are in flight already; fgs_collect one first");
     if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_submit: sample / skip_pass_b need fgs_evaluate");
     if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_submit: nominated pods are set (their per-batch columns are not double-buffered): use fgs_evaluate");
     cudaSetDevice(e->device);
@@ -1395,12 +1457,28 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
         if (rc) return rc;
     }
     if (e->peer) return e->submit_sharded(pods, opts, false);
-    // the slot that is not in flight (in_flight == 1: the other one; 0: keep the current one)
-    const int k = e->in_flight == 0 ? e->cur_slot : (e->oldest_slot + e->in_flight) % e->ring();
+    return e->submit_single(pods, opts, false);
+}
+
+int Engine::submit_single(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident) {
+    Engine* e = this;
+    fgs_engine* eh = (fgs_engine*)this;
+    // the next slot of the ring (the ring is walked round-robin, so a job of n batches keeps its slots)
+    const int k = e->in_flight == 0 ? (e->next_slot >= 0 && e->next_slot < e->ring() ? e->next_slot : e->cur_slot) : (e->oldest_slot + e->in_flight) % e->ring();
     if (k != e->cur_slot) e->bind_slot(k);
     if (e->in_flight == 0) e->oldest_slot = k;
-    int rc = stage_pods_impl(e, pods, true);
-    if (rc) return rc;
+    e->next_slot = (k + 1) % e->ring();
+    int rc;
+    if (resident) {
+        if (!e->have_pods) return fail(FGS_E_STATE, "fgs_resubmit: no batch is resident in this pipeline slot (fgs_submit fills the slots in turn)");
+        if (e->slots[k].node_gen != e->node_gen) return fail(FGS_E_STATE, "fgs_resubmit: the node table changed since this batch was staged: fgs_submit it again");
+        FGS_CUDA(e, cudaEventRecord(e->events[0], e->stream));
+        FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
+    } else {
+        rc = stage_pods_impl(e, pods, true);
+        if (rc) return rc;
+        e->slots[k].node_gen = e->node_gen;
+    }
     e->emitted = false;
     e->was_fused = false;
     if (e->fused_eligible(opts)) {

@@ -60,6 +60,8 @@ struct Engine {
     int64_t stage_max[PD_FIXED_COLS + FGS_MAX_SCALARS] = {0};
     uint32_t stage_present_or = 0;
     bool force_wide = false;   // FGS_FORCE_INT64=1: always take the int64 kernels (tests)
+    bool no_dma = false;       // FGS_NO_DMA=1: always stage through the engine's own pinned buffer (tests)
+    bool staged_by_dma = false; // the last staged batch came by DMA straight from the caller's table
     bool reduce_was_narrow = false, emit_was_narrow = false;
     void* d_nn = nullptr;
     void* d_pn = nullptr;
@@ -88,6 +90,7 @@ struct Engine {
         void *d_pods = nullptr, *h_pods = nullptr, *d_perpod = nullptr, *h_perpod = nullptr, *d_pn = nullptr;
         int64_t p_pad_cap = 0, pn_cap = 0, n_pods = 0, p_pad = 0;
         bool narrow_batch = false, emitted = false, sampled = false, have_pods = false, busy = false;
+        uint64_t node_gen = 0; // Engine::node_gen when the batch was staged (fgs_resubmit refuses a stale batch)
         int key_shift = 40;
         cudaEvent_t ev_done = nullptr;
         // sharded pipeline (peer attached): the emit pass of a batch is issued with the NEXT submit (or by collect)
@@ -97,9 +100,16 @@ struct Engine {
         bool have_opts = false;
         cudaEvent_t ev_reduce = nullptr, ev_merge1 = nullptr, ev_emit = nullptr, ev_merge2 = nullptr;
     };
-    static constexpr int kSlots = 3; // two in flight on one GPU; three in the sharded pipeline (see submit_sharded)
+    static constexpr int kSlots = 32; // upper bound of fgs_set_resident_batches
     Slot slots[kSlots];
-    int ring() const { return peer ? 3 : 2; } // a third batch in flight buys nothing on one GPU (tools/pipe_breakdown.py)
+    // batches in flight: two on one GPU (a third buys nothing there, tools/pipe_breakdown.py), three in the sharded
+    // pipeline (see submit_sharded). The ring of slots is that long too unless fgs_set_resident_batches asked for more:
+    // extra slots only keep more batches RESIDENT for fgs_resubmit.
+    int max_in_flight() const { return peer ? 3 : 2; }
+    int resident_cfg = 0;
+    int ring() const { return resident_cfg > max_in_flight() ? resident_cfg : max_in_flight(); }
+    int next_slot = -1;      // slot the next submit takes (-1: the current one) — the ring is walked round-robin
+    int submit_single(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident);
     uint64_t submit_seq = 0; // batches submitted so far: the sharded pipeline alternates two bitmaps by its parity
     int cur_slot = 0;       // slot whose buffers the members alias
     int in_flight = 0;      // submitted, not yet collected

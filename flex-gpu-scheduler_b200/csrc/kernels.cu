@@ -697,6 +697,19 @@ void launch_finalize_pods(const int64_t* perpod, int64_t* compact, int64_t n_pod
                                                                                      emitted, sc_flex);
 }
 
+namespace {
+// PD_META of a pod table that arrived column by column (DMA straight from the caller's table): flags | present << 32
+__global__ void make_pod_meta(const uint32_t* __restrict__ flags, const uint32_t* __restrict__ present, i64* __restrict__ meta, i64 n_pods, i64 p_pad) {
+    const i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p_pad) return;
+    meta[i] = i < n_pods ? (i64)(((u64)present[i] << 32) | (u64)flags[i]) : 0;
+}
+} // namespace
+
+void launch_make_pod_meta(const uint32_t* flags, const uint32_t* present, int64_t* meta, int64_t n_pods, int64_t p_pad, void* stream) {
+    make_pod_meta<<<(unsigned)((p_pad + 255) / 256), 256, 0, (cudaStream_t)stream>>>(flags, present, (i64*)meta, n_pods, p_pad);
+}
+
 void launch_init_perpod(int64_t* perpod, int64_t p_pad, void* stream) {
     init_perpod<<<(unsigned)((p_pad + 255) / 256), 256, 0, (cudaStream_t)stream>>>((i64*)perpod, (i64)p_pad);
 }

@@ -119,6 +119,7 @@ void launch_init_perpod(int64_t* perpod, int64_t p_pad, void* stream);
 // [2] selected score, [3] FGS_PODERR_* bits — int64 [4][p_pad]
 void launch_finalize_pods(const int64_t* perpod, int64_t* compact, int64_t n_pods, int64_t p_pad, int key_shift, int emitted, int sc_flex,
                           void* stream);
+void launch_make_pod_meta(const uint32_t* flags, const uint32_t* present, int64_t* meta, int64_t n_pods, int64_t p_pad, void* stream);
 void launch_derive(const DeriveParams& p, void* stream);
 void launch_eval_reduce(const EvalParams& p, void* stream);
 void launch_eval_emit(const EvalParams& p, void* stream);

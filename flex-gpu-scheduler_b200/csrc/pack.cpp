@@ -6,6 +6,10 @@
 // and each pending pod is reduced once to the numbers the plugins derive from it on every call.
 #include "pack.h"
 
+#include <cuda_runtime_api.h>
+
+#include <utility>
+
 #include <cstring>
 #include <new>
 
@@ -58,6 +62,7 @@ void PackedPods::make_view() {
     view.acct_nz_mcpu = acct_nz_mcpu.data();
     view.acct_nz_mem = acct_nz_mem.data();
     view.index_annot = index_annot.data();
+    view.stats = &stats;
 }
 
 static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::string* err);
@@ -221,6 +226,11 @@ int pack_pods(const fgs_podset* pods, int64_t p0, int64_t p1, PackedPods* out, s
     t.ns.assign((size_t)P, 0);
     t.pg.assign((size_t)P, -1);
     t.priority.assign((size_t)P, 0);
+    std::memset(&t.stats, 0, sizeof(t.stats));
+    auto acc = [&](int c, int64_t v) { // every quantity is >= 0 here (checked below)
+        t.stats.or_bits[c] |= (uint64_t)v;
+        if (v > t.stats.max_val[c]) t.stats.max_val[c] = v;
+    };
     for (int64_t i = 0; i < P; ++i) {
         const int64_t src = p0 + i;
         const PodLimits l = pod_limits(pods, src);
@@ -254,6 +264,9 @@ int pack_pods(const fgs_podset* pods, int64_t p0, int64_t p1, PackedPods* out, s
         t.ns[(size_t)i] = pods->ns ? pods->ns[src] : 0;
         t.pg[(size_t)i] = pods->pg ? pods->pg[src] : -1;
         t.priority[(size_t)i] = pods->priority ? pods->priority[src] : 0;
+        acc(0, l.gpu), acc(1, l.mem), acc(2, r.v[0]), acc(3, r.v[1]), acc(4, r.v[2]), acc(5, r.score_mcpu), acc(6, r.score_mem);
+        for (int s = 0; s < S; ++s) acc(8 + s, r.v[3 + s]);
+        t.stats.present_or |= r.scalar_keys;
     }
     t.make_view();
     return FGS_OK;
@@ -268,7 +281,49 @@ struct fgs_packer {
     fgs::PackedNodes nodes;
     fgs::PackedPods pods;
     std::string err;
+    // fgs_packer_pin: the pod-table columns the engine copies, as currently page-locked (pointer, bytes)
+    bool pin = false;
+    std::vector<std::pair<void*, size_t>> locked;
+    void unlock_all() {
+        for (auto& r : locked) cudaHostUnregister(r.first);
+        locked.clear();
+    }
+    int lock_columns();
 };
+
+int fgs_packer::lock_columns() {
+    fgs::PackedPods& t = pods;
+    std::vector<std::pair<void*, size_t>> want;
+    auto add = [&](const void* p, size_t bytes) {
+        if (p && bytes) want.push_back({(void*)p, bytes});
+    };
+    const size_t P = (size_t)t.n;
+    add(t.flex_gpu_limit.data(), P * 8), add(t.flex_mem_limit.data(), P * 8), add(t.req_mcpu.data(), P * 8), add(t.req_mem.data(), P * 8);
+    add(t.req_eph.data(), P * 8), add(t.nz_mcpu.data(), P * 8), add(t.nz_mem.data(), P * 8), add(t.req_scalar.data(), P * 8 * (size_t)t.S);
+    add(t.flags.data(), P * 4), add(t.req_scalar_present.data(), P * 4);
+    t.stats.flags &= ~FGS_POD_STATS_PINNED;
+    if (want != locked) { // the vectors moved or changed size: lock them anew
+        unlock_all();
+        for (auto& r : want) {
+            const cudaError_t ce = cudaHostRegister(r.first, r.second, cudaHostRegisterDefault);
+            if (ce != cudaSuccess) {
+                cudaGetLastError();
+                err = std::string("fgs_packer_pin: cudaHostRegister: ") + cudaGetErrorString(ce);
+                unlock_all();
+                return FGS_E_CUDA;
+            }
+            locked.push_back(r);
+        }
+    }
+    if (!want.empty()) t.stats.flags |= FGS_POD_STATS_PINNED;
+    return FGS_OK;
+}
+
+extern "C" int fgs_packer_pin(fgs_packer* p) {
+    if (!p) return FGS_E_INVALID;
+    p->pin = true;
+    return p->lock_columns();
+}
 
 extern "C" int fgs_packer_create(int32_t n_scalars, fgs_packer** out) {
     if (!out || n_scalars < 2 || n_scalars > FGS_MAX_SCALARS) return FGS_E_INVALID;
@@ -279,7 +334,10 @@ extern "C" int fgs_packer_create(int32_t n_scalars, fgs_packer** out) {
     return FGS_OK;
 }
 
-extern "C" void fgs_packer_destroy(fgs_packer* p) { delete p; }
+extern "C" void fgs_packer_destroy(fgs_packer* p) {
+    if (p) p->unlock_all();
+    delete p;
+}
 
 extern "C" const char* fgs_packer_error(const fgs_packer* p) { return p ? p->err.c_str() : "null packer"; }
 
@@ -303,6 +361,10 @@ extern "C" int fgs_packer_pods(fgs_packer* p, const fgs_podset* pods, int64_t p0
     }
     const int rc = fgs::pack_pods(pods, p0, p1, &p->pods, &p->err);
     if (rc) return rc;
+    if (p->pin) {
+        const int rc2 = p->lock_columns();
+        if (rc2) return rc2;
+    }
     *out = &p->pods.view;
     return FGS_OK;
 }

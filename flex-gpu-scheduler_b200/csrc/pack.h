@@ -26,6 +26,7 @@ struct PackedPods {
     std::vector<uint32_t> flags, req_scalar_present;
     std::vector<int32_t> ns, pg, priority, index_annot;
     fgs_pod_table view;
+    fgs_pod_stats stats; // OR / MAX of the int64 columns, collected while packing (view.stats points here)
     void make_view();
 };
 

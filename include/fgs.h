@@ -138,6 +138,11 @@ int fgs_packer_nodes(fgs_packer* p, const fgs_snapshot* snap, int64_t n0, int64_
 int fgs_packer_pods(fgs_packer* p, const fgs_podset* pods, int64_t p0, int64_t p1,
                     const fgs_pod_table** out);
 
+/* Page-locks the packer's pod-table columns (cudaHostRegister, now and after every later fgs_packer_pods), so that the
+ * engine can DMA them to the GPU without a staging copy (fgs_pod_stats). The one packer call that needs a CUDA device.
+ * A pinned table that was handed to fgs_submit must not be packed over before that batch's fgs_collect. */
+int fgs_packer_pin(fgs_packer* p);
+
 /* ---- upload + evaluate ----------------------------------------------------------------- */
 
 /* H2D of the node table and derivation of the pod-independent columns on the GPU
@@ -181,10 +186,16 @@ int fgs_collect(fgs_engine* e, fgs_results* out);
 /* Node-sharded engines (fgs_peer_attach): fgs_evaluate, fgs_submit and fgs_collect include the two cross-shard
  * merges; every rank must make the same sequence of calls. In the submit / collect pipeline the merges run on their
  * own stream and overlap a pass of the OTHER batch in flight: the emit pass of a batch is issued by the next
- * fgs_submit, or by fgs_collect when nothing follows. fgs_resubmit evaluates again the batch that an earlier
- * fgs_submit left resident in the next pipeline slot (no staging, no H2D): steady-state measurements with the
- * tables already in HBM. */
+ * fgs_submit, or by fgs_collect when nothing follows. */
+/* fgs_resubmit evaluates again the batch that an earlier fgs_submit left resident in the next pipeline slot (no staging,
+ * no H2D): steady-state measurements with the tables already in HBM, on single and on node-sharded engines alike. The
+ * slots are walked round-robin. By default there are as many slots as batches in flight (2, or 3 with a peer group);
+ * fgs_set_resident_batches(e, n), 3 <= n <= 32, makes the ring n slots long, so that a job of n batches — BASELINE's
+ * config 5: 1 000 000 pods in 65 536-pod batches — stays resident and n fgs_resubmit calls walk it once (the limit on
+ * batches IN FLIGHT does not change); n = 0 restores the default. A batch staged before the node table last changed is
+ * refused (FGS_E_STATE). */
 int fgs_resubmit(fgs_engine* e, const fgs_eval_opts* opts);
+int fgs_set_resident_batches(fgs_engine* e, int32_t n);
 
 /* The same evaluation in stages, for node-sharded multi-GPU runs (one engine per GPU/process):
  *   fgs_stage_pods → fgs_pass_reduce → [merge reduce_max / reduce_sum across shards]

@@ -224,6 +224,22 @@ typedef struct fgs_node_table {
 #define FGS_PF_MEM_LIMIT 2u  /* a container has a flex memory limit key */
 #define FGS_PF_REQ_NONE 4u   /* fit.go:270-275: request is all zero and has no scalar keys */
 
+/* Optional companion of a pod table: what the engine's staging pass would otherwise compute by reading every value —
+ * the OR and the MAX of each int64 column (they pick the exact power-of-two shifts of the int32 kernels) — and whether
+ * the columns lie in page-locked host memory. With both, fgs_submit / fgs_evaluate copy the columns to the GPU by DMA
+ * straight from the table (no host pass, no staging copy): the table must then stay untouched until the batch has been
+ * collected. The packer fills it (fgs_packer_pods; FGS_POD_STATS_PINNED after fgs_packer_pin). A caller that builds
+ * tables itself may pass supersets: or_bits with extra bits and max_val too high are safe, missing bits are not.
+ * Column index: 0 flex_gpu_limit, 1 flex_mem_limit, 2 req_mcpu, 3 req_mem, 4 req_eph, 5 nz_mcpu, 6 nz_mem, 7 unused,
+ * 8+s req_scalar[s]. */
+#define FGS_POD_STATS_PINNED 1u
+typedef struct fgs_pod_stats {
+    uint64_t or_bits[8 + FGS_MAX_SCALARS];
+    int64_t max_val[8 + FGS_MAX_SCALARS];
+    uint32_t present_or; /* OR of req_scalar_present */
+    uint32_t flags;      /* FGS_POD_STATS_* */
+} fgs_pod_stats;
+
 typedef struct fgs_pod_table {
     int64_t n_pods;
     int32_t n_scalars;
@@ -250,6 +266,8 @@ typedef struct fgs_pod_table {
     /* optional (the packer leaves it NULL): pod UIDs, so that a pod that is itself nominated does not yield to
      * itself in the nominated-pod filter pass (runtime/framework.go:812) */
     const int64_t* uid;
+    /* optional (NULL = the engine reads the columns itself): see fgs_pod_stats */
+    const fgs_pod_stats* stats;
 } fgs_pod_table;
 
 #ifdef __cplusplus

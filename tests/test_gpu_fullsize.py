@@ -145,3 +145,129 @@ def test_config3_and_4_full_size_against_oracle_sample(gpu_ok, oracle):
     ref = oracle.quota_prefilter(s4.pending, s4.quotas)
     assert np.array_equal(code, ref)
     eng.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# BASELINE.json's configurations at their stated sizes against the oracle: C1 and C2 exhaustively — every
+# (pod,node) pair —, C4 and C5 on hashed blocks of pods × ALL nodes. The planes stay on the device; the oracle's rows go
+# up in chunks and are compared there.
+# ---------------------------------------------------------------------------------------------------------------------
+
+def _ncpu():
+    return max(1, os.cpu_count() or 1)
+
+
+def _compare_rows(torch, oracle, s, cfg, res, bm, sc, p0, p1, N, base=0, status=None):
+    """pods [p0,p1) of the synthetic set = rows [p0-base, p1-base) of the engine's current batch: feasibility bits, count,
+    error bits, totals on every feasible pair, selectHost's score, the chosen node inside the oracle's tie set, and (if
+    given) the merged Filter status plane. Returns the number of (pod,node) pairs compared."""
+    ref = oracle.evaluate(s.snapshot, s.pending, cfg, p0, p1, workers=_ncpu())
+    r0, r1 = p0 - base, p1 - base
+    shifts = torch.arange(32, device="cuda", dtype=torch.int32)
+    bits = ((bm[r0:r1].unsqueeze(-1) >> shifts) & 1).view(r1 - r0, -1)[:, :N].bool()
+    feas_ref = torch.from_numpy(ref.status == 0).cuda()
+    assert torch.equal(bits, feas_ref), f"feasibility differs in pods [{p0},{p1})"
+    assert np.array_equal(res.feasible_count[r0:r1], ref.feasible_count)
+    assert np.array_equal(res.pod_err[r0:r1], ref.pod_err)
+    if status is not None:
+        assert np.array_equal(status[r0:r1], ref.status), f"status plane differs in pods [{p0},{p1})"
+    ok = (ref.pod_err == 0) & (ref.feasible_count >= 1)  # scores of a cycle that errors out are not defined
+    m = feas_ref & torch.from_numpy(ok).cuda()[:, None]
+    tot_ref = torch.from_numpy(ref.total).cuda()
+    assert torch.equal(sc[r0:r1, :N][m], tot_ref[m]), f"scores differ in pods [{p0},{p1})"
+    idx = np.nonzero(ok)[0]
+    sel = res.selected_node[r0:r1]
+    assert np.all(sel[ref.feasible_count == 0] == -1)
+    assert np.all(sel[idx] >= 0)
+    assert np.array_equal(res.selected_score[r0:r1][idx], ref.max_total[idx])
+    assert np.array_equal(ref.total[idx, sel[idx]], ref.max_total[idx]), "selected node outside the max-score tie set"
+    assert np.all(ref.status[idx, sel[idx]] == 0)
+    return (p1 - p0) * N
+
+
+def _exhaustive(torch, oracle, cfg_id, chunk):
+    s = fgs.config_synth(cfg_id)
+    cfg = fgs.config_plugins(cfg_id)
+    N, P = s.n_nodes, s.n_pending
+    eng, table, res = _run(False, s, cfg)
+    t = eng.timings()
+    assert t["reduce_lookup"] and t["emit_int32"]
+    bm, sc = _planes(torch, eng, P)
+    status = eng.status_plane(0)
+    done = 0
+    for p0 in range(0, P, chunk):
+        done += _compare_rows(torch, oracle, s, cfg, res, bm, sc, p0, min(P, p0 + chunk), N, status=status)
+    assert done == N * P
+    eng.close()
+    return s, cfg
+
+
+def test_config1_full_size_every_pair_against_the_oracle(gpu_ok, oracle):
+    import torch
+    _exhaustive(torch, oracle, 1, 2048)  # 1 000 nodes x 10 000 pods: 1e7 pairs
+
+
+def test_config2_full_size_every_pair_against_the_oracle(gpu_ok, oracle):
+    import torch
+    _exhaustive(torch, oracle, 2, 2048)  # 5 000 nodes x 100 000 pods: 5e8 pairs
+
+
+def _hashed_blocks(n_items, block, want, seed):
+    """`want` distinct block indices of [0, n_items / block), chosen by a multiplicative hash (deterministic)"""
+    n_blocks = n_items // block
+    order = sorted(range(n_blocks), key=lambda b: ((b + seed) * 0x9E3779B1) & 0xffffffff)
+    return sorted(order[:want])
+
+
+def test_config4_full_size_quota_prefilter_and_fit_on_hashed_pods(gpu_ok, oracle):
+    """C4 as BASELINE.json states it: 20 000 nodes, 500 namespaces, 100 000 pods — CapacityScheduling.PreFilter for every
+    pod, and the FlexGPU + NodeResourcesFit evaluation on 2 048 hashed pods x all 20 000 nodes (4.1e7 pairs)"""
+    import torch
+    s = fgs.config_synth(4)
+    cfg = fgs.config_plugins(4)
+    N, P = s.n_nodes, s.n_pending
+    assert (N, P) == (20000, 100000)
+    eng, table, res = _run(False, s, cfg)
+    code = eng.quota_check(table, s.quotas)
+    ref_code = oracle.quota_prefilter(s.pending, s.quotas)
+    assert np.array_equal(code, ref_code)
+    assert set(np.unique(ref_code)) >= {0, 1}
+    bm, sc = _planes(torch, eng, P)
+    done = 0
+    for b in _hashed_blocks(P, 16, 128, 4):
+        done += _compare_rows(torch, oracle, s, cfg, res, bm, sc, 16 * b, 16 * b + 16, N)
+    assert done == 2048 * N
+    # the pods the quota admits are the ones whose evaluation the cycle goes on with: they are among the compared ones
+    assert (ref_code[[16 * b for b in _hashed_blocks(P, 16, 128, 4)]] == 0).any()
+    eng.close()
+
+
+def test_config5_one_gpu_hashed_pods_all_nodes(gpu_ok, oracle):
+    """C5 on ONE GPU: 50 000 nodes x 1 000 000 pods in 65 536-pod batches; 4 096 hashed pods (256 blocks of 16, spread over
+    all batches) x all 50 000 nodes against the oracle: 2e8 pairs = 1/244 of the matrix, whole rows, so that the per-pod
+    reductions (count, NormalizeScore maximum through the totals, selectHost) are covered too"""
+    import torch
+    s = fgs.config_synth(5)
+    cfg = fgs.config_plugins(5)
+    N, P = s.n_nodes, s.n_pending
+    assert (N, P) == (50000, 1000000)
+    eng = fgs.Engine(device=0, n_scalars=2, total_nodes=N)
+    eng.set_plugins(cfg)
+    eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot))
+    blocks = _hashed_blocks(P, 16, 256, 5)
+    BATCH = 65536
+    done = 0
+    pk = fgs.Packer(2)
+    for b0 in range(0, P, BATCH):
+        b1 = min(P, b0 + BATCH)
+        mine = [b for b in blocks if b0 <= 16 * b < b1]
+        if not mine:
+            continue
+        res = eng.evaluate(pk.pods(s.pending, b0, b1))
+        t = eng.timings()
+        assert t["reduce_lookup"] and t["emit_int32"]
+        bm, sc = _planes(torch, eng, b1 - b0)
+        for b in mine:
+            done += _compare_rows(torch, oracle, s, cfg, res, bm, sc, 16 * b, 16 * b + 16, N, base=b0)
+    assert done == 4096 * N
+    eng.close()

@@ -501,3 +501,91 @@ def test_fused_pass_equals_the_two_passes(gpu_ok, oracle, monkeypatch):
         m = feas & ok[:, None]
         assert np.array_equal(a.scores[:, :s.n_nodes][m], ref.total[m]), kw
     monkeypatch.delenv("FGS_FUSED")
+
+
+@pytest.mark.parametrize("cfg_id,S,extra", [(2, 2, {}), (1, 2, {}), (2, 4, dict(pm_extra_scalar=400))])
+def test_pinned_packer_tables_go_by_dma_and_give_the_same_results(gpu_ok, oracle, cfg_id, S, extra):
+    """fgs_packer_pin + fgs_pod_stats: the engine copies the columns straight from the packer's table (no staging pass);
+    results equal those of the staged path bit for bit, in the blocking call and in the submit / collect pipeline"""
+    s = fgs.config_synth(cfg_id, n_nodes=900, n_pending=3000, n_scalars=S, **extra)
+    cfg = fgs.config_plugins(cfg_id)
+    eng = fgs.Engine(device=0, n_scalars=S)
+    eng.set_plugins(cfg)
+    eng.upload_nodes(fgs.Packer(S).nodes(s.snapshot))
+    bounds = [(0, 3000), (5, 1030), (1030, 1031), (2000, 2960)]
+    plain = [fgs.Packer(S) for _ in bounds]
+    pinned = [fgs.Packer(S, pin=True) for _ in bounds]
+    want = [eng.evaluate(pk.pods(s.pending, a, b), want_planes=True) for pk, (a, b) in zip(plain, bounds)]
+    tabs = [pk.pods(s.pending, a, b) for pk, (a, b) in zip(pinned, bounds)]
+    for t in tabs:
+        st = t.contents.stats.contents
+        assert st.flags & 1 and st.max_val[2] > 0
+    N = s.n_nodes
+    for w, t in zip(want, tabs):
+        g = eng.evaluate(t, want_planes=True)
+        assert np.array_equal(w.feasible(N), g.feasible(N))
+        f = w.feasible(N)
+        assert np.array_equal(w.scores[:, :N][f], g.scores[:, :N][f])
+        for k in ("feasible_count", "selected_node", "selected_score", "pod_err"):
+            assert np.array_equal(getattr(w, k), getattr(g, k)), k
+    got = []
+    eng.submit(tabs[0])
+    for t in tabs[1:]:
+        eng.submit(t)
+        got.append(eng.collect())
+    got.append(eng.collect())
+    for w, g in zip(want, got):
+        for k in ("feasible_count", "selected_node", "selected_score", "pod_err"):
+            assert np.array_equal(getattr(w, k), getattr(g, k)), k
+    # the oracle on the first batch, so that the DMA path stands on its own
+    ref = oracle.evaluate(s.snapshot, s.pending, cfg, 0, 3000, workers=4)
+    assert np.array_equal(got[0].feasible_count, ref.feasible_count) and np.array_equal(got[0].pod_err, ref.pod_err)
+    ok = (ref.pod_err == 0) & (ref.feasible_count > 0)
+    assert np.array_equal(got[0].selected_score[ok], ref.max_total[ok])
+    eng.close()
+
+
+def test_resident_batches_and_resubmit_on_one_engine(gpu_ok):
+    """fgs_set_resident_batches + fgs_resubmit: a job of five batches stays resident in five pipeline slots; walking the
+    ring again (two batches in flight) returns each batch's results in order; a node update makes the resident batches
+    stale"""
+    s = fgs.config_synth(2, n_nodes=1500, n_pending=2600)
+    cfg = fgs.config_plugins(2)
+    eng = fgs.Engine(device=0)
+    eng.set_plugins(cfg)
+    pkn = fgs.Packer(2)
+    eng.upload_nodes(pkn.nodes(s.snapshot))
+    bounds = [(0, 640), (640, 1000), (1000, 1001), (1001, 2000), (2000, 2600)]
+    packers = [fgs.Packer(2) for _ in bounds]
+    tables = [pk.pods(s.pending, a, b) for pk, (a, b) in zip(packers, bounds)]
+    want = [eng.evaluate(t) for t in tables]
+    eng.set_resident_batches(len(tables))
+
+    def walk(sub):
+        out, inflight = [], 0
+        for i in range(len(tables)):
+            sub(i)
+            inflight += 1
+            if inflight == 2:
+                out.append(eng.collect())
+                inflight -= 1
+        while inflight:
+            out.append(eng.collect())
+            inflight -= 1
+        return out
+
+    first = walk(lambda i: eng.submit(tables[i]))
+    for _ in range(2):
+        again = walk(lambda i: eng.resubmit(bounds[i][1] - bounds[i][0]))
+        for w, a, b in zip(want, first, again):
+            for k in ("feasible_count", "selected_node", "selected_score", "pod_err"):
+                assert np.array_equal(getattr(w, k), getattr(a, k)) and np.array_equal(getattr(w, k), getattr(b, k)), k
+    eng.update_nodes(pkn.nodes(s.snapshot, 3, 4), [3])
+    with pytest.raises(fgs.FgsError):
+        eng.resubmit(640)
+    with pytest.raises(fgs.FgsError):
+        eng.set_resident_batches(33)
+    eng.set_resident_batches(0)
+    r = eng.evaluate(tables[1])
+    assert np.array_equal(r.feasible_count, want[1].feasible_count)
+    eng.close()
