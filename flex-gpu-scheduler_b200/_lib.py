@@ -186,6 +186,7 @@ ABI = {
     "fgs_submit": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts)]),
     "fgs_collect": (C.c_int, [C.c_void_p, C.POINTER(Results)]),
     "fgs_packer_pin": (C.c_int, [C.c_void_p]),
+    "fgs_score_masked": (C.c_int, [C.c_void_p, p_u32, C.c_int32, C.POINTER(EvalOpts), C.POINTER(Results)]),
     "fgs_resubmit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
     "fgs_set_resident_batches": (C.c_int, [C.c_void_p, C.c_int32]),
     "fgs_stage_pods": (C.c_int, [C.c_void_p, C.POINTER(PodTable)]),

@@ -276,6 +276,22 @@ class Engine:
         r.next_start_node_index = int(cr.next_start_node_index)
         return r
 
+    def score_masked(self, mask_bool, want_planes=False, **opts):
+        """fgs_score_masked: Score / NormalizeScore / selectHost of the filtered batch under the framework's feasible list.
+        mask_bool: bool [P][n_nodes of this engine] — True = the node passed every filter plugin of the profile."""
+        P = self.n_pods
+        m = np.asarray(mask_bool, bool)
+        W = (m.shape[1] + 1023) // 1024 * 1024 // 32
+        bits = np.zeros((P, W * 32), np.uint8)
+        bits[:, :m.shape[1]] = m
+        words = np.packbits(bits.reshape(P, W, 32), axis=2, bitorder="little").view(np.uint32).reshape(P, W)
+        words = np.ascontiguousarray(words)
+        r, cr = self._results(P, want_planes)
+        o = self._opts(**opts)
+        self._check(self._lib.fgs_score_masked(self._h, _ptr(words, C.c_uint32), 0, C.byref(o), C.byref(cr)))
+        r.words_per_row, r.score_row_stride = int(cr.words_per_row), int(cr.score_row_stride)
+        return r
+
     def select_victims(self, snapshot, pending, p, quotas=None, tracks_pods=True, pick=False):
         """Dry-run preemption of pending pod p on every node (fgs_select_victims):
         (status [N] FGS_PREEMPT_*, victim flags [pods in the snapshot], victims per node [N]);

@@ -133,6 +133,7 @@ void Engine::free_all() {
     if (d_special) cudaFree(d_special);
     if (d_order) cudaFree(d_order);
     if (d_order_scratch) cudaFree(d_order_scratch);
+    if (d_mask) cudaFree(d_mask);
     if (d_walk) cudaFree(d_walk);
     if (h_walk) cudaFreeHost(h_walk);
     if (d_nom) cudaFree(d_nom);
@@ -263,7 +264,7 @@ void Engine::fill_eval_params(EvalParams* p, const fgs_eval_opts* opts) const {
     if (cfg.score_mask & FGS_PL_FIT) max_total += 100 * p->w_fit;
     if (cfg.score_mask & FGS_PL_ALLOCATABLE) max_total += 100 * p->w_alloc;
     p->key_shift = (max_total < ((int64_t)1 << 23) && !p->emit_raw) ? 40 : 24;
-    p->feas_from_bitmap = sampled ? 1 : 0;
+    p->feas_from_bitmap = (sampled || masked) ? 1 : 0;
     // pods per CTA: enough CTAs for a few waves of 148 SMs × 2 resident CTAs
     const int64_t node_tiles = n_pad / kTileN;
     const int64_t target_ctas = 148 * 2 * 4;
@@ -845,6 +846,7 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
         if (rc2) return rc2;
         FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
         e->have_pods = true;
+        e->reduced = false;
         e->staged_by_dma = true;
         return FGS_OK;
     }
@@ -927,6 +929,7 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
     if (rc) return rc;
     FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
     e->have_pods = true;
+    e->reduced = false;
     return FGS_OK;
 }
 
@@ -989,6 +992,7 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_reduce before fgs_stage_pods");
     cudaSetDevice(e->device);
     e->sampled = false;
+    e->masked = false;
     e->was_fused = false;
     EvalParams p;
     e->fill_eval_params(&p, nullptr);
@@ -1060,6 +1064,7 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
         if (rc) return rc;
     }
     FGS_CUDA(e, cudaEventRecord(e->events[2], e->stream));
+    e->reduced = true;
     return FGS_OK;
 }
 
@@ -1214,6 +1219,87 @@ extern "C" int fgs_evaluate(fgs_engine* eh, const fgs_pod_table* pods, const fgs
         }
     } else if (opts->sample) { // Filter only, truncated as the reference's walk would
         rc = e->run_sampling(opts);
+        if (rc) return rc;
+    }
+    return fgs_fetch_results(eh, out);
+}
+
+// RunScorePlugins under the framework's feasible list (generic_scheduler.go:420-426, runtime/framework.go:861-933): the
+// bitmap pass A left is ANDed with the caller's mask, NormalizeScore's reductions are redone over what is left (feasible
+// counts, max FlexGPU score, Allocatable hi / lo, the special-node rows), the shards are merged, and pass B scores and
+// selects over that list.
+extern "C" int fgs_score_masked(fgs_engine* eh, const uint32_t* mask, int32_t mask_on_device, const fgs_eval_opts* opts, fgs_results* out) {
+    if (!eh || !out) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
+    if (!mask) return e->fail(FGS_E_INVALID, "fgs_score_masked: null mask");
+    if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_score_masked while submitted batches are in flight: fgs_collect them first");
+    if (!e->have_pods || !e->reduced)
+        return e->fail(FGS_E_STATE, "fgs_score_masked: no filtered batch — run fgs_evaluate with skip_pass_b (or fgs_stage_pods + fgs_pass_reduce) first");
+    if (e->was_fused) return e->fail(FGS_E_STATE, "fgs_score_masked after the fused pass: its bitmap has been scored already; stage the batch again");
+    if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_score_masked: sample / skip_pass_b make no sense here");
+    cudaSetDevice(e->device);
+    const int64_t P = e->n_pods, W = e->words_per_row;
+    if (P > 0) {
+        const uint32_t* d_m = mask;
+        if (!mask_on_device) {
+            const size_t need = sizeof(uint32_t) * (size_t)P * (size_t)W;
+            if (need > e->mask_bytes) {
+                FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+                if (e->d_mask) cudaFree(e->d_mask);
+                e->d_mask = nullptr;
+                e->mask_bytes = 0;
+                FGS_CUDA(e, cudaMalloc(&e->d_mask, need));
+                e->mask_bytes = need;
+            }
+            FGS_CUDA(e, cudaMemcpyAsync(e->d_mask, mask, need, cudaMemcpyHostToDevice, e->stream));
+            d_m = (const uint32_t*)e->d_mask;
+        }
+        if (!ft_rows_fit(W)) return e->fail(FGS_E_TOO_LARGE, "fgs_score_masked: bitmap rows beyond the kernel's shared memory (1.6 M nodes per engine)");
+        FtMaskParams mp;
+        std::memset(&mp, 0, sizeof(mp));
+        const bool orders = e->ft && e->ft->valid && e->ft->node_gen == e->node_gen && e->ft->n_pad == e->n_pad;
+        if (orders) mp.v = e->ft->v;
+        mp.have_orders = orders ? 1 : 0;
+        mp.pods = (const int64_t*)e->d_pods;
+        mp.nd = (const int64_t*)e->d_nd;
+        mp.n_pods = P;
+        mp.p_pad = e->p_pad;
+        mp.n_nodes = e->n_nodes;
+        mp.n_pad = e->n_pad;
+        mp.W = W;
+        mp.bitmap = (uint32_t*)e->d_bitmap;
+        mp.mask = d_m;
+        mp.reduce_max = (int64_t*)e->d_perpod;
+        mp.reduce_sum = (int64_t*)e->d_perpod + (int64_t)FGS_REDUCE_ROWS * e->p_pad;
+        mp.sc_flex = (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0;
+        mp.sc_alloc = (e->cfg.score_mask & FGS_PL_ALLOCATABLE) ? 1 : 0;
+        FGS_CUDA(e, ft_launch_masked(mp, e->stream));
+        e->launches++;
+        if ((e->cfg.score_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
+            launch_special_pass((const uint32_t*)e->d_bitmap, e->words_per_row, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special,
+                                (const int64_t*)e->d_pods, (int64_t*)e->d_perpod, e->n_pods, e->p_pad, e->stream);
+            e->launches++;
+            FGS_CUDA(e, cudaGetLastError());
+        }
+    }
+    e->emitted = false;
+    e->masked = true; // the int64 emit kernel recomputes Filter: it must AND the bitmap in, as after node sampling
+    int rc;
+    if (e->peer) { // node-sharded: the other shards' maxima and counts over THEIR part of the list
+        rc = e->peer_merge(0, e->stream);
+        if (rc) return rc;
+    }
+    {
+        fgs_eval_opts o;
+        std::memset(&o, 0, sizeof(o));
+        if (opts) o = *opts;
+        o.sample = 0;
+        rc = fgs_pass_emit(eh, &o);
+        if (rc) return rc;
+    }
+    if (e->peer) {
+        rc = e->peer_merge(1, e->stream);
         if (rc) return rc;
     }
     return fgs_fetch_results(eh, out);

@@ -154,6 +154,11 @@ struct Engine {
     int ensure_filter_tables(bool* use);
     void ft_free();
 
+    void* d_mask = nullptr;  // fgs_score_masked: the caller's feasible mask when it comes from the host
+    size_t mask_bytes = 0;
+    bool reduced = false;    // the staged batch has been through pass A (fgs_score_masked needs its bitmap)
+    bool masked = false;     // … and its bitmap has been cut down to the caller's feasible list since
+
     GangState* gang = nullptr;
     SeqState* seq = nullptr;
     struct PeerState* peer = nullptr; // peer_merge.cu: the other shards' exchange buffers

@@ -328,6 +328,64 @@ __global__ void __launch_bounds__(kRowsWarps * 32, NDIMS ? 5 : 4) filter_rows(co
     }
 }
 
+// The bitmap ANDed with the caller's mask — the feasible list the framework hands to RunScorePlugins when other filter
+// plugins of the profile rejected some of the engine's nodes — and everything NormalizeScore needs over what is left: one
+// warp per pod, as filter_rows. With the node orders at hand the maxima are first-feasible walks, else the set bits are
+// scanned.
+__global__ void __launch_bounds__(kRowsWarps * 32) masked_rows(const __grid_constant__ FtMaskParams prm) {
+    extern __shared__ __align__(16) uint32_t s_rows[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const i64 p = (i64)blockIdx.x * kRowsWarps + warp;
+    if (p >= prm.n_pods) return;
+    const i64 W = prm.W;
+    uint32_t* row = s_rows + (size_t)warp * W;
+    const uint32_t kind = (uint32_t)__ldg(prm.pods + (i64)PD_META * prm.p_pad + p) & 3u;
+    uint4* bm4 = (uint4*)(prm.bitmap + p * W);
+    const uint4* mk4 = (const uint4*)(prm.mask + p * W);
+    uint4* row4 = (uint4*)row;
+    const int W4 = (int)(W >> 2);
+    uint32_t cnt = 0;
+    for (int c = lane; c < W4; c += 32) {
+        uint4 a = bm4[c];
+        const uint4 m = __ldg(mk4 + c);
+        a.x &= m.x, a.y &= m.y, a.z &= m.z, a.w &= m.w;
+        row4[c] = a;
+        bm4[c] = a;
+        cnt += (uint32_t)(__popc(a.x) + __popc(a.y) + __popc(a.z) + __popc(a.w));
+    }
+    __syncwarp();
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    i64 vflex = kMin, vhi = kMin, vnlo = kMin;
+    if (cnt > 0) {
+        if (prm.sc_flex) {
+            if (kind == 0) {
+                vflex = 0;
+            } else {
+                const int o = (kind & 1u) ? FT_ORD_GSCORE : FT_ORD_MSCORE;
+                if (!(prm.have_orders && walk_order(prm.v.ord + (i64)o * prm.n_pad, prm.v.ord_val + (i64)o * prm.n_pad, prm.n_nodes, row, lane, false, &vflex)))
+                    vflex = scan_bits(row, W, prm.nd + (i64)((kind & 1u) ? ND_GPU_SCORE : ND_MEM_SCORE) * prm.n_pad, lane, false);
+            }
+        }
+        if (prm.sc_alloc) {
+            const int* ord = prm.v.ord + (i64)FT_ORD_ARAW * prm.n_pad;
+            const i64* val = prm.v.ord_val + (i64)FT_ORD_ARAW * prm.n_pad;
+            const i64* col = prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad;
+            if (!(prm.have_orders && walk_order(ord, val, prm.n_nodes, row, lane, false, &vhi))) vhi = scan_bits(row, W, col, lane, false);
+            i64 lo;
+            if (prm.have_orders && walk_order(ord, val, prm.n_nodes, row, lane, true, &lo)) vnlo = -lo;
+            else vnlo = scan_bits(row, W, col, lane, true);
+        }
+    }
+    if (lane == 0) {
+        prm.reduce_sum[p] = (i64)cnt;
+        prm.reduce_max[(i64)RR_FLEX_MAX * prm.p_pad + p] = vflex;
+        prm.reduce_max[(i64)RR_ALLOC_HI * prm.p_pad + p] = vhi;
+        prm.reduce_max[(i64)RR_ALLOC_NEGLO * prm.p_pad + p] = vnlo;
+        prm.reduce_max[(i64)RR_NEG_MAG * prm.p_pad + p] = 0; // rewritten by special_pass over the nodes that are left
+        prm.reduce_max[(i64)RR_SCORE_PANIC * prm.p_pad + p] = 0;
+    }
+}
+
 // Which pods would make the reference panic inside FlexGPU.Filter (see filter_panic_pass in kernels_narrow.cu): a pod
 // with ONE flex limit that passes the limit-sum checks (flex_gpu.go:85-98) on a node whose device state makes NewGPUNode
 // panic (:101, gpu_node.go:40-58,109,115) and, when NodeResourcesFit runs first, passes Fit too (runtime/framework.go:667-693).
@@ -532,6 +590,14 @@ cudaError_t ft_launch_rows(const FtRowsParams& p, int* rowidx, cudaStream_t st) 
         if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(filter_rows<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         filter_rows<0><<<grid, kRowsWarps * 32, smem, st>>>(p, rowidx);
     }
+    return cudaGetLastError();
+}
+
+cudaError_t ft_launch_masked(const FtMaskParams& p, cudaStream_t st) {
+    if (p.n_pods <= 0) return cudaSuccess;
+    const size_t smem = (size_t)p.W * 4 * kRowsWarps;
+    if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(masked_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    masked_rows<<<(unsigned)((p.n_pods + kRowsWarps - 1) / kRowsWarps), kRowsWarps * 32, smem, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -92,6 +92,22 @@ struct FtRowsParams {
 cudaError_t ft_launch_rows(const FtRowsParams& p, int* rowidx, cudaStream_t stream);
 bool ft_rows_fit(int64_t W); // the row of one pod fits the kernel's shared memory
 
+// bitmap &= mask per pod, then count and maxima over what is left (fgs_score_masked). v.ord / v.ord_val are read only
+// with have_orders; W = words per bitmap row.
+struct FtMaskParams {
+    FtView v;
+    int have_orders;
+    const int64_t* pods;
+    const int64_t* nd;
+    int64_t n_pods, p_pad, n_nodes, n_pad, W;
+    uint32_t* bitmap;
+    const uint32_t* mask;
+    int64_t* reduce_max;
+    int64_t* reduce_sum;
+    int sc_flex, sc_alloc;
+};
+cudaError_t ft_launch_masked(const FtMaskParams& p, cudaStream_t stream);
+
 // the pods that reach NewGPUNode's panic inside FlexGPU.Filter → RR_FILTER_PANIC, from the int64 tables (any S)
 void ft_launch_filter_panic(const int64_t* nd, const int64_t* pods, const int64_t* special, int64_t n_pad, int n_special, int64_t n_pods,
                             int64_t p_pad, int S, uint32_t filter_mask, uint32_t fit_ignored, int flex_first, int64_t* reduce_max,

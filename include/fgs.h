@@ -164,6 +164,21 @@ int fgs_update_nodes(fgs_engine* e, const fgs_node_table* rows, const int64_t* d
 int fgs_evaluate(fgs_engine* e, const fgs_pod_table* pods, const fgs_eval_opts* opts,
                  fgs_results* out);
 
+/* Score + NormalizeScore + selectHost under the framework's OWN feasible list — the PreScore / Score half of the drop-in
+ * when the profile keeps filter plugins outside this path (the reference's chart only ADDS FlexGPU to the in-tree
+ * defaults, manifests/flexgpu/templates/configmap.yaml:12-28). prioritizeNodes hands RunScorePlugins the nodes that
+ * passed EVERY filter plugin (sched/generic_scheduler.go:420-426), and each NormalizeScore runs over that list
+ * (sched/framework/runtime/framework.go:861-933: DefaultNormalizeScore's maxCount, Allocatable's hi / lo) — a shorter list
+ * than the engine's own as soon as another plugin rejected a node. Sequence: fgs_evaluate with skip_pass_b = 1 (or
+ * fgs_stage_pods + fgs_pass_reduce) answers Filter; the Go side runs its other filters; at PreScore it calls this with
+ *   mask[P][words_per_row]   bit n%32 of word n/32 of row p = node n is in pod p's feasible list (host memory, or
+ *                            device memory with mask_on_device = 1; on a node-sharded engine: this shard's nodes)
+ * The engine ANDs its bitmap with the mask (a node its own filters rejected stays out), recounts, redoes the
+ * NormalizeScore reductions over what is left, merges across shards when a peer group is attached (every rank calls),
+ * scores, selects and fills `out` as fgs_evaluate does; the planes then describe the masked list. Calling it again for
+ * the same batch can only shrink the list further. */
+int fgs_score_masked(fgs_engine* e, const uint32_t* mask, int32_t mask_on_device, const fgs_eval_opts* opts, fgs_results* out);
+
 /* The PodNominator's content: pods an earlier preemption nominated to nodes (Status.NominatedNodeName).
  * While it is set, every evaluation filters a node that has such pods the way RunFilterPluginsWithNominatedPods
  * does (sched/framework/runtime/framework.go:752-823): once with the nominated pods whose priority is >= the

@@ -70,6 +70,13 @@ int fgs_oracle_evaluate_nominated(const fgs_snapshot* snap, const fgs_podset* pe
                                   const int32_t* nom_node, const int64_t* nom_uid, const int64_t* pending_uid,
                                   fgs_oracle_out* out);
 
+/* fgs_oracle_evaluate when the profile has filter plugins OUTSIDE this path (the in-tree defaults the reference's chart
+ * keeps enabled): ext_mask[(p - p0) * N + n] == 0 means one of them rejected node n for pod p, so the node is missing
+ * from the feasible list that prioritizeNodes / RunScorePlugins are handed (generic_scheduler.go:420-426,
+ * runtime/framework.go:861-933) and NormalizeScore / selectHost run over the rest. Such a node's status reads 0xE2. */
+int fgs_oracle_evaluate_masked(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg,
+                               int64_t p0, int64_t p1, int workers, const uint8_t* ext_mask, fgs_oracle_out* out);
+
 /* numFeasibleNodesToFind (generic_scheduler.go:171-191): percentage 0 = adaptive, >= 100 = all nodes. */
 int32_t fgs_oracle_num_feasible_nodes_to_find(int32_t numAllNodes, int32_t percentageOfNodesToScore);
 

@@ -67,6 +67,9 @@ def load():
     lib.fgs_oracle_evaluate_nominated.restype = C.c_int
     lib.fgs_oracle_evaluate_nominated.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64, C.c_int64,
                                                   C.c_int, C.POINTER(L.Podset), L.p_i32, L.p_i64, L.p_i64, C.POINTER(OracleOut)]
+    lib.fgs_oracle_evaluate_masked.restype = C.c_int
+    lib.fgs_oracle_evaluate_masked.argtypes = [C.POINTER(L.Snapshot), C.POINTER(L.Podset), C.POINTER(L.PluginCfg), C.c_int64, C.c_int64,
+                                               C.c_int, L.p_u8, C.POINTER(OracleOut)]
     lib.fgs_oracle_pick_preemption_node.restype = C.c_int64
     lib.fgs_oracle_pick_preemption_node.argtypes = [C.POINTER(L.Snapshot), L.p_u8, L.p_u8, L.p_u8]
     lib.fgs_oracle_select_victims.restype = C.c_int
@@ -90,10 +93,12 @@ def num_feasible_nodes_to_find(n_nodes, percentage=0):
 
 
 def evaluate(snapshot, pending, cfg, p0=0, p1=None, workers=1, planes=("status", "total"), per_plugin=False, sample=None,
-             nominated=None):
+             nominated=None, ext_mask=None):
     """Run the oracle on pods [p0,p1). Returns numpy arrays; planes are [p1-p0][N].
     sample=(percentage, start_index): the reference's node sampling at one worker; adds r.processed [P] and
-    r.next_start (status 0xEE = node not visited)."""
+    r.next_start (status 0xEE = node not visited).
+    ext_mask: uint8 [P][N], 0 = a filter plugin outside this path rejected the node (status 0xE2): scoring, NormalizeScore
+    and selectHost run over the remaining list."""
     lib = load()
     N = int(snapshot.contents.n_nodes)
     if p1 is None:
@@ -119,7 +124,11 @@ def evaluate(snapshot, pending, cfg, p0=0, p1=None, workers=1, planes=("status",
     out.max_total = r.max_total.ctypes.data_as(L.p_i64)
     out.tie_count = r.tie_count.ctypes.data_as(L.p_i32)
     out.first_max = r.first_max.ctypes.data_as(L.p_i32)
-    if nominated is not None:  # (podset pointer, node index array, uid array or None, pending uid array or None)
+    if ext_mask is not None:
+        em = np.ascontiguousarray(ext_mask, np.uint8)
+        assert em.shape == (P, N)
+        rc = lib.fgs_oracle_evaluate_masked(snapshot, pending, C.byref(cfg), p0, p1, workers, em.ctypes.data_as(L.p_u8), C.byref(out))
+    elif nominated is not None:  # (podset pointer, node index array, uid array or None, pending uid array or None)
         nps, nnode, nuid, puid = nominated
         nnode = np.ascontiguousarray(nnode, np.int32)
         nu = np.ascontiguousarray(nuid, np.int64).ctypes.data_as(L.p_i64) if nuid is not None else None

@@ -599,6 +599,9 @@ struct Sampling {
     const int32_t* nomNode = nullptr;   // [Q] snapshot index of NominatedNodeName, < 0 none
     const int64_t* nomUid = nullptr;    // [Q] optional
     const int64_t* pendingUid = nullptr; // [P] optional
+    // the verdicts of the filter plugins OUTSIDE this path (the framework's other Filter plugins): [p1-p0][N], 0 = some
+    // other plugin rejected the node, so it is not in the list RunScorePlugins is handed (generic_scheduler.go:420-426)
+    const uint8_t* extMask = nullptr;
 };
 int evaluateImpl(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg, int64_t p0,
                  int64_t p1, int workers, fgs_oracle_out* out, const Sampling& smp);
@@ -636,6 +639,13 @@ extern "C" int fgs_oracle_evaluate_sampled(const fgs_snapshot* snap, const fgs_p
     smp.start = start_index;
     smp.processed = processed;
     return evaluateImpl(snap, pending, cfg, p0, p1, 1, out, smp);
+}
+
+extern "C" int fgs_oracle_evaluate_masked(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_plugin_cfg* cfg, int64_t p0,
+                                          int64_t p1, int workers, const uint8_t* ext_mask, fgs_oracle_out* out) {
+    Sampling smp;
+    smp.extMask = ext_mask;
+    return evaluateImpl(snap, pending, cfg, p0, p1, workers, out, smp);
 }
 
 namespace {
@@ -759,6 +769,8 @@ int evaluateImpl(const fgs_snapshot* snap, const fgs_podset* pending, const fgs_
 
         feasible.clear();
         for (i64 n = 0; n < N; ++n) {
+            // a node another filter plugin of the profile rejected: Unschedulable with a plugin id outside this path
+            if (smp.extMask && status[(size_t)n] == FGS_CODE_SUCCESS && !smp.extMask[row * N + n]) status[(size_t)n] = 0xE0 | FGS_CODE_UNSCHEDULABLE;
             if (status[(size_t)n] == FGS_CODE_SUCCESS) feasible.push_back((int)n);
             if (panicked[(size_t)n]) err |= FGS_PODERR_REF_PANIC;
         }

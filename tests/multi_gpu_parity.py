@@ -40,9 +40,9 @@ def check_calls_with_merges(fgs, eng, s, ref, P):
                 same(eng.collect(), *cuts[q.pop(0)])
         while q:
             same(eng.collect(), *cuts[q.pop(0)])
-    # the three batches left resident in the ring of slots again, without staging: the slot of the LAST batch comes
-    # first, then the ring goes on (third to last, second to last)
-    ring = [cuts[order[-1]], cuts[order[-3]], cuts[order[-2]]]
+    # the three batches left resident in the ring of slots again, without staging: the ring is walked round-robin, so
+    # the slot after the last one filled comes first — it holds the third-to-last batch
+    ring = [cuts[order[-3]], cuts[order[-2]], cuts[order[-1]]]
     for c in ring:
         eng.resubmit(c[1] - c[0])
     same(eng.collect(), *ring[0])
@@ -50,6 +50,45 @@ def check_calls_with_merges(fgs, eng, s, ref, P):
     for c in ring[1:] + ring[:1]:
         same(eng.collect(), *c)
     eng.peer_status()
+
+
+def check_growing_batches(fgs, eng, s, ref, P):
+    """a batch larger than any before makes the engine replace its bitmap / score planes while the previous batch still
+    waits for its emit pass (the sharded pipeline defers it by one submit): results must not change"""
+    sizes = [min(P, 300), min(P, 700), P]
+    packers = [fgs.Packer(2, pin=(k % 2 == 1)) for k in range(len(sizes))]
+    tabs = [pk.pods(s.pending, 0, n) for pk, n in zip(packers, sizes)]
+    for t in tabs:
+        eng.submit(t)
+    for n in sizes:
+        r = eng.collect()
+        ok = (ref.pod_err[:n] == 0) & (ref.feasible_count[:n] >= 1)
+        assert np.array_equal(r.feasible_count, ref.feasible_count[:n]), "growing batches: counts"
+        assert np.array_equal(r.pod_err, ref.pod_err[:n]), "growing batches: error bits"
+        assert np.array_equal(r.selected_score[ok], ref.max_total[:n][ok]), "growing batches: selected score"
+    eng.peer_status()
+
+
+def check_masked_scoring(fgs, eng, s, cfg, table, oracle, N, P, n0, n1):
+    """fgs_score_masked on a sharded engine: every rank passes its shard's columns of the same feasible mask"""
+    rng = np.random.default_rng(1234 + N)
+    keep = rng.uniform(0.3, 0.9, size=(P, 1))
+    mask = rng.random((P, N)) < keep
+    mask[P // 2] = False
+    eng.evaluate(table, skip_pass_b=1)
+    got = eng.score_masked(mask[:, n0:n1], want_planes=True)
+    ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=2, ext_mask=mask.astype(np.uint8))
+    feas = ref.status == 0
+    assert np.array_equal(got.feasible(n1 - n0), feas[:, n0:n1]), "masked: bitmap shard"
+    assert np.array_equal(got.feasible_count, ref.feasible_count), "masked: merged counts"
+    assert np.array_equal(got.pod_err, ref.pod_err), "masked: error bits"
+    ok = (ref.pod_err == 0) & (ref.feasible_count >= 1)
+    m = feas[:, n0:n1] & ok[:, None]
+    assert np.array_equal(got.scores[:, :n1 - n0][m], ref.total[:, n0:n1][m]), "masked: scores (normalised over the masked list of ALL shards)"
+    idx = np.nonzero(ok)[0]
+    assert np.array_equal(got.selected_score[idx], ref.max_total[idx]), "masked: selected score"
+    assert np.array_equal(ref.total[idx, got.selected_node[idx]], ref.max_total[idx]) and np.all(feas[idx, got.selected_node[idx]])
+    assert np.all(got.selected_node[ref.feasible_count == 0] == -1)
 
 
 def main():
@@ -71,6 +110,7 @@ def main():
         eng = fgs.Engine(device=local, n_scalars=2, node_index_base=n0, total_nodes=N, stream=stream.cuda_stream)
         eng.set_plugins(cfg)
         eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot, n0, n1))
+        ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=2)
         px = None
         if mode != "nccl":
             px, why = D.try_peer_exchange(torch, dist, eng, P, multicast=(mode == "multicast"))
@@ -82,6 +122,7 @@ def main():
                 eng.close()
                 continue
         if px is not None:
+            check_growing_batches(fgs, eng, s, ref, P)
             table = fgs.Packer(2).pods(s.pending)
             for _ in range(3):  # repeated merges: epochs and buffer reuse
                 res = D.evaluate_sharded(torch, dist, eng, table, peer=px)
@@ -106,9 +147,9 @@ def main():
               if pending is not None:
                   pending.wait()
               res = eng.fetch_results(want_planes=True)
-        ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=2)
         if px is not None:
             check_calls_with_merges(fgs, eng, s, ref, P)
+            check_masked_scoring(fgs, eng, s, cfg, table, oracle, N, P, n0, n1)
         feas_ref = ref.status == 0
         # this shard's planes against the oracle's columns
         assert np.array_equal(res.feasible(n1 - n0), feas_ref[:, n0:n1]), "bitmap shard"
