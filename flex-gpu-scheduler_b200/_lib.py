@@ -44,7 +44,7 @@ class Snapshot(C.Structure):
     _fields_ = [
         ("n_nodes", C.c_int64), ("n_scalars", C.c_int32), ("_pad0", C.c_int32),
         ("node_valid", p_u8), ("alloc", p_i64), ("alloc_scalar_present", p_u32), ("requested", p_i64), ("nonzero", p_i64),
-        ("pod_off", p_i64), ("pods", Podset),
+        ("pod_off", p_i64), ("pods", Podset), ("generation", p_i64),
     ]
 
 
@@ -186,6 +186,9 @@ ABI = {
     "fgs_submit": (C.c_int, [C.c_void_p, C.POINTER(PodTable), C.POINTER(EvalOpts)]),
     "fgs_collect": (C.c_int, [C.c_void_p, C.POINTER(Results)]),
     "fgs_packer_pin": (C.c_int, [C.c_void_p]),
+    "fgs_packer_node_rows": (C.c_int, [C.c_void_p, C.POINTER(Snapshot), p_i64, C.c_int64, C.POINTER(C.POINTER(NodeTable))]),
+    "fgs_sync_nodes": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Snapshot), C.c_int64, C.c_int64, p_i64]),
+    "fgs_gang_postfilter": (C.c_int, [C.c_void_p, C.POINTER(Snapshot), C.POINTER(Podset), C.POINTER(Podgroups), p_u8, p_i32]),
     "fgs_score_masked": (C.c_int, [C.c_void_p, p_u32, C.c_int32, C.POINTER(EvalOpts), C.POINTER(Results)]),
     "fgs_resubmit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
     "fgs_set_resident_batches": (C.c_int, [C.c_void_p, C.c_int32]),

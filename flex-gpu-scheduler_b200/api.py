@@ -240,6 +240,14 @@ class Engine:
         self._check(self._lib.fgs_upload_nodes(self._h, table))
         self.n_nodes = int(table.contents.n_nodes)
 
+    def sync_nodes(self, packer, snapshot, n0=0, n1=None):
+        """fgs_sync_nodes: repack and re-upload only the rows whose NodeInfo.Generation moved; returns how many"""
+        if n1 is None:
+            n1 = int(snapshot.contents.n_nodes)
+        n = C.c_int64(0)
+        self._check(self._lib.fgs_sync_nodes(self._h, packer._h, snapshot, n0, n1, C.byref(n)))
+        return int(n.value)
+
     def update_nodes(self, rows, dirty_idx):
         idx = np.ascontiguousarray(dirty_idx, dtype=np.int64)
         self._check(self._lib.fgs_update_nodes(self._h, rows, _ptr(idx, C.c_int64)))
@@ -488,6 +496,13 @@ class Engine:
         self._check(self._lib.fgs_gang_check(self._h, snapshot, pending, podgroups, _ptr(pre, C.c_uint8), _ptr(permit, C.c_uint8),
                                              _ptr(assigned, C.c_int32)))
         return pre[:P], permit[:P], assigned[:G]
+
+    def gang_postfilter(self, snapshot, pending, podgroups):
+        """Coscheduling.PostFilter's decision per pending pod (fgs_gang_postfilter): FGS_GANG_POSTFILTER_* codes"""
+        P = int(pending.contents.n_pods)
+        code = np.zeros(max(P, 1), np.uint8)
+        self._check(self._lib.fgs_gang_postfilter(self._h, snapshot, pending, podgroups, _ptr(code, C.c_uint8), None))
+        return code[:P]
 
     def quota_check(self, pod_table, quotas, nominated_table=None, pod_uid=None, nominated_uid=None):
         P = int(pod_table.contents.n_pods)

@@ -753,6 +753,7 @@ extern "C" int fgs_upload_nodes(fgs_engine* eh, const fgs_node_table* t) {
     stage_node_columns(e, t, 0, t->n_nodes, 0);
     FGS_CUDA(e, cudaMemcpyAsync(e->d_raw, e->h_raw, sizeof(int64_t) * nr_cols(e->S, e->D) * e->n_pad, cudaMemcpyHostToDevice, e->stream));
     e->have_nodes = true;
+    e->synced_gen.clear(); // fgs_sync_nodes re-fills it when the upload came from there
     return run_derive(e);
 }
 
@@ -778,6 +779,48 @@ extern "C" int fgs_update_nodes(fgs_engine* eh, const fgs_node_table* rows, cons
                                       sizeof(int64_t), (size_t)ncols, cudaMemcpyHostToDevice, e->stream));
     }
     return run_derive(e);
+}
+
+// Cache.UpdateSnapshot's incremental walk for the device tables: only the rows whose NodeInfo.Generation moved
+extern "C" int fgs_sync_nodes(fgs_engine* eh, fgs_packer* pk, const fgs_snapshot* snap, int64_t n0, int64_t n1, int64_t* n_repacked) {
+    if (!eh || !pk || !snap) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
+    if (!snap->generation) return e->fail(FGS_E_INVALID, "fgs_sync_nodes: the snapshot carries no generation column");
+    if (n0 < 0 || n1 < n0 || n1 > snap->n_nodes) return e->fail(FGS_E_INVALID, "fgs_sync_nodes: node range outside the snapshot");
+    const int64_t N = n1 - n0;
+    std::vector<int64_t> stale;
+    bool full = !e->have_nodes || e->n_nodes != N || (int64_t)e->synced_gen.size() != N;
+    if (!full) {
+        for (int64_t i = 0; i < N; ++i)
+            if (snap->generation[n0 + i] != e->synced_gen[(size_t)i]) stale.push_back(n0 + i);
+        if ((int64_t)stale.size() * 2 > N) full = true;
+    }
+    const fgs_node_table* t = nullptr;
+    int rc;
+    if (!full && !stale.empty()) {
+        rc = fgs_packer_node_rows(pk, snap, stale.data(), (int64_t)stale.size(), &t);
+        if (rc) return e->fail(rc, std::string("fgs_sync_nodes: ") + fgs_packer_error(pk));
+        if (t->n_devices > e->D) full = true; // a stale row grew more devices than the uploaded table has slots for
+    }
+    if (full) {
+        rc = fgs_packer_nodes(pk, snap, n0, n1, &t);
+        if (rc) return e->fail(rc, std::string("fgs_sync_nodes: ") + fgs_packer_error(pk));
+        rc = fgs_upload_nodes(eh, t);
+        if (rc) return rc;
+        e->synced_gen.assign(snap->generation + n0, snap->generation + n1);
+        if (n_repacked) *n_repacked = N;
+        return FGS_OK;
+    }
+    if (!stale.empty()) {
+        std::vector<int64_t> local(stale.size());
+        for (size_t i = 0; i < stale.size(); ++i) local[i] = stale[i] - n0;
+        rc = fgs_update_nodes(eh, t, local.data());
+        if (rc) return rc;
+        for (size_t i = 0; i < stale.size(); ++i) e->synced_gen[(size_t)local[i]] = snap->generation[stale[i]];
+    }
+    if (n_repacked) *n_repacked = (int64_t)stale.size();
+    return FGS_OK;
 }
 
 // async: called by fgs_submit — the staging buffers belong to a pipeline slot that is known to be free, so the
@@ -1272,6 +1315,7 @@ extern "C" int fgs_score_masked(fgs_engine* eh, const uint32_t* mask, int32_t ma
         mp.mask = d_m;
         mp.reduce_max = (int64_t*)e->d_perpod;
         mp.reduce_sum = (int64_t*)e->d_perpod + (int64_t)FGS_REDUCE_ROWS * e->p_pad;
+        mp.select_key = (int64_t*)e->d_perpod + (int64_t)(FGS_REDUCE_ROWS + 1) * e->p_pad;
         mp.sc_flex = (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0;
         mp.sc_alloc = (e->cfg.score_mask & FGS_PL_ALLOCATABLE) ? 1 : 0;
         FGS_CUDA(e, ft_launch_masked(mp, e->stream));

@@ -4,6 +4,7 @@
 
 #include <atomic>
 #include <string>
+#include <vector>
 
 #include "../../include/fgs.h"
 #include "kernels.cuh"
@@ -154,6 +155,7 @@ struct Engine {
     int ensure_filter_tables(bool* use);
     void ft_free();
 
+    std::vector<int64_t> synced_gen; // fgs_sync_nodes: NodeInfo.Generation of every row of the shard as last uploaded
     void* d_mask = nullptr;  // fgs_score_masked: the caller's feasible mask when it comes from the host
     size_t mask_bytes = 0;
     bool reduced = false;    // the staged batch has been through pass A (fgs_score_masked needs its bitmap)

@@ -383,6 +383,7 @@ __global__ void __launch_bounds__(kRowsWarps * 32) masked_rows(const __grid_cons
         prm.reduce_max[(i64)RR_ALLOC_NEGLO * prm.p_pad + p] = vnlo;
         prm.reduce_max[(i64)RR_NEG_MAG * prm.p_pad + p] = 0; // rewritten by special_pass over the nodes that are left
         prm.reduce_max[(i64)RR_SCORE_PANIC * prm.p_pad + p] = 0;
+        for (int r = 0; r < 3; ++r) prm.select_key[(i64)r * prm.p_pad + p] = 0; // the emit pass max-accumulates into these
     }
 }
 

@@ -104,6 +104,7 @@ struct FtMaskParams {
     const uint32_t* mask;
     int64_t* reduce_max;
     int64_t* reduce_sum;
+    int64_t* select_key; // [3][p_pad]: cleared, the emit pass that follows accumulates into it
     int sc_flex, sc_alloc;
 };
 cudaError_t ft_launch_masked(const FtMaskParams& p, cudaStream_t stream);

@@ -236,18 +236,34 @@ __global__ void __launch_bounds__(256) gang_check_groups(const __grid_constant__
 
 __global__ void gang_pod_codes(const int32_t* __restrict__ pend_pg, i64 n_pend, const uint8_t* __restrict__ gcode,
                                const uint8_t* __restrict__ gflags, const int32_t* __restrict__ counts, const int32_t* __restrict__ min_member,
-                               i64 G, uint8_t* __restrict__ prefilter, uint8_t* __restrict__ permit) {
+                               i64 G, uint8_t* __restrict__ prefilter, uint8_t* __restrict__ permit, uint8_t* __restrict__ postfilter) {
     const i64 p = (i64)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pend) return;
     const int32_t g = pend_pg[p];
     if (g < 0 || g >= G) {
         prefilter[p] = 0;
         permit[p] = 2; // PodGroupNotSpecified (core.go:201-203)
+        postfilter[p] = FGS_GANG_POSTFILTER_NO_GROUP;
         return;
     }
     prefilter[p] = gcode[g];
     if (!(gflags[g] & 1u)) permit[p] = 3; // PodGroupNotFound (:204-207)
     else permit[p] = (counts[G + g] + 1 >= min_member[g]) ? 0 : 1; // :209-215
+    // Coscheduling.PostFilter (pkg/coscheduling/coscheduling.go:140-176): what happens to the pod's GROUP once the pod
+    // turned out unschedulable
+    uint8_t pf;
+    const int assigned = counts[G + g], mm = min_member[g];
+    if (!(gflags[g] & 1u)) {
+        pf = FGS_GANG_POSTFILTER_NO_GROUP; // GetPodGroup found no PodGroup object (:143-147)
+    } else if (assigned >= mm) {
+        pf = FGS_GANG_POSTFILTER_ENOUGH_ASSIGNED; // :151-155
+    } else {
+        // notAssignedPercentage := float32(int(MinMember)-assigned) / float32(MinMember); <= 0.1 (:159-163): IEEE single
+        // precision division, round to nearest, as Go compiles it; 0.1 is the float32 nearest to one tenth
+        const float pct = __fdiv_rn((float)(mm - assigned), (float)mm);
+        pf = pct <= 0.1f ? FGS_GANG_POSTFILTER_SMALL_GAP : FGS_GANG_POSTFILTER_REJECT_GROUP;
+    }
+    postfilter[p] = pf;
 }
 
 // ---- quota ---------------------------------------------------------------------------------------
@@ -668,11 +684,27 @@ extern "C" int fgs_status_plane(fgs_engine* eh, uint32_t plugin, uint8_t* out) {
     return rc;
 }
 
+static int gang_check_impl(Engine* e, const fgs_snapshot* snap, const fgs_podset* pending, const fgs_podgroups* pgs, uint8_t* prefilter_code,
+                           uint8_t* permit_status, int32_t* assigned, uint8_t* postfilter_code);
+
 extern "C" int fgs_gang_check(fgs_engine* eh, const fgs_snapshot* snap, const fgs_podset* pending, const fgs_podgroups* pgs,
                               uint8_t* prefilter_code, uint8_t* permit_status, int32_t* assigned) {
     if (!eh || !snap || !pending || !pgs) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
     FGS_ENTER(e);
+    return gang_check_impl(e, snap, pending, pgs, prefilter_code, permit_status, assigned, nullptr);
+}
+
+extern "C" int fgs_gang_postfilter(fgs_engine* eh, const fgs_snapshot* snap, const fgs_podset* pending, const fgs_podgroups* pgs,
+                                   uint8_t* postfilter_code, int32_t* assigned) {
+    if (!eh || !snap || !pending || !pgs || !postfilter_code) return FGS_E_INVALID;
+    Engine* e = (Engine*)eh;
+    FGS_ENTER(e);
+    return gang_check_impl(e, snap, pending, pgs, nullptr, nullptr, assigned, postfilter_code);
+}
+
+static int gang_check_impl(Engine* e, const fgs_snapshot* snap, const fgs_podset* pending, const fgs_podgroups* pgs, uint8_t* prefilter_code,
+                           uint8_t* permit_status, int32_t* assigned, uint8_t* postfilter_code) {
     if (!e->have_nodes) return e->fail(FGS_E_STATE, "fgs_gang_check before fgs_upload_nodes");
     if (snap->n_nodes != e->n_nodes) return e->fail(FGS_E_INVALID, "fgs_gang_check: snapshot does not match the uploaded node table");
     if (snap->n_scalars != e->S || pgs->n_scalars != e->S) return e->fail(FGS_E_INVALID, "fgs_gang_check: n_scalars mismatch");
@@ -704,7 +736,7 @@ extern "C" int fgs_gang_check(fgs_engine* eh, const fgs_snapshot* snap, const fg
     const size_t in_bytes = b.off;
     const size_t o_cand = b.take(sizeof(int64_t) * K * e->n_pad), o_colmax = b.take(sizeof(int64_t) * K);
     const size_t o_counts = b.take(sizeof(int32_t) * 2 * G), o_gcode = b.take(G);
-    const size_t o_pre = b.take(NP), o_permit = b.take(NP);
+    const size_t o_pre = b.take(NP), o_permit = b.take(NP), o_post = b.take(NP);
     int rc = arena_reserve(e, b.off);
     if (rc) return rc;
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
@@ -787,18 +819,20 @@ extern "C" int fgs_gang_check(fgs_engine* eh, const fgs_snapshot* snap, const fg
         gang_pod_codes<<<(unsigned)((NP + 255) / 256), 256, 0, e->stream>>>((const int32_t*)(d + o_pend_pg), NP, (const uint8_t*)(d + o_gcode),
                                                                             (const uint8_t*)(d + o_gfl), (const int32_t*)(d + o_counts),
                                                                             (const int32_t*)(d + o_mm), G, (uint8_t*)(d + o_pre),
-                                                                            (uint8_t*)(d + o_permit));
+                                                                            (uint8_t*)(d + o_permit), (uint8_t*)(d + o_post));
         e->launches++;
     }
     FGS_CUDA(e, cudaGetLastError());
     if (NP > 0) {
         FGS_CUDA(e, cudaMemcpyAsync(h + o_pre, d + o_pre, NP, cudaMemcpyDeviceToHost, e->stream));
         FGS_CUDA(e, cudaMemcpyAsync(h + o_permit, d + o_permit, NP, cudaMemcpyDeviceToHost, e->stream));
+        FGS_CUDA(e, cudaMemcpyAsync(h + o_post, d + o_post, NP, cudaMemcpyDeviceToHost, e->stream));
     }
     if (G > 0) FGS_CUDA(e, cudaMemcpyAsync(h + o_counts, d + o_counts, sizeof(int32_t) * 2 * G, cudaMemcpyDeviceToHost, e->stream));
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
     if (prefilter_code && NP) std::memcpy(prefilter_code, h + o_pre, NP);
     if (permit_status && NP) std::memcpy(permit_status, h + o_permit, NP);
+    if (postfilter_code && NP) std::memcpy(postfilter_code, h + o_post, NP);
     if (assigned && G) std::memcpy(assigned, h + o_counts + sizeof(int32_t) * G, sizeof(int32_t) * G);
     return FGS_OK;
 }

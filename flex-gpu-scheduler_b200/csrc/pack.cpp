@@ -65,7 +65,26 @@ void PackedPods::make_view() {
     view.stats = &stats;
 }
 
-static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::string* err);
+// rows == NULL: every row of `snap` in order; else table row i = snapshot row rows[i] (k of them)
+static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::string* err, const int64_t* rows = nullptr, int64_t k = 0);
+
+int pack_node_rows(const fgs_snapshot* snap, const int64_t* rows, int64_t k, PackedNodes* out, std::string* err) {
+    if (!snap || snap->n_nodes < 0 || snap->n_scalars < 2 || snap->n_scalars > FGS_MAX_SCALARS) {
+        *err = "pack_node_rows: bad snapshot header";
+        return FGS_E_INVALID;
+    }
+    if (k < 0 || (k > 0 && !rows)) {
+        *err = "pack_node_rows: bad row list";
+        return FGS_E_INVALID;
+    }
+    for (int64_t i = 0; i < k; ++i)
+        if (rows[i] < 0 || rows[i] >= snap->n_nodes) {
+            *err = "pack_node_rows: row outside the snapshot";
+            return FGS_E_INVALID;
+        }
+    static const int64_t none = 0;
+    return pack_nodes_all(snap, out, err, k ? rows : &none, k);
+}
 
 int pack_nodes(const fgs_snapshot* snap, int64_t n0, int64_t n1, PackedNodes* out, std::string* err) {
     if (!snap || snap->n_nodes < 0 || snap->n_scalars < 2 || snap->n_scalars > FGS_MAX_SCALARS) {
@@ -89,12 +108,13 @@ int pack_nodes(const fgs_snapshot* snap, int64_t n0, int64_t n1, PackedNodes* ou
     return pack_nodes_all(&sub, out, err);
 }
 
-static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::string* err) {
-    const int64_t N = snap->n_nodes;
+static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::string* err, const int64_t* rows, int64_t k) {
+    const int64_t N = rows ? k : snap->n_nodes;
     const int S = snap->n_scalars, AW = 4 + S, RW = 3 + S;
     // device slots = largest gpu count on any node
     int D = 1;
-    for (int64_t n = 0; n < N; ++n) {
+    for (int64_t i = 0; i < N; ++i) {
+        const int64_t n = rows ? rows[i] : i;
         if (!((snap->alloc_scalar_present[n] >> FGS_SCALAR_FLEX_GPU) & 1u)) continue;
         const int64_t g = snap->alloc[n * AW + 4 + FGS_SCALAR_FLEX_GPU];
         if (g > FGS_MAX_DEVICES) {
@@ -117,7 +137,8 @@ static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::strin
     t.flags.assign((size_t)N, 0);
 
     const fgs_podset* ps = &snap->pods;
-    for (int64_t n = 0; n < N; ++n) {
+    for (int64_t i = 0; i < N; ++i) {
+        const int64_t n = rows ? rows[i] : i; // snapshot row → table row i
         const int64_t* al = snap->alloc + n * AW;
         const int64_t* rq = snap->requested + n * RW;
         for (int k = 0; k < AW; ++k)
@@ -130,27 +151,27 @@ static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::strin
                 *err = "pack_nodes: requested of node " + std::to_string(n) + " out of range";
                 return FGS_E_RANGE;
             }
-        t.alloc_mcpu[(size_t)n] = al[0];
-        t.alloc_mem[(size_t)n] = al[1];
-        t.alloc_eph[(size_t)n] = al[2];
-        t.alloc_pods[(size_t)n] = al[3];
-        t.req_mcpu[(size_t)n] = rq[0];
-        t.req_mem[(size_t)n] = rq[1];
-        t.req_eph[(size_t)n] = rq[2];
-        t.nz_mcpu[(size_t)n] = snap->nonzero[n * 2 + 0];
-        t.nz_mem[(size_t)n] = snap->nonzero[n * 2 + 1];
-        if (!in_range(t.nz_mcpu[(size_t)n]) || !in_range(t.nz_mem[(size_t)n])) {
+        t.alloc_mcpu[(size_t)i] = al[0];
+        t.alloc_mem[(size_t)i] = al[1];
+        t.alloc_eph[(size_t)i] = al[2];
+        t.alloc_pods[(size_t)i] = al[3];
+        t.req_mcpu[(size_t)i] = rq[0];
+        t.req_mem[(size_t)i] = rq[1];
+        t.req_eph[(size_t)i] = rq[2];
+        t.nz_mcpu[(size_t)i] = snap->nonzero[n * 2 + 0];
+        t.nz_mem[(size_t)i] = snap->nonzero[n * 2 + 1];
+        if (!in_range(t.nz_mcpu[(size_t)i]) || !in_range(t.nz_mem[(size_t)i])) {
             *err = "pack_nodes: non-zero requested of node " + std::to_string(n) + " out of range";
             return FGS_E_RANGE;
         }
         const uint32_t present = snap->alloc_scalar_present[n];
-        t.alloc_scalar_present[(size_t)n] = present;
+        t.alloc_scalar_present[(size_t)i] = present;
         for (int s = 0; s < S; ++s) {
-            t.alloc_scalar[(size_t)(s * N + n)] = ((present >> s) & 1u) ? al[4 + s] : 0;
-            t.req_scalar[(size_t)(s * N + n)] = rq[3 + s];
+            t.alloc_scalar[(size_t)(s * N + i)] = ((present >> s) & 1u) ? al[4 + s] : 0;
+            t.req_scalar[(size_t)(s * N + i)] = rq[3 + s];
         }
         const int64_t p0 = snap->pod_off[n], p1 = snap->pod_off[n + 1];
-        t.num_pods[(size_t)n] = p1 - p0;
+        t.num_pods[(size_t)i] = p1 - p0;
 
         uint32_t fl = 0;
         if (snap->node_valid[n]) fl |= FGS_NF_VALID;
@@ -181,7 +202,7 @@ static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::strin
             }
             if (l.gpu_exist) mono |= 1u << idx;
             if (l.mem_exist) {
-                int64_t& u = t.used_mem[(size_t)((int64_t)idx * N + n)];
+                int64_t& u = t.used_mem[(size_t)((int64_t)idx * N + i)];
                 u = wrap_add(u, l.mem);
             }
         }
@@ -190,14 +211,14 @@ static int pack_nodes_all(const fgs_snapshot* snap, PackedNodes* out, std::strin
             return FGS_E_RANGE;
         }
         for (int d = 0; d < D; ++d)
-            if (!in_range(t.used_mem[(size_t)((int64_t)d * N + n)])) {
+            if (!in_range(t.used_mem[(size_t)((int64_t)d * N + i)])) {
                 *err = "pack_nodes: per-device used memory of node " + std::to_string(n) + " out of range";
                 return FGS_E_RANGE;
             }
-        t.flex_gpu_sum[(size_t)n] = gsum;
-        t.flex_mem_sum[(size_t)n] = msum;
-        t.monopoly_mask[(size_t)n] = mono;
-        t.flags[(size_t)n] = fl;
+        t.flex_gpu_sum[(size_t)i] = gsum;
+        t.flex_mem_sum[(size_t)i] = msum;
+        t.monopoly_mask[(size_t)i] = mono;
+        t.flags[(size_t)i] = fl;
     }
     t.make_view();
     return FGS_OK;
@@ -348,6 +369,18 @@ extern "C" int fgs_packer_nodes(fgs_packer* p, const fgs_snapshot* snap, int64_t
         return FGS_E_INVALID;
     }
     const int rc = fgs::pack_nodes(snap, n0, n1, &p->nodes, &p->err);
+    if (rc) return rc;
+    *out = &p->nodes.view;
+    return FGS_OK;
+}
+
+extern "C" int fgs_packer_node_rows(fgs_packer* p, const fgs_snapshot* snap, const int64_t* rows, int64_t n_rows, const fgs_node_table** out) {
+    if (!p || !out) return FGS_E_INVALID;
+    if (snap && snap->n_scalars != p->S) {
+        p->err = "fgs_packer_node_rows: snapshot n_scalars differs from the packer's";
+        return FGS_E_INVALID;
+    }
+    const int rc = fgs::pack_node_rows(snap, rows, n_rows, &p->nodes, &p->err);
     if (rc) return rc;
     *out = &p->nodes.view;
     return FGS_OK;

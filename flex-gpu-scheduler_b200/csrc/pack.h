@@ -32,6 +32,8 @@ struct PackedPods {
 
 // Both return FGS_OK or a negative FGS_E_* with `err` set.
 int pack_nodes(const fgs_snapshot* snap, int64_t n0, int64_t n1, PackedNodes* out, std::string* err);
+// table row i = snapshot row rows[i]: the rows a generation diff found stale (fgs_sync_nodes)
+int pack_node_rows(const fgs_snapshot* snap, const int64_t* rows, int64_t k, PackedNodes* out, std::string* err);
 int pack_pods(const fgs_podset* pods, int64_t p0, int64_t p1, PackedPods* out, std::string* err);
 
 // Range rule shared by the packer and the table-level entry points: every quantity must satisfy

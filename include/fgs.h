@@ -131,6 +131,11 @@ const char* fgs_packer_error(const fgs_packer* p);
 int fgs_packer_nodes(fgs_packer* p, const fgs_snapshot* snap, int64_t n0, int64_t n1,
                      const fgs_node_table** out);
 
+/* The same for an arbitrary list of snapshot rows: table row i = snapshot row rows[i] (what a generation diff found
+ * stale; the table then goes to fgs_update_nodes with `rows` as the dirty indices — fgs_sync_nodes does both). */
+int fgs_packer_node_rows(fgs_packer* p, const fgs_snapshot* snap, const int64_t* rows, int64_t n_rows,
+                         const fgs_node_table** out);
+
 /* Pods [p0, p1) of the podset → SoA pod table (a batch; 0..n_pods = all). Takes over podResourceLimit (flex_gpu.go:121-131),
  * computePodResourceRequest (fit.go:162-180) and calculatePodResourceRequest
  * (sched/framework/plugins/noderesources/resource_allocation.go:119-143).
@@ -153,6 +158,15 @@ int fgs_upload_nodes(fgs_engine* e, const fgs_node_table* t);
 
 /* Same for a subset of rows: `rows` has n_dirty rows, row r replaces node dirty_idx[r]. */
 int fgs_update_nodes(fgs_engine* e, const fgs_node_table* rows, const int64_t* dirty_idx);
+
+/* The incremental form of the two calls above, keyed by NodeInfo.Generation as the scheduler cache's own snapshot update
+ * is (sched/internal/cache/cache.go:197-276: UpdateSnapshot walks the NodeInfos whose Generation is newer than the
+ * snapshot's and re-clones only those): the engine remembers the generation of every row of its shard [n0, n1) as of
+ * the last call; rows whose snap->generation differs are packed (fgs_packer_node_rows) and patched (fgs_update_nodes),
+ * the rest stays on the GPU. The first call, a shard of another size, a stale row with more device slots than the
+ * uploaded table, or more than half of the rows stale fall back to a full pack + fgs_upload_nodes. Needs
+ * snap->generation. n_repacked (optional) <- rows packed and copied by this call. */
+int fgs_sync_nodes(fgs_engine* e, fgs_packer* p, const fgs_snapshot* snap, int64_t n0, int64_t n1, int64_t* n_repacked);
 
 /* One batched scheduling evaluation = for every pod: findNodesThatPassFilters over all nodes
  * (sched/generic_scheduler.go:266-338 with percentageOfNodesToScore=100; FlexGPU.Filter
@@ -347,6 +361,20 @@ int fgs_reserve(fgs_engine* e, const fgs_pod_table* pods, const int32_t* node, i
 int fgs_gang_check(fgs_engine* e, const fgs_snapshot* snap, const fgs_podset* pending,
                    const fgs_podgroups* pgs, uint8_t* prefilter_code, uint8_t* permit_status,
                    int32_t* assigned);
+
+/* Coscheduling.PostFilter's decision for every pending pod, should the pod turn out unschedulable
+ * (pkg/coscheduling/coscheduling.go:140-176): CalculateAssignedPods of the pod's group (core.go:301-318) against
+ * Spec.MinMember, then the gap test notAssignedPercentage = float32(MinMember - assigned) / float32(MinMember) <= 0.1 in
+ * IEEE single precision as Go evaluates it. postfilter_code[p] = FGS_GANG_POSTFILTER_*; only REJECT_GROUP makes the plugin
+ * reject the group's waiting pods, add the group to lastDeniedPG and drop it from permittedPG (:168-172) — the Go side
+ * does that with the code in hand; every code returns Unschedulable to the framework. assigned[g] (optional) as in
+ * fgs_gang_check. Same inputs and preconditions as fgs_gang_check. */
+#define FGS_GANG_POSTFILTER_NO_GROUP 1        /* "can not find pod group" (:143-147): no label, or no PodGroup object */
+#define FGS_GANG_POSTFILTER_ENOUGH_ASSIGNED 2 /* assigned >= MinMember (:151-155): the group stands */
+#define FGS_GANG_POSTFILTER_SMALL_GAP 3       /* gap <= 10 % (:159-163): later pods may still complete the group */
+#define FGS_GANG_POSTFILTER_REJECT_GROUP 4    /* "PodGroup … gets rejected due to Pod … is unschedulable even after PostFilter" */
+int fgs_gang_postfilter(fgs_engine* e, const fgs_snapshot* snap, const fgs_podset* pending, const fgs_podgroups* pgs,
+                        uint8_t* postfilter_code, int32_t* assigned);
 
 /* CapacityScheduling.PreFilter for every pending pod
  * (pkg/capacityscheduling/capacity_scheduling.go:201-275; elasticquota.go:40-51,90-100,161-181).

@@ -135,6 +135,10 @@ typedef struct fgs_snapshot {
     const int64_t* nonzero;               /* [N][2]   NodeInfo.NonZeroRequested {mcpu, mem} */
     const int64_t* pod_off;               /* [N+1] rows of `pods` on node n (snapshot list order) */
     fgs_podset pods;                      /* NodeInfo.Pods of all nodes, grouped by node */
+    /* optional (NULL = not tracked): NodeInfo.Generation (sched/framework/types.go:396-398), the counter the scheduler
+     * cache bumps whenever a NodeInfo changes; fgs_sync_nodes repacks and re-uploads only the rows whose generation moved
+     * since its last call, as Cache.UpdateSnapshot does for the Go snapshot (sched/internal/cache/cache.go:197-276) */
+    const int64_t* generation;            /* [N] */
 } fgs_snapshot;
 
 typedef struct fgs_podgroups {

@@ -589,3 +589,126 @@ def test_resident_batches_and_resubmit_on_one_engine(gpu_ok):
     r = eng.evaluate(tables[1])
     assert np.array_equal(r.feasible_count, want[1].feasible_count)
     eng.close()
+
+
+def test_gang_postfilter_decision_around_the_ten_percent_gap(gpu_ok):
+    """Coscheduling.PostFilter (pkg/coscheduling/coscheduling.go:140-176): assigned >= MinMember keeps the group, a gap of
+    at most 10 % — float32(MinMember - assigned) / float32(MinMember) <= 0.1 in single precision, as Go computes it —
+    keeps it too, anything else rejects the whole group. Hand cases on both sides of the edge, plus a synthetic
+    cluster against the same formula in numpy float32."""
+    cases = [(10, 9), (10, 8), (11, 10), (11, 9), (20, 18), (20, 17), (9, 8), (30, 27), (30, 26), (7, 7), (5, 6), (1000, 900), (1000, 899),
+             (41, 37), (3, 0), (1, 0)]
+    groups = [dict(min_member=mm, ns=0) for mm, _ in cases] + [dict(min_member=4, ns=0, exists=False)]
+    on_node = []
+    for g, (mm, a) in enumerate(cases):
+        on_node += [B.pod([B.ctr({"cpu": 10})], pg=g, ns=0, node_name=True) for _ in range(a)]
+    on_node += [B.pod([B.ctr({"cpu": 10})], pg=0, ns=0, node_name=False)]  # not assigned: Spec.NodeName is empty (core.go:311)
+    on_node += [B.pod([B.ctr({"cpu": 10})], pg=1, ns=3, node_name=True)]   # another namespace: not a member
+    snap = B.build_snapshot([B.node({"cpu": 10 ** 7, "memory": 1 << 40, "pods": 10 ** 5}, on_node)])
+    pend = B.build_podset([B.pod([B.ctr({"cpu": 10})], pg=g, ns=0) for g in range(len(groups))] + [B.pod([B.ctr({"cpu": 10})], pg=-1, ns=0)])
+    pgs = B.build_podgroups(groups)
+    eng = fgs.Engine(device=0)
+    eng.upload_nodes(fgs.Packer(2).nodes(snap.ptr))
+    code = eng.gang_postfilter(snap.ptr, pend.ptr, pgs.ptr)
+    want = []
+    for mm, a in cases:
+        if a >= mm:
+            want.append(2)
+        else:
+            want.append(3 if np.float32(mm - a) / np.float32(mm) <= np.float32(0.1) else 4)
+    want += [1, 1]  # PodGroup object not found; pod without the label
+    assert list(code) == want, (list(code), want)
+    assert want[:9] == [3, 4, 3, 4, 3, 4, 4, 3, 4]  # the edge itself, written out: 1/10, 2/20 and 3/30 pass, 1/9 and 3/20 do not
+    eng.close()
+    s = fgs.config_synth(3, n_nodes=800, n_pending=3000, n_groups=120, n_namespaces=5)
+    eng = fgs.Engine(device=0)
+    eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot))
+    code = eng.gang_postfilter(s.snapshot, s.pending, s.podgroups)
+    _, _, assigned = eng.gang_check(s.snapshot, s.pending, s.podgroups)
+    G_ = int(s.podgroups.contents.n_groups)
+    pg = np.ctypeslib.as_array(s.pending.contents.pg, shape=(s.n_pending,))
+    mm = np.ctypeslib.as_array(s.podgroups.contents.min_member, shape=(G_,))
+    ex = np.ctypeslib.as_array(s.podgroups.contents.exists, shape=(G_,))
+    exp = np.ones(s.n_pending, np.uint8)
+    has = pg >= 0
+    g = pg[has]
+    a = assigned[g]
+    gap = ((mm[g] - a).astype(np.float32) / mm[g].astype(np.float32)) <= np.float32(0.1)
+    exp[has] = np.where(ex[g] == 0, 1, np.where(a >= mm[g], 2, np.where(gap, 3, 4)))
+    assert np.array_equal(code, exp)
+    assert set(np.unique(code)) >= {2, 4}
+    eng.close()
+
+
+def test_sync_nodes_repacks_only_the_rows_whose_generation_moved(gpu_ok, oracle):
+    """fgs_sync_nodes: the device tables follow the snapshot the way Cache.UpdateSnapshot follows the cache
+    (vendor/k8s.io/kubernetes/pkg/scheduler/internal/cache/cache.go:197-276) — by NodeInfo.Generation. After every sync
+    the evaluation equals the oracle's on the NEW snapshot and that of an engine that uploaded everything."""
+    import random
+    from oracle import cross_fuzz as F
+    rng = random.Random(99)
+    S = 2
+    nodes = [F.rand_node(rng, S) for _ in range(300)]
+    for nd in nodes:  # at most 8 devices at first, so that a later 11-device row overflows the uploaded slots
+        if nd["alloc"].get(("scalar", 0), 0) > 8:
+            nd["alloc"][("scalar", 0)] = 8
+    pods = [F.rand_pod(rng, S) for _ in range(200)]
+    pend = B.build_podset(pods, S)
+    cfg = fgs.config_plugins(2)
+    eng = fgs.Engine(device=0)
+    eng.set_plugins(cfg)
+    pk = fgs.Packer(S)
+    table = fgs.Packer(S).pods(pend.ptr)
+    gen = np.arange(1, len(nodes) + 1, dtype=np.int64)
+    next_gen = [len(nodes) + 1]
+
+    def sync_and_check(expect_repacked):
+        snap = B.build_snapshot(nodes, S)
+        snap.struct.generation = gen.ctypes.data_as(L.p_i64)
+        n = eng.sync_nodes(pk, snap.ptr)
+        assert n == expect_repacked, (n, expect_repacked)
+        got = eng.evaluate(table, want_planes=True)
+        ref = oracle.evaluate(snap.ptr, pend.ptr, cfg, workers=4)
+        N = len(nodes)
+        assert np.array_equal(got.feasible(N), ref.status == 0)
+        assert np.array_equal(got.feasible_count, ref.feasible_count) and np.array_equal(got.pod_err, ref.pod_err)
+        ok = (ref.pod_err == 0) & (ref.feasible_count >= 1)
+        m = (ref.status == 0) & ok[:, None]
+        assert np.array_equal(got.scores[:, :N][m], ref.total[m])
+        fresh = fgs.Engine(device=0)
+        fresh.set_plugins(cfg)
+        fresh.upload_nodes(fgs.Packer(S).nodes(snap.ptr))
+        want = fresh.evaluate(table)
+        assert np.array_equal(want.selected_score[ok], got.selected_score[ok]) and np.array_equal(want.feasible_count, got.feasible_count)
+        fresh.close()
+
+    def touch(i, node):
+        nodes[i] = node
+        gen[i] = next_gen[0]
+        next_gen[0] += 1
+
+    sync_and_check(300)          # the first call uploads everything
+    sync_and_check(0)            # nothing moved
+    for i in (3, 77, 299):       # three NodeInfos changed (pods added / removed, allocatable edited)
+        nd = F.rand_node(rng, S)
+        if nd["alloc"].get(("scalar", 0), 0) > 8:
+            nd["alloc"][("scalar", 0)] = 8
+        touch(i, nd)
+    sync_and_check(3)
+    gen[5] = next_gen[0]         # a generation bump without a change is repacked too (the cache cannot tell)
+    next_gen[0] += 1
+    sync_and_check(1)
+    big = F.rand_node(rng, S)
+    big["alloc"][("scalar", 0)] = 11   # more devices than the uploaded table has slots: everything goes up again
+    big["alloc"][("scalar", 1)] = 11 * 16384
+    touch(8, big)
+    sync_and_check(300)
+    for i in range(0, 300, 2):   # more than half stale: a full upload is cheaper than 150 patches
+        gen[i] = next_gen[0]
+        next_gen[0] += 1
+    touch(1, F.rand_node(rng, S))
+    sync_and_check(300)
+    snap = B.build_snapshot(nodes, S)  # no generation column: refused
+    with pytest.raises(fgs.FgsError):
+        eng.sync_nodes(pk, snap.ptr)
+    eng.close()

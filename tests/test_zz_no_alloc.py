@@ -24,9 +24,9 @@ pytestmark = pytest.mark.gpu
 S = 3
 
 
-def _device_tables(torch, synth, pod_table):
+def _device_tables(torch, quotas, pod_table):
     """Copy the quota table and the pods' request columns into torch-owned device memory."""
-    q = synth.quotas.contents
+    q = quotas.contents
     NS, W = int(q.n_ns), 2 + S
     P = int(pod_table.contents.n_pods)
     pt = pod_table.contents
@@ -62,7 +62,7 @@ def _call_static(lib, torch, t, NS, P):
     return t["code"].cpu().numpy()
 
 
-def test_static_quota_check_matches_engine_twice(gpu_ok):
+def test_static_quota_check_matches_engine_twice(gpu_ok, oracle):
     import torch
     lib = L.load()
     eng = fgs.Engine(device=0, n_scalars=S)
@@ -74,10 +74,32 @@ def test_static_quota_check_matches_engine_twice(gpu_ok):
         pk = fgs.Packer(S)
         table = pk.pods(s.pending)
         want = eng.quota_check(table, s.quotas)  # the existing entry point (allocates its own arena)
-        t, NS, P = _device_tables(torch, s, table)
+        t, NS, P = _device_tables(torch, s.quotas, table)
         got = _call_static(lib, torch, t, NS, P)
         assert np.array_equal(got, want)  # integer verdicts: exact equality is the tolerance
+        assert np.array_equal(got, oracle.quota_prefilter(s.pending, s.quotas))  # … and the CPU restatement of the Go plugin agrees
         assert set(np.unique(want)) >= {0, 1}
+    # a third call on a hand-made table that reaches every verdict, the "aggregated used over the sum of Min" one
+    # included (capacity_scheduling.go:262-272), which the synthetic quotas above never produce
+    import builders as B
+    GPU = ("scalar", 0)
+    quotas = B.build_quotas({0: dict(min={"cpu": 1000, GPU: 2}, max={"cpu": 5000, GPU: 8}, used={"cpu": 900, GPU: 2}),
+                             1: dict(min={"cpu": 1000, GPU: 2}, max={"cpu": 1200, GPU: 8}, used={"cpu": 900, GPU: 1})}, n_ns=4, S=S)
+    pods = [B.pod([B.ctr({"cpu": 100})], ns=0),            # stays within its Min: Success
+            B.pod([B.ctr({"cpu": 300})], ns=0),            # over its Min and the cluster's Min is spent: code 2
+            B.pod([B.ctr({"cpu": 400})], ns=1),            # over its Max: code 1
+            B.pod([B.ctr({"cpu": 50, GPU: 1})], ns=0),     # the scalar key: used 2 + 1 over Min 2, aggregate 4 > 4 is false … cpu 950 <= 1000
+            B.pod([B.ctr({"cpu": 50, GPU: 2})], ns=0),     # aggregate gpu 3 + 2 > 4: code 2
+            B.pod([B.ctr({"cpu": 10 ** 6})], ns=3)]        # a namespace without an ElasticQuota: Success
+    pend = B.build_podset(pods, S)
+    table = fgs.Packer(S).pods(pend.ptr)
+    want = eng.quota_check(table, quotas.ptr)
+    ref = oracle.quota_prefilter(pend.ptr, quotas.ptr)
+    assert np.array_equal(want, ref)
+    assert 2 in set(ref) and 1 in set(ref) and 0 in set(ref), list(ref)
+    t, NS, P = _device_tables(torch, quotas.ptr, table)
+    got = _call_static(lib, torch, t, NS, P)
+    assert np.array_equal(got, ref)
     eng.close()
 
 
