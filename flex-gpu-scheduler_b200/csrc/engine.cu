@@ -151,7 +151,7 @@ void Engine::free_all() {
         }
         for (auto& sl : slots) {
             if (sl.ev_done) cudaEventDestroy(sl.ev_done);
-            for (cudaEvent_t ev : {sl.ev_reduce, sl.ev_merge1, sl.ev_emit, sl.ev_merge2})
+            for (cudaEvent_t ev : {sl.ev_reduce, sl.ev_merge1, sl.ev_emit, sl.ev_merge2, sl.ev_t0, sl.ev_emit0})
                 if (ev) cudaEventDestroy(ev);
         }
         if (merge_stream) cudaStreamDestroy(merge_stream);
@@ -328,6 +328,11 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
         e->no_fused = !(nf && nf[0] == '1');
         const char* nd_ = getenv("FGS_NO_DMA");
         e->no_dma = nd_ && nd_[0] == '1';
+        const char* tr = getenv("FGS_PIPE_TRACE");
+        if (tr && tr[0]) {
+            e->pipe_trace = true;
+            e->pipe_trace_path = std::string(tr) + "." + std::to_string(c->device);
+        }
         const char* fm = getenv("FGS_FILTER");
         e->filter_mode = fm ? (fm[0] == 'c' ? 1 : (fm[0] == 'l' ? 2 : 0)) : 0;
         const char* ht = getenv("FGS_HOST_THREADS");
@@ -393,6 +398,8 @@ extern "C" void fgs_destroy(fgs_engine* eh) {
     Engine* e = (Engine*)eh;
     cudaSetDevice(e->device);
     cudaStreamSynchronize(e->stream);
+    e->trace_dump();
+    if (e->trace_epoch) cudaEventDestroy(e->trace_epoch);
     e->free_all();
     delete e;
 }
@@ -636,6 +643,30 @@ int Engine::ensure_filter_tables(bool* use) {
     *use = ft->valid && ft_rows_fit(ft->v.W);
     if (!*use && filter_mode == 2) return fail(FGS_E_STATE, "FGS_FILTER=lookup: the level tables exceed their memory limit for this node table");
     return FGS_OK;
+}
+
+void Engine::trace_collect(int k) {
+    Slot& sl = slots[k];
+    if (!trace_epoch) return;
+    for (cudaEvent_t ev : {sl.ev_t0, sl.ev_reduce, sl.ev_merge1, sl.ev_emit0, sl.ev_emit, sl.ev_merge2, sl.ev_done}) {
+        float ms = -1.f;
+        if (cudaEventElapsedTime(&ms, trace_epoch, ev) != cudaSuccess) {
+            cudaGetLastError();
+            ms = -1.f;
+        }
+        trace_rows.push_back(ms);
+    }
+}
+
+void Engine::trace_dump() {
+    if (!pipe_trace || trace_rows.empty()) return;
+    if (FILE* f = fopen(pipe_trace_path.c_str(), "w")) {
+        fprintf(f, "# ms since the first batch: filter_start filter_end merge1_end emit_start emit_end merge2_end d2h_end\n");
+        for (size_t i = 0; i + 7 <= trace_rows.size(); i += 7)
+            fprintf(f, "%.4f %.4f %.4f %.4f %.4f %.4f %.4f\n", trace_rows[i], trace_rows[i + 1], trace_rows[i + 2], trace_rows[i + 3],
+                    trace_rows[i + 4], trace_rows[i + 5], trace_rows[i + 6]);
+        fclose(f);
+    }
 }
 
 void Engine::fill_derive_params(DeriveParams* dp) const {
@@ -1044,8 +1075,6 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
         const int rc = e->ensure_filter_tables(&lookup);
         if (rc) return rc;
     }
-    launch_init_perpod((int64_t*)e->d_perpod, e->p_pad, e->stream);
-    e->launches++;
     bool done = false;
     e->reduce_was_lookup = lookup;
     if (lookup) { // Filter by table look-up: one warp per pod ANDs the level rows of its values (filter_tables.cu)
@@ -1063,8 +1092,14 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
         rp.bitmap = (uint32_t*)e->d_bitmap;
         rp.reduce_max = p.reduce_max;
         rp.reduce_sum = p.reduce_sum;
+        rp.select_key = p.select_key;
         rp.sc_flex = (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0;
         rp.sc_alloc = (e->cfg.score_mask & FGS_PL_ALLOCATABLE) ? 1 : 0;
+        // the per-pod rows the special nodes feed are written by the same kernel: no initialisation, no side passes
+        rp.special = (const int64_t*)e->d_special;
+        rp.n_special = e->node_an_valid ? e->node_an.n_special : 0;
+        rp.filter_mask = e->cfg.filter_mask;
+        rp.flex_first = p.flex_filter_first;
         const int64_t need_idx = (int64_t)rp.v.n_dims * e->p_pad;
         if (need_idx > e->ft->rowidx_cap) {
             if (e->ft->d_rowidx) cudaFree(e->ft->d_rowidx);
@@ -1075,20 +1110,16 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
         }
         FGS_CUDA(e, ft_launch_rows(rp, (int*)e->ft->d_rowidx, e->stream));
         e->launches += 2;
-        if ((e->cfg.filter_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
-            ft_launch_filter_panic((const int64_t*)e->d_nd, (const int64_t*)e->d_pods, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special,
-                                   e->n_pods, e->p_pad, e->S, e->cfg.filter_mask, e->cfg.fit_ignored_scalar_mask, p.flex_filter_first,
-                                   (int64_t*)e->d_perpod, e->stream);
-            e->launches++;
-        }
     } else {
-    if (e->narrow_batch) {
-        NarrowParams np;
-        e->fill_narrow_params(&np);
-        done = launch_reduce_narrow(np, narrow_spec(e), e->stream);
-    }
-    if (!done) launch_eval_reduce(p, e->stream);
-    e->launches++;
+        launch_init_perpod((int64_t*)e->d_perpod, e->p_pad, e->stream);
+        e->launches++;
+        if (e->narrow_batch) {
+            NarrowParams np;
+            e->fill_narrow_params(&np);
+            done = launch_reduce_narrow(np, narrow_spec(e), e->stream);
+        }
+        if (!done) launch_eval_reduce(p, e->stream);
+        e->launches++;
     }
     e->reduce_was_narrow = done;
     if (done && (e->cfg.filter_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) { // the narrow loop leaves this flag to a side pass
@@ -1096,7 +1127,7 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
                                  (e->cfg.filter_mask & FGS_PL_FIT) ? 1 : 0, p.flex_filter_first, (int64_t*)e->d_perpod, e->stream);
         e->launches++;
     }
-    if ((e->cfg.score_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
+    if (!lookup && (e->cfg.score_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
         launch_special_pass((const uint32_t*)e->d_bitmap, e->words_per_row, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special,
                             (const int64_t*)e->d_pods, (int64_t*)e->d_perpod, e->n_pods, e->p_pad, e->stream);
         e->launches++;
@@ -1414,14 +1445,15 @@ static int ensure_pipeline(Engine* e) {
         FGS_CUDA(e, cudaStreamCreateWithFlags(&e->d2h_stream, cudaStreamNonBlocking));
         FGS_CUDA(e, cudaEventCreateWithFlags(&e->ev_h2d, cudaEventDisableTiming));
         FGS_CUDA(e, cudaEventCreateWithFlags(&e->ev_kernels, cudaEventDisableTiming));
-        for (auto& sl : e->slots) FGS_CUDA(e, cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
+        for (auto& sl : e->slots) FGS_CUDA(e, cudaEventCreateWithFlags(&sl.ev_done, e->pipe_trace ? cudaEventDefault : cudaEventDisableTiming));
     }
     if (e->peer && !e->merge_stream) {
         int lo = 0, hi = 0;
         FGS_CUDA(e, cudaDeviceGetStreamPriorityRange(&lo, &hi));
         FGS_CUDA(e, cudaStreamCreateWithPriority(&e->merge_stream, cudaStreamNonBlocking, hi)); // its few CTAs go first
         for (auto& sl : e->slots)
-            for (cudaEvent_t* ev : {&sl.ev_reduce, &sl.ev_merge1, &sl.ev_emit, &sl.ev_merge2}) FGS_CUDA(e, cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+            for (cudaEvent_t* ev : {&sl.ev_reduce, &sl.ev_merge1, &sl.ev_emit, &sl.ev_merge2, &sl.ev_t0, &sl.ev_emit0})
+                FGS_CUDA(e, cudaEventCreateWithFlags(ev, e->pipe_trace ? cudaEventDefault : cudaEventDisableTiming));
     }
     return FGS_OK;
 }
@@ -1454,6 +1486,7 @@ int Engine::issue_emit_sharded(int j) {
     auto body = [&]() -> int {
         Engine* e = this;
         FGS_CUDA(e, cudaStreamWaitEvent(stream, sl.ev_merge1, 0));
+        if (pipe_trace) FGS_CUDA(e, cudaEventRecord(sl.ev_emit0, stream));
         {
             BitmapFor bm(this, sl.bitmap_sel);
             const int rc = fgs_pass_emit((fgs_engine*)this, sl.have_opts ? &sl.opts : nullptr);
@@ -1520,6 +1553,13 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
         }
     }
     Slot& sl = slots[k];
+    if (pipe_trace) {
+        if (!trace_epoch) {
+            FGS_CUDA(e, cudaEventCreate(&trace_epoch));
+            FGS_CUDA(e, cudaEventRecord(trace_epoch, stream));
+        }
+        FGS_CUDA(e, cudaEventRecord(sl.ev_t0, stream));
+    }
     {
         BitmapFor bm(this, sl.bitmap_sel);
         const int rc = fgs_pass_reduce((fgs_engine*)this);
@@ -1647,6 +1687,7 @@ extern "C" int fgs_collect(fgs_engine* eh, fgs_results* out) {
         if (rc) return rc;
     }
     FGS_CUDA(e, cudaEventSynchronize(e->slots[k].ev_done));
+    if (e->pipe_trace && e->peer) e->trace_collect(k);
     if (e->peer) { // a merge of this batch timed out: drop the batch, report
         const int rc = e->peer_check_error(k);
         if (rc) {

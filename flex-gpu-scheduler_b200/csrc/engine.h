@@ -100,6 +100,7 @@ struct Engine {
         fgs_eval_opts opts;
         bool have_opts = false;
         cudaEvent_t ev_reduce = nullptr, ev_merge1 = nullptr, ev_emit = nullptr, ev_merge2 = nullptr;
+        cudaEvent_t ev_t0 = nullptr, ev_emit0 = nullptr; // FGS_PIPE_TRACE: start of the filter pass / of the emit pass
     };
     static constexpr int kSlots = 32; // upper bound of fgs_set_resident_batches
     Slot slots[kSlots];
@@ -109,6 +110,14 @@ struct Engine {
     int max_in_flight() const { return peer ? 3 : 2; }
     int resident_cfg = 0;
     int ring() const { return resident_cfg > max_in_flight() ? resident_cfg : max_in_flight(); }
+    // FGS_PIPE_TRACE=<file>: the sharded pipeline's events are created with timing and every collected batch appends one
+    // line (ms since the first batch's start): filter start, filter end, merge 1 end, emit start, emit end, merge 2 end, D2H end
+    bool pipe_trace = false;
+    std::string pipe_trace_path;
+    cudaEvent_t trace_epoch = nullptr;
+    std::vector<float> trace_rows;
+    void trace_collect(int slot);
+    void trace_dump();
     int next_slot = -1;      // slot the next submit takes (-1: the current one) — the ring is walked round-robin
     int submit_single(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident);
     uint64_t submit_seq = 0; // batches submitted so far: the sharded pipeline alternates two bitmaps by its parity

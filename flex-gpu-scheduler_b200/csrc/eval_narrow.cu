@@ -570,6 +570,12 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     (void)flags_or;
     (void)node_panic;
     constexpr bool tile_has_panic = false; // panic nodes are handled through the thresholds (see reduce_narrow)
+    // A warp whose 128 nodes all lie beyond the table (the tail of the last node tile: a 6 250-node shard fills 106 of its
+    // last 1 024 columns) has no score to write and no key to offer: it leaves zeros in its column of the per-warp keys once
+    // and sits the pod loops out, so that the tail tile costs an eighth of the issue slots of a full one.
+    const bool warp_active = FUSED || __any_sync(0xffffffffu, inr[0] | inr[1] | inr[2] | inr[3]);
+    if (!warp_active)
+        for (int i = lane; i < 2 * kTileP; i += 32) ((uint32_t*)(smem + L.wkey))[i * kWarps + warp] = 0u;
     if (tid < kTileP) derive(0);
     __syncthreads();
     if (tid == 0 && n_tiles > 2) {
@@ -592,7 +598,8 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
 
         i64* rowp = (i64*)prm.scores + tile_p0 * prm.score_stride + node_tile0 + nloc[0];
         // (unrolling this loop costs registers and with them the third CTA per SM: 0.699 vs 0.665 ms)
-        for (int jp = 0; jp < n_valid; ++jp, rowp += prm.score_stride, bm_out += prm.words_per_row) {
+        const int n_loop = warp_active ? n_valid : 0;
+        for (int jp = 0; jp < n_loop; ++jp, rowp += prm.score_stride, bm_out += prm.words_per_row) {
             const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz200c nz200m
             const uint4 q3 = *(const uint4*)&s_pod[jp].fmag;   // fmag amag fsh ash
             const int4 q4 = *(const int4*)&s_pod[jp].fmax;     // fmax count arange32 kind

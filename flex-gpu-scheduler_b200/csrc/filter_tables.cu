@@ -320,11 +320,66 @@ __global__ void __launch_bounds__(kRowsWarps * 32, NDIMS ? 5 : 4) filter_rows(co
             else vnlo = scan_bits(row, W, col, lane, true);
         }
     }
+    // ---- the nodes that feed the pod's error bits: lane k looks at special node k, k + 32, … -----------------------------
+    // RR_FILTER_PANIC: the pod reaches NewGPUNode's panic inside FlexGPU.Filter on such a node (flex_gpu.go:101) — it has ONE
+    // flex limit, passes the limit-sum checks (:85-98) and, when NodeResourcesFit runs first, Fit as well;
+    // RR_NEG_MAG / RR_SCORE_PANIC: a FEASIBLE node with a negative MemScore (fractional pods only) / on which Score's
+    // NewGPUNode panics (:148) — finalize_pods turns them into FGS_PODERR_* once counts and maxima are merged.
+    i64 neg = 0;
+    int spanic = 0, fpanic = 0;
+    if (prm.n_special > 0) {
+        const bool flex_f = prm.filter_mask & FGS_PL_FLEXGPU;
+        const bool one_limit = kind == 1 || kind == 2;
+        i64 lim = 0, rc = 0, rm = 0, re = 0;
+        uint32_t smask = 0;
+        bool none = false;
+        const bool fit_first = (prm.filter_mask & FGS_PL_FIT) && !prm.flex_first;
+        if (flex_f && one_limit) {
+            auto P = [&](int c) { return __ldg(prm.pods + (i64)c * prm.p_pad + p); };
+            const u64 meta = (u64)P(PD_META);
+            lim = kind == 1 ? P(PD_GPU_LIM) : P(PD_MEM_LIM);
+            none = (uint32_t)meta & FGS_PF_REQ_NONE;
+            smask = (uint32_t)(meta >> 32) & ~prm.fit_ignored;
+            if (fit_first) rc = P(PD_REQ_CPU), rm = P(PD_REQ_MEM), re = P(PD_REQ_EPH);
+        }
+        for (int k = lane; k < prm.n_special; k += 32) {
+            const i64 e = __ldg(prm.special + k);
+            const i64 n = e & 0xffffffffll;
+            const bool is_panic = (e >> 40) != 0;
+            if ((row[n >> 5] >> (n & 31)) & 1u) {
+                const i64 mag = __ldg(prm.special + prm.n_pad + k);
+                if (kind == 2 && mag > neg) neg = mag; // MemScore is the raw score of fractional pods only (flex_gpu.go:160-162)
+                if (is_panic) spanic = 1;
+            }
+            if (is_panic && flex_f && one_limit && !fpanic) {
+                auto C = [&](int c) { return __ldg(prm.nd + (i64)c * prm.n_pad + n); };
+                const uint32_t fl = (uint32_t)C(ND_FLAGS);
+                bool reach = (fl & FGS_NF_VALID) && lim <= C(kind == 1 ? ND_THR_GPU : ND_THR_MEM);
+                if (reach && fit_first) {
+                    bool fit_ok = fl & NDF_PODS_OK;
+                    if (fit_ok && !none) {
+                        fit_ok = rc <= C(ND_FREE_CPU) && rm <= C(ND_FREE_MEM) && re <= C(ND_FREE_EPH);
+                        for (int sidx = 0; sidx < prm.S && fit_ok; ++sidx)
+                            if (((smask >> sidx) & 1u) && __ldg(prm.pods + (i64)(PD_FIXED_COLS + sidx) * prm.p_pad + p) > C(nd_free_scalar(sidx))) fit_ok = false;
+                    }
+                    reach = fit_ok;
+                }
+                if (reach) fpanic = 1;
+            }
+        }
+        neg = warp_max_i64(neg);
+        spanic = __any_sync(0xffffffffu, spanic);
+        fpanic = __any_sync(0xffffffffu, fpanic);
+    }
     if (lane == 0) {
         prm.reduce_sum[p] = (i64)cnt;
         prm.reduce_max[(i64)RR_FLEX_MAX * prm.p_pad + p] = vflex;
         prm.reduce_max[(i64)RR_ALLOC_HI * prm.p_pad + p] = vhi;
         prm.reduce_max[(i64)RR_ALLOC_NEGLO * prm.p_pad + p] = vnlo;
+        prm.reduce_max[(i64)RR_FILTER_PANIC * prm.p_pad + p] = fpanic ? 1 : 0;
+        prm.reduce_max[(i64)RR_NEG_MAG * prm.p_pad + p] = neg;
+        prm.reduce_max[(i64)RR_SCORE_PANIC * prm.p_pad + p] = spanic ? 1 : 0;
+        for (int r = 0; r < 3; ++r) prm.select_key[(i64)r * prm.p_pad + p] = 0; // the emit pass max-accumulates into these
     }
 }
 

@@ -85,7 +85,15 @@ struct FtRowsParams {
     uint32_t* bitmap;        // [P][W]
     int64_t* reduce_max;     // [FGS_REDUCE_ROWS][p_pad]
     int64_t* reduce_sum;     // [p_pad]
+    int64_t* select_key;     // [3][p_pad]: cleared here (the emit pass max-accumulates into it)
     int sc_flex, sc_alloc;
+    // the few nodes that feed a pod's error bits (negative MemScore, NewGPUNode panics): special[0][k] = node | panic << 40,
+    // special[1][k] = |MemScore| when negative. With them the kernel also writes RR_FILTER_PANIC / RR_NEG_MAG /
+    // RR_SCORE_PANIC, so that no separate per-pod pass (or initialisation) is needed.
+    const int64_t* special;
+    int n_special;
+    uint32_t filter_mask;
+    int flex_first;
 };
 // pass A: bitmap rows, feasible counts, max FlexGPU score, Allocatable hi / −lo of every pod — two launches: the row of
 // every (pod, dimension) into rowidx (int32 [n_dims][p_pad], caller's scratch), then one warp per pod

@@ -123,12 +123,19 @@ class Handle {
     fgs_engine* engine() const { return e_; }
     fgs_packer* packer() const { return pk_; }
     const fgs_snapshot* snapshot() const { return snap_; }
-    // Cache.UpdateSnapshot's role (internal/cache/cache.go:197-276): pack + upload
-    void UpdateSnapshot(const fgs_snapshot* snap) {
-        const fgs_node_table* t = nullptr;
-        if (fgs_packer_nodes(pk_, snap, 0, snap->n_nodes, &t) != FGS_OK) throw std::runtime_error(std::string("pack: ") + fgs_packer_error(pk_));
-        Check(fgs_upload_nodes(e_, t));
+    // Cache.UpdateSnapshot's role (internal/cache/cache.go:197-276): pack + upload — incrementally, by
+    // NodeInfo.Generation, when the snapshot carries the column (fgs_sync_nodes); returns the rows that went up
+    int64_t UpdateSnapshot(const fgs_snapshot* snap) {
+        int64_t repacked = snap->n_nodes;
+        if (snap->generation) {
+            Check(fgs_sync_nodes(e_, pk_, snap, 0, snap->n_nodes, &repacked));
+        } else {
+            const fgs_node_table* t = nullptr;
+            if (fgs_packer_nodes(pk_, snap, 0, snap->n_nodes, &t) != FGS_OK) throw std::runtime_error(std::string("pack: ") + fgs_packer_error(pk_));
+            Check(fgs_upload_nodes(e_, t));
+        }
         snap_ = snap;
+        return repacked;
     }
     void Check(int rc) const {
         if (rc != FGS_OK) throw std::runtime_error(fgs_last_error(e_));
@@ -289,6 +296,35 @@ class Framework {
         if (Scores(FGS_PL_FIT)) emit(FGS_PL_FIT, true, ev->fit_score);
         if (Scores(FGS_PL_ALLOCATABLE)) emit(FGS_PL_ALLOCATABLE, true, ev->alloc_raw), emit(FGS_PL_ALLOCATABLE, false, ev->alloc_norm);
         state.Write(kStateKey, ev);
+        if (ev->pod_err & FGS_PODERR_REF_PANIC) return Status(Code::Error, "the reference panics in NewGPUNode on a node this pod reaches");
+        return Status();
+    }
+
+    // RunScorePlugins (runtime/framework.go:861-933) as prioritizeNodes calls it (generic_scheduler.go:420-426): over the
+    // nodes that passed EVERY filter plugin of the profile — the engine's own verdicts AND those of the plugins outside
+    // this path. `nodes` = that list (snapshot indices). Every NormalizeScore then runs over it: the totals, the
+    // selected node and its score in the CycleState are replaced by those of the masked list (fgs_score_masked).
+    // Call after RunPreFilterPlugins of the same pod; returns Error when a normalised score leaves [0, 100].
+    framework::Status RunScorePlugins(CycleState& state, const std::vector<int64_t>& nodes) {
+        using framework::Code;
+        using framework::Status;
+        auto ev = state.Read(kStateKey);
+        const int64_t N = ev->n_nodes, n_pad = (std::max<int64_t>(N, 1) + 1023) / 1024 * 1024;
+        std::vector<uint32_t> mask((size_t)(n_pad / 32), 0u);
+        for (int64_t n : nodes)
+            if (n >= 0 && n < N) mask[(size_t)(n >> 5)] |= 1u << (n & 31);
+        std::vector<int64_t> plane((size_t)n_pad);
+        fgs_results r{};
+        r.feasible_count = &ev->feasible_count;
+        r.selected_node = &ev->selected_node;
+        r.selected_score = &ev->selected_score;
+        r.pod_err = &ev->pod_err;
+        r.feasible_bitmap = ev->feasible.data();
+        r.scores = plane.data();
+        fgs_engine* e = h_.engine();
+        if (fgs_score_masked(e, mask.data(), 0, nullptr, &r) != FGS_OK) return Status(Code::Error, fgs_last_error(e));
+        ev->total.assign(plane.begin(), plane.begin() + N);
+        if (ev->pod_err & FGS_PODERR_SCORE_RANGE) return Status(Code::Error, "a plugin returns an invalid score, it should in the range of [0, 100] after normalizing");
         if (ev->pod_err & FGS_PODERR_REF_PANIC) return Status(Code::Error, "the reference panics in NewGPUNode on a node this pod reaches");
         return Status();
     }
@@ -458,7 +494,9 @@ class Coscheduling {
         const size_t P = (size_t)std::max<int64_t>(pending->n_pods, 1);
         pre_.assign(P, 0);
         permit_.assign(P, 0);
+        post_.assign(P, 0);
         h_.Check(fgs_gang_check(h_.engine(), h_.snapshot(), pending, pgs, pre_.data(), permit_.data(), nullptr));
+        h_.Check(fgs_gang_postfilter(h_.engine(), h_.snapshot(), pending, pgs, post_.data(), nullptr));
     }
     // PreFilter — coscheduling.go:124-137 → PodGroupManager.PreFilter core.go:149-196; any failure is
     // UnschedulableAndUnresolvable "to avoid any preemption attempts"
@@ -484,9 +522,26 @@ class Coscheduling {
         }
     }
 
+    // PostFilter — coscheduling.go:140-176: every outcome is Unschedulable; *reject_group tells the caller to reject the
+    // group's waiting pods, AddDeniedPodGroup and DeletePermittedPodGroup (:164-172)
+    framework::Status PostFilter(int64_t pod, const std::string& pg_full_name, const std::string& pod_name, bool* reject_group) const {
+        using framework::Code;
+        using framework::Status;
+        if (reject_group) *reject_group = false;
+        switch (post_[(size_t)pod]) {
+            case FGS_GANG_POSTFILTER_NO_GROUP: return Status(Code::Unschedulable, "can not find pod group");          // :143-147
+            case FGS_GANG_POSTFILTER_ENOUGH_ASSIGNED: return Status(Code::Unschedulable);                              // :151-155
+            case FGS_GANG_POSTFILTER_SMALL_GAP: return Status(Code::Unschedulable);                                    // :159-163
+            default:
+                if (reject_group) *reject_group = true;
+                return Status(Code::Unschedulable,
+                              "PodGroup " + pg_full_name + " gets rejected due to Pod " + pod_name + " is unschedulable even after PostFilter"); // :173-175
+        }
+    }
+
   private:
     Handle& h_;
-    std::vector<uint8_t> pre_, permit_;
+    std::vector<uint8_t> pre_, permit_, post_;
 };
 
 // ---- CapacityScheduling — pkg/capacityscheduling/capacity_scheduling.go ---------------------------------------------------------

@@ -152,6 +152,15 @@ static void TestFlexGPU(Handle& h) {
         CHECK(flex.Reserve(pods.get(), 0, 1, &idx).IsSuccess() && idx == 1); // device 0 is a monopoly
         CHECK(st.Read(Framework::kStateKey)->feasible_count == 3);
         CHECK(RunFilterPlugins(fw, st, 3).FailedPlugin() == FlexGPU::Name);
+        // prioritizeNodes hands RunScorePlugins the nodes that passed EVERY filter plugin (generic_scheduler.go:420-426): say
+        // another plugin of the profile rejected node 1. NormalizeScore now runs over {0, 2}: MemScore 32 and 10 GiB →
+        // 100 − 100·32/32 = 0 and 100 − 100·10/32 = 69, so node 2 wins by far more than the LeastAllocated terms differ.
+        auto ev = st.Read(Framework::kStateKey);
+        CHECK(fw.RunScorePlugins(st, {0, 2}).IsSuccess());
+        CHECK(ev->feasible_count == 2 && ev->Feasible(0) && !ev->Feasible(1) && ev->Feasible(2) && !ev->Feasible(3));
+        CHECK(fw.SelectHost(st) == 2 && ev->selected_score == ev->total[2] && ev->total[2] - ev->total[0] > 60);
+        CHECK(fw.RunScorePlugins(st, {3}).IsSuccess()); // a node the engine's own filters rejected stays out, whatever the list says
+        CHECK(ev->feasible_count == 0 && fw.SelectHost(st) == -1);
     }
     { // whole GPU
         CycleState st;
@@ -305,6 +314,14 @@ static void TestCoscheduling(Handle& h) {
     CHECK(co.Permit(0).GetCode() == Code::Success);                              // 1 assigned + this one >= MinMember 2
     CHECK(co.Permit(2).GetCode() == Code::Wait);                                 // 0 assigned + 1 < 2
     CHECK(co.Permit(6).GetCode() == Code::Success);                              // PodGroupNotSpecified
+    // PostFilter (coscheduling.go:140-176): group 0 has 1 of its 2 members assigned — a gap of 50 % — so an unschedulable
+    // member takes the whole group down; a pod without a group only reports that
+    bool reject = false;
+    Status pf = co.PostFilter(0, "default/pg0", "pod-0", &reject);
+    CHECK(reject && pf.GetCode() == Code::Unschedulable &&
+          pf.Message() == "PodGroup default/pg0 gets rejected due to Pod pod-0 is unschedulable even after PostFilter");
+    pf = co.PostFilter(6, "", "pod-6", &reject);
+    CHECK(!reject && pf.GetCode() == Code::Unschedulable && pf.Message() == "can not find pod group");
 }
 
 int main() {
