@@ -192,6 +192,7 @@ ABI = {
     "fgs_score_masked": (C.c_int, [C.c_void_p, p_u32, C.c_int32, C.POINTER(EvalOpts), C.POINTER(Results)]),
     "fgs_resubmit": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),
     "fgs_set_resident_batches": (C.c_int, [C.c_void_p, C.c_int32]),
+    "fgs_max_in_flight": (C.c_int, [C.c_void_p]),
     "fgs_stage_pods": (C.c_int, [C.c_void_p, C.POINTER(PodTable)]),
     "fgs_pass_reduce": (C.c_int, [C.c_void_p]),
     "fgs_fused_eligible": (C.c_int, [C.c_void_p, C.POINTER(EvalOpts)]),

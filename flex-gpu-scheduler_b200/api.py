@@ -349,6 +349,9 @@ class Engine:
         """fgs_set_resident_batches: a ring of n pipeline slots, so that a job of n batches stays resident for resubmit()"""
         self._check(self._lib.fgs_set_resident_batches(self._h, int(n)))
 
+    def max_in_flight(self):
+        return int(self._lib.fgs_max_in_flight(self._h))
+
     def collect(self):
         """Per-pod results of the oldest submitted batch (blocks until it is done)."""
         P = self._pending.pop(0)

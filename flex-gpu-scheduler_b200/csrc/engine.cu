@@ -1205,6 +1205,18 @@ extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
     return FGS_OK;
 }
 
+// the compact rows finalize_pods wrote (16 bytes per pod) → the caller's arrays
+static void unpack_results(const int64_t* h, int64_t P, int64_t pp, fgs_results* out) {
+    for (int64_t p = 0; p < P; ++p) {
+        const uint64_t w = (uint64_t)h[p];
+        const uint32_t lo = (uint32_t)w;
+        if (out->feasible_count) out->feasible_count[p] = (int32_t)(lo & 0x0fffffffu);
+        if (out->pod_err) out->pod_err[p] = lo >> 28;
+        if (out->selected_node) out->selected_node[p] = (int32_t)(uint32_t)(w >> 32);
+        if (out->selected_score) out->selected_score[p] = h[pp + p];
+    }
+}
+
 extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
     if (!eh || !out) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
@@ -1218,7 +1230,7 @@ extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
                          (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0, e->stream);
     e->launches++;
     FGS_CUDA(e, cudaGetLastError());
-    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, d_compact, sizeof(int64_t) * 4 * pp, cudaMemcpyDeviceToHost, e->stream));
+    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, d_compact, sizeof(int64_t) * 2 * pp, cudaMemcpyDeviceToHost, e->stream));
     if (out->feasible_bitmap)
         FGS_CUDA(e, cudaMemcpyAsync(out->feasible_bitmap, e->d_bitmap, sizeof(uint32_t) * P * e->words_per_row, cudaMemcpyDeviceToHost, e->stream));
     if (out->scores && e->emitted)
@@ -1244,12 +1256,7 @@ extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
         for (int64_t p = 0; p < P; ++p) out->processed_nodes[p] = (int32_t)e->n_nodes;
     }
     const int64_t* h = (const int64_t*)e->h_perpod;
-    for (int64_t p = 0; p < P; ++p) { // widths of the caller's arrays differ from the device rows: plain copies
-        if (out->feasible_count) out->feasible_count[p] = (int32_t)h[p];
-        if (out->selected_node) out->selected_node[p] = (int32_t)h[pp + p];
-        if (out->selected_score) out->selected_score[p] = h[2 * pp + p];
-        if (out->pod_err) out->pod_err[p] = (uint32_t)h[3 * pp + p];
-    }
+    unpack_results(h, P, pp, out);
     out->words_per_row = e->words_per_row;
     out->score_row_stride = e->score_stride;
     cudaEventElapsedTime(&e->tm.h2d_ms, e->events[0], e->events[1]);
@@ -1502,7 +1509,7 @@ int Engine::issue_emit_sharded(int j) {
         FGS_CUDA(e, cudaGetLastError());
         FGS_CUDA(e, cudaEventRecord(sl.ev_merge2, merge_stream));
         FGS_CUDA(e, cudaStreamWaitEvent(d2h_stream, sl.ev_merge2, 0));
-        FGS_CUDA(e, cudaMemcpyAsync(h_perpod, d_compact, sizeof(int64_t) * 4 * p_pad, cudaMemcpyDeviceToHost, d2h_stream));
+        FGS_CUDA(e, cudaMemcpyAsync(h_perpod, d_compact, sizeof(int64_t) * 2 * p_pad, cudaMemcpyDeviceToHost, d2h_stream));
         {
             const int rc2 = peer_fetch_error(j, d2h_stream);
             if (rc2) return rc2;
@@ -1586,8 +1593,7 @@ extern "C" int fgs_resubmit(fgs_engine* eh, const fgs_eval_opts* opts) {
     Engine* e = (Engine*)eh;
     FGS_ENTER(e);
     if (e->in_flight >= e->max_in_flight())
-        return e->fail(FGS_E_STATE, e->peer ? "fgs_resubmit: three batches are in flight already; fgs_collect one first"
-                                            : "fgs_resubmit: two batches are in flight already; fgs_collect one first");
+        return e->fail(FGS_E_STATE, "fgs_resubmit: " + std::to_string(e->max_in_flight()) + " batches are in flight already; fgs_collect one first");
     if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_resubmit: nominated pods are set: use fgs_evaluate");
     if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_resubmit: sample / skip_pass_b need fgs_evaluate");
     cudaSetDevice(e->device);
@@ -1612,13 +1618,17 @@ extern "C" int fgs_set_resident_batches(fgs_engine* eh, int32_t n) {
     return FGS_OK;
 }
 
+extern "C" int fgs_max_in_flight(fgs_engine* eh) {
+    if (!eh) return FGS_E_INVALID;
+    return ((Engine*)eh)->max_in_flight();
+}
+
 extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_eval_opts* opts) {
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
     FGS_ENTER(e);
     if (e->in_flight >= e->max_in_flight())
-        return e->fail(FGS_E_STATE, e->peer ? "fgs_submit: three batches are in flight already; fgs_collect one first"
-                                            : "fgs_submit: two batches are in flight already; fgs_collect one first");
+        return e->fail(FGS_E_STATE, "fgs_submit: " + std::to_string(e->max_in_flight()) + " batches are in flight already; fgs_collect one first");
     if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_submit: sample / skip_pass_b need fgs_evaluate");
     if (e->nom_q > 0) return e->fail(FGS_E_STATE, "fgs_submit: nominated pods are set (their per-batch columns are not double-buffered): use fgs_evaluate");
     cudaSetDevice(e->device);
@@ -1668,7 +1678,7 @@ int Engine::submit_single(const fgs_pod_table* pods, const fgs_eval_opts* opts, 
     // the D2H of the per-pod results runs on its own stream: the next batch's kernels do not wait for it
     FGS_CUDA(e, cudaEventRecord(e->ev_kernels, e->stream));
     FGS_CUDA(e, cudaStreamWaitEvent(e->d2h_stream, e->ev_kernels, 0));
-    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, d_compact, sizeof(int64_t) * 4 * pp, cudaMemcpyDeviceToHost, e->d2h_stream));
+    FGS_CUDA(e, cudaMemcpyAsync(e->h_perpod, d_compact, sizeof(int64_t) * 2 * pp, cudaMemcpyDeviceToHost, e->d2h_stream));
     FGS_CUDA(e, cudaEventRecord(e->slots[k].ev_done, e->d2h_stream));
     e->slots[k].busy = true;
     e->in_flight++;
@@ -1701,13 +1711,9 @@ extern "C" int fgs_collect(fgs_engine* eh, fgs_results* out) {
     const bool is_cur = k == e->cur_slot;
     const int64_t P = is_cur ? e->n_pods : e->slots[k].n_pods, pp = is_cur ? e->p_pad : e->slots[k].p_pad;
     const int64_t* h = (const int64_t*)(is_cur ? e->h_perpod : e->slots[k].h_perpod);
-    for (int64_t p = 0; p < P; ++p) {
-        if (out->feasible_count) out->feasible_count[p] = (int32_t)h[p];
-        if (out->selected_node) out->selected_node[p] = (int32_t)h[pp + p];
-        if (out->selected_score) out->selected_score[p] = h[2 * pp + p];
-        if (out->pod_err) out->pod_err[p] = (uint32_t)h[3 * pp + p];
-        if (out->processed_nodes) out->processed_nodes[p] = (int32_t)e->n_nodes;
-    }
+    unpack_results(h, P, pp, out);
+    if (out->processed_nodes)
+        for (int64_t p = 0; p < P; ++p) out->processed_nodes[p] = (int32_t)e->n_nodes;
     out->words_per_row = e->words_per_row;
     out->score_row_stride = e->score_stride;
     out->next_start_node_index = -1;

@@ -104,12 +104,15 @@ struct Engine {
     };
     static constexpr int kSlots = 32; // upper bound of fgs_set_resident_batches
     Slot slots[kSlots];
-    // batches in flight: two on one GPU (a third buys nothing there, tools/pipe_breakdown.py), three in the sharded
-    // pipeline (see submit_sharded). The ring of slots is that long too unless fgs_set_resident_batches asked for more:
-    // extra slots only keep more batches RESIDENT for fgs_resubmit.
-    int max_in_flight() const { return peer ? 3 : 2; }
+    // batches in flight: two on one GPU (a third buys nothing there while the tables are resident, tools/pipe_breakdown.py),
+    // three in the sharded pipeline (see submit_sharded). The ring of slots is that long too unless
+    // fgs_set_resident_batches asked for more: extra slots keep more batches RESIDENT for fgs_resubmit, and the first
+    // of them also lets ONE more batch be in flight — its H2D copy is then issued a whole pass earlier, which is what
+    // hides it when the results of the oldest batch are slow to come back (8 GPUs on one host).
+    int base_in_flight() const { return peer ? 3 : 2; }
     int resident_cfg = 0;
-    int ring() const { return resident_cfg > max_in_flight() ? resident_cfg : max_in_flight(); }
+    int ring() const { return resident_cfg > base_in_flight() ? resident_cfg : base_in_flight(); }
+    int max_in_flight() const { return ring() > base_in_flight() ? base_in_flight() + 1 : base_in_flight(); }
     // FGS_PIPE_TRACE=<file>: the sharded pipeline's events are created with timing and every collected batch appends one
     // line (ms since the first batch's start): filter start, filter end, merge 1 end, emit start, emit end, merge 2 end, D2H end
     bool pipe_trace = false;

@@ -683,10 +683,9 @@ __global__ void finalize_pods(const i64* __restrict__ perpod, i64* __restrict__ 
         sel = (i64)(k & 0xffffffu);
         score = (i64)(k >> key_shift);
     }
-    compact[0 * p_pad + p] = count;
-    compact[1 * p_pad + p] = sel;
-    compact[2 * p_pad + p] = score;
-    compact[3 * p_pad + p] = (i64)err;
+    // 16 bytes per pod for the D2H: {count (28 bits) | error bits << 28 | selected node << 32, score}
+    compact[0 * p_pad + p] = (i64)((u64)(uint32_t)((uint32_t)count | (err << 28)) | ((u64)(uint32_t)(int32_t)sel << 32));
+    compact[1 * p_pad + p] = score;
 }
 } // namespace
 

@@ -115,8 +115,8 @@ struct EvalParams {
 cudaError_t eval_setup();
 // reduce_max rows := INT64_MIN (panic row := 0), reduce_sum := 0, select_key rows := 0
 void launch_init_perpod(int64_t* perpod, int64_t p_pad, void* stream);
-// per-pod results in the form the host reads back: [0] feasible count, [1] selected node (global index, -1 none),
-// [2] selected score, [3] FGS_PODERR_* bits — int64 [4][p_pad]
+// per-pod results in the form the host reads back — int64 [2][p_pad], 16 bytes per pod:
+// [0] feasible count (low 28 bits) | FGS_PODERR_* bits << 28 | selected node (global index, -1 none) << 32, [1] selected score
 void launch_finalize_pods(const int64_t* perpod, int64_t* compact, int64_t n_pods, int64_t p_pad, int key_shift, int emitted, int sc_flex,
                           void* stream);
 void launch_make_pod_meta(const uint32_t* flags, const uint32_t* present, int64_t* meta, int64_t n_pods, int64_t p_pad, void* stream);

@@ -220,11 +220,13 @@ int fgs_collect(fgs_engine* e, fgs_results* out);
  * no H2D): steady-state measurements with the tables already in HBM, on single and on node-sharded engines alike. The
  * slots are walked round-robin. By default there are as many slots as batches in flight (2, or 3 with a peer group);
  * fgs_set_resident_batches(e, n), 3 <= n <= 32, makes the ring n slots long, so that a job of n batches — BASELINE's
- * config 5: 1 000 000 pods in 65 536-pod batches — stays resident and n fgs_resubmit calls walk it once (the limit on
- * batches IN FLIGHT does not change); n = 0 restores the default. A batch staged before the node table last changed is
+ * config 5: 1 000 000 pods in 65 536-pod batches — stays resident and n fgs_resubmit calls walk it once; a longer ring
+ * also admits ONE more batch in flight (3, or 4 with a peer group), so that fgs_submit issues a batch's H2D copy a whole
+ * pass earlier; n = 0 restores the default. A batch staged before the node table last changed is
  * refused (FGS_E_STATE). */
 int fgs_resubmit(fgs_engine* e, const fgs_eval_opts* opts);
 int fgs_set_resident_batches(fgs_engine* e, int32_t n);
+int fgs_max_in_flight(fgs_engine* e); /* batches fgs_submit / fgs_resubmit accept before an fgs_collect is due (2..4) */
 
 /* The same evaluation in stages, for node-sharded multi-GPU runs (one engine per GPU/process):
  *   fgs_stage_pods → fgs_pass_reduce → [merge reduce_max / reduce_sum across shards]
