@@ -14,6 +14,8 @@
 // These are small, L2-resident problems: latency-bound, not HBM-bound.
 #include <cuda_runtime.h>
 
+#include <atomic>
+
 #include <algorithm>
 #include <cstring>
 #include <vector>
@@ -953,7 +955,10 @@ constexpr int kStaticMaxDevices = 64;
 
 // In host code this name is only a handle for cudaGetSymbolAddress — not an address a kernel could use.
 static __device__ __align__(256) unsigned char g_quota_static_scratch[kStaticBytes];
-static void* g_quota_static_dev_ptr[kStaticMaxDevices]; // device address of the array, per device ordinal
+// device address of the array, per device ordinal: resolved by the first call on a device. Two host threads may make that
+// first call together: both resolve the same address, the atomic only keeps the publication well defined. The address
+// does not outlive the device's primary context (cudaDeviceReset): a process that resets a device must not call again.
+static std::atomic<void*> g_quota_static_dev_ptr[kStaticMaxDevices];
 
 void static_err(char* buf, int64_t len, const char* msg) {
     if (!buf || len <= 0) return;
@@ -988,16 +993,18 @@ extern "C" int fgs_quota_check_static(void* stream, int32_t n_scalars, int64_t n
         return FGS_E_CUDA;
     }
     // once per device, with that device current: resolve the device address of the scratch array
-    if (!g_quota_static_dev_ptr[dev]) {
+    void* resolved = g_quota_static_dev_ptr[dev].load(std::memory_order_acquire);
+    if (!resolved) {
         void* ptr = nullptr;
         ce = cudaGetSymbolAddress((void**)&ptr, g_quota_static_scratch);
         if (ce != cudaSuccess || !ptr) {
             static_err(errbuf, errbuf_len, cudaGetErrorString(ce));
             return FGS_E_CUDA;
         }
-        g_quota_static_dev_ptr[dev] = ptr;
+        g_quota_static_dev_ptr[dev].store(ptr, std::memory_order_release);
+        resolved = ptr;
     }
-    unsigned char* scratch = (unsigned char*)g_quota_static_dev_ptr[dev];
+    unsigned char* scratch = (unsigned char*)resolved;
     cudaStream_t st = (cudaStream_t)stream;
     // the array still holds the previous call's aggregate and flags: start from zero
     ce = cudaMemsetAsync(scratch, 0, kStaticOverOff + (size_t)n_ns, st);

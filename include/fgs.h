@@ -424,7 +424,9 @@ int fgs_select_victims(fgs_engine* e, const fgs_snapshot* snap, const fgs_podset
  * errbuf (may be NULL). The first call on a device resolves the array's device address: make it at start-up,
  * before any stream capture on that device. All calls share the array (each clears what it reads first), so
  * two calls that can overlap on the GPU race: keep them on one stream or order them with events.
- * Asynchronous on `stream`; the result is ready when the stream reaches that point. */
+ * `stream` must belong to the device that is current when the call is made (the array that is used is that device's).
+ * The resolved address does not survive cudaDeviceReset. Asynchronous on `stream`; the result is ready when the stream
+ * reaches that point. */
 int fgs_quota_check_static(void* stream, int32_t n_scalars, int64_t n_ns, const uint8_t* dev_has_eq,
                            const int64_t* dev_min, const int64_t* dev_max, const int64_t* dev_used,
                            const uint32_t* dev_used_present, int64_t n_pods, const int64_t* dev_pod_req,
