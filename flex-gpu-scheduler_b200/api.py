@@ -452,7 +452,7 @@ class Engine:
         self._check(self._lib.fgs_get_timings(self._h, C.byref(t)))
         return dict(h2d_ms=t.h2d_ms, reduce_ms=t.reduce_ms, emit_ms=t.emit_ms, d2h_ms=t.d2h_ms, kernel_launches=t.kernel_launches,
                     reduce_int32=bool(t.reduce_int32), emit_int32=bool(t.emit_int32), seq_ms=t.seq_ms, seq_ctas=int(t.seq_ctas),
-                    fused=bool(t.fused), reduce_lookup=bool(t.reduce_lookup))
+                    fused=bool(t.fused), reduce_lookup=bool(t.reduce_lookup), small=bool(t.small))
 
     # -- sequential cycles: assume + Reserve between pods -------------------------------------------------
     def schedule_sequential(self, pod_table, reserve_flex=True, quotas=None):

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -136,6 +137,8 @@ void Engine::free_all() {
     if (d_mask) cudaFree(d_mask);
     if (d_walk) cudaFree(d_walk);
     if (h_walk) cudaFreeHost(h_walk);
+    if (h_small) cudaFreeHost(h_small);
+    if (d_small_done) cudaFree(d_small_done);
     if (d_nom) cudaFree(d_nom);
     if (d_pod_aux) cudaFree(d_pod_aux);
     if (h_pod_aux) cudaFreeHost(h_pod_aux);
@@ -333,6 +336,8 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
             e->pipe_trace = true;
             e->pipe_trace_path = std::string(tr) + "." + std::to_string(c->device);
         }
+        const char* sm_ = getenv("FGS_SMALL");
+        e->small_off = sm_ && sm_[0] == '0';
         const char* fm = getenv("FGS_FILTER");
         e->filter_mode = fm ? (fm[0] == 'c' ? 1 : (fm[0] == 'l' ? 2 : 0)) : 0;
         const char* ht = getenv("FGS_HOST_THREADS");
@@ -422,7 +427,7 @@ static int tz64(uint64_t v) { return v ? __builtin_ctzll(v) : 62; }
 
 static uint32_t narrow_spec(const Engine* e);
 
-int Engine::decide_narrow(const fgs_pod_table* t) {
+int Engine::decide_narrow(const fgs_pod_table* t, bool launch_pods) {
     narrow_batch = false;
     if (force_wide || !node_an_valid || S < 2) return FGS_OK;
     const bool sc_flex = cfg.score_mask & FGS_PL_FLEXGPU, sc_fit = cfg.score_mask & FGS_PL_FIT, sc_alloc = cfg.score_mask & FGS_PL_ALLOCATABLE;
@@ -482,8 +487,10 @@ int Engine::decide_narrow(const fgs_pod_table* t) {
         narrow_sh = sh;
         orders_valid = false; // the fused pass's node orders follow the narrow node table
     }
-    launch_narrow_pods((const int64_t*)d_pods, p_pad, S, sh, cfg.fit_ignored_scalar_mask, (int*)d_pn, stream);
-    launches++;
+    if (launch_pods) {
+        launch_narrow_pods((const int64_t*)d_pods, p_pad, S, sh, cfg.fit_ignored_scalar_mask, (int*)d_pn, stream);
+        launches++;
+    }
     FGS_CUDA(this, cudaGetLastError());
     narrow_batch = true;
     return FGS_OK;
@@ -1259,15 +1266,159 @@ extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
     unpack_results(h, P, pp, out);
     out->words_per_row = e->words_per_row;
     out->score_row_stride = e->score_stride;
-    cudaEventElapsedTime(&e->tm.h2d_ms, e->events[0], e->events[1]);
-    cudaEventElapsedTime(&e->tm.reduce_ms, e->events[1], e->events[2]);
+    // an event that was never recorded (the batch came through the one-launch path) makes cudaEventElapsedTime fail and
+    // leaves the error behind for the next cudaGetLastError: read 0 and clear it
+    auto elapsed = [](cudaEvent_t a, cudaEvent_t b) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, a, b) != cudaSuccess) {
+            cudaGetLastError();
+            ms = 0.f;
+        }
+        return ms;
+    };
+    e->tm.h2d_ms = elapsed(e->events[0], e->events[1]);
+    e->tm.reduce_ms = elapsed(e->events[1], e->events[2]);
     if (e->emitted) {
-        cudaEventElapsedTime(&e->tm.emit_ms, e->events[2], e->events[3]);
-        cudaEventElapsedTime(&e->tm.d2h_ms, e->events[3], e->events[4]);
+        e->tm.emit_ms = elapsed(e->events[2], e->events[3]);
+        e->tm.d2h_ms = elapsed(e->events[3], e->events[4]);
     } else {
         e->tm.emit_ms = 0.f;
-        cudaEventElapsedTime(&e->tm.d2h_ms, e->events[2], e->events[4]);
+        e->tm.d2h_ms = elapsed(e->events[2], e->events[4]);
     }
+    return FGS_OK;
+}
+
+// The reference's call shape — one pod (or a handful) per cycle, sched/scheduler.go:425-455 — in ONE launch: see small_cycle.
+// *done = false: the batch does not qualify (too many pods, options, a sharded engine, values outside the int32 range, level
+// tables over their memory limit …) and nothing was changed; the caller takes the general path.
+int Engine::evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fgs_results* out, bool* done) {
+    Engine* e = this;
+    *done = false;
+    if (small_off || !t || t->n_pods < 1 || t->n_pods > kSmallMaxPods || peer || nom_q > 0 || in_flight || !have_nodes || filter_mode == 1 || force_wide) return FGS_OK;
+    if (t->n_scalars != S) return FGS_OK; // the general path reports it
+    if (opts && (opts->sample || opts->skip_pass_b || opts->emit_raw || (opts->emit_mask != 0 && opts->emit_mask != cfg.score_mask))) return FGS_OK;
+    cudaSetDevice(device);
+    int rc;
+    {   // every call that leaves work on the stream waits for it before it returns (or keeps in_flight > 0), so the stream is
+        // idle here; only a reallocation below wants the device drained for certain
+        const int64_t pp2 = round_up(std::max<int64_t>(t->n_pods, 1), kTileP);
+        if (pp2 > p_pad_cap || pp2 > p_plane_cap || n_pad / 32 != words_per_row || n_pad != score_stride) FGS_CUDA(e, cudaStreamSynchronize(stream));
+        rc = ensure_pods(t->n_pods);
+        if (rc) return rc;
+    }
+    if (!nodes_derived) {
+        rc = derive_now();
+        if (rc) return rc;
+    }
+    bool lookup = false;
+    rc = ensure_filter_tables(&lookup);
+    if (rc) return rc;
+    if (!lookup) return FGS_OK;
+    const int64_t P = t->n_pods;
+    const int ncols = pd_cols(S);
+    if (!h_small) {
+        FGS_CUDA(e, cudaHostAlloc(&h_small, sizeof(int64_t) * ((size_t)(PD_FIXED_COLS + FGS_MAX_SCALARS + 2) * kSmallMaxPods + 8), cudaHostAllocMapped));
+        std::memset(h_small, 0, sizeof(int64_t) * ((size_t)(PD_FIXED_COLS + FGS_MAX_SCALARS + 2) * kSmallMaxPods + 8));
+        FGS_CUDA(e, cudaMalloc(&d_small_done, 256));
+        FGS_CUDA(e, cudaMemset(d_small_done, 0, 256));
+    }
+    int64_t* hp = (int64_t*)h_small;
+    int64_t* hc = hp + (int64_t)(PD_FIXED_COLS + FGS_MAX_SCALARS) * kSmallMaxPods;
+    volatile uint64_t* hflag = (volatile uint64_t*)(hc + 2 * kSmallMaxPods);
+    const int64_t* src[PD_FIXED_COLS + FGS_MAX_SCALARS] = {nullptr};
+    src[PD_GPU_LIM] = t->flex_gpu_limit, src[PD_MEM_LIM] = t->flex_mem_limit, src[PD_REQ_CPU] = t->req_mcpu, src[PD_REQ_MEM] = t->req_mem;
+    src[PD_REQ_EPH] = t->req_eph, src[PD_NZ_CPU] = t->nz_mcpu, src[PD_NZ_MEM] = t->nz_mem;
+    for (int s2 = 0; s2 < S; ++s2) src[PD_FIXED_COLS + s2] = t->req_scalar + (int64_t)s2 * P;
+    stage_present_or = 0;
+    for (int c = 0; c < ncols; ++c) {
+        uint64_t o = 0;
+        int64_t m = 0;
+        for (int64_t i = 0; i < P; ++i) {
+            int64_t v;
+            if (c == PD_META) {
+                v = (int64_t)(((uint64_t)t->req_scalar_present[i] << 32) | (uint64_t)t->flags[i]);
+                stage_present_or |= t->req_scalar_present[i];
+            } else {
+                v = src[c][i];
+                o |= (uint64_t)v;
+                m = v > m ? v : m;
+            }
+            hp[(int64_t)c * kSmallMaxPods + i] = v;
+        }
+        stage_or[c] = c == PD_META ? 0 : o;
+        stage_max[c] = c == PD_META ? 0 : m;
+    }
+    n_pods = P;
+    rc = decide_narrow(t, false); // shifts for this batch (and the int32 node table when they moved); the pods' int32 values are the kernel's
+    if (rc) return rc;
+    if (!narrow_batch) return FGS_OK; // the general path stages again and takes the int64 kernels
+    EvalParams ep;
+    fill_eval_params(&ep, nullptr);
+    if (ep.key_shift != 40) return FGS_OK;
+    SmallParams sp;
+    std::memset(&sp, 0, sizeof(sp));
+    sp.v = ft->v;
+    sp.h_pods = hp;
+    sp.h_compact = hc;
+    sp.d_pods = (int64_t*)d_pods;
+    sp.d_pn = (int*)d_pn;
+    sp.nn = (const int*)d_nn;
+    sp.nd = (const int64_t*)d_nd;
+    sp.perpod = (int64_t*)d_perpod;
+    sp.bitmap = (uint32_t*)d_bitmap;
+    sp.scores = (int64_t*)d_scores;
+    sp.n_pods = P;
+    sp.p_pad = p_pad;
+    sp.n_nodes = n_nodes;
+    sp.n_pad = n_pad;
+    sp.node_base = node_base;
+    sp.W = words_per_row;
+    sp.score_stride = score_stride;
+    sp.S = S;
+    sp.fit_ignored = cfg.fit_ignored_scalar_mask;
+    sp.filter_mask = cfg.filter_mask;
+    sp.score_mask = cfg.score_mask;
+    sp.flex_first = ep.flex_filter_first;
+    sp.fit_most = cfg.fit_strategy == 1;
+    sp.w_eq = ep.fit_w_cpu == ep.fit_w_mem;
+    sp.w_flex = (int)ep.w_flex, sp.w_fit = (int)ep.w_fit, sp.w_alloc = (int)ep.w_alloc;
+    sp.fit_w_cpu = ep.fit_w_cpu, sp.fit_w_mem = ep.fit_w_mem;
+    sp.fit_inv_wsum = ep.fit_inv_wsum;
+    for (int d2 = 0; d2 < ND_DIMS; ++d2) sp.sh[d2] = narrow_sh.s[d2];
+    sp.seed = seed;
+    sp.special = (const int64_t*)d_special;
+    sp.n_special = node_an_valid ? node_an.n_special : 0;
+    sp.d_done = (unsigned int*)d_small_done;
+    sp.h_flag = hflag;
+    sp.seq = ++small_seq;
+    FGS_CUDA(e, ft_launch_small(sp, stream));
+    launches++;
+    if (out->feasible_bitmap || out->scores) { // planes to the host: copies behind the kernel, then the stream
+        if (out->feasible_bitmap)
+            FGS_CUDA(e, cudaMemcpyAsync(out->feasible_bitmap, d_bitmap, sizeof(uint32_t) * P * words_per_row, cudaMemcpyDeviceToHost, stream));
+        if (out->scores) FGS_CUDA(e, cudaMemcpyAsync(out->scores, d_scores, sizeof(int64_t) * P * score_stride, cudaMemcpyDeviceToHost, stream));
+        FGS_CUDA(e, cudaStreamSynchronize(stream));
+    } else { // per-pod results only: watch the completion word the last CTA stores (a few µs sooner than the stream reports)
+        const auto t0 = std::chrono::steady_clock::now();
+        for (unsigned spin = 1; *hflag != sp.seq; ++spin) {
+            if ((spin & 0xfff) == 0 && std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(20)) {
+                FGS_CUDA(e, cudaStreamSynchronize(stream)); // something is wrong (or very slow): let the runtime say what
+                if (*hflag != sp.seq) return fail(FGS_E_CUDA, "small-batch kernel finished without reporting");
+                break;
+            }
+        }
+    }
+    unpack_results(hc, P, kSmallMaxPods, out);
+    if (out->processed_nodes)
+        for (int64_t i = 0; i < P; ++i) out->processed_nodes[i] = (int32_t)n_nodes;
+    out->words_per_row = words_per_row;
+    out->score_row_stride = score_stride;
+    out->next_start_node_index = -1;
+    have_pods = true, reduced = true, emitted = true, sampled = false, masked = false, was_fused = false, staged_by_dma = false;
+    reduce_was_lookup = true, reduce_was_narrow = false, emit_was_narrow = true, was_small = true;
+    last_key_shift = 40;
+    tm.h2d_ms = tm.reduce_ms = tm.emit_ms = tm.d2h_ms = 0.f;
+    *done = true;
     return FGS_OK;
 }
 
@@ -1275,6 +1426,13 @@ extern "C" int fgs_evaluate(fgs_engine* eh, const fgs_pod_table* pods, const fgs
     if (!eh) return FGS_E_INVALID;
     Engine* e = (Engine*)eh;
     FGS_ENTER(e);
+    e->was_small = false;
+    if (out) {
+        bool done = false;
+        const int rc0 = e->evaluate_small(pods, opts, out, &done);
+        if (rc0) return rc0;
+        if (done) return FGS_OK;
+    }
     int rc = fgs_stage_pods(eh, pods);
     if (rc) return rc;
     e->emitted = false;
@@ -1422,6 +1580,7 @@ extern "C" int fgs_get_timings(fgs_engine* eh, fgs_timings* t) {
     t->emit_int32 = e->emit_was_narrow ? 1 : 0;
     t->fused = e->was_fused ? 1 : 0;
     t->reduce_lookup = e->reduce_was_lookup ? 1 : 0;
+    t->small = e->was_small ? 1 : 0;
     return FGS_OK;
 }
 

@@ -70,7 +70,15 @@ struct Engine {
     void* d_special = nullptr; // int64 [2][n_pad]: nodes with a negative MemScore or on which NewGPUNode panics
     int64_t special_cap = 0;
     int64_t nn_cap = 0, pn_cap = 0;
-    int decide_narrow(const fgs_pod_table* t);
+    int decide_narrow(const fgs_pod_table* t, bool launch_pods = true);
+    // small batches (<= 64 pods): the whole cycle of every pod in one launch (filter_tables.cu: small_cycle); pod columns and
+    // result records travel through one block of mapped host memory. FGS_SMALL=0 turns the path off (tests).
+    void* h_small = nullptr; // mapped: int64 [pd_cols][64] pod columns, then int64 [2][64] result records, then the completion word
+    void* d_small_done = nullptr; // device counter of finished pods
+    uint64_t small_seq = 0;
+    bool small_off = false;
+    bool was_small = false;  // the last fgs_evaluate took it
+    int evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fgs_results* out, bool* done);
     void fill_narrow_params(NarrowParams* p) const;
     // the fused pass (eval_narrow.cu: filters + scores in ONE pass over pod × node, after a per-pod prepass for the
     // FlexGPU maximum): node orders by GPUScore / MemScore, rebuilt whenever the narrow node table is
@@ -179,7 +187,7 @@ struct Engine {
     struct PreemptCache* pcache = nullptr; // preempt.cu: the snapshot's pods as device columns, kept between calls
     uint64_t node_gen = 0;                 // bumped whenever the node table changes (upload, patch, sequential commits)
 
-    fgs_timings tm = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    fgs_timings tm = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     int64_t launches = 0;
 
     // one caller at a time: the thread inside an entry point owns the engine (entry points call each other, so the

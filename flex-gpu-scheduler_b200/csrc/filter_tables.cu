@@ -20,6 +20,7 @@
 
 #include "filter_tables.cuh"
 #include "kernels.cuh"
+#include "kernels_narrow.cuh"
 
 namespace fgs {
 
@@ -442,6 +443,316 @@ __global__ void __launch_bounds__(kRowsWarps * 32) masked_rows(const __grid_cons
     }
 }
 
+// ---- the whole cycle of one pod in one CTA (small batches) -------------------------------------------------------------------
+constexpr int kSmallThreads = 1024; // one CTA per pod and few pods: the SM is the CTA's alone, latency is what counts
+constexpr int kNoneI = (int)0x80000000, kPassI = (int)0x80000001, kNeverI = 0x7fffffff; // as in kernels_narrow.cu
+
+__device__ __forceinline__ int qmagic32(uint32_t x2, uint32_t m, int l) { return (int)(__umulhi(x2, m) >> l); }
+
+// lower bound (number of elements below v) in a sorted array by one warp: 32 probes per step instead of one — three dependent
+// loads where a binary search over 5 000 levels needs thirteen
+__device__ __forceinline__ int warp_lower_bound(const i64* __restrict__ lev, int n, i64 v, int lane) {
+    int lo = 0, hi = n; // everything before lo is < v, everything from hi on is >= v
+    while (hi - lo > 32) {
+        const int span = hi - lo, stride = (span + 31) >> 5;
+        int idx = lo + (lane + 1) * stride - 1;
+        idx = idx < hi ? idx : hi - 1;
+        const uint32_t below = __ballot_sync(0xffffffffu, __ldg(lev + idx) < v); // a prefix of the lanes
+        const int c = __popc(below);
+        const int last_true = lo + c * stride - 1, first_false = lo + (c + 1) * stride - 1;
+        if (c > 0) lo = (last_true < hi ? last_true : hi - 1) + 1;
+        if (c < 32) hi = first_false < hi ? first_false : hi - 1;
+        if (lo > hi) lo = hi;
+    }
+    const int idx = lo + lane;
+    const uint32_t below = __ballot_sync(0xffffffffu, idx < hi && __ldg(lev + idx) < v);
+    return lo + __popc(below);
+}
+
+__global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_constant__ SmallParams prm) {
+    extern __shared__ __align__(16) uint32_t s_row[]; // the pod's bitmap row, then reduction scratch
+    __shared__ i64 s_pod[PD_FIXED_COLS + FGS_MAX_SCALARS];
+    __shared__ uint32_t s_off[kFtMaxDims];
+    __shared__ i64 s_red[4];      // flex max, alloc hi, alloc -lo, negative-score magnitude
+    __shared__ int s_flags[2];    // score-time panic, filter-time panic
+    __shared__ uint32_t s_cnt[kSmallThreads / 32];
+    __shared__ u64 s_key[kSmallThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const i64 p = blockIdx.x;
+    const i64 W = prm.W, pp = prm.p_pad;
+    const int S = prm.S, ncols = pd_cols(S), n_dims = 5 + S;
+
+    // ---- the pod's columns: mapped host memory → shared memory and the device table ----------------------------------------
+    if (tid < ncols) {
+        const i64 v = prm.h_pods[(i64)tid * kSmallMaxPods + p];
+        s_pod[tid] = v;
+        prm.d_pods[(i64)tid * pp + p] = v;
+    }
+    __syncthreads();
+    const u64 meta = (u64)s_pod[PD_META];
+    const uint32_t pf = (uint32_t)meta, kind = pf & 3u;
+    const bool none = pf & FGS_PF_REQ_NONE;
+    const uint32_t smask = (uint32_t)(meta >> 32) & ~prm.fit_ignored;
+    // int32 pod values, as narrow_pods derives them
+    const int nzc = (int)(s_pod[PD_NZ_CPU] >> prm.sh[DIM_CPU]), nzm = (int)(s_pod[PD_NZ_MEM] >> prm.sh[DIM_MEM]);
+    if (tid == 0) {
+        auto Wn = [&](int c, int v) { prm.d_pn[(i64)c * pp + p] = v; };
+        Wn(PN_LIM_G, kind == 1 ? (int)s_pod[PD_GPU_LIM] : (kind == 3 ? kNeverI : kPassI));
+        Wn(PN_LIM_M, kind == 2 ? (int)(s_pod[PD_MEM_LIM] >> prm.sh[DIM_FM]) : (kind == 3 ? kNeverI : kPassI));
+        Wn(PN_RC, none ? kPassI : (int)(s_pod[PD_REQ_CPU] >> prm.sh[DIM_CPU]));
+        Wn(PN_RM, none ? kPassI : (int)(s_pod[PD_REQ_MEM] >> prm.sh[DIM_MEM]));
+        Wn(PN_RE, none ? kPassI : (int)(s_pod[PD_REQ_EPH] >> prm.sh[DIM_EPH]));
+        Wn(PN_RS0, (none || !(smask & 1u)) ? kPassI : (int)(s_pod[PD_FIXED_COLS + 0] >> prm.sh[DIM_S0]));
+        Wn(PN_RS1, (none || !(smask & 2u)) ? kPassI : (int)(s_pod[PD_FIXED_COLS + 1] >> prm.sh[DIM_S1]));
+        Wn(PN_NZC, nzc);
+        Wn(PN_NZM, nzm);
+        Wn(PN_KIND, (int)kind);
+    }
+    // ---- the row of every dimension (ft_pod_rows): warp d searches dimension d's levels ------------------------------------
+    if (warp < n_dims) {
+        const int d = warp;
+        i64 v;
+        bool skip = false;
+        if (d == FT_GPU) {
+            v = kind == 1 ? s_pod[PD_GPU_LIM] : (kind == 3 ? kMax : kLow1);
+            skip = kind == 2;
+        } else if (d == FT_FMEM) {
+            v = kind == 2 ? s_pod[PD_MEM_LIM] : kLow1;
+            skip = kind != 2;
+        } else if (d == FT_CPU) v = none ? kLow1 : s_pod[PD_REQ_CPU];
+        else if (d == FT_MEM) v = none ? kLow1 : s_pod[PD_REQ_MEM];
+        else if (d == FT_EPH) v = none ? kLow1 : s_pod[PD_REQ_EPH];
+        else v = (none || !((smask >> (d - FT_SCALAR0)) & 1u)) ? kLow1 : s_pod[PD_FIXED_COLS + (d - FT_SCALAR0)];
+        i64 rowi = prm.v.ones_row;
+        if (!skip) {
+            const int lo = warp_lower_bound(prm.v.levels + (i64)d * prm.v.lev_stride, prm.v.R[d], v, lane);
+            if (lo > 0 || d == FT_GPU || d == FT_FMEM) rowi = prm.v.row0[d] + lo;
+        }
+        if (lane == 0) s_off[d] = (uint32_t)((rowi * W) >> 2);
+    }
+    __syncthreads();
+    // ---- the bitmap row and the feasible count ----------------------------------------------------------------------------
+    {
+        const uint4* T = (const uint4*)prm.v.table;
+        uint4* out4 = (uint4*)(prm.bitmap + p * W);
+        uint4* row4 = (uint4*)s_row;
+        const int W4 = (int)(W >> 2);
+        uint32_t cnt = 0;
+        for (int c = tid; c < W4; c += kSmallThreads) {
+            uint4 a = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+            for (int d = 0; d < n_dims; ++d) {
+                const uint4 x = __ldg(T + (size_t)s_off[d] + c);
+                a.x &= x.x, a.y &= x.y, a.z &= x.z, a.w &= x.w;
+            }
+            row4[c] = a;
+            out4[c] = a;
+            cnt += (uint32_t)(__popc(a.x) + __popc(a.y) + __popc(a.z) + __popc(a.w));
+        }
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (lane == 0) s_cnt[warp] = cnt;
+    }
+    __syncthreads();
+    uint32_t count = 0;
+#pragma unroll
+    for (int w = 0; w < kSmallThreads / 32; ++w) count += s_cnt[w];
+    const bool sc_flex = prm.score_mask & FGS_PL_FLEXGPU, sc_fit = prm.score_mask & FGS_PL_FIT, sc_alloc = prm.score_mask & FGS_PL_ALLOCATABLE;
+    // ---- NormalizeScore's maxima (warp 0) and the special nodes (warp 1): as filter_rows -----------------------------------
+    if (warp == 0) {
+        i64 vflex = kMin, vhi = kMin, vnlo = kMin;
+        if (count > 0) {
+            if (sc_flex) {
+                if (kind == 0) {
+                    vflex = 0;
+                } else {
+                    const int o = (kind & 1u) ? FT_ORD_GSCORE : FT_ORD_MSCORE;
+                    if (!walk_order(prm.v.ord + (i64)o * prm.n_pad, prm.v.ord_val + (i64)o * prm.n_pad, prm.n_nodes, s_row, lane, false, &vflex))
+                        vflex = scan_bits(s_row, W, prm.nd + (i64)((kind & 1u) ? ND_GPU_SCORE : ND_MEM_SCORE) * prm.n_pad, lane, false);
+                }
+            }
+            if (sc_alloc) {
+                const int* ord = prm.v.ord + (i64)FT_ORD_ARAW * prm.n_pad;
+                const i64* val = prm.v.ord_val + (i64)FT_ORD_ARAW * prm.n_pad;
+                const i64* col = prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad;
+                if (!walk_order(ord, val, prm.n_nodes, s_row, lane, false, &vhi)) vhi = scan_bits(s_row, W, col, lane, false);
+                i64 lo;
+                if (walk_order(ord, val, prm.n_nodes, s_row, lane, true, &lo)) vnlo = -lo;
+                else vnlo = scan_bits(s_row, W, col, lane, true);
+            }
+        }
+        if (lane == 0) s_red[0] = vflex, s_red[1] = vhi, s_red[2] = vnlo;
+    } else if (warp == 1) {
+        i64 neg = 0;
+        int spanic = 0, fpanic = 0;
+        if (prm.n_special > 0) {
+            const bool flex_f = prm.filter_mask & FGS_PL_FLEXGPU;
+            const bool one_limit = kind == 1 || kind == 2;
+            const i64 lim = kind == 1 ? s_pod[PD_GPU_LIM] : s_pod[PD_MEM_LIM];
+            const bool fit_first = (prm.filter_mask & FGS_PL_FIT) && !prm.flex_first;
+            for (int k = lane; k < prm.n_special; k += 32) {
+                const i64 e = __ldg(prm.special + k);
+                const i64 n = e & 0xffffffffll;
+                const bool is_panic = (e >> 40) != 0;
+                if ((s_row[n >> 5] >> (n & 31)) & 1u) {
+                    const i64 mag = __ldg(prm.special + prm.n_pad + k);
+                    if (kind == 2 && mag > neg) neg = mag;
+                    if (is_panic) spanic = 1;
+                }
+                if (is_panic && flex_f && one_limit && !fpanic) {
+                    auto C = [&](int c) { return __ldg(prm.nd + (i64)c * prm.n_pad + n); };
+                    const uint32_t fl = (uint32_t)C(ND_FLAGS);
+                    bool reach = (fl & FGS_NF_VALID) && lim <= C(kind == 1 ? ND_THR_GPU : ND_THR_MEM);
+                    if (reach && fit_first) {
+                        bool fit_ok = fl & NDF_PODS_OK;
+                        if (fit_ok && !none) {
+                            fit_ok = s_pod[PD_REQ_CPU] <= C(ND_FREE_CPU) && s_pod[PD_REQ_MEM] <= C(ND_FREE_MEM) && s_pod[PD_REQ_EPH] <= C(ND_FREE_EPH);
+                            for (int sidx = 0; sidx < S && fit_ok; ++sidx)
+                                if (((smask >> sidx) & 1u) && s_pod[PD_FIXED_COLS + sidx] > C(nd_free_scalar(sidx))) fit_ok = false;
+                        }
+                        reach = fit_ok;
+                    }
+                    if (reach) fpanic = 1;
+                }
+            }
+            neg = warp_max_i64(neg);
+            spanic = __any_sync(0xffffffffu, spanic);
+            fpanic = __any_sync(0xffffffffu, fpanic);
+        }
+        if (lane == 0) s_red[3] = neg, s_flags[0] = spanic ? 1 : 0, s_flags[1] = fpanic ? 1 : 0;
+    }
+    __syncthreads();
+    // ---- Score, NormalizeScore, weights, sum, selectHost key: emit_narrow's arithmetic, one node at a time --------------------
+    const i64 raw_fmax = s_red[0];
+    i64 fmx = raw_fmax < 0 ? 0 : raw_fmax; // maxCount starts at 0 (normalize_score.go:27)
+    if (kind == 2) fmx >>= prm.sh[DIM_FM];
+    const int fmax = (int)fmx;
+    int fsh = 0, ash = 0;
+    const uint32_t fmag = narrow_magic((uint32_t)fmax, &fsh);
+    i64 alo = 0, arange64 = 0;
+    int arange32 = 0;
+    uint32_t amag = 0;
+    if (sc_alloc && count > 0) {
+        const i64 hi = s_red[1], lo = -s_red[2];
+        arange64 = (i64)((u64)hi - (u64)lo);
+        alo = lo;
+        if (arange64 >= 0 && arange64 < (1 << 24)) {
+            arange32 = (int)arange64;
+            amag = narrow_magic((uint32_t)arange64, &ash);
+        } else {
+            arange32 = -1;
+        }
+    }
+    uint32_t h = (uint32_t)(prm.seed ^ (prm.seed >> 32)) ^ ((uint32_t)p * 0x85EBCA6Bu);
+    h ^= h >> 15;
+    h *= 0x9E3779B1u;
+    const uint32_t hmul = h | 1u, ph8 = (h >> 20) & 0xffu;
+    const int ks = (sc_flex && fmax != 0) ? ((kind & 1u) ? 1 : (kind == 2 ? 2 : 0)) : 0;
+    const uint32_t nz200c = 200u * (uint32_t)nzc, nz200m = 200u * (uint32_t)nzm;
+    u64 best = 0;
+    i64* srow = prm.scores + p * prm.score_stride;
+    for (i64 n = tid; n < prm.n_nodes; n += kSmallThreads) {
+        auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
+        int t = 0;
+        if (sc_flex) {
+            int v = 100;
+            if (ks == 1) {
+                v = 100 - qmagic32(200u * (uint32_t)C(NN_GSCORE), fmag, fsh);
+            } else if (ks == 2) {
+                const int ms = C(NN_MSCORE);
+                const int q = qmagic32(200u * (uint32_t)(ms < 0 ? -ms : ms), fmag, fsh);
+                v = ms < 0 ? 100 + q : 100 - q;
+            }
+            t += v * prm.w_flex;
+        }
+        if (sc_fit) {
+            const int capc = C(NN_CAP_C), xc = C(NN_X_C), capm = C(NN_CAP_M), xm = C(NN_X_M);
+            const uint32_t magc = (uint32_t)C(NN_MAG_C), magm = (uint32_t)C(NN_MAG_M);
+            const int shs = C(NN_MAG_SH), shc = shs & 0xff, shm = (shs >> 8) & 0xff;
+            int sc, sm;
+            if (!prm.fit_most) {
+                sc = qmagic32(200u * (uint32_t)xc - nz200c, magc, shc);
+                sm = qmagic32(200u * (uint32_t)xm - nz200m, magm, shm);
+                sc = nzc > xc ? 0 : sc;
+                sm = nzm > xm ? 0 : sm;
+            } else {
+                sc = qmagic32(200u * (uint32_t)xc + nz200c, magc, shc);
+                sm = qmagic32(200u * (uint32_t)xm + nz200m, magm, shm);
+                sc = nzc > capc - xc ? 100 : sc;
+                sm = nzm > capm - xm ? 100 : sm;
+            }
+            int v;
+            if (prm.w_eq) {
+                v = (sc + sm) >> 1;
+            } else {
+                const int num = sc * prm.fit_w_cpu + sm * prm.fit_w_mem;
+                v = __float_as_int(__fadd_rd(((float)num + 0.5f) * prm.fit_inv_wsum, 8388608.0f)) & 0x7fffff;
+            }
+            t += v * prm.w_fit;
+        }
+        if (sc_alloc) {
+            int v = 0;
+            const i64 araw = __ldg(prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n);
+            if (arange32 > 0) {
+                const int a = (int)(uint32_t)((u64)araw - (u64)alo);
+                v = qmagic32(200u * (uint32_t)a, amag, ash);
+            } else if (arange32 < 0) {
+                v = (int)((i64)((u64)((i64)((u64)araw - (u64)alo)) * 100ull) / arange64);
+            }
+            t += v * prm.w_alloc;
+        }
+        srow[n] = (i64)(u64)(uint32_t)t;
+        if ((s_row[n >> 5] >> (n & 31)) & 1u) { // selectHost candidate: the key emit_narrow's tiles arrive at
+            const uint32_t nloc = (uint32_t)(n & 1023), tile = (uint32_t)(n >> 10);
+            const uint32_t h8 = ((nloc * 0x9E3779B1u) >> 24) ^ ph8;
+            const uint32_t h16 = (h8 << 8) | ((tile * 0x9E3779B1u ^ hmul) >> 24);
+            const u64 key = (((u64)(uint32_t)t << 40) | ((u64)h16 << 24) | (u64)(prm.node_base + n)) + 1;
+            best = key > best ? key : best;
+        }
+    }
+    best = (u64)warp_max_i64((i64)best);
+    if (lane == 0) s_key[warp] = best;
+    __syncthreads();
+    // ---- the per-pod rows and the result record (finalize_pods) ---------------------------------------------------------------
+    if (tid == 0) {
+        u64 key = 0;
+#pragma unroll
+        for (int w = 0; w < kSmallThreads / 32; ++w) key = s_key[w] > key ? s_key[w] : key;
+        i64* rm = prm.perpod;
+        rm[(i64)RR_FLEX_MAX * pp + p] = raw_fmax;
+        rm[(i64)RR_ALLOC_HI * pp + p] = s_red[1];
+        rm[(i64)RR_ALLOC_NEGLO * pp + p] = s_red[2];
+        rm[(i64)RR_FILTER_PANIC * pp + p] = s_flags[1];
+        rm[(i64)RR_NEG_MAG * pp + p] = s_red[3];
+        rm[(i64)RR_SCORE_PANIC * pp + p] = s_flags[0];
+        rm[(i64)FGS_REDUCE_ROWS * pp + p] = (i64)count;
+        rm[(i64)(FGS_REDUCE_ROWS + 1) * pp + p] = (i64)key;
+        rm[(i64)(FGS_REDUCE_ROWS + 2) * pp + p] = 0;
+        rm[(i64)(FGS_REDUCE_ROWS + 3) * pp + p] = 0;
+        uint32_t err = 0;
+        if (s_flags[1]) err |= FGS_PODERR_REF_PANIC;
+        if (sc_flex && count >= 2) {
+            if (s_flags[0]) err |= FGS_PODERR_REF_PANIC;
+            if (raw_fmax > 0 && s_red[3] > 0 && 100 * s_red[3] >= raw_fmax) err |= FGS_PODERR_SCORE_RANGE;
+        }
+        i64 sel = -1, score = 0;
+        if (key > 0) {
+            const u64 k = key - 1;
+            sel = (i64)(k & 0xffffffu);
+            score = (i64)(k >> 40);
+        }
+        const i64 w0 = (i64)((u64)(uint32_t)(count | (err << 28)) | ((u64)(uint32_t)(int32_t)sel << 32));
+        rm[(i64)(FGS_REDUCE_ROWS + 4) * pp + p] = w0;
+        rm[(i64)(FGS_REDUCE_ROWS + 5) * pp + p] = score;
+        prm.h_compact[p] = w0;
+        prm.h_compact[kSmallMaxPods + p] = score;
+        __threadfence_system();
+        if (atomicAdd(prm.d_done, 1u) == (unsigned)(prm.n_pods - 1)) { // every other pod's record is out: tell the host
+            *prm.d_done = 0;
+            __threadfence_system();
+            *prm.h_flag = prm.seq;
+        }
+    }
+}
+
 // Which pods would make the reference panic inside FlexGPU.Filter (see filter_panic_pass in kernels_narrow.cu): a pod
 // with ONE flex limit that passes the limit-sum checks (flex_gpu.go:85-98) on a node whose device state makes NewGPUNode
 // panic (:101, gpu_node.go:40-58,109,115) and, when NodeResourcesFit runs first, passes Fit too (runtime/framework.go:667-693).
@@ -654,6 +965,14 @@ cudaError_t ft_launch_masked(const FtMaskParams& p, cudaStream_t st) {
     const size_t smem = (size_t)p.W * 4 * kRowsWarps;
     if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(masked_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     masked_rows<<<(unsigned)((p.n_pods + kRowsWarps - 1) / kRowsWarps), kRowsWarps * 32, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t ft_launch_small(const SmallParams& p, cudaStream_t st) {
+    if (p.n_pods <= 0) return cudaSuccess;
+    const size_t smem = (size_t)p.W * 4;
+    if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(small_cycle, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    small_cycle<<<(unsigned)p.n_pods, kSmallThreads, smem, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -117,6 +117,41 @@ struct FtMaskParams {
 };
 cudaError_t ft_launch_masked(const FtMaskParams& p, cudaStream_t stream);
 
+// ---- small batches: the whole cycle of a pod in ONE CTA, the batch in ONE launch ---------------------------------------------
+// What the reference's scheduleOne does per pod (sched/scheduler.go:425-455 → generic_scheduler.go:93-167): up to 64 pods,
+// one CTA each — the pod's columns are read straight from mapped host memory, Filter is the AND of the level rows, the
+// normaliser reductions are block reductions, every node is scored with the int32 arithmetic of emit_narrow (same magic
+// multipliers, same selectHost key) and the 16-byte result record goes straight back to mapped host memory.
+constexpr int kSmallMaxPods = 64;
+struct SmallParams {
+    FtView v;
+    const int64_t* h_pods;   // mapped host block int64 [pd_cols(S)][kSmallMaxPods]
+    int64_t* h_compact;      // mapped host block int64 [2][kSmallMaxPods]: the result records
+    int64_t* d_pods;         // device pod table [pd_cols(S)][p_pad], filled for the plane getters
+    int* d_pn;               // int32 pod table [PN_COLS][p_pad], filled for later emit passes
+    const int* nn;           // int32 node table
+    const int64_t* nd;       // derived node table
+    int64_t* perpod;         // per-pod block: reduce rows | count | select keys | compact rows
+    uint32_t* bitmap;
+    int64_t* scores;
+    int64_t n_pods, p_pad, n_nodes, n_pad, node_base, W, score_stride;
+    int S;
+    uint32_t fit_ignored, filter_mask, score_mask;
+    int flex_first, fit_most, w_eq;
+    int w_flex, w_fit, w_alloc, fit_w_cpu, fit_w_mem;
+    float fit_inv_wsum;
+    int sh[8];               // NarrowShifts
+    uint64_t seed;
+    const int64_t* special;
+    int n_special;
+    // completion without a stream synchronisation: the CTA that finishes last (device counter) stores `seq` into the mapped
+    // word behind the records once every record is visible to the host
+    unsigned int* d_done;
+    volatile uint64_t* h_flag;
+    uint64_t seq;
+};
+cudaError_t ft_launch_small(const SmallParams& p, cudaStream_t stream);
+
 // the pods that reach NewGPUNode's panic inside FlexGPU.Filter → RR_FILTER_PANIC, from the int64 tables (any S)
 void ft_launch_filter_panic(const int64_t* nd, const int64_t* pods, const int64_t* special, int64_t n_pad, int n_special, int64_t n_pods,
                             int64_t p_pad, int S, uint32_t filter_mask, uint32_t fit_ignored, int flex_first, int64_t* reduce_max,

@@ -1,0 +1,96 @@
+"""Small batches — the reference's own call shape is one pod per scheduling cycle
+(vendor/k8s.io/kubernetes/pkg/scheduler/scheduler.go:425-455): fgs_evaluate with at most 64 pods runs the whole cycle of
+every pod in ONE launch (a CTA per pod). Its answers against the oracle, and against the general path bit for bit —
+selectHost's choice included, the two build the same key."""
+import os
+
+import numpy as np
+import pytest
+
+import flex_gpu_scheduler_b200 as fgs
+from flex_gpu_scheduler_b200 import _lib as L
+
+pytestmark = pytest.mark.gpu
+
+CASES = [
+    ("c2", dict(cfg=2, n_nodes=5000, pm_quirk_nodes=60), None),
+    ("c2-panics-flex-first", dict(cfg=2, n_nodes=900, pm_quirk_nodes=150, pm_panic_nodes=80, pm_nongpu_nodes=60, pm_invalid_nodes=20),
+     dict(filter_plugins=("FlexGPU", "NodeResourcesFit"))),
+    ("c1-allocatable", dict(cfg=1, n_nodes=1300), None),
+    ("most-allocated-weights", dict(cfg=2, n_nodes=700),
+     dict(score_plugins=(("FlexGPU", 3), ("NodeResourcesFit", 2)), fit_strategy="MostAllocated", fit_resources=(("cpu", 3), ("memory", 7)))),
+    ("all-three", dict(cfg=2, n_nodes=1100),
+     dict(score_plugins=(("FlexGPU", 2), ("NodeResourcesFit", 1), ("NodeResourcesAllocatable", 5)), alloc_mode="Most")),
+    ("fit-only", dict(cfg=2, n_nodes=600), dict(filter_plugins=("NodeResourcesFit",), score_plugins=(("NodeResourcesFit", 1),))),
+]
+
+
+def _engine(s, cfg, small):
+    os.environ["FGS_SMALL"] = "1" if small else "0"
+    try:
+        eng = fgs.Engine(device=0, n_scalars=2, total_nodes=s.n_nodes)
+    finally:
+        os.environ.pop("FGS_SMALL", None)
+    eng.set_plugins(cfg)
+    eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot))
+    return eng
+
+
+@pytest.mark.parametrize("name,skw,pkw", CASES, ids=[c[0] for c in CASES])
+def test_one_launch_cycles_match_the_oracle_and_the_general_path(gpu_ok, oracle, name, skw, pkw):
+    skw = dict(skw)
+    cfg_id = skw.pop("cfg")
+    s = fgs.config_synth(cfg_id, n_pending=200, **skw)
+    cfg = fgs.config_plugins(cfg_id) if pkw is None else fgs.plugin_cfg(**pkw)
+    N = s.n_nodes
+    small, general = _engine(s, cfg, True), _engine(s, cfg, False)
+    ref_all = oracle.evaluate(s.snapshot, s.pending, cfg, workers=4)
+    seen_err = 0
+    for p0, P in ((0, 1), (1, 1), (7, 2), (10, 63), (100, 64), (40, 17)):
+        t = fgs.Packer(2).pods(s.pending, p0, p0 + P)
+        a = small.evaluate(t, want_planes=True)
+        assert small.timings()["small"]
+        b = general.evaluate(t, want_planes=True)
+        assert not general.timings()["small"]
+        ref_status = ref_all.status[p0:p0 + P]
+        feas = ref_status == 0
+        assert np.array_equal(a.feasible(N), feas)
+        assert np.array_equal(a.feasible_count, ref_all.feasible_count[p0:p0 + P])
+        assert np.array_equal(a.pod_err, ref_all.pod_err[p0:p0 + P])
+        seen_err |= int(a.pod_err.max())
+        ok = (a.pod_err == 0) & (a.feasible_count >= 1)
+        m = feas & ok[:, None]
+        assert np.array_equal(a.scores[:, :N][m], ref_all.total[p0:p0 + P][m])
+        idx = np.nonzero(ok)[0]
+        assert np.array_equal(a.selected_score[idx], ref_all.max_total[p0:p0 + P][idx])
+        assert np.all(a.selected_node[a.feasible_count == 0] == -1)
+        # … and the general path, including which node of the tie set is chosen
+        for k in ("feasible_count", "selected_node", "selected_score", "pod_err"):
+            assert np.array_equal(getattr(a, k), getattr(b, k)), k
+        assert np.array_equal(a.feasible(N), b.feasible(N))
+        assert np.array_equal(a.scores[:, :N], b.scores[:, :N])
+        # the staged batch is as the general path leaves it: the status plane, a per-plugin emit pass, masked scoring
+        assert np.array_equal(small.status_plane(0), ref_status)
+    if "panics" in name:
+        assert seen_err & L.FGS_PODERR_REF_PANIC
+    t = fgs.Packer(2).pods(s.pending, 0, 32)
+    a = small.evaluate(t, want_planes=True)
+    assert small.timings()["small"]
+    if cfg.score_mask & L.FGS_PL_FLEXGPU:
+        one = small.evaluate(t, want_planes=True, emit_mask=L.FGS_PL_FLEXGPU)  # options: the general path takes over
+        assert not small.timings()["small"]
+        two = general.evaluate(t, want_planes=True, emit_mask=L.FGS_PL_FLEXGPU)
+        assert np.array_equal(one.scores[:, :N], two.scores[:, :N])
+    a = small.evaluate(t, want_planes=True)
+    rng = np.random.default_rng(5)
+    mask = rng.random((32, N)) < 0.6
+    got = small.score_masked(mask, want_planes=True)
+    ref = oracle.evaluate(s.snapshot, s.pending, cfg, 0, 32, workers=4, ext_mask=mask.astype(np.uint8))
+    assert np.array_equal(got.feasible(N), ref.status == 0) and np.array_equal(got.feasible_count, ref.feasible_count)
+    okm = (ref.pod_err == 0) & (ref.feasible_count >= 1)
+    assert np.array_equal(got.selected_score[okm], ref.max_total[okm])
+    big = small.evaluate(fgs.Packer(2).pods(s.pending, 0, 65))
+    assert not small.timings()["small"]
+    assert np.array_equal(big.feasible_count, ref_all.feasible_count[:65])
+    small.close()
+    general.close()
