@@ -1296,6 +1296,7 @@ int Engine::evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fg
     *done = false;
     if (small_off || !t || t->n_pods < 1 || t->n_pods > kSmallMaxPods || peer || nom_q > 0 || in_flight || !have_nodes || filter_mode == 1 || force_wide) return FGS_OK;
     if (t->n_scalars != S) return FGS_OK; // the general path reports it
+    if (t->n_pods > 64 && t->n_pods * n_nodes > ((int64_t)4 << 20)) return FGS_OK; // a CTA per pod stops paying: the tiled kernels take over
     if (opts && (opts->sample || opts->skip_pass_b || opts->emit_raw || (opts->emit_mask != 0 && opts->emit_mask != cfg.score_mask))) return FGS_OK;
     cudaSetDevice(device);
     int rc;

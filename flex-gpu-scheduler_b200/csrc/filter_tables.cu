@@ -649,6 +649,7 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     const uint32_t nz200c = 200u * (uint32_t)nzc, nz200m = 200u * (uint32_t)nzm;
     u64 best = 0;
     i64* srow = prm.scores + p * prm.score_stride;
+#pragma unroll 4 // the column loads of several nodes in flight together: the loop is a chain of L2 round trips otherwise
     for (i64 n = tid; n < prm.n_nodes; n += kSmallThreads) {
         auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
         int t = 0;

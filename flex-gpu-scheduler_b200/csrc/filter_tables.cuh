@@ -118,11 +118,11 @@ struct FtMaskParams {
 cudaError_t ft_launch_masked(const FtMaskParams& p, cudaStream_t stream);
 
 // ---- small batches: the whole cycle of a pod in ONE CTA, the batch in ONE launch ---------------------------------------------
-// What the reference's scheduleOne does per pod (sched/scheduler.go:425-455 → generic_scheduler.go:93-167): up to 64 pods,
+// What the reference's scheduleOne does per pod (sched/scheduler.go:425-455 → generic_scheduler.go:93-167): up to 256 pods,
 // one CTA each — the pod's columns are read straight from mapped host memory, Filter is the AND of the level rows, the
 // normaliser reductions are block reductions, every node is scored with the int32 arithmetic of emit_narrow (same magic
 // multipliers, same selectHost key) and the 16-byte result record goes straight back to mapped host memory.
-constexpr int kSmallMaxPods = 64;
+constexpr int kSmallMaxPods = 256;
 struct SmallParams {
     FtView v;
     const int64_t* h_pods;   // mapped host block int64 [pd_cols(S)][kSmallMaxPods]

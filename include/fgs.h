@@ -177,7 +177,7 @@ int fgs_sync_nodes(fgs_engine* e, fgs_packer* p, const fgs_snapshot* snap, int64
  * (:146-167). Host pod table in, per-pod results out (H2D + kernels + D2H). */
 int fgs_evaluate(fgs_engine* e, const fgs_pod_table* pods, const fgs_eval_opts* opts,
                  fgs_results* out);
-/* The reference's own call shape is ONE pod per cycle (sched/scheduler.go:425-455). For up to 64 pods, default options, a
+/* The reference's own call shape is ONE pod per cycle (sched/scheduler.go:425-455). For up to 256 pods, default options, a
  * single engine and values in the int32 range, fgs_evaluate runs as a single launch — one CTA per pod reads the pod's
  * columns from mapped host memory, ANDs the level rows, reduces, scores every node and writes the result record back to
  * mapped host memory — and leaves the same device state behind as the general path (planes, per-pod rows, staged batch),
@@ -450,7 +450,7 @@ typedef struct fgs_timings {
                                                  the per-pod prepass, emit_ms = the fused kernel) */
     int32_t reduce_lookup;                    /* 1: the last reduce pass ran Filter as table look-ups (level tables of the node
                                                  side) instead of the compare kernels (then reduce_int32 = 0) */
-    int32_t small;                            /* 1: the last fgs_evaluate ran as ONE launch (at most 64 pods, a CTA per pod: Filter,
+    int32_t small;                            /* 1: the last fgs_evaluate ran as ONE launch (at most 256 pods, a CTA per pod: Filter,
                                                  reductions, Score, selectHost and the result record; the *_ms fields are 0 then) */
     int32_t _pad;
 } fgs_timings;

@@ -1,5 +1,5 @@
 """Small batches — the reference's own call shape is one pod per scheduling cycle
-(vendor/k8s.io/kubernetes/pkg/scheduler/scheduler.go:425-455): fgs_evaluate with at most 64 pods runs the whole cycle of
+(vendor/k8s.io/kubernetes/pkg/scheduler/scheduler.go:425-455): fgs_evaluate with at most 256 pods runs the whole cycle of
 every pod in ONE launch (a CTA per pod). Its answers against the oracle, and against the general path bit for bit —
 selectHost's choice included, the two build the same key."""
 import os
@@ -40,13 +40,13 @@ def _engine(s, cfg, small):
 def test_one_launch_cycles_match_the_oracle_and_the_general_path(gpu_ok, oracle, name, skw, pkw):
     skw = dict(skw)
     cfg_id = skw.pop("cfg")
-    s = fgs.config_synth(cfg_id, n_pending=200, **skw)
+    s = fgs.config_synth(cfg_id, n_pending=400, **skw)
     cfg = fgs.config_plugins(cfg_id) if pkw is None else fgs.plugin_cfg(**pkw)
     N = s.n_nodes
     small, general = _engine(s, cfg, True), _engine(s, cfg, False)
     ref_all = oracle.evaluate(s.snapshot, s.pending, cfg, workers=4)
     seen_err = 0
-    for p0, P in ((0, 1), (1, 1), (7, 2), (10, 63), (100, 64), (40, 17)):
+    for p0, P in ((0, 1), (1, 1), (7, 2), (10, 63), (100, 64), (40, 17), (0, 256), (130, 255)):
         t = fgs.Packer(2).pods(s.pending, p0, p0 + P)
         a = small.evaluate(t, want_planes=True)
         assert small.timings()["small"]
@@ -89,8 +89,8 @@ def test_one_launch_cycles_match_the_oracle_and_the_general_path(gpu_ok, oracle,
     assert np.array_equal(got.feasible(N), ref.status == 0) and np.array_equal(got.feasible_count, ref.feasible_count)
     okm = (ref.pod_err == 0) & (ref.feasible_count >= 1)
     assert np.array_equal(got.selected_score[okm], ref.max_total[okm])
-    big = small.evaluate(fgs.Packer(2).pods(s.pending, 0, 65))
+    big = small.evaluate(fgs.Packer(2).pods(s.pending, 0, 257))
     assert not small.timings()["small"]
-    assert np.array_equal(big.feasible_count, ref_all.feasible_count[:65])
+    assert np.array_equal(big.feasible_count, ref_all.feasible_count[:257])
     small.close()
     general.close()

@@ -1,5 +1,5 @@
 // latency.cpp — what one scheduling cycle costs through the C ABI, without an interpreter in the way: fgs_evaluate for
-// P = 1, 2, 16, 64 (one launch) and 65, 256 (general path) pods on the 5 000-node C2 cluster, host pod table in, per-pod
+// P = 1 … 256 (one launch) and 257, 4096 (general path) pods on the 5 000-node C2 cluster, host pod table in, per-pod
 // results out. Build: g++ -O2 -std=c++17 -I include tools/latency.cpp -L flex-gpu-scheduler_b200 -lfgs -Wl,-rpath,$PWD/flex-gpu-scheduler_b200
 #include <chrono>
 #include <cstdio>
@@ -37,7 +37,7 @@ int main(int argc, char** argv) {
         return 1;
     }
     std::printf("{\"nodes\": %lld", (long long)n_nodes);
-    for (int P : {1, 2, 16, 64, 65, 256}) {
+    for (int P : {1, 2, 16, 64, 256, 257, 4096}) {
         const fgs_pod_table* t = nullptr;
         fgs_packer_pods(pp, fgs_synth_pending(sy), 0, P, &t);
         std::vector<int32_t> cnt(P), sel(P);
