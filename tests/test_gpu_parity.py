@@ -712,3 +712,59 @@ def test_sync_nodes_repacks_only_the_rows_whose_generation_moved(gpu_ok, oracle)
     with pytest.raises(fgs.FgsError):
         eng.sync_nodes(pk, snap.ptr)
     eng.close()
+
+
+def test_calls_that_would_corrupt_batches_in_flight_are_refused(gpu_ok):
+    """While submitted batches are in flight the node table, the plugin set and the nominated pods must not change (the
+    emit pass of a batch may still be queued behind the call), and a second thread entering the engine gets FGS_E_STATE
+    instead of sharing its staging slots."""
+    import threading
+    s = fgs.config_synth(2, n_nodes=2000, n_pending=20000)
+    cfg = fgs.config_plugins(2)
+    eng = fgs.Engine(device=0)
+    eng.set_plugins(cfg)
+    pkn = fgs.Packer(2)
+    nodes = pkn.nodes(s.snapshot)
+    eng.upload_nodes(nodes)
+    t = fgs.Packer(2).pods(s.pending)
+    want = eng.evaluate(t)
+    eng.submit(t)
+    for call in (lambda: eng.upload_nodes(nodes), lambda: eng.update_nodes(pkn.nodes(s.snapshot, 3, 4), [3]), lambda: eng.set_plugins(cfg),
+                 lambda: eng.set_nominated(t, np.zeros(20000, np.int32)), lambda: eng.schedule_sequential(t), lambda: eng.evaluate(t),
+                 lambda: eng.set_resident_batches(8)):
+        with pytest.raises(fgs.FgsError) as ei:
+            call()
+        assert ei.value.code == L.FGS_E_STATE
+    got = eng.collect()
+    assert np.array_equal(got.selected_node, want.selected_node)
+    # two threads: one evaluates in a loop, the other keeps calling in; every call either runs alone or is refused
+    stop = threading.Event()
+    refused, ran, wrong = [0], [0], [0]
+
+    def intruder():
+        while not stop.is_set():
+            try:
+                r = eng.evaluate(t)
+                ran[0] += 1
+                if not np.array_equal(r.selected_node, want.selected_node):
+                    wrong[0] += 1
+            except fgs.FgsError as ex:
+                if ex.code == L.FGS_E_STATE:
+                    refused[0] += 1
+                else:
+                    raise
+
+    th = threading.Thread(target=intruder)
+    th.start()
+    mine = 0
+    for _ in range(60):
+        try:
+            r = eng.evaluate(t)
+            mine += 1
+            assert np.array_equal(r.selected_node, want.selected_node)
+        except fgs.FgsError as ex:
+            assert ex.code == L.FGS_E_STATE
+    stop.set()
+    th.join()
+    assert wrong[0] == 0 and mine + ran[0] > 0
+    eng.close()
