@@ -138,7 +138,8 @@ class PeerGroup(C.Structure):
 class Timings(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("reduce_ms", C.c_float), ("emit_ms", C.c_float), ("d2h_ms", C.c_float),
                 ("kernel_launches", C.c_int64), ("reduce_int32", C.c_int32), ("emit_int32", C.c_int32),
-                ("seq_ms", C.c_float), ("seq_ctas", C.c_int32), ("fused", C.c_int32), ("reduce_lookup", C.c_int32), ("small", C.c_int32), ("_pad", C.c_int32)]
+                ("seq_ms", C.c_float), ("seq_ctas", C.c_int32), ("fused", C.c_int32), ("reduce_lookup", C.c_int32), ("small", C.c_int32), ("_pad", C.c_int32),
+                ("node_patches", C.c_int64), ("node_patch_redos", C.c_int64)]
 
 
 class SeqOpts(C.Structure):

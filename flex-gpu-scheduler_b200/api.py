@@ -148,6 +148,14 @@ class Packer:
         t._owner = self  # the table lives inside the packer: keep it alive with the pointer
         return t
 
+    def node_rows(self, snapshot, rows):
+        """fgs_packer_node_rows: table row i = snapshot row rows[i] (for fgs_update_nodes with the same list)"""
+        idx = np.ascontiguousarray(rows, dtype=np.int64)
+        t = C.POINTER(L.NodeTable)()
+        self._check(self._lib.fgs_packer_node_rows(self._h, snapshot, _ptr(idx, C.c_int64), len(idx), C.byref(t)))
+        t._owner = self
+        return t
+
     def pods(self, podset, p0=0, p1=None):
         if p1 is None:
             p1 = int(podset.contents.n_pods)
@@ -246,6 +254,7 @@ class Engine:
             n1 = int(snapshot.contents.n_nodes)
         n = C.c_int64(0)
         self._check(self._lib.fgs_sync_nodes(self._h, packer._h, snapshot, n0, n1, C.byref(n)))
+        self.n_nodes = n1 - n0  # the result planes are sized by it
         return int(n.value)
 
     def update_nodes(self, rows, dirty_idx):
@@ -452,7 +461,8 @@ class Engine:
         self._check(self._lib.fgs_get_timings(self._h, C.byref(t)))
         return dict(h2d_ms=t.h2d_ms, reduce_ms=t.reduce_ms, emit_ms=t.emit_ms, d2h_ms=t.d2h_ms, kernel_launches=t.kernel_launches,
                     reduce_int32=bool(t.reduce_int32), emit_int32=bool(t.emit_int32), seq_ms=t.seq_ms, seq_ctas=int(t.seq_ctas),
-                    fused=bool(t.fused), reduce_lookup=bool(t.reduce_lookup), small=bool(t.small))
+                    fused=bool(t.fused), reduce_lookup=bool(t.reduce_lookup), small=bool(t.small),
+                    node_patches=int(t.node_patches), node_patch_redos=int(t.node_patch_redos))
 
     # -- sequential cycles: assume + Reserve between pods -------------------------------------------------
     def schedule_sequential(self, pod_table, reserve_flex=True, quotas=None):

@@ -21,6 +21,7 @@
 #include "engine.h"
 #include "filter_tables.cuh"
 #include "kernels.cuh"
+#include "node_patch.cuh"
 #include "pack.h"
 #include "sample.cuh"
 
@@ -139,6 +140,10 @@ void Engine::free_all() {
     if (h_walk) cudaFreeHost(h_walk);
     if (h_small) cudaFreeHost(h_small);
     if (d_small_done) cudaFree(d_small_done);
+    if (d_patch_flag) cudaFree(d_patch_flag);
+    if (h_patch_flag) cudaFreeHost((void*)h_patch_flag);
+    if (h_patch) cudaFreeHost(h_patch);
+    if (d_patch) cudaFree(d_patch);
     if (d_nom) cudaFree(d_nom);
     if (d_pod_aux) cudaFree(d_pod_aux);
     if (h_pod_aux) cudaFreeHost(h_pod_aux);
@@ -338,6 +343,10 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
         }
         const char* sm_ = getenv("FGS_SMALL");
         e->small_off = sm_ && sm_[0] == '0';
+        const char* po_ = getenv("FGS_PATCH"); // 0: fgs_update_nodes always re-derives and re-analyses the whole table
+        e->patch_off = po_ && po_[0] == '0';
+        const char* sd_ = getenv("FGS_SMALL_DIRECT"); // 0: never compare in the small kernel, 1: always, unset: when the level tables are stale
+        e->small_direct = sd_ && (sd_[0] == '0' || sd_[0] == '1') ? sd_[0] - '0' : -1;
         const char* fm = getenv("FGS_FILTER");
         e->filter_mode = fm ? (fm[0] == 'c' ? 1 : (fm[0] == 'l' ? 2 : 0)) : 0;
         const char* ht = getenv("FGS_HOST_THREADS");
@@ -428,13 +437,31 @@ static int tz64(uint64_t v) { return v ? __builtin_ctzll(v) : 62; }
 static uint32_t narrow_spec(const Engine* e);
 
 int Engine::decide_narrow(const fgs_pod_table* t, bool launch_pods) {
+    const int rc0 = decide_narrow_once(t, launch_pods);
+    if (rc0 || narrow_batch || !an_loose || !narrow_refused_by_nodes) return rc0;
+    // Not eligible, under an analysis that row patches only ever widened (a row that left the table still counts in its OR
+    // and MAX): take it again over the table as it is now, once
+    const int rc1 = resolve_patch();
+    if (rc1) return rc1;
+    if (an_loose) {
+        const int rc2 = analyze_nodes_now(false);
+        if (rc2) return rc2;
+    }
+    return decide_narrow_once(t, launch_pods);
+}
+
+int Engine::decide_narrow_once(const fgs_pod_table* t, bool launch_pods) {
     narrow_batch = false;
+    narrow_refused_by_nodes = false;
     if (force_wide || !node_an_valid || S < 2) return FGS_OK;
     const bool sc_flex = cfg.score_mask & FGS_PL_FLEXGPU, sc_fit = cfg.score_mask & FGS_PL_FIT, sc_alloc = cfg.score_mask & FGS_PL_ALLOCATABLE;
     EvalParams ep;
     fill_eval_params(&ep, nullptr);
     if (sc_fit && !ep.fit_fast) return FGS_OK;                 // scoring resources beyond cpu/memory
-    if (sc_fit && (node_an.flags & 1)) return FGS_OK;          // a node with zero cpu/memory capacity drops out of the average
+    if (sc_fit && (node_an.flags & 1)) {                       // a node with zero cpu/memory capacity drops out of the average
+        narrow_refused_by_nodes = true;
+        return FGS_OK;
+    }
     const int64_t wsum = (sc_flex ? ep.w_flex : 0) + (sc_fit ? ep.w_fit : 0) + (sc_alloc ? ep.w_alloc : 0);
     if (ep.w_flex > 163 || ep.w_fit > 163 || ep.w_alloc > 163 || wsum * 100 + 1 >= (1 << 14)) return FGS_OK; // 14-bit score field of the warp key
     (void)t;
@@ -462,7 +489,10 @@ int Engine::decide_narrow(const fgs_pod_table* t, bool launch_pods) {
         if (s > 40) s = 40;
         const int64_t m = std::max(mx[d], (int64_t)node_an.max_val[d]) >> s;
         const int64_t limit = (d == DIM_EPH || d == DIM_S0 || d == DIM_S1) ? ((int64_t)1 << 30) : ((int64_t)1 << 24);
-        if (m >= limit) return FGS_OK;
+        if (m >= limit) {
+            narrow_refused_by_nodes = true;
+            return FGS_OK;
+        }
         sh.s[d] = s;
     }
     // buffers
@@ -693,11 +723,18 @@ void Engine::fill_derive_params(DeriveParams* dp) const {
 }
 
 // node-side analysis for the int32 specialisation (one small round trip)
-int Engine::analyze_nodes_now() {
+int Engine::analyze_nodes_now(bool table_changed) {
     Engine* e = this;
+    e->an_loose = false;
     e->node_an_valid = false;
     e->narrow_nodes_sig = -1;
-    e->node_gen++; // every change of the node table comes through here (upload, patch, sequential commits)
+    if (e->patch_spec) { // a full analysis supersedes what the row patches assumed
+        FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+        e->patch_spec = false;
+        *e->h_patch_flag = 0;
+        FGS_CUDA(e, cudaMemsetAsync(e->d_patch_flag, 0, sizeof(int), e->stream));
+    }
+    if (table_changed) e->node_gen++; // upload, full re-derive, sequential commits (row patches count their own)
     if (!e->d_an) FGS_CUDA(e, cudaMalloc(&e->d_an, sizeof(NodeAnalysis)));
     NodeAnalysis init;
     std::memset(&init, 0, sizeof(init));
@@ -731,6 +768,100 @@ static int run_derive(Engine* e) {
 }
 
 int Engine::derive_now() { return run_derive(this); }
+
+// Rows patched by patch_nodes were assumed to stay inside the node analysis the host holds. Calls that read the analysis,
+// the narrow node table or the special list wait for the patch here and redo the analysis when a row did not.
+int Engine::resolve_patch() {
+    if (!patch_spec) return FGS_OK;
+    FGS_CUDA(this, cudaStreamSynchronize(stream));
+    if (*h_patch_flag) {
+        patch_redos++;
+        return analyze_nodes_now(false);
+    }
+    patch_spec = false;
+    return FGS_OK;
+}
+
+int Engine::nodes_ready() {
+    if (!nodes_derived) return derive_now();
+    return resolve_patch();
+}
+
+// one row of a node table in the raw column order (stage_node_columns for a single row, row-major)
+static void node_row_values(const Engine* e, const fgs_node_table* t, int64_t src, int64_t* out) {
+    const int S = e->S, D = e->D;
+    out[NR_ALLOC_MCPU] = t->alloc_mcpu[src], out[NR_ALLOC_MEM] = t->alloc_mem[src], out[NR_ALLOC_EPH] = t->alloc_eph[src];
+    out[NR_ALLOC_PODS] = t->alloc_pods[src], out[NR_REQ_MCPU] = t->req_mcpu[src], out[NR_REQ_MEM] = t->req_mem[src];
+    out[NR_REQ_EPH] = t->req_eph[src], out[NR_NUM_PODS] = t->num_pods[src], out[NR_NZ_MCPU] = t->nz_mcpu[src], out[NR_NZ_MEM] = t->nz_mem[src];
+    out[NR_FLEX_GPU_SUM] = t->flex_gpu_sum[src], out[NR_FLEX_MEM_SUM] = t->flex_mem_sum[src];
+    out[NR_META] = (int64_t)(((uint64_t)t->monopoly_mask[src] << 32) | (uint64_t)t->flags[src]);
+    out[NR_PRESENT] = (int64_t)t->alloc_scalar_present[src];
+    for (int s = 0; s < S; ++s) {
+        out[nr_alloc_scalar(s)] = t->alloc_scalar[(int64_t)s * t->n_nodes + src];
+        out[nr_req_scalar(S, s)] = t->req_scalar[(int64_t)s * t->n_nodes + src];
+    }
+    for (int d = 0; d < D; ++d) out[nr_used(S, d)] = d < t->n_devices ? t->used_mem[(int64_t)d * t->n_nodes + src] : 0;
+}
+
+// fgs_update_nodes, asynchronous form: see patch_nodes (kernels_narrow.cu)
+int Engine::patch_rows(const fgs_node_table* rows, const int64_t* dirty_idx) {
+    Engine* e = this;
+    const int64_t R = rows->n_nodes;
+    const int ncols = nr_cols(S, D);
+    if (!d_patch_flag) {
+        FGS_CUDA(e, cudaMalloc(&d_patch_flag, sizeof(int)));
+        FGS_CUDA(e, cudaMemset(d_patch_flag, 0, sizeof(int)));
+        FGS_CUDA(e, cudaHostAlloc((void**)&h_patch_flag, sizeof(int), cudaHostAllocMapped));
+        *h_patch_flag = 0;
+    }
+    PatchParams pp;
+    fill_derive_params(&pp.dp);
+    pp.rows = nullptr, pp.idx = nullptr;
+    pp.n_dirty = (int)R, pp.ncols = ncols;
+    pp.ref = node_an;
+    pp.special = (long long*)d_special;
+    pp.nn = (int*)d_nn;
+    pp.sh = narrow_sh;
+    pp.fit_most = cfg.fit_strategy == 1;
+    pp.narrow_valid = d_nn && narrow_nodes_sig == cfg.fit_strategy && nn_cap >= n_pad;
+    pp.d_flag = d_patch_flag;
+    pp.h_flag = h_patch_flag;
+    if (R <= kPatchInline) {
+        for (int64_t r = 0; r < R; ++r) {
+            pp.inline_idx[r] = dirty_idx[r];
+            node_row_values(this, rows, r, (int64_t*)pp.inline_rows[r]);
+        }
+    } else {
+        const size_t need = sizeof(int64_t) * (size_t)R * (size_t)(ncols + 1);
+        if (need > patch_bytes) {
+            FGS_CUDA(e, cudaStreamSynchronize(stream));
+            if (h_patch) cudaFreeHost(h_patch);
+            if (d_patch) cudaFree(d_patch);
+            h_patch = d_patch = nullptr;
+            patch_bytes = 0;
+            FGS_CUDA(e, cudaMallocHost(&h_patch, need * 2));
+            FGS_CUDA(e, cudaMalloc(&d_patch, need * 2));
+            patch_bytes = need * 2;
+        } else if (patch_spec) {
+            FGS_CUDA(e, cudaStreamSynchronize(stream)); // the copy of the previous patch may still read the staging buffer
+        }
+        int64_t* h = (int64_t*)h_patch;
+        for (int64_t r = 0; r < R; ++r) {
+            node_row_values(this, rows, r, h + r * ncols);
+            h[R * ncols + r] = dirty_idx[r];
+        }
+        FGS_CUDA(e, cudaMemcpyAsync(d_patch, h_patch, need, cudaMemcpyHostToDevice, stream));
+        pp.rows = (const long long*)d_patch;
+        pp.idx = (const long long*)d_patch + R * ncols;
+    }
+    FGS_CUDA(e, launch_patch_nodes(pp, stream));
+    launches++;
+    node_gen++;
+    patch_spec = true;
+    an_loose = true;
+    patches++;
+    return FGS_OK;
+}
 
 // copy one table row-set into the pinned column-major staging buffer
 static void stage_node_columns(Engine* e, const fgs_node_table* t, int64_t dst0, int64_t count, int64_t src0) {
@@ -806,11 +937,15 @@ extern "C" int fgs_update_nodes(fgs_engine* eh, const fgs_node_table* rows, cons
     if (rows->n_devices > e->D) return e->fail(FGS_E_INVALID, "fgs_update_nodes: more device slots than the uploaded table; re-upload");
     if (rows->n_nodes && !dirty_idx) return e->fail(FGS_E_INVALID, "fgs_update_nodes: null dirty_idx");
     cudaSetDevice(e->device);
+    for (int64_t r = 0; r < rows->n_nodes; ++r)
+        if (dirty_idx[r] < 0 || dirty_idx[r] >= e->n_nodes) return e->fail(FGS_E_INVALID, "fgs_update_nodes: dirty index out of range");
+    if (rows->n_nodes == 0) return FGS_OK;
+    // a few rows of a table whose analysis the host holds: patched, derived and checked on the device, without waiting
+    if (!e->patch_off && e->nodes_derived && e->node_an_valid && rows->n_nodes <= Engine::kPatchMaxRows) return e->patch_rows(rows, dirty_idx);
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
     const int ncols = nr_cols(e->S, e->D);
     for (int64_t r = 0; r < rows->n_nodes; ++r) {
         const int64_t n = dirty_idx[r];
-        if (n < 0 || n >= e->n_nodes) return e->fail(FGS_E_INVALID, "fgs_update_nodes: dirty index out of range");
         stage_node_columns(e, rows, n, 1, r);
         // one small strided copy per dirty row: ncols values, pitch = n_pad
         FGS_CUDA(e, cudaMemcpy2DAsync((int64_t*)e->d_raw + n, sizeof(int64_t) * e->n_pad, (int64_t*)e->h_raw + n, sizeof(int64_t) * e->n_pad,
@@ -882,10 +1017,8 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
     if (!async) FGS_CUDA(e, cudaStreamSynchronize(e->stream));
     int rc = e->ensure_pods(t->n_pods);
     if (rc) return rc;
-    if (!e->nodes_derived) {
-        rc = run_derive(e);
-        if (rc) return rc;
-    }
+    rc = e->nodes_ready(); // derived columns, and a settled node analysis (row patches are checked on the device)
+    if (rc) return rc;
     e->n_pods = t->n_pods;
     const int64_t P = t->n_pods, pp = e->p_pad;
     const int S = e->S;
@@ -927,6 +1060,7 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
         if (rc2) return rc2;
         FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
         e->have_pods = true;
+        e->staged_gen = e->node_gen;
         e->reduced = false;
         e->staged_by_dma = true;
         return FGS_OK;
@@ -1010,6 +1144,7 @@ static int stage_pods_impl(Engine* e, const fgs_pod_table* t, bool async) {
     if (rc) return rc;
     FGS_CUDA(e, cudaEventRecord(e->events[1], e->stream));
     e->have_pods = true;
+    e->staged_gen = e->node_gen;
     e->reduced = false;
     return FGS_OK;
 }
@@ -1071,6 +1206,8 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     Engine* e = (Engine*)eh;
     FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_reduce before fgs_stage_pods");
+    if (e->staged_gen != e->node_gen)
+        return e->fail(FGS_E_STATE, "fgs_pass_reduce: the node table changed since the batch was staged (its int32 columns follow the node table): stage it again");
     cudaSetDevice(e->device);
     e->sampled = false;
     e->masked = false;
@@ -1188,6 +1325,8 @@ extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
     Engine* e = (Engine*)eh;
     FGS_ENTER(e);
     if (!e->have_pods) return e->fail(FGS_E_STATE, "fgs_pass_emit before fgs_stage_pods");
+    if (e->staged_gen != e->node_gen)
+        return e->fail(FGS_E_STATE, "fgs_pass_emit: the node table changed since the batch was staged (its int32 columns follow the node table): stage it again");
     cudaSetDevice(e->device);
     if (opts && opts->sample) { // keep only the nodes the reference's walk would have found
         const int rc = e->run_sampling(opts);
@@ -1311,11 +1450,27 @@ int Engine::evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fg
         rc = derive_now();
         if (rc) return rc;
     }
-    bool lookup = false;
-    rc = ensure_filter_tables(&lookup);
-    if (rc) return rc;
-    if (!lookup) return FGS_OK;
+    // Level tables that describe THIS node table are used; stale ones (the caller's loop changed a node since: bind, delete,
+    // NodeInfo update) are not rebuilt for a handful of pods — the kernel compares instead, which costs it one pass over
+    // the node columns per pod (from L2) and nothing up front.
     const int64_t P = t->n_pods;
+    const bool tables_current = ft && ft->valid && ft->node_gen == node_gen && ft->filter_mask == cfg.filter_mask && ft->n_pad == n_pad &&
+                                ft->v.n_dims == 5 + S && ft_rows_fit(ft->v.W);
+    // … unless the same node table keeps being asked: from the ninth call on the tables are worth their build
+    if (small_gen != node_gen) small_gen = node_gen, small_same = 0;
+    else small_same++;
+    bool direct = small_direct == 1 || (small_direct != 0 && filter_mode != 2 && !tables_current && P * n_nodes <= ((int64_t)1 << 19) && small_same < 8);
+    if (!direct) {
+        rc = resolve_patch(); // the look-up form reads the special list
+        if (rc) return rc;
+        bool lookup = false;
+        rc = ensure_filter_tables(&lookup);
+        if (rc) return rc;
+        if (!lookup) {
+            if (small_direct == 0 || filter_mode == 2 || P * n_nodes > ((int64_t)1 << 21)) return FGS_OK;
+            direct = true; // no room for the tables
+        }
+    }
     const int ncols = pd_cols(S);
     if (!h_small) {
         FGS_CUDA(e, cudaHostAlloc(&h_small, sizeof(int64_t) * ((size_t)(PD_FIXED_COLS + FGS_MAX_SCALARS + 2) * kSmallMaxPods + 8), cudaHostAllocMapped));
@@ -1358,7 +1513,8 @@ int Engine::evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fg
     if (ep.key_shift != 40) return FGS_OK;
     SmallParams sp;
     std::memset(&sp, 0, sizeof(sp));
-    sp.v = ft->v;
+    if (!direct) sp.v = ft->v;
+    sp.direct = direct ? 1 : 0;
     sp.h_pods = hp;
     sp.h_compact = hc;
     sp.d_pods = (int64_t*)d_pods;
@@ -1392,6 +1548,7 @@ int Engine::evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fg
     sp.d_done = (unsigned int*)d_small_done;
     sp.h_flag = hflag;
     sp.seq = ++small_seq;
+    sp.spec_flag = patch_spec ? d_patch_flag : nullptr;
     FGS_CUDA(e, ft_launch_small(sp, stream));
     launches++;
     if (out->feasible_bitmap || out->scores) { // planes to the host: copies behind the kernel, then the stream
@@ -1401,22 +1558,30 @@ int Engine::evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fg
         FGS_CUDA(e, cudaStreamSynchronize(stream));
     } else { // per-pod results only: watch the completion word the last CTA stores (a few µs sooner than the stream reports)
         const auto t0 = std::chrono::steady_clock::now();
-        for (unsigned spin = 1; *hflag != sp.seq; ++spin) {
+        for (unsigned spin = 1; (*hflag & ~kSmallDeclined) != sp.seq; ++spin) {
             if ((spin & 0xfff) == 0 && std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(20)) {
                 FGS_CUDA(e, cudaStreamSynchronize(stream)); // something is wrong (or very slow): let the runtime say what
-                if (*hflag != sp.seq) return fail(FGS_E_CUDA, "small-batch kernel finished without reporting");
+                if ((*hflag & ~kSmallDeclined) != sp.seq) return fail(FGS_E_CUDA, "small-batch kernel finished without reporting");
                 break;
             }
         }
     }
+    if (*hflag & kSmallDeclined) { // a patched row changed the node analysis under this launch: settle it and go again
+        rc = resolve_patch();
+        if (rc) return rc;
+        if (patch_spec) return fail(FGS_E_STATE, "small-batch kernel declined without a raised patch flag");
+        return evaluate_small(t, opts, out, done);
+    }
+    patch_spec = false; // the launch ran behind the patches and found the flag down
     unpack_results(hc, P, kSmallMaxPods, out);
     if (out->processed_nodes)
         for (int64_t i = 0; i < P; ++i) out->processed_nodes[i] = (int32_t)n_nodes;
     out->words_per_row = words_per_row;
     out->score_row_stride = score_stride;
     out->next_start_node_index = -1;
+    staged_gen = node_gen;
     have_pods = true, reduced = true, emitted = true, sampled = false, masked = false, was_fused = false, staged_by_dma = false;
-    reduce_was_lookup = true, reduce_was_narrow = false, emit_was_narrow = true, was_small = true;
+    reduce_was_lookup = !direct, reduce_was_narrow = false, emit_was_narrow = true, was_small = true;
     last_key_shift = 40;
     tm.h2d_ms = tm.reduce_ms = tm.emit_ms = tm.d2h_ms = 0.f;
     *done = true;
@@ -1476,6 +1641,8 @@ extern "C" int fgs_score_masked(fgs_engine* eh, const uint32_t* mask, int32_t ma
     if (e->in_flight) return e->fail(FGS_E_STATE, "fgs_score_masked while submitted batches are in flight: fgs_collect them first");
     if (!e->have_pods || !e->reduced)
         return e->fail(FGS_E_STATE, "fgs_score_masked: no filtered batch — run fgs_evaluate with skip_pass_b (or fgs_stage_pods + fgs_pass_reduce) first");
+    if (e->staged_gen != e->node_gen)
+        return e->fail(FGS_E_STATE, "fgs_score_masked: the node table changed since the batch was staged (its int32 columns follow the node table): stage it again");
     if (e->was_fused) return e->fail(FGS_E_STATE, "fgs_score_masked after the fused pass: its bitmap has been scored already; stage the batch again");
     if (opts && (opts->sample || opts->skip_pass_b)) return e->fail(FGS_E_INVALID, "fgs_score_masked: sample / skip_pass_b make no sense here");
     cudaSetDevice(e->device);
@@ -1582,6 +1749,8 @@ extern "C" int fgs_get_timings(fgs_engine* eh, fgs_timings* t) {
     t->fused = e->was_fused ? 1 : 0;
     t->reduce_lookup = e->reduce_was_lookup ? 1 : 0;
     t->small = e->was_small ? 1 : 0;
+    t->node_patches = (int64_t)e->patches;
+    t->node_patch_redos = (int64_t)e->patch_redos;
     return FGS_OK;
 }
 

@@ -71,12 +71,29 @@ struct Engine {
     int64_t special_cap = 0;
     int64_t nn_cap = 0, pn_cap = 0;
     int decide_narrow(const fgs_pod_table* t, bool launch_pods = true);
+    int decide_narrow_once(const fgs_pod_table* t, bool launch_pods);
+    bool narrow_refused_by_nodes = false; // the last decide_narrow_once said no because of the node analysis
     // small batches (<= 64 pods): the whole cycle of every pod in one launch (filter_tables.cu: small_cycle); pod columns and
     // result records travel through one block of mapped host memory. FGS_SMALL=0 turns the path off (tests).
     void* h_small = nullptr; // mapped: int64 [pd_cols][64] pod columns, then int64 [2][64] result records, then the completion word
     void* d_small_done = nullptr; // device counter of finished pods
     uint64_t small_seq = 0;
     bool small_off = false;
+    int small_direct = -1;
+    uint64_t small_gen = ~0ull; // node_gen of the last small-batch call, and how many calls in a row it has served
+    int small_same = 0;
+    // row patches (patch_nodes): the flag a row outside the host's node analysis raises, the staging pair for many rows
+    bool patch_off = false, patch_spec = false;
+    bool an_loose = false; // rows were patched since the last full analysis: it may be wider than the table needs
+    int* d_patch_flag = nullptr;
+    volatile int* h_patch_flag = nullptr;
+    void *h_patch = nullptr, *d_patch = nullptr;
+    size_t patch_bytes = 0;
+    uint64_t patches = 0, patch_redos = 0;
+    uint64_t staged_gen = 0; // node_gen when the current batch was staged
+    int resolve_patch();
+    int nodes_ready();
+    int patch_rows(const fgs_node_table* rows, const int64_t* dirty_idx);
     bool was_small = false;  // the last fgs_evaluate took it
     int evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fgs_results* out, bool* done);
     void fill_narrow_params(NarrowParams* p) const;
@@ -110,6 +127,7 @@ struct Engine {
         cudaEvent_t ev_reduce = nullptr, ev_merge1 = nullptr, ev_emit = nullptr, ev_merge2 = nullptr;
         cudaEvent_t ev_t0 = nullptr, ev_emit0 = nullptr; // FGS_PIPE_TRACE: start of the filter pass / of the emit pass
     };
+    static constexpr int64_t kPatchMaxRows = 4096; // fgs_update_nodes beyond this re-derives the whole table
     static constexpr int kSlots = 32; // upper bound of fgs_set_resident_batches
     Slot slots[kSlots];
     // batches in flight: two on one GPU (a third buys nothing there while the tables are resident, tools/pipe_breakdown.py),
@@ -207,7 +225,7 @@ struct Engine {
     void preempt_free();
     void fill_derive_params(DeriveParams* dp) const;
     int derive_now();        // derive_node_columns over the whole table + analysis
-    int analyze_nodes_now(); // node-side analysis for the int32 specialisation (after any change of d_nd)
+    int analyze_nodes_now(bool table_changed = true); // node-side analysis for the int32 specialisation (after any change of d_nd)
 };
 
 // first statement of every entry point that takes an engine

@@ -482,6 +482,14 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     const i64 W = prm.W, pp = prm.p_pad;
     const int S = prm.S, ncols = pd_cols(S), n_dims = 5 + S;
 
+    if (prm.spec_flag && *(const volatile int*)prm.spec_flag) { // a patched row left the node analysis: the host redoes it and calls again
+        if (tid == 0 && atomicAdd(prm.d_done, 1u) == (unsigned)(prm.n_pods - 1)) {
+            *prm.d_done = 0;
+            __threadfence_system();
+            *prm.h_flag = prm.seq | kSmallDeclined;
+        }
+        return;
+    }
     // ---- the pod's columns: mapped host memory → shared memory and the device table ----------------------------------------
     if (tid < ncols) {
         const i64 v = prm.h_pods[(i64)tid * kSmallMaxPods + p];
@@ -508,6 +516,83 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
         Wn(PN_NZM, nzm);
         Wn(PN_KIND, (int)kind);
     }
+    const bool sc_flex = prm.score_mask & FGS_PL_FLEXGPU, sc_fit = prm.score_mask & FGS_PL_FIT, sc_alloc = prm.score_mask & FGS_PL_ALLOCATABLE;
+    uint32_t count = 0;
+    if (prm.direct) {
+        // ---- no level tables (the node table changed since they were built, and a handful of pods does not pay for a rebuild):
+        // Filter by comparing, as eval_kernel<REDUCE> does; warp w owns the bitmap words w, w + 32, …
+        __shared__ i64 s_w[4][kSmallThreads / 32];
+        __shared__ int s_wf[2][kSmallThreads / 32];
+        const bool flex_f = prm.filter_mask & FGS_PL_FLEXGPU, fit_f = prm.filter_mask & FGS_PL_FIT;
+        const i64 lim = kind == 1 ? s_pod[PD_GPU_LIM] : s_pod[PD_MEM_LIM];
+        i64 vflex = kMin, vhi = kMin, vnlo = kMin, neg = 0;
+        int spanic = 0, fpanic = 0;
+        uint32_t cnt = 0;
+        for (i64 n0 = (i64)warp * 32; n0 < prm.n_pad; n0 += kSmallThreads) {
+            const i64 n = n0 + lane;
+            bool feas = false;
+            if (n < prm.n_nodes) {
+                auto C = [&](int c) { return __ldg(prm.nd + (i64)c * prm.n_pad + n); };
+                const uint32_t fl = (uint32_t)C(ND_FLAGS);
+                const bool valid = fl & FGS_NF_VALID;
+                bool flex_ok = true;
+                if (flex_f) { // flex_gpu.go:41-119: no limit passes, both limits never, else limit <= per-kind threshold
+                    if (kind == 3) flex_ok = false;
+                    else if (kind == 1) flex_ok = lim <= C(ND_THR_GPU);
+                    else if (kind == 2) flex_ok = lim <= C(ND_THR_MEM);
+                }
+                bool fit_ok = true;
+                if (fit_f) { // fit.go:256-329
+                    fit_ok = fl & NDF_PODS_OK;
+                    if (fit_ok && !none) {
+                        fit_ok = s_pod[PD_REQ_CPU] <= C(ND_FREE_CPU) && s_pod[PD_REQ_MEM] <= C(ND_FREE_MEM) && s_pod[PD_REQ_EPH] <= C(ND_FREE_EPH);
+                        for (int sidx = 0; sidx < S && fit_ok; ++sidx)
+                            if (((smask >> sidx) & 1u) && s_pod[PD_FIXED_COLS + sidx] > C(nd_free_scalar(sidx))) fit_ok = false;
+                    }
+                }
+                // NewGPUNode would panic inside FlexGPU.Filter (flex_gpu.go:101) when the filter gets that far on such a node
+                const bool reach = flex_f && (kind == 1 || kind == 2) && flex_ok && (fl & FGS_NF_REF_PANIC) && (prm.flex_first || fit_ok) && valid;
+                if (reach) fpanic = 1;
+                feas = flex_ok && fit_ok && valid && !reach;
+                if (feas) {
+                    const i64 ms = C(ND_MEM_SCORE);
+                    const i64 sc = (kind & 1u) ? C(ND_GPU_SCORE) : (kind == 2 ? ms : 0);
+                    vflex = sc > vflex ? sc : vflex;
+                    const i64 ar = C(ND_ALLOC_RAW);
+                    vhi = ar > vhi ? ar : vhi;
+                    vnlo = -ar > vnlo ? -ar : vnlo;
+                    if (kind == 2 && ms < 0 && -ms > neg) neg = -ms;
+                    if (fl & FGS_NF_REF_PANIC) spanic = 1;
+                }
+            }
+            const uint32_t word = __ballot_sync(0xffffffffu, feas);
+            if (lane == 0) {
+                s_row[n0 >> 5] = word;
+                prm.bitmap[p * W + (n0 >> 5)] = word;
+                cnt += (uint32_t)__popc(word);
+            }
+        }
+        vflex = warp_max_i64(vflex), vhi = warp_max_i64(vhi), vnlo = warp_max_i64(vnlo), neg = warp_max_i64(neg);
+        spanic = __any_sync(0xffffffffu, spanic);
+        fpanic = __any_sync(0xffffffffu, fpanic);
+        if (lane == 0) {
+            s_cnt[warp] = cnt;
+            s_w[0][warp] = vflex, s_w[1][warp] = vhi, s_w[2][warp] = vnlo, s_w[3][warp] = neg;
+            s_wf[0][warp] = spanic ? 1 : 0, s_wf[1][warp] = fpanic ? 1 : 0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int w = 0; w < kSmallThreads / 32; ++w) count += s_cnt[w];
+        if (warp == 0) {
+            i64 r0 = warp_max_i64(s_w[0][lane]), r1 = warp_max_i64(s_w[1][lane]), r2 = warp_max_i64(s_w[2][lane]), r3 = warp_max_i64(s_w[3][lane]);
+            const int f0 = __any_sync(0xffffffffu, s_wf[0][lane]), f1 = __any_sync(0xffffffffu, s_wf[1][lane]);
+            if (lane == 0) {
+                s_red[0] = sc_flex ? r0 : kMin, s_red[1] = sc_alloc ? r1 : kMin, s_red[2] = sc_alloc ? r2 : kMin, s_red[3] = r3;
+                s_flags[0] = f0 ? 1 : 0, s_flags[1] = f1 ? 1 : 0;
+            }
+        }
+        __syncthreads();
+    } else {
     // ---- the row of every dimension (ft_pod_rows): warp d searches dimension d's levels ------------------------------------
     if (warp < n_dims) {
         const int d = warp;
@@ -552,10 +637,8 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
         if (lane == 0) s_cnt[warp] = cnt;
     }
     __syncthreads();
-    uint32_t count = 0;
 #pragma unroll
     for (int w = 0; w < kSmallThreads / 32; ++w) count += s_cnt[w];
-    const bool sc_flex = prm.score_mask & FGS_PL_FLEXGPU, sc_fit = prm.score_mask & FGS_PL_FIT, sc_alloc = prm.score_mask & FGS_PL_ALLOCATABLE;
     // ---- NormalizeScore's maxima (warp 0) and the special nodes (warp 1): as filter_rows -----------------------------------
     if (warp == 0) {
         i64 vflex = kMin, vhi = kMin, vnlo = kMin;
@@ -620,6 +703,7 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
         if (lane == 0) s_red[3] = neg, s_flags[0] = spanic ? 1 : 0, s_flags[1] = fpanic ? 1 : 0;
     }
     __syncthreads();
+    }
     // ---- Score, NormalizeScore, weights, sum, selectHost key: emit_narrow's arithmetic, one node at a time --------------------
     const i64 raw_fmax = s_red[0];
     i64 fmx = raw_fmax < 0 ? 0 : raw_fmax; // maxCount starts at 0 (normalize_score.go:27)

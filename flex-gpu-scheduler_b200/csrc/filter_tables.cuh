@@ -123,6 +123,7 @@ cudaError_t ft_launch_masked(const FtMaskParams& p, cudaStream_t stream);
 // normaliser reductions are block reductions, every node is scored with the int32 arithmetic of emit_narrow (same magic
 // multipliers, same selectHost key) and the 16-byte result record goes straight back to mapped host memory.
 constexpr int kSmallMaxPods = 256;
+constexpr uint64_t kSmallDeclined = 1ull << 63;
 struct SmallParams {
     FtView v;
     const int64_t* h_pods;   // mapped host block int64 [pd_cols(S)][kSmallMaxPods]
@@ -149,6 +150,9 @@ struct SmallParams {
     unsigned int* d_done;
     volatile uint64_t* h_flag;
     uint64_t seq;
+    const int* spec_flag; // row patches not yet confirmed by the host (patch_nodes): non-zero → the node analysis this launch was
+                          // parameterised by no longer holds; every CTA leaves and the completion word carries kSmallDeclined
+    int direct; // 1: no level tables (stale or over their limit): Filter by comparing every node's thresholds, maxima by reduction
 };
 cudaError_t ft_launch_small(const SmallParams& p, cudaStream_t stream);
 

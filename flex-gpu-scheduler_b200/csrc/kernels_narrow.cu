@@ -19,6 +19,8 @@
 
 #include "kernels.cuh"
 #include "kernels_narrow.cuh"
+#include "node_patch.cuh"
+#include "derive.cuh"
 
 namespace fgs {
 
@@ -74,56 +76,83 @@ __device__ __forceinline__ int qfix32(int x, int d, float est) {
 
 // ---- narrowing kernels --------------------------------------------------------------------------
 
-// OR and MAX of the derived node columns per resource dimension (valid nodes only)
+// What one derived node row adds to the analysis (valid nodes only): OR and MAX per resource dimension, the two flags,
+// whether the per-pod error bits depend on the node (special_pass) and with which magnitude
+struct RowAnalysis {
+    u64 o[ND_DIMS];
+    i64 mx[ND_DIMS];
+    i64 araw, mag;
+    int capzero, negscore, valid, special, panic;
+};
+
+__device__ __forceinline__ void analyze_row(const i64* nd, i64 n_pad, i64 n, RowAnalysis& a) {
+    for (int d = 0; d < ND_DIMS; ++d) {
+        a.o[d] = 0;
+        a.mx[d] = 0;
+    }
+    a.araw = 0, a.mag = 0;
+    a.capzero = a.negscore = a.valid = a.special = a.panic = 0;
+    auto C = [&](int c) { return nd[(i64)c * n_pad + n]; };
+    const uint32_t fl = (uint32_t)C(ND_FLAGS);
+    if (!(fl & FGS_NF_VALID)) return;
+    a.valid = 1;
+    auto acc = [&](int d, i64 v) { // negative values are clamped to -1 by the narrowing, so only v >= 0 matters
+        if (v > 0) {
+            a.o[d] |= (u64)v;
+            if (v > a.mx[d]) a.mx[d] = v;
+        }
+    };
+    acc(DIM_CPU, C(ND_FREE_CPU));
+    acc(DIM_CPU, C(ND_CAP_CPU));
+    acc(DIM_CPU, C(ND_NZR_CPU));
+    acc(DIM_MEM, C(ND_FREE_MEM));
+    acc(DIM_MEM, C(ND_CAP_MEM));
+    acc(DIM_MEM, C(ND_NZR_MEM));
+    acc(DIM_EPH, C(ND_FREE_EPH));
+    acc(DIM_S0, C(nd_free_scalar(0)));
+    acc(DIM_S1, C(nd_free_scalar(1)));
+    const i64 tg = C(ND_THR_GPU), tm = C(ND_THR_MEM);
+    if (tg != kI64Min) acc(DIM_FG, tg);
+    if (tm != kI64Min && tm != 0x7fffffffffffffffll) acc(DIM_FM, tm);
+    acc(DIM_FG, C(ND_GPU_SCORE));
+    const i64 ms = C(ND_MEM_SCORE);
+    acc(DIM_FM, ms < 0 ? -ms : ms); // a negative MemScore (over-committed device) keeps its sign when narrowed
+    if (ms < 0) a.negscore = 1;
+    if (ms < 0 || (fl & FGS_NF_REF_PANIC)) { // nodes the per-pod error bits depend on (special_pass)
+        a.special = 1;
+        a.panic = (fl & FGS_NF_REF_PANIC) ? 1 : 0;
+        a.mag = ms < 0 ? -ms : 0;
+    }
+    if (C(ND_CAP_CPU) <= 0 || C(ND_CAP_MEM) <= 0) a.capzero = 1;
+    a.araw = C(ND_ALLOC_RAW);
+}
+
 __global__ void __launch_bounds__(256) analyze_nodes(const i64* __restrict__ nd, i64 n_nodes, i64 n_pad, int S, NodeAnalysis* out,
                                                      i64* __restrict__ special) {
     const i64 n = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-    u64 o[ND_DIMS];
-    i64 mx[ND_DIMS];
+    (void)S;
+    RowAnalysis ra;
     for (int d = 0; d < ND_DIMS; ++d) {
-        o[d] = 0;
-        mx[d] = 0;
+        ra.o[d] = 0;
+        ra.mx[d] = 0;
     }
+    ra.capzero = ra.negscore = ra.valid = 0;
     i64 amin = 0x7fffffffffffffffll, amax = kI64Min;
-    int capzero = 0, negscore = 0, anyvalid = 0;
     if (n < n_nodes) {
-        auto C = [&](int c) { return nd[(i64)c * n_pad + n]; };
-        const uint32_t fl = (uint32_t)C(ND_FLAGS);
-        if (fl & FGS_NF_VALID) {
-            anyvalid = 1;
-            auto acc = [&](int d, i64 v) { // negative values are clamped to -1 by the narrowing, so only v >= 0 matters
-                if (v > 0) {
-                    o[d] |= (u64)v;
-                    if (v > mx[d]) mx[d] = v;
-                }
-            };
-            acc(DIM_CPU, C(ND_FREE_CPU));
-            acc(DIM_CPU, C(ND_CAP_CPU));
-            acc(DIM_CPU, C(ND_NZR_CPU));
-            acc(DIM_MEM, C(ND_FREE_MEM));
-            acc(DIM_MEM, C(ND_CAP_MEM));
-            acc(DIM_MEM, C(ND_NZR_MEM));
-            acc(DIM_EPH, C(ND_FREE_EPH));
-            acc(DIM_S0, C(nd_free_scalar(0)));
-            acc(DIM_S1, C(nd_free_scalar(1)));
-            const i64 tg = C(ND_THR_GPU), tm = C(ND_THR_MEM);
-            if (tg != kI64Min) acc(DIM_FG, tg);
-            if (tm != kI64Min && tm != 0x7fffffffffffffffll) acc(DIM_FM, tm);
-            acc(DIM_FG, C(ND_GPU_SCORE));
-            const i64 ms = C(ND_MEM_SCORE);
-            acc(DIM_FM, ms < 0 ? -ms : ms); // a negative MemScore (over-committed device) keeps its sign when narrowed
-            if (ms < 0) negscore = 1;
-            if (ms < 0 || (fl & FGS_NF_REF_PANIC)) { // nodes the per-pod error bits depend on (special_pass)
+        analyze_row(nd, n_pad, n, ra);
+        if (ra.valid) {
+            if (ra.special) {
                 const int k = atomicAdd(&out->n_special, 1);
-                special[k] = n | ((fl & FGS_NF_REF_PANIC) ? ((i64)1 << 40) : 0);
-                special[n_pad + k] = ms < 0 ? -ms : 0;
+                special[k] = n | (ra.panic ? ((i64)1 << 40) : 0);
+                special[n_pad + k] = ra.mag;
             }
-            if (C(ND_CAP_CPU) <= 0 || C(ND_CAP_MEM) <= 0) capzero = 1;
-            const i64 ar = C(ND_ALLOC_RAW);
-            amin = ar;
-            amax = ar;
+            amin = ra.araw;
+            amax = ra.araw;
         }
     }
+    u64(&o)[ND_DIMS] = ra.o;
+    i64(&mx)[ND_DIMS] = ra.mx;
+    const int capzero = ra.capzero, negscore = ra.negscore, anyvalid = ra.valid;
     // block reduce through shared memory atomics, then one global atomic per block and value
     __shared__ u64 s_or[ND_DIMS];
     __shared__ i64 s_mx[ND_DIMS];
@@ -186,12 +215,10 @@ __global__ void __launch_bounds__(128) special_pass(const uint32_t* __restrict__
 
 __device__ __forceinline__ int narrow_free(i64 v, int sh) { return v < 0 ? -1 : (int)(v >> sh); }
 
-__global__ void __launch_bounds__(256) narrow_nodes(const i64* __restrict__ nd, i64 n_pad, NarrowShifts sh, int fit_most, int* __restrict__ nn) {
-    const i64 n = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= n_pad) return;
+template <typename NdPtr>
+__device__ __forceinline__ void narrow_one_node(NdPtr nd, i64 n_pad, const NarrowShifts& sh, int fit_most, int* __restrict__ nn, i64 n) {
     auto C = [&](int c) { return nd[(i64)c * n_pad + n]; };
     auto W = [&](int c, int v) { nn[(i64)c * n_pad + n] = v; };
-    auto WF = [&](int c, float v) { nn[(i64)c * n_pad + n] = __float_as_int(v); };
     const i64 tg = C(ND_THR_GPU), tm = C(ND_THR_MEM);
     W(NN_THR_GPU, tg == kI64Min ? -1 : (tg < 0 ? -1 : (int)(tg > 0x3fffffff ? 0x3fffffff : tg)));
     // thr_mem == INT64_MAX cannot happen (min with a finite headroom), negative → -1
@@ -223,6 +250,55 @@ __global__ void __launch_bounds__(256) narrow_nodes(const i64* __restrict__ nd, 
     W(NN_MAG_C, (int)narrow_magic(capc > 0 ? (uint32_t)capc : 0u, &lc));
     W(NN_MAG_M, (int)narrow_magic(capm > 0 ? (uint32_t)capm : 0u, &lm));
     W(NN_MAG_SH, lc | (lm << 8));
+}
+
+
+__global__ void __launch_bounds__(256) narrow_nodes(const i64* __restrict__ nd, i64 n_pad, NarrowShifts sh, int fit_most, int* __restrict__ nn) {
+    const i64 n = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= n_pad) return;
+    narrow_one_node(nd, n_pad, sh, fit_most, nn, n);
+}
+
+// fgs_update_nodes for a few rows, one thread per row and no host round trip: the raw columns are stored, the row is derived
+// again (derive_row, from the values handed in), narrowed under the shifts in force, and checked against the analysis the
+// host decides by. A row that stays inside it — no bit below a dimension's lowest set bit, no value above its maximum, no
+// new flag, and the same membership of the special list — changes nothing the host knows; any other row raises the
+// flag, and the next call that needs the analysis redoes it for the whole table (Engine::resolve_patch). The small-batch
+// kernel reads the flag itself and declines to run, so a patch and the cycle that follows need no synchronisation.
+__global__ void __launch_bounds__(128) patch_nodes(const __grid_constant__ PatchParams prm) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= prm.n_dirty) return;
+    const i64 n = prm.rows ? prm.idx[r] : prm.inline_idx[r];
+    const i64* row = prm.rows ? prm.rows + (i64)r * prm.ncols : &prm.inline_rows[r][0];
+    const i64 np = prm.dp.n_pad;
+    i64* nd = (i64*)prm.dp.nd;
+    i64* raw = (i64*)prm.dp.raw;
+    const uint32_t fl0 = (uint32_t)nd[(i64)ND_FLAGS * np + n];
+    const bool special0 = (fl0 & FGS_NF_VALID) && (nd[(i64)ND_MEM_SCORE * np + n] < 0 || (fl0 & FGS_NF_REF_PANIC));
+    for (int c = 0; c < prm.ncols; ++c) raw[(i64)c * np + n] = row[c];
+    derive_row(prm.dp, row, 1, nd + n, np);
+    RowAnalysis a;
+    analyze_row(nd, np, n, a);
+    bool inside = special0 == (bool)a.special;
+    for (int d = 0; d < ND_DIMS; ++d) {
+        const u64 ro = prm.ref.or_bits[d];
+        const u64 below = ro ? ((ro & (0 - ro)) - 1) : ~0ull; // the bits under the lowest one any node had set
+        if ((a.o[d] & below) || a.mx[d] > prm.ref.max_val[d]) inside = false;
+    }
+    if ((a.capzero | (a.negscore << 1)) & ~prm.ref.flags) inside = false;
+    if (!inside) {
+        *prm.d_flag = 1;
+        *prm.h_flag = 1;
+        return;
+    }
+    if (a.special) { // its entry of the special list, in place
+        for (int k = 0; k < prm.ref.n_special; ++k)
+            if ((prm.special[k] & 0xffffffffll) == n) {
+                prm.special[k] = n | (a.panic ? ((i64)1 << 40) : 0);
+                prm.special[np + k] = a.mag;
+            }
+    }
+    if (prm.narrow_valid) narrow_one_node((const i64*)nd, np, prm.sh, prm.fit_most, prm.nn, n);
 }
 
 __global__ void __launch_bounds__(256) narrow_pods(const i64* __restrict__ pods, i64 p_pad, int S, NarrowShifts sh, uint32_t fit_ignored,
@@ -259,6 +335,11 @@ void launch_special_pass(const uint32_t* bitmap, int64_t words_per_row, const in
     if (n_special <= 0 || n_pods <= 0) return;
     special_pass<<<(unsigned)((n_pods + 127) / 128), 128, 0, (cudaStream_t)stream>>>(bitmap, words_per_row, (const i64*)special, n_pad, n_special,
                                                                                   (const i64*)pods, (i64*)reduce_max, n_pods, p_pad);
+}
+
+cudaError_t launch_patch_nodes(const PatchParams& p, void* stream) {
+    patch_nodes<<<(unsigned)((p.n_dirty + 127) / 128), 128, 0, (cudaStream_t)stream>>>(p);
+    return cudaGetLastError();
 }
 
 void launch_narrow_nodes(const int64_t* nd, int64_t n_pad, const NarrowShifts& sh, int fit_most, int* nn, void* stream) {

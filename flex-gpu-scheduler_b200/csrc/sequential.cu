@@ -177,10 +177,8 @@ extern "C" int fgs_schedule_sequential(fgs_engine* eh, const fgs_pod_table* t, c
         return e->fail(FGS_E_STATE, "fgs_schedule_sequential: the engine must hold the whole cluster (node_index_base 0)");
     cudaSetDevice(e->device);
     FGS_CUDA(e, cudaStreamSynchronize(e->stream));
-    if (!e->nodes_derived) {
-        rc = e->derive_now();
-        if (rc) return rc;
-    }
+    rc = e->nodes_ready();
+    if (rc) return rc;
     const int64_t P = t->n_pods;
     if (P == 0) return FGS_OK;
     const int64_t pp = round_up64(P, kSeqTileP);

@@ -453,6 +453,8 @@ typedef struct fgs_timings {
     int32_t small;                            /* 1: the last fgs_evaluate ran as ONE launch (at most 256 pods, a CTA per pod: Filter,
                                                  reductions, Score, selectHost and the result record; the *_ms fields are 0 then) */
     int32_t _pad;
+    int64_t node_patches;                     /* fgs_update_nodes calls served by the row-patch kernel (no host round trip), and … */
+    int64_t node_patch_redos;                 /* … how many times a patched row left the node analysis, so that it was redone */
 } fgs_timings;
 int fgs_get_timings(fgs_engine* e, fgs_timings* t);
 

@@ -25,31 +25,36 @@ CASES = [
 ]
 
 
-def _engine(s, cfg, small):
+def _engine(s, cfg, small, direct=None):
     os.environ["FGS_SMALL"] = "1" if small else "0"
+    if direct is not None:
+        os.environ["FGS_SMALL_DIRECT"] = "1" if direct else "0"
     try:
         eng = fgs.Engine(device=0, n_scalars=2, total_nodes=s.n_nodes)
     finally:
         os.environ.pop("FGS_SMALL", None)
+        os.environ.pop("FGS_SMALL_DIRECT", None)
     eng.set_plugins(cfg)
     eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot))
     return eng
 
 
+@pytest.mark.parametrize("direct", [False, True], ids=["level-tables", "compare"])
 @pytest.mark.parametrize("name,skw,pkw", CASES, ids=[c[0] for c in CASES])
-def test_one_launch_cycles_match_the_oracle_and_the_general_path(gpu_ok, oracle, name, skw, pkw):
+def test_one_launch_cycles_match_the_oracle_and_the_general_path(gpu_ok, oracle, name, skw, pkw, direct):
+    """direct: the kernel's Filter without level tables (what it does when the node table changed since they were built)"""
     skw = dict(skw)
     cfg_id = skw.pop("cfg")
     s = fgs.config_synth(cfg_id, n_pending=400, **skw)
     cfg = fgs.config_plugins(cfg_id) if pkw is None else fgs.plugin_cfg(**pkw)
     N = s.n_nodes
-    small, general = _engine(s, cfg, True), _engine(s, cfg, False)
+    small, general = _engine(s, cfg, True, direct), _engine(s, cfg, False)
     ref_all = oracle.evaluate(s.snapshot, s.pending, cfg, workers=4)
     seen_err = 0
     for p0, P in ((0, 1), (1, 1), (7, 2), (10, 63), (100, 64), (40, 17), (0, 256), (130, 255)):
         t = fgs.Packer(2).pods(s.pending, p0, p0 + P)
         a = small.evaluate(t, want_planes=True)
-        assert small.timings()["small"]
+        assert small.timings()["small"] and small.timings()["reduce_lookup"] == (not direct)
         b = general.evaluate(t, want_planes=True)
         assert not general.timings()["small"]
         ref_status = ref_all.status[p0:p0 + P]
@@ -94,3 +99,58 @@ def test_one_launch_cycles_match_the_oracle_and_the_general_path(gpu_ok, oracle,
     assert np.array_equal(big.feasible_count, ref_all.feasible_count[:257])
     small.close()
     general.close()
+
+
+def test_cycles_between_node_changes_need_no_table_rebuild(gpu_ok, oracle):
+    """The reference's loop: schedule one pod, bind it (the node's NodeInfo changes), schedule the next
+    (scheduler.go:425-455, cache.go:197-276). After fgs_sync_nodes the level tables describe the OLD node table; a small
+    batch is answered by the compare form of the one-launch kernel instead of rebuilding them, a large one rebuilds."""
+    import ctypes as C
+    S, N = 2, 2500
+    s = fgs.config_synth(2, n_nodes=N, n_pending=300, pm_quirk_nodes=40)
+    cfg = fgs.config_plugins(2)
+    # a private copy of the snapshot whose aggregates this test edits the way a bind does (NodeInfo.AddPod:
+    # Requested / NonZeroRequested grow, Generation moves)
+    snap = L.Snapshot()
+    C.memmove(C.byref(snap), s.snapshot, C.sizeof(L.Snapshot))
+    req = np.ctypeslib.as_array(snap.requested, shape=(N, 3 + S)).copy()
+    nz = np.ctypeslib.as_array(snap.nonzero, shape=(N, 2)).copy()
+    gen = np.arange(1, N + 1, dtype=np.int64)
+    snap.requested, snap.nonzero, snap.generation = (a.ctypes.data_as(L.p_i64) for a in (req, nz, gen))
+    snap_p = C.pointer(snap)
+    eng = fgs.Engine(device=0)
+    eng.set_plugins(cfg)
+    pk = fgs.Packer(S)
+
+    def check(p0, p1, want_lookup):
+        eng.sync_nodes(pk, snap_p)
+        got = eng.evaluate(fgs.Packer(S).pods(s.pending, p0, p1), want_planes=True)
+        tm = eng.timings()
+        assert tm["small"] and tm["reduce_lookup"] == want_lookup, tm
+        ref = oracle.evaluate(snap_p, s.pending, cfg, p0, p1, workers=2)
+        assert np.array_equal(got.feasible(N), ref.status == 0)
+        assert np.array_equal(got.feasible_count, ref.feasible_count) and np.array_equal(got.pod_err, ref.pod_err)
+        ok = (ref.pod_err == 0) & (ref.feasible_count >= 1)
+        m = (ref.status == 0) & ok[:, None]
+        assert np.array_equal(got.scores[:, :N][m], ref.total[m])
+        assert np.array_equal(got.selected_score[ok], ref.max_total[ok])
+        idx = np.nonzero(ok)[0]
+        assert np.array_equal(ref.total[idx, got.selected_node[idx]], ref.max_total[idx])
+        return got
+
+    check(0, 1, False)        # nothing built yet: one pod does not pay for the tables
+    check(0, 256, True)       # 256 pods do (256 x 2500 is still one launch)
+    check(5, 6, True)         # ... and now they are current
+    g = N + 1
+    rng = np.random.default_rng(4242)
+    for cycle in range(12):   # the pod of the last cycle is bound to the node chosen for it before the next one runs
+        got = check(cycle, cycle + 1 + cycle % 3, cycle == 0)
+        i = int(got.selected_node[0]) if got.feasible_count[0] > 0 else int(rng.integers(N))
+        req[i, 0] += 500
+        req[i, 1] += 256 << 20
+        nz[i, 0] += 500
+        nz[i, 1] += 256 << 20
+        gen[i] = g
+        g += 1
+    check(0, 256, True)
+    eng.close()

@@ -59,6 +59,58 @@ int main(int argc, char** argv) {
         fgs_get_timings(e, &tm);
         std::printf(", \"evaluate_%d_pods_us\": %.1f, \"one_launch_%d\": %d", P, us, P, tm.small);
     }
+    // The reference's real loop: between two cycles a NodeInfo changed (the pod just bound; cache.go:197-276 bumps its
+    // Generation). fgs_sync_nodes repacks and patches that row, then the next pod is evaluated — the level tables are
+    // stale every time, so the one-launch kernel filters by comparing.
+    {
+        fgs_snapshot snap = *fgs_synth_snapshot(sy);
+        std::vector<int64_t> gen(n_nodes);
+        for (int64_t i = 0; i < n_nodes; ++i) gen[i] = i + 1;
+        snap.generation = gen.data();
+        int64_t g = n_nodes + 1, nrep = 0;
+        if (fgs_sync_nodes(e, pn, &snap, 0, n_nodes, &nrep)) {
+            std::fprintf(stderr, "%s\n", fgs_last_error(e));
+            return 1;
+        }
+        std::vector<const fgs_pod_table*> one(64);
+        std::vector<fgs_packer*> pks(64);
+        for (int k = 0; k < 64; ++k) {
+            fgs_packer_create(2, &pks[k]);
+            fgs_packer_pods(pks[k], fgs_synth_pending(sy), k, k + 1, &one[k]);
+        }
+        int32_t cnt = 0, sel = 0;
+        int64_t sc = 0;
+        uint32_t err = 0;
+        fgs_results r;
+        std::memset(&r, 0, sizeof(r));
+        r.feasible_count = &cnt, r.selected_node = &sel, r.selected_score = &sc, r.pod_err = &err;
+        const int reps = 2000;
+        double sync_us = 0, eval_us = 0;
+        int direct = 0;
+        for (int k = -50; k < reps; ++k) {
+            const auto t0 = std::chrono::steady_clock::now();
+            gen[(int64_t)(k + 50) * 37 % n_nodes] = g++;
+            if (fgs_sync_nodes(e, pn, &snap, 0, n_nodes, &nrep) || nrep != 1) {
+                std::fprintf(stderr, "sync: %s (%lld rows)\n", fgs_last_error(e), (long long)nrep);
+                return 1;
+            }
+            const auto t1 = std::chrono::steady_clock::now();
+            if (fgs_evaluate(e, one[(k + 50) & 63], nullptr, &r)) {
+                std::fprintf(stderr, "%s\n", fgs_last_error(e));
+                return 1;
+            }
+            const auto t2 = std::chrono::steady_clock::now();
+            if (k >= 0) {
+                sync_us += std::chrono::duration<double, std::micro>(t1 - t0).count();
+                eval_us += std::chrono::duration<double, std::micro>(t2 - t1).count();
+                fgs_timings tm;
+                fgs_get_timings(e, &tm);
+                direct += tm.small && !tm.reduce_lookup;
+            }
+        }
+        std::printf(", \"cycle_sync_one_row_us\": %.1f, \"cycle_evaluate_1_pod_us\": %.1f, \"cycle_total_us\": %.1f, \"cycles_without_tables\": %d, \"cycles\": %d",
+                    sync_us / reps, eval_us / reps, (sync_us + eval_us) / reps, direct, reps);
+    }
     std::printf("}\n");
     fgs_destroy(e);
     return 0;
