@@ -343,6 +343,8 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
         }
         const char* sm_ = getenv("FGS_SMALL");
         e->small_off = sm_ && sm_[0] == '0';
+        const char* sc_ = getenv("FGS_SMALL_CLUSTER"); // 0: one CTA per pod whatever the node count
+        e->small_cluster = !(sc_ && sc_[0] == '0');
         const char* po_ = getenv("FGS_PATCH"); // 0: fgs_update_nodes always re-derives and re-analyses the whole table
         e->patch_off = po_ && po_[0] == '0';
         const char* sd_ = getenv("FGS_SMALL_DIRECT"); // 0: never compare in the small kernel, 1: always, unset: when the level tables are stale
@@ -965,8 +967,15 @@ extern "C" int fgs_sync_nodes(fgs_engine* eh, fgs_packer* pk, const fgs_snapshot
     std::vector<int64_t> stale;
     bool full = !e->have_nodes || e->n_nodes != N || (int64_t)e->synced_gen.size() != N;
     if (!full) {
-        for (int64_t i = 0; i < N; ++i)
-            if (snap->generation[n0 + i] != e->synced_gen[(size_t)i]) stale.push_back(n0 + i);
+        // block-wise: a loop that may push_back does not vectorise, memcmp over 256 generations does, and almost every block is clean
+        const int64_t* gnow = snap->generation + n0;
+        const int64_t* gold = e->synced_gen.data();
+        for (int64_t b0 = 0; b0 < N; b0 += 256) {
+            const int64_t b1 = std::min<int64_t>(N, b0 + 256);
+            if (std::memcmp(gnow + b0, gold + b0, sizeof(int64_t) * (size_t)(b1 - b0)) == 0) continue;
+            for (int64_t i = b0; i < b1; ++i)
+                if (gnow[i] != gold[i]) stale.push_back(n0 + i);
+        }
         if ((int64_t)stale.size() * 2 > N) full = true;
     }
     const fgs_node_table* t = nullptr;
@@ -1456,10 +1465,13 @@ int Engine::evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fg
     const int64_t P = t->n_pods;
     const bool tables_current = ft && ft->valid && ft->node_gen == node_gen && ft->filter_mask == cfg.filter_mask && ft->n_pad == n_pad &&
                                 ft->v.n_dims == 5 + S && ft_rows_fit(ft->v.W);
-    // … unless the same node table keeps being asked: from the ninth call on the tables are worth their build
+    // … unless the same node table keeps being asked: from the ninth call on the tables are worth their build.
+    // A handful of pods against a long node list go to a cluster of CTAs per pod, which always compares. (More pods than
+    // that gain nothing: a GPC places about two clusters of eight at a time, 16 pods took as long as with one CTA each.)
+    const bool cluster = small_cluster && small_direct != 0 && filter_mode != 2 && P <= kSmallInlinePods && n_pad >= 2048;
     if (small_gen != node_gen) small_gen = node_gen, small_same = 0;
     else small_same++;
-    bool direct = small_direct == 1 || (small_direct != 0 && filter_mode != 2 && !tables_current && P * n_nodes <= ((int64_t)1 << 19) && small_same < 8);
+    bool direct = cluster || small_direct == 1 || (small_direct != 0 && filter_mode != 2 && !tables_current && P * n_nodes <= ((int64_t)1 << 19) && small_same < 8);
     if (!direct) {
         rc = resolve_patch(); // the look-up form reads the special list
         if (rc) return rc;
@@ -1515,6 +1527,10 @@ int Engine::evaluate_small(const fgs_pod_table* t, const fgs_eval_opts* opts, fg
     std::memset(&sp, 0, sizeof(sp));
     if (!direct) sp.v = ft->v;
     sp.direct = direct ? 1 : 0;
+    sp.cluster = cluster ? kSmallCluster : 1;
+    sp.n_inline = P <= kSmallInlinePods ? (int)P : 0;
+    for (int64_t i = 0; i < sp.n_inline; ++i)
+        for (int c = 0; c < ncols; ++c) sp.pods_inline[i][c] = hp[(int64_t)c * kSmallMaxPods + i];
     sp.h_pods = hp;
     sp.h_compact = hc;
     sp.d_pods = (int64_t*)d_pods;

@@ -80,6 +80,7 @@ struct Engine {
     uint64_t small_seq = 0;
     bool small_off = false;
     int small_direct = -1;
+    bool small_cluster = true;
     uint64_t small_gen = ~0ull; // node_gen of the last small-batch call, and how many calls in a row it has served
     int small_same = 0;
     // row patches (patch_nodes): the flag a row outside the host's node analysis raises, the staging pair for many rows

@@ -13,6 +13,7 @@
 // their ranks. Reads of the tables are this GPU's own memory only.
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -21,6 +22,8 @@
 #include "filter_tables.cuh"
 #include "kernels.cuh"
 #include "kernels_narrow.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace fgs {
 
@@ -469,6 +472,7 @@ __device__ __forceinline__ int warp_lower_bound(const i64* __restrict__ lev, int
     return lo + __popc(below);
 }
 
+template <int CL>
 __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_constant__ SmallParams prm) {
     extern __shared__ __align__(16) uint32_t s_row[]; // the pod's bitmap row, then reduction scratch
     __shared__ i64 s_pod[PD_FIXED_COLS + FGS_MAX_SCALARS];
@@ -477,24 +481,36 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     __shared__ int s_flags[2];    // score-time panic, filter-time panic
     __shared__ uint32_t s_cnt[kSmallThreads / 32];
     __shared__ u64 s_key[kSmallThreads / 32];
+    __shared__ i64 s_x[8];        // CL > 1: what this CTA's slice contributes, read by the other CTAs of the cluster
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const i64 p = blockIdx.x;
+    const i64 p = blockIdx.x / CL;
+    const int rank = CL > 1 ? (int)cg::this_cluster().block_rank() : 0;
     const i64 W = prm.W, pp = prm.p_pad;
     const int S = prm.S, ncols = pd_cols(S), n_dims = 5 + S;
+    // this CTA's slice of the node list, in whole 1024-node units
+    i64 n_lo = 0, n_hi = prm.n_pad;
+    if (CL > 1) {
+        const i64 units = prm.n_pad >> 10, per = (units + CL - 1) / CL;
+        n_lo = (i64)rank * per << 10;
+        n_hi = n_lo + (per << 10);
+        if (n_lo > prm.n_pad) n_lo = prm.n_pad;
+        if (n_hi > prm.n_pad) n_hi = prm.n_pad;
+    }
+    (void)n_dims;
 
     if (prm.spec_flag && *(const volatile int*)prm.spec_flag) { // a patched row left the node analysis: the host redoes it and calls again
-        if (tid == 0 && atomicAdd(prm.d_done, 1u) == (unsigned)(prm.n_pods - 1)) {
+        if (tid == 0 && rank == 0 && atomicAdd(prm.d_done, 1u) == (unsigned)(prm.n_pods - 1)) {
             *prm.d_done = 0;
             __threadfence_system();
             *prm.h_flag = prm.seq | kSmallDeclined;
         }
-        return;
+        return; // every CTA of a cluster reads the same word: none is left waiting at a cluster barrier
     }
     // ---- the pod's columns: mapped host memory → shared memory and the device table ----------------------------------------
     if (tid < ncols) {
-        const i64 v = prm.h_pods[(i64)tid * kSmallMaxPods + p];
+        const i64 v = prm.n_inline ? prm.pods_inline[p][tid] : prm.h_pods[(i64)tid * kSmallMaxPods + p];
         s_pod[tid] = v;
-        prm.d_pods[(i64)tid * pp + p] = v;
+        if (rank == 0) prm.d_pods[(i64)tid * pp + p] = v;
     }
     __syncthreads();
     const u64 meta = (u64)s_pod[PD_META];
@@ -503,7 +519,7 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     const uint32_t smask = (uint32_t)(meta >> 32) & ~prm.fit_ignored;
     // int32 pod values, as narrow_pods derives them
     const int nzc = (int)(s_pod[PD_NZ_CPU] >> prm.sh[DIM_CPU]), nzm = (int)(s_pod[PD_NZ_MEM] >> prm.sh[DIM_MEM]);
-    if (tid == 0) {
+    if (tid == 0 && rank == 0) {
         auto Wn = [&](int c, int v) { prm.d_pn[(i64)c * pp + p] = v; };
         Wn(PN_LIM_G, kind == 1 ? (int)s_pod[PD_GPU_LIM] : (kind == 3 ? kNeverI : kPassI));
         Wn(PN_LIM_M, kind == 2 ? (int)(s_pod[PD_MEM_LIM] >> prm.sh[DIM_FM]) : (kind == 3 ? kNeverI : kPassI));
@@ -518,60 +534,70 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     }
     const bool sc_flex = prm.score_mask & FGS_PL_FLEXGPU, sc_fit = prm.score_mask & FGS_PL_FIT, sc_alloc = prm.score_mask & FGS_PL_ALLOCATABLE;
     uint32_t count = 0;
-    if (prm.direct) {
+    if (CL > 1 || prm.direct) {
         // ---- no level tables (the node table changed since they were built, and a handful of pods does not pay for a rebuild):
-        // Filter by comparing, as eval_kernel<REDUCE> does; warp w owns the bitmap words w, w + 32, …
+        // Filter by comparing, on the int32 node table as reduce_narrow does (flex_gpu.go:54-116, fit.go:256-329). A thread
+        // takes four neighbouring nodes per step with 16-byte loads, eight lanes make one bitmap word.
         __shared__ i64 s_w[4][kSmallThreads / 32];
         __shared__ int s_wf[2][kSmallThreads / 32];
         const bool flex_f = prm.filter_mask & FGS_PL_FLEXGPU, fit_f = prm.filter_mask & FGS_PL_FIT;
-        const i64 lim = kind == 1 ? s_pod[PD_GPU_LIM] : s_pod[PD_MEM_LIM];
+        const int lim_g = kind == 1 ? (int)s_pod[PD_GPU_LIM] : (kind == 3 ? kNeverI : kPassI);
+        const int lim_m = kind == 2 ? (int)(s_pod[PD_MEM_LIM] >> prm.sh[DIM_FM]) : (kind == 3 ? kNeverI : kPassI);
+        const int rc = none ? kPassI : (int)(s_pod[PD_REQ_CPU] >> prm.sh[DIM_CPU]);
+        const int rm = none ? kPassI : (int)(s_pod[PD_REQ_MEM] >> prm.sh[DIM_MEM]);
+        const int re = none ? kPassI : (int)(s_pod[PD_REQ_EPH] >> prm.sh[DIM_EPH]);
+        const int rs0 = (none || !(smask & 1u)) ? kPassI : (int)(s_pod[PD_FIXED_COLS + 0] >> prm.sh[DIM_S0]);
+        const int rs1 = (none || !(smask & 2u)) ? kPassI : (int)(s_pod[PD_FIXED_COLS + 1] >> prm.sh[DIM_S1]);
+        const bool has_limit = kind == 1 || kind == 2;
         i64 vflex = kMin, vhi = kMin, vnlo = kMin, neg = 0;
         int spanic = 0, fpanic = 0;
         uint32_t cnt = 0;
-        for (i64 n0 = (i64)warp * 32; n0 < prm.n_pad; n0 += kSmallThreads) {
-            const i64 n = n0 + lane;
-            bool feas = false;
-            if (n < prm.n_nodes) {
-                auto C = [&](int c) { return __ldg(prm.nd + (i64)c * prm.n_pad + n); };
-                const uint32_t fl = (uint32_t)C(ND_FLAGS);
+        for (i64 n0 = n_lo + (i64)tid * 4; n0 < n_hi; n0 += (i64)kSmallThreads * 4) { // warp-uniform trip count: whole 1024-node units
+            auto C4 = [&](int c) { return __ldg((const int4*)(prm.nn + (i64)c * prm.n_pad + n0)); };
+            const int4 fl4 = C4(NN_FLAGS), tg4 = C4(NN_THR_GPU), tm4 = C4(NN_THR_MEM), fc4 = C4(NN_FREE_CPU), fm4 = C4(NN_FREE_MEM);
+            const int4 fe4 = C4(NN_FREE_EPH), f04 = C4(NN_FS0), f14 = C4(NN_FS1), gs4 = C4(NN_GSCORE), ms4 = C4(NN_MSCORE);
+            auto at = [](const int4& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w)); };
+            uint32_t bits = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const uint32_t fl = (uint32_t)at(fl4, k);
                 const bool valid = fl & FGS_NF_VALID;
-                bool flex_ok = true;
-                if (flex_f) { // flex_gpu.go:41-119: no limit passes, both limits never, else limit <= per-kind threshold
-                    if (kind == 3) flex_ok = false;
-                    else if (kind == 1) flex_ok = lim <= C(ND_THR_GPU);
-                    else if (kind == 2) flex_ok = lim <= C(ND_THR_MEM);
-                }
-                bool fit_ok = true;
-                if (fit_f) { // fit.go:256-329
-                    fit_ok = fl & NDF_PODS_OK;
-                    if (fit_ok && !none) {
-                        fit_ok = s_pod[PD_REQ_CPU] <= C(ND_FREE_CPU) && s_pod[PD_REQ_MEM] <= C(ND_FREE_MEM) && s_pod[PD_REQ_EPH] <= C(ND_FREE_EPH);
-                        for (int sidx = 0; sidx < S && fit_ok; ++sidx)
-                            if (((smask >> sidx) & 1u) && s_pod[PD_FIXED_COLS + sidx] > C(nd_free_scalar(sidx))) fit_ok = false;
-                    }
-                }
+                const bool flex_ok = !flex_f || (lim_g <= at(tg4, k) && lim_m <= at(tm4, k));
+                const bool fit_ok = !fit_f || ((fl & NDF_PODS_OK) && rc <= at(fc4, k) && rm <= at(fm4, k) && re <= at(fe4, k) && rs0 <= at(f04, k) &&
+                                               rs1 <= at(f14, k));
                 // NewGPUNode would panic inside FlexGPU.Filter (flex_gpu.go:101) when the filter gets that far on such a node
-                const bool reach = flex_f && (kind == 1 || kind == 2) && flex_ok && (fl & FGS_NF_REF_PANIC) && (prm.flex_first || fit_ok) && valid;
-                if (reach) fpanic = 1;
-                feas = flex_ok && fit_ok && valid && !reach;
+                const bool on_panic = flex_f && has_limit && (fl & FGS_NF_REF_PANIC);
+                if (on_panic && valid && flex_ok && (prm.flex_first || fit_ok)) fpanic = 1;
+                const bool feas = valid && flex_ok && fit_ok && !on_panic;
                 if (feas) {
-                    const i64 ms = C(ND_MEM_SCORE);
-                    const i64 sc = (kind & 1u) ? C(ND_GPU_SCORE) : (kind == 2 ? ms : 0);
+                    bits |= 1u << k;
+                    const int ms = at(ms4, k);
+                    const i64 sc = (kind & 1u) ? (i64)at(gs4, k) : (kind == 2 ? ((i64)ms << prm.sh[DIM_FM]) : 0); // exact: see narrow_nodes
                     vflex = sc > vflex ? sc : vflex;
-                    const i64 ar = C(ND_ALLOC_RAW);
-                    vhi = ar > vhi ? ar : vhi;
-                    vnlo = -ar > vnlo ? -ar : vnlo;
-                    if (kind == 2 && ms < 0 && -ms > neg) neg = -ms;
+                    if (sc_alloc) {
+                        const i64 ar = __ldg(prm.nd + (i64)ND_ALLOC_RAW * prm.n_pad + n0 + k);
+                        vhi = ar > vhi ? ar : vhi;
+                        vnlo = -ar > vnlo ? -ar : vnlo;
+                    }
+                    if (kind == 2 && ms < 0) {
+                        const i64 mag = (i64)(-(i64)ms) << prm.sh[DIM_FM];
+                        neg = mag > neg ? mag : neg;
+                    }
                     if (fl & FGS_NF_REF_PANIC) spanic = 1;
                 }
             }
-            const uint32_t word = __ballot_sync(0xffffffffu, feas);
-            if (lane == 0) {
+            uint32_t word = bits << (4 * (lane & 7));
+            word |= __shfl_xor_sync(0xffffffffu, word, 1);
+            word |= __shfl_xor_sync(0xffffffffu, word, 2);
+            word |= __shfl_xor_sync(0xffffffffu, word, 4);
+            if ((lane & 7) == 0) {
                 s_row[n0 >> 5] = word;
                 prm.bitmap[p * W + (n0 >> 5)] = word;
                 cnt += (uint32_t)__popc(word);
             }
         }
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, 8);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, 16);
         vflex = warp_max_i64(vflex), vhi = warp_max_i64(vhi), vnlo = warp_max_i64(vnlo), neg = warp_max_i64(neg);
         spanic = __any_sync(0xffffffffu, spanic);
         fpanic = __any_sync(0xffffffffu, fpanic);
@@ -592,6 +618,28 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
             }
         }
         __syncthreads();
+        if (CL > 1) { // the other slices' share, through distributed shared memory
+            cg::cluster_group cluster = cg::this_cluster();
+            if (tid == 0) {
+                s_x[0] = (i64)count, s_x[1] = s_red[0], s_x[2] = s_red[1], s_x[3] = s_red[2], s_x[4] = s_red[3];
+                s_x[5] = s_flags[0], s_x[6] = s_flags[1];
+            }
+            cluster.sync();
+            if (tid == 0) {
+                i64 c = 0, r0 = kMin, r1 = kMin, r2 = kMin, r3 = 0, f0 = 0, f1 = 0;
+                for (int r = 0; r < CL; ++r) {
+                    const i64* x = cluster.map_shared_rank(s_x, r);
+                    c += x[0];
+                    r0 = x[1] > r0 ? x[1] : r0, r1 = x[2] > r1 ? x[2] : r1, r2 = x[3] > r2 ? x[3] : r2, r3 = x[4] > r3 ? x[4] : r3;
+                    f0 |= x[5], f1 |= x[6];
+                }
+                s_red[0] = r0, s_red[1] = r1, s_red[2] = r2, s_red[3] = r3;
+                s_flags[0] = (int)f0, s_flags[1] = (int)f1;
+                s_cnt[0] = (uint32_t)c;
+            }
+            __syncthreads();
+            count = s_cnt[0];
+        }
     } else {
     // ---- the row of every dimension (ft_pod_rows): warp d searches dimension d's levels ------------------------------------
     if (warp < n_dims) {
@@ -733,8 +781,10 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     const uint32_t nz200c = 200u * (uint32_t)nzc, nz200m = 200u * (uint32_t)nzm;
     u64 best = 0;
     i64* srow = prm.scores + p * prm.score_stride;
-#pragma unroll 4 // the column loads of several nodes in flight together: the loop is a chain of L2 round trips otherwise
-    for (i64 n = tid; n < prm.n_nodes; n += kSmallThreads) {
+    // (unrolled: the column loads of several nodes in flight together — the loop is a chain of L2 round trips otherwise)
+    const i64 n_end = n_hi < prm.n_nodes ? n_hi : prm.n_nodes;
+#pragma unroll 4
+    for (i64 n = n_lo + tid; n < n_end; n += kSmallThreads) {
         auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
         int t = 0;
         if (sc_flex) {
@@ -797,10 +847,26 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     if (lane == 0) s_key[warp] = best;
     __syncthreads();
     // ---- the per-pod rows and the result record (finalize_pods) ---------------------------------------------------------------
-    if (tid == 0) {
-        u64 key = 0;
+    if (CL > 1) { // the cluster's best key: rank 0 reads every slice's
+        if (tid == 0) {
+            u64 key = 0;
 #pragma unroll
-        for (int w = 0; w < kSmallThreads / 32; ++w) key = s_key[w] > key ? s_key[w] : key;
+            for (int w = 0; w < kSmallThreads / 32; ++w) key = s_key[w] > key ? s_key[w] : key;
+            s_x[7] = (i64)key;
+        }
+        cg::this_cluster().sync();
+    }
+    if (tid == 0 && rank == 0) {
+        u64 key = 0;
+        if (CL > 1) {
+            for (int r = 0; r < CL; ++r) {
+                const u64 k = (u64)*cg::this_cluster().map_shared_rank(&s_x[7], r);
+                key = k > key ? k : key;
+            }
+        } else {
+#pragma unroll
+            for (int w = 0; w < kSmallThreads / 32; ++w) key = s_key[w] > key ? s_key[w] : key;
+        }
         i64* rm = prm.perpod;
         rm[(i64)RR_FLEX_MAX * pp + p] = raw_fmax;
         rm[(i64)RR_ALLOC_HI * pp + p] = s_red[1];
@@ -836,6 +902,7 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
             *prm.h_flag = prm.seq;
         }
     }
+    if (CL > 1) cg::this_cluster().sync(); // no CTA leaves while rank 0 may still read its shared memory
 }
 
 // Which pods would make the reference panic inside FlexGPU.Filter (see filter_panic_pass in kernels_narrow.cu): a pod
@@ -1056,8 +1123,22 @@ cudaError_t ft_launch_masked(const FtMaskParams& p, cudaStream_t st) {
 cudaError_t ft_launch_small(const SmallParams& p, cudaStream_t st) {
     if (p.n_pods <= 0) return cudaSuccess;
     const size_t smem = (size_t)p.W * 4;
-    if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(small_cycle, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_cycle<<<(unsigned)p.n_pods, kSmallThreads, smem, st>>>(p);
+    if (p.cluster > 1) {
+        if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(small_cycle<kSmallCluster>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)p.n_pods * kSmallCluster);
+        cfg.blockDim = dim3(kSmallThreads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = kSmallCluster, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        return cudaLaunchKernelEx(&cfg, small_cycle<kSmallCluster>, p);
+    }
+    if (smem > 48 * 1024) FT_TRY(cudaFuncSetAttribute(small_cycle<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    small_cycle<1><<<(unsigned)p.n_pods, kSmallThreads, smem, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -15,6 +15,7 @@
 #include <cstdint>
 
 #include "../../include/fgs.h"
+#include "kernels.cuh"
 
 namespace fgs {
 
@@ -124,6 +125,8 @@ cudaError_t ft_launch_masked(const FtMaskParams& p, cudaStream_t stream);
 // multipliers, same selectHost key) and the 16-byte result record goes straight back to mapped host memory.
 constexpr int kSmallMaxPods = 256;
 constexpr uint64_t kSmallDeclined = 1ull << 63;
+constexpr int kSmallCluster = 8;    // portable cluster size
+constexpr int kSmallInlinePods = 8; // pods that travel as kernel arguments
 struct SmallParams {
     FtView v;
     const int64_t* h_pods;   // mapped host block int64 [pd_cols(S)][kSmallMaxPods]
@@ -153,6 +156,12 @@ struct SmallParams {
     const int* spec_flag; // row patches not yet confirmed by the host (patch_nodes): non-zero → the node analysis this launch was
                           // parameterised by no longer holds; every CTA leaves and the completion word carries kSmallDeclined
     int direct; // 1: no level tables (stale or over their limit): Filter by comparing every node's thresholds, maxima by reduction
+    // A handful of pods against a long node list: a thread-block CLUSTER per pod instead of one CTA — each CTA takes a slice of
+    // the nodes (always the compare form), the maxima, the count and the selectHost keys are merged through distributed
+    // shared memory. The pods then travel as kernel arguments (no read of host memory on the way in).
+    int cluster;  // CTAs per pod: 1, or kSmallCluster
+    int n_inline; // > 0: pods_inline holds the pod columns, h_pods is not read
+    int64_t pods_inline[kSmallInlinePods][PD_FIXED_COLS + FGS_MAX_SCALARS];
 };
 cudaError_t ft_launch_small(const SmallParams& p, cudaStream_t stream);
 

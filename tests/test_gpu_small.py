@@ -22,6 +22,8 @@ CASES = [
     ("all-three", dict(cfg=2, n_nodes=1100),
      dict(score_plugins=(("FlexGPU", 2), ("NodeResourcesFit", 1), ("NodeResourcesAllocatable", 5)), alloc_mode="Most")),
     ("fit-only", dict(cfg=2, n_nodes=600), dict(filter_plugins=("NodeResourcesFit",), score_plugins=(("NodeResourcesFit", 1),))),
+    # a long node list: up to eight pods take a cluster of CTAs each (two 1024-node units per CTA here, merged through DSMEM)
+    ("c1-long-node-list", dict(cfg=1, n_nodes=15400, pm_quirk_nodes=40, pm_panic_nodes=20), None),
 ]
 
 
@@ -140,11 +142,12 @@ def test_cycles_between_node_changes_need_no_table_rebuild(gpu_ok, oracle):
 
     check(0, 1, False)        # nothing built yet: one pod does not pay for the tables
     check(0, 256, True)       # 256 pods do (256 x 2500 is still one launch)
-    check(5, 6, True)         # ... and now they are current
+    check(5, 25, True)        # ... and now they are current
+    check(5, 6, False)        # (up to eight pods on 2048+ nodes: a cluster of CTAs per pod, which never needs them)
     g = N + 1
     rng = np.random.default_rng(4242)
     for cycle in range(12):   # the pod of the last cycle is bound to the node chosen for it before the next one runs
-        got = check(cycle, cycle + 1 + cycle % 3, cycle == 0)
+        got = check(cycle, cycle + 1 + (cycle % 3) * 7, False)
         i = int(got.selected_node[0]) if got.feasible_count[0] > 0 else int(rng.integers(N))
         req[i, 0] += 500
         req[i, 1] += 256 << 20
