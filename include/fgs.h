@@ -156,7 +156,10 @@ int fgs_packer_pin(fgs_packer* p);
  * per-cycle input (sched/internal/cache/cache.go:197-276). */
 int fgs_upload_nodes(fgs_engine* e, const fgs_node_table* t);
 
-/* Same for a subset of rows: `rows` has n_dirty rows, row r replaces node dirty_idx[r]. */
+/* Same for a subset of rows: `rows` has n_dirty rows, row r replaces node dirty_idx[r]. Up to 4 096 rows are stored,
+ * re-derived and checked by one kernel and the call returns without waiting for it (the next evaluation is ordered behind it
+ * on the engine's stream). A batch staged before the call no longer matches the node table: fgs_pass_reduce / fgs_pass_emit /
+ * fgs_score_masked / fgs_resubmit on it return FGS_E_STATE until it is staged again. */
 int fgs_update_nodes(fgs_engine* e, const fgs_node_table* rows, const int64_t* dirty_idx);
 
 /* The incremental form of the two calls above, keyed by NodeInfo.Generation as the scheduler cache's own snapshot update
