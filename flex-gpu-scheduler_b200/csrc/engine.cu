@@ -166,6 +166,9 @@ void Engine::free_all() {
         if (d_bitmap_alt) cudaFree(d_bitmap_alt);
         if (ev_h2d) cudaEventDestroy(ev_h2d);
         if (ev_kernels) cudaEventDestroy(ev_kernels);
+        if (front_stream) cudaStreamDestroy(front_stream);
+        for (cudaEvent_t ev : {ev_front, ev_back, ev_plane[0], ev_plane[1]})
+            if (ev) cudaEventDestroy(ev);
         if (copy_stream) cudaStreamDestroy(copy_stream);
         if (d2h_stream) cudaStreamDestroy(d2h_stream);
     }
@@ -343,6 +346,8 @@ extern "C" int fgs_create(const fgs_config* c, fgs_engine** out) {
         }
         const char* sm_ = getenv("FGS_SMALL");
         e->small_off = sm_ && sm_[0] == '0';
+        const char* ov_ = getenv("FGS_OVERLAP"); // 0: pass A and the emit pass of consecutive submitted batches share one stream
+        e->overlap_filter = !(ov_ && ov_[0] == '0');
         const char* sc_ = getenv("FGS_SMALL_CLUSTER"); // 0: one CTA per pod whatever the node count
         e->small_cluster = !(sc_ && sc_[0] == '0');
         const char* po_ = getenv("FGS_PATCH"); // 0: fgs_update_nodes always re-derives and re-analyses the whole table
@@ -513,6 +518,10 @@ int Engine::decide_narrow_once(const fgs_pod_table* t, bool launch_pods) {
     }
     const int sig = cfg.fit_strategy;
     if (narrow_nodes_sig != sig || std::memcmp(&sh, &narrow_sh, sizeof(sh)) != 0) {
+        if (window_back) { // the int32 node table is rewritten on the front stream: the emit pass in flight on the compute stream reads it
+            FGS_CUDA(this, cudaEventRecord(ev_back, window_back));
+            FGS_CUDA(this, cudaStreamWaitEvent(stream, ev_back, 0));
+        }
         launch_narrow_nodes((const int64_t*)d_nd, n_pad, sh, cfg.fit_strategy, (int*)d_nn, stream);
         launches++;
         narrow_nodes_sig = sig;
@@ -808,8 +817,31 @@ static void node_row_values(const Engine* e, const fgs_node_table* t, int64_t sr
 // fgs_update_nodes, asynchronous form: see patch_nodes (kernels_narrow.cu)
 int Engine::patch_rows(const fgs_node_table* rows, const int64_t* dirty_idx) {
     Engine* e = this;
-    const int64_t R = rows->n_nodes;
+    const int64_t R_in = rows->n_nodes;
     const int ncols = nr_cols(S, D);
+    // a node listed twice: the later row wins, as with the copies of the synchronous form (a thread per row would race)
+    std::vector<int64_t> keep; // table rows to apply, when some were dropped
+    {
+        bool dup = false;
+        if (R_in <= 8) {
+            for (int64_t a = 0; a < R_in && !dup; ++a)
+                for (int64_t b = a + 1; b < R_in; ++b)
+                    if (dirty_idx[a] == dirty_idx[b]) dup = true;
+        } else {
+            std::vector<int64_t> srt(dirty_idx, dirty_idx + R_in);
+            std::sort(srt.begin(), srt.end());
+            dup = std::adjacent_find(srt.begin(), srt.end()) != srt.end();
+        }
+        if (dup) {
+            std::vector<int64_t> order((size_t)R_in);
+            for (int64_t r = 0; r < R_in; ++r) order[(size_t)r] = r;
+            std::stable_sort(order.begin(), order.end(), [&](int64_t a, int64_t b) { return dirty_idx[a] < dirty_idx[b]; });
+            for (int64_t k = 0; k < R_in; ++k)
+                if (k + 1 == R_in || dirty_idx[order[(size_t)k]] != dirty_idx[order[(size_t)k + 1]]) keep.push_back(order[(size_t)k]);
+        }
+    }
+    const int64_t R = keep.empty() ? R_in : (int64_t)keep.size();
+    auto src_row = [&](int64_t r) { return keep.empty() ? r : keep[(size_t)r]; };
     if (!d_patch_flag) {
         FGS_CUDA(e, cudaMalloc(&d_patch_flag, sizeof(int)));
         FGS_CUDA(e, cudaMemset(d_patch_flag, 0, sizeof(int)));
@@ -830,8 +862,8 @@ int Engine::patch_rows(const fgs_node_table* rows, const int64_t* dirty_idx) {
     pp.h_flag = h_patch_flag;
     if (R <= kPatchInline) {
         for (int64_t r = 0; r < R; ++r) {
-            pp.inline_idx[r] = dirty_idx[r];
-            node_row_values(this, rows, r, (int64_t*)pp.inline_rows[r]);
+            pp.inline_idx[r] = dirty_idx[src_row(r)];
+            node_row_values(this, rows, src_row(r), (int64_t*)pp.inline_rows[r]);
         }
     } else {
         const size_t need = sizeof(int64_t) * (size_t)R * (size_t)(ncols + 1);
@@ -849,8 +881,8 @@ int Engine::patch_rows(const fgs_node_table* rows, const int64_t* dirty_idx) {
         }
         int64_t* h = (int64_t*)h_patch;
         for (int64_t r = 0; r < R; ++r) {
-            node_row_values(this, rows, r, h + r * ncols);
-            h[R * ncols + r] = dirty_idx[r];
+            node_row_values(this, rows, src_row(r), h + r * ncols);
+            h[R * ncols + r] = dirty_idx[src_row(r)];
         }
         FGS_CUDA(e, cudaMemcpyAsync(d_patch, h_patch, need, cudaMemcpyHostToDevice, stream));
         pp.rows = (const long long*)d_patch;
@@ -1985,6 +2017,35 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
     return e->submit_single(pods, opts, false);
 }
 
+namespace {
+// `stream` names the front stream while a submitted batch is staged and filtered (every launch in between follows it)
+struct FrontWindow {
+    Engine* e;
+    cudaStream_t back;
+    bool open;
+    FrontWindow(Engine* e_, bool on) : e(e_), back(e_->stream), open(on) {
+        if (open) {
+            e->window_back = back;
+            e->stream = e->front_stream;
+        }
+    }
+    void close() {
+        if (open) {
+            e->stream = back;
+            e->window_back = nullptr;
+            open = false;
+        }
+    }
+    ~FrontWindow() { close(); }
+};
+} // namespace
+
+// Single engine, per batch k:
+//     front stream (high priority)   stage kernels(k), pass A(k)              stage kernels(k+1), pass A(k+1) …
+//     compute stream                          wait A(k) → emit(k), finalize(k)          wait A(k+1) → emit(k+1) …
+// Pass A is bound by L2 look-ups and instruction issue, the emit pass by HBM writes: side by side the first mostly hides
+// behind the second. Consecutive batches filter into two bitmaps in turn (A(k+2) waits for emit(k) to have read its one);
+// everything else a batch touches belongs to its pipeline slot or is written by one stream only.
 int Engine::submit_single(const fgs_pod_table* pods, const fgs_eval_opts* opts, bool resident) {
     Engine* e = this;
     fgs_engine* eh = (fgs_engine*)this;
@@ -1994,6 +2055,22 @@ int Engine::submit_single(const fgs_pod_table* pods, const fgs_eval_opts* opts, 
     if (e->in_flight == 0) e->oldest_slot = k;
     e->next_slot = (k + 1) % e->ring();
     int rc;
+    const bool overlap = e->overlap_filter && e->no_fused && e->nom_q == 0 && !(opts && (opts->sample || opts->skip_pass_b));
+    if (overlap) {
+        if (!e->front_stream) {
+            int lo = 0, hi = 0;
+            FGS_CUDA(e, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            FGS_CUDA(e, cudaStreamCreateWithPriority(&e->front_stream, cudaStreamNonBlocking, hi));
+            for (cudaEvent_t* ev : {&e->ev_front, &e->ev_back, &e->ev_plane[0], &e->ev_plane[1]}) FGS_CUDA(e, cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+        }
+        rc = e->nodes_ready(); // a pending row patch is settled on the compute stream, before the window
+        if (rc) return rc;
+        if (e->in_flight == 0) { // whatever ran on the compute stream so far (uploads, patches, other calls) comes first
+            FGS_CUDA(e, cudaEventRecord(e->ev_back, e->stream));
+            FGS_CUDA(e, cudaStreamWaitEvent(e->front_stream, e->ev_back, 0));
+        }
+    }
+    FrontWindow win(e, overlap);
     if (resident) {
         if (!e->have_pods) return fail(FGS_E_STATE, "fgs_resubmit: no batch is resident in this pipeline slot (fgs_submit fills the slots in turn)");
         if (e->slots[k].node_gen != e->node_gen) return fail(FGS_E_STATE, "fgs_resubmit: the node table changed since this batch was staged: fgs_submit it again");
@@ -2006,13 +2083,40 @@ int Engine::submit_single(const fgs_pod_table* pods, const fgs_eval_opts* opts, 
     }
     e->emitted = false;
     e->was_fused = false;
-    if (e->fused_eligible(opts)) {
+    int sel = 0;
+    if (overlap) {
+        sel = (int)(e->submit_seq++ & 1);
+        if (sel == 1) { // the second bitmap, as large as the first
+            const size_t need = sizeof(uint32_t) * (size_t)e->p_plane_cap * (size_t)e->words_per_row;
+            if (need > e->bitmap_alt_bytes) {
+                FGS_CUDA(e, cudaDeviceSynchronize());
+                if (e->d_bitmap_alt) cudaFree(e->d_bitmap_alt);
+                e->d_bitmap_alt = nullptr;
+                e->bitmap_alt_bytes = 0;
+                FGS_CUDA(e, cudaMalloc(&e->d_bitmap_alt, need));
+                e->bitmap_alt_bytes = need;
+            }
+        }
+        if (e->plane_used[sel]) FGS_CUDA(e, cudaStreamWaitEvent(e->stream, e->ev_plane[sel], 0)); // the emit pass that read this bitmap last
+    }
+    if (!overlap && e->fused_eligible(opts)) {
         rc = e->run_fused(opts, 3);
         if (rc) return rc;
     } else {
-        rc = fgs_pass_reduce(eh);
+        {
+            BitmapFor bf(e, sel);
+            rc = fgs_pass_reduce(eh);
+        }
         if (rc) return rc;
-        rc = fgs_pass_emit(eh, opts);
+        if (overlap) {
+            FGS_CUDA(e, cudaEventRecord(e->ev_front, e->stream));
+            win.close();
+            FGS_CUDA(e, cudaStreamWaitEvent(e->stream, e->ev_front, 0));
+        }
+        {
+            BitmapFor bf(e, sel);
+            rc = fgs_pass_emit(eh, opts);
+        }
         if (rc) return rc;
     }
     const int64_t P = e->n_pods, pp = e->p_pad;
@@ -2020,6 +2124,10 @@ int Engine::submit_single(const fgs_pod_table* pods, const fgs_eval_opts* opts, 
     launch_finalize_pods((const int64_t*)e->d_perpod, d_compact, P, pp, e->last_key_shift, 1, (e->cfg.score_mask & FGS_PL_FLEXGPU) ? 1 : 0, e->stream);
     e->launches++;
     FGS_CUDA(e, cudaGetLastError());
+    if (overlap) {
+        FGS_CUDA(e, cudaEventRecord(e->ev_plane[sel], e->stream));
+        e->plane_used[sel] = true;
+    }
     // the D2H of the per-pod results runs on its own stream: the next batch's kernels do not wait for it
     FGS_CUDA(e, cudaEventRecord(e->ev_kernels, e->stream));
     FGS_CUDA(e, cudaStreamWaitEvent(e->d2h_stream, e->ev_kernels, 0));

@@ -387,7 +387,11 @@ __host__ __device__ inline SmemE smem_emit(bool fused) {
     return L;
 }
 
-template <uint32_t SPEC, bool FUSED>
+// TAIL: the last node tile of a table that fills at most half of it (a 6 250-node shard of C5 fills 106 of 1 024 columns).
+// A warp owns 128 nodes and walks every pod of the CTA's chunk, so such a CTA would take as long as a full one with one
+// warp in eight working. Here the warps whose nodes lie beyond the table take a share of the pods instead: with A = 1, 2
+// or 4 node groups in range, warp w works on node group w mod A and on every (8/A)-th pod.
+template <uint32_t SPEC, bool FUSED, bool TAIL = false>
 __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant__ NarrowParams prm) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr bool kFlex = SPEC & SP_SC_FLEX, kFit = SPEC & SP_SC_FIT, kAlloc = SPEC & SP_SC_ALLOC, kMost = SPEC & SP_FIT_MOST;
@@ -396,14 +400,19 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     PodR* const s_podf_base = (PodR*)(smem + L.pod + 2 * kTileP * (int)sizeof(PodE)); // fused: the pods' filter records
     uint64_t* bars = (uint64_t*)(smem + L.bars); // [0,1] pod columns, [2,3] bitmap rows
 
+    static_assert(!(FUSED && TAIL), "the fused pass writes bitmap words per warp: no pod split there");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const i64 node_tile0 = (i64)blockIdx.x * kTileNe;
+    const uint32_t tile_idx = (uint32_t)prm.tile_first + blockIdx.x;
+    const i64 node_tile0 = (i64)tile_idx * kTileNe;
     const i64 pod_begin = (i64)blockIdx.y * prm.pods_per_cta;
     i64 pod_end = pod_begin + prm.pods_per_cta;
     if (pod_end > prm.p_pad) pod_end = prm.p_pad;
     const int n_tiles = (int)((pod_end - pod_begin + kTileP - 1) / kTileP);
     if (n_tiles <= 0) return;
     const i64 word0 = node_tile0 / 32;
+    const int ngrp = TAIL ? (warp & (prm.tail_groups - 1)) : warp;      // which 128 nodes of the tile
+    const int pod_step = TAIL ? kWarps / prm.tail_groups : 1;           // this warp takes every pod_step-th pod …
+    const int pod_first = TAIL ? warp / prm.tail_groups : 0;            // … from this one on
 
     auto issue_pods = [&](int it) { // one thread
         const int stage = it & 1;
@@ -511,7 +520,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     uint32_t flags_or = 0;
 #pragma unroll
     for (int j = 0; j < kNPTe; ++j) {
-        nloc[j] = warp * (32 * kNPTe) + j * 32 + lane;
+        nloc[j] = ngrp * (32 * kNPTe) + j * 32 + lane;
         if (FUSED) {
             const i64 n = node_tile0 + nloc[j];
             auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
@@ -574,7 +583,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     // last 1 024 columns) has no score to write and no key to offer: it leaves zeros in its column of the per-warp keys once
     // and sits the pod loops out, so that the tail tile costs an eighth of the issue slots of a full one.
     const bool warp_active = FUSED || __any_sync(0xffffffffu, inr[0] | inr[1] | inr[2] | inr[3]);
-    if (!warp_active)
+    if (!warp_active || TAIL) // (TAIL: the pods this warp skips keep the zero)
         for (int i = lane; i < 2 * kTileP; i += 32) ((uint32_t*)(smem + L.wkey))[i * kWarps + warp] = 0u;
     if (tid < kTileP) derive(0);
     __syncthreads();
@@ -590,16 +599,17 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         const int n_valid = left >= kTileP ? kTileP : (left > 0 ? (int)left : 0);
         const PodE* s_pod = (const PodE*)(smem + L.pod) + stage * kTileP;
         uint32_t* wkey = (uint32_t*)(smem + L.wkey) + stage * kTileP * kWarps;
-        const uint32_t* bmrow = (const uint32_t*)(smem + L.bm) + stage * kTileP * kWordsTe + warp * kNPTe;
+        const uint32_t* bmrow = (const uint32_t*)(smem + L.bm) + stage * kTileP * kWordsTe + ngrp * kNPTe;
         const PodR* s_podf = s_podf_base + stage * kTileP;
         uint32_t* wcnt = (uint32_t*)(smem + L.bm) + stage * kTileP * kWarps; // fused only
         uint32_t* bm_out = prm.bitmap + tile_p0 * prm.words_per_row + word0 + warp * kNPTe; // fused: this warp's four words
         if (!FUSED) mbar_wait(&bars[2 + stage], (uint32_t)((it >> 1) & 1));
 
-        i64* rowp = (i64*)prm.scores + tile_p0 * prm.score_stride + node_tile0 + nloc[0];
+        i64* rowp = (i64*)prm.scores + (tile_p0 + pod_first) * prm.score_stride + node_tile0 + nloc[0];
         // (unrolling this loop costs registers and with them the third CTA per SM: 0.699 vs 0.665 ms)
         const int n_loop = warp_active ? n_valid : 0;
-        for (int jp = 0; jp < n_loop; ++jp, rowp += prm.score_stride, bm_out += prm.words_per_row) {
+        const i64 row_step = TAIL ? prm.score_stride * pod_step : prm.score_stride;
+        for (int jp = pod_first; jp < n_loop; jp += pod_step, rowp += row_step, bm_out += prm.words_per_row) {
             const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz200c nz200m
             const uint4 q3 = *(const uint4*)&s_pod[jp].fmag;   // fmag amag fsh ash
             const int4 q4 = *(const int4*)&s_pod[jp].fmax;     // fmax count arange32 kind
@@ -738,7 +748,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                 const u64 t = (u64)(k >> 18) - 1, h8 = (k >> 10) & 0xffu, nl = k & 0x3ffu;
                 const u64 ng = (u64)(prm.node_base + node_tile0) + nl;
                 // cross-tile ties: mix the tile index into the low hash byte so that no tile is favoured
-                const uint32_t h16 = ((uint32_t)h8 << 8) | (((uint32_t)blockIdx.x * 0x9E3779B1u ^ s_pod[tid].hmul) >> 24);
+                const uint32_t h16 = ((uint32_t)h8 << 8) | ((tile_idx * 0x9E3779B1u ^ s_pod[tid].hmul) >> 24);
                 const u64 key64 = ((t << 40) | ((u64)h16 << 24) | ng) + 1; // layout shared with the int64 kernels
                 atomicMax((i64*)prm.select_key + p, (i64)key64);
             }
@@ -806,12 +816,35 @@ void launch_emit_spec(NarrowParams p, cudaStream_t st) {
     static int ready = 0;
     if (!ready) {
         cudaFuncSetAttribute(emit_narrow<SPEC, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+        if (!FUSED) cudaFuncSetAttribute(emit_narrow<SPEC, false, !FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
         ready = 1;
     }
     static const int waves = env_waves(FUSED ? "FGS_WAVES_FUSED" : "FGS_WAVES_EMIT", FUSED ? 6 : 24);
-    p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC, FUSED>, sm, p, waves, kTileNe);
-    const dim3 grid((unsigned)(p.n_pad / kTileNe), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
-    emit_narrow<SPEC, FUSED><<<grid, kThreads, sm, st>>>(p);
+    static const int tail_on = []() { const char* v = getenv("FGS_EMIT_TAIL"); return !(v && v[0] == '0') ? 1 : 0; }();
+    const i64 node_tiles = p.n_pad / kTileNe;
+    const i64 tail_nodes = p.n_nodes - (node_tiles - 1) * kTileNe; // nodes in the last tile, 1 … 1024
+    const int a = (int)((tail_nodes + 32 * kNPTe - 1) / (32 * kNPTe));
+    const bool split_tail = !FUSED && tail_on && a <= 4;
+    p.tile_first = 0;
+    p.tail_groups = kWarps;
+    if (!split_tail || node_tiles > 1) {
+        NarrowParams q = p;
+        if (split_tail) q.n_pad = p.n_pad - kTileNe; // geometry only: the grid below and the chunking skip the tail tile
+        p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC, FUSED>, sm, q, waves, kTileNe);
+        const dim3 grid((unsigned)(q.n_pad / kTileNe), (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
+        emit_narrow<SPEC, FUSED><<<grid, kThreads, sm, st>>>(p);
+    }
+    if constexpr (!FUSED) {
+        if (split_tail) { // the tail tile: all eight warps on its one, two or four node groups
+            NarrowParams q = p;
+            q.n_pad = kTileNe;
+            p.tile_first = (int)(node_tiles - 1);
+            p.tail_groups = a <= 1 ? 1 : (a <= 2 ? 2 : 4);
+            p.pods_per_cta = pods_per_cta_for(emit_narrow<SPEC, false, true>, sm, q, 4, kTileNe);
+            const dim3 grid(1u, (unsigned)((p.p_pad + p.pods_per_cta - 1) / p.pods_per_cta), 1);
+            emit_narrow<SPEC, false, true><<<grid, kThreads, sm, st>>>(p);
+        }
+    }
 }
 
 // ---- the maxima the fused pass needs up front --------------------------------------------------------------------

@@ -69,6 +69,8 @@ struct NarrowParams {
     int64_t n_pods, p_pad;
     int64_t words_per_row, score_stride;
     int pods_per_cta;
+    int tile_first; // emit pass: the node tile of blockIdx.x == 0 (the tail tile is launched on its own when it is mostly empty)
+    int tail_groups; // emit pass, tail launch: warps per node group A in {1, 2, 4}: the 8 warps split the pods 8/A ways
     int flex_filter_first;
     NarrowShifts sh;
     int w_flex, w_fit, w_alloc;

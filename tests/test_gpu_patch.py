@@ -150,6 +150,24 @@ def test_a_row_outside_the_node_analysis_is_caught_on_the_device(gpu_ok, oracle)
     eng.close()
 
 
+def test_a_node_listed_twice_takes_the_later_row(gpu_ok):
+    a = fgs.config_synth(2, n_nodes=300, n_pending=50)
+    b = fgs.config_synth(2, n_nodes=300, n_pending=50, seed_nodes=0x1234)
+    cfg = fgs.config_plugins(2)
+    t = fgs.Packer(2).pods(a.pending)
+    for k in (3, 12):  # as kernel arguments, and through the compact buffer
+        got, want = _engine(cfg), _engine(cfg, patch=False)
+        for e in (got, want):
+            e.upload_nodes(fgs.Packer(2).nodes(a.snapshot))
+        rows = np.array(list(range(10, 10 + k)) + [10 + k - 1, 10], np.int64)       # table rows: b's nodes ...
+        dirty = np.array(list(range(40, 40 + k)) + [40, 40 + k - 1], np.int64)      # ... onto these; 40 and 40+k-1 twice
+        for e in (got, want):
+            e.update_nodes(fgs.Packer(2).node_rows(b.snapshot, rows), dirty)
+        _same(got.evaluate(t, want_planes=True), want.evaluate(t, want_planes=True), 300)
+        got.close()
+        want.close()
+
+
 def test_a_batch_staged_before_a_node_change_is_refused(gpu_ok):
     """The staged batch's int32 columns follow the node table's shifts: passes over it after fgs_update_nodes are refused"""
     s = fgs.config_synth(2, n_nodes=500, n_pending=100)
