@@ -164,10 +164,11 @@ void Engine::free_all() {
         }
         if (merge_stream) cudaStreamDestroy(merge_stream);
         if (d_bitmap_alt) cudaFree(d_bitmap_alt);
+        if (d_bitmap_alt2) cudaFree(d_bitmap_alt2);
         if (ev_h2d) cudaEventDestroy(ev_h2d);
         if (ev_kernels) cudaEventDestroy(ev_kernels);
         if (front_stream) cudaStreamDestroy(front_stream);
-        for (cudaEvent_t ev : {ev_front, ev_back, ev_plane[0], ev_plane[1]})
+        for (cudaEvent_t ev : {ev_front, ev_back, ev_plane[0], ev_plane[1], ev_plane[2]})
             if (ev) cudaEventDestroy(ev);
         if (copy_stream) cudaStreamDestroy(copy_stream);
         if (d2h_stream) cudaStreamDestroy(d2h_stream);
@@ -1385,7 +1386,7 @@ extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
     }
     if (!done) launch_eval_emit(p, e->stream);
     e->emit_was_narrow = done;
-    e->launches++;
+    e->launches += done ? narrow_last_emit_launches() : 1;
     FGS_CUDA(e, cudaGetLastError());
     FGS_CUDA(e, cudaEventRecord(e->events[3], e->stream));
     e->emitted = true;
@@ -1849,8 +1850,41 @@ struct BitmapFor {
     void* saved;
     BitmapFor(Engine* e_, int sel) : e(e_), saved(e_->d_bitmap) {
         if (sel == 1 && e->d_bitmap_alt) e->d_bitmap = e->d_bitmap_alt;
+        if (sel == 2 && e->d_bitmap_alt2) e->d_bitmap = e->d_bitmap_alt2;
     }
     ~BitmapFor() { e->d_bitmap = saved; }
+};
+} // namespace
+
+int Engine::ensure_front_stream() {
+    if (front_stream) return FGS_OK;
+    int lo = 0, hi = 0;
+    FGS_CUDA(this, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    FGS_CUDA(this, cudaStreamCreateWithPriority(&front_stream, cudaStreamNonBlocking, hi));
+    for (cudaEvent_t* ev : {&ev_front, &ev_back, &ev_plane[0], &ev_plane[1], &ev_plane[2]}) FGS_CUDA(this, cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+    return FGS_OK;
+}
+
+namespace {
+// `stream` names the front stream while a submitted batch is staged and filtered (every launch in between follows it)
+struct FrontWindow {
+    Engine* e;
+    cudaStream_t back;
+    bool open;
+    FrontWindow(Engine* e_, bool on) : e(e_), back(e_->stream), open(on) {
+        if (open) {
+            e->window_back = back;
+            e->stream = e->front_stream;
+        }
+    }
+    void close() {
+        if (open) {
+            e->stream = back;
+            e->window_back = nullptr;
+            open = false;
+        }
+    }
+    ~FrontWindow() { close(); }
 };
 } // namespace
 
@@ -1877,6 +1911,10 @@ int Engine::issue_emit_sharded(int j) {
             if (rc) return rc;
         }
         FGS_CUDA(e, cudaEventRecord(sl.ev_emit, stream));
+        if (ev_plane[sl.bitmap_sel]) {
+            FGS_CUDA(e, cudaEventRecord(ev_plane[sl.bitmap_sel], stream));
+            plane_used[sl.bitmap_sel] = true;
+        }
         FGS_CUDA(e, cudaStreamWaitEvent(merge_stream, sl.ev_emit, 0));
         const int rc = peer_merge(1, merge_stream, true);
         if (rc) return rc;
@@ -1907,6 +1945,20 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
     if (k != cur_slot) bind_slot(k);
     if (in_flight == 0) oldest_slot = k;
     next_slot = (k + 1) % ring();
+    // Pass A of this batch goes to the front stream, beside the emit passes of the two batches before it (one running or
+    // queued, one issued at the end of this call): three bitmaps are live then.
+    const bool overlap = overlap_filter && nom_q == 0;
+    if (overlap) {
+        int rc = ensure_front_stream();
+        if (rc) return rc;
+        rc = nodes_ready();
+        if (rc) return rc;
+        if (in_flight == 0) {
+            FGS_CUDA(e, cudaEventRecord(ev_back, stream));
+            FGS_CUDA(e, cudaStreamWaitEvent(front_stream, ev_back, 0));
+        }
+    }
+    FrontWindow win(this, overlap);
     if (resident) {
         if (!have_pods) return fail(FGS_E_STATE, "fgs_resubmit: no batch is resident in this pipeline slot (fgs_submit fills the slots in turn)");
         if (slots[k].node_gen != node_gen) return fail(FGS_E_STATE, "fgs_resubmit: the node table changed since this batch was staged: fgs_submit it again");
@@ -1915,25 +1967,36 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
         // previous batch has still to read: issue that pass first and let everything in flight drain.
         if (pods && in_flight > 0 && round_up(std::max<int64_t>(pods->n_pods, 1), kTileP) > p_plane_cap) {
             if (newest >= 0 && slots[newest].emit_pending) {
+                win.close();
                 const int rc = issue_emit_sharded(newest);
                 if (rc) return rc;
             }
             FGS_CUDA(e, cudaDeviceSynchronize());
+            if (overlap && win.open == false) {
+                window_back = stream;
+                stream = front_stream;
+                win.open = true;
+            }
         }
         const int rc = stage_pods_impl(e, pods, true);
         if (rc) return rc;
     }
     emitted = false;
     slots[k].node_gen = node_gen;
-    slots[k].bitmap_sel = (int)(submit_seq++ & 1);
-    if (slots[k].bitmap_sel == 1) { // the second bitmap, as large as the first
+    const int n_bitmaps = overlap ? 3 : 2;
+    slots[k].bitmap_sel = (int)(submit_seq++ % (uint64_t)n_bitmaps);
+    for (int which = 1; which <= 2; ++which) { // the second / third bitmap, as large as the first
+        if (slots[k].bitmap_sel != which) continue;
+        void*& buf = which == 1 ? d_bitmap_alt : d_bitmap_alt2;
+        size_t& have = which == 1 ? bitmap_alt_bytes : bitmap_alt2_bytes;
         const size_t need = sizeof(uint32_t) * (size_t)p_plane_cap * (size_t)words_per_row;
-        if (need > bitmap_alt_bytes) {
+        if (need > have) {
             FGS_CUDA(e, cudaDeviceSynchronize());
-            if (d_bitmap_alt) cudaFree(d_bitmap_alt);
-            d_bitmap_alt = nullptr;
-            FGS_CUDA(e, cudaMalloc(&d_bitmap_alt, need));
-            bitmap_alt_bytes = need;
+            if (buf) cudaFree(buf);
+            buf = nullptr;
+            have = 0;
+            FGS_CUDA(e, cudaMalloc(&buf, need));
+            have = need;
         }
     }
     Slot& sl = slots[k];
@@ -1944,12 +2007,14 @@ int Engine::submit_sharded(const fgs_pod_table* pods, const fgs_eval_opts* opts,
         }
         FGS_CUDA(e, cudaEventRecord(sl.ev_t0, stream));
     }
+    if (overlap && plane_used[sl.bitmap_sel]) FGS_CUDA(e, cudaStreamWaitEvent(stream, ev_plane[sl.bitmap_sel], 0)); // the emit pass that read this bitmap last
     {
         BitmapFor bm(this, sl.bitmap_sel);
         const int rc = fgs_pass_reduce((fgs_engine*)this);
         if (rc) return rc;
     }
     FGS_CUDA(e, cudaEventRecord(sl.ev_reduce, stream));
+    win.close();
     FGS_CUDA(e, cudaStreamWaitEvent(merge_stream, sl.ev_reduce, 0));
     {
         const int rc = peer_merge(0, merge_stream, true);
@@ -2017,29 +2082,6 @@ extern "C" int fgs_submit(fgs_engine* eh, const fgs_pod_table* pods, const fgs_e
     return e->submit_single(pods, opts, false);
 }
 
-namespace {
-// `stream` names the front stream while a submitted batch is staged and filtered (every launch in between follows it)
-struct FrontWindow {
-    Engine* e;
-    cudaStream_t back;
-    bool open;
-    FrontWindow(Engine* e_, bool on) : e(e_), back(e_->stream), open(on) {
-        if (open) {
-            e->window_back = back;
-            e->stream = e->front_stream;
-        }
-    }
-    void close() {
-        if (open) {
-            e->stream = back;
-            e->window_back = nullptr;
-            open = false;
-        }
-    }
-    ~FrontWindow() { close(); }
-};
-} // namespace
-
 // Single engine, per batch k:
 //     front stream (high priority)   stage kernels(k), pass A(k)              stage kernels(k+1), pass A(k+1) …
 //     compute stream                          wait A(k) → emit(k), finalize(k)          wait A(k+1) → emit(k+1) …
@@ -2057,12 +2099,8 @@ int Engine::submit_single(const fgs_pod_table* pods, const fgs_eval_opts* opts, 
     int rc;
     const bool overlap = e->overlap_filter && e->no_fused && e->nom_q == 0 && !(opts && (opts->sample || opts->skip_pass_b));
     if (overlap) {
-        if (!e->front_stream) {
-            int lo = 0, hi = 0;
-            FGS_CUDA(e, cudaDeviceGetStreamPriorityRange(&lo, &hi));
-            FGS_CUDA(e, cudaStreamCreateWithPriority(&e->front_stream, cudaStreamNonBlocking, hi));
-            for (cudaEvent_t* ev : {&e->ev_front, &e->ev_back, &e->ev_plane[0], &e->ev_plane[1]}) FGS_CUDA(e, cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
-        }
+        rc = e->ensure_front_stream();
+        if (rc) return rc;
         rc = e->nodes_ready(); // a pending row patch is settled on the compute stream, before the window
         if (rc) return rc;
         if (e->in_flight == 0) { // whatever ran on the compute stream so far (uploads, patches, other calls) comes first

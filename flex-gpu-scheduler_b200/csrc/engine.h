@@ -161,12 +161,15 @@ struct Engine {
     // every other batch uses a second bitmap (the emit pass of batch k-1 reads its rows while the reduce pass of batch k writes)
     cudaStream_t merge_stream = nullptr;
     void* d_bitmap_alt = nullptr;
+    void* d_bitmap_alt2 = nullptr; // sharded pipeline with pass A on the front stream: three batches' bitmaps are live at a time
+    size_t bitmap_alt2_bytes = 0;
     size_t bitmap_alt_bytes = 0;
     // single-engine pipeline: pass A of batch k+1 on a second (higher-priority) stream next to the emit pass of batch k
     bool overlap_filter = true;
     cudaStream_t front_stream = nullptr, window_back = nullptr; // window_back: the compute stream while `stream` is swapped for front_stream
-    cudaEvent_t ev_front = nullptr, ev_back = nullptr, ev_plane[2] = {nullptr, nullptr};
-    bool plane_used[2] = {false, false};
+    cudaEvent_t ev_front = nullptr, ev_back = nullptr, ev_plane[3] = {nullptr, nullptr, nullptr};
+    bool plane_used[3] = {false, false, false};
+    int ensure_front_stream();
     int peer_merge(int which, cudaStream_t on, bool overlapped = false); // peer_merge.cu
     int peer_fetch_error(int slot, cudaStream_t on); // copy of the merge error word, behind the merges on `on`
     int peer_check_error(int slot);                  // FGS_E_STATE when that copy says a merge timed out

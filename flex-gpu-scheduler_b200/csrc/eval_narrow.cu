@@ -402,17 +402,19 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
 
     static_assert(!(FUSED && TAIL), "the fused pass writes bitmap words per warp: no pod split there");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t tile_idx = (uint32_t)prm.tile_first + blockIdx.x;
-    const i64 node_tile0 = (i64)tile_idx * kTileNe;
+    const uint32_t tile_idx = TAIL ? (uint32_t)prm.tile_first + blockIdx.x : blockIdx.x; // (the main launch starts at tile 0)
+    const i64 node_tile0 = TAIL ? (i64)tile_idx * kTileNe : (i64)blockIdx.x * kTileNe;
     const i64 pod_begin = (i64)blockIdx.y * prm.pods_per_cta;
     i64 pod_end = pod_begin + prm.pods_per_cta;
     if (pod_end > prm.p_pad) pod_end = prm.p_pad;
     const int n_tiles = (int)((pod_end - pod_begin + kTileP - 1) / kTileP);
     if (n_tiles <= 0) return;
     const i64 word0 = node_tile0 / 32;
-    const int ngrp = TAIL ? (warp & (prm.tail_groups - 1)) : warp;      // which 128 nodes of the tile
-    const int pod_step = TAIL ? kWarps / prm.tail_groups : 1;           // this warp takes every pod_step-th pod …
-    const int pod_first = TAIL ? warp / prm.tail_groups : 0;            // … from this one on
+    // TAIL only (the other instantiation keeps the expressions it was tuned with: a different but equivalent form cost it
+    // three registers and 1.5 % — 677 vs 667 µs on C2):
+    const int ngrp = TAIL ? (warp & (prm.tail_groups - 1)) : 0;   // which 128 nodes of the tile
+    const int pod_step = TAIL ? kWarps / prm.tail_groups : 1;      // this warp takes every pod_step-th pod …
+    const int pod_first = TAIL ? warp / prm.tail_groups : 0;       // … from this one on
 
     auto issue_pods = [&](int it) { // one thread
         const int stage = it & 1;
@@ -520,7 +522,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     uint32_t flags_or = 0;
 #pragma unroll
     for (int j = 0; j < kNPTe; ++j) {
-        nloc[j] = ngrp * (32 * kNPTe) + j * 32 + lane;
+        nloc[j] = (TAIL ? ngrp : warp) * (32 * kNPTe) + j * 32 + lane;
         if (FUSED) {
             const i64 n = node_tile0 + nloc[j];
             auto C = [&](int c) { return __ldg(prm.nn + (i64)c * prm.n_pad + n); };
@@ -599,17 +601,17 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
         const int n_valid = left >= kTileP ? kTileP : (left > 0 ? (int)left : 0);
         const PodE* s_pod = (const PodE*)(smem + L.pod) + stage * kTileP;
         uint32_t* wkey = (uint32_t*)(smem + L.wkey) + stage * kTileP * kWarps;
-        const uint32_t* bmrow = (const uint32_t*)(smem + L.bm) + stage * kTileP * kWordsTe + ngrp * kNPTe;
+        const uint32_t* bmrow = (const uint32_t*)(smem + L.bm) + stage * kTileP * kWordsTe + (TAIL ? ngrp : warp) * kNPTe;
         const PodR* s_podf = s_podf_base + stage * kTileP;
         uint32_t* wcnt = (uint32_t*)(smem + L.bm) + stage * kTileP * kWarps; // fused only
         uint32_t* bm_out = prm.bitmap + tile_p0 * prm.words_per_row + word0 + warp * kNPTe; // fused: this warp's four words
         if (!FUSED) mbar_wait(&bars[2 + stage], (uint32_t)((it >> 1) & 1));
 
-        i64* rowp = (i64*)prm.scores + (tile_p0 + pod_first) * prm.score_stride + node_tile0 + nloc[0];
+        i64* rowp = (i64*)prm.scores + (TAIL ? tile_p0 + pod_first : tile_p0) * prm.score_stride + node_tile0 + nloc[0];
         // (unrolling this loop costs registers and with them the third CTA per SM: 0.699 vs 0.665 ms)
         const int n_loop = warp_active ? n_valid : 0;
-        const i64 row_step = TAIL ? prm.score_stride * pod_step : prm.score_stride;
-        for (int jp = pod_first; jp < n_loop; jp += pod_step, rowp += row_step, bm_out += prm.words_per_row) {
+        for (int jp = TAIL ? pod_first : 0; jp < n_loop;
+             jp += TAIL ? pod_step : 1, rowp += TAIL ? prm.score_stride * pod_step : prm.score_stride, bm_out += prm.words_per_row) {
             const int4 q2 = *(const int4*)&s_pod[jp].nzc;      // nzc nzm nz200c nz200m
             const uint4 q3 = *(const uint4*)&s_pod[jp].fmag;   // fmag amag fsh ash
             const int4 q4 = *(const int4*)&s_pod[jp].fmax;     // fmax count arange32 kind
@@ -748,7 +750,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                 const u64 t = (u64)(k >> 18) - 1, h8 = (k >> 10) & 0xffu, nl = k & 0x3ffu;
                 const u64 ng = (u64)(prm.node_base + node_tile0) + nl;
                 // cross-tile ties: mix the tile index into the low hash byte so that no tile is favoured
-                const uint32_t h16 = ((uint32_t)h8 << 8) | ((tile_idx * 0x9E3779B1u ^ s_pod[tid].hmul) >> 24);
+                const uint32_t h16 = ((uint32_t)h8 << 8) | (((TAIL ? tile_idx : (uint32_t)blockIdx.x) * 0x9E3779B1u ^ s_pod[tid].hmul) >> 24);
                 const u64 key64 = ((t << 40) | ((u64)h16 << 24) | ng) + 1; // layout shared with the int64 kernels
                 atomicMax((i64*)prm.select_key + p, (i64)key64);
             }
@@ -769,6 +771,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
 
 // ---- launch geometry: one wave of CTAs, each with a long run of pod tiles ------------------------------------
 int g_num_sms = 0;
+thread_local int g_last_emit_launches = 1; // kernels the last launch_emit_narrow of this thread issued (the tail tile may go separately)
 
 // CTAs per resident slot: 1 = a single wave of long CTAs; more = shorter CTAs the hardware scheduler can
 // rebalance. Measured on C2 (profiles/): see kWavesReduce / kWavesEmit. FGS_WAVES_REDUCE / FGS_WAVES_EMIT override.
@@ -827,6 +830,7 @@ void launch_emit_spec(NarrowParams p, cudaStream_t st) {
     const bool split_tail = !FUSED && tail_on && a <= 4;
     p.tile_first = 0;
     p.tail_groups = kWarps;
+    g_last_emit_launches = (split_tail && node_tiles > 1) ? 2 : 1;
     if (!split_tail || node_tiles > 1) {
         NarrowParams q = p;
         if (split_tail) q.n_pad = p.n_pad - kTileNe; // geometry only: the grid below and the chunking skip the tail tile
@@ -957,6 +961,8 @@ bool launch_fused_narrow(const NarrowParams& p0, uint32_t spec, const int* ord_g
             return false;
     }
 }
+
+int narrow_last_emit_launches() { return g_last_emit_launches; }
 
 bool launch_emit_narrow(const NarrowParams& p, uint32_t spec, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;

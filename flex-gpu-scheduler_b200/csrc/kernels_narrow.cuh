@@ -94,6 +94,7 @@ uint32_t narrow_spec_bits(bool flex_f, bool fit_f, bool sc_flex, bool sc_fit, bo
 // false = no instantiation for that plugin combination (the caller falls back to the int64 kernels)
 bool launch_reduce_narrow(const NarrowParams& p, uint32_t spec, void* stream);
 bool launch_emit_narrow(const NarrowParams& p, uint32_t spec, void* stream);
+int narrow_last_emit_launches(); // 1, or 2 when the tail node tile was launched on its own
 // The fused pass (one pass over pod × node; no Allocatable among the score plugins): node orders, then prepass + kernel.
 // ev_between (cudaEvent_t, optional) is recorded between the prepass and the main kernel.
 size_t narrow_orders_scratch_bytes(int64_t n_nodes);
