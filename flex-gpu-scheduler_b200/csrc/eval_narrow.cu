@@ -419,16 +419,17 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     auto issue_pods = [&](int it) { // one thread
         const int stage = it & 1;
         const i64 p0 = pod_begin + (i64)it * kTileP;
+        constexpr int tn = kTileP;
         int* dst = (int*)(smem + L.raw + stage * L.raw_stage_bytes);
         mbar_expect_tx(&bars[stage], (uint32_t)L.raw_stage_bytes);
-        bulk_g2s(dst + 0 * kTileP, prm.pn + (i64)PN_KIND * prm.p_pad + p0, kTileP * 4, &bars[stage]);
-        bulk_g2s(dst + 1 * kTileP, prm.pn + (i64)PN_NZC * prm.p_pad + p0, kTileP * 4, &bars[stage]);
-        bulk_g2s(dst + 2 * kTileP, prm.pn + (i64)PN_NZM * prm.p_pad + p0, kTileP * 4, &bars[stage]);
+        bulk_g2s(dst + 0 * kTileP, prm.pn + (i64)PN_KIND * prm.p_pad + p0, tn * 4, &bars[stage]);
+        bulk_g2s(dst + 1 * kTileP, prm.pn + (i64)PN_NZC * prm.p_pad + p0, tn * 4, &bars[stage]);
+        bulk_g2s(dst + 2 * kTileP, prm.pn + (i64)PN_NZM * prm.p_pad + p0, tn * 4, &bars[stage]);
         i64* d2 = (i64*)(dst + 3 * kTileP);
-        bulk_g2s(d2 + 0 * kTileP, prm.reduce_max + (i64)RR_FLEX_MAX * prm.p_pad + p0, kTileP * 8, &bars[stage]);
-        bulk_g2s(d2 + 1 * kTileP, prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + p0, kTileP * 8, &bars[stage]);
-        bulk_g2s(d2 + 2 * kTileP, prm.reduce_max + (i64)RR_ALLOC_NEGLO * prm.p_pad + p0, kTileP * 8, &bars[stage]);
-        bulk_g2s(d2 + 3 * kTileP, prm.reduce_sum + p0, kTileP * 8, &bars[stage]);
+        bulk_g2s(d2 + 0 * kTileP, prm.reduce_max + (i64)RR_FLEX_MAX * prm.p_pad + p0, tn * 8, &bars[stage]);
+        bulk_g2s(d2 + 1 * kTileP, prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + p0, tn * 8, &bars[stage]);
+        bulk_g2s(d2 + 2 * kTileP, prm.reduce_max + (i64)RR_ALLOC_NEGLO * prm.p_pad + p0, tn * 8, &bars[stage]);
+        bulk_g2s(d2 + 3 * kTileP, prm.reduce_sum + p0, tn * 8, &bars[stage]);
         if (FUSED) {
             int* d3 = (int*)(d2 + 4 * kTileP);
             for (int c = 0; c < 7; ++c) bulk_g2s(d3 + c * kTileP, prm.pn + (i64)(PN_LIM_G + c) * prm.p_pad + p0, kTileP * 4, &bars[stage]);
@@ -472,8 +473,11 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
             if (range >= 0 && range < (1 << 24)) {
                 u.arange32 = (int)range;
                 u.amag = narrow_magic((uint32_t)range, &u.ash);
-            } else {
+            } else { // the exact 64-bit path: the two fields carry the reciprocal of the range (alloc_div100)
                 u.arange32 = -1;
+                const u64 m = alloc_recip(range);
+                u.amag = (uint32_t)m;
+                u.ash = (int)(uint32_t)(m >> 32);
             }
         }
         uint32_t h = (uint32_t)(prm.seed ^ (prm.seed >> 32)) ^ ((uint32_t)(tile_p0 + tid) * 0x85EBCA6Bu);
@@ -709,7 +713,7 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                         } else if (q4.z < 0) {
                             const i64 alo = s_pod[jp].alo;
                             const i64 range = (i64)((u64)__ldg((const i64*)prm.reduce_max + (i64)RR_ALLOC_HI * prm.p_pad + tile_p0 + jp) - (u64)alo);
-                            v = (int)((i64)((u64)((i64)((u64)araw[j] - (u64)alo)) * 100ull) / range);
+                            v = alloc_div100((i64)((u64)araw[j] - (u64)alo), range, ((u64)q3.w << 32) | (u64)q3.y);
                         }
                         t += v * prm.w_alloc;
                     }

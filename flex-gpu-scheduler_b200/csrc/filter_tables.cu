@@ -762,6 +762,7 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     i64 alo = 0, arange64 = 0;
     int arange32 = 0;
     uint32_t amag = 0;
+    u64 arecip = 0;
     if (sc_alloc && count > 0) {
         const i64 hi = s_red[1], lo = -s_red[2];
         arange64 = (i64)((u64)hi - (u64)lo);
@@ -771,6 +772,7 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
             amag = narrow_magic((uint32_t)arange64, &ash);
         } else {
             arange32 = -1;
+            arecip = alloc_recip(arange64);
         }
     }
     uint32_t h = (uint32_t)(prm.seed ^ (prm.seed >> 32)) ^ ((uint32_t)p * 0x85EBCA6Bu);
@@ -830,7 +832,7 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
                 const int a = (int)(uint32_t)((u64)araw - (u64)alo);
                 v = qmagic32(200u * (uint32_t)a, amag, ash);
             } else if (arange32 < 0) {
-                v = (int)((i64)((u64)((i64)((u64)araw - (u64)alo)) * 100ull) / arange64);
+                v = alloc_div100((i64)((u64)araw - (u64)alo), arange64, arecip);
             }
             t += v * prm.w_alloc;
         }

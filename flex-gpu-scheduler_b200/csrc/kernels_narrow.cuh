@@ -47,6 +47,36 @@ inline uint32_t narrow_magic(uint32_t d, int* l) {
     return (uint32_t)((1ull << (31 + lg)) / d + 1ull);
 }
 
+// Allocatable.NormalizeScore outside the int32 range (allocatable.go:160: score = (raw − lowest) · 100 / (highest − lowest)):
+// (x · 100) / range with Go's int64 semantics — the product wraps, the quotient truncates toward zero. A 64-bit division is a
+// ~100-instruction subroutine and the divisor is one per POD, so the pod carries m = floor((2^64 − 1) / range) (range > 0;
+// m = 0 says "no reciprocal") and a node multiplies: for a = |x| · 100 < 2^63, q = hi64(a · m) is Q, Q − 1 or Q − 2
+// (a · m / 2^64 > a / range − (a / 2^64)(1 + 1 / range) > Q − 2), and the exact remainder settles which. Every other input
+// takes the division itself: the result is exact for all of them (tests/cpp/magic_test.cpp).
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline unsigned long long alloc_recip(long long range) { return range > 0 ? ~0ull / (unsigned long long)range : 0ull; }
+
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline int alloc_div100(long long x, long long range, unsigned long long m) {
+    if (m != 0 && x > -(1ll << 56) && x < (1ll << 56)) {
+        const unsigned long long a = (unsigned long long)(x < 0 ? -x : x) * 100ull;
+#if defined(__CUDA_ARCH__)
+        unsigned long long q = __umul64hi(a, m);
+#else
+        unsigned long long q = (unsigned long long)(((unsigned __int128)a * m) >> 64);
+#endif
+        unsigned long long r = a - q * (unsigned long long)range;
+        if (r >= (unsigned long long)range) ++q, r -= (unsigned long long)range;
+        if (r >= (unsigned long long)range) ++q;
+        return (int)(x < 0 ? -(long long)q : (long long)q);
+    }
+    return (int)((long long)((unsigned long long)x * 100ull) / range);
+}
+
 enum NarrowNodeCol : int {
     NN_THR_GPU = 0, NN_THR_MEM, NN_FREE_CPU, NN_FREE_MEM, NN_FREE_EPH, NN_FS0, NN_FS1, NN_FLAGS,
     NN_CAP_C, NN_X_C, NN_CAP_M, NN_X_M, NN_GSCORE, NN_MSCORE,

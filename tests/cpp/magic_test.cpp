@@ -43,6 +43,42 @@ int main() {
     for (int k = 0; k < 200000; ++k) divisor((uint32_t)(rng() % 0x7fffffffu) + 1, rng); // random divisors up to 2^31 - 1
     int l = 7;
     if (fgs::narrow_magic(0, &l) != 0 || l != 0) ++bad; // capacity 0 → quotient 0 (least_allocated.go:48-50)
-    std::printf("%lld checks, %lld failed\n", checks, bad);
+    // alloc_div100: (x * 100) / range as Go computes it (wrapping product, truncation toward zero), for every kind of input
+    long long dchecks = 0;
+    auto dcheck = [&](long long x, long long range) {
+        if (range == 0) return;
+        const long long prod = (long long)((unsigned long long)x * 100ull);
+        if (prod == INT64_MIN && range == -1) return; // the one quotient int64 cannot hold
+        const int want = (int)(prod / range);
+        const int got = fgs::alloc_div100(x, range, fgs::alloc_recip(range));
+        if (fgs::alloc_div100(x, range, 0) != want) ++bad; // no reciprocal: the division itself
+        ++dchecks;
+        if (want != got) {
+            if (bad < 10) std::printf("alloc_div100(%lld, %lld): %d != %d\n", x, range, got, want);
+            ++bad;
+        }
+    };
+    for (int k = 0; k < 4000000; ++k) {
+        const int rb = 1 + (int)(rng() % 62), xb = 1 + (int)(rng() % 63);
+        long long range = (long long)(rng() >> (64 - rb));
+        long long x = (long long)(rng() >> (64 - xb));
+        if (rng() & 1) x = -x;
+        if ((rng() & 15) == 0) range = -range;
+        dcheck(x, range);
+        if (range > 0) { // exact multiples and their neighbours, x inside [0, range] (the case the scores come from)
+            const long long y = (long long)(rng() % (unsigned long long)range);
+            dcheck(y, range);
+            const long long q = (long long)(rng() % 101);
+            if (range < (1ll << 55)) {
+                const long long m = (q * range) / 100;
+                dcheck(m, range), dcheck(m + 1, range), dcheck(m - 1, range);
+            }
+            dcheck(range, range), dcheck(range - 1, range), dcheck(-range, range);
+        }
+    }
+    for (long long range : {1ll, 2ll, 3ll, (1ll << 24), (1ll << 24) + 1, (1ll << 53) - 1, (1ll << 53) + 1, (1ll << 56), (long long)INT64_MAX})
+        for (long long x : {0ll, 1ll, -1ll, (1ll << 56) - 1, -(1ll << 56) + 1, (1ll << 56), -(1ll << 56), (long long)INT64_MAX, (long long)INT64_MIN, (long long)INT64_MIN + 1})
+            dcheck(x, range);
+    std::printf("%lld checks, %lld division checks, %lld failed\n", checks, dchecks, bad);
     return bad ? 1 : 0;
 }
