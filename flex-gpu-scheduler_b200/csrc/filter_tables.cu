@@ -481,7 +481,8 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     __shared__ int s_flags[2];    // score-time panic, filter-time panic
     __shared__ uint32_t s_cnt[kSmallThreads / 32];
     __shared__ u64 s_key[kSmallThreads / 32];
-    __shared__ i64 s_x[8];        // CL > 1: what this CTA's slice contributes, read by the other CTAs of the cluster
+    __shared__ i64 s_xall[CL][8]; // CL > 1: row r = what CTA r's slice contributes (count, maxima, flags), stored here by CTA r itself
+    __shared__ u64 s_keys[CL];    // CL > 1, rank 0: every slice's best selectHost key
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const i64 p = blockIdx.x / CL;
     const int rank = CL > 1 ? (int)cg::this_cluster().block_rank() : 0;
@@ -618,24 +619,29 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
             }
         }
         __syncthreads();
-        if (CL > 1) { // the other slices' share, through distributed shared memory
+        if (CL > 1) { // the other slices' share, through distributed shared memory: every CTA stores its seven numbers into row
+                      // `rank` of every CTA's table (lane r → CTA r), one cluster barrier, and reads its own copy
             cg::cluster_group cluster = cg::this_cluster();
-            if (tid == 0) {
-                s_x[0] = (i64)count, s_x[1] = s_red[0], s_x[2] = s_red[1], s_x[3] = s_red[2], s_x[4] = s_red[3];
-                s_x[5] = s_flags[0], s_x[6] = s_flags[1];
+            if (warp == 0 && lane < CL) {
+                i64* dst = cluster.map_shared_rank(&s_xall[rank][0], lane);
+                dst[0] = (i64)count, dst[1] = s_red[0], dst[2] = s_red[1], dst[3] = s_red[2], dst[4] = s_red[3];
+                dst[5] = s_flags[0], dst[6] = s_flags[1];
             }
             cluster.sync();
-            if (tid == 0) {
-                i64 c = 0, r0 = kMin, r1 = kMin, r2 = kMin, r3 = 0, f0 = 0, f1 = 0;
-                for (int r = 0; r < CL; ++r) {
-                    const i64* x = cluster.map_shared_rank(s_x, r);
-                    c += x[0];
-                    r0 = x[1] > r0 ? x[1] : r0, r1 = x[2] > r1 ? x[2] : r1, r2 = x[3] > r2 ? x[3] : r2, r3 = x[4] > r3 ? x[4] : r3;
-                    f0 |= x[5], f1 |= x[6];
+            if (warp == 0) {
+                const bool on = lane < CL;
+                i64 c = on ? s_xall[on ? lane : 0][0] : 0;
+                const i64 r0 = warp_max_i64(on ? s_xall[on ? lane : 0][1] : kMin), r1 = warp_max_i64(on ? s_xall[on ? lane : 0][2] : kMin);
+                const i64 r2 = warp_max_i64(on ? s_xall[on ? lane : 0][3] : kMin), r3 = warp_max_i64(on ? s_xall[on ? lane : 0][4] : 0);
+                const int f0 = __any_sync(0xffffffffu, on && s_xall[on ? lane : 0][5] != 0);
+                const int f1 = __any_sync(0xffffffffu, on && s_xall[on ? lane : 0][6] != 0);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+                if (lane == 0) {
+                    s_red[0] = r0, s_red[1] = r1, s_red[2] = r2, s_red[3] = r3;
+                    s_flags[0] = f0 ? 1 : 0, s_flags[1] = f1 ? 1 : 0;
+                    s_cnt[0] = (uint32_t)c;
                 }
-                s_red[0] = r0, s_red[1] = r1, s_red[2] = r2, s_red[3] = r3;
-                s_flags[0] = (int)f0, s_flags[1] = (int)f1;
-                s_cnt[0] = (uint32_t)c;
             }
             __syncthreads();
             count = s_cnt[0];
@@ -849,22 +855,21 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     if (lane == 0) s_key[warp] = best;
     __syncthreads();
     // ---- the per-pod rows and the result record (finalize_pods) ---------------------------------------------------------------
-    if (CL > 1) { // the cluster's best key: rank 0 reads every slice's
+    if (CL > 1) { // the cluster's best key: every slice's goes into rank 0's table; after the barrier only rank 0 has work left
         if (tid == 0) {
             u64 key = 0;
 #pragma unroll
             for (int w = 0; w < kSmallThreads / 32; ++w) key = s_key[w] > key ? s_key[w] : key;
-            s_x[7] = (i64)key;
+            *cg::this_cluster().map_shared_rank(&s_keys[rank], 0) = key;
         }
         cg::this_cluster().sync();
+        if (rank != 0) return; // (nobody reads a finished CTA's shared memory: the stores above went the other way)
     }
-    if (tid == 0 && rank == 0) {
+    if (tid == 0) {
         u64 key = 0;
         if (CL > 1) {
-            for (int r = 0; r < CL; ++r) {
-                const u64 k = (u64)*cg::this_cluster().map_shared_rank(&s_x[7], r);
-                key = k > key ? k : key;
-            }
+#pragma unroll
+            for (int r = 0; r < CL; ++r) key = s_keys[r] > key ? s_keys[r] : key;
         } else {
 #pragma unroll
             for (int w = 0; w < kSmallThreads / 32; ++w) key = s_key[w] > key ? s_key[w] : key;
@@ -898,13 +903,14 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
         prm.h_compact[p] = w0;
         prm.h_compact[kSmallMaxPods + p] = score;
         __threadfence_system();
-        if (atomicAdd(prm.d_done, 1u) == (unsigned)(prm.n_pods - 1)) { // every other pod's record is out: tell the host
+        if (prm.n_pods == 1) { // the record above is the only one
+            *prm.h_flag = prm.seq;
+        } else if (atomicAdd(prm.d_done, 1u) == (unsigned)(prm.n_pods - 1)) { // every other pod's record is out: tell the host
             *prm.d_done = 0;
             __threadfence_system();
             *prm.h_flag = prm.seq;
         }
     }
-    if (CL > 1) cg::this_cluster().sync(); // no CTA leaves while rank 0 may still read its shared memory
 }
 
 // Which pods would make the reference panic inside FlexGPU.Filter (see filter_panic_pass in kernels_narrow.cu): a pod
