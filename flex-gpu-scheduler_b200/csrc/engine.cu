@@ -129,7 +129,8 @@ void Engine::free_all() {
     if (d_perpod) cudaFree(d_perpod);
     if (d_bitmap) cudaFree(d_bitmap);
     if (d_scores) cudaFree(d_scores);
-    if (d_nn) cudaFree(d_nn);
+    for (auto& en : nn_ring)
+        if (en.d) cudaFree(en.d);
     if (d_pn) cudaFree(d_pn);
     if (d_an) cudaFree(d_an);
     if (d_special) cudaFree(d_special);
@@ -504,30 +505,15 @@ int Engine::decide_narrow_once(const fgs_pod_table* t, bool launch_pods) {
         sh.s[d] = s;
     }
     // buffers
-    if (n_pad > nn_cap) {
-        if (d_nn) cudaFree(d_nn);
-        d_nn = nullptr;
-        FGS_CUDA(this, cudaMalloc(&d_nn, sizeof(int) * NN_COLS * n_pad));
-        nn_cap = n_pad;
-        narrow_nodes_sig = -1;
-    }
     if (p_pad > pn_cap) {
         if (d_pn) cudaFree(d_pn);
         d_pn = nullptr;
         FGS_CUDA(this, cudaMalloc(&d_pn, sizeof(int) * PN_COLS * p_pad));
         pn_cap = p_pad;
     }
-    const int sig = cfg.fit_strategy;
-    if (narrow_nodes_sig != sig || std::memcmp(&sh, &narrow_sh, sizeof(sh)) != 0) {
-        if (window_back) { // the int32 node table is rewritten on the front stream: the emit pass in flight on the compute stream reads it
-            FGS_CUDA(this, cudaEventRecord(ev_back, window_back));
-            FGS_CUDA(this, cudaStreamWaitEvent(stream, ev_back, 0));
-        }
-        launch_narrow_nodes((const int64_t*)d_nd, n_pad, sh, cfg.fit_strategy, (int*)d_nn, stream);
-        launches++;
-        narrow_nodes_sig = sig;
-        narrow_sh = sh;
-        orders_valid = false; // the fused pass's node orders follow the narrow node table
+    {
+        const int rc = use_nn(sh, cfg.fit_strategy);
+        if (rc) return rc;
     }
     if (launch_pods) {
         launch_narrow_pods((const int64_t*)d_pods, p_pad, S, sh, cfg.fit_ignored_scalar_mask, (int*)d_pn, stream);
@@ -535,6 +521,59 @@ int Engine::decide_narrow_once(const fgs_pod_table* t, bool launch_pods) {
     }
     FGS_CUDA(this, cudaGetLastError());
     narrow_batch = true;
+    return FGS_OK;
+}
+
+void Engine::invalidate_nn() {
+    for (auto& en : nn_ring) en.sig = -1;
+    narrow_nodes_sig = -1;
+}
+
+int Engine::use_nn(const NarrowShifts& sh, int sig) {
+    if (n_pad > nn_cap) { // the node table grew: every entry is too small
+        FGS_CUDA(this, cudaDeviceSynchronize());
+        for (auto& en : nn_ring) {
+            if (en.d) cudaFree(en.d);
+            en.d = nullptr;
+            en.sig = -1;
+        }
+        d_nn = nullptr;
+        nn_cur = -1;
+        nn_cap = n_pad;
+    }
+    int hit = -1;
+    for (int i = 0; i < kNnRing; ++i)
+        if (nn_ring[i].sig == sig && nn_ring[i].gen == node_gen && std::memcmp(&nn_ring[i].sh, &sh, sizeof(sh)) == 0) hit = i;
+    if (hit < 0) {
+        // an entry no batch in flight reads: an empty one, else the least recently used
+        bool in_use[kNnRing] = {false};
+        for (const Slot& sl : slots)
+            if (sl.busy && sl.nn_idx >= 0) in_use[sl.nn_idx] = true;
+        int victim = -1;
+        for (int i = 0; i < kNnRing; ++i) {
+            if (in_use[i]) continue;
+            if (nn_ring[i].sig < 0 || nn_ring[i].gen != node_gen) {
+                victim = i;
+                break;
+            }
+            if (victim < 0 || nn_ring[i].last_use < nn_ring[victim].last_use) victim = i;
+        }
+        if (victim < 0) return fail(FGS_E_STATE, "int32 node tables: every entry is in use by a batch in flight");
+        NnEntry& en = nn_ring[victim];
+        if (!en.d) FGS_CUDA(this, cudaMalloc(&en.d, sizeof(int) * NN_COLS * nn_cap));
+        launch_narrow_nodes((const int64_t*)d_nd, n_pad, sh, sig, (int*)en.d, stream);
+        launches++;
+        FGS_CUDA(this, cudaGetLastError());
+        en.sh = sh, en.sig = sig, en.gen = node_gen;
+        hit = victim;
+    }
+    nn_ring[hit].last_use = ++nn_clock;
+    if (hit != nn_cur || narrow_nodes_sig != sig) orders_valid = false; // the fused pass's node orders follow the narrow node table
+    nn_cur = hit;
+    d_nn = nn_ring[hit].d;
+    narrow_sh = sh;
+    narrow_nodes_sig = sig;
+    slots[cur_slot].nn_idx = hit;
     return FGS_OK;
 }
 
@@ -739,7 +778,7 @@ int Engine::analyze_nodes_now(bool table_changed) {
     Engine* e = this;
     e->an_loose = false;
     e->node_an_valid = false;
-    e->narrow_nodes_sig = -1;
+    e->invalidate_nn();
     if (e->patch_spec) { // a full analysis supersedes what the row patches assumed
         FGS_CUDA(e, cudaStreamSynchronize(e->stream));
         e->patch_spec = false;
@@ -858,7 +897,7 @@ int Engine::patch_rows(const fgs_node_table* rows, const int64_t* dirty_idx) {
     pp.nn = (int*)d_nn;
     pp.sh = narrow_sh;
     pp.fit_most = cfg.fit_strategy == 1;
-    pp.narrow_valid = d_nn && narrow_nodes_sig == cfg.fit_strategy && nn_cap >= n_pad;
+    pp.narrow_valid = d_nn && nn_cur >= 0 && nn_ring[nn_cur].gen == node_gen && narrow_nodes_sig == cfg.fit_strategy && nn_cap >= n_pad;
     pp.d_flag = d_patch_flag;
     pp.h_flag = h_patch_flag;
     if (R <= kPatchInline) {
@@ -892,6 +931,7 @@ int Engine::patch_rows(const fgs_node_table* rows, const int64_t* dirty_idx) {
     FGS_CUDA(e, launch_patch_nodes(pp, stream));
     launches++;
     node_gen++;
+    if (pp.narrow_valid && nn_cur >= 0) nn_ring[nn_cur].gen = node_gen; // the table in use was patched along: it describes the new version
     patch_spec = true;
     an_loose = true;
     patches++;
@@ -1251,6 +1291,10 @@ extern "C" int fgs_pass_reduce(fgs_engine* eh) {
     if (e->staged_gen != e->node_gen)
         return e->fail(FGS_E_STATE, "fgs_pass_reduce: the node table changed since the batch was staged (its int32 columns follow the node table): stage it again");
     cudaSetDevice(e->device);
+    {
+        const int rc = e->ensure_slot_nn();
+        if (rc) return rc;
+    }
     e->sampled = false;
     e->masked = false;
     e->was_fused = false;
@@ -1370,6 +1414,10 @@ extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
     if (e->staged_gen != e->node_gen)
         return e->fail(FGS_E_STATE, "fgs_pass_emit: the node table changed since the batch was staged (its int32 columns follow the node table): stage it again");
     cudaSetDevice(e->device);
+    {
+        const int rc = e->ensure_slot_nn();
+        if (rc) return rc;
+    }
     if (opts && opts->sample) { // keep only the nodes the reference's walk would have found
         const int rc = e->run_sampling(opts);
         if (rc) return rc;
@@ -1817,11 +1865,27 @@ void Engine::bind_slot(int k) {
     o.d_pods = d_pods, o.h_pods = h_pods, o.d_perpod = d_perpod, o.h_perpod = h_perpod, o.d_pn = d_pn;
     o.p_pad_cap = p_pad_cap, o.pn_cap = pn_cap, o.n_pods = n_pods, o.p_pad = p_pad;
     o.narrow_batch = narrow_batch, o.emitted = emitted, o.sampled = sampled, o.have_pods = have_pods, o.key_shift = last_key_shift;
+    o.sh = narrow_sh, o.nn_sig = narrow_nodes_sig;
     const Slot& n = slots[k];
     d_pods = n.d_pods, h_pods = n.h_pods, d_perpod = n.d_perpod, h_perpod = n.h_perpod, d_pn = n.d_pn;
     p_pad_cap = n.p_pad_cap, pn_cap = n.pn_cap, n_pods = n.n_pods, p_pad = n.p_pad;
     narrow_batch = n.narrow_batch, emitted = n.emitted, sampled = n.sampled, have_pods = n.have_pods, last_key_shift = n.key_shift;
     cur_slot = k;
+    // the int32 node table that goes with the slot's batch: its ring entry if that still holds it (always, while the batch is in
+    // flight); a resident batch whose entry was recycled gets a new one from use_nn before its passes run (ensure_slot_nn)
+    narrow_sh = n.sh, narrow_nodes_sig = n.nn_sig;
+    nn_cur = -1, d_nn = nullptr;
+    if (n.have_pods && n.narrow_batch && n.nn_idx >= 0) {
+        const NnEntry& en = nn_ring[n.nn_idx];
+        if (en.sig == n.nn_sig && en.sig >= 0 && en.gen == node_gen && std::memcmp(&en.sh, &n.sh, sizeof(n.sh)) == 0) nn_cur = n.nn_idx, d_nn = en.d;
+    }
+}
+
+int Engine::ensure_slot_nn() {
+    if (!have_pods || !narrow_batch || (nn_cur >= 0 && d_nn)) return FGS_OK;
+    if (narrow_nodes_sig < 0) return fail(FGS_E_STATE, "the staged batch has no int32 node table: stage it again");
+    const NarrowShifts sh = narrow_sh;
+    return use_nn(sh, narrow_nodes_sig);
 }
 
 static int ensure_pipeline(Engine* e) {

@@ -64,7 +64,23 @@ struct Engine {
     bool no_dma = false;       // FGS_NO_DMA=1: always stage through the engine's own pinned buffer (tests)
     bool staged_by_dma = false; // the last staged batch came by DMA straight from the caller's table
     bool reduce_was_narrow = false, emit_was_narrow = false;
-    void* d_nn = nullptr;
+    void* d_nn = nullptr; // the int32 node table in use: one entry of nn_ring
+    // The int32 node table depends on the batch's shifts, and several batches are in flight (or resident in pipeline slots):
+    // a small ring of tables keyed by (node table version, fit strategy, shifts). A batch keeps its entry until it is
+    // collected; an entry no batch in flight uses is recycled, least recently used first.
+    static constexpr int kNnRing = 8;
+    struct NnEntry {
+        void* d = nullptr;
+        NarrowShifts sh;
+        int sig = -1; // fit strategy the table was built for, -1 = holds nothing
+        uint64_t gen = 0, last_use = 0;
+    };
+    NnEntry nn_ring[kNnRing];
+    int nn_cur = -1;
+    uint64_t nn_clock = 0;
+    int use_nn(const NarrowShifts& sh, int sig); // d_nn / narrow_sh / narrow_nodes_sig ← a table narrowed under sh (built if no entry holds one)
+    void invalidate_nn();
+    int ensure_slot_nn(); // after bind_slot: the bound batch's int32 node table is there (rebuilt if its ring entry was recycled)
     void* d_pn = nullptr;
     void* d_an = nullptr;
     void* d_special = nullptr; // int64 [2][n_pad]: nodes with a negative MemScore or on which NewGPUNode panics
@@ -119,6 +135,9 @@ struct Engine {
         bool narrow_batch = false, emitted = false, sampled = false, have_pods = false, busy = false;
         uint64_t node_gen = 0; // Engine::node_gen when the batch was staged (fgs_resubmit refuses a stale batch)
         int key_shift = 40;
+        NarrowShifts sh;     // the shifts its int32 pod table was narrowed under, and …
+        int nn_sig = -1;     // … the fit strategy of the node table that goes with them
+        int nn_idx = -1;     // the ring entry it uses while it is in flight
         cudaEvent_t ev_done = nullptr;
         // sharded pipeline (peer attached): the emit pass of a batch is issued with the NEXT submit (or by collect)
         bool emit_pending = false;

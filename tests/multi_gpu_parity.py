@@ -91,6 +91,53 @@ def check_masked_scoring(fgs, eng, s, cfg, table, oracle, N, P, n0, n1):
     assert np.all(got.selected_node[ref.feasible_count == 0] == -1)
 
 
+def check_mixed_shift_batches(fgs, D, oracle, torch, dist, world, rank, local):
+    """batches that need different int32 shifts, in flight together on a sharded engine: the emit pass of a batch is issued
+    by the NEXT submit, after that batch was staged — it must still read the node table narrowed for its own shifts"""
+    import builders as B
+    import mixed_shifts as M
+    N = 2600
+    snap = B.build_snapshot(M.cluster(N))
+    cfg = fgs.config_plugins(2)
+    sets = {k: B.build_podset(M.batch(k, n, seed)) for k, n, seed in (("A", 900, 1), ("B", 700, 2), ("C", 1100, 3))}
+    refs = {k: oracle.evaluate(snap.ptr, v.ptr, cfg, workers=2) for k, v in sets.items()}
+    n0, n1 = D.shard_bounds(N, world, rank)
+    stream = torch.cuda.Stream()
+    eng = fgs.Engine(device=local, n_scalars=2, node_index_base=n0, total_nodes=N, stream=stream.cuda_stream)
+    eng.set_plugins(cfg)
+    eng.upload_nodes(fgs.Packer(2).nodes(snap.ptr, n0, n1))
+    px, why = D.try_peer_exchange(torch, dist, eng, 1100, multicast=True)
+    if px is None:
+        if rank == 0:
+            print("mixed-shift batches: no peer exchange:", why)
+        eng.close()
+        return
+    packers = {k: fgs.Packer(2, pin=(k != "B")) for k in sets}
+    tabs = {k: packers[k].pods(v.ptr) for k, v in sets.items()}
+
+    def same(got, ref):
+        assert np.array_equal(got.feasible_count, ref.feasible_count), "mixed shifts: counts"
+        assert np.array_equal(got.pod_err, ref.pod_err), "mixed shifts: error bits"
+        ok = (ref.pod_err == 0) & (ref.feasible_count >= 1)
+        assert np.array_equal(got.selected_score[ok], ref.max_total[ok]), "mixed shifts: selected score"
+        idx = np.nonzero(ok)[0]
+        assert np.array_equal(ref.total[idx, got.selected_node[idx]], ref.max_total[idx]), "mixed shifts: selected node outside tie set"
+
+    depth = eng.max_in_flight()
+    for order in ("ABCABC", "AABBCC", "CBACAB"):
+        q = []
+        for k in order:
+            eng.submit(tabs[k])
+            q.append(k)
+            if len(q) == depth:
+                same(eng.collect(), refs[q.pop(0)])
+        while q:
+            same(eng.collect(), refs[q.pop(0)])
+    eng.peer_status()
+    px.close()
+    eng.close()
+
+
 def main():
     import torch
     import torch.distributed as dist
@@ -168,6 +215,7 @@ def main():
             px.close()
         eng.close()
         modes_run.append(mode)
+    check_mixed_shift_batches(fgs, D, oracle, torch, dist, world, rank, local)
     dist.barrier()
     dist.destroy_process_group()
     if rank == 0:
