@@ -18,6 +18,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 
 #include "filter_tables.cuh"
 #include "kernels.cuh"
@@ -90,6 +91,104 @@ __global__ void __launch_bounds__(256) ft_scatter(const i64* __restrict__ ks, co
     node_rank[perm[i]] = r;
     if (head[i]) levels[r] = ks[i];
     if (i == n - 1) *count = scan[i];
+}
+
+// Node tables of up to 16 384 (padded) rows: every sort of the build — the 5+S threshold columns ascending, the three score
+// orders descending — in ONE launch, a CTA per column, bitonic in shared memory on (key, node index) pairs (the order a
+// stable radix sort gives, so both forms of the build produce the same tables bit for bit), followed for the threshold columns
+// by what ft_heads / InclusiveSum / ft_scatter do: rank = number of distinct keys before, levels[rank], node_rank[node], count.
+constexpr int kSortThreads = 1024;
+constexpr int kSortMax = 16384; // 16 384 x 12 bytes = 192 KB of the 227 KB a CTA may have
+struct FtSortParams {
+    const i64* thr; // [n_dims + FT_ORDERS][stride]
+    i64 stride, n_pad, n_nodes;
+    int n_dims;
+    i64* levels;    // [n_dims][stride + 1]
+    int* node_rank; // [n_dims][stride]
+    int* counts;    // [n_dims]
+    int* ord;       // [FT_ORDERS][stride]
+    i64* ord_val;   // [FT_ORDERS][stride]
+};
+__global__ void __launch_bounds__(kSortThreads) ft_sort_small(const __grid_constant__ FtSortParams prm) {
+    extern __shared__ __align__(16) unsigned char sort_smem[];
+    const int col = blockIdx.x;
+    const bool is_order = col >= prm.n_dims;
+    const int n = (int)(is_order ? prm.n_nodes : prm.n_pad);
+    int M = 1024;
+    while (M < n) M <<= 1;
+    i64* key = (i64*)sort_smem;
+    int* val = (int*)(sort_smem + (size_t)M * 8);
+    __shared__ int s_warp[kSortThreads / 32];
+    const int tid = threadIdx.x;
+    const i64* src = prm.thr + (i64)col * prm.stride;
+    const i64 pad = is_order ? kMin : kMax;
+    for (int i = tid; i < M; i += kSortThreads) {
+        key[i] = i < n ? src[i] : pad;
+        val[i] = i;
+    }
+    __syncthreads();
+    // a before b: ascending by (key, index); the orders descending by key, ascending by index
+    auto before = [&](i64 ka, int va, i64 kb, int vb) { return ka != kb ? (is_order ? ka > kb : ka < kb) : va < vb; };
+    for (int k = 2; k <= M; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < (M >> 1); t += kSortThreads) {
+                const int lo = ((t & ~(j - 1)) << 1) | (t & (j - 1)), hi = lo | j; // the pair (lo, lo + j)
+                const bool up = (lo & k) == 0;
+                const i64 ka = key[lo], kb = key[hi];
+                const int va = val[lo], vb = val[hi];
+                if (before(kb, vb, ka, va) == up) {
+                    key[lo] = kb, key[hi] = ka;
+                    val[lo] = vb, val[hi] = va;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    if (is_order) {
+        const int o = col - prm.n_dims;
+        for (int i = tid; i < n; i += kSortThreads) {
+            prm.ord[(i64)o * prm.stride + i] = val[i];
+            prm.ord_val[(i64)o * prm.stride + i] = key[i];
+        }
+        return;
+    }
+    // heads and their inclusive scan: a thread owns M / 1024 consecutive positions
+    const int per = M / kSortThreads, i0 = tid * per;
+    int local = 0;
+    for (int u = 0; u < per; ++u) {
+        const int i = i0 + u;
+        if (i < n && (i == 0 || key[i] != key[i - 1])) ++local;
+    }
+    int incl = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((tid & 31) >= o) incl += v;
+    }
+    if ((tid & 31) == 31) s_warp[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+        int w = s_warp[tid];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, w, o);
+            if (tid >= o) w += v;
+        }
+        s_warp[tid] = w;
+    }
+    __syncthreads();
+    int run = incl - local + ((tid >> 5) ? s_warp[(tid >> 5) - 1] : 0); // distinct keys before this thread's first position
+    i64* levels = prm.levels + (i64)col * (prm.stride + 1);
+    int* node_rank = prm.node_rank + (i64)col * prm.stride;
+    for (int u = 0; u < per; ++u) {
+        const int i = i0 + u;
+        if (i >= n) break;
+        const bool head = i == 0 || key[i] != key[i - 1];
+        if (head) levels[run] = key[i];
+        run += head ? 1 : 0;
+        node_rank[val[i]] = run - 1;
+        if (i == n - 1) prm.counts[col] = run;
+    }
 }
 
 // T_d[r][w] = bits of the nodes 32w..32w+31 whose rank in dimension d is >= r, for r = 0..R_d (row R_d is empty).
@@ -1027,8 +1126,29 @@ cudaError_t ft_build(FilterTables* ft, const FtBuildParams& bp, cudaStream_t st,
     const unsigned nb = (unsigned)((n + 255) / 256);
 
     ft_thresholds<<<nb, 256, 0, st>>>(bp.nd, n_nodes, n, bp.S, bp.filter_mask, thr, stride);
+    *launches += 1;
+    const char* sort_env = getenv("FGS_FT_SORT"); // "cub": the library sorts whatever the size (read per build: the tests switch it)
+    const bool small_sort_on = !(sort_env && sort_env[0] == 'c');
+    const bool small_sort = small_sort_on && n <= kSortMax;
+    if (small_sort) {
+        FtSortParams sp;
+        sp.thr = thr, sp.stride = stride, sp.n_pad = n, sp.n_nodes = n_nodes, sp.n_dims = n_dims;
+        sp.levels = (i64*)ft->d_levels, sp.node_rank = (int*)ft->d_node_rank, sp.counts = (int*)ft->d_counts;
+        sp.ord = (int*)ft->d_ord, sp.ord_val = (i64*)ft->d_ord_val;
+        int M = 1024;
+        while (M < n) M <<= 1;
+        const size_t sm = (size_t)M * 12;
+        static bool attr_set = false;
+        if (!attr_set) {
+            FT_TRY(cudaFuncSetAttribute(ft_sort_small, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortMax * 12));
+            attr_set = true;
+        }
+        ft_sort_small<<<(unsigned)(n_dims + FT_ORDERS), kSortThreads, sm, st>>>(sp);
+        *launches += 1;
+        FT_TRY(cudaGetLastError());
+    } else {
     ft_iota<<<nb, 256, 0, st>>>(iota, n);
-    *launches += 2;
+    *launches += 1;
     for (int d = 0; d < n_dims; ++d) {
         FT_TRY(cub::DeviceRadixSort::SortPairs(tmp, tb, (const i64*)(thr + (i64)d * stride), keys_out, (const int*)iota, perm, (int)n, 0, 64, st));
         ft_heads<<<nb, 256, 0, st>>>(keys_out, n, head);
@@ -1041,6 +1161,7 @@ cudaError_t ft_build(FilterTables* ft, const FtBuildParams& bp, cudaStream_t st,
     for (int o = 0; o < FT_ORDERS; ++o) {
         FT_TRY(cub::DeviceRadixSort::SortPairsDescending(tmp, tb, (const i64*)(thr + (i64)(n_dims + o) * stride), (i64*)ft->d_ord_val + (i64)o * stride,
                                                          (const int*)iota, (int*)ft->d_ord + (i64)o * stride, (int)n_nodes, 0, 64, st));
+    }
     }
     int counts[kFtMaxDims] = {0};
     FT_TRY(cudaMemcpyAsync(counts, ft->d_counts, sizeof(int) * n_dims, cudaMemcpyDeviceToHost, st));

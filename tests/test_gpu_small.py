@@ -157,3 +157,30 @@ def test_cycles_between_node_changes_need_no_table_rebuild(gpu_ok, oracle):
         g += 1
     check(0, 256, True)
     eng.close()
+
+
+def test_level_tables_built_by_either_sort_answer_alike(gpu_ok, oracle):
+    """the level tables of a node table of up to 16 384 rows are sorted in shared memory in one launch, larger ones by the
+    library's radix sort; both orders are (key, node index), so every answer — tie-breaks included — is the same"""
+    s = fgs.config_synth(2, n_nodes=9000, n_pending=2000, pm_quirk_nodes=150, pm_panic_nodes=40, pm_nongpu_nodes=60, pm_invalid_nodes=20)
+    cfg = fgs.config_plugins(2)
+    got = []
+    for mode in (None, "cub"):
+        if mode:
+            os.environ["FGS_FT_SORT"] = mode
+        try:
+            eng = fgs.Engine(device=0)
+            eng.set_plugins(cfg)
+            eng.upload_nodes(fgs.Packer(2).nodes(s.snapshot))
+            got.append(eng.evaluate(fgs.Packer(2).pods(s.pending), want_planes=True))
+            assert eng.timings()["reduce_lookup"]
+            eng.close()
+        finally:
+            os.environ.pop("FGS_FT_SORT", None)
+    a, b = got
+    N = s.n_nodes
+    for k in ("feasible_count", "selected_node", "selected_score", "pod_err"):
+        assert np.array_equal(getattr(a, k), getattr(b, k)), k
+    assert np.array_equal(a.feasible(N), b.feasible(N)) and np.array_equal(a.scores[:, :N], b.scores[:, :N])
+    ref = oracle.evaluate(s.snapshot, s.pending, cfg, workers=4)
+    assert np.array_equal(a.feasible(N), ref.status == 0) and np.array_equal(a.feasible_count, ref.feasible_count)
