@@ -141,6 +141,7 @@ void Engine::free_all() {
     if (h_walk) cudaFreeHost(h_walk);
     if (h_small) cudaFreeHost(h_small);
     if (d_small_done) cudaFree(d_small_done);
+    if (d_sample_scratch) cudaFree(d_sample_scratch);
     if (d_patch_flag) cudaFree(d_patch_flag);
     if (h_patch_flag) cudaFreeHost((void*)h_patch_flag);
     if (h_patch) cudaFreeHost(h_patch);
@@ -1271,8 +1272,21 @@ int Engine::run_sampling(const fgs_eval_opts* opts) {
     sp.p_pad = e->p_pad;
     sp.k = num_feasible_nodes_to_find(e->n_nodes, opts->percentage_of_nodes_to_score);
     sp.start = opts->start_node_index;
+    {   // the block maps of the composed walk (long batches on node tables of up to 16 384 rows)
+        const int64_t need = fgs::sample_scratch_bytes(e->n_nodes, e->n_pods);
+        if (need > e->sample_scratch_cap) {
+            FGS_CUDA(e, cudaStreamSynchronize(e->stream));
+            if (e->d_sample_scratch) cudaFree(e->d_sample_scratch);
+            e->d_sample_scratch = nullptr;
+            e->sample_scratch_cap = 0;
+            FGS_CUDA(e, cudaMalloc(&e->d_sample_scratch, (size_t)need));
+            e->sample_scratch_cap = need;
+        }
+        sp.scratch = need > 0 ? e->d_sample_scratch : nullptr;
+        sp.scratch_bytes = e->sample_scratch_cap;
+    }
     FGS_CUDA(e, launch_sampling(sp, e->stream));
-    e->launches += 3;
+    e->launches += sample_launch_count(e->n_nodes, e->n_pods, sp.scratch != nullptr);
     if ((e->cfg.score_mask & FGS_PL_FLEXGPU) && e->node_an_valid && e->node_an.n_special > 0) {
         launch_special_pass((const uint32_t*)e->d_bitmap, e->words_per_row, (const int64_t*)e->d_special, e->n_pad, e->node_an.n_special,
                             (const int64_t*)e->d_pods, (int64_t*)e->d_perpod, e->n_pods, e->p_pad, e->stream);

@@ -95,6 +95,8 @@ struct Engine {
     void* d_small_done = nullptr; // device counter of finished pods
     uint64_t small_seq = 0;
     bool small_off = false;
+    void* d_sample_scratch = nullptr; // node sampling: block maps of the composed walk
+    int64_t sample_scratch_cap = 0;
     int small_direct = -1;
     bool small_cluster = true;
     uint64_t small_gen = ~0ull; // node_gen of the last small-batch call, and how many calls in a row it has served

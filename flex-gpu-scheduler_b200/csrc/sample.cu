@@ -17,6 +17,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 #include "kernels.cuh"
 #include "sample.cuh"
@@ -75,8 +76,20 @@ __device__ __forceinline__ int select_bit(uint32_t x, int r) {
 }
 
 // ---- the walk: one warp, one pod after the other ------------------------------------------------------------
-__global__ void __launch_bounds__(32, 1) sample_chain(const uint32_t* __restrict__ bitmap, i64 W, i64 n_nodes, i64 n_pods, i64 K, i64 start0,
-                                                      int2* __restrict__ walk, i64* __restrict__ reduce_sum, i64* __restrict__ next_start) {
+// block_pods == 0: the whole batch from start0. Otherwise CTA b walks pods [b·block_pods, (b+1)·block_pods) from starts[b]
+// (sample_block_starts), all blocks at once.
+__global__ void __launch_bounds__(32, 1) sample_chain(const uint32_t* __restrict__ bitmap, i64 W, i64 n_nodes, i64 n_pods_all, i64 K, i64 start0,
+                                                      int2* __restrict__ walk, i64* __restrict__ reduce_sum, i64* __restrict__ next_start,
+                                                      i64 block_pods, const int* __restrict__ starts) {
+    const i64 pod0 = block_pods ? (i64)blockIdx.x * block_pods : 0;
+    i64 n_pods = block_pods ? (n_pods_all - pod0 < block_pods ? n_pods_all - pod0 : block_pods) : n_pods_all;
+    if (n_pods <= 0) return;
+    if (block_pods) {
+        start0 = starts[blockIdx.x];
+        bitmap += pod0 * W;
+        walk += pod0;
+        reduce_sum += pod0;
+    }
     extern __shared__ __align__(128) unsigned char smem[];
     uint64_t* bars = (uint64_t*)smem;                // [kStages]
     uint32_t* rows = (uint32_t*)(smem + 64);         // [kStages][W]
@@ -162,6 +175,210 @@ __global__ void __launch_bounds__(32, 1) sample_chain(const uint32_t* __restrict
         s = nxt;
         __syncwarp();
     }
+    if (lane == 0 && !block_pods) *next_start = s; // (blocks: sample_block_starts wrote it)
+}
+
+// ---- the walk without the chain --------------------------------------------------------------------------------------
+// Pod p turns a start index s into the next one: with b_0 < b_1 < … < b_{T-1} the feasible nodes of its row and i(s) the number
+// of them before s, next(s) = b_{(i(s) + K) mod T} when T > K, and s itself otherwise. That is a monotone (cyclically
+// order-preserving) step function with at most T steps, and so is every composition of such functions — with fewer and fewer
+// steps, because two starts between which a row has no feasible node stay together for good. sample_compose (a CTA per
+// block of kBlockPods pods) composes its block's functions: it keeps the distinct values reachable after each pod (at first
+// all feasible nodes of the block's first pod with T > K), maps them through the next pod's rank/select, and every few
+// pods merges equal neighbours; the result is, for every interval i of that first pod, where a walk that enters the block
+// in it stands after the block. sample_block_starts (one warp) then hops from block to block — one rank in the first pod's row
+// and one table look-up each — and sample_chain walks all blocks at once from the starts it found. The chain of P dependent
+// steps becomes P / kBlockPods hops plus kBlockPods steps.
+constexpr int kBlockPods = 256;
+constexpr int kComposeThreads = 512;
+constexpr int kComposeMaxNodes = 16384; // four uint16 arrays of that many entries, the row ring and the prefix: 140 KB of shared memory
+constexpr int kComposeStages = 4;
+constexpr int kMergeEvery = 8;
+
+struct ComposeParams {
+    const uint32_t* bitmap;
+    i64 W, n_nodes, n_pods, K;
+    unsigned short* out; // [n_blocks][n_nodes]: interval of the block's first walking pod → start index after the block
+    int* blk_q;          // [n_blocks]: that pod (index in the batch), or -1: no pod of the block moves the start
+    int* blk_T;          // [n_blocks]: its feasible count
+};
+
+__global__ void __launch_bounds__(kComposeThreads) sample_compose(const __grid_constant__ ComposeParams prm) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int W = (int)prm.W, N = (int)prm.n_nodes, K = (int)prm.K;
+    const i64 pod0 = (i64)blockIdx.x * kBlockPods;
+    const int n_pods = (int)(prm.n_pods - pod0 < kBlockPods ? prm.n_pods - pod0 : kBlockPods);
+    uint64_t* bars = (uint64_t*)smem;                                  // [kComposeStages]
+    uint32_t* rows = (uint32_t*)(smem + 64);                           // [kComposeStages][W]
+    int* pre = (int*)(rows + (size_t)kComposeStages * W);              // [W + 1] feasible nodes before word w
+    unsigned short* val = (unsigned short*)(pre + W + 1 + ((W + 1) & 1)); // [N] the distinct reachable start indices, in cyclic order
+    unsigned short* aux = val + kComposeMaxNodes;                      // [N] new values / merged values
+    unsigned short* idx = aux + kComposeMaxNodes;                      // [N] slot → merged slot
+    unsigned short* grp = idx + kComposeMaxNodes;                      // [T_q] initial slot → current slot
+    __shared__ int s_warp[kComposeThreads / 32];
+    __shared__ int s_m, s_T;
+    const uint32_t row_bytes = (uint32_t)(W * 4);
+    if (tid == 0) {
+        for (int k = 0; k < kComposeStages; ++k) mbar_init(&bars[k], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int p) { // one thread
+        const int st = p % kComposeStages;
+        mbar_expect_tx(&bars[st], row_bytes);
+        bulk_g2s(rows + (size_t)st * W, prm.bitmap + (pod0 + p) * prm.W, row_bytes, &bars[st]);
+    };
+    if (tid == 0)
+        for (int p = 0; p < kComposeStages - 1 && p < n_pods; ++p) issue(p);
+
+    // block-wide inclusive scan of one int per thread (in thread order); returns the inclusive value, *total ← the sum
+    auto block_scan = [&](int x, int* total) {
+        int incl = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        __syncthreads(); // s_warp may still be read from the scan before
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        int base = 0, tot = 0;
+#pragma unroll
+        for (int w = 0; w < kComposeThreads / 32; ++w) {
+            const int v = s_warp[w];
+            if (w < warp) base += v;
+            tot += v;
+        }
+        *total = tot;
+        return incl + base;
+    };
+
+    int q = -1, Tq = 0, m = 0, since_merge = 0;
+    for (int p = 0; p < n_pods; ++p) {
+        const int st = p % kComposeStages;
+        if (tid == 0 && p + kComposeStages - 1 < n_pods) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // the stage being refilled held row p-1: all threads passed the barrier below
+            issue(p + kComposeStages - 1);
+        }
+        mbar_wait(&bars[st], (uint32_t)((p / kComposeStages) & 1));
+        const uint32_t* row = rows + (size_t)st * W;
+        // pre[w] = feasible nodes in words 0..w-1 (W <= 512: one or two words per thread would do; a strided loop keeps it general)
+        {
+            const int per = (W + kComposeThreads - 1) / kComposeThreads, w0 = tid * per;
+            int c = 0;
+            for (int u = 0; u < per; ++u)
+                if (w0 + u < W) c += __popc(row[w0 + u]);
+            int T = 0;
+            const int incl = block_scan(c, &T);
+            int run = incl - c;
+            for (int u = 0; u < per; ++u)
+                if (w0 + u < W) {
+                    pre[w0 + u] = run;
+                    run += __popc(row[w0 + u]);
+                }
+            if (tid == 0) pre[W] = T, s_T = T;
+            __syncthreads();
+        }
+        const int T = s_T;
+        if (T >= K + 1) {
+            auto select = [&](int r) { // position of the r-th (0-based) feasible node of the row
+                int lo = 0, hi = W; // pre[lo] <= r < pre[hi]
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (pre[mid] <= r) lo = mid;
+                    else hi = mid;
+                }
+                return lo * 32 + select_bit(row[lo], r - pre[lo]);
+            };
+            if (q < 0) { // the block's first pod that moves the start: every feasible node of its row is reachable
+                q = p, Tq = T, m = T;
+                for (int j = tid; j < T; j += kComposeThreads) {
+                    val[j] = (unsigned short)select(j);
+                    grp[j] = (unsigned short)j;
+                }
+                since_merge = 0;
+            } else {
+                for (int j = tid; j < m; j += kComposeThreads) {
+                    const int v = val[j];
+                    const int sw = v >> 5;
+                    int r = pre[sw] + __popc(row[sw] & ((1u << (v & 31)) - 1u)) + K;
+                    if (r >= T) r -= T;
+                    aux[j] = (unsigned short)select(r);
+                }
+                __syncthreads();
+                for (int j = tid; j < m; j += kComposeThreads) val[j] = aux[j];
+                ++since_merge;
+            }
+            __syncthreads();
+            if (since_merge >= kMergeEvery && m > 1) { // equal values are neighbours (cyclically): one slot per run
+                since_merge = 0;
+                const int per = (m + kComposeThreads - 1) / kComposeThreads, j0 = tid * per;
+                const int last = val[m - 1];
+                int c = 0;
+                for (int u = 0; u < per; ++u) {
+                    const int j = j0 + u;
+                    if (j < m && val[j] != (j ? val[j - 1] : last)) ++c;
+                }
+                int heads = 0;
+                const int incl = block_scan(c, &heads);
+                // (a cyclic sequence changes value at no position or at two or more: heads is 0 or >= 2)
+                int run = incl - c;
+                for (int u = 0; u < per; ++u) {
+                    const int j = j0 + u;
+                    if (j >= m) break;
+                    const bool head = val[j] != (j ? val[j - 1] : last);
+                    run += head ? 1 : 0;
+                    const int slot = heads == 0 ? 0 : (run > 0 ? run - 1 : heads - 1); // values before the first change continue the LAST run
+                    idx[j] = (unsigned short)slot;
+                    if (head || (heads == 0 && j == 0)) aux[slot] = (unsigned short)val[j];
+                }
+                if (heads == 0) heads = 1; // every value equal: one slot
+                __syncthreads();
+                for (int i = tid; i < Tq; i += kComposeThreads) grp[i] = idx[grp[i]];
+                __syncthreads();
+                for (int j = tid; j < heads; j += kComposeThreads) val[j] = aux[j];
+                if (tid == 0) s_m = heads;
+                __syncthreads();
+                m = s_m;
+            }
+        }
+        __syncthreads(); // every thread is done with this stage's row before the ring refills it
+    }
+    if (tid == 0) prm.blk_q[blockIdx.x] = q >= 0 ? (int)(pod0 + q) : -1, prm.blk_T[blockIdx.x] = Tq;
+    if (q >= 0) {
+        unsigned short* out = prm.out + (size_t)blockIdx.x * (size_t)N;
+        for (int i = tid; i < Tq; i += kComposeThreads) {
+            int j = i + K;
+            if (j >= Tq) j -= Tq;
+            out[i] = val[grp[j]];
+        }
+    }
+}
+
+// block b starts where block b-1 left the index: one warp, one hop per block
+__global__ void __launch_bounds__(32, 1) sample_block_starts(const uint32_t* __restrict__ bitmap, i64 W, i64 n_nodes, i64 out_stride, int n_blocks, i64 start0,
+                                                             const unsigned short* __restrict__ out, const int* __restrict__ blk_q,
+                                                             const int* __restrict__ blk_T, int* __restrict__ starts, i64* __restrict__ next_start) {
+    const int lane = threadIdx.x;
+    const i64 N = n_nodes;
+    int s = (int)(((start0 % N) + N) % N);
+    for (int b = 0; b < n_blocks; ++b) {
+        if (lane == 0) starts[b] = s;
+        const int q = blk_q[b];
+        if (q < 0) continue;
+        const uint32_t* row = bitmap + (i64)q * W;
+        const int sw = s >> 5;
+        int before = 0;
+        for (int w = lane; w <= sw && w < (int)W; w += 32) {
+            const uint32_t x = __ldg(row + w);
+            before += w < sw ? __popc(x) : __popc(x & ((1u << (s & 31)) - 1u));
+        }
+        before = __reduce_add_sync(0xffffffffu, before);
+        const int T = blk_T[b];
+        if (before >= T) before -= T; // behind the last feasible node: the interval of the first one
+        s = (int)__ldg(out + (size_t)b * (size_t)out_stride + before);
+    }
     if (lane == 0) *next_start = s;
 }
 
@@ -246,14 +463,47 @@ int64_t num_feasible_nodes_to_find(int64_t n_nodes, int32_t percentage) {
     return k < 100 ? 100 : k;
 }
 
+static bool compose_applies(i64 n_nodes, i64 n_pods) {
+    const char* v = getenv("FGS_SAMPLE_SERIAL"); // 1: always the serial walk
+    if (v && v[0] == '1') return false;
+    return n_nodes <= kComposeMaxNodes && n_pods >= 4 * kBlockPods;
+}
+
+int64_t sample_scratch_bytes(int64_t n_nodes, int64_t n_pods) {
+    if (!compose_applies(n_nodes, n_pods)) return 0;
+    const i64 nb = (n_pods + kBlockPods - 1) / kBlockPods;
+    return (i64)sizeof(unsigned short) * nb * ((n_nodes + 7) & ~7ll) + (i64)sizeof(int) * 3 * (nb + 8);
+}
+
+int sample_launch_count(int64_t n_nodes, int64_t n_pods, bool have_scratch) { return have_scratch && compose_applies(n_nodes, n_pods) ? 5 : 3; }
+
 cudaError_t launch_sampling(const SampleParams& sp, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     if (sp.n_pods <= 0 || sp.n_nodes <= 0) return cudaSuccess;
     const size_t smem = 64 + (size_t)kStages * (size_t)sp.words_per_row * 4;
     cudaError_t ce = cudaFuncSetAttribute(sample_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (ce != cudaSuccess) return ce;
-    sample_chain<<<1, 32, smem, stream>>>(sp.bitmap, sp.words_per_row, sp.n_nodes, sp.n_pods, sp.k, sp.start, (int2*)sp.walk, (i64*)sp.reduce_sum,
-                                           (i64*)sp.next_start);
+    if (sp.scratch && compose_applies(sp.n_nodes, sp.n_pods) && sp.scratch_bytes >= sample_scratch_bytes(sp.n_nodes, sp.n_pods)) {
+        const i64 nb = (sp.n_pods + kBlockPods - 1) / kBlockPods;
+        const i64 n8 = (sp.n_nodes + 7) & ~7ll;
+        ComposeParams cp;
+        cp.bitmap = sp.bitmap, cp.W = sp.words_per_row, cp.n_nodes = n8, cp.n_pods = sp.n_pods, cp.K = sp.k;
+        cp.out = (unsigned short*)sp.scratch;
+        cp.blk_q = (int*)((char*)sp.scratch + sizeof(unsigned short) * nb * n8);
+        cp.blk_T = cp.blk_q + (nb + 8);
+        int* starts = cp.blk_T + (nb + 8);
+        const size_t W = (size_t)sp.words_per_row;
+        const size_t csmem = 64 + (size_t)kComposeStages * W * 4 + ((W + 2) & ~(size_t)1) * 4 + 4 * (size_t)kComposeMaxNodes * 2;
+        ce = cudaFuncSetAttribute(sample_compose, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem);
+        if (ce != cudaSuccess) return ce;
+        sample_compose<<<(unsigned)nb, kComposeThreads, csmem, stream>>>(cp);
+        sample_block_starts<<<1, 32, 0, stream>>>(sp.bitmap, sp.words_per_row, sp.n_nodes, n8, (int)nb, sp.start, cp.out, cp.blk_q, cp.blk_T, starts, (i64*)sp.next_start);
+        sample_chain<<<(unsigned)nb, 32, smem, stream>>>(sp.bitmap, sp.words_per_row, sp.n_nodes, sp.n_pods, sp.k, sp.start, (int2*)sp.walk,
+                                                        (i64*)sp.reduce_sum, (i64*)sp.next_start, kBlockPods, starts);
+    } else {
+        sample_chain<<<1, 32, smem, stream>>>(sp.bitmap, sp.words_per_row, sp.n_nodes, sp.n_pods, sp.k, sp.start, (int2*)sp.walk, (i64*)sp.reduce_sum,
+                                               (i64*)sp.next_start, 0, nullptr);
+    }
     const i64 total = sp.n_pods * sp.words_per_row;
     sample_truncate<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(sp.bitmap, sp.words_per_row, sp.n_nodes, sp.n_pods, (const int2*)sp.walk);
     reduce_from_bitmap<<<(unsigned)((sp.n_pods * 32 + 255) / 256), 256, 0, stream>>>(sp.bitmap, sp.words_per_row, sp.n_pods, sp.p_pad, sp.n_pad,

@@ -17,7 +17,13 @@ struct SampleParams {
     int64_t words_per_row, n_nodes, n_pad, n_pods, p_pad;
     int64_t k;               // numFeasibleNodesToFind
     int64_t start;           // nextStartNodeIndex before the first pod
+    void* scratch;           // sample_scratch_bytes(): the block maps of the composed walk (may be NULL: the serial walk runs)
+    int64_t scratch_bytes;
 };
+
+// the walk over blocks of pods (sample.cu: sample_compose / sample_block_starts): bytes of scratch it needs, 0 = not applicable
+int64_t sample_scratch_bytes(int64_t n_nodes, int64_t n_pods);
+int sample_launch_count(int64_t n_nodes, int64_t n_pods, bool have_scratch);
 
 int64_t num_feasible_nodes_to_find(int64_t n_nodes, int32_t percentage);
 // sample_chain + sample_truncate + reduce_from_bitmap (3 launches)

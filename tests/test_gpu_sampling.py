@@ -71,3 +71,42 @@ def test_sampling_is_a_chain_over_batches(gpu_ok, oracle):
     assert full.next_start_node_index == -1 and (full.processed_nodes == 1200).all()
     assert (full.feasible_count >= whole.feasible_count).all()
     eng.close()
+
+
+@pytest.mark.parametrize("cfg_id,n_nodes,n_pods,pct,start,kw", [
+    (2, 1500, 5000, 0, 77, {}),
+    (2, 5000, 3000, 10, 4999, {}),
+    (1, 2100, 2500, 0, 0, {}),
+    (2, 3000, 4100, 5, 1, dict(pm_nongpu_nodes=700, pm_quirk_nodes=100)),   # many pods with fewer than K feasible nodes: their walk leaves the index alone
+    (2, 16384, 1100, 3, 16000, {}),                                         # the largest table the composed walk takes
+])
+def test_long_batches_walk_in_blocks_and_land_where_the_chain_does(gpu_ok, oracle, cfg_id, n_nodes, n_pods, pct, start, kw):
+    """1 024 pods or more on up to 16 384 nodes: the walk is composed per block of 256 pods (sample_compose), the blocks are hopped
+    over (sample_block_starts) and walked at once (sample_chain). Same kept sets, processed counts and final index as the
+    oracle's one-pod-after-the-other walk, and as the serial kernel (FGS_SAMPLE_SERIAL=1)."""
+    s = fgs.config_synth(cfg_id, n_nodes=n_nodes, n_pending=n_pods, pm_invalid_nodes=5, **kw)
+    cfg = fgs.config_plugins(cfg_id)
+    ref = oracle.evaluate(s.snapshot, s.pending, cfg, sample=(pct, start))
+    got = {}
+    for serial in (False, True):
+        if serial:
+            os.environ["FGS_SAMPLE_SERIAL"] = "1"
+        try:
+            eng = _engine(s, cfg, False)
+            l0 = eng.timings()["kernel_launches"]
+            r = eng.evaluate(fgs.Packer(2).pods(s.pending), want_planes=True, sample=1, percentage_of_nodes_to_score=pct, start_node_index=start)
+            got[serial] = (r, eng.timings()["kernel_launches"] - l0)
+            eng.close()
+        finally:
+            os.environ.pop("FGS_SAMPLE_SERIAL", None)
+    assert got[False][1] == got[True][1] + 2  # sample_compose and sample_block_starts ran
+    for serial in (False, True):
+        r = got[serial][0]
+        assert np.array_equal(r.processed_nodes, ref.processed), serial
+        assert r.next_start_node_index == ref.next_start, serial
+        assert np.array_equal(r.feasible(n_nodes), ref.status == 0), serial
+        assert np.array_equal(r.feasible_count, ref.feasible_count) and np.array_equal(r.pod_err, ref.pod_err)
+        ok = (ref.pod_err == 0) & (ref.feasible_count > 0)
+        assert np.array_equal(r.selected_score[ok], ref.max_total[ok])
+    assert np.array_equal(got[False][0].selected_node, got[True][0].selected_node)
+    assert (ref.processed < n_nodes).any() and (ref.processed == n_nodes).any() or n_nodes > 10000 or cfg_id == 1 or not kw
