@@ -191,8 +191,9 @@ __global__ void __launch_bounds__(32, 1) sample_chain(const uint32_t* __restrict
 // steps becomes P / kBlockPods hops plus kBlockPods steps.
 constexpr int kBlockPods = 256;
 constexpr int kComposeThreads = 512;
-constexpr int kComposeMaxNodes = 16384; // four uint16 arrays of that many entries, the row ring and the prefix: 140 KB of shared memory
-constexpr int kComposeStages = 4;
+constexpr int kComposeSmallNodes = 16384; // up to here all four uint16 arrays live in shared memory (128 KB + the row ring)
+constexpr int kComposeMaxNodes = 65528;   // beyond: the two arrays only the merges touch live in global scratch (values are 16-bit)
+constexpr int kComposeStagesMax = 4;
 constexpr int kMergeEvery = 8;
 
 struct ComposeParams {
@@ -201,6 +202,9 @@ struct ComposeParams {
     unsigned short* out; // [n_blocks][n_nodes]: interval of the block's first walking pod → start index after the block
     int* blk_q;          // [n_blocks]: that pod (index in the batch), or -1: no pod of the block moves the start
     int* blk_T;          // [n_blocks]: its feasible count
+    unsigned short* g_idx; // [n_blocks][n_nodes] and
+    unsigned short* g_grp; // [n_blocks][n_nodes]: the merge arrays of a long node table (NULL: shared memory)
+    int stages;            // depth of the row ring
 };
 
 __global__ void __launch_bounds__(kComposeThreads) sample_compose(const __grid_constant__ ComposeParams prm) {
@@ -209,13 +213,14 @@ __global__ void __launch_bounds__(kComposeThreads) sample_compose(const __grid_c
     const int W = (int)prm.W, N = (int)prm.n_nodes, K = (int)prm.K;
     const i64 pod0 = (i64)blockIdx.x * kBlockPods;
     const int n_pods = (int)(prm.n_pods - pod0 < kBlockPods ? prm.n_pods - pod0 : kBlockPods);
-    uint64_t* bars = (uint64_t*)smem;                                  // [kComposeStages]
-    uint32_t* rows = (uint32_t*)(smem + 64);                           // [kComposeStages][W]
+    const int kComposeStages = prm.stages;
+    uint64_t* bars = (uint64_t*)smem;                                  // [stages]
+    uint32_t* rows = (uint32_t*)(smem + 64);                           // [stages][W]
     int* pre = (int*)(rows + (size_t)kComposeStages * W);              // [W + 1] feasible nodes before word w
     unsigned short* val = (unsigned short*)(pre + W + 1 + ((W + 1) & 1)); // [N] the distinct reachable start indices, in cyclic order
-    unsigned short* aux = val + kComposeMaxNodes;                      // [N] new values / merged values
-    unsigned short* idx = aux + kComposeMaxNodes;                      // [N] slot → merged slot
-    unsigned short* grp = idx + kComposeMaxNodes;                      // [T_q] initial slot → current slot
+    unsigned short* aux = val + N;                                     // [N] new values / merged values
+    unsigned short* idx = prm.g_idx ? prm.g_idx + (size_t)blockIdx.x * (size_t)N : aux + N; // [N] slot → merged slot
+    unsigned short* grp = prm.g_grp ? prm.g_grp + (size_t)blockIdx.x * (size_t)N : idx + N; // [T_q] initial slot → current slot
     __shared__ int s_warp[kComposeThreads / 32];
     __shared__ int s_m, s_T;
     const uint32_t row_bytes = (uint32_t)(W * 4);
@@ -472,7 +477,9 @@ static bool compose_applies(i64 n_nodes, i64 n_pods) {
 int64_t sample_scratch_bytes(int64_t n_nodes, int64_t n_pods) {
     if (!compose_applies(n_nodes, n_pods)) return 0;
     const i64 nb = (n_pods + kBlockPods - 1) / kBlockPods;
-    return (i64)sizeof(unsigned short) * nb * ((n_nodes + 7) & ~7ll) + (i64)sizeof(int) * 3 * (nb + 8);
+    const i64 n8 = (n_nodes + 7) & ~7ll;
+    const i64 tables = n_nodes > kComposeSmallNodes ? 3 : 1; // out, and for a long node table the two merge arrays
+    return (i64)sizeof(unsigned short) * nb * n8 * tables + (i64)sizeof(int) * 3 * (nb + 8);
 }
 
 int sample_launch_count(int64_t n_nodes, int64_t n_pods, bool have_scratch) { return have_scratch && compose_applies(n_nodes, n_pods) ? 5 : 3; }
@@ -489,11 +496,15 @@ cudaError_t launch_sampling(const SampleParams& sp, void* stream_) {
         ComposeParams cp;
         cp.bitmap = sp.bitmap, cp.W = sp.words_per_row, cp.n_nodes = n8, cp.n_pods = sp.n_pods, cp.K = sp.k;
         cp.out = (unsigned short*)sp.scratch;
-        cp.blk_q = (int*)((char*)sp.scratch + sizeof(unsigned short) * nb * n8);
+        const bool big = sp.n_nodes > kComposeSmallNodes;
+        cp.g_idx = big ? cp.out + (size_t)nb * (size_t)n8 : nullptr;
+        cp.g_grp = big ? cp.g_idx + (size_t)nb * (size_t)n8 : nullptr;
+        cp.stages = big ? 2 : kComposeStagesMax;
+        cp.blk_q = (int*)((char*)sp.scratch + sizeof(unsigned short) * nb * n8 * (big ? 3 : 1));
         cp.blk_T = cp.blk_q + (nb + 8);
         int* starts = cp.blk_T + (nb + 8);
         const size_t W = (size_t)sp.words_per_row;
-        const size_t csmem = 64 + (size_t)kComposeStages * W * 4 + ((W + 2) & ~(size_t)1) * 4 + 4 * (size_t)kComposeMaxNodes * 2;
+        const size_t csmem = 64 + (size_t)cp.stages * W * 4 + ((W + 2) & ~(size_t)1) * 4 + (big ? 2 : 4) * (size_t)n8 * 2;
         ce = cudaFuncSetAttribute(sample_compose, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem);
         if (ce != cudaSuccess) return ce;
         sample_compose<<<(unsigned)nb, kComposeThreads, csmem, stream>>>(cp);

@@ -78,10 +78,11 @@ def test_sampling_is_a_chain_over_batches(gpu_ok, oracle):
     (2, 5000, 3000, 10, 4999, {}),
     (1, 2100, 2500, 0, 0, {}),
     (2, 3000, 4100, 5, 1, dict(pm_nongpu_nodes=700, pm_quirk_nodes=100)),   # many pods with fewer than K feasible nodes: their walk leaves the index alone
-    (2, 16384, 1100, 3, 16000, {}),                                         # the largest table the composed walk takes
+    (2, 16384, 1100, 3, 16000, {}),                                         # the largest table whose merge arrays fit in shared memory
+    (2, 21000, 1300, 2, 20999, {}),                                         # beyond: they live in global scratch
 ])
 def test_long_batches_walk_in_blocks_and_land_where_the_chain_does(gpu_ok, oracle, cfg_id, n_nodes, n_pods, pct, start, kw):
-    """1 024 pods or more on up to 16 384 nodes: the walk is composed per block of 256 pods (sample_compose), the blocks are hopped
+    """1 024 pods or more on up to 65 528 nodes: the walk is composed per block of 256 pods (sample_compose), the blocks are hopped
     over (sample_block_starts) and walked at once (sample_chain). Same kept sets, processed counts and final index as the
     oracle's one-pod-after-the-other walk, and as the serial kernel (FGS_SAMPLE_SERIAL=1)."""
     s = fgs.config_synth(cfg_id, n_nodes=n_nodes, n_pending=n_pods, pm_invalid_nodes=5, **kw)
