@@ -421,7 +421,8 @@ extern "C" void fgs_destroy(fgs_engine* eh) {
     if (!eh) return;
     Engine* e = (Engine*)eh;
     cudaSetDevice(e->device);
-    cudaStreamSynchronize(e->stream);
+    for (cudaStream_t st : {e->stream, e->front_stream, e->copy_stream, e->d2h_stream, e->merge_stream})
+        if (st || st == e->stream) cudaStreamSynchronize(st); // batches submitted and never collected: let their work and copies end
     e->trace_dump();
     if (e->trace_epoch) cudaEventDestroy(e->trace_epoch);
     e->free_all();

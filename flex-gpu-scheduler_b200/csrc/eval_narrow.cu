@@ -392,7 +392,7 @@ __host__ __device__ inline SmemE smem_emit(bool fused) {
 // warp in eight working. Here the warps whose nodes lie beyond the table take a share of the pods instead: with A = 1, 2
 // or 4 node groups in range, warp w works on node group w mod A and on every (8/A)-th pod.
 template <uint32_t SPEC, bool FUSED, bool TAIL = false>
-__global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant__ NarrowParams prm) {
+__global__ void __launch_bounds__(kThreads, (TAIL || ((SPEC & SP_SC_ALLOC) && (SPEC & SP_SC_FIT))) ? 2 : 3) emit_narrow(const __grid_constant__ NarrowParams prm) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr bool kFlex = SPEC & SP_SC_FLEX, kFit = SPEC & SP_SC_FIT, kAlloc = SPEC & SP_SC_ALLOC, kMost = SPEC & SP_FIT_MOST;
     static_assert(!(FUSED && kAlloc), "the fused pass has no Allocatable hi/lo (they would need the feasible set first)");
@@ -557,8 +557,10 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
             xc[j] = C(NN_X_C);
             capm[j] = C(NN_CAP_M);
             xm[j] = C(NN_X_M);
-            x200c[j] = 200u * (uint32_t)xc[j];
-            x200m[j] = 200u * (uint32_t)xm[j];
+            // Least: a request above what is left scores 0 (least_allocated.go:48-55): the dividend is 200·x − min(200·x, 200·nz), and
+            // x < 0 ("everything exceeds it") is kept as x = 0 for that purpose
+            x200c[j] = (!kMost && xc[j] < 0) ? 0u : 200u * (uint32_t)xc[j];
+            x200m[j] = (!kMost && xm[j] < 0) ? 0u : 200u * (uint32_t)xm[j];
             magc[j] = (uint32_t)C(NN_MAG_C);
             magm[j] = (uint32_t)C(NN_MAG_M);
             const int shs = C(NN_MAG_SH);
@@ -580,6 +582,11 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     asm volatile("" : "+r"(inr[0]), "+r"(inr[1]), "+r"(inr[2]), "+r"(inr[3]));
     asm volatile("" : "+r"(nh[0]), "+r"(nh[1]), "+r"(nh[2]), "+r"(nh[3])); // opaque: one register per node instead of rebuilding it per pod
 
+    const int c100flex = 100 * prm.w_flex;
+    if (kFlex && !FUSED) { // the doubled dividends stay in registers (the compiler would rather rebuild them from the scores per pod)
+        asm volatile("" : "+r"(m200[0]), "+r"(m200[1]), "+r"(m200[2]), "+r"(m200[3]));
+        asm volatile("" : "+r"(g200[0]), "+r"(g200[1]), "+r"(g200[2]), "+r"(g200[3]));
+    }
     uint32_t lanebit = 1u << lane;
     asm volatile("" : "+r"(lanebit)); // opaque: keeps the feasibility test a single LOP3 with predicate output
     (void)flags_or;
@@ -589,6 +596,9 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
     // last 1 024 columns) has no score to write and no key to offer: it leaves zeros in its column of the per-warp keys once
     // and sits the pod loops out, so that the tail tile costs an eighth of the issue slots of a full one.
     const bool warp_active = FUSED || __any_sync(0xffffffffu, inr[0] | inr[1] | inr[2] | inr[3]);
+    // a negative MemScore (over-committed device) is rare: warps without one run the MemScore body without the sign handling
+    bool warp_neg = false;
+    if (kFlex) warp_neg = __any_sync(0xffffffffu, mneg[0] | mneg[1] | mneg[2] | mneg[3]);
     if (!warp_active || TAIL) // (TAIL: the pods this warp skips keep the zero)
         for (int i = lane; i < 2 * kTileP; i += 32) ((uint32_t*)(smem + L.wkey))[i * kWarps + warp] = 0u;
     if (tid < kTileP) derive(0);
@@ -667,29 +677,28 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
             // instead of per-node selects. KS = 0: the FlexGPU term is the constant 100 (no limit, or max == 0);
             // 1: GPUScore (a gpu limit wins over a memory limit, flex_gpu.go:157-159); 2: MemScore.
             auto pod_body = [&](auto KSEL) {
-                constexpr int KS = decltype(KSEL)::value;
+                constexpr int KS = decltype(KSEL)::value & 3;
+                constexpr bool kSigned = (decltype(KSEL)::value & 4) != 0; // KS == 2 only: some node of this warp has a negative MemScore
                 int tot[kNPTe];
                 uint32_t key = 0;
 #pragma unroll
                 for (int j = 0; j < kNPTe; ++j) {
                     int t = 0;
                     if (kFlex) { // FlexGPU.Score + DefaultNormalizeScore(reverse) (flex_gpu.go:142-176, normalize_score.go:26-54)
-                        int v = 100;
+                        // (100 ∓ q) · w as 100·w ∓ q·w: one multiply-add per node
+                        t = c100flex;
                         if (KS == 1) {
-                            v = 100 - qmagic(g200[j], q3.x, (int)q3.z);
+                            t -= qmagic(g200[j], q3.x, (int)q3.z) * prm.w_flex;
                         } else if (KS == 2) { // magnitude and sign: Go's '/' truncates toward zero
-                            const int q = qmagic(m200[j], q3.x, (int)q3.z);
-                            v = mneg[j] ? 100 + q : 100 - q;
+                            const int qw = qmagic(m200[j], q3.x, (int)q3.z) * prm.w_flex;
+                            t = (kSigned && mneg[j]) ? t + qw : t - qw;
                         }
-                        t += v * prm.w_flex;
                     }
                     if (kFit) { // Least/MostAllocated over cpu and memory, non-zero requests (least_allocated.go:29-57, most_allocated.go:29-61)
                         int sc, sm;
                         if (!kMost) {
-                            sc = qmagic(x200c[j] - (uint32_t)q2.z, magc[j], shc[j]);
-                            sm = qmagic(x200m[j] - (uint32_t)q2.w, magm[j], shm[j]);
-                            sc = q2.x > xc[j] ? 0 : sc; // requested > capacity → 0
-                            sm = q2.y > xm[j] ? 0 : sm;
+                            sc = qmagic(x200c[j] - min(x200c[j], (uint32_t)q2.z), magc[j], shc[j]); // requested > capacity → 0
+                            sm = qmagic(x200m[j] - min(x200m[j], (uint32_t)q2.w), magm[j], shm[j]);
                         } else {
                             sc = qmagic(x200c[j] + (uint32_t)q2.z, magc[j], shc[j]);
                             sm = qmagic(x200m[j] + (uint32_t)q2.w, magm[j], shm[j]);
@@ -731,8 +740,10 @@ __global__ void __launch_bounds__(kThreads, 2) emit_narrow(const __grid_constant
                 if (lane == 0) wkey[jp * kWarps + warp] = key;
             };
             const int ks = (kFlex && q4.x != 0) ? ((kind & 1) ? 1 : (kind == 2 ? 2 : 0)) : 0;
-            if (ks == 2) pod_body(std::integral_constant<int, 2>{});
-            else if (ks == 1) pod_body(std::integral_constant<int, 1>{});
+            if (ks == 2) {
+                if (warp_neg) pod_body(std::integral_constant<int, 6>{});
+                else pod_body(std::integral_constant<int, 2>{});
+            } else if (ks == 1) pod_body(std::integral_constant<int, 1>{});
             else pod_body(std::integral_constant<int, 0>{});
         }
         if (tid < kTileP && it + 1 < n_tiles) derive(it + 1);
