@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(kThreads, (TAIL || ((SPEC & SP_SC_ALLOC) && (S
         if (fmx < 0) fmx = 0; // maxCount starts at 0 (normalize_score.go:27)
         if (u.kind == 2) fmx >>= prm.sh.s[DIM_FM];
         u.fmax = (int)fmx;
-        u.fmag = narrow_magic((uint32_t)u.fmax, &u.fsh);
+        u.fmag = narrow_magic_fast((uint32_t)u.fmax, &u.fsh);
         u.count = (int)raw64[3 * kTileP + tid];
         u.alo = 0;
         u.arange32 = 0;
@@ -472,7 +472,7 @@ __global__ void __launch_bounds__(kThreads, (TAIL || ((SPEC & SP_SC_ALLOC) && (S
             u.alo = lo;
             if (range >= 0 && range < (1 << 24)) {
                 u.arange32 = (int)range;
-                u.amag = narrow_magic((uint32_t)range, &u.ash);
+                u.amag = narrow_magic_fast((uint32_t)range, &u.ash);
             } else { // the exact 64-bit path: the two fields carry the reciprocal of the range (alloc_div100)
                 u.arange32 = -1;
                 const u64 m = alloc_recip(range);

@@ -863,7 +863,7 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
     if (kind == 2) fmx >>= prm.sh[DIM_FM];
     const int fmax = (int)fmx;
     int fsh = 0, ash = 0;
-    const uint32_t fmag = narrow_magic((uint32_t)fmax, &fsh);
+    const uint32_t fmag = narrow_magic_fast((uint32_t)fmax, &fsh);
     i64 alo = 0, arange64 = 0;
     int arange32 = 0;
     uint32_t amag = 0;
@@ -874,7 +874,7 @@ __global__ void __launch_bounds__(kSmallThreads) small_cycle(const __grid_consta
         alo = lo;
         if (arange64 >= 0 && arange64 < (1 << 24)) {
             arange32 = (int)arange64;
-            amag = narrow_magic((uint32_t)arange64, &ash);
+            amag = narrow_magic_fast((uint32_t)arange64, &ash);
         } else {
             arange32 = -1;
             arecip = alloc_recip(arange64);

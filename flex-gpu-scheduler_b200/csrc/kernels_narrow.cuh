@@ -47,6 +47,32 @@ inline uint32_t narrow_magic(uint32_t d, int* l) {
     return (uint32_t)((1ull << (31 + lg)) / d + 1ull);
 }
 
+// The same pair without the search loop and the 64-bit division — it sits on every emit CTA's start-up path, where 64 threads
+// derive the pods' multipliers while the other warps wait: ceil(log2 d) from the leading zeros, and floor(2^(31+l) / d) from a
+// double quotient (within one of it, the quotient being below 2^32) settled by the exact remainder. Equal to narrow_magic
+// for every d (tests/cpp/magic_test.cpp: all d up to 2^24 and random ones up to 2^31).
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline uint32_t narrow_magic_fast(uint32_t d, int* l) {
+    if (d == 0) {
+        *l = 0;
+        return 0;
+    }
+#if defined(__CUDA_ARCH__)
+    const int lg = d == 1 ? 0 : 32 - __clz((int)(d - 1));
+#else
+    const int lg = d == 1 ? 0 : 32 - __builtin_clz(d - 1);
+#endif
+    *l = lg;
+    const double q = (double)(1ull << (31 + lg)) / (double)d; // in [2^31, 2^32)
+    uint32_t m = (uint32_t)q;
+    const long long r = (long long)((1ull << (31 + lg)) - (unsigned long long)m * (unsigned long long)d);
+    if (r < 0) --m;
+    else if (r >= (long long)d) ++m;
+    return m + 1u;
+}
+
 // Allocatable.NormalizeScore outside the int32 range (allocatable.go:160: score = (raw − lowest) · 100 / (highest − lowest)):
 // (x · 100) / range with Go's int64 semantics — the product wraps, the quotient truncates toward zero. A 64-bit division is a
 // ~100-instruction subroutine and the divisor is one per POD, so the pod carries m = floor((2^64 − 1) / range) (range > 0;

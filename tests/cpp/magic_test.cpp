@@ -43,6 +43,25 @@ int main() {
     for (int k = 0; k < 200000; ++k) divisor((uint32_t)(rng() % 0x7fffffffu) + 1, rng); // random divisors up to 2^31 - 1
     int l = 7;
     if (fgs::narrow_magic(0, &l) != 0 || l != 0) ++bad; // capacity 0 → quotient 0 (least_allocated.go:48-50)
+    // narrow_magic_fast == narrow_magic
+    long long mchecks = 0;
+    auto mcheck = [&](uint32_t d) {
+        int l0 = -1, l1 = -1;
+        const uint32_t m0 = fgs::narrow_magic(d, &l0), m1 = fgs::narrow_magic_fast(d, &l1);
+        ++mchecks;
+        if (m0 != m1 || l0 != l1) {
+            if (bad < 10) std::printf("narrow_magic_fast(%u): %u/%d != %u/%d\n", d, m1, l1, m0, l0);
+            ++bad;
+        }
+    };
+    for (uint32_t d = 0; d <= (1u << 24) + 16; ++d) mcheck(d);
+    for (int e = 24; e <= 31; ++e)
+        for (int o = -3; o <= 3; ++o) {
+            const int64_t d = ((int64_t)1 << e) + o;
+            if (d >= 1 && d < ((int64_t)1 << 31)) mcheck((uint32_t)d);
+        }
+    for (int k = 0; k < 2000000; ++k) mcheck((uint32_t)(rng() % 0x7fffffffu) + 1);
+    std::printf("%lld magic pairs compared\n", mchecks);
     // alloc_div100: (x * 100) / range as Go computes it (wrapping product, truncation toward zero), for every kind of input
     long long dchecks = 0;
     auto dcheck = [&](long long x, long long range) {
