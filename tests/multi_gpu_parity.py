@@ -133,6 +133,28 @@ def check_mixed_shift_batches(fgs, D, oracle, torch, dist, world, rank, local):
                 same(eng.collect(), refs[q.pop(0)])
         while q:
             same(eng.collect(), refs[q.pop(0)])
+    # node rows change on every shard (row patches on the device), then the same batches again
+    nodes = M.cluster(N)
+    spare = M.cluster(N, seed=77)
+    rnd = np.random.default_rng(5)
+    for rounds in range(3):
+        changed = np.sort(rnd.choice(N, size=[1, 6, 40][rounds], replace=False))
+        for i in changed:
+            nodes[i], spare[i] = spare[i], nodes[i]
+        snap2 = B.build_snapshot(nodes)
+        mine = changed[(changed >= n0) & (changed < n1)].astype(np.int64)
+        if len(mine):
+            eng.update_nodes(fgs.Packer(2).node_rows(snap2.ptr, mine), mine - n0)
+        refs2 = {k: oracle.evaluate(snap2.ptr, v.ptr, cfg, workers=2) for k, v in sets.items()}
+        q = []
+        for k in "BACB":
+            eng.submit(tabs[k])
+            q.append(k)
+            if len(q) == depth:
+                same(eng.collect(), refs2[q.pop(0)])
+        while q:
+            same(eng.collect(), refs2[q.pop(0)])
+        same(eng.evaluate(tabs["A"]), refs2["A"])
     eng.peer_status()
     px.close()
     eng.close()
