@@ -1458,14 +1458,17 @@ extern "C" int fgs_pass_emit(fgs_engine* eh, const fgs_eval_opts* opts) {
 
 // the compact rows finalize_pods wrote (16 bytes per pod) → the caller's arrays
 static void unpack_results(const int64_t* h, int64_t P, int64_t pp, fgs_results* out) {
-    for (int64_t p = 0; p < P; ++p) {
-        const uint64_t w = (uint64_t)h[p];
-        const uint32_t lo = (uint32_t)w;
-        if (out->feasible_count) out->feasible_count[p] = (int32_t)(lo & 0x0fffffffu);
-        if (out->pod_err) out->pod_err[p] = lo >> 28;
-        if (out->selected_node) out->selected_node[p] = (int32_t)(uint32_t)(w >> 32);
-        if (out->selected_score) out->selected_score[p] = h[pp + p];
-    }
+    // one plain loop per output array (no test inside: they vectorise); 16 bytes per pod in, 20 out
+    int32_t* cnt = out->feasible_count;
+    uint32_t* err = out->pod_err;
+    int32_t* sel = out->selected_node;
+    if (cnt)
+        for (int64_t p = 0; p < P; ++p) cnt[p] = (int32_t)((uint32_t)(uint64_t)h[p] & 0x0fffffffu);
+    if (err)
+        for (int64_t p = 0; p < P; ++p) err[p] = (uint32_t)(uint64_t)h[p] >> 28;
+    if (sel)
+        for (int64_t p = 0; p < P; ++p) sel[p] = (int32_t)(uint32_t)((uint64_t)h[p] >> 32);
+    if (out->selected_score) std::memcpy(out->selected_score, h + pp, sizeof(int64_t) * (size_t)P);
 }
 
 extern "C" int fgs_fetch_results(fgs_engine* eh, fgs_results* out) {
