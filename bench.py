@@ -673,7 +673,10 @@ def run_ours(args):
                          "traffic_source": traffic_src, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": emit_bytes // nb, "launches_per_step": nb,
                          "path_frac": (path_bytes / ((ms / args.steps) * 1e-3) / 1e9) / peak,
-                         "path_frac_note": "SURVEY §8(d) B_alg of the whole step / ms_per_step / peak"},
+                         "path_frac_note": "SURVEY §8(d) B_alg of the whole step / ms_per_step / peak",
+                         "peak_note": "the peak is the copy figure (read + write); a pure write stream reaches 7.5 TB/s on this GPU and the emit "
+                                      "pass's own store pattern without its arithmetic 7.16 TB/s (profiles/r02_write_peak.json, "
+                                      "tools/write_pattern.cu, DESIGN.md §14)"},
             "e2e": ({"value": e2e["pipe"]["value"], "unit": UNIT, "h2d_bytes_per_step": pd_cols * P * 8, "d2h_bytes_per_step": 2 * p_pad * 8,
                      "steps": e2e["pipe"]["steps"],
                      "api": "fgs_submit + fgs_collect, %d batches in flight: pinned host pod tables in (fgs_packer_pin: DMA straight from the "
